@@ -1,0 +1,465 @@
+// noracle_math.h — CPU restatement of the Nori hot-path arithmetic (TEST INFRASTRUCTURE).
+//
+// This header is part of the parity oracle. It is never linked into the product
+// (libnori_b200.so); only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline
+// legs may use anything under oracle/.
+//
+// Two kinds of functions live here (citations are relative to /root/reference):
+//   REF   — the reference ships an implementation; the restatement follows it operation
+//           for operation (including Eigen's 3-vector reduction order x0+(x1+x2),
+//           ext/eigen/Eigen/src/Core/Redux.h:94-103) and is pinned bit-exactly against the
+//           compiled reference (oracle/_ref, tests/test_oracle_pins.py).
+//   STUB  — the reference declares the function but throws / leaves it empty
+//           (SURVEY.md §0 F3-F5); the restatement follows the course definition and is
+//           pinned by the reference's own chi2/t-test fixtures (scenes/pa5/tests, pa4/tests).
+//
+// Plain C++11, no dependencies, no FMA contraction (build with -ffp-contract=off, no
+// -march=native, no -ffast-math: the reference's CMake sets none of them).
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstddef>
+#include <cstring>
+#include <algorithm>
+#include <limits>
+#include <vector>
+
+namespace noracle {
+
+static const float kEpsilon  = 1e-4f;                       // include/nori/common.h:50
+static const float kPi       = 3.14159265358979323846f;     // common.h:55
+static const float kInvPi    = 0.31830988618379067154f;     // common.h:56
+static const float kInf      = std::numeric_limits<float>::infinity();
+
+// ---------------------------------------------------------------------------------------
+// Small vector types (Eigen-order arithmetic)
+// ---------------------------------------------------------------------------------------
+struct V2 { float x, y; };
+struct V3 {
+    float x, y, z;
+    float operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+};
+struct C3 { float r, g, b; };   // Color3f
+
+inline V3 mk(float x, float y, float z) { V3 v = {x, y, z}; return v; }
+inline C3 mkc(float r, float g, float b) { C3 c = {r, g, b}; return c; }
+inline V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline V3 operator-(V3 a)       { return mk(-a.x, -a.y, -a.z); }
+inline V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+inline V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+inline V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+inline C3 operator+(C3 a, C3 b) { return mkc(a.r + b.r, a.g + b.g, a.b + b.b); }
+inline C3 operator*(C3 a, C3 b) { return mkc(a.r * b.r, a.g * b.g, a.b * b.b); }
+inline C3 operator*(C3 a, float s) { return mkc(a.r * s, a.g * s, a.b * s); }
+inline C3 operator/(C3 a, float s) { return mkc(a.r / s, a.g / s, a.b / s); }
+inline bool isZero(C3 c) { return c.r == 0.0f && c.g == 0.0f && c.b == 0.0f; }
+inline float maxCoeff(C3 c) { return std::max(c.r, std::max(c.g, c.b)); }
+
+/// Eigen fixed-size 3-vector reduction: x0 + (x1 + x2)  (Redux.h:94-103)
+inline float dot(V3 a, V3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
+/// Eigen cross (Geometry/OrthoMethods.h:43-47)
+inline V3 cross(V3 a, V3 b) {
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+inline float squaredNorm(V3 a) { return dot(a, a); }
+inline float norm(V3 a) { return std::sqrt(squaredNorm(a)); }
+/// Eigen normalized(): divide by sqrt(squaredNorm) when it is > 0 (Core/Dot.h:123-133)
+inline V3 normalized(V3 a) {
+    float z = squaredNorm(a);
+    if (z > 0.0f) return a / std::sqrt(z);
+    return a;
+}
+
+// ---------------------------------------------------------------------------------------
+// REF: PCG32 (ext/pcg32/pcg32.h:40-161) and the `independent` sampler (src/independent.cpp)
+// ---------------------------------------------------------------------------------------
+struct Pcg32 {
+    uint64_t state, inc;
+    Pcg32() : state(0x853c49e6748fea9bULL), inc(0xda3e39cb94b95bdbULL) {}
+    Pcg32(uint64_t initstate, uint64_t initseq) { seed(initstate, initseq); }
+
+    void seed(uint64_t initstate, uint64_t initseq) {   // pcg32.h:55-61
+        state = 0u;
+        inc = (initseq << 1u) | 1u;
+        nextUInt();
+        state += initstate;
+        nextUInt();
+    }
+    uint32_t nextUInt() {                                // pcg32.h:64-70
+        uint64_t old = state;
+        state = old * 0x5851f42d4c957f2dULL + inc;
+        uint32_t xorshifted = (uint32_t) (((old >> 18u) ^ old) >> 27u);
+        uint32_t rot = (uint32_t) (old >> 59u);
+        return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+    }
+    float nextFloat() {                                  // pcg32.h:104-112
+        uint32_t u = (nextUInt() >> 9) | 0x3f800000u;
+        float f; std::memcpy(&f, &u, 4);
+        return f - 1.0f;
+    }
+    void advance(int64_t delta_) {                       // pcg32.h:140-161
+        uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+        uint64_t delta = (uint64_t) delta_;
+        while (delta > 0) {
+            if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+            cur_plus = (cur_mult + 1) * cur_plus;
+            cur_mult *= cur_mult;
+            delta /= 2;
+        }
+        state = acc_mult * state + acc_plus;
+    }
+};
+
+/// Sampler contract (include/nori/sampler.h:68-98). next2D draws x first, then y: that is
+/// what g++ emits for `Point2f(m_random.nextFloat(), m_random.nextFloat())`
+/// (src/independent.cpp:62-67) — pinned against the compiled reference in tests.
+struct Sampler {
+    Pcg32 rng;
+    float next1D() { return rng.nextFloat(); }
+    V2 next2D() { V2 r; r.x = rng.nextFloat(); r.y = rng.nextFloat(); return r; }
+};
+
+// ---------------------------------------------------------------------------------------
+// REF: rays, frames, Fresnel (include/nori/ray.h, frame.h, src/common.cpp)
+// ---------------------------------------------------------------------------------------
+struct Ray {
+    V3 o, d, dRcp;
+    float mint, maxt;
+    Ray() : mint(kEpsilon), maxt(kInf) {}
+    Ray(V3 o_, V3 d_, float mint_ = kEpsilon, float maxt_ = kInf)   // ray.h:49-62
+        : o(o_), d(d_), mint(mint_), maxt(maxt_) { update(); }
+    void update() { dRcp = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z); }   // ray.h:75-77
+};
+
+/// src/common.cpp:260-269
+inline void coordinateSystem(V3 a, V3 &b, V3 &c) {
+    if (std::abs(a.x) > std::abs(a.y)) {
+        float invLen = 1.0f / std::sqrt(a.x * a.x + a.z * a.z);
+        c = mk(a.z * invLen, 0.0f, -a.x * invLen);
+    } else {
+        float invLen = 1.0f / std::sqrt(a.y * a.y + a.z * a.z);
+        c = mk(0.0f, a.z * invLen, -a.y * invLen);
+    }
+    b = cross(c, a);
+}
+
+/// include/nori/frame.h:32-62
+struct Frame {
+    V3 s, t, n;
+    Frame() {}
+    explicit Frame(V3 n_) : n(n_) { coordinateSystem(n, s, t); }
+    V3 toLocal(V3 v) const { return mk(dot(v, s), dot(v, t), dot(v, n)); }
+    /// s*v.x + t*v.y + n*v.z, evaluated left to right (frame.h:60-62)
+    V3 toWorld(V3 v) const { return (s * v.x + t * v.y) + n * v.z; }
+};
+
+/// src/common.cpp:271-300
+inline float fresnel(float cosThetaI, float extIOR, float intIOR) {
+    float etaI = extIOR, etaT = intIOR;
+    if (extIOR == intIOR) return 0.0f;
+    if (cosThetaI < 0.0f) { std::swap(etaI, etaT); cosThetaI = -cosThetaI; }
+    float eta = etaI / etaT, sinThetaTSqr = eta * eta * (1 - cosThetaI * cosThetaI);
+    if (sinThetaTSqr > 1.0f) return 1.0f;
+    float cosThetaT = std::sqrt(1.0f - sinThetaTSqr);
+    float Rs = (etaI * cosThetaI - etaT * cosThetaT) / (etaI * cosThetaI + etaT * cosThetaT);
+    float Rp = (etaT * cosThetaI - etaI * cosThetaT) / (etaT * cosThetaI + etaI * cosThetaT);
+    return (Rs * Rs + Rp * Rp) / 2.0f;
+}
+
+/// src/common.cpp:210-221
+inline bool isValid(C3 c) {
+    const float v[3] = {c.r, c.g, c.b};
+    for (int i = 0; i < 3; ++i) if (v[i] < 0 || !std::isfinite(v[i])) return false;
+    return true;
+}
+inline float luminance(C3 c) { return c.r * 0.212671f + c.g * 0.715160f + c.b * 0.072169f; }
+
+// ---------------------------------------------------------------------------------------
+// REF: Möller–Trumbore (src/mesh.cpp:51-88) and the slab test (include/nori/bbox.h:335-362)
+// ---------------------------------------------------------------------------------------
+inline bool rayTriangle(V3 p0, V3 p1, V3 p2, const Ray &ray, float &u, float &v, float &t) {
+    V3 edge1 = p1 - p0, edge2 = p2 - p0;
+    V3 pvec = cross(ray.d, edge2);
+    float det = dot(edge1, pvec);
+    if (det > -1e-8f && det < 1e-8f) return false;
+    float inv_det = 1.0f / det;
+    V3 tvec = ray.o - p0;
+    u = dot(tvec, pvec) * inv_det;
+    if (u < 0.0 || u > 1.0) return false;
+    V3 qvec = cross(tvec, edge1);
+    v = dot(ray.d, qvec) * inv_det;
+    if (v < 0.0 || u + v > 1.0) return false;
+    t = dot(edge2, qvec) * inv_det;
+    return t >= ray.mint && t <= ray.maxt;
+}
+
+struct BBox {
+    V3 min, max;
+    BBox() { reset(); }
+    void reset() { min = mk(kInf, kInf, kInf); max = mk(-kInf, -kInf, -kInf); }
+    void expandBy(V3 p) {
+        min = mk(std::min(min.x, p.x), std::min(min.y, p.y), std::min(min.z, p.z));
+        max = mk(std::max(max.x, p.x), std::max(max.y, p.y), std::max(max.z, p.z));
+    }
+    void expandBy(const BBox &b) { expandBy(b.min); expandBy(b.max); }
+    float surfaceArea() const {           // bbox.h:86-99 (3D: 2*(dx*dy + dy*dz + dz*dx))
+        V3 d = max - min;
+        return 2.0f * (d.x * d.y + d.y * d.z + d.z * d.x);
+    }
+    int largestAxis() const {             // bbox.h:311-320
+        V3 e = max - min;
+        if (e.x >= e.y && e.x >= e.z) return 0;
+        if (e.y >= e.x && e.y >= e.z) return 1;
+        return 2;
+    }
+    bool rayIntersect(const Ray &ray) const {   // bbox.h:335-362
+        float nearT = -kInf, farT = kInf;
+        for (int i = 0; i < 3; i++) {
+            float origin = ray.o[i], minVal = min[i], maxVal = max[i];
+            if (ray.d[i] == 0) {
+                if (origin < minVal || origin > maxVal) return false;
+            } else {
+                float t1 = (minVal - origin) * ray.dRcp[i];
+                float t2 = (maxVal - origin) * ray.dRcp[i];
+                if (t1 > t2) std::swap(t1, t2);
+                nearT = std::max(t1, nearT);
+                farT = std::min(t2, farT);
+                if (!(nearT <= farT)) return false;
+            }
+        }
+        return ray.mint <= farT && nearT <= ray.maxt;
+    }
+};
+
+// ---------------------------------------------------------------------------------------
+// REF: reconstruction filters (src/rfilter.cpp:28-120)
+// ---------------------------------------------------------------------------------------
+enum FilterType { kGaussian = 0, kMitchell = 1, kTent = 2, kBox = 3 };
+struct Filter {
+    int type; float radius, p0, p1;   // gaussian: p0 = stddev; mitchell: p0 = B, p1 = C
+    float eval(float x) const {
+        switch (type) {
+        case kGaussian: {
+            float alpha = -1.0f / (2.0f * p0 * p0);
+            return std::max(0.0f, std::exp(alpha * x * x) - std::exp(alpha * radius * radius));
+        }
+        case kMitchell: {
+            float B = p0, C = p1;
+            x = std::abs(2.0f * x / radius);
+            float x2 = x * x, x3 = x2 * x;
+            if (x < 1)
+                return 1.0f / 6.0f * ((12 - 9 * B - 6 * C) * x3 + (-18 + 12 * B + 6 * C) * x2 + (6 - 2 * B));
+            else if (x < 2)
+                return 1.0f / 6.0f * ((-B - 6 * C) * x3 + (6 * B + 30 * C) * x2 + (-12 * B - 48 * C) * x + (8 * B + 24 * C));
+            return 0.0f;
+        }
+        case kTent: return std::max(0.0f, 1.0f - std::abs(x));
+        default:    return 1.0f;
+        }
+    }
+};
+inline Filter gaussianFilter(float radius = 2.0f, float stddev = 0.5f) { Filter f = {kGaussian, radius, stddev, 0}; return f; }
+inline Filter mitchellFilter(float radius = 2.0f, float B = 1.0f / 3.0f, float C = 1.0f / 3.0f) { Filter f = {kMitchell, radius, B, C}; return f; }
+inline Filter tentFilter() { Filter f = {kTent, 1.0f, 0, 0}; return f; }
+inline Filter boxFilter() { Filter f = {kBox, 0.5f, 0, 0}; return f; }
+
+// ---------------------------------------------------------------------------------------
+// STUB S1: warps (include/nori/warp.h:30-69; src/warp.cpp:33-79 all throw)
+// ---------------------------------------------------------------------------------------
+inline float tent1(float xi) { return xi < 0.5f ? std::sqrt(2.0f * xi) - 1.0f : 1.0f - std::sqrt(2.0f - 2.0f * xi); }
+inline V2 squareToTent(V2 s) { V2 r = {tent1(s.x), tent1(s.y)}; return r; }
+inline float squareToTentPdf(V2 p) {
+    float ax = std::abs(p.x), ay = std::abs(p.y);
+    return (ax <= 1.0f && ay <= 1.0f) ? (1.0f - ax) * (1.0f - ay) : 0.0f;
+}
+inline V2 squareToUniformDisk(V2 s) {
+    float r = std::sqrt(s.x), phi = 2.0f * kPi * s.y;
+    V2 p = {r * std::cos(phi), r * std::sin(phi)};
+    return p;
+}
+inline float squareToUniformDiskPdf(V2 p) { return (p.x * p.x + p.y * p.y <= 1.0f) ? kInvPi : 0.0f; }
+inline V3 squareToUniformSphere(V2 s) {
+    float z = 1.0f - 2.0f * s.x, r = std::sqrt(std::max(0.0f, 1.0f - z * z)), phi = 2.0f * kPi * s.y;
+    return mk(r * std::cos(phi), r * std::sin(phi), z);
+}
+inline float squareToUniformSpherePdf(V3) { return 0.25f * kInvPi; }
+inline V3 squareToUniformHemisphere(V2 s) {
+    float z = s.x, r = std::sqrt(std::max(0.0f, 1.0f - z * z)), phi = 2.0f * kPi * s.y;
+    return mk(r * std::cos(phi), r * std::sin(phi), z);
+}
+inline float squareToUniformHemispherePdf(V3 v) { return v.z >= 0.0f ? 0.5f * kInvPi : 0.0f; }
+inline V3 squareToCosineHemisphere(V2 s) {
+    V2 d = squareToUniformDisk(s);
+    float z = std::sqrt(std::max(0.0f, 1.0f - d.x * d.x - d.y * d.y));
+    return mk(d.x, d.y, z);
+}
+inline float squareToCosineHemispherePdf(V3 v) { return v.z > 0.0f ? v.z * kInvPi : 0.0f; }
+/// Beckmann normal: phi = 2 pi xi1, tan^2(theta) = -alpha^2 ln(1 - xi2)
+inline V3 squareToBeckmann(V2 s, float alpha) {
+    float phi = 2.0f * kPi * s.x;
+    float tan2 = -alpha * alpha * std::log(1.0f - s.y);
+    float cosTheta = 1.0f / std::sqrt(1.0f + tan2);
+    float sinTheta = std::sqrt(std::max(0.0f, 1.0f - cosTheta * cosTheta));
+    return mk(sinTheta * std::cos(phi), sinTheta * std::sin(phi), cosTheta);
+}
+/// Beckmann D(m) * cos(theta_m)
+inline float squareToBeckmannPdf(V3 m, float alpha) {
+    if (m.z <= 0.0f) return 0.0f;
+    float c2 = m.z * m.z, tan2 = (1.0f - c2) / c2, a2 = alpha * alpha;
+    return std::exp(-tan2 / a2) / (kPi * a2 * c2 * m.z);
+}
+
+// ---------------------------------------------------------------------------------------
+// BSDFs (include/nori/bsdf.h:29-112). REF: diffuse, mirror. STUB S2/S3: microfacet, dielectric.
+// ---------------------------------------------------------------------------------------
+enum Measure { kUnknownMeasure = 0, kSolidAngle = 1, kDiscrete = 2 };   // common.h EMeasure
+enum BsdfType { kDiffuse = 0, kMirror = 1, kDielectric = 2, kMicrofacet = 3 };
+
+struct BsdfQuery { V3 wi, wo; float eta; int measure; };
+
+struct Bsdf {
+    int type;
+    C3 albedo;                 // diffuse albedo / microfacet kd
+    float alpha, intIOR, extIOR, ks;
+
+    bool isDiffuse() const { return type == kDiffuse || type == kMicrofacet; }
+
+    static float g1(V3 wv, V3 wh, float alpha) {
+        // chi+((wv.wh)/(wv.n)) * rational approximation of the Beckmann shadowing term
+        if (dot(wv, wh) / wv.z <= 0.0f) return 0.0f;
+        float c = wv.z, t2 = 1.0f - c * c;
+        if (t2 <= 0.0f) return 1.0f;
+        float tanTheta = std::sqrt(t2) / c;             // Frame::tanTheta (frame.h:82-87)
+        float b = 1.0f / (alpha * tanTheta);
+        if (b >= 1.6f) return 1.0f;
+        float b2 = b * b;
+        return (3.535f * b + 2.181f * b2) / (1.0f + 2.276f * b + 2.577f * b2);
+    }
+
+    C3 eval(const BsdfQuery &q) const {
+        switch (type) {
+        case kDiffuse:                                   // src/diffuse.cpp:35-45
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return mkc(0, 0, 0);
+            return albedo * kInvPi;
+        case kMicrofacet: {                              // S2
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return mkc(0, 0, 0);
+            V3 wh = normalized(q.wi + q.wo);
+            float D = squareToBeckmannPdf(wh, alpha) / wh.z;
+            float F = fresnel(dot(wh, q.wi), extIOR, intIOR);
+            float G = g1(q.wi, wh, alpha) * g1(q.wo, wh, alpha);
+            float spec = ks * D * F * G / (4.0f * q.wi.z * q.wo.z);
+            return albedo * kInvPi + mkc(spec, spec, spec);
+        }
+        default: return mkc(0, 0, 0);                    // mirror.cpp:31-34, dielectric.cpp:35-38
+        }
+    }
+
+    float pdf(const BsdfQuery &q) const {
+        switch (type) {
+        case kDiffuse:                                   // src/diffuse.cpp:48-62
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return 0.0f;
+            return kInvPi * q.wo.z;
+        case kMicrofacet: {
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return 0.0f;
+            V3 wh = normalized(q.wi + q.wo);
+            float jac = 1.0f / (4.0f * dot(wh, q.wo));
+            return ks * squareToBeckmannPdf(wh, alpha) * jac + (1.0f - ks) * q.wo.z * kInvPi;
+        }
+        default: return 0.0f;
+        }
+    }
+
+    /// Returns eval*cos/pdf; fills wo, measure, eta. Zero = failed sample.
+    C3 sample(BsdfQuery &q, V2 s) const {
+        switch (type) {
+        case kDiffuse:                                   // src/diffuse.cpp:65-83
+            if (q.wi.z <= 0) return mkc(0, 0, 0);
+            q.measure = kSolidAngle;
+            q.wo = squareToCosineHemisphere(s);
+            q.eta = 1.0f;
+            return albedo;
+        case kMirror:                                    // src/mirror.cpp:39-55
+            if (q.wi.z <= 0) return mkc(0, 0, 0);
+            q.wo = mk(-q.wi.x, -q.wi.y, q.wi.z);
+            q.measure = kDiscrete;
+            q.eta = 1.0f;
+            return mkc(1, 1, 1);
+        case kDielectric: {                              // S3 (convention: DESIGN.md "unpinned")
+            float cosThetaI = q.wi.z;
+            float F = fresnel(cosThetaI, extIOR, intIOR);
+            q.measure = kDiscrete;
+            if (s.x < F) {
+                q.wo = mk(-q.wi.x, -q.wi.y, q.wi.z);
+                q.eta = 1.0f;
+                return mkc(1, 1, 1);
+            }
+            bool entering = cosThetaI > 0.0f;
+            float eta = entering ? extIOR / intIOR : intIOR / extIOR;    // eta_i / eta_t
+            float cosThetaT = std::sqrt(std::max(0.0f, 1.0f - eta * eta * (1.0f - cosThetaI * cosThetaI)));
+            q.wo = mk(-eta * q.wi.x, -eta * q.wi.y, entering ? -cosThetaT : cosThetaT);
+            q.eta = entering ? intIOR / extIOR : extIOR / intIOR;
+            float w = eta * eta;                          // radiance scaling (eta_i/eta_t)^2
+            return mkc(w, w, w);
+        }
+        case kMicrofacet: {
+            if (q.wi.z <= 0) return mkc(0, 0, 0);
+            q.measure = kSolidAngle;
+            q.eta = 1.0f;
+            if (s.x < ks) {
+                V2 r = {s.x / ks, s.y};
+                V3 n = squareToBeckmann(r, alpha);
+                q.wo = n * (2.0f * dot(q.wi, n)) - q.wi;
+            } else {
+                V2 r = {(s.x - ks) / (1.0f - ks), s.y};
+                q.wo = squareToCosineHemisphere(r);
+            }
+            if (q.wo.z <= 0) return mkc(0, 0, 0);
+            float p = pdf(q);
+            if (!(p > 0.0f)) return mkc(0, 0, 0);
+            return eval(q) * q.wo.z / p;
+        }
+        }
+        return mkc(0, 0, 0);
+    }
+};
+inline Bsdf makeDiffuse(C3 albedo) { Bsdf b = {kDiffuse, albedo, 0, 0, 0, 0}; return b; }
+inline Bsdf makeMirror() { Bsdf b = {kMirror, mkc(0, 0, 0), 0, 0, 0, 0}; return b; }
+inline Bsdf makeDielectric(float intIOR, float extIOR) { Bsdf b = {kDielectric, mkc(0, 0, 0), 0, intIOR, extIOR, 0}; return b; }
+inline Bsdf makeMicrofacet(float alpha, float intIOR, float extIOR, C3 kd) {
+    Bsdf b = {kMicrofacet, kd, alpha, intIOR, extIOR, 1.0f - maxCoeff(kd)};   // microfacet.cpp:48
+    return b;
+}
+
+// ---------------------------------------------------------------------------------------
+// REF: DiscretePDF (include/nori/dpdf.h:33-160)
+// ---------------------------------------------------------------------------------------
+struct DiscretePdf {
+    std::vector<float> cdf;
+    float sum, normalization;
+    DiscretePdf() : sum(0), normalization(0) { cdf.push_back(0.0f); }
+    void clear() { cdf.clear(); cdf.push_back(0.0f); sum = normalization = 0; }
+    void append(float v) { cdf.push_back(cdf.back() + v); }        // dpdf.h:57-59
+    float normalize() {                                            // dpdf.h:94-108
+        sum = cdf.back();
+        if (sum > 0) {
+            normalization = 1.0f / sum;
+            for (size_t i = 1; i < cdf.size(); ++i) cdf[i] *= normalization;
+            cdf.back() = 1.0f;
+        } else normalization = 0.0f;
+        return sum;
+    }
+    size_t size() const { return cdf.size() - 1; }
+    size_t sample(float v) const {                                 // dpdf.h:118-123
+        std::ptrdiff_t e = std::lower_bound(cdf.begin(), cdf.end(), v) - cdf.begin();
+        size_t index = (size_t) std::max((std::ptrdiff_t) 0, e - 1);
+        return std::min(index, cdf.size() - 2);
+    }
+    size_t sampleReuse(float &v) const {                           // dpdf.h:151-156
+        size_t index = sample(v);
+        v = (v - cdf[index]) / (cdf[index + 1] - cdf[index]);
+        return index;
+    }
+};
+
+} // namespace noracle
