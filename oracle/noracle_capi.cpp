@@ -57,7 +57,11 @@ void noracle_scene_set_camera(void *s_, const float *s2c, const float *c2w, int 
 
 void noracle_scene_set_filter(void *s_, int type, float radius, float p0, float p1) {
     Filter f = {type, radius, p0, p1};
-    ((Scene *) s_)->filter = f;
+    ((Scene *) s_)->setFilter(f);
+}
+void noracle_scene_set_filter_table(void *s_, float radius, const float *table33) {
+    Scene *s = (Scene *) s_;
+    s->filterRadius = radius; std::memcpy(s->filterTable, table33, sizeof(s->filterTable));
 }
 
 void noracle_scene_set_integrator(void *s_, int type, int rrStart, float rrMax, int maxDepth,
@@ -203,8 +207,8 @@ int noracle_block_order(int W, int H, int bs, int *out, int cap) {
 }
 
 /// ImageBlock::put over n samples in order into one full-frame block; rgbw is (H+2b)x(W+2b)x4.
-uint64_t noracle_splat(int W, int H, int ftype, float radius, float p0, float p1, int n, const float *pos, const float *rgb, float *rgbw) {
-    Filter f = {ftype, radius, p0, p1}; FilterTable ft; ft.init(f);
+uint64_t noracle_splat(int W, int H, float radius, const float *table33, int n, const float *pos, const float *rgb, float *rgbw) {
+    FilterTable ft; ft.init(radius, table33);
     ImageBlock b; b.init(W, H, ft);
     for (int i = 0; i < n; ++i) { V2 p = {pos[2 * i], pos[2 * i + 1]}; b.put(p, mkc(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2])); }
     std::memcpy(rgbw, b.data.data(), b.data.size() * 4);
@@ -234,7 +238,7 @@ void noracle_sample_radiance(void *s_, int n, const uint32_t *pixel, const uint3
 /// rgbw: (H+2b) x (W+2b) x 4 == ImageBlock::data(). stats: {closest, shadow, segments, dropped}.
 void noracle_render(void *s_, int mode, uint32_t sampleFirst, uint32_t sampleLast, int threads, float *rgbw, uint64_t *stats) {
     const Scene *s = (const Scene *) s_;
-    FilterTable ft; ft.init(s->filter);
+    FilterTable ft; ft.init(s->filterRadius, s->filterTable);
     int W = s->camera.width, H = s->camera.height;
     std::vector<int> order; blockOrder(W, H, kBlockSize, order);
     int nb = (int) order.size() / 4;

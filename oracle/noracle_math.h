@@ -70,6 +70,15 @@ inline V3 normalized(V3 a) {
     if (z > 0.0f) return a / std::sqrt(z);
     return a;
 }
+/// normalized() of an expression over DYNAMIC-size Eigen blocks (e.g. `N.col(i)` sums in
+/// src/accel.cpp:101-104): the temporary has run-time size, so Eigen's reduction is the plain
+/// sequential loop (x0 + x1) + x2 instead of the fixed-size tree. Pinned against the compiled
+/// reference (tests/test_oracle_pins.py::test_intersection_records).
+inline V3 normalizedDynamic(V3 a) {
+    float z = (a.x * a.x + a.y * a.y) + a.z * a.z;
+    if (z > 0.0f) return a / std::sqrt(z);
+    return a;
+}
 
 // ---------------------------------------------------------------------------------------
 // REF: PCG32 (ext/pcg32/pcg32.h:40-161) and the `independent` sampler (src/independent.cpp)
@@ -111,13 +120,15 @@ struct Pcg32 {
     }
 };
 
-/// Sampler contract (include/nori/sampler.h:68-98). next2D draws x first, then y: that is
-/// what g++ emits for `Point2f(m_random.nextFloat(), m_random.nextFloat())`
-/// (src/independent.cpp:62-67) — pinned against the compiled reference in tests.
+/// Sampler contract (include/nori/sampler.h:68-98). next2D is
+/// `Point2f(m_random.nextFloat(), m_random.nextFloat())` (src/independent.cpp:62-67): C++ leaves
+/// the argument order unspecified and g++ (x86-64) evaluates right to left, so the FIRST draw
+/// lands in y and the second in x. Pinned against the compiled reference
+/// (tests/test_oracle_pins.py::test_next2d_order); the CUDA sampler follows the same order.
 struct Sampler {
     Pcg32 rng;
     float next1D() { return rng.nextFloat(); }
-    V2 next2D() { V2 r; r.x = rng.nextFloat(); r.y = rng.nextFloat(); return r; }
+    V2 next2D() { V2 r; r.y = rng.nextFloat(); r.x = rng.nextFloat(); return r; }
 };
 
 // ---------------------------------------------------------------------------------------

@@ -97,11 +97,16 @@ struct Scene {
     std::vector<Bsdf> bsdfs;
     std::vector<EmitterData> emitters;
     CameraData camera;
-    Filter filter;
+    float filterRadius, filterTable[33];      // ImageBlock's tabulated filter (src/block.cpp:31-39)
     IntegratorParams integrator;
     int sampleCount;
     Accel accel;
-    Scene() : sampleCount(1) { filter = gaussianFilter(); }
+    Scene() : sampleCount(1) { setFilter(gaussianFilter()); }
+    void setFilter(const Filter &f) {
+        filterRadius = f.radius;
+        for (int i = 0; i < 32; ++i) filterTable[i] = f.eval((f.radius * i) / 32);
+        filterTable[32] = 0.0f;
+    }
 
     /// Build emitter CDFs (S4) and the acceleration structure; call after filling the arrays.
     void activate(bool useBvh = true) {
@@ -285,7 +290,7 @@ inline void fillHit(const Scene &s, uint32_t gid, float t, float u, float v, Hit
     } else { its.uv.x = u; its.uv.y = v; }
     its.geo = Frame(normalized(cross(p1 - p0, p2 - p0)));
     if (!m.N.empty())
-        its.sh = Frame(normalized((bary.x * m.nrm(i0) + bary.y * m.nrm(i1)) + bary.z * m.nrm(i2)));
+        its.sh = Frame(normalizedDynamic((bary.x * m.nrm(i0) + bary.y * m.nrm(i1)) + bary.z * m.nrm(i2)));
     else its.sh = its.geo;
 }
 
@@ -307,10 +312,15 @@ struct FilterTable {
     float radius, lookupFactor, table[kFilterRes + 1];
     int border;
     void init(const Filter &f) {                              // block.cpp:31-39
-        radius = f.radius;
+        float t[kFilterRes + 1];
+        for (int i = 0; i < kFilterRes; ++i) t[i] = f.eval((f.radius * i) / kFilterRes);
+        t[kFilterRes] = 0.0f;
+        init(f.radius, t);
+    }
+    void init(float r, const float *t) {
+        radius = r;
         border = (int) std::ceil(radius - 0.5f);
-        for (int i = 0; i < kFilterRes; ++i) table[i] = f.eval((radius * i) / kFilterRes);
-        table[kFilterRes] = 0.0f;
+        std::memcpy(table, t, sizeof(table));
         lookupFactor = kFilterRes / radius;
     }
 };

@@ -1,0 +1,371 @@
+"""ctypes bindings of the parity oracle (TEST INFRASTRUCTURE).
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this module;
+the product package (nori_b200) never does.
+
+* ``Port``  — oracle/liboracle.so, the standalone CPU restatement (builds anywhere).
+* ``Ref``   — oracle/_ref/libnori_ref.so, the reference's own sources compiled by
+  oracle/Makefile (present in the authoring container; travels prebuilt to GPU boxes).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from nori_b200.scene import FlatMesh, FlatScene
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libnori_ref.so")
+REFERENCE_ROOT = "/root/reference"
+
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+def build_port() -> str:
+    subprocess.check_call(["make", "-s", "-C", HERE, "port"])
+    return PORT_SO
+
+
+def build_ref() -> str:
+    if not os.path.isdir(REFERENCE_ROOT):
+        raise RuntimeError("reference sources absent: oracle/_ref can only be built where /root/reference exists")
+    subprocess.check_call(["make", "-s", "-j8", "-C", HERE, "ref"])
+    return REF_SO
+
+
+def have_ref() -> bool:
+    return os.path.exists(REF_SO)
+
+
+def _optional(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class PortScene:
+    """A FlatScene loaded into the standalone port."""
+
+    def __init__(self, lib: "Port", scene: FlatScene, use_bvh: bool = True):
+        self.lib, self.L, self.scene = lib, lib.L, scene
+        L = self.L
+        self.h = C.c_void_p(L.noracle_scene_create())
+        for m in scene.meshes:
+            b = L.noracle_scene_add_bsdf(self.h, int(m.bsdf_type), _f32(m.bsdf_params))
+            mi = L.noracle_scene_add_mesh(self.h, m.V, m.V.shape[0], _optional(m.N), _optional(m.UV), m.F, m.F.shape[0], b)
+            if m.is_emitter:
+                L.noracle_scene_add_emitter(self.h, mi, _f32(m.radiance))
+        L.noracle_scene_set_camera(self.h, _f32(scene.sample_to_camera).ravel(), _f32(scene.camera_to_world).ravel(),
+                                   scene.width, scene.height, C.c_float(scene.near_clip), C.c_float(scene.far_clip))
+        L.noracle_scene_set_filter_table(self.h, C.c_float(scene.filter_radius), _f32(scene.filter_table))
+        L.noracle_scene_set_integrator(self.h, scene.integrator, scene.rr_start, C.c_float(scene.rr_max), scene.max_depth,
+                                       _f32(scene.light_pos), _f32(scene.light_energy))
+        L.noracle_scene_activate(self.h, int(use_bvh))
+
+    def __del__(self):
+        try:
+            self.L.noracle_scene_destroy(self.h)
+        except Exception:
+            pass
+
+    def set_integrator(self, integrator: int):
+        s = self.scene
+        self.L.noracle_scene_set_integrator(self.h, integrator, s.rr_start, C.c_float(s.rr_max), s.max_depth,
+                                            _f32(s.light_pos), _f32(s.light_energy))
+
+    def camera_rays(self, pixel_samples):
+        ps = _f32(pixel_samples, (-1, 2)); out = np.empty((ps.shape[0], 8), np.float32)
+        self.L.noracle_camera_rays(self.h, ps.shape[0], ps, out)
+        return out
+
+    def trace(self, rays, shadow=False, use_bvh=True, count=False):
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        tri = np.empty(n, np.uint32); mesh = np.empty(n, np.uint32); tuv = np.empty((n, 3), np.float32)
+        counters = np.zeros(3, np.uint64)
+        self.L.noracle_scene_set_use_bvh(self.h, int(use_bvh))
+        self.L.noracle_trace(self.h, rays, n, int(shadow), tri, mesh, tuv, counters.ctypes.data_as(C.c_void_p) if count else None)
+        return (tri, mesh, tuv, counters) if count else (tri, mesh, tuv)
+
+    def intersect(self, rays, use_bvh=True):
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        out = np.empty((n, 24), np.float32); valid = np.empty(n, np.int32)
+        self.L.noracle_scene_set_use_bvh(self.h, int(use_bvh))
+        self.L.noracle_intersect(self.h, rays, n, out, valid)
+        return out, valid.astype(bool)
+
+    def sample_radiance(self, pixel, sample):
+        pixel = np.ascontiguousarray(pixel, np.uint32); sample = np.ascontiguousarray(sample, np.uint32)
+        n = pixel.shape[0]
+        rgb = np.empty((n, 3), np.float32); pos = np.empty((n, 2), np.float32); stats = np.zeros(3, np.uint64)
+        self.L.noracle_sample_radiance(self.h, n, pixel, sample, rgb, pos, stats)
+        return rgb, pos, stats
+
+    def render(self, mode=0, sample_first=0, sample_last=None, threads=0):
+        if sample_last is None:
+            sample_last = self.scene.sample_count
+        out = np.empty(self.scene.block_shape(), np.float32); stats = np.zeros(4, np.uint64)
+        self.L.noracle_render(self.h, mode, sample_first, sample_last, threads, out, stats)
+        return out, stats
+
+
+class Port:
+    def __init__(self, build: bool = True):
+        if build or not os.path.exists(PORT_SO):
+            build_port()
+        L = self.L = C.CDLL(PORT_SO)
+        L.noracle_scene_create.restype = C.c_void_p
+        L.noracle_scene_destroy.argtypes = [C.c_void_p]
+        L.noracle_scene_add_bsdf.argtypes = [C.c_void_p, C.c_int, _f32p]
+        L.noracle_scene_add_mesh.argtypes = [C.c_void_p, _f32p, C.c_uint32, C.c_void_p, C.c_void_p, _u32p, C.c_uint32, C.c_int]
+        L.noracle_scene_add_emitter.argtypes = [C.c_void_p, C.c_int, _f32p]
+        L.noracle_scene_set_camera.argtypes = [C.c_void_p, _f32p, _f32p, C.c_int, C.c_int, C.c_float, C.c_float]
+        L.noracle_scene_set_filter.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float]
+        L.noracle_scene_set_filter_table.argtypes = [C.c_void_p, C.c_float, _f32p]
+        L.noracle_scene_set_integrator.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_int, _f32p, _f32p]
+        L.noracle_scene_activate.argtypes = [C.c_void_p, C.c_int]
+        L.noracle_scene_set_use_bvh.argtypes = [C.c_void_p, C.c_int]
+        L.noracle_pcg32_uints.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int, _u32p]
+        L.noracle_pcg32_floats.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int, _f32p]
+        L.noracle_camera_rays.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p]
+        L.noracle_trace.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _u32p, _u32p, _f32p, C.c_void_p]
+        L.noracle_intersect.argtypes = [C.c_void_p, _f32p, C.c_int, _f32p, _i32p]
+        L.noracle_bsdf_sample.argtypes = [C.c_int, _f32p, C.c_int, _f32p, _f32p, _f32p, _f32p, _f32p, _f32p, _i32p]
+        L.noracle_bsdf_eval_pdf.argtypes = [C.c_int, _f32p, C.c_int, _f32p, _f32p, _f32p, _f32p]
+        L.noracle_warp.argtypes = [C.c_int, C.c_float, C.c_int, _f32p, _f32p, _f32p]
+        L.noracle_fresnel.argtypes = [C.c_int, _f32p, C.c_float, C.c_float, _f32p]
+        L.noracle_filter_table.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float, _f32p, _i32p]
+        L.noracle_block_order.argtypes = [C.c_int, C.c_int, C.c_int, _i32p, C.c_int]
+        L.noracle_splat.argtypes = [C.c_int, C.c_int, C.c_float, _f32p, C.c_int, _f32p, _f32p, _f32p]
+        L.noracle_splat.restype = C.c_uint64
+        L.noracle_sample_radiance.argtypes = [C.c_void_p, C.c_int, _u32p, _u32p, _f32p, _f32p, _u64p]
+        L.noracle_render.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _f32p, _u64p]
+
+    def scene(self, scene: FlatScene, use_bvh=True) -> PortScene:
+        return PortScene(self, scene, use_bvh)
+
+    def pcg32_uints(self, initstate, initseq, n, advance=0):
+        out = np.empty(n, np.uint32); self.L.noracle_pcg32_uints(initstate, initseq, advance, n, out); return out
+
+    def pcg32_floats(self, initstate, initseq, n, advance=0):
+        out = np.empty(n, np.float32); self.L.noracle_pcg32_floats(initstate, initseq, advance, n, out); return out
+
+    def bsdf_sample(self, btype, params, wi, xi):
+        wi = _f32(wi, (-1, 3)); xi = _f32(xi, (-1, 2)); n = wi.shape[0]
+        wo = np.empty((n, 3), np.float32); w = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        eta = np.empty(n, np.float32); meas = np.empty(n, np.int32)
+        self.L.noracle_bsdf_sample(btype, _f32(params), n, wi, xi, wo, w, pdf, eta, meas)
+        return wo, w, pdf, eta, meas
+
+    def bsdf_eval_pdf(self, btype, params, wi, wo):
+        wi = _f32(wi, (-1, 3)); wo = _f32(wo, (-1, 3)); n = wi.shape[0]
+        f = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        self.L.noracle_bsdf_eval_pdf(btype, _f32(params), n, wi, wo, f, pdf)
+        return f, pdf
+
+    def warp(self, wid, xi, param=0.0):
+        xi = _f32(xi, (-1, 2)); n = xi.shape[0]
+        out = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        self.L.noracle_warp(wid, param, n, xi, out, pdf)
+        return out, pdf
+
+    def fresnel(self, cos_i, ext_ior, int_ior):
+        c = _f32(cos_i).ravel(); out = np.empty_like(c); self.L.noracle_fresnel(c.shape[0], c, ext_ior, int_ior, out); return out
+
+    def filter_table(self, ftype, radius, p0=0.0, p1=0.0):
+        t = np.empty(33, np.float32); b = np.zeros(1, np.int32)
+        self.L.noracle_filter_table(ftype, radius, p0, p1, t, b)
+        return t, int(b[0])
+
+    def block_order(self, W, H, bs=32):
+        cap = ((W + bs - 1) // bs) * ((H + bs - 1) // bs)
+        out = np.empty((cap, 4), np.int32)
+        n = self.L.noracle_block_order(W, H, bs, out, cap)
+        return out[:n]
+
+    def splat(self, W, H, radius, table, pos, rgb):
+        pos = _f32(pos, (-1, 2)); rgb = _f32(rgb, (-1, 3))
+        b = int(np.ceil(np.float32(radius) - np.float32(0.5)))
+        out = np.empty((H + 2 * b, W + 2 * b, 4), np.float32)
+        dropped = self.L.noracle_splat(W, H, radius, _f32(table), pos.shape[0], pos, rgb, out)
+        return out, int(dropped)
+
+
+class RefScene:
+    """A scene loaded by the reference's own parser (loadFromXML)."""
+
+    def __init__(self, lib: "Ref", handle):
+        self.lib, self.L, self.h = lib, lib.L, C.c_void_p(handle)
+
+    def flatten(self) -> FlatScene:
+        L = self.L
+        meshes = []
+        for i in range(L.ref_scene_mesh_count(self.h)):
+            nV, nF = C.c_uint32(), C.c_uint32()
+            hasN, hasUV, btype, isEm = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+            params = np.zeros(6, np.float32); rad = np.zeros(3, np.float32)
+            if L.ref_scene_mesh_info(self.h, i, C.byref(nV), C.byref(nF), C.byref(hasN), C.byref(hasUV),
+                                     C.byref(btype), params, C.byref(isEm), rad) != 0:
+                raise RuntimeError(L.ref_last_error().decode())
+            V = np.empty((nV.value, 3), np.float32); F = np.empty((nF.value, 3), np.uint32)
+            N = np.empty((nV.value, 3), np.float32) if hasN.value else None
+            UV = np.empty((nV.value, 2), np.float32) if hasUV.value else None
+            L.ref_scene_mesh_copy(self.h, i, V.ctypes.data_as(C.c_void_p), _optional(N), _optional(UV), F.ctypes.data_as(C.c_void_p))
+            meshes.append(FlatMesh(V=V, F=F, N=N, UV=UV, bsdf_type=btype.value, bsdf_params=params,
+                                   is_emitter=bool(isEm.value), radiance=rad))
+        s2c = np.zeros(16, np.float32); c2w = np.zeros(16, np.float32)
+        W, H = C.c_int(), C.c_int(); near, far, fov = C.c_float(), C.c_float(), C.c_float()
+        if L.ref_scene_camera(self.h, s2c, c2w, C.byref(W), C.byref(H), C.byref(near), C.byref(far), C.byref(fov)) != 0:
+            raise RuntimeError("camera is not a PerspectiveCamera")
+        radius = C.c_float(); table = np.zeros(33, np.float32); border = C.c_int()
+        L.ref_scene_filter(self.h, C.byref(radius), table, C.byref(border))
+        ip = np.zeros(3, np.int32); fp = np.zeros(7, np.float32)
+        if L.ref_scene_integrator(self.h, ip, fp) != 0:
+            raise RuntimeError("integrator is not an oracle integrator")
+        return FlatScene(meshes=meshes, sample_to_camera=s2c.reshape(4, 4), camera_to_world=c2w.reshape(4, 4),
+                         width=W.value, height=H.value, near_clip=near.value, far_clip=far.value, fov=fov.value,
+                         filter_radius=radius.value, filter_table=table, integrator=int(ip[0]), rr_start=int(ip[1]),
+                         max_depth=int(ip[2]), rr_max=float(fp[0]), light_pos=fp[1:4].copy(), light_energy=fp[4:7].copy(),
+                         sample_count=L.ref_scene_sample_count(self.h))
+
+    def camera_rays(self, pixel_samples):
+        ps = _f32(pixel_samples, (-1, 2)); out = np.empty((ps.shape[0], 8), np.float32)
+        self.L.ref_camera_rays(self.h, ps.shape[0], ps, out)
+        return out
+
+    def trace(self, rays, shadow=False, use_bvh=False):
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        tri = np.empty(n, np.uint32); mesh = np.empty(n, np.uint32); tuv = np.empty((n, 3), np.float32)
+        self.L.ref_trace(self.h, rays, n, int(shadow), int(use_bvh), tri, mesh, tuv)
+        return tri, mesh, tuv
+
+    def intersect(self, rays, use_bvh=False):
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        out = np.empty((n, 24), np.float32); valid = np.empty(n, np.int32)
+        self.L.ref_intersect(self.h, rays, n, int(use_bvh), out, valid)
+        return out, valid.astype(bool)
+
+    def stock_intersect(self, mesh_index, rays, shadow=False):
+        """The UNMODIFIED reference Accel (single mesh, brute force) on mesh `mesh_index`."""
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        out = np.empty((n, 24), np.float32); valid = np.empty(n, np.int32)
+        self.L.ref_stock_intersect(C.c_void_p(self.L.ref_scene_mesh_ptr(self.h, mesh_index)), rays, n, int(shadow), out, valid)
+        return out, valid.astype(bool)
+
+    def bsdf_sample(self, mesh_index, wi, xi):
+        wi = _f32(wi, (-1, 3)); xi = _f32(xi, (-1, 2)); n = wi.shape[0]
+        wo = np.empty((n, 3), np.float32); w = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        eta = np.empty(n, np.float32); meas = np.empty(n, np.int32)
+        self.L.ref_bsdf_sample(self.h, mesh_index, n, wi, xi, wo, w, pdf, eta, meas)
+        return wo, w, pdf, eta, meas
+
+    def bsdf_eval_pdf(self, mesh_index, wi, wo):
+        wi = _f32(wi, (-1, 3)); wo = _f32(wo, (-1, 3)); n = wi.shape[0]
+        f = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        self.L.ref_bsdf_eval_pdf(self.h, mesh_index, n, wi, wo, f, pdf)
+        return f, pdf
+
+    def sample_radiance(self, pixel, sample, use_bvh=True):
+        pixel = np.ascontiguousarray(pixel, np.uint32); sample = np.ascontiguousarray(sample, np.uint32)
+        n = pixel.shape[0]
+        rgb = np.empty((n, 3), np.float32); pos = np.empty((n, 2), np.float32)
+        self.L.ref_sample_radiance(self.h, n, pixel, sample, int(use_bvh), rgb, pos)
+        return rgb, pos
+
+    def render(self, shape, mode=0, sample_first=0, sample_last=1, threads=0, use_bvh=True):
+        out = np.empty(shape, np.float32)
+        sec = self.L.ref_render(self.h, mode, sample_first, sample_last, threads, int(use_bvh), out)
+        return out, sec
+
+
+class Ref:
+    def __init__(self, build: bool = False):
+        if build:
+            build_ref()
+        if not os.path.exists(REF_SO):
+            raise RuntimeError("oracle/_ref/libnori_ref.so missing (run `make -C oracle ref` where /root/reference exists)")
+        L = self.L = C.CDLL(REF_SO)
+        L.ref_last_error.restype = C.c_char_p
+        L.ref_load_xml.restype = C.c_void_p; L.ref_load_xml.argtypes = [C.c_char_p]
+        L.ref_scene_mesh_ptr.restype = C.c_void_p; L.ref_scene_mesh_ptr.argtypes = [C.c_void_p, C.c_int]
+        L.ref_scene_mesh_count.argtypes = [C.c_void_p]
+        L.ref_scene_mesh_info.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [_f32p, C.c_void_p, _f32p]
+        L.ref_scene_mesh_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_scene_camera.argtypes = [C.c_void_p, _f32p, _f32p] + [C.c_void_p] * 5
+        L.ref_scene_filter.argtypes = [C.c_void_p, C.c_void_p, _f32p, C.c_void_p]
+        L.ref_scene_sample_count.argtypes = [C.c_void_p]
+        L.ref_scene_integrator.argtypes = [C.c_void_p, _i32p, _f32p]
+        L.ref_pcg32_uints.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int, _u32p]
+        L.ref_pcg32_floats.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int, _f32p]
+        L.ref_sampler_next2d.argtypes = [C.c_int, C.c_int, C.c_int, _f32p]
+        L.ref_camera_rays.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p]
+        L.ref_trace.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, C.c_int, _u32p, _u32p, _f32p]
+        L.ref_intersect.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _f32p, _i32p]
+        L.ref_stock_intersect.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _f32p, _i32p]
+        L.ref_bsdf_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, _f32p, _f32p, _f32p, _f32p, _f32p, _f32p, _i32p]
+        L.ref_bsdf_eval_pdf.argtypes = [C.c_void_p, C.c_int, C.c_int, _f32p, _f32p, _f32p, _f32p]
+        L.ref_fresnel.argtypes = [C.c_int, _f32p, C.c_float, C.c_float, _f32p]
+        L.ref_frames.argtypes = [C.c_int, _f32p, _f32p]
+        L.ref_filter_table.argtypes = [C.c_char_p, C.c_float, C.c_float, C.c_float, C.c_void_p, _f32p]
+        L.ref_block_order.argtypes = [C.c_int, C.c_int, C.c_int, _i32p, C.c_int]
+        L.ref_splat.argtypes = [C.c_int, C.c_int, C.c_char_p, C.c_int, _f32p, _f32p, _f32p]
+        L.ref_render.restype = C.c_double
+        L.ref_render.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_int, _f32p]
+        L.ref_sample_radiance.argtypes = [C.c_void_p, C.c_int, _u32p, _u32p, C.c_int, _f32p, _f32p]
+        L.ref_accel_counters.argtypes = [C.c_int, C.c_void_p, C.c_int]
+
+    def load_xml(self, path: str) -> RefScene:
+        """loadFromXML; statistical tests embedded in the file run during activate()."""
+        h = self.L.ref_load_xml(path.encode())
+        if not h:
+            raise RuntimeError(self.L.ref_last_error().decode())
+        return RefScene(self, h)
+
+    def pcg32_uints(self, initstate, initseq, n, advance=0):
+        out = np.empty(n, np.uint32); self.L.ref_pcg32_uints(initstate, initseq, advance, n, out); return out
+
+    def pcg32_floats(self, initstate, initseq, n, advance=0):
+        out = np.empty(n, np.float32); self.L.ref_pcg32_floats(initstate, initseq, advance, n, out); return out
+
+    def sampler_next2d(self, ox, oy, n):
+        out = np.empty((n, 2), np.float32); self.L.ref_sampler_next2d(ox, oy, n, out); return out
+
+    def fresnel(self, cos_i, ext_ior, int_ior):
+        c = _f32(cos_i).ravel(); out = np.empty_like(c); self.L.ref_fresnel(c.shape[0], c, ext_ior, int_ior, out); return out
+
+    def frames(self, normals):
+        nrm = _f32(normals, (-1, 3)); out = np.empty((nrm.shape[0], 6), np.float32)
+        self.L.ref_frames(nrm.shape[0], nrm, out); return out
+
+    def filter_table(self, name, radius=2.0, p0=0.5, p1=0.0):
+        r = C.c_float(); t = np.empty(33, np.float32)
+        if self.L.ref_filter_table(name.encode(), radius, p0, p1, C.byref(r), t) != 0:
+            raise RuntimeError(self.L.ref_last_error().decode())
+        return r.value, t
+
+    def block_order(self, W, H, bs=32):
+        cap = ((W + bs - 1) // bs) * ((H + bs - 1) // bs)
+        out = np.empty((cap, 4), np.int32)
+        n = self.L.ref_block_order(W, H, bs, out, cap)
+        return out[:n]
+
+    def splat(self, W, H, name, pos, rgb, border):
+        pos = _f32(pos, (-1, 2)); rgb = _f32(rgb, (-1, 3))
+        out = np.empty((H + 2 * border, W + 2 * border, 4), np.float32)
+        if self.L.ref_splat(W, H, name.encode(), pos.shape[0], pos, rgb, out) != 0:
+            raise RuntimeError(self.L.ref_last_error().decode())
+        return out
+
+    def traversal_counters(self, enable=True, reset=False):
+        out = np.zeros(3, np.uint64)
+        self.L.ref_accel_counters(int(enable), out.ctypes.data_as(C.c_void_p), int(reset))
+        return out

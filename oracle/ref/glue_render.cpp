@@ -29,7 +29,8 @@ public:
     void generate() {}
     void advance() {}
     float next1D() { return m_random.nextFloat(); }
-    Point2f next2D() { float x = m_random.nextFloat(); float y = m_random.nextFloat(); return Point2f(x, y); }
+    /// same draw order as the compiled `independent` plugin: first draw -> y, second -> x
+    Point2f next2D() { float y = m_random.nextFloat(); float x = m_random.nextFloat(); return Point2f(x, y); }
     std::string toString() const { return "StreamSampler[]"; }
 private:
     pcg32 m_random;
