@@ -1,0 +1,173 @@
+/* nori_gpu.h — C ABI of libnori_b200.so, the B200 (sm_100a) execution engine behind Nori's
+ * render path.
+ *
+ * The reference (joyDeng/nori) has no FFI: its plugins are C++ translation units that register
+ * with NoriObjectFactory (include/nori/object.h:142-161) and are driven by render()
+ * (src/main.cpp:69-151). This header is the boundary a maintainer binds instead: the host side
+ * (XML parser, object factory, OBJ loader — unchanged) flattens its Scene into the PODs below and
+ * ONE call, nori_gpu_render, replaces everything inside `tbb::parallel_for` (src/main.cpp:93-121).
+ * Each entry point cites the reference interface it stands in for; INTEGRATION.md shows the
+ * reference-side stub.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success and a negative
+ * NORI_GPU_E* code otherwise; nori_gpu_last_error() returns the message (the C++ wrapper rethrows it
+ * as NoriException, include/nori/common.h:147-152). Host arrays are borrowed for the duration of a
+ * call. One ctx = one CUDA device; calls on one ctx are serialised by the caller. There is no CPU
+ * fallback: without a usable CUDA device nori_gpu_create fails.
+ */
+#ifndef NORI_GPU_H
+#define NORI_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nori_gpu_ctx nori_gpu_ctx;
+
+enum {
+    NORI_GPU_OK = 0,
+    NORI_GPU_EINVAL = -1,     /* bad argument / call order */
+    NORI_GPU_ECUDA = -2,      /* CUDA runtime error (message has the call site) */
+    NORI_GPU_ENODEVICE = -3,  /* no CUDA device: the product has no CPU path */
+    NORI_GPU_EUNSUPPORTED = -4
+};
+
+/* BSDF models: src/diffuse.cpp, src/mirror.cpp, src/dielectric.cpp, src/microfacet.cpp */
+enum { NORI_BSDF_DIFFUSE = 0, NORI_BSDF_MIRROR = 1, NORI_BSDF_DIELECTRIC = 2, NORI_BSDF_MICROFACET = 3 };
+
+/* Integrator::Li implementations (include/nori/integrator.h:54), selected by the XML type name */
+enum {
+    NORI_INT_NORMALS = 0, NORI_INT_PATH_MATS = 1, NORI_INT_PATH_EMS = 2, NORI_INT_PATH_MIS = 3,
+    NORI_INT_WHITTED = 4, NORI_INT_PRIMARY_SHADOW = 5, NORI_INT_SIMPLE = 6, NORI_INT_AO = 7
+};
+
+/* Sampler stream modes (src/independent.cpp:48-53).
+ * BLOCK: the reference's stream — one PCG32 per 32x32 block seeded (offset.x, offset.y), consumed
+ *        serially; reproducible on the device only for integrators that draw a fixed number of
+ *        values per camera sample (normals, simple), via pcg32::advance (ext/pcg32/pcg32.h:140-161).
+ * PER_SAMPLE: seed(initstate = y*W + x, initseq = sample index) per camera sample; independent of
+ *        any partitioning of the work over GPUs. */
+enum { NORI_STREAM_BLOCK = 0, NORI_STREAM_PER_SAMPLE = 1 };
+
+/* Ray-triangle test: REFERENCE_MT reproduces src/mesh.cpp:51-88 operation for operation. */
+enum { NORI_ISECT_REFERENCE_MT = 0, NORI_ISECT_WATERTIGHT = 1 };
+
+/* One Mesh (include/nori/mesh.h:172-175): column-major Eigen buffers == C arrays below. */
+typedef struct {
+    const float *V;        /* 3 x nV positions (world space; obj.cpp applies toWorld at load) */
+    const float *N;        /* 3 x nV vertex normals, or NULL */
+    const float *UV;       /* 2 x nV texture coordinates, or NULL */
+    const uint32_t *F;     /* 3 x nF vertex indices */
+    uint32_t nV, nF;
+    int32_t bsdf_type;     /* NORI_BSDF_* (Mesh::getBSDF; default diffuse, mesh.cpp:35-41) */
+    float bsdf_params[6];  /* albedo|kd rgb, alpha, intIOR, extIOR */
+    int32_t is_emitter;    /* Mesh::isEmitter (mesh.h:140) : `area` emitter attached */
+    float radiance[3];
+} NoriGpuMeshDesc;
+
+/* PerspectiveCamera after activate() (src/perspective.cpp:53-86); matrices row-major 4x4. */
+typedef struct {
+    float sample_to_camera[16];
+    float camera_to_world[16];
+    int32_t width, height;
+    float near_clip, far_clip;
+} NoriGpuCameraDesc;
+
+typedef struct {
+    int32_t integrator;      /* NORI_INT_* */
+    int32_t stream_mode;     /* NORI_STREAM_* */
+    uint32_t sample_first;   /* samples [first, last) of every pixel (Sampler::getSampleCount range) */
+    uint32_t sample_last;
+    int32_t rr_start;        /* Russian roulette from this depth (oracle: 3) */
+    float rr_max;            /* continuation probability cap (oracle: 0.99) */
+    int32_t max_depth;       /* <= 0: unbounded */
+    int32_t intersect_mode;  /* NORI_ISECT_* */
+    float light_pos[3];      /* `simple` integrator (scenes/pa3/ajax-simple.xml:9-10) */
+    float light_energy[3];
+    int32_t clear;           /* 1: zero the accumulated ImageBlock first (ImageBlock::clear) */
+    int32_t deterministic;   /* 1: splat in the reference's sample order (bit-reproducible image) */
+} NoriGpuRenderDesc;
+
+typedef struct {
+    uint64_t camera_samples;
+    uint64_t closest_rays;
+    uint64_t shadow_rays;
+    uint64_t segments;        /* path vertices processed */
+    uint64_t dropped;         /* invalid radiance samples (src/block.cpp:75-79) */
+    uint64_t iterations;      /* wavefront iterations */
+    uint64_t kernel_launches;
+    float ms_total;           /* device time of the whole call (CUDA events) */
+    float ms_trace_closest, ms_trace_shadow, ms_shade, ms_generate, ms_splat;  /* filled when profiling=1 */
+} NoriGpuRenderStats;
+
+typedef struct {
+    uint32_t n_triangles, n_nodes, n_leaves, max_leaf_size, depth;
+    float sah_cost;
+    float build_ms;
+} NoriGpuAccelStats;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+int nori_gpu_create(nori_gpu_ctx **out, int device_id);
+void nori_gpu_destroy(nori_gpu_ctx *ctx);
+const char *nori_gpu_last_error(const nori_gpu_ctx *ctx);   /* ctx may be NULL: last create() error */
+int nori_gpu_device_name(const nori_gpu_ctx *ctx, char *buf, int cap);
+
+/* ---- scene upload: replaces Scene::addChild/activate (src/scene.cpp:39-96) ------------------- */
+int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int n);   /* Accel::addMesh (accel.h:39) for all meshes, emitters incl. */
+int nori_gpu_set_camera(nori_gpu_ctx *ctx, const NoriGpuCameraDesc *cam);              /* camera.h:56-64 */
+int nori_gpu_set_filter(nori_gpu_ctx *ctx, float radius, const float table33[33]);     /* ImageBlock ctor table, src/block.cpp:31-39 */
+int nori_gpu_build_accel(nori_gpu_ctx *ctx, NoriGpuAccelStats *out);                   /* Accel::build (accel.h:45) — device BVH */
+
+/* ---- the hot path: replaces render()'s parallel_for (src/main.cpp:93-121) -------------------- */
+int nori_gpu_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuRenderStats *out);
+/* ImageBlock::data() of the full-frame result, RowMajor (H+2b) x (W+2b) x RGBW (src/block.cpp:48) */
+int nori_gpu_download_block(nori_gpu_ctx *ctx, float *rgbw);
+/* ImageBlock::toBitmap (src/block.cpp:57-63): H x W x RGB, rgb/w, border cropped */
+int nori_gpu_download_bitmap(nori_gpu_ctx *ctx, float *rgb);
+/* Device-side access for the cross-GPU sum of ImageBlocks (`result.put(block)`, block.cpp:105-114):
+ * the accumulator is a device array of block_floats() floats that NCCL reduces in place. */
+int nori_gpu_block_device_ptr(nori_gpu_ctx *ctx, void **dptr, uint64_t *n_floats);
+int nori_gpu_block_dims(const nori_gpu_ctx *ctx, int *rows, int *cols, int *border);
+int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on);   /* per-stage CUDA-event timing (serialises stages) */
+int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n_paths);
+
+/* ---- raw operators (parity and Mrays/s) ----------------------------------------------------- */
+/* Accel::rayIntersect (src/accel.cpp:35-55). rays: n x 8 [o.xyz, mint, d.xyz, maxt] (HOST memory).
+ * tri_id: mesh-local triangle index or 0xffffffff; mesh_id likewise; tuv: n x 3 (t,u,v) or NULL. */
+int nori_gpu_trace(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint32_t *tri_id, uint32_t *mesh_id, float *tuv);
+/* Same on DEVICE buffers already resident (no copies): for kernel-only timing. ms = device time. */
+int nori_gpu_trace_device(nori_gpu_ctx *ctx, const void *d_rays, int n, int shadow, void *d_hits /* n x 16 B: t,u,v,gid */, float *ms);
+/* Work counters of the device BVH for n rays: counts[0] = node visits (two child boxes per visit),
+ * counts[1] = ray-triangle tests (Mesh::rayIntersect calls). Source of the roofline's bytes per ray. */
+int nori_gpu_trace_count(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint64_t counts[2]);
+/* Accel::rayIntersect post-processing (src/accel.cpp:57-108): n x 24 floats
+ * [p(3) t uv(2) sh.s sh.t sh.n geo.s geo.t geo.n], valid[i] = hit. */
+int nori_gpu_intersect(nori_gpu_ctx *ctx, const float *rays, int n, float *out24, int32_t *valid);
+/* PerspectiveCamera::sampleRay (src/perspective.cpp:88-109): pixel samples n x 2 -> rays n x 8 */
+int nori_gpu_camera_rays(nori_gpu_ctx *ctx, const float *pixel_samples, int n, float *rays);
+/* BSDF::sample (include/nori/bsdf.h:71) for n (wi, xi) pairs; pdf = BSDF::pdf of the sampled
+ * direction (0 for discrete); used by the chi2/t-test harness (src/chi2test.cpp, src/ttest.cpp). */
+int nori_gpu_bsdf_sample(nori_gpu_ctx *ctx, int bsdf_type, const float params[6], int n, const float *wi, const float *xi,
+                         float *wo, float *weight, float *pdf, float *eta, int32_t *measure);
+/* BSDF::eval / BSDF::pdf (bsdf.h:82,99) in solid-angle measure */
+int nori_gpu_bsdf_eval_pdf(nori_gpu_ctx *ctx, int bsdf_type, const float params[6], int n, const float *wi, const float *wo,
+                           float *f, float *pdf);
+/* Warp::squareTo* and *Pdf (include/nori/warp.h:30-69); ids in src/warptest.cpp:91-94 order:
+ * 0 square 1 tent 2 disk 3 uniform_sphere 4 uniform_hemisphere 5 cosine_hemisphere 6 beckmann */
+int nori_gpu_warp(nori_gpu_ctx *ctx, int warp_id, float param, int n, const float *xi, float *out3, float *pdf);
+/* pcg32 (ext/pcg32/pcg32.h:55-112,140-161): seed, advance, n x nextUInt */
+int nori_gpu_pcg32(nori_gpu_ctx *ctx, uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out);
+/* ImageBlock::put(pos, value) (src/block.cpp:74-103) for n samples into a zeroed full-frame block
+ * of the current camera/filter; rgbw as nori_gpu_download_block; dropped = invalid samples. */
+int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb, int deterministic, float *rgbw, uint64_t *dropped);
+/* Radiance of individual camera samples (PER_SAMPLE stream): pixel index y*W+x and sample index
+ * per entry -> rgb n x 3 and the pixelSample position n x 2 handed to ImageBlock::put. */
+int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const uint32_t *pixel, const uint32_t *sample,
+                             float *rgb, float *pos);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NORI_GPU_H */

@@ -1,0 +1,622 @@
+// capi.cu — the C ABI of include/nori_gpu.h: context, scene upload, render loop, operators.
+// No CPU path exists here: every entry point either runs CUDA kernels or fails.
+#include "engine.h"
+#include <vector>
+#include <string>
+#include <cstring>
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <algorithm>
+
+using namespace ng;
+
+static thread_local std::string g_createError;
+
+struct nori_gpu_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    cudaDeviceProp prop;
+    // scene
+    std::vector<MeshInfo> meshes;
+    std::vector<EmitterInfo> emitters;
+    float4 *d_vpos = nullptr, *d_vnrm = nullptr; float2 *d_vuv = nullptr; uint4 *d_tris = nullptr;
+    MeshInfo *d_meshes = nullptr; EmitterInfo *d_emitters = nullptr; float *d_cdf = nullptr;
+    uint32_t nTris = 0, nVerts = 0;
+    BvhDevice bvh; BvhParams bvhParams; bool haveBvh = false, haveCamera = false, haveFilter = false;
+    Camera cam; FilterTab filter;
+    // accumulator
+    float *d_block = nullptr; size_t blockFloats = 0;
+    // wavefront pool
+    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 21;
+    Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
+    float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
+    uint32_t *tileDone = nullptr; size_t tileDoneCap = 0;
+    bool profiling = false;
+};
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + " failed: " + cudaGetErrorString(e_); return NORI_GPU_ECUDA; } } while (0)
+#define REQUIRE(cond, msg) do { if (!(cond)) { ctx->err = (msg); return NORI_GPU_EINVAL; } } while (0)
+
+namespace {
+
+template <class T> struct DevBuf {          // scoped device scratch
+    T *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc((void **) &p, std::max<size_t>(n, 1) * sizeof(T)); }
+};
+
+DeviceScene deviceScene(const nori_gpu_ctx *c) {
+    DeviceScene s;
+    memset(&s, 0, sizeof(s));
+    s.vpos = c->d_vpos; s.vnrm = c->d_vnrm; s.vuv = c->d_vuv; s.tris = c->d_tris;
+    s.meshes = c->d_meshes; s.emitters = c->d_emitters; s.emitterCdf = c->d_cdf;
+    s.nMeshes = (int) c->meshes.size(); s.nEmitters = (int) c->emitters.size();
+    s.nTris = c->nTris; s.nVerts = c->nVerts;
+    s.nodes = c->bvh.nodes; s.leafTris = c->bvh.leafTris; s.nNodes = c->bvh.nNodes;
+    s.cam = c->cam; s.filter = c->filter;
+    return s;
+}
+
+void freeScene(nori_gpu_ctx *c) {
+    cudaFree(c->d_vpos); cudaFree(c->d_vnrm); cudaFree(c->d_vuv); cudaFree(c->d_tris);
+    cudaFree(c->d_meshes); cudaFree(c->d_emitters); cudaFree(c->d_cdf);
+    cudaFree(c->bvh.nodes); cudaFree(c->bvh.leafTris);
+    c->d_vpos = c->d_vnrm = nullptr; c->d_vuv = nullptr; c->d_tris = nullptr; c->d_meshes = nullptr; c->d_emitters = nullptr; c->d_cdf = nullptr;
+    c->bvh = BvhDevice(); c->haveBvh = false; c->meshes.clear(); c->emitters.clear(); c->nTris = c->nVerts = 0;
+}
+
+void freePool(nori_gpu_ctx *c) {
+    if (!c->havePool) return;
+    Pool &p = c->pool;
+    cudaFree(p.rayO); cudaFree(p.rayD); cudaFree(p.hit); cudaFree(p.thr); cudaFree(p.rad); cudaFree(p.rng); cudaFree(p.meta);
+    cudaFree(p.pos); cudaFree(p.sortQueue); cudaFree(p.shadow);
+    c->havePool = false;
+}
+
+int ensurePool(nori_gpu_ctx *ctx) {
+    if (ctx->havePool && ctx->pool.capacity == ctx->poolSize) return 0;
+    freePool(ctx);
+    Pool &p = ctx->pool; const size_t n = ctx->poolSize;
+    memset(&p, 0, sizeof(p));
+    p.capacity = ctx->poolSize;
+    CK(cudaMalloc((void **) &p.rayO, n * 16)); CK(cudaMalloc((void **) &p.rayD, n * 16)); CK(cudaMalloc((void **) &p.hit, n * 16));
+    CK(cudaMalloc((void **) &p.thr, n * 16)); CK(cudaMalloc((void **) &p.rad, n * 16)); CK(cudaMalloc((void **) &p.rng, n * 16));
+    CK(cudaMalloc((void **) &p.meta, n * 16)); CK(cudaMalloc((void **) &p.pos, n * 8));
+    CK(cudaMalloc((void **) &p.sortQueue, n * 4 * kNumKeys)); CK(cudaMalloc((void **) &p.shadow, n * 48));
+    ctx->havePool = true;
+    return 0;
+}
+
+int ensureBlock(nori_gpu_ctx *ctx) {
+    size_t need = (size_t) (ctx->cam.width + 2 * ctx->filter.border) * (ctx->cam.height + 2 * ctx->filter.border) * 4;
+    if (ctx->d_block && ctx->blockFloats == need) return 0;
+    cudaFree(ctx->d_block); ctx->d_block = nullptr;
+    CK(cudaMalloc((void **) &ctx->d_block, need * sizeof(float)));
+    CK(cudaMemsetAsync(ctx->d_block, 0, need * sizeof(float), ctx->stream));
+    ctx->blockFloats = need;
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
+    if (!out) return NORI_GPU_EINVAL;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_createError = std::string("no CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") + "): libnori_b200 has no CPU path";
+        return NORI_GPU_ENODEVICE;
+    }
+    if (device_id < 0 || device_id >= n) { g_createError = "device id out of range"; return NORI_GPU_EINVAL; }
+    if ((e = cudaSetDevice(device_id)) != cudaSuccess) { g_createError = cudaGetErrorString(e); return NORI_GPU_ECUDA; }
+    nori_gpu_ctx *ctx = new nori_gpu_ctx();
+    ctx->device = device_id;
+    cudaGetDeviceProperties(&ctx->prop, device_id);
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaMalloc((void **) &ctx->d_counters, sizeof(Counters))) != cudaSuccess ||
+        (e = cudaMallocHost((void **) &ctx->h_counters, sizeof(Counters))) != cudaSuccess) {
+        g_createError = cudaGetErrorString(e); delete ctx; return NORI_GPU_ECUDA;
+    }
+    memset(&ctx->cam, 0, sizeof(ctx->cam)); memset(&ctx->filter, 0, sizeof(ctx->filter)); memset(&ctx->pool, 0, sizeof(ctx->pool));
+    if (const char *s = getenv("NORI_GPU_POOL")) ctx->poolSize = std::max(256u, (uint32_t) strtoul(s, nullptr, 10) / 256u * 256u);
+    if (const char *s = getenv("NORI_GPU_PLOC_RADIUS")) ctx->bvhParams.plocRadius = atoi(s);
+    if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
+    if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
+    if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
+    *out = ctx;
+    return NORI_GPU_OK;
+}
+
+void nori_gpu_destroy(nori_gpu_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    freeScene(ctx); freePool(ctx);
+    cudaFree(ctx->d_block); cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
+    cudaFree(ctx->recA); cudaFree(ctx->recB); cudaFree(ctx->tileDone);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *nori_gpu_last_error(const nori_gpu_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+int nori_gpu_device_name(const nori_gpu_ctx *ctx, char *buf, int cap) {
+    if (!ctx || !buf || cap <= 0) return NORI_GPU_EINVAL;
+    snprintf(buf, (size_t) cap, "%s (sm_%d%d, %d SMs)", ctx->prop.name, ctx->prop.major, ctx->prop.minor, ctx->prop.multiProcessorCount);
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on) { if (!ctx) return NORI_GPU_EINVAL; ctx->profiling = on != 0; return NORI_GPU_OK; }
+int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(n >= 256, "pool size must be >= 256");
+    ctx->poolSize = n / 256u * 256u;
+    return NORI_GPU_OK;
+}
+
+/// Scene::addChild(EMesh) + Accel::addMesh for every mesh (src/scene.cpp:58-66, accel.cpp:24-29,
+/// without the reference's single-mesh limit), Mesh::addChild(BSDF/Emitter) (mesh.cpp:104-126).
+int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int n) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(meshes && n > 0, "upload_meshes: no meshes");
+    CK(cudaSetDevice(ctx->device));
+    freeScene(ctx);
+    size_t nV = 0, nF = 0;
+    for (int i = 0; i < n; ++i) {
+        REQUIRE(meshes[i].V && meshes[i].F && meshes[i].nV > 0, "upload_meshes: mesh without vertices or faces");
+        REQUIRE(meshes[i].bsdf_type >= 0 && meshes[i].bsdf_type <= 3, "upload_meshes: unknown BSDF type");
+        nV += meshes[i].nV; nF += meshes[i].nF;
+    }
+    REQUIRE(nF > 0 && nF < (1u << 28), "upload_meshes: triangle count out of range");
+    std::vector<float4> vpos(nV), vnrm(nV); std::vector<float2> vuv(nV); std::vector<uint4> tris(nF);
+    std::vector<float> cdf;
+    size_t vo = 0, fo = 0;
+    for (int i = 0; i < n; ++i) {
+        const NoriGpuMeshDesc &m = meshes[i];
+        MeshInfo mi; memset(&mi, 0, sizeof(mi));
+        mi.bsdfType = m.bsdf_type;
+        Bsdf b = makeBsdf(m.bsdf_type, m.bsdf_params);
+        mi.albedo[0] = b.albedo.x; mi.albedo[1] = b.albedo.y; mi.albedo[2] = b.albedo.z;
+        mi.alpha = b.alpha; mi.intIOR = b.intIOR; mi.extIOR = b.extIOR; mi.ks = b.ks;
+        mi.emitter = -1; mi.hasN = m.N != nullptr; mi.hasUV = m.UV != nullptr;
+        mi.triOffset = (uint32_t) fo; mi.nTris = m.nF; mi.vertOffset = (uint32_t) vo; mi.nVerts = m.nV;
+        for (uint32_t v = 0; v < m.nV; ++v) {
+            vpos[vo + v] = make_float4(m.V[3 * v], m.V[3 * v + 1], m.V[3 * v + 2], 0.f);
+            vnrm[vo + v] = m.N ? make_float4(m.N[3 * v], m.N[3 * v + 1], m.N[3 * v + 2], 0.f) : make_float4(0, 0, 0, 0);
+            vuv[vo + v] = m.UV ? make_float2(m.UV[2 * v], m.UV[2 * v + 1]) : make_float2(0, 0);
+        }
+        for (uint32_t f = 0; f < m.nF; ++f) {
+            uint32_t a = m.F[3 * f], bb = m.F[3 * f + 1], c = m.F[3 * f + 2];
+            REQUIRE(a < m.nV && bb < m.nV && c < m.nV, "upload_meshes: face index out of range");
+            tris[fo + f] = make_uint4((uint32_t) vo + a, (uint32_t) vo + bb, (uint32_t) vo + c, (uint32_t) i);
+        }
+        if (m.is_emitter) {
+            // `area` emitter: DiscretePDF over triangle areas (Mesh::surfaceArea src/mesh.cpp:43-49;
+            // append/normalize include/nori/dpdf.h:57-59,94-108). Sequential float sums on the host
+            // so the table equals the reference's bit for bit.
+            REQUIRE(m.nF > 0, "upload_meshes: emitter mesh without triangles");
+            EmitterInfo e; memset(&e, 0, sizeof(e));
+            e.mesh = i; e.radiance[0] = m.radiance[0]; e.radiance[1] = m.radiance[1]; e.radiance[2] = m.radiance[2];
+            e.cdfOffset = (uint32_t) cdf.size(); e.nTris = m.nF; e.triOffset = (uint32_t) fo;
+            cdf.push_back(0.0f);
+            for (uint32_t f = 0; f < m.nF; ++f) {
+                const float4 &A = vpos[vo + m.F[3 * f]], &B = vpos[vo + m.F[3 * f + 1]], &C = vpos[vo + m.F[3 * f + 2]];
+                V3 p0 = mk(A.x, A.y, A.z), p1 = mk(B.x, B.y, B.z), p2 = mk(C.x, C.y, C.z);
+                volatile float area = 0.5f * sqrtf(squaredNorm(cross(p1 - p0, p2 - p0)));
+                cdf.push_back(cdf.back() + area);
+            }
+            float sum = cdf.back();
+            if (sum > 0) {
+                float norm = 1.0f / sum;
+                for (size_t k = e.cdfOffset + 1; k < cdf.size(); ++k) cdf[k] *= norm;
+                cdf.back() = 1.0f;
+            }
+            e.area = sum;
+            mi.emitter = (int) ctx->emitters.size();
+            ctx->emitters.push_back(e);
+        }
+        ctx->meshes.push_back(mi);
+        vo += m.nV; fo += m.nF;
+    }
+    ctx->nTris = (uint32_t) nF; ctx->nVerts = (uint32_t) nV;
+    CK(cudaMalloc((void **) &ctx->d_vpos, nV * sizeof(float4))); CK(cudaMalloc((void **) &ctx->d_vnrm, nV * sizeof(float4)));
+    CK(cudaMalloc((void **) &ctx->d_vuv, nV * sizeof(float2))); CK(cudaMalloc((void **) &ctx->d_tris, nF * sizeof(uint4)));
+    CK(cudaMalloc((void **) &ctx->d_meshes, ctx->meshes.size() * sizeof(MeshInfo)));
+    CK(cudaMalloc((void **) &ctx->d_emitters, std::max<size_t>(1, ctx->emitters.size()) * sizeof(EmitterInfo)));
+    CK(cudaMalloc((void **) &ctx->d_cdf, std::max<size_t>(1, cdf.size()) * sizeof(float)));
+    CK(cudaMemcpy(ctx->d_vpos, vpos.data(), nV * sizeof(float4), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_vnrm, vnrm.data(), nV * sizeof(float4), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_vuv, vuv.data(), nV * sizeof(float2), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_tris, tris.data(), nF * sizeof(uint4), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_meshes, ctx->meshes.data(), ctx->meshes.size() * sizeof(MeshInfo), cudaMemcpyHostToDevice));
+    if (!ctx->emitters.empty()) CK(cudaMemcpy(ctx->d_emitters, ctx->emitters.data(), ctx->emitters.size() * sizeof(EmitterInfo), cudaMemcpyHostToDevice));
+    if (!cdf.empty()) CK(cudaMemcpy(ctx->d_cdf, cdf.data(), cdf.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_set_camera(nori_gpu_ctx *ctx, const NoriGpuCameraDesc *cam) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(cam && cam->width > 0 && cam->height > 0, "set_camera: bad output size");
+    memcpy(ctx->cam.s2c, cam->sample_to_camera, 64); memcpy(ctx->cam.c2w, cam->camera_to_world, 64);
+    ctx->cam.width = cam->width; ctx->cam.height = cam->height;
+    ctx->cam.nearClip = cam->near_clip; ctx->cam.farClip = cam->far_clip;
+    ctx->cam.invW = 1.0f / (float) cam->width; ctx->cam.invH = 1.0f / (float) cam->height;   // perspective.cpp:38
+    ctx->haveCamera = true;
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_set_filter(nori_gpu_ctx *ctx, float radius, const float table33[33]) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(table33 && radius > 0, "set_filter: bad filter");
+    ctx->filter.radius = radius;
+    ctx->filter.border = (int) std::ceil(radius - 0.5f);                   // block.cpp:32
+    ctx->filter.lookupFactor = 32 / radius;                                // block.cpp:38 (NORI_FILTER_RESOLUTION 32)
+    memcpy(ctx->filter.table, table33, 33 * sizeof(float));
+    REQUIRE(ctx->filter.border <= kMaxBorder, "set_filter: filter radius above 4.5 is not supported");
+    ctx->haveFilter = true;
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_build_accel(nori_gpu_ctx *ctx, NoriGpuAccelStats *out) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(ctx->d_tris, "build_accel: upload meshes first");
+    CK(cudaSetDevice(ctx->device));
+    cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.leafTris); ctx->bvh = BvhDevice(); ctx->haveBvh = false;
+    NoriGpuAccelStats st;
+    if (!buildBvh(ctx->d_vpos, ctx->d_tris, ctx->nTris, ctx->bvhParams, ctx->stream, ctx->bvh, st, ctx->err)) return NORI_GPU_ECUDA;
+    ctx->haveBvh = true;
+    if (out) *out = st;
+    return NORI_GPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The render call: replaces the body of render() between BlockGenerator construction and
+// toBitmap (src/main.cpp:75-127).
+static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uint32_t *d_listPixel, const uint32_t *d_listSample, uint32_t listCount,
+                        NoriGpuRenderStats *out) {
+    const bool list = d_listPixel != nullptr;
+    REQUIRE(ctx->haveBvh && ctx->haveCamera && ctx->haveFilter, "render: scene, camera, filter and accel must be set first");
+    REQUIRE(d->integrator >= NORI_INT_NORMALS && d->integrator <= NORI_INT_AO, "render: unknown integrator");
+    REQUIRE(list || d->sample_last > d->sample_first, "render: empty sample range");
+    if (d->intersect_mode != NORI_ISECT_REFERENCE_MT) { ctx->err = "render: only NORI_ISECT_REFERENCE_MT is implemented"; return NORI_GPU_EUNSUPPORTED; }
+    if (!list && d->stream_mode == NORI_STREAM_BLOCK && d->integrator != NORI_INT_NORMALS && d->integrator != NORI_INT_SIMPLE) {
+        ctx->err = "render: NORI_STREAM_BLOCK (one serial PCG32 stream per block) is only reproducible for integrators that draw no random numbers (normals, simple)";
+        return NORI_GPU_EUNSUPPORTED;
+    }
+    CK(cudaSetDevice(ctx->device));
+    if (int r = ensurePool(ctx)) return r;
+    if (int r = ensureBlock(ctx)) return r;
+    cudaStream_t st = ctx->stream;
+    const int W = ctx->cam.width, H = ctx->cam.height;
+
+    RenderParams rp; memset(&rp, 0, sizeof(rp));
+    rp.integrator = d->integrator; rp.streamMode = d->stream_mode;
+    rp.sampleFirst = d->sample_first; rp.sampleCount = list ? 1 : d->sample_last - d->sample_first;
+    rp.rrStart = d->rr_start; rp.rrMax = d->rr_max; rp.maxDepth = d->max_depth;
+    rp.lightPos = mk(d->light_pos[0], d->light_pos[1], d->light_pos[2]);
+    rp.lightEnergy = mk(d->light_energy[0], d->light_energy[1], d->light_energy[2]);
+    rp.tilesX = (W + kTile - 1) / kTile; rp.tilesY = (H + kTile - 1) / kTile; rp.numTiles = (uint32_t) (rp.tilesX * rp.tilesY);
+    rp.block = ctx->d_block; rp.blockCols = W + 2 * ctx->filter.border; rp.blockRows = H + 2 * ctx->filter.border;
+    uint64_t totalSamples;
+    if (list) {
+        rp.K = rp.Klast = 1; rp.numPasses = 1; rp.passSlots = listCount; rp.totalIssue = listCount; rp.ring = 1;
+        rp.listPixel = d_listPixel; rp.listSample = d_listSample; totalSamples = listCount;
+    } else {
+        // pass = K samples of every pixel; sized to a few pool refills so stragglers never stall the ring
+        const uint64_t slotsPerSpp = (uint64_t) rp.numTiles * 1024u;
+        uint32_t K = (uint32_t) std::max<uint64_t>(1, (4ull * ctx->pool.capacity + slotsPerSpp - 1) / slotsPerSpp);
+        K = std::min(K, rp.sampleCount);
+        rp.K = K; rp.numPasses = (rp.sampleCount + K - 1) / K; rp.Klast = rp.sampleCount - (rp.numPasses - 1) * K;
+        rp.passSlots = slotsPerSpp * K; rp.ring = kMaxRing;
+        rp.totalIssue = (uint64_t) (rp.numPasses - 1) * rp.passSlots + slotsPerSpp * rp.Klast;
+        totalSamples = (uint64_t) W * H * rp.sampleCount;
+    }
+    const size_t recNeed = (size_t) rp.ring * rp.passSlots;
+    if (recNeed > ctx->recCap) {
+        cudaFree(ctx->recA); cudaFree(ctx->recB); ctx->recA = nullptr; ctx->recB = nullptr; ctx->recCap = 0;
+        CK(cudaMalloc((void **) &ctx->recA, recNeed * sizeof(float4))); CK(cudaMalloc((void **) &ctx->recB, recNeed * sizeof(float)));
+        ctx->recCap = recNeed;
+    }
+    const size_t tdNeed = (size_t) rp.ring * rp.numTiles;
+    if (tdNeed > ctx->tileDoneCap) {
+        cudaFree(ctx->tileDone); ctx->tileDone = nullptr;
+        CK(cudaMalloc((void **) &ctx->tileDone, tdNeed * sizeof(uint32_t))); ctx->tileDoneCap = tdNeed;
+    }
+    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone;
+    CK(cudaMemsetAsync(ctx->tileDone, 0, tdNeed * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), st));
+    CK(cudaMemsetAsync(ctx->pool.meta, 0, (size_t) ctx->pool.capacity * sizeof(uint4), st));
+    if (d->clear && !list) CK(cudaMemsetAsync(ctx->d_block, 0, ctx->blockFloats * sizeof(float), st));
+
+    const DeviceScene sc = deviceScene(ctx);
+    cudaEvent_t e0, e1, evCopy, stage[6];
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreateWithFlags(&evCopy, cudaEventDisableTiming));
+    for (auto &e : stage) CK(cudaEventCreate(&e));
+    StageTimes tm = {0, 0, 0, 0, 0};
+    CK(cudaEventRecord(e0, st));
+    uint64_t launches = 0;
+    // Iterations are enqueued in batches; the host looks at the counters of batch i while batch
+    // i+1 is already queued, so the device never waits for the host.
+    const int batch = ctx->profiling ? 1 : 8;
+    bool done = false;
+    uint64_t guard = 0;
+    const uint64_t samplesDoneTarget = totalSamples;
+    while (!done) {
+        for (int k = 0; k < batch; ++k) {
+            launches += (uint64_t) enqueueIteration(sc, ctx->pool, rp, ctx->d_counters, st, ctx->profiling ? stage : nullptr);
+            if (ctx->profiling) {
+                CK(cudaStreamSynchronize(st));
+                float ms;
+                cudaEventElapsedTime(&ms, stage[0], stage[1]); tm.generate += ms;
+                cudaEventElapsedTime(&ms, stage[1], stage[2]); tm.traceClosest += ms;
+                cudaEventElapsedTime(&ms, stage[2], stage[3]); tm.shade += ms;
+                cudaEventElapsedTime(&ms, stage[3], stage[4]); tm.traceShadow += ms;
+                cudaEventElapsedTime(&ms, stage[4], stage[5]); tm.splat += ms;
+            }
+        }
+        CK(cudaStreamSynchronize(st) == cudaSuccess ? cudaSuccess : cudaGetLastError());
+        CK(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(evCopy, st));
+        CK(cudaEventSynchronize(evCopy));
+        const Counters &hc = *ctx->h_counters;
+        const bool allFinished = hc.finished >= samplesDoneTarget;
+        const bool allSplatted = list || hc.completedPasses >= rp.numPasses;
+        done = allFinished && allSplatted;
+        if (++guard > 4000000ull) { ctx->err = "render: wavefront did not terminate (internal error)"; return NORI_GPU_ECUDA; }
+    }
+    // one more k_prepare-equivalent pass is not needed: counters of the last iteration are folded here
+    CK(cudaEventRecord(e1, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(evCopy); for (auto &e : stage) cudaEventDestroy(e);
+    if (out) {
+        const Counters &hc = *ctx->h_counters;
+        memset(out, 0, sizeof(*out));
+        uint64_t rays = hc.closestRays, shadows = hc.shadowRays + hc.shadowCount;
+        for (int k = 0; k < kNumKeys; ++k) rays += hc.sortCount[k];
+        out->camera_samples = hc.finished; out->closest_rays = rays; out->shadow_rays = shadows; out->segments = rays;
+        out->dropped = hc.dropped; out->iterations = hc.iterations; out->kernel_launches = launches; out->ms_total = ms;
+        out->ms_generate = tm.generate; out->ms_trace_closest = tm.traceClosest; out->ms_shade = tm.shade;
+        out->ms_trace_shadow = tm.traceShadow; out->ms_splat = tm.splat;
+    }
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuRenderStats *out) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(desc, "render: null descriptor");
+    if (desc->deterministic) { ctx->err = "render: deterministic splat order is only offered by nori_gpu_splat"; return NORI_GPU_EUNSUPPORTED; }
+    return runWavefront(ctx, desc, nullptr, nullptr, 0, out);
+}
+
+int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const uint32_t *pixel, const uint32_t *sample, float *rgb, float *pos) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(desc && n > 0 && pixel && sample && rgb, "sample_radiance: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<uint32_t> dp, ds;
+    CK(dp.alloc(n)); CK(ds.alloc(n));
+    CK(cudaMemcpy(dp.p, pixel, (size_t) n * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(ds.p, sample, (size_t) n * 4, cudaMemcpyHostToDevice));
+    NoriGpuRenderStats st;
+    if (int r = runWavefront(ctx, desc, dp.p, ds.p, (uint32_t) n, &st)) return r;
+    std::vector<float4> a(n); std::vector<float> b(n);
+    CK(cudaMemcpy(a.data(), ctx->recA, (size_t) n * 16, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(b.data(), ctx->recB, (size_t) n * 4, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; ++i) {
+        rgb[3 * i] = a[i].z; rgb[3 * i + 1] = a[i].w; rgb[3 * i + 2] = b[i];
+        if (pos) { pos[2 * i] = a[i].x; pos[2 * i + 1] = a[i].y; }
+    }
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_block_dims(const nori_gpu_ctx *ctx, int *rows, int *cols, int *border) {
+    if (!ctx || !ctx->haveCamera || !ctx->haveFilter) return NORI_GPU_EINVAL;
+    if (rows) *rows = ctx->cam.height + 2 * ctx->filter.border;
+    if (cols) *cols = ctx->cam.width + 2 * ctx->filter.border;
+    if (border) *border = ctx->filter.border;
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_block_device_ptr(nori_gpu_ctx *ctx, void **dptr, uint64_t *n_floats) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(ctx->haveCamera && ctx->haveFilter, "block_device_ptr: camera and filter must be set first");
+    CK(cudaSetDevice(ctx->device));
+    if (int r = ensureBlock(ctx)) return r;
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (dptr) *dptr = ctx->d_block;
+    if (n_floats) *n_floats = ctx->blockFloats;
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_download_block(nori_gpu_ctx *ctx, float *rgbw) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(rgbw && ctx->d_block, "download_block: nothing rendered");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(rgbw, ctx->d_block, ctx->blockFloats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_download_bitmap(nori_gpu_ctx *ctx, float *rgb) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(rgb && ctx->d_block, "download_bitmap: nothing rendered");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = (size_t) ctx->cam.width * ctx->cam.height * 3;
+    DevBuf<float> d; CK(d.alloc(n));
+    launchToBitmap(ctx->d_block, ctx->cam.width, ctx->cam.height, ctx->filter.border, d.p, ctx->stream);
+    CK(cudaMemcpyAsync(rgb, d.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return NORI_GPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Raw operators. Host arrays in, host arrays out; the work itself runs on the device.
+#define NEED_SCENE() REQUIRE(ctx->haveBvh, "operator needs an uploaded scene with a built accel")
+
+static void splitHits(const std::vector<float4> &h, const nori_gpu_ctx *ctx, int n, uint32_t *tri_id, uint32_t *mesh_id, float *tuv) {
+    for (int i = 0; i < n; ++i) {
+        uint32_t gid; memcpy(&gid, &h[i].w, 4);
+        if (gid == 0xffffffffu) { tri_id[i] = 0xffffffffu; if (mesh_id) mesh_id[i] = 0xffffffffu; }
+        else {
+            // global id -> (mesh, local index): meshes are concatenated in upload order
+            size_t lo = 0, hi = ctx->meshes.size();
+            while (hi - lo > 1) { size_t mid = (lo + hi) / 2; if (ctx->meshes[mid].triOffset <= gid) lo = mid; else hi = mid; }
+            tri_id[i] = gid - ctx->meshes[lo].triOffset; if (mesh_id) mesh_id[i] = (uint32_t) lo;
+        }
+        if (tuv) { tuv[3 * i] = h[i].x; tuv[3 * i + 1] = h[i].y; tuv[3 * i + 2] = h[i].z; }
+    }
+}
+
+int nori_gpu_trace(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint32_t *tri_id, uint32_t *mesh_id, float *tuv) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    NEED_SCENE(); REQUIRE(rays && tri_id && n >= 0, "trace: bad arguments");
+    if (n == 0) return NORI_GPU_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float4> dr, dh; CK(dr.alloc(2 * (size_t) n)); CK(dh.alloc(n));
+    CK(cudaMemcpyAsync(dr.p, rays, (size_t) n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    launchTrace(deviceScene(ctx), dr.p, n, shadow != 0, dh.p, ctx->stream);
+    std::vector<float4> h(n);
+    CK(cudaMemcpyAsync(h.data(), dh.p, (size_t) n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    splitHits(h, ctx, n, tri_id, mesh_id, tuv);
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_trace_device(nori_gpu_ctx *ctx, const void *d_rays, int n, int shadow, void *d_hits, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    NEED_SCENE(); REQUIRE(d_rays && d_hits && n > 0, "trace_device: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, ctx->stream));
+    launchTrace(deviceScene(ctx), (const float4 *) d_rays, n, shadow != 0, (float4 *) d_hits, ctx->stream);
+    CK(cudaEventRecord(e1, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    float t = 0; cudaEventElapsedTime(&t, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (ms) *ms = t;
+    return NORI_GPU_OK;
+}
+
+/// Traversal work counters of the device BVH for n rays: counts[0] = node visits (two child
+/// boxes each), counts[1] = triangle tests. Feeds the algorithmic-bytes figure of the roofline.
+int nori_gpu_trace_count(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint64_t counts[2]) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    NEED_SCENE(); REQUIRE(rays && counts && n > 0, "trace_count: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float4> dr, dh; DevBuf<unsigned long long> dc; CK(dr.alloc(2 * (size_t) n)); CK(dh.alloc(n)); CK(dc.alloc(2));
+    CK(cudaMemcpyAsync(dr.p, rays, (size_t) n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(dc.p, 0, 16, ctx->stream));
+    launchTraceCount(deviceScene(ctx), dr.p, n, shadow != 0, dh.p, dc.p, ctx->stream);
+    unsigned long long h[2];
+    CK(cudaMemcpyAsync(h, dc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    counts[0] = h[0]; counts[1] = h[1];
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_intersect(nori_gpu_ctx *ctx, const float *rays, int n, float *out24, int32_t *valid) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    NEED_SCENE(); REQUIRE(rays && out24 && valid && n >= 0, "intersect: bad arguments");
+    if (n == 0) return NORI_GPU_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float4> dr; DevBuf<float> dout; DevBuf<int> dv; CK(dr.alloc(2 * (size_t) n)); CK(dout.alloc(24 * (size_t) n)); CK(dv.alloc(n));
+    CK(cudaMemcpyAsync(dr.p, rays, (size_t) n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    launchIntersect(deviceScene(ctx), dr.p, n, dout.p, dv.p, ctx->stream);
+    CK(cudaMemcpyAsync(out24, dout.p, (size_t) n * 96, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(valid, dv.p, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_camera_rays(nori_gpu_ctx *ctx, const float *pixel_samples, int n, float *rays) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(ctx->haveCamera, "camera_rays: set the camera first"); REQUIRE(pixel_samples && rays && n >= 0, "camera_rays: bad arguments");
+    if (n == 0) return NORI_GPU_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float2> dp; DevBuf<float4> dr; CK(dp.alloc(n)); CK(dr.alloc(2 * (size_t) n));
+    CK(cudaMemcpyAsync(dp.p, pixel_samples, (size_t) n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    launchCameraRays(deviceScene(ctx), dp.p, n, dr.p, ctx->stream);
+    CK(cudaMemcpyAsync(rays, dr.p, (size_t) n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_bsdf_sample(nori_gpu_ctx *ctx, int bsdf_type, const float params[6], int n, const float *wi, const float *xi,
+                         float *wo, float *weight, float *pdf, float *eta, int32_t *measure) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(bsdf_type >= 0 && bsdf_type <= 3 && params && n > 0 && wi && xi && wo && weight && pdf && eta && measure, "bsdf_sample: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float> dwi, dxi, dwo, dw, dpdf, deta; DevBuf<int> dm;
+    CK(dwi.alloc(3 * (size_t) n)); CK(dxi.alloc(2 * (size_t) n)); CK(dwo.alloc(3 * (size_t) n)); CK(dw.alloc(3 * (size_t) n));
+    CK(dpdf.alloc(n)); CK(deta.alloc(n)); CK(dm.alloc(n));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(dwi.p, wi, (size_t) n * 12, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(dxi.p, xi, (size_t) n * 8, cudaMemcpyHostToDevice, st));
+    launchBsdfSample(makeBsdf(bsdf_type, params), n, dwi.p, dxi.p, dwo.p, dw.p, dpdf.p, deta.p, dm.p, st);
+    CK(cudaMemcpyAsync(wo, dwo.p, (size_t) n * 12, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(weight, dw.p, (size_t) n * 12, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(pdf, dpdf.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(eta, deta.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(measure, dm.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_bsdf_eval_pdf(nori_gpu_ctx *ctx, int bsdf_type, const float params[6], int n, const float *wi, const float *wo, float *f, float *pdf) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(bsdf_type >= 0 && bsdf_type <= 3 && params && n > 0 && wi && wo && f && pdf, "bsdf_eval_pdf: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float> dwi, dwo, df, dpdf;
+    CK(dwi.alloc(3 * (size_t) n)); CK(dwo.alloc(3 * (size_t) n)); CK(df.alloc(3 * (size_t) n)); CK(dpdf.alloc(n));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(dwi.p, wi, (size_t) n * 12, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(dwo.p, wo, (size_t) n * 12, cudaMemcpyHostToDevice, st));
+    launchBsdfEvalPdf(makeBsdf(bsdf_type, params), n, dwi.p, dwo.p, df.p, dpdf.p, st);
+    CK(cudaMemcpyAsync(f, df.p, (size_t) n * 12, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(pdf, dpdf.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_warp(nori_gpu_ctx *ctx, int warp_id, float param, int n, const float *xi, float *out3, float *pdf) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(warp_id >= 0 && warp_id <= 6 && n > 0 && xi && out3 && pdf, "warp: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float> dxi, dout, dpdf; CK(dxi.alloc(2 * (size_t) n)); CK(dout.alloc(3 * (size_t) n)); CK(dpdf.alloc(n));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(dxi.p, xi, (size_t) n * 8, cudaMemcpyHostToDevice, st));
+    launchWarp(warp_id, param, n, dxi.p, dout.p, dpdf.p, st);
+    CK(cudaMemcpyAsync(out3, dout.p, (size_t) n * 12, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(pdf, dpdf.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_pcg32(nori_gpu_ctx *ctx, uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(n > 0 && out, "pcg32: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<uint32_t> d; CK(d.alloc(n));
+    launchPcg32(initstate, initseq, advance, n, d.p, ctx->stream);
+    CK(cudaMemcpyAsync(out, d.p, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb, int deterministic, float *rgbw, uint64_t *dropped) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(ctx->haveCamera && ctx->haveFilter, "splat: set camera and filter first"); REQUIRE(n > 0 && pos && rgb && rgbw, "splat: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    const size_t cells = (size_t) (ctx->cam.width + 2 * ctx->filter.border) * (ctx->cam.height + 2 * ctx->filter.border);
+    DevBuf<float2> dp; DevBuf<float> dc, db; DevBuf<unsigned long long> dd;
+    CK(dp.alloc(n)); CK(dc.alloc(3 * (size_t) n)); CK(db.alloc(cells * 4)); CK(dd.alloc(1));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(dp.p, pos, (size_t) n * 8, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(dc.p, rgb, (size_t) n * 12, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(db.p, 0, cells * 16, st)); CK(cudaMemsetAsync(dd.p, 0, 8, st));
+    if (deterministic) launchSplatOrdered(deviceScene(ctx), n, dp.p, dc.p, db.p, dd.p, st);
+    else launchSplatList(deviceScene(ctx), n, dp.p, dc.p, db.p, dd.p, st);
+    unsigned long long hd = 0;
+    CK(cudaMemcpyAsync(rgbw, db.p, cells * 16, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(&hd, dd.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (dropped) *dropped = hd;
+    return NORI_GPU_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,85 @@
+// engine.h — host-side declarations shared by capi.cu, render.cu and operators.cu.
+#pragma once
+#include "scene.cuh"
+#include "bvh.h"
+#include <string>
+
+namespace ng {
+
+// meta.z bits of a path slot
+constexpr uint32_t kFlagAlive = 1u << 16;       // has a ray in flight
+constexpr uint32_t kFlagHasSample = 1u << 17;   // finished camera sample waiting to be recorded
+constexpr uint32_t kFlagDiscrete = 1u << 18;    // last bounce was a discrete BSDF (or the camera)
+constexpr uint32_t kFlagMulT = 1u << 19;        // final value = throughput * radiance (whitted)
+constexpr uint32_t kDepthMask = 0xffffu;
+constexpr int kNumKeys = 5;                     // diffuse, mirror, dielectric, microfacet, miss
+constexpr int kKeyMiss = 4;
+constexpr int kMaxRing = 4;
+constexpr int kTile = 32;                       // NORI_BLOCK_SIZE (include/nori/block.h:29)
+constexpr int kMaxBorder = 4;
+
+/// Wavefront path pool: structure of arrays, one entry per path slot.
+struct Pool {
+    uint32_t capacity;
+    float4 *rayO;        // o.xyz, mint
+    float4 *rayD;        // d.xyz, maxt
+    float4 *hit;         // t, u, v, bits(global triangle id | kNoHit)
+    float4 *thr;         // throughput rgb, BSDF pdf of the last sampled direction
+    float4 *rad;         // radiance rgb, eta product
+    ulonglong2 *rng;     // pcg32 state, inc
+    uint4 *meta;         // pixel index, sample index, flags | depth | ring slot << 24, record index
+    float2 *pos;         // pixelSample handed to ImageBlock::put
+    uint32_t *sortQueue; // kNumKeys x capacity slot indices, by material key of the hit
+    float4 *shadow;      // 3 x capacity: (o, maxt) (d, bits(slot)) (contribution, -)
+};
+
+struct Counters {
+    unsigned long long issue, issueLimit, finished;
+    unsigned long long closestRays, shadowRays, segments, dropped, iterations;
+    unsigned int sortCount[8];
+    unsigned int shadowCount;
+    unsigned int completedPasses;
+    unsigned int tilesSplatted[kMaxRing];   // cumulative per ring slot
+    unsigned int slotPass[kMaxRing];        // pass currently held by a ring slot
+    unsigned int pad[2];
+};
+
+struct RenderParams {
+    int integrator, streamMode;
+    uint32_t sampleFirst, sampleCount;
+    int rrStart; float rrMax; int maxDepth;
+    V3 lightPos, lightEnergy;
+    // issue order: pass-major, tile-major, sample, pixel-in-tile
+    int tilesX, tilesY; uint32_t numTiles;
+    uint32_t K, Klast, numPasses;
+    unsigned long long passSlots, totalIssue;
+    int ring;
+    // explicit sample list (nori_gpu_sample_radiance)
+    const uint32_t *listPixel, *listSample;
+    // sample records of the passes in flight
+    float4 *recA; float *recB;
+    uint32_t *tileDone;                      // ring x numTiles
+    float *block;                            // (H+2b) x (W+2b) x RGBW accumulator
+    int blockCols, blockRows;
+};
+
+struct StageTimes { float generate, traceClosest, shade, traceShadow, splat; };
+
+/// One wavefront iteration, enqueued on `st`. Returns the number of kernel launches.
+int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,
+                     cudaEvent_t *stageEvents /* 6 or nullptr */);
+
+// raw operators (operators.cu); all pointers are device pointers
+void launchTrace(const DeviceScene &sc, const float4 *rays /* 2 per ray */, int n, bool shadow, float4 *hits, cudaStream_t st);
+void launchTraceCount(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned long long *counts2, cudaStream_t st);
+void launchIntersect(const DeviceScene &sc, const float4 *rays, int n, float *out24, int *valid, cudaStream_t st);
+void launchCameraRays(const DeviceScene &sc, const float2 *ps, int n, float4 *rays, cudaStream_t st);
+void launchBsdfSample(Bsdf b, int n, const float *wi, const float *xi, float *wo, float *weight, float *pdf, float *eta, int *measure, cudaStream_t st);
+void launchBsdfEvalPdf(Bsdf b, int n, const float *wi, const float *wo, float *f, float *pdf, cudaStream_t st);
+void launchWarp(int id, float param, int n, const float *xi, float *out3, float *pdf, cudaStream_t st);
+void launchPcg32(uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out, cudaStream_t st);
+void launchSplatList(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
+void launchSplatOrdered(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
+void launchToBitmap(const float *block, int W, int H, int border, float *rgb, cudaStream_t st);
+
+} // namespace ng

@@ -1,0 +1,332 @@
+// nmath.cuh — device-side arithmetic of the Nori hot path (sm_100a).
+//
+// Every function states the reference code it stands in for (paths relative to the reference
+// tree). The translation unit is compiled with -fmad=false and IEEE division/sqrt so that the
+// operation order written here is the order executed: Moeller-Trumbore, camera rays, frames and
+// the PCG32 stream then agree bit for bit with the x86-64 build of the reference (which has no
+// FMA), and only libm calls (sin/cos/log/exp) differ in the last ulp.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+namespace ng {
+
+#define NG_HD __host__ __device__ __forceinline__
+#define NG_D __device__ __forceinline__
+
+constexpr float kEpsilon = 1e-4f;                    // include/nori/common.h:50
+constexpr float kPi = 3.14159265358979323846f;       // common.h:55
+constexpr float kInvPi = 0.31830988618379067154f;    // common.h:56
+
+struct V2 { float x, y; };
+struct V3 { float x, y, z; };
+
+NG_HD V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+NG_HD V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+NG_HD V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+NG_HD V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+NG_HD V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+NG_HD V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+NG_HD V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }   // Color3f cwise product
+NG_HD V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+NG_HD bool isZero(V3 c) { return c.x == 0.0f && c.y == 0.0f && c.z == 0.0f; }
+NG_HD float maxCoeff(V3 c) { return fmaxf(c.x, fmaxf(c.y, c.z)); }
+
+/// Eigen fixed-size 3-vector reduction x0 + (x1 + x2) (ext/eigen/Eigen/src/Core/Redux.h:94-103)
+NG_HD float dot(V3 a, V3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
+/// Eigen cross (ext/eigen/Eigen/src/Geometry/OrthoMethods.h:43-47)
+NG_HD V3 cross(V3 a, V3 b) { return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+NG_HD float squaredNorm(V3 a) { return dot(a, a); }
+/// Eigen normalized(): divides by sqrt(squaredNorm) when it is > 0 (Eigen/src/Core/Dot.h:123-133)
+NG_HD V3 normalized(V3 a) {
+    float z = squaredNorm(a);
+    if (z > 0.0f) return a / sqrtf(z);
+    return a;
+}
+/// normalized() of a run-time-sized Eigen expression (the `N.col(i)` sum of src/accel.cpp:101-104):
+/// sequential reduction (x0 + x1) + x2.
+NG_HD V3 normalizedDynamic(V3 a) {
+    float z = (a.x * a.x + a.y * a.y) + a.z * a.z;
+    if (z > 0.0f) return a / sqrtf(z);
+    return a;
+}
+
+// ---- pcg32 (ext/pcg32/pcg32.h:40-161) and the `independent` sampler (src/independent.cpp) ----
+struct Pcg32 {
+    uint64_t state, inc;
+    NG_HD void seed(uint64_t initstate, uint64_t initseq) {      // pcg32.h:55-61
+        state = 0u;
+        inc = (initseq << 1u) | 1u;
+        nextUInt();
+        state += initstate;
+        nextUInt();
+    }
+    NG_HD uint32_t nextUInt() {                                   // pcg32.h:64-70
+        uint64_t old = state;
+        state = old * 0x5851f42d4c957f2dULL + inc;
+        uint32_t xorshifted = (uint32_t) (((old >> 18u) ^ old) >> 27u);
+        uint32_t rot = (uint32_t) (old >> 59u);
+        return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+    }
+    NG_HD float nextFloat() {                                     // pcg32.h:104-112
+        uint32_t u = (nextUInt() >> 9) | 0x3f800000u;
+#ifdef __CUDA_ARCH__
+        return __uint_as_float(u) - 1.0f;
+#else
+        union { uint32_t u; float f; } x; x.u = u; return x.f - 1.0f;
+#endif
+    }
+    NG_HD void advance(int64_t delta_) {                          // pcg32.h:140-161
+        uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+        uint64_t delta = (uint64_t) delta_;
+        while (delta > 0) {
+            if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+            cur_plus = (cur_mult + 1) * cur_plus;
+            cur_mult *= cur_mult;
+            delta /= 2;
+        }
+        state = acc_mult * state + acc_plus;
+    }
+    NG_HD float next1D() { return nextFloat(); }                  // independent.cpp:58-60
+    /// independent.cpp:62-67 builds Point2f(nextFloat(), nextFloat()); the reference's x86-64 g++
+    /// build evaluates the arguments right to left, so the first draw is y (oracle pin
+    /// tests/test_oracle_pins.py::test_next2d_order).
+    NG_HD V2 next2D() { V2 r; r.y = nextFloat(); r.x = nextFloat(); return r; }
+};
+
+// ---- frames, Fresnel (include/nori/frame.h, src/common.cpp) --------------------------------
+/// src/common.cpp:260-269
+NG_HD void coordinateSystem(V3 a, V3 &b, V3 &c) {
+    if (fabsf(a.x) > fabsf(a.y)) {
+        float invLen = 1.0f / sqrtf(a.x * a.x + a.z * a.z);
+        c = mk(a.z * invLen, 0.0f, -a.x * invLen);
+    } else {
+        float invLen = 1.0f / sqrtf(a.y * a.y + a.z * a.z);
+        c = mk(0.0f, a.z * invLen, -a.y * invLen);
+    }
+    b = cross(c, a);
+}
+
+/// include/nori/frame.h:32-62
+struct Frame {
+    V3 s, t, n;
+    NG_HD Frame() {}
+    NG_HD explicit Frame(V3 n_) : n(n_) { coordinateSystem(n, s, t); }
+    NG_HD V3 toLocal(V3 v) const { return mk(dot(v, s), dot(v, t), dot(v, n)); }
+    NG_HD V3 toWorld(V3 v) const { return (s * v.x + t * v.y) + n * v.z; }
+};
+
+/// src/common.cpp:271-300
+NG_HD float fresnel(float cosThetaI, float extIOR, float intIOR) {
+    float etaI = extIOR, etaT = intIOR;
+    if (extIOR == intIOR) return 0.0f;
+    if (cosThetaI < 0.0f) { float tmp = etaI; etaI = etaT; etaT = tmp; cosThetaI = -cosThetaI; }
+    float eta = etaI / etaT, sinThetaTSqr = eta * eta * (1 - cosThetaI * cosThetaI);
+    if (sinThetaTSqr > 1.0f) return 1.0f;
+    float cosThetaT = sqrtf(1.0f - sinThetaTSqr);
+    float Rs = (etaI * cosThetaI - etaT * cosThetaT) / (etaI * cosThetaI + etaT * cosThetaT);
+    float Rp = (etaT * cosThetaI - etaI * cosThetaT) / (etaT * cosThetaI + etaI * cosThetaT);
+    return (Rs * Rs + Rp * Rp) / 2.0f;
+}
+
+/// Color3f::isValid (src/common.cpp:210-217)
+NG_HD bool isValidColor(V3 c) {
+    if (c.x < 0 || !isfinite(c.x)) return false;
+    if (c.y < 0 || !isfinite(c.y)) return false;
+    if (c.z < 0 || !isfinite(c.z)) return false;
+    return true;
+}
+
+// ---- rays (include/nori/ray.h:49-77) ---------------------------------------------------------
+struct Ray {
+    V3 o, d;
+    float mint, maxt;
+};
+NG_HD Ray mkRay(V3 o, V3 d, float mint = kEpsilon, float maxt = INFINITY) {
+    Ray r; r.o = o; r.d = d; r.mint = mint; r.maxt = maxt; return r;
+}
+
+/// Mesh::rayIntersect (src/mesh.cpp:51-88), operation for operation. The reference compares
+/// u, v against double literals (`u < 0.0 || u > 1.0`): float->double promotion is exact, so the
+/// float comparisons below are the same predicates.
+NG_HD bool rayTriangle(V3 p0, V3 p1, V3 p2, V3 o, V3 d, float mint, float maxt, float &u, float &v, float &t) {
+    V3 edge1 = p1 - p0, edge2 = p2 - p0;
+    V3 pvec = cross(d, edge2);
+    float det = dot(edge1, pvec);
+    if (det > -1e-8f && det < 1e-8f) return false;
+    float inv_det = 1.0f / det;
+    V3 tvec = o - p0;
+    u = dot(tvec, pvec) * inv_det;
+    if (u < 0.0f || u > 1.0f) return false;
+    V3 qvec = cross(tvec, edge1);
+    v = dot(d, qvec) * inv_det;
+    if (v < 0.0f || u + v > 1.0f) return false;
+    t = dot(edge2, qvec) * inv_det;
+    return t >= mint && t <= maxt;
+}
+
+// ---- warps (include/nori/warp.h:30-69; the reference's src/warp.cpp:33-79 throws: course spec) -
+NG_HD float tent1(float xi) { return xi < 0.5f ? sqrtf(2.0f * xi) - 1.0f : 1.0f - sqrtf(2.0f - 2.0f * xi); }
+NG_HD V2 squareToTent(V2 s) { V2 r; r.x = tent1(s.x); r.y = tent1(s.y); return r; }
+NG_HD float squareToTentPdf(V2 p) {
+    float ax = fabsf(p.x), ay = fabsf(p.y);
+    return (ax <= 1.0f && ay <= 1.0f) ? (1.0f - ax) * (1.0f - ay) : 0.0f;
+}
+NG_HD V2 squareToUniformDisk(V2 s) {
+    float r = sqrtf(s.x), phi = 2.0f * kPi * s.y;
+    V2 p; p.x = r * cosf(phi); p.y = r * sinf(phi);
+    return p;
+}
+NG_HD float squareToUniformDiskPdf(V2 p) { return (p.x * p.x + p.y * p.y <= 1.0f) ? kInvPi : 0.0f; }
+NG_HD V3 squareToUniformSphere(V2 s) {
+    float z = 1.0f - 2.0f * s.x, r = sqrtf(fmaxf(0.0f, 1.0f - z * z)), phi = 2.0f * kPi * s.y;
+    return mk(r * cosf(phi), r * sinf(phi), z);
+}
+NG_HD float squareToUniformSpherePdf(V3) { return 0.25f * kInvPi; }
+NG_HD V3 squareToUniformHemisphere(V2 s) {
+    float z = s.x, r = sqrtf(fmaxf(0.0f, 1.0f - z * z)), phi = 2.0f * kPi * s.y;
+    return mk(r * cosf(phi), r * sinf(phi), z);
+}
+NG_HD float squareToUniformHemispherePdf(V3 v) { return v.z >= 0.0f ? 0.5f * kInvPi : 0.0f; }
+NG_HD V3 squareToCosineHemisphere(V2 s) {
+    V2 d = squareToUniformDisk(s);
+    float z = sqrtf(fmaxf(0.0f, 1.0f - d.x * d.x - d.y * d.y));
+    return mk(d.x, d.y, z);
+}
+NG_HD float squareToCosineHemispherePdf(V3 v) { return v.z > 0.0f ? v.z * kInvPi : 0.0f; }
+NG_HD V3 squareToBeckmann(V2 s, float alpha) {
+    float phi = 2.0f * kPi * s.x;
+    float tan2 = -alpha * alpha * logf(1.0f - s.y);
+    float cosTheta = 1.0f / sqrtf(1.0f + tan2);
+    float sinTheta = sqrtf(fmaxf(0.0f, 1.0f - cosTheta * cosTheta));
+    return mk(sinTheta * cosf(phi), sinTheta * sinf(phi), cosTheta);
+}
+NG_HD float squareToBeckmannPdf(V3 m, float alpha) {
+    if (m.z <= 0.0f) return 0.0f;
+    float c2 = m.z * m.z, tan2 = (1.0f - c2) / c2, a2 = alpha * alpha;
+    return expf(-tan2 / a2) / (kPi * a2 * c2 * m.z);
+}
+
+// ---- BSDFs (include/nori/bsdf.h:29-112) ------------------------------------------------------
+enum Measure { kUnknownMeasure = 0, kSolidAngle = 1, kDiscrete = 2 };      // common.h EMeasure
+enum BsdfType { kDiffuse = 0, kMirror = 1, kDielectric = 2, kMicrofacet = 3 };
+
+struct BsdfQuery { V3 wi, wo; float eta; int measure; };
+
+struct Bsdf {
+    int type;
+    V3 albedo;                 // diffuse albedo / microfacet kd
+    float alpha, intIOR, extIOR, ks;
+
+    NG_HD bool isDiffuse() const { return type == kDiffuse || type == kMicrofacet; }
+
+    /// Beckmann shadowing-masking, rational approximation (course definition; pinned by
+    /// scenes/pa5/tests/ttest-microfacet.xml through the oracle)
+    static NG_HD float g1(V3 wv, V3 wh, float alpha) {
+        if (dot(wv, wh) / wv.z <= 0.0f) return 0.0f;
+        float c = wv.z, t2 = 1.0f - c * c;
+        if (t2 <= 0.0f) return 1.0f;
+        float tanTheta = sqrtf(t2) / c;                 // Frame::tanTheta (frame.h:82-87)
+        float b = 1.0f / (alpha * tanTheta);
+        if (b >= 1.6f) return 1.0f;
+        float b2 = b * b;
+        return (3.535f * b + 2.181f * b2) / (1.0f + 2.276f * b + 2.577f * b2);
+    }
+
+    NG_HD V3 eval(const BsdfQuery &q) const {
+        switch (type) {
+        case kDiffuse:                                   // src/diffuse.cpp:35-45
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return mk(0, 0, 0);
+            return albedo * kInvPi;
+        case kMicrofacet: {                              // src/microfacet.cpp:52-54 (spec at :65-69)
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return mk(0, 0, 0);
+            V3 wh = normalized(q.wi + q.wo);
+            float D = squareToBeckmannPdf(wh, alpha) / wh.z;
+            float F = fresnel(dot(wh, q.wi), extIOR, intIOR);
+            float G = g1(q.wi, wh, alpha) * g1(q.wo, wh, alpha);
+            float spec = ks * D * F * G / (4.0f * q.wi.z * q.wo.z);
+            return albedo * kInvPi + mk(spec, spec, spec);
+        }
+        default: return mk(0, 0, 0);                     // mirror.cpp:31-34, dielectric.cpp:35-38
+        }
+    }
+
+    NG_HD float pdf(const BsdfQuery &q) const {
+        switch (type) {
+        case kDiffuse:                                   // src/diffuse.cpp:48-62
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return 0.0f;
+            return kInvPi * q.wo.z;
+        case kMicrofacet: {                              // src/microfacet.cpp:57-59
+            if (q.measure != kSolidAngle || q.wi.z <= 0 || q.wo.z <= 0) return 0.0f;
+            V3 wh = normalized(q.wi + q.wo);
+            float jac = 1.0f / (4.0f * dot(wh, q.wo));
+            return ks * squareToBeckmannPdf(wh, alpha) * jac + (1.0f - ks) * q.wo.z * kInvPi;
+        }
+        default: return 0.0f;
+        }
+    }
+
+    /// BSDF::sample: returns eval*cos/pdf, fills wo/measure/eta; zero = failed sample.
+    NG_HD V3 sample(BsdfQuery &q, V2 s) const {
+        switch (type) {
+        case kDiffuse:                                   // src/diffuse.cpp:65-83
+            if (q.wi.z <= 0) return mk(0, 0, 0);
+            q.measure = kSolidAngle;
+            q.wo = squareToCosineHemisphere(s);
+            q.eta = 1.0f;
+            return albedo;
+        case kMirror:                                    // src/mirror.cpp:39-55
+            if (q.wi.z <= 0) return mk(0, 0, 0);
+            q.wo = mk(-q.wi.x, -q.wi.y, q.wi.z);
+            q.measure = kDiscrete;
+            q.eta = 1.0f;
+            return mk(1, 1, 1);
+        case kDielectric: {                              // src/dielectric.cpp:45-47 throws; DESIGN.md "unpinned"
+            float cosThetaI = q.wi.z;
+            float F = fresnel(cosThetaI, extIOR, intIOR);
+            q.measure = kDiscrete;
+            if (s.x < F) {
+                q.wo = mk(-q.wi.x, -q.wi.y, q.wi.z);
+                q.eta = 1.0f;
+                return mk(1, 1, 1);
+            }
+            bool entering = cosThetaI > 0.0f;
+            float eta = entering ? extIOR / intIOR : intIOR / extIOR;
+            float cosThetaT = sqrtf(fmaxf(0.0f, 1.0f - eta * eta * (1.0f - cosThetaI * cosThetaI)));
+            q.wo = mk(-eta * q.wi.x, -eta * q.wi.y, entering ? -cosThetaT : cosThetaT);
+            q.eta = entering ? intIOR / extIOR : extIOR / intIOR;
+            float w = eta * eta;
+            return mk(w, w, w);
+        }
+        case kMicrofacet: {                              // src/microfacet.cpp:62-74
+            if (q.wi.z <= 0) return mk(0, 0, 0);
+            q.measure = kSolidAngle;
+            q.eta = 1.0f;
+            if (s.x < ks) {
+                V2 r; r.x = s.x / ks; r.y = s.y;
+                V3 n = squareToBeckmann(r, alpha);
+                q.wo = n * (2.0f * dot(q.wi, n)) - q.wi;
+            } else {
+                V2 r; r.x = (s.x - ks) / (1.0f - ks); r.y = s.y;
+                q.wo = squareToCosineHemisphere(r);
+            }
+            if (q.wo.z <= 0) return mk(0, 0, 0);
+            float p = pdf(q);
+            if (!(p > 0.0f)) return mk(0, 0, 0);
+            return eval(q) * q.wo.z / p;
+        }
+        }
+        return mk(0, 0, 0);
+    }
+};
+
+NG_HD Bsdf makeBsdf(int type, const float *p /* albedo|kd rgb, alpha, intIOR, extIOR */) {
+    Bsdf b;
+    b.type = type; b.albedo = mk(p[0], p[1], p[2]); b.alpha = p[3]; b.intIOR = p[4]; b.extIOR = p[5];
+    b.ks = 1.0f - maxCoeff(b.albedo);                    // src/microfacet.cpp:48
+    if (type == kMirror || type == kDielectric) b.albedo = mk(0, 0, 0);
+    return b;
+}
+
+} // namespace ng

@@ -1,0 +1,546 @@
+// render.cu — the wavefront path tracer: everything the reference runs inside
+// `tbb::parallel_for` (src/main.cpp:93-121: renderBlock -> Camera::sampleRay -> Integrator::Li ->
+// ImageBlock::put) as a fixed pool of path slots advanced by one bounce per iteration:
+//
+//   k_prepare      (1 thread)  statistics, ring bookkeeping, sample issue limit
+//   k_finishRegen  (slot)      record finished camera samples; draw new ones in place
+//                              (Sampler stream + PerspectiveCamera::sampleRay)
+//   k_traceClosest (slot)      Accel::rayIntersect(ray, its, false); queue the slot by material
+//   k_shade        (queue)     one Li loop body per path: emitter, next-event estimation (queues a
+//                              shadow ray), BSDF sample, Russian roulette — material-sorted
+//   k_traceShadow  (queue)     Accel::rayIntersect(ray, its, true); add unoccluded contributions
+//   k_splat        (tile)      ImageBlock::put for all samples of a finished 32x32 tile, accumulated
+//                              in shared memory, then added to the full-frame block
+//
+// Integrator semantics follow oracle/noracle_integrators.h statement for statement (the reference
+// ships no Integrator subclass: SURVEY.md F3), including the order in which a path consumes its
+// random numbers, so that a camera sample yields the same radiance on both sides.
+#include "engine.h"
+#include "traverse.cuh"
+
+namespace ng {
+
+__device__ __forceinline__ unsigned laneId() { return threadIdx.x & 31u; }
+__device__ __forceinline__ unsigned lanemaskLt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
+
+/// Warp-aggregated `atomicAdd(counter, 1)` for the lanes with pred set; returns this lane's index.
+__device__ __forceinline__ uint32_t warpAppend(unsigned int *counter, bool pred) {
+    unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (!m) return 0;
+    int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int) laneId() == leader) base = atomicAdd(counter, (unsigned) __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(m & lanemaskLt());
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void k_prepare(Counters *c, RenderParams rp) {
+    unsigned rays = 0;
+    for (int k = 0; k < kNumKeys; ++k) { rays += c->sortCount[k]; c->sortCount[k] = 0; }
+    c->closestRays += rays; c->segments += rays;
+    c->shadowRays += c->shadowCount; c->shadowCount = 0;
+    c->iterations++;
+    unsigned cp = c->completedPasses;
+    while (cp < rp.numPasses && c->tilesSplatted[cp % rp.ring] >= rp.numTiles * (cp / rp.ring + 1)) ++cp;
+    c->completedPasses = cp;
+    for (int s = 0; s < rp.ring; ++s) c->slotPass[s] = s + rp.ring * (c->tilesSplatted[s] / rp.numTiles);
+    unsigned long long limitPass = min((unsigned long long) rp.numPasses, (unsigned long long) cp + rp.ring);
+    unsigned long long limit = limitPass == rp.numPasses ? rp.totalIssue : limitPass * rp.passSlots;
+    if (rp.listPixel) limit = rp.totalIssue;
+    if (c->issue > limit) c->issue = limit;       // lanes that overshot discarded their index
+    c->issueLimit = limit;
+}
+
+/// Pixel of slot r (< 1024) inside a tile: warps cover 8x4 pixel patches (coherent primary rays).
+__device__ __forceinline__ void tilePixel(uint32_t pix, int &lx, int &ly) {
+    uint32_t w = pix >> 5, l = pix & 31u;
+    lx = (int) ((w & 3u) * 8u + (l & 7u));
+    ly = (int) ((w >> 2) * 4u + (l >> 3));
+}
+
+__global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;      // capacity is a multiple of 256
+    uint4 meta = pool.meta[i];
+    const bool dead = !(meta.z & kFlagAlive);
+    const int W = sc.cam.width, H = sc.cam.height;
+
+    // ---- record a finished camera sample -------------------------------------------------
+    const bool fin = dead && (meta.z & kFlagHasSample);
+    if (fin) {
+        float4 rad = pool.rad[i];
+        V3 L = mk(rad.x, rad.y, rad.z);
+        if (meta.z & kFlagMulT) { float4 t = pool.thr[i]; L = mk(t.x, t.y, t.z) * L; }
+        const uint32_t slot = meta.z >> 24;
+        const size_t r = (size_t) slot * rp.passSlots + meta.w;
+        float2 ps = pool.pos[i];
+        rp.recA[r] = make_float4(ps.x, ps.y, L.x, L.y);
+        rp.recB[r] = L.z;
+    }
+    if (!rp.listPixel) {
+        // one atomic per (ring slot, tile) present in the warp
+        uint32_t tile = 0xffffffffu;
+        if (fin) {
+            uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
+            tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
+        }
+        unsigned peers = __match_any_sync(0xffffffffu, tile);
+        if (fin && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
+    }
+    {
+        unsigned m = __ballot_sync(0xffffffffu, fin);
+        if (m && (int) laneId() == __ffs(m) - 1) atomicAdd(&c->finished, (unsigned long long) __popc(m));
+    }
+
+    // ---- draw the next camera sample into the free slot ------------------------------------
+    bool need = dead;
+    const unsigned long long limit = c->issueLimit;
+    uint32_t x = 0, y = 0, sampleK = 0, rec = 0, slot = 0;
+    int lx = 0, ly = 0, ox = 0, oy = 0;
+    for (;;) {
+        unsigned m = __ballot_sync(0xffffffffu, need);
+        if (!m) break;
+        int leader = __ffs(m) - 1;
+        unsigned long long base = 0;
+        if ((int) laneId() == leader) base = atomicAdd(&c->issue, (unsigned long long) __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (base >= limit) break;
+        if (need) {
+            unsigned long long g = base + __popc(m & lanemaskLt());
+            if (g < limit) {
+                if (rp.listPixel) {
+                    uint32_t p = rp.listPixel[g];
+                    x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g; slot = 0;
+                    need = false;
+                } else {
+                    uint32_t pass = (uint32_t) (g / rp.passSlots), j = (uint32_t) (g % rp.passSlots);
+                    uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
+                    uint32_t tile = j / (1024u * Kp), r = j % (1024u * Kp);
+                    tilePixel(r & 1023u, lx, ly);
+                    ox = (int) (tile % (uint32_t) rp.tilesX) * kTile; oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
+                    x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
+                    if (tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H) {
+                        sampleK = pass * rp.K + (r >> 10); rec = j; slot = pass % (uint32_t) rp.ring;
+                        need = false;
+                    }
+                }
+            }
+        }
+    }
+    if (!dead) return;
+    if (need) {                                   // nothing left to issue: the slot stays empty
+        if (meta.z != 0) { meta.z = 0; pool.meta[i] = meta; }
+        return;
+    }
+    Pcg32 rng;
+    const uint32_t sampleIndex = rp.sampleFirst + sampleK;
+    if (rp.streamMode == NORI_STREAM_PER_SAMPLE || rp.listPixel) {
+        rng.seed((uint64_t) y * (uint64_t) W + x, (uint64_t) sampleIndex);
+    } else {
+        // src/independent.cpp:48-53: seed(offset.x, offset.y); renderBlock (src/main.cpp:49-66)
+        // consumes 4 values per camera sample in (y, x, sample) order when Li draws none.
+        const int bw = min(W - ox, kTile);
+        rng.seed((uint64_t) (int64_t) ox, (uint64_t) (int64_t) oy);
+        rng.advance(4ll * (((long long) ly * bw + lx) * (long long) rp.sampleCount + sampleK));
+    }
+    V2 r2 = rng.next2D();
+    V2 ps; ps.x = (float) x + r2.x; ps.y = (float) y + r2.y;      // src/main.cpp:52
+    rng.next2D();                                                // apertureSample (main.cpp:53)
+    Ray ray = sampleRay(sc.cam, ps);
+    pool.rayO[i] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
+    pool.rayD[i] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
+    pool.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+    pool.rad[i] = make_float4(0.f, 0.f, 0.f, 1.f);
+    pool.rng[i] = make_ulonglong2(rng.state, rng.inc);
+    pool.pos[i] = make_float2(ps.x, ps.y);
+    pool.meta[i] = make_uint4(y * (uint32_t) W + x, sampleIndex, kFlagAlive | kFlagDiscrete | (slot << 24), rec);
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_traceClosest(DeviceScene sc, Pool pool, Counters *c) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool alive = pool.meta[i].z & kFlagAlive;
+    int key = -1;
+    if (alive) {
+        const float4 ro = pool.rayO[i], rd = pool.rayD[i];
+        float t = 0.f, u = 0.f, v = 0.f;
+        uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), ro.w, rd.w, t, u, v);
+        pool.hit[i] = make_float4(t, u, v, __uint_as_float(gid));
+        key = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
+    }
+    // material-sorted queues: one atomic per key present in the warp
+    unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (alive) {
+        int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if ((int) laneId() == leader) base = atomicAdd(&c->sortCount[key], (unsigned) __popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        pool.sortQueue[(size_t) key * pool.capacity + base + __popc(peers & lanemaskLt())] = i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// `area` emitter (oracle/noracle_integrators.h:55-88, noracle_scene.h:135-147)
+struct LightSample { V3 p, n, wi; float dist, pdf; V3 Le; };
+
+/// DiscretePDF::sample (include/nori/dpdf.h:118-123): lower_bound on the CDF.
+__device__ __forceinline__ uint32_t cdfSample(const float *__restrict__ cdf, uint32_t nEntries /* size()+1 */, float v) {
+    uint32_t lo = 0, len = nEntries;
+    while (len > 0) {                              // std::lower_bound
+        uint32_t half = len >> 1;
+        if (__ldg(cdf + lo + half) < v) { lo += half + 1; len -= half + 1; } else len = half;
+    }
+    int idx = max(0, (int) lo - 1);
+    return min((uint32_t) idx, nEntries - 2);
+}
+
+__device__ __forceinline__ void emitterSamplePoint(const DeviceScene &s, const EmitterInfo &em, V2 xi, V3 &p, V3 &n) {
+    const float *cdf = s.emitterCdf + em.cdfOffset;
+    float x = xi.x;
+    uint32_t f = cdfSample(cdf, em.nTris + 1, x);
+    float c0 = __ldg(cdf + f), c1 = __ldg(cdf + f + 1);
+    x = (x - c0) / (c1 - c0);                      // DiscretePDF::sampleReuse (dpdf.h:151-156)
+    float su = sqrtf(1.0f - x);
+    float b0 = 1.0f - su, b1 = xi.y * su, b2 = 1.0f - b0 - b1;
+    uint4 tri = __ldg(s.tris + em.triOffset + f);
+    V3 p0 = ld3(s.vpos, tri.x), p1 = ld3(s.vpos, tri.y), p2 = ld3(s.vpos, tri.z);
+    p = (b0 * p0 + b1 * p1) + b2 * p2;
+    if (s.meshes[em.mesh].hasN) n = normalized((b0 * ld3(s.vnrm, tri.x) + b1 * ld3(s.vnrm, tri.y)) + b2 * ld3(s.vnrm, tri.z));
+    else n = normalized(cross(p1 - p0, p2 - p0));
+}
+
+/// One emitter picked uniformly from u, then a uniform point by area (noracle_integrators.h:73-88).
+__device__ __forceinline__ bool sampleLights(const DeviceScene &s, V3 ref, float u, V2 xi, LightSample &ls) {
+    int n = s.nEmitters;
+    if (n == 0) return false;
+    int e = min((int) (u * (float) n), n - 1);
+    const EmitterInfo &em = s.emitters[e];
+    emitterSamplePoint(s, em, xi, ls.p, ls.n);
+    V3 d = ls.p - ref;
+    float dist2 = squaredNorm(d);
+    ls.dist = sqrtf(dist2);
+    ls.wi = d / ls.dist;
+    float cosL = dot(ls.n, -ls.wi);
+    if (!(cosL > 0.0f) || !(ls.dist > 0.0f)) { ls.pdf = 0.0f; return false; }
+    ls.pdf = dist2 / (cosL * em.area) / (float) n;
+    ls.Le = mk(em.radiance[0], em.radiance[1], em.radiance[2]);
+    return true;
+}
+
+__device__ __forceinline__ float emitterPdfSolidAngle(const EmitterInfo &em, V3 ref, V3 p, V3 n) {
+    V3 d = p - ref;
+    float dist2 = squaredNorm(d);
+    float dist = sqrtf(dist2);
+    float cosL = dot(n, -(d / dist));
+    if (!(cosL > 0.0f)) return 0.0f;
+    return dist2 / (cosL * em.area);
+}
+
+__device__ __forceinline__ Bsdf meshBsdf(const MeshInfo &m) {
+    Bsdf b;
+    b.type = m.bsdfType; b.albedo = mk(m.albedo[0], m.albedo[1], m.albedo[2]);
+    b.alpha = m.alpha; b.intIOR = m.intIOR; b.extIOR = m.extIOR; b.ks = m.ks;
+    return b;
+}
+
+struct ShadowOut { bool cast; V3 o, d; float maxt; V3 contrib; };
+
+/// Body of the Li loops of oracle/noracle_integrators.h for ONE path vertex. Returns true while
+/// the path continues (a new ray was written to `ray`).
+template <int INTEGRATOR>
+__device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderParams &rp, Ray &ray, uint32_t gid, float t, float u, float v,
+                                            Pcg32 &rng, V3 &T, V3 &L, float &eta, float &bsdfPdf, uint32_t &flags, ShadowOut &sh) {
+    sh.cast = false;
+    if (gid == kNoHit) return false;
+    Hit its;
+    fillHit(sc, gid, t, u, v, its);
+    const MeshInfo &mesh = sc.meshes[its.mesh];
+    const int nLights = sc.nEmitters;
+
+    if (INTEGRATOR == NORI_INT_NORMALS) {                        // LiNormals
+        L = mk(fabsf(its.sh.n.x), fabsf(its.sh.n.y), fabsf(its.sh.n.z));
+        return false;
+    }
+    if (INTEGRATOR == NORI_INT_SIMPLE) {                         // LiSimple
+        V3 d = rp.lightPos - its.p;
+        float dist2 = squaredNorm(d), dist = sqrtf(dist2);
+        V3 wi = d / dist;
+        float c = dot(its.sh.n, wi);
+        if (!(c > 0.0f)) return false;
+        sh.cast = true; sh.o = its.p; sh.d = wi; sh.maxt = dist - kEpsilon;
+        sh.contrib = rp.lightEnergy * (c / (4.0f * kPi * kPi * dist2));
+        return false;
+    }
+    if (INTEGRATOR == NORI_INT_AO) {                             // LiAo
+        V3 dl = squareToCosineHemisphere(rng.next2D());
+        sh.cast = true; sh.o = its.p; sh.d = its.sh.toWorld(dl); sh.maxt = INFINITY; sh.contrib = mk(1, 1, 1);
+        return false;
+    }
+    if (INTEGRATOR == NORI_INT_PRIMARY_SHADOW) {                 // LiPrimaryShadow
+        if (nLights == 0) return false;
+        float uu = rng.next1D();
+        V2 xi = rng.next2D();
+        LightSample ls;
+        if (!sampleLights(sc, its.p, uu, xi, ls)) return false;
+        float c = fabsf(dot(its.sh.n, ls.wi));
+        sh.cast = true; sh.o = its.p; sh.d = ls.wi; sh.maxt = ls.dist - kEpsilon; sh.contrib = mk(c, c, c);
+        return false;
+    }
+    const Bsdf bsdf = meshBsdf(mesh);
+    const V3 wiLocal = its.sh.toLocal(-ray.d);
+
+    if (INTEGRATOR == NORI_INT_WHITTED) {                        // LiWhitted
+        if (bsdf.isDiffuse()) {
+            flags |= kFlagMulT;                                  // value = T * (Le + direct)
+            if (mesh.emitter >= 0) {
+                const EmitterInfo &em = sc.emitters[mesh.emitter];
+                if (dot(its.sh.n, -ray.d) > 0.0f) L = L + mk(em.radiance[0], em.radiance[1], em.radiance[2]);
+            }
+            if (nLights > 0) {
+                float uu = rng.next1D();
+                V2 xi = rng.next2D();
+                LightSample ls;
+                if (sampleLights(sc, its.p, uu, xi, ls)) {
+                    BsdfQuery q; q.wi = wiLocal; q.wo = its.sh.toLocal(ls.wi); q.eta = 1.0f; q.measure = kSolidAngle;
+                    V3 f = bsdf.eval(q);
+                    if (!isZero(f)) {
+                        sh.cast = true; sh.o = its.p; sh.d = ls.wi; sh.maxt = ls.dist - kEpsilon;
+                        sh.contrib = f * ls.Le * (fabsf(q.wo.z) / ls.pdf);
+                    }
+                }
+            }
+            return false;
+        }
+        if (!(rng.next1D() < 0.95f)) { L = mk(0, 0, 0); T = mk(0, 0, 0); flags |= kFlagMulT; return false; }
+        BsdfQuery q; q.wi = wiLocal; q.eta = 1.0f; q.measure = kUnknownMeasure;
+        V3 wgt = bsdf.sample(q, rng.next2D());
+        if (isZero(wgt)) { L = mk(0, 0, 0); T = mk(0, 0, 0); flags |= kFlagMulT; return false; }
+        T = T * wgt / 0.95f;
+        ray = mkRay(its.p, its.sh.toWorld(q.wo));
+        return true;
+    }
+
+    // ---- LiPath: path_mats / path_ems / path_mis ------------------------------------------
+    constexpr bool useEms = INTEGRATOR == NORI_INT_PATH_EMS || INTEGRATOR == NORI_INT_PATH_MIS;
+    constexpr bool useMats = INTEGRATOR == NORI_INT_PATH_MATS || INTEGRATOR == NORI_INT_PATH_MIS;
+    constexpr bool mis = INTEGRATOR == NORI_INT_PATH_MIS;
+    const bool discrete = flags & kFlagDiscrete;
+    uint32_t depth = flags & kDepthMask;
+
+    if (mesh.emitter >= 0) {
+        const EmitterInfo &em = sc.emitters[mesh.emitter];
+        if (dot(its.sh.n, -ray.d) > 0.0f) {
+            V3 Le = mk(em.radiance[0], em.radiance[1], em.radiance[2]);
+            if (!isZero(Le)) {
+                if (discrete || !useEms) L = L + T * Le;
+                else if (useMats) {
+                    float pl = emitterPdfSolidAngle(em, ray.o, its.p, its.sh.n) / (float) nLights;
+                    float wgt = bsdfPdf / (bsdfPdf + pl);
+                    L = L + T * Le * wgt;
+                }
+            }
+        }
+    }
+    if (rp.maxDepth > 0 && (int) depth + 1 >= rp.maxDepth) return false;
+
+    if (useEms && bsdf.isDiffuse() && nLights > 0) {
+        float uu = rng.next1D();
+        V2 xi = rng.next2D();
+        LightSample ls;
+        if (sampleLights(sc, its.p, uu, xi, ls)) {
+            BsdfQuery q; q.wi = wiLocal; q.wo = its.sh.toLocal(ls.wi); q.eta = 1.0f; q.measure = kSolidAngle;
+            V3 f = bsdf.eval(q);
+            if (!isZero(f)) {
+                float wgt = 1.0f;
+                if (mis) { float pb = bsdf.pdf(q); wgt = ls.pdf / (ls.pdf + pb); }
+                float c = fabsf(q.wo.z);
+                sh.cast = true; sh.o = its.p; sh.d = ls.wi; sh.maxt = ls.dist - kEpsilon;
+                sh.contrib = T * f * ls.Le * (c * wgt / ls.pdf);
+            }
+        }
+    }
+
+    BsdfQuery q; q.wi = wiLocal; q.eta = 1.0f; q.measure = kUnknownMeasure;
+    V3 wgt = bsdf.sample(q, rng.next2D());
+    if (isZero(wgt)) return false;
+    T = T * wgt;
+    eta *= q.eta;
+    const bool nowDiscrete = q.measure == kDiscrete;
+    bsdfPdf = nowDiscrete ? 0.0f : bsdf.pdf(q);
+    ray = mkRay(its.p, its.sh.toWorld(q.wo));
+    ++depth;
+    flags = (flags & ~(kDepthMask | kFlagDiscrete)) | (depth & kDepthMask) | (nowDiscrete ? kFlagDiscrete : 0u);
+    if ((int) depth >= rp.rrStart) {
+        float qc = fminf(maxCoeff(T) * eta * eta, rp.rrMax);
+        if (!(rng.next1D() < qc)) return false;
+        T = T / qc;
+    }
+    return true;
+}
+
+template <int INTEGRATOR>
+__global__ void __launch_bounds__(256) k_shade(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    // locate this thread's entry in the concatenation of the material queues
+    int key = -1; uint32_t idx = g;
+    {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int k = 0; k < kNumKeys; ++k) {
+            uint32_t n = c->sortCount[k];
+            if (key < 0 && g < acc + n) { key = k; idx = g - acc; }
+            acc += n;
+        }
+    }
+    ShadowOut sh; sh.cast = false;
+    uint32_t slot = 0;
+    if (key >= 0) {
+        slot = pool.sortQueue[(size_t) key * pool.capacity + idx];
+        const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
+        const ulonglong2 rs = pool.rng[slot];
+        uint4 meta = pool.meta[slot];
+        Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
+        Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
+        V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
+        float bsdfPdf = th.w, eta = ra.w;
+        uint32_t flags = meta.z;
+        bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
+        if (cont) {
+            pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
+            pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
+            pool.rng[slot] = make_ulonglong2(rng.state, rng.inc);
+        } else flags = (flags & ~kFlagAlive) | kFlagHasSample;
+        pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
+        pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
+        meta.z = flags;
+        pool.meta[slot] = meta;
+    }
+    // shadow-ray queue (compacted)
+    const uint32_t q = warpAppend(&c->shadowCount, sh.cast);
+    if (sh.cast) {
+        float4 *e = pool.shadow + 3 * (size_t) q;
+        e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
+        e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
+        e[2] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_traceShadow(DeviceScene sc, Pool pool, const Counters *c) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= c->shadowCount) return;
+    const float4 *e = pool.shadow + 3 * (size_t) g;
+    const float4 a = e[0], b = e[1], k = e[2];
+    float t, u, v;
+    uint32_t gid = traverse<true>(sc.nodes, sc.leafTris, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), kEpsilon, a.w, t, u, v);
+    if (gid != kNoHit) return;
+    const uint32_t slot = __float_as_uint(b.w);
+    float4 r = pool.rad[slot];
+    r.x = r.x + k.x; r.y = r.y + k.y; r.z = r.z + k.z;
+    pool.rad[slot] = r;
+}
+
+// ------------------------------------------------------------------------------------------
+/// ImageBlock::put(pos, value) (src/block.cpp:74-103) for every sample of a finished tile, into a
+/// shared-memory ImageBlock of (tile + 2*border)^2 cells kept as four planes (R, G, B, W), then
+/// `result.put(block)` (src/block.cpp:105-114) into the full-frame accumulator.
+constexpr int kSplatSide = kTile + 2 * kMaxBorder;
+__global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, Counters *c) {
+    __shared__ float plane[4][kSplatSide * kSplatSide];
+    __shared__ unsigned sDropped;
+    const uint32_t tile = blockIdx.x, slot = blockIdx.y;
+    const uint32_t pass = c->slotPass[slot];
+    if (pass >= rp.numPasses) return;
+    const int W = sc.cam.width, H = sc.cam.height, b = sc.filter.border;
+    const int ox = (int) (tile % (uint32_t) rp.tilesX) * kTile, oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
+    const int tw = min(W - ox, kTile), th = min(H - oy, kTile);
+    const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
+    if (rp.tileDone[slot * rp.numTiles + tile] != (uint32_t) (tw * th) * Kp) return;
+
+    const int cols = tw + 2 * b, rows = th + 2 * b;
+    for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
+    if (threadIdx.x == 0) sDropped = 0;
+    __syncthreads();
+    const float radius = sc.filter.radius, lookup = sc.filter.lookupFactor;
+    const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp;
+    for (uint32_t r = threadIdx.x; r < 1024u * Kp; r += blockDim.x) {
+        int lx, ly; tilePixel(r & 1023u, lx, ly);
+        if (lx >= tw || ly >= th) continue;
+        const float4 a = rp.recA[base + r];
+        const V3 val = mk(a.z, a.w, rp.recB[base + r]);
+        if (!isValidColor(val)) { atomicAdd(&sDropped, 1u); continue; }          // block.cpp:75-79
+        const float px = a.x - 0.5f - (float) (ox - b), py = a.y - 0.5f - (float) (oy - b);   // block.cpp:82-85
+        const int x0 = max((int) ceilf(px - radius), 0), y0 = max((int) ceilf(py - radius), 0);
+        const int x1 = min((int) floorf(px + radius), cols - 1), y1 = min((int) floorf(py + radius), rows - 1);
+        float wx[2 * kMaxBorder + 2], wy[2 * kMaxBorder + 2];
+#pragma unroll
+        for (int k = 0; k < 2 * kMaxBorder + 2; ++k) {
+            int x = x0 + k, y = y0 + k;
+            wx[k] = x <= x1 ? sc.filter.table[(int) (fabsf((float) x - px) * lookup)] : 0.f;
+            wy[k] = y <= y1 ? sc.filter.table[(int) (fabsf((float) y - py) * lookup)] : 0.f;
+        }
+#pragma unroll
+        for (int yr = 0; yr < 2 * kMaxBorder + 2; ++yr) {
+            const int y = y0 + yr;
+            if (y > y1) break;
+#pragma unroll
+            for (int xr = 0; xr < 2 * kMaxBorder + 2; ++xr) {
+                const int x = x0 + xr;
+                if (x > x1) break;
+                const int cell = y * cols + x;
+                atomicAdd(&plane[0][cell], val.x * wx[xr] * wy[yr]);
+                atomicAdd(&plane[1][cell], val.y * wx[xr] * wy[yr]);
+                atomicAdd(&plane[2][cell], val.z * wx[xr] * wy[yr]);
+                atomicAdd(&plane[3][cell], 1.0f * wx[xr] * wy[yr]);
+            }
+        }
+    }
+    __syncthreads();
+    // result.put(block): tile cell (x, y) is full-frame cell (ox + x, oy + y); borders of
+    // neighbouring tiles overlap, hence atomics.
+    for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) {
+        const int x = k % cols, y = k / cols;
+        float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + y) * rp.blockCols + (ox + x);
+        atomicAdd(dst, make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]));
+    }
+    if (threadIdx.x == 0) {
+        rp.tileDone[slot * rp.numTiles + tile] = 0;
+        if (sDropped) atomicAdd(&c->dropped, (unsigned long long) sDropped);
+        __threadfence();
+        atomicAdd(&c->tilesSplatted[slot], 1u);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
+    k_shade<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
+}
+
+int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st, cudaEvent_t *ev) {
+    const uint32_t grid = pool.capacity / 256;
+    int launches = 0;
+    if (ev) cudaEventRecord(ev[0], st);
+    k_prepare<<<1, 1, 0, st>>>(c, rp); ++launches;
+    k_finishRegen<<<grid, 256, 0, st>>>(sc, pool, rp, c); ++launches;
+    if (ev) cudaEventRecord(ev[1], st);
+    k_traceClosest<<<grid, 256, 0, st>>>(sc, pool, c); ++launches;
+    if (ev) cudaEventRecord(ev[2], st);
+    switch (rp.integrator) {
+    case NORI_INT_NORMALS: launchShade<NORI_INT_NORMALS>(sc, pool, rp, c, st); break;
+    case NORI_INT_PATH_MATS: launchShade<NORI_INT_PATH_MATS>(sc, pool, rp, c, st); break;
+    case NORI_INT_PATH_EMS: launchShade<NORI_INT_PATH_EMS>(sc, pool, rp, c, st); break;
+    case NORI_INT_PATH_MIS: launchShade<NORI_INT_PATH_MIS>(sc, pool, rp, c, st); break;
+    case NORI_INT_WHITTED: launchShade<NORI_INT_WHITTED>(sc, pool, rp, c, st); break;
+    case NORI_INT_PRIMARY_SHADOW: launchShade<NORI_INT_PRIMARY_SHADOW>(sc, pool, rp, c, st); break;
+    case NORI_INT_SIMPLE: launchShade<NORI_INT_SIMPLE>(sc, pool, rp, c, st); break;
+    default: launchShade<NORI_INT_AO>(sc, pool, rp, c, st); break;
+    }
+    ++launches;
+    if (ev) cudaEventRecord(ev[3], st);
+    if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<grid, 256, 0, st>>>(sc, pool, c); ++launches; }
+    if (ev) cudaEventRecord(ev[4], st);
+    if (!rp.listPixel) { k_splat<<<dim3(rp.numTiles, rp.ring), 256, 0, st>>>(sc, rp, c); ++launches; }
+    if (ev) cudaEventRecord(ev[5], st);
+    return launches;
+}
+
+} // namespace ng

@@ -1,0 +1,308 @@
+"""ctypes binding of libnori_b200.so (include/nori_gpu.h) — the Python view of the C ABI.
+
+The product path: there is no CPU fallback. Loading fails loudly when the library has not been
+built (``python -m nori_b200.build``) and ``Engine()`` fails loudly when no CUDA device is present.
+
+The method names mirror the reference operators they stand in for (Accel::rayIntersect ->
+``trace``/``intersect``, PerspectiveCamera::sampleRay -> ``camera_rays``, BSDF::sample ->
+``bsdf_sample``, ImageBlock::put -> ``splat``, render() -> ``render``), so the parity tests read
+like calls into the reference.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .scene import FlatScene
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnori_b200.so")
+
+EXPORTS = [
+    "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",
+    "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel",
+    "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_block_device_ptr",
+    "nori_gpu_block_dims", "nori_gpu_set_profiling", "nori_gpu_set_pool_size",
+    "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
+    "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_pcg32", "nori_gpu_splat",
+    "nori_gpu_sample_radiance",
+]
+
+
+class NoriGpuError(RuntimeError):
+    """Raised for every non-zero return of the C ABI (the C++ wrapper's NoriException)."""
+
+
+class MeshDesc(C.Structure):
+    _fields_ = [("V", C.c_void_p), ("N", C.c_void_p), ("UV", C.c_void_p), ("F", C.c_void_p),
+                ("nV", C.c_uint32), ("nF", C.c_uint32), ("bsdf_type", C.c_int32), ("bsdf_params", C.c_float * 6),
+                ("is_emitter", C.c_int32), ("radiance", C.c_float * 3)]
+
+
+class CameraDesc(C.Structure):
+    _fields_ = [("sample_to_camera", C.c_float * 16), ("camera_to_world", C.c_float * 16),
+                ("width", C.c_int32), ("height", C.c_int32), ("near_clip", C.c_float), ("far_clip", C.c_float)]
+
+
+class RenderDesc(C.Structure):
+    _fields_ = [("integrator", C.c_int32), ("stream_mode", C.c_int32), ("sample_first", C.c_uint32), ("sample_last", C.c_uint32),
+                ("rr_start", C.c_int32), ("rr_max", C.c_float), ("max_depth", C.c_int32), ("intersect_mode", C.c_int32),
+                ("light_pos", C.c_float * 3), ("light_energy", C.c_float * 3), ("clear", C.c_int32), ("deterministic", C.c_int32)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("camera_samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("segments", C.c_uint64),
+                ("dropped", C.c_uint64), ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64), ("ms_total", C.c_float),
+                ("ms_trace_closest", C.c_float), ("ms_trace_shadow", C.c_float), ("ms_shade", C.c_float),
+                ("ms_generate", C.c_float), ("ms_splat", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class AccelStats(C.Structure):
+    _fields_ = [("n_triangles", C.c_uint32), ("n_nodes", C.c_uint32), ("n_leaves", C.c_uint32), ("max_leaf_size", C.c_uint32),
+                ("depth", C.c_uint32), ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """dlopen libnori_b200.so; never falls back to anything else."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NoriGpuError(f"{LIB_PATH} is missing: build it with `python -m nori_b200.build` (nvcc, sm_100a). "
+                           "nori_b200 has no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, ip = C.c_void_p, C.c_int
+    L.nori_gpu_create.argtypes = [C.POINTER(vp), ip]
+    L.nori_gpu_destroy.argtypes = [vp]; L.nori_gpu_destroy.restype = None
+    L.nori_gpu_last_error.argtypes = [vp]; L.nori_gpu_last_error.restype = C.c_char_p
+    L.nori_gpu_device_name.argtypes = [vp, C.c_char_p, ip]
+    L.nori_gpu_upload_meshes.argtypes = [vp, C.POINTER(MeshDesc), ip]
+    L.nori_gpu_set_camera.argtypes = [vp, C.POINTER(CameraDesc)]
+    L.nori_gpu_set_filter.argtypes = [vp, C.c_float, vp]
+    L.nori_gpu_build_accel.argtypes = [vp, C.POINTER(AccelStats)]
+    L.nori_gpu_render.argtypes = [vp, C.POINTER(RenderDesc), C.POINTER(RenderStats)]
+    L.nori_gpu_download_block.argtypes = [vp, vp]
+    L.nori_gpu_download_bitmap.argtypes = [vp, vp]
+    L.nori_gpu_block_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
+    L.nori_gpu_block_dims.argtypes = [vp, C.POINTER(ip), C.POINTER(ip), C.POINTER(ip)]
+    L.nori_gpu_set_profiling.argtypes = [vp, ip]
+    L.nori_gpu_set_pool_size.argtypes = [vp, C.c_uint32]
+    L.nori_gpu_trace.argtypes = [vp, vp, ip, ip, vp, vp, vp]
+    L.nori_gpu_trace_device.argtypes = [vp, vp, ip, ip, vp, C.POINTER(C.c_float)]
+    L.nori_gpu_trace_count.argtypes = [vp, vp, ip, ip, vp]
+    L.nori_gpu_intersect.argtypes = [vp, vp, ip, vp, vp]
+    L.nori_gpu_camera_rays.argtypes = [vp, vp, ip, vp]
+    L.nori_gpu_bsdf_sample.argtypes = [vp, ip, vp, ip, vp, vp, vp, vp, vp, vp, vp]
+    L.nori_gpu_bsdf_eval_pdf.argtypes = [vp, ip, vp, ip, vp, vp, vp, vp]
+    L.nori_gpu_warp.argtypes = [vp, ip, C.c_float, ip, vp, vp, vp]
+    L.nori_gpu_pcg32.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int64, ip, vp]
+    L.nori_gpu_splat.argtypes = [vp, ip, vp, vp, ip, vp, C.POINTER(C.c_uint64)]
+    L.nori_gpu_sample_radiance.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp, vp]
+    _lib = L
+    return L
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Engine:
+    """One nori_gpu_ctx on one CUDA device."""
+
+    def __init__(self, device: int = 0):
+        self.L = load_library()
+        h = C.c_void_p()
+        rc = self.L.nori_gpu_create(C.byref(h), device)
+        if rc != 0:
+            raise NoriGpuError(f"nori_gpu_create failed ({rc}): {self.L.nori_gpu_last_error(None).decode()}")
+        self.h = h
+        self.scene: FlatScene | None = None
+        self.accel_stats: dict | None = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.nori_gpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise NoriGpuError(f"[{rc}] {self.L.nori_gpu_last_error(self.h).decode()}")
+
+    @property
+    def device_name(self) -> str:
+        buf = C.create_string_buffer(256)
+        self._ck(self.L.nori_gpu_device_name(self.h, buf, 256))
+        return buf.value.decode()
+
+    # ---- scene ---------------------------------------------------------------------------
+    def load_scene(self, scene: FlatScene) -> dict:
+        """Scene::activate: upload meshes/materials/emitters, camera, filter; build the accel."""
+        descs = (MeshDesc * len(scene.meshes))()
+        keep = []
+        for d, m in zip(descs, scene.meshes):
+            keep.append(m)
+            d.V, d.F = _p(m.V), _p(m.F)
+            d.N, d.UV = _p(m.N), _p(m.UV)
+            d.nV, d.nF = m.V.shape[0], m.F.shape[0]
+            d.bsdf_type = int(m.bsdf_type)
+            d.bsdf_params = (C.c_float * 6)(*[float(x) for x in m.bsdf_params])
+            d.is_emitter = int(m.is_emitter)
+            d.radiance = (C.c_float * 3)(*[float(x) for x in m.radiance])
+        self._ck(self.L.nori_gpu_upload_meshes(self.h, descs, len(scene.meshes)))
+        self.scene = scene
+        self.set_camera(scene.sample_to_camera, scene.camera_to_world, scene.width, scene.height, scene.near_clip, scene.far_clip)
+        self.set_filter(scene.filter_radius, scene.filter_table)
+        st = AccelStats()
+        self._ck(self.L.nori_gpu_build_accel(self.h, C.byref(st)))
+        self.accel_stats = st.as_dict()
+        return self.accel_stats
+
+    def set_camera(self, s2c, c2w, width, height, near_clip, far_clip):
+        cam = CameraDesc()
+        cam.sample_to_camera = (C.c_float * 16)(*_f32(s2c).ravel().tolist())
+        cam.camera_to_world = (C.c_float * 16)(*_f32(c2w).ravel().tolist())
+        cam.width, cam.height, cam.near_clip, cam.far_clip = int(width), int(height), float(near_clip), float(far_clip)
+        self._ck(self.L.nori_gpu_set_camera(self.h, C.byref(cam)))
+        self._wh = (int(width), int(height))
+
+    def set_filter(self, radius, table33):
+        t = _f32(table33, (33,))
+        self._ck(self.L.nori_gpu_set_filter(self.h, C.c_float(float(radius)), _p(t)))
+
+    def set_profiling(self, on: bool):
+        self._ck(self.L.nori_gpu_set_profiling(self.h, int(on)))
+
+    def set_pool_size(self, n: int):
+        self._ck(self.L.nori_gpu_set_pool_size(self.h, int(n)))
+
+    def block_dims(self):
+        r, c, b = C.c_int(), C.c_int(), C.c_int()
+        self._ck(self.L.nori_gpu_block_dims(self.h, C.byref(r), C.byref(c), C.byref(b)))
+        return r.value, c.value, b.value
+
+    def block_device_ptr(self):
+        p, n = C.c_void_p(), C.c_uint64()
+        self._ck(self.L.nori_gpu_block_device_ptr(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    # ---- render --------------------------------------------------------------------------
+    def render_desc(self, integrator=None, stream_mode=1, sample_first=0, sample_last=None, clear=True) -> RenderDesc:
+        s = self.scene
+        d = RenderDesc()
+        d.integrator = int(s.integrator if integrator is None else integrator)
+        d.stream_mode = int(stream_mode)
+        d.sample_first = int(sample_first)
+        d.sample_last = int(s.sample_count if sample_last is None else sample_last)
+        d.rr_start, d.rr_max, d.max_depth, d.intersect_mode = int(s.rr_start), float(s.rr_max), int(s.max_depth), 0
+        d.light_pos = (C.c_float * 3)(*[float(x) for x in s.light_pos])
+        d.light_energy = (C.c_float * 3)(*[float(x) for x in s.light_energy])
+        d.clear, d.deterministic = int(clear), 0
+        return d
+
+    def render(self, integrator=None, stream_mode=1, sample_first=0, sample_last=None, clear=True, download=True):
+        """render(): all samples [first, last) of every pixel. Returns (ImageBlock data, stats)."""
+        d = self.render_desc(integrator, stream_mode, sample_first, sample_last, clear)
+        st = RenderStats()
+        self._ck(self.L.nori_gpu_render(self.h, C.byref(d), C.byref(st)))
+        return (self.download_block() if download else None), st.as_dict()
+
+    def download_block(self):
+        r, c, _ = self.block_dims()
+        out = np.empty((r, c, 4), np.float32)
+        self._ck(self.L.nori_gpu_download_block(self.h, _p(out)))
+        return out
+
+    def download_bitmap(self):
+        w, h = self._wh
+        out = np.empty((h, w, 3), np.float32)
+        self._ck(self.L.nori_gpu_download_bitmap(self.h, _p(out)))
+        return out
+
+    def sample_radiance(self, pixel, sample, integrator=None):
+        pixel = np.ascontiguousarray(pixel, np.uint32); sample = np.ascontiguousarray(sample, np.uint32)
+        n = pixel.shape[0]
+        rgb = np.empty((n, 3), np.float32); pos = np.empty((n, 2), np.float32)
+        d = self.render_desc(integrator)
+        self._ck(self.L.nori_gpu_sample_radiance(self.h, C.byref(d), n, _p(pixel), _p(sample), _p(rgb), _p(pos)))
+        return rgb, pos
+
+    # ---- operators -----------------------------------------------------------------------
+    def camera_rays(self, pixel_samples):
+        ps = _f32(pixel_samples, (-1, 2)); out = np.empty((ps.shape[0], 8), np.float32)
+        self._ck(self.L.nori_gpu_camera_rays(self.h, _p(ps), ps.shape[0], _p(out)))
+        return out
+
+    def trace(self, rays, shadow=False):
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        tri = np.empty(n, np.uint32); mesh = np.empty(n, np.uint32); tuv = np.empty((n, 3), np.float32)
+        self._ck(self.L.nori_gpu_trace(self.h, _p(rays), n, int(shadow), _p(tri), _p(mesh), _p(tuv)))
+        return tri, mesh, tuv
+
+    def trace_count(self, rays, shadow=False):
+        rays = _f32(rays, (-1, 8)); counts = np.zeros(2, np.uint64)
+        self._ck(self.L.nori_gpu_trace_count(self.h, _p(rays), rays.shape[0], int(shadow), _p(counts)))
+        return int(counts[0]), int(counts[1])
+
+    def trace_device(self, d_rays_ptr: int, n: int, d_hits_ptr: int, shadow=False) -> float:
+        ms = C.c_float()
+        self._ck(self.L.nori_gpu_trace_device(self.h, C.c_void_p(d_rays_ptr), n, int(shadow), C.c_void_p(d_hits_ptr), C.byref(ms)))
+        return ms.value
+
+    def intersect(self, rays):
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        out = np.empty((n, 24), np.float32); valid = np.empty(n, np.int32)
+        self._ck(self.L.nori_gpu_intersect(self.h, _p(rays), n, _p(out), _p(valid)))
+        return out, valid.astype(bool)
+
+    def bsdf_sample(self, btype, params, wi, xi):
+        wi = _f32(wi, (-1, 3)); xi = _f32(xi, (-1, 2)); n = wi.shape[0]; prm = _f32(params, (6,))
+        wo = np.empty((n, 3), np.float32); w = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        eta = np.empty(n, np.float32); meas = np.empty(n, np.int32)
+        self._ck(self.L.nori_gpu_bsdf_sample(self.h, int(btype), _p(prm), n, _p(wi), _p(xi), _p(wo), _p(w), _p(pdf), _p(eta), _p(meas)))
+        return wo, w, pdf, eta, meas
+
+    def bsdf_eval_pdf(self, btype, params, wi, wo):
+        wi = _f32(wi, (-1, 3)); wo = _f32(wo, (-1, 3)); n = wi.shape[0]; prm = _f32(params, (6,))
+        f = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        self._ck(self.L.nori_gpu_bsdf_eval_pdf(self.h, int(btype), _p(prm), n, _p(wi), _p(wo), _p(f), _p(pdf)))
+        return f, pdf
+
+    def warp(self, wid, xi, param=0.0):
+        xi = _f32(xi, (-1, 2)); n = xi.shape[0]
+        out = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
+        self._ck(self.L.nori_gpu_warp(self.h, int(wid), C.c_float(param), n, _p(xi), _p(out), _p(pdf)))
+        return out, pdf
+
+    def pcg32_uints(self, initstate, initseq, n, advance=0):
+        out = np.empty(n, np.uint32)
+        self._ck(self.L.nori_gpu_pcg32(self.h, initstate, initseq, advance, n, _p(out)))
+        return out
+
+    def splat(self, pos, rgb, deterministic=False):
+        pos = _f32(pos, (-1, 2)); rgb = _f32(rgb, (-1, 3))
+        r, c, _ = self.block_dims()
+        out = np.empty((r, c, 4), np.float32); dropped = C.c_uint64()
+        self._ck(self.L.nori_gpu_splat(self.h, pos.shape[0], _p(pos), _p(rgb), int(deterministic), _p(out), C.byref(dropped)))
+        return out, int(dropped.value)
