@@ -100,6 +100,7 @@ typedef struct {
     uint64_t kernel_launches;
     float ms_total;           /* device time of the whole call (CUDA events) */
     float ms_trace_closest, ms_trace_shadow, ms_shade, ms_generate, ms_splat;  /* filled when profiling=1 */
+    uint64_t late_samples;    /* samples splatted one by one after their pass had been closed */
 } NoriGpuRenderStats;
 
 typedef struct {

@@ -32,7 +32,7 @@ struct nori_gpu_ctx {
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 21;
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
-    uint32_t *tileDone = nullptr; size_t tileDoneCap = 0;
+    uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
 };
 
@@ -138,7 +138,7 @@ void nori_gpu_destroy(nori_gpu_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     freeScene(ctx); freePool(ctx);
     cudaFree(ctx->d_block); cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
-    cudaFree(ctx->recA); cudaFree(ctx->recB); cudaFree(ctx->tileDone);
+    cudaFree(ctx->recA); cudaFree(ctx->recB); cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -324,52 +324,56 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     }
     const size_t tdNeed = (size_t) rp.ring * rp.numTiles;
     if (tdNeed > ctx->tileDoneCap) {
-        cudaFree(ctx->tileDone); ctx->tileDone = nullptr;
-        CK(cudaMalloc((void **) &ctx->tileDone, tdNeed * sizeof(uint32_t))); ctx->tileDoneCap = tdNeed;
+        cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive); ctx->tileDone = ctx->tileGen = ctx->tileArrive = nullptr;
+        CK(cudaMalloc((void **) &ctx->tileArrive, tdNeed * sizeof(uint32_t)));
+        CK(cudaMalloc((void **) &ctx->tileDone, tdNeed * sizeof(uint32_t))); CK(cudaMalloc((void **) &ctx->tileGen, tdNeed * sizeof(uint32_t)));
+        ctx->tileDoneCap = tdNeed;
     }
-    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone;
+    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.poolCapacity = ctx->pool.capacity;
     CK(cudaMemsetAsync(ctx->tileDone, 0, tdNeed * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(ctx->tileGen, 0, tdNeed * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(ctx->tileArrive, 0, tdNeed * sizeof(uint32_t), st));
+    if (!list) CK(cudaMemsetAsync(ctx->recA, 0xff, recNeed * sizeof(float4), st));        // NaN position = no sample recorded
     CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), st));
     CK(cudaMemsetAsync(ctx->pool.meta, 0, (size_t) ctx->pool.capacity * sizeof(uint4), st));
     if (d->clear && !list) CK(cudaMemsetAsync(ctx->d_block, 0, ctx->blockFloats * sizeof(float), st));
 
     const DeviceScene sc = deviceScene(ctx);
-    cudaEvent_t e0, e1, evCopy, stage[6];
+    // Stage events (profiling): 6 per iteration of a batch, read back after the batch's one
+    // synchronisation, so that profiling does not change how the kernels are queued.
+    const int batch = 8;
+    cudaEvent_t e0, e1, evCopy;
+    std::vector<cudaEvent_t> stage(ctx->profiling ? 6 * batch : 0);
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreateWithFlags(&evCopy, cudaEventDisableTiming));
     for (auto &e : stage) CK(cudaEventCreate(&e));
     StageTimes tm = {0, 0, 0, 0, 0};
     CK(cudaEventRecord(e0, st));
     uint64_t launches = 0;
-    // Iterations are enqueued in batches; the host looks at the counters of batch i while batch
-    // i+1 is already queued, so the device never waits for the host.
-    const int batch = ctx->profiling ? 1 : 8;
     bool done = false;
+    const bool debug = getenv("NORI_GPU_DEBUG") != nullptr;
     uint64_t guard = 0;
-    const uint64_t samplesDoneTarget = totalSamples;
     while (!done) {
-        for (int k = 0; k < batch; ++k) {
-            launches += (uint64_t) enqueueIteration(sc, ctx->pool, rp, ctx->d_counters, st, ctx->profiling ? stage : nullptr);
-            if (ctx->profiling) {
-                CK(cudaStreamSynchronize(st));
-                float ms;
-                cudaEventElapsedTime(&ms, stage[0], stage[1]); tm.generate += ms;
-                cudaEventElapsedTime(&ms, stage[1], stage[2]); tm.traceClosest += ms;
-                cudaEventElapsedTime(&ms, stage[2], stage[3]); tm.shade += ms;
-                cudaEventElapsedTime(&ms, stage[3], stage[4]); tm.traceShadow += ms;
-                cudaEventElapsedTime(&ms, stage[4], stage[5]); tm.splat += ms;
-            }
-        }
-        CK(cudaStreamSynchronize(st) == cudaSuccess ? cudaSuccess : cudaGetLastError());
+        for (int k = 0; k < batch; ++k)
+            launches += (uint64_t) enqueueIteration(sc, ctx->pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 6 * k : nullptr);
         CK(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(evCopy, st));
         CK(cudaEventSynchronize(evCopy));
+        CK(cudaGetLastError());
+        if (ctx->profiling) {
+            for (int k = 0; k < batch; ++k) {
+                cudaEvent_t *ev = stage.data() + 6 * k; float ms;
+                cudaEventElapsedTime(&ms, ev[0], ev[1]); tm.generate += ms;
+                cudaEventElapsedTime(&ms, ev[1], ev[2]); tm.traceClosest += ms;
+                cudaEventElapsedTime(&ms, ev[2], ev[3]); tm.shade += ms;
+                cudaEventElapsedTime(&ms, ev[3], ev[4]); tm.traceShadow += ms;
+                cudaEventElapsedTime(&ms, ev[4], ev[5]); tm.splat += ms;
+            }
+        }
         const Counters &hc = *ctx->h_counters;
-        const bool allFinished = hc.finished >= samplesDoneTarget;
-        const bool allSplatted = list || hc.completedPasses >= rp.numPasses;
-        done = allFinished && allSplatted;
+        if (debug) fprintf(stderr, "[nori_gpu] it=%llu issue=%llu/%llu limit=%llu finished=%llu/%llu passes=%u/%u splat=[%u %u %u %u]\n", (unsigned long long) hc.iterations, (unsigned long long) hc.issue, (unsigned long long) rp.totalIssue, (unsigned long long) hc.issueLimit, (unsigned long long) hc.finished, (unsigned long long) totalSamples, hc.completedPasses, rp.numPasses, hc.tilesSplatted[0], hc.tilesSplatted[1], hc.tilesSplatted[2], hc.tilesSplatted[3]);
+        done = hc.finished >= totalSamples && (list || hc.completedPasses >= rp.numPasses);
         if (++guard > 4000000ull) { ctx->err = "render: wavefront did not terminate (internal error)"; return NORI_GPU_ECUDA; }
     }
-    // one more k_prepare-equivalent pass is not needed: counters of the last iteration are folded here
     CK(cudaEventRecord(e1, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
@@ -383,7 +387,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         out->camera_samples = hc.finished; out->closest_rays = rays; out->shadow_rays = shadows; out->segments = rays;
         out->dropped = hc.dropped; out->iterations = hc.iterations; out->kernel_launches = launches; out->ms_total = ms;
         out->ms_generate = tm.generate; out->ms_trace_closest = tm.traceClosest; out->ms_shade = tm.shade;
-        out->ms_trace_shadow = tm.traceShadow; out->ms_splat = tm.splat;
+        out->ms_trace_shadow = tm.traceShadow; out->ms_splat = tm.splat; out->late_samples = hc.lateSamples;
     }
     return NORI_GPU_OK;
 }

@@ -41,7 +41,8 @@ struct Counters {
     unsigned int completedPasses;
     unsigned int tilesSplatted[kMaxRing];   // cumulative per ring slot
     unsigned int slotPass[kMaxRing];        // pass currently held by a ring slot
-    unsigned int pad[2];
+    unsigned int forcePass;                 // pass whose tiles are splatted now although samples are still in flight
+    unsigned int lateSamples;               // samples that finished after their pass was closed (direct splat)
 };
 
 struct RenderParams {
@@ -58,7 +59,10 @@ struct RenderParams {
     const uint32_t *listPixel, *listSample;
     // sample records of the passes in flight
     float4 *recA; float *recB;
-    uint32_t *tileDone;                      // ring x numTiles
+    uint32_t *tileDone;                      // ring x numTiles: finished samples of the pass held by the slot
+    uint32_t *tileGen;                       // ring x numTiles: passes already splatted for this (slot, tile)
+    uint32_t *tileArrive;                    // ring x numTiles: k_splat CTAs of the tile that finished (reset by the last)
+    uint32_t poolCapacity;
     float *block;                            // (H+2b) x (W+2b) x RGBW accumulator
     int blockCols, blockRows;
 };

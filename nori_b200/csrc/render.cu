@@ -41,6 +41,8 @@ __global__ void k_prepare(Counters *c, RenderParams rp) {
     c->closestRays += rays; c->segments += rays;
     c->shadowRays += c->shadowCount; c->shadowCount = 0;
     c->iterations++;
+    // lanes that drew an index at or past the previous limit discarded it: hand those indices out again
+    if (c->issue > c->issueLimit) c->issue = c->issueLimit;
     unsigned cp = c->completedPasses;
     while (cp < rp.numPasses && c->tilesSplatted[cp % rp.ring] >= rp.numTiles * (cp / rp.ring + 1)) ++cp;
     c->completedPasses = cp;
@@ -48,8 +50,10 @@ __global__ void k_prepare(Counters *c, RenderParams rp) {
     unsigned long long limitPass = min((unsigned long long) rp.numPasses, (unsigned long long) cp + rp.ring);
     unsigned long long limit = limitPass == rp.numPasses ? rp.totalIssue : limitPass * rp.passSlots;
     if (rp.listPixel) limit = rp.totalIssue;
-    if (c->issue > limit) c->issue = limit;       // lanes that overshot discarded their index
     c->issueLimit = limit;
+    // Ring about to run dry while the oldest pass still waits for a few long paths: close that pass
+    // now (k_splat takes the samples it has); its stragglers are splatted one by one when they finish.
+    c->forcePass = (!rp.listPixel && cp < rp.numPasses && limit < rp.totalIssue && c->issue + rp.poolCapacity > limit) ? cp : 0xffffffffu;
 }
 
 /// Pixel of slot r (< 1024) inside a tile: warps cover 8x4 pixel patches (coherent primary rays).
@@ -57,6 +61,25 @@ __device__ __forceinline__ void tilePixel(uint32_t pix, int &lx, int &ly) {
     uint32_t w = pix >> 5, l = pix & 31u;
     lx = (int) ((w & 3u) * 8u + (l & 7u));
     ly = (int) ((w >> 2) * 4u + (l >> 3));
+}
+
+/// ImageBlock::put(pos, value) (src/block.cpp:74-103) straight into the full-frame block with float
+/// atomics: only for the few samples that finish after their pass was closed.
+__device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Counters *c, float2 ps, V3 val) {
+    if (!isValidColor(val)) { atomicAdd(&c->dropped, 1ull); return; }
+    const int b = sc.filter.border;
+    const float radius = sc.filter.radius, lookup = sc.filter.lookupFactor;
+    const float px = ps.x - 0.5f - (float) (0 - b), py = ps.y - 0.5f - (float) (0 - b);
+    const int x0 = max((int) ceilf(px - radius), 0), y0 = max((int) ceilf(py - radius), 0);
+    const int x1 = min((int) floorf(px + radius), rp.blockCols - 1), y1 = min((int) floorf(py + radius), rp.blockRows - 1);
+    for (int y = y0; y <= y1; ++y) {
+        const float wy = sc.filter.table[(int) (fabsf((float) y - py) * lookup)];
+        for (int x = x0; x <= x1; ++x) {
+            const float wx = sc.filter.table[(int) (fabsf((float) x - px) * lookup)];
+            float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) y * rp.blockCols + x;
+            atomicAdd(dst, make_float4(val.x * wx * wy, val.y * wx * wy, val.z * wx * wy, 1.0f * wx * wy));
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
@@ -67,57 +90,78 @@ __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, 
 
     // ---- record a finished camera sample -------------------------------------------------
     const bool fin = dead && (meta.z & kFlagHasSample);
+    bool late = false;
     if (fin) {
         float4 rad = pool.rad[i];
         V3 L = mk(rad.x, rad.y, rad.z);
         if (meta.z & kFlagMulT) { float4 t = pool.thr[i]; L = mk(t.x, t.y, t.z) * L; }
         const uint32_t slot = meta.z >> 24;
-        const size_t r = (size_t) slot * rp.passSlots + meta.w;
         float2 ps = pool.pos[i];
-        rp.recA[r] = make_float4(ps.x, ps.y, L.x, L.y);
-        rp.recB[r] = L.z;
+        late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
+        if (late) {
+            splatDirect(sc, rp, c, ps, L);
+            atomicAdd(&c->lateSamples, 1u);
+        } else {
+            const size_t r = (size_t) slot * rp.passSlots + meta.w;
+            rp.recA[r] = make_float4(ps.x, ps.y, L.x, L.y);
+            rp.recB[r] = L.z;
+        }
     }
     if (!rp.listPixel) {
         // one atomic per (ring slot, tile) present in the warp
         uint32_t tile = 0xffffffffu;
-        if (fin) {
+        if (fin && !late) {
             uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
             tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
         }
         unsigned peers = __match_any_sync(0xffffffffu, tile);
-        if (fin && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
+        if (fin && !late && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
     }
+    // one atomic per CTA for the finished-sample count and for the sample indices drawn below
+    __shared__ unsigned long long sBase;
+    __shared__ unsigned sWarp[8], sTotal;
+    const unsigned warp = threadIdx.x >> 5;
     {
-        unsigned m = __ballot_sync(0xffffffffu, fin);
-        if (m && (int) laneId() == __ffs(m) - 1) atomicAdd(&c->finished, (unsigned long long) __popc(m));
+        const int nfin = __syncthreads_count(fin);
+        if (threadIdx.x == 0 && nfin) atomicAdd(&c->finished, (unsigned long long) nfin);
     }
 
     // ---- draw the next camera sample into the free slot ------------------------------------
-    bool need = dead;
     const unsigned long long limit = c->issueLimit;
+    const bool want = dead && *(volatile unsigned long long *) &c->issue < limit;
+    bool need = want;
     uint32_t x = 0, y = 0, sampleK = 0, rec = 0, slot = 0;
     int lx = 0, ly = 0, ox = 0, oy = 0;
     for (;;) {
-        unsigned m = __ballot_sync(0xffffffffu, need);
-        if (!m) break;
-        int leader = __ffs(m) - 1;
-        unsigned long long base = 0;
-        if ((int) laneId() == leader) base = atomicAdd(&c->issue, (unsigned long long) __popc(m));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (base >= limit) break;
+        const unsigned m = __ballot_sync(0xffffffffu, need);
+        if (laneId() == 0) sWarp[warp] = __popc(m);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned tot = 0;
+            for (int w = 0; w < 8; ++w) { unsigned n = sWarp[w]; sWarp[w] = tot; tot += n; }
+            sTotal = tot;
+            if (tot) sBase = atomicAdd(&c->issue, (unsigned long long) tot);
+        }
+        __syncthreads();
+        const unsigned tot = sTotal;
+        const unsigned long long base = sBase;
+        const unsigned off = sWarp[warp];
+        __syncthreads();
+        if (!tot || base >= limit) break;
         if (need) {
-            unsigned long long g = base + __popc(m & lanemaskLt());
+            unsigned long long g = base + off + __popc(m & lanemaskLt());
             if (g < limit) {
                 if (rp.listPixel) {
                     uint32_t p = rp.listPixel[g];
                     x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g; slot = 0;
                     need = false;
                 } else {
-                    uint32_t pass = (uint32_t) (g / rp.passSlots), j = (uint32_t) (g % rp.passSlots);
+                    uint32_t pass = (uint32_t) (g / rp.passSlots), j = (uint32_t) (g - (unsigned long long) pass * rp.passSlots);
                     uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
-                    uint32_t tile = j / (1024u * Kp), r = j % (1024u * Kp);
+                    uint32_t tile = j / (1024u * Kp), r = j - tile * (1024u * Kp);
                     tilePixel(r & 1023u, lx, ly);
-                    ox = (int) (tile % (uint32_t) rp.tilesX) * kTile; oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
+                    uint32_t tyi = tile / (uint32_t) rp.tilesX, txi = tile - tyi * (uint32_t) rp.tilesX;
+                    ox = (int) txi * kTile; oy = (int) tyi * kTile;
                     x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
                     if (tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H) {
                         sampleK = pass * rp.K + (r >> 10); rec = j; slot = pass % (uint32_t) rp.ring;
@@ -128,7 +172,7 @@ __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, 
         }
     }
     if (!dead) return;
-    if (need) {                                   // nothing left to issue: the slot stays empty
+    if (!want || need) {                          // nothing left to issue: the slot stays empty
         if (meta.z != 0) { meta.z = 0; pool.meta[i] = meta; }
         return;
     }
@@ -444,69 +488,81 @@ __global__ void __launch_bounds__(256) k_traceShadow(DeviceScene sc, Pool pool, 
 /// shared-memory ImageBlock of (tile + 2*border)^2 cells kept as four planes (R, G, B, W), then
 /// `result.put(block)` (src/block.cpp:105-114) into the full-frame accumulator.
 constexpr int kSplatSide = kTile + 2 * kMaxBorder;
+constexpr int kSplatSplit = 8;      // CTAs sharing one tile (each takes the samples k = z, z + Z, ...)
 __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, Counters *c) {
     __shared__ float plane[4][kSplatSide * kSplatSide];
+    __shared__ float sTable[33];
     __shared__ unsigned sDropped;
-    const uint32_t tile = blockIdx.x, slot = blockIdx.y;
+    const uint32_t tile = blockIdx.x, slot = blockIdx.y, z = blockIdx.z, Z = gridDim.z;
     const uint32_t pass = c->slotPass[slot];
     if (pass >= rp.numPasses) return;
     const int W = sc.cam.width, H = sc.cam.height, b = sc.filter.border;
     const int ox = (int) (tile % (uint32_t) rp.tilesX) * kTile, oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
     const int tw = min(W - ox, kTile), th = min(H - oy, kTile);
     const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
-    if (rp.tileDone[slot * rp.numTiles + tile] != (uint32_t) (tw * th) * Kp) return;
+    const uint32_t ti = slot * rp.numTiles + tile;
+    // All Z CTAs of a tile take the same decision: the bookkeeping below is only changed by the
+    // last of them to arrive.
+    if (rp.tileGen[ti] != pass / (uint32_t) rp.ring) return;                     // this pass of the tile is already in the block
+    const bool force = pass == c->forcePass;
+    if (!force && rp.tileDone[ti] != (uint32_t) (tw * th) * Kp) return;
 
     const int cols = tw + 2 * b, rows = th + 2 * b;
-    for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
-    if (threadIdx.x == 0) sDropped = 0;
-    __syncthreads();
-    const float radius = sc.filter.radius, lookup = sc.filter.lookupFactor;
-    const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp;
-    for (uint32_t r = threadIdx.x; r < 1024u * Kp; r += blockDim.x) {
-        int lx, ly; tilePixel(r & 1023u, lx, ly);
-        if (lx >= tw || ly >= th) continue;
-        const float4 a = rp.recA[base + r];
-        const V3 val = mk(a.z, a.w, rp.recB[base + r]);
-        if (!isValidColor(val)) { atomicAdd(&sDropped, 1u); continue; }          // block.cpp:75-79
-        const float px = a.x - 0.5f - (float) (ox - b), py = a.y - 0.5f - (float) (oy - b);   // block.cpp:82-85
-        const int x0 = max((int) ceilf(px - radius), 0), y0 = max((int) ceilf(py - radius), 0);
-        const int x1 = min((int) floorf(px + radius), cols - 1), y1 = min((int) floorf(py + radius), rows - 1);
-        float wx[2 * kMaxBorder + 2], wy[2 * kMaxBorder + 2];
-#pragma unroll
-        for (int k = 0; k < 2 * kMaxBorder + 2; ++k) {
-            int x = x0 + k, y = y0 + k;
-            wx[k] = x <= x1 ? sc.filter.table[(int) (fabsf((float) x - px) * lookup)] : 0.f;
-            wy[k] = y <= y1 ? sc.filter.table[(int) (fabsf((float) y - py) * lookup)] : 0.f;
-        }
-#pragma unroll
-        for (int yr = 0; yr < 2 * kMaxBorder + 2; ++yr) {
-            const int y = y0 + yr;
-            if (y > y1) break;
-#pragma unroll
-            for (int xr = 0; xr < 2 * kMaxBorder + 2; ++xr) {
-                const int x = x0 + xr;
-                if (x > x1) break;
-                const int cell = y * cols + x;
-                atomicAdd(&plane[0][cell], val.x * wx[xr] * wy[yr]);
-                atomicAdd(&plane[1][cell], val.y * wx[xr] * wy[yr]);
-                atomicAdd(&plane[2][cell], val.z * wx[xr] * wy[yr]);
-                atomicAdd(&plane[3][cell], 1.0f * wx[xr] * wy[yr]);
+    if (z < Kp) {
+        for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
+        if (threadIdx.x < 33) sTable[threadIdx.x] = sc.filter.table[threadIdx.x];
+        if (threadIdx.x == 0) sDropped = 0;
+        __syncthreads();
+        const float radius = sc.filter.radius, lookup = sc.filter.lookupFactor;
+        const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp;
+        for (uint32_t k = z; k < Kp; k += Z) {
+            for (uint32_t pix = threadIdx.x; pix < 1024u; pix += blockDim.x) {
+                int lx, ly; tilePixel(pix, lx, ly);
+                if (lx >= tw || ly >= th) continue;
+                const size_t r = base + k * 1024u + pix;
+                const float4 a = rp.recA[r];
+                if (isnan(a.x)) continue;                                        // sample still in flight (forced close)
+                const V3 val = mk(a.z, a.w, rp.recB[r]);
+                rp.recA[r].x = __int_as_float(0x7fc00000);                       // consumed: free for pass + ring
+                if (!isValidColor(val)) { atomicAdd(&sDropped, 1u); continue; }  // block.cpp:75-79
+                const float px = a.x - 0.5f - (float) (ox - b), py = a.y - 0.5f - (float) (oy - b);   // block.cpp:82-85
+                const int x0 = max((int) ceilf(px - radius), 0), y0 = max((int) ceilf(py - radius), 0);
+                const int x1 = min((int) floorf(px + radius), cols - 1), y1 = min((int) floorf(py + radius), rows - 1);
+                for (int y = y0; y <= y1; ++y) {
+                    const float wy = sTable[(int) (fabsf((float) y - py) * lookup)];
+                    for (int x = x0; x <= x1; ++x) {
+                        const float wx = sTable[(int) (fabsf((float) x - px) * lookup)];
+                        const int cell = y * cols + x;
+                        atomicAdd(&plane[0][cell], val.x * wx * wy);             // block.cpp:100-102
+                        atomicAdd(&plane[1][cell], val.y * wx * wy);
+                        atomicAdd(&plane[2][cell], val.z * wx * wy);
+                        atomicAdd(&plane[3][cell], 1.0f * wx * wy);
+                    }
+                }
             }
         }
+        __syncthreads();
+        // result.put(block): tile cell (x, y) is full-frame cell (ox + x, oy + y); borders of
+        // neighbouring tiles overlap and Z CTAs share the tile, hence atomics.
+        for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) {
+            const int x = k % cols, y = k / cols;
+            const float4 v = make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]);
+            if (v.w == 0.f && v.x == 0.f && v.y == 0.f && v.z == 0.f) continue;
+            float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + y) * rp.blockCols + (ox + x);
+            atomicAdd(dst, v);
+        }
     }
     __syncthreads();
-    // result.put(block): tile cell (x, y) is full-frame cell (ox + x, oy + y); borders of
-    // neighbouring tiles overlap, hence atomics.
-    for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) {
-        const int x = k % cols, y = k / cols;
-        float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + y) * rp.blockCols + (ox + x);
-        atomicAdd(dst, make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]));
-    }
     if (threadIdx.x == 0) {
-        rp.tileDone[slot * rp.numTiles + tile] = 0;
-        if (sDropped) atomicAdd(&c->dropped, (unsigned long long) sDropped);
+        if (z < Kp && sDropped) atomicAdd(&c->dropped, (unsigned long long) sDropped);
         __threadfence();
-        atomicAdd(&c->tilesSplatted[slot], 1u);
+        if (atomicAdd(rp.tileArrive + ti, 1u) == Z - 1) {                        // last CTA of this tile
+            rp.tileArrive[ti] = 0;
+            rp.tileDone[ti] = 0;
+            rp.tileGen[ti] = pass / (uint32_t) rp.ring + 1;
+            __threadfence();
+            atomicAdd(&c->tilesSplatted[slot], 1u);
+        }
     }
 }
 
@@ -538,7 +594,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     if (ev) cudaEventRecord(ev[3], st);
     if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<grid, 256, 0, st>>>(sc, pool, c); ++launches; }
     if (ev) cudaEventRecord(ev[4], st);
-    if (!rp.listPixel) { k_splat<<<dim3(rp.numTiles, rp.ring), 256, 0, st>>>(sc, rp, c); ++launches; }
+    if (!rp.listPixel) { k_splat<<<dim3(rp.numTiles, rp.ring, min((uint32_t) kSplatSplit, rp.K)), 256, 0, st>>>(sc, rp, c); ++launches; }
     if (ev) cudaEventRecord(ev[5], st);
     return launches;
 }

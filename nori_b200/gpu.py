@@ -56,7 +56,7 @@ class RenderStats(C.Structure):
     _fields_ = [("camera_samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("segments", C.c_uint64),
                 ("dropped", C.c_uint64), ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64), ("ms_total", C.c_float),
                 ("ms_trace_closest", C.c_float), ("ms_trace_shadow", C.c_float), ("ms_shade", C.c_float),
-                ("ms_generate", C.c_float), ("ms_splat", C.c_float)]
+                ("ms_generate", C.c_float), ("ms_splat", C.c_float), ("late_samples", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -269,4 +269,27 @@ void noracle_render(void *s_, int mode, uint32_t sampleFirst, uint32_t sampleLas
     if (stats) { stats[0] = total.closest; stats[1] = total.shadow; stats[2] = total.segments; stats[3] = dropped; }
 }
 
+/// Single-threaded render with traversal work counters, closest-hit and shadow rays apart:
+/// counters = {rays, boxTests, triTests} x {closest, shadow}. Source of the algorithmic bytes per
+/// ray of SURVEY.md 8(d) (box tests and triangle tests of the oracle's binary SAH BVH, <= 4 tris/leaf).
+void noracle_render_counted(void *s_, int mode, uint32_t sampleFirst, uint32_t sampleLast, int stride, uint64_t *counters6, uint64_t *stats3) {
+    Scene *s = (Scene *) s_;
+    FilterTable ft; ft.init(s->filterRadius, s->filterTable);
+    int W = s->camera.width, H = s->camera.height;
+    std::vector<int> order; blockOrder(W, H, kBlockSize, order);
+    int nb = (int) order.size() / 4;
+    TraversalCounters c0, c1; PathStats st;
+    s->accel.counters = &c0; s->accel.shadowCounters = &c1;
+    RenderJob job = {mode, sampleFirst, sampleLast};
+    for (int i = 0; i < nb; i += (stride > 0 ? stride : 1)) {
+        ImageBlock b; b.init(order[4 * i + 2], order[4 * i + 3], ft);
+        b.ox = order[4 * i]; b.oy = order[4 * i + 1];
+        renderBlock(*s, job, b, st);
+    }
+    s->accel.counters = 0; s->accel.shadowCounters = 0;
+    counters6[0] = c0.rays; counters6[1] = c0.boxTests; counters6[2] = c0.triTests;
+    counters6[3] = c1.rays; counters6[4] = c1.boxTests; counters6[5] = c1.triTests;
+    if (stats3) { stats3[0] = st.closest; stats3[1] = st.shadow; stats3[2] = st.segments; }
+}
+
 } // extern "C"

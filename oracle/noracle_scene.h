@@ -85,8 +85,10 @@ struct Accel {
     std::vector<BvhNode> nodes;
     bool useBvh;
     mutable TraversalCounters *counters;       // optional (single-threaded callers only)
-    Accel() : scene(0), useBvh(true), counters(0) {}
+    mutable TraversalCounters *shadowCounters; // optional: shadow rays counted apart from closest-hit rays
+    Accel() : scene(0), useBvh(true), counters(0), shadowCounters(0), active(0) {}
     void build(const Scene *s, int leafSize = 4);
+    mutable TraversalCounters *active;         // counter set of the ray being traced
     bool testTri(uint32_t gid, const Ray &ray, float &u, float &v, float &t) const;
     /// closest hit: returns global triangle id or 0xffffffff; any hit when shadowRay.
     uint32_t trace(const Ray &ray_, bool shadowRay, float &tOut, float &uOut, float &vOut) const;
@@ -150,14 +152,15 @@ struct Scene {
 inline bool Accel::testTri(uint32_t gid, const Ray &ray, float &u, float &v, float &t) const {
     const MeshData &m = scene->meshes[triMesh[gid]];
     uint32_t f = triLocal[gid];
-    if (counters) counters->triTests++;
+    if (active) active->triTests++;
     return rayTriangle(m.pos(m.F[3 * f]), m.pos(m.F[3 * f + 1]), m.pos(m.F[3 * f + 2]), ray, u, v, t);
 }
 
 inline uint32_t Accel::trace(const Ray &ray_, bool shadowRay, float &tOut, float &uOut, float &vOut) const {
     Ray ray(ray_);
     uint32_t best = 0xffffffffu;
-    if (counters) counters->rays++;
+    active = (shadowRay && shadowCounters) ? shadowCounters : counters;
+    if (active) active->rays++;
     if (!useBvh) {
         // src/accel.cpp:42-55 over the concatenation of all meshes (mesh order, then index):
         // `t <= maxt` with maxt tightened per hit => among equal t the highest id wins.
@@ -174,7 +177,7 @@ inline uint32_t Accel::trace(const Ray &ray_, bool shadowRay, float &tOut, float
     uint32_t stack[64]; int sp = 0; stack[sp++] = 0;
     while (sp > 0) {
         const BvhNode &n = nodes[stack[--sp]];
-        if (counters) counters->boxTests++;
+        if (active) active->boxTests++;
         if (!n.box.rayIntersect(ray)) continue;
         if (n.count > 0) {
             for (uint32_t i = 0; i < n.count; ++i) {

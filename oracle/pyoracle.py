@@ -110,6 +110,12 @@ class PortScene:
         self.L.noracle_sample_radiance(self.h, n, pixel, sample, rgb, pos, stats)
         return rgb, pos, stats
 
+    def render_counted(self, mode=1, sample_first=0, sample_last=1, stride=1):
+        """Traversal work of the oracle BVH over a render: ({rays, box, tri} closest, same for shadow)."""
+        c = np.zeros(6, np.uint64); st = np.zeros(3, np.uint64)
+        self.L.noracle_render_counted(self.h, mode, sample_first, sample_last, stride, c, st)
+        return c[:3].astype(np.int64), c[3:].astype(np.int64)
+
     def render(self, mode=0, sample_first=0, sample_last=None, threads=0):
         if sample_last is None:
             sample_last = self.scene.sample_count
@@ -149,6 +155,7 @@ class Port:
         L.noracle_splat.restype = C.c_uint64
         L.noracle_sample_radiance.argtypes = [C.c_void_p, C.c_int, _u32p, _u32p, _f32p, _f32p, _u64p]
         L.noracle_render.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _f32p, _u64p]
+        L.noracle_render_counted.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _u64p, _u64p]
 
     def scene(self, scene: FlatScene, use_bvh=True) -> PortScene:
         return PortScene(self, scene, use_bvh)
