@@ -43,6 +43,7 @@ struct Counters {
     unsigned int slotPass[kMaxRing];        // pass currently held by a ring slot
     unsigned int forcePass;                 // pass whose tiles are splatted now although samples are still in flight
     unsigned int lateSamples;               // samples that finished after their pass was closed (direct splat)
+    unsigned int traceCursor[2];            // next ray of the persistent traversal kernels (closest, shadow)
 };
 
 struct RenderParams {

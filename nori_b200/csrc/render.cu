@@ -16,7 +16,7 @@
 // ships no Integrator subclass: SURVEY.md F3), including the order in which a path consumes its
 // random numbers, so that a camera sample yields the same radiance on both sides.
 #include "engine.h"
-#include "traverse.cuh"
+#include "traverse_persistent.cuh"
 
 namespace ng {
 
@@ -41,6 +41,7 @@ __global__ void k_prepare(Counters *c, RenderParams rp) {
     c->closestRays += rays; c->segments += rays;
     c->shadowRays += c->shadowCount; c->shadowCount = 0;
     c->iterations++;
+    c->traceCursor[0] = 0; c->traceCursor[1] = 0;
     // lanes that drew an index at or past the previous limit discarded it: hand those indices out again
     if (c->issue > c->issueLimit) c->issue = c->issueLimit;
     unsigned cp = c->completedPasses;
@@ -201,26 +202,51 @@ __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, 
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_traceClosest(DeviceScene sc, Pool pool, Counters *c) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool alive = pool.meta[i].z & kFlagAlive;
-    int key = -1;
-    if (alive) {
+struct ClosestIO {
+    Pool pool;
+    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        if (!(pool.meta[i].z & kFlagAlive)) return false;
         const float4 ro = pool.rayO[i], rd = pool.rayD[i];
-        float t = 0.f, u = 0.f, v = 0.f;
-        uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), ro.w, rd.w, t, u, v);
+        o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float t, float u, float v) const {
         pool.hit[i] = make_float4(t, u, v, __uint_as_float(gid));
+    }
+};
+
+/// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
+__global__ void __launch_bounds__(128, 8) k_traceClosest(DeviceScene sc, Pool pool, Counters *c) {
+    ClosestIO io; io.pool = pool;
+    tracePersistent<false>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io);
+}
+
+/// Material-sorted queues for the shade stage: slot indices grouped by the BSDF of the surface hit
+/// (or "miss"), slot order preserved inside a group; five atomics per CTA.
+__global__ void __launch_bounds__(256) k_sortByMaterial(DeviceScene sc, Pool pool, Counters *c) {
+    __shared__ unsigned sCnt[8][kNumKeys], sBase[kNumKeys];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned warp = threadIdx.x >> 5;
+    int key = -1;
+    if (pool.meta[i].z & kFlagAlive) {
+        const uint32_t gid = __float_as_uint(pool.hit[i].w);
         key = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
     }
-    // material-sorted queues: one atomic per key present in the warp
-    unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (alive) {
-        int leader = __ffs(peers) - 1;
-        uint32_t base = 0;
-        if ((int) laneId() == leader) base = atomicAdd(&c->sortCount[key], (unsigned) __popc(peers));
-        base = __shfl_sync(peers, base, leader);
-        pool.sortQueue[(size_t) key * pool.capacity + base + __popc(peers & lanemaskLt())] = i;
+    unsigned rank = 0;
+#pragma unroll
+    for (int k = 0; k < kNumKeys; ++k) {
+        const unsigned m = __ballot_sync(0xffffffffu, key == k);
+        if (key == k) rank = __popc(m & lanemaskLt());
+        if (laneId() == 0) sCnt[warp][k] = __popc(m);
     }
+    __syncthreads();
+    if (threadIdx.x < kNumKeys) {
+        unsigned tot = 0;
+        for (int w = 0; w < 8; ++w) { unsigned n = sCnt[w][threadIdx.x]; sCnt[w][threadIdx.x] = tot; tot += n; }
+        sBase[threadIdx.x] = tot ? atomicAdd(&c->sortCount[threadIdx.x], tot) : 0u;
+    }
+    __syncthreads();
+    if (key >= 0) pool.sortQueue[(size_t) key * pool.capacity + sBase[key] + sCnt[warp][key] + rank] = i;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -469,18 +495,29 @@ __global__ void __launch_bounds__(256) k_shade(DeviceScene sc, Pool pool, Render
     }
 }
 
-__global__ void __launch_bounds__(256) k_traceShadow(DeviceScene sc, Pool pool, const Counters *c) {
-    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= c->shadowCount) return;
-    const float4 *e = pool.shadow + 3 * (size_t) g;
-    const float4 a = e[0], b = e[1], k = e[2];
-    float t, u, v;
-    uint32_t gid = traverse<true>(sc.nodes, sc.leafTris, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), kEpsilon, a.w, t, u, v);
-    if (gid != kNoHit) return;
-    const uint32_t slot = __float_as_uint(b.w);
-    float4 r = pool.rad[slot];
-    r.x = r.x + k.x; r.y = r.y + k.y; r.z = r.z + k.z;
-    pool.rad[slot] = r;
+struct ShadowIO {
+    Pool pool;
+    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        const float4 a = pool.shadow[3 * (size_t) i], b = pool.shadow[3 * (size_t) i + 1];
+        o = mk(a.x, a.y, a.z); d = mk(b.x, b.y, b.z); mint = kEpsilon; maxt = a.w;
+        return true;
+    }
+    /// Unoccluded: the light sample's contribution joins the path's radiance (one shadow ray per
+    /// path and iteration, so no two lanes touch the same slot).
+    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float, float, float) const {
+        if (gid != kNoHit) return;
+        const float4 b = pool.shadow[3 * (size_t) i + 1], k = pool.shadow[3 * (size_t) i + 2];
+        const uint32_t slot = __float_as_uint(b.w);
+        float4 r = pool.rad[slot];
+        r.x = r.x + k.x; r.y = r.y + k.y; r.z = r.z + k.z;
+        pool.rad[slot] = r;
+    }
+};
+
+/// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
+__global__ void __launch_bounds__(128, 8) k_traceShadow(DeviceScene sc, Pool pool, Counters *c) {
+    ShadowIO io; io.pool = pool;
+    tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -571,6 +608,13 @@ template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool
     k_shade<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
 
+/// One CTA slot per resident block: 8 CTAs of 128 threads per SM (launch bounds of the trace kernels).
+static unsigned persistentGrid() {
+    static unsigned g = 0;
+    if (!g) { int dev = 0, sms = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); g = (unsigned) sms * 8u; }
+    return g;
+}
+
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st, cudaEvent_t *ev) {
     const uint32_t grid = pool.capacity / 256;
     int launches = 0;
@@ -578,8 +622,9 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     k_prepare<<<1, 1, 0, st>>>(c, rp); ++launches;
     k_finishRegen<<<grid, 256, 0, st>>>(sc, pool, rp, c); ++launches;
     if (ev) cudaEventRecord(ev[1], st);
-    k_traceClosest<<<grid, 256, 0, st>>>(sc, pool, c); ++launches;
+    k_traceClosest<<<persistentGrid(), 128, 0, st>>>(sc, pool, c); ++launches;
     if (ev) cudaEventRecord(ev[2], st);
+    k_sortByMaterial<<<grid, 256, 0, st>>>(sc, pool, c); ++launches;
     switch (rp.integrator) {
     case NORI_INT_NORMALS: launchShade<NORI_INT_NORMALS>(sc, pool, rp, c, st); break;
     case NORI_INT_PATH_MATS: launchShade<NORI_INT_PATH_MATS>(sc, pool, rp, c, st); break;
@@ -592,7 +637,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     }
     ++launches;
     if (ev) cudaEventRecord(ev[3], st);
-    if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<grid, 256, 0, st>>>(sc, pool, c); ++launches; }
+    if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<persistentGrid(), 128, 0, st>>>(sc, pool, c); ++launches; }
     if (ev) cudaEventRecord(ev[4], st);
     if (!rp.listPixel) { k_splat<<<dim3(rp.numTiles, rp.ring, min((uint32_t) kSplatSplit, rp.K)), 256, 0, st>>>(sc, rp, c); ++launches; }
     if (ev) cudaEventRecord(ev[5], st);

@@ -1,0 +1,114 @@
+// traverse_persistent.cuh — persistent-warp traversal with dynamic ray fetch (the "while-while"
+// scheme of Aila & Laine): a warp keeps its 32 lanes busy by refilling lanes whose ray has
+// terminated from a global work counter as soon as enough of them are idle, instead of idling
+// until the slowest ray of the warp is done (ncu on the one-ray-per-thread kernel: 6.4 of 32
+// lanes active per issued instruction, profiles/r01_trace_before.md).
+//
+// Same node layout, slab and Moeller-Trumbore arithmetic and tie rule as traverse() in
+// traverse.cuh, i.e. the result is the triangle the reference's brute-force loop reports
+// (src/accel.cpp:42-55, src/mesh.cpp:51-88).
+//
+// IO concept:  bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt)   false: no ray at i
+//              void store(uint32_t i, uint32_t gid, float t, float u, float v)
+#pragma once
+#include "traverse.cuh"
+
+namespace ng {
+
+constexpr int kFetchThreshold = 20;   // refill when fewer than this many lanes still traverse
+
+template <bool ANY_HIT, class IO>
+NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
+                          unsigned int *workCounter, IO &io) {
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned ltMask; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(ltMask));
+    int stack[kStackSize];
+    int sp = 0, cur = 0;
+    bool active = false;
+    uint32_t rayIdx = 0xffffffffu, best = kNoHit;
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
+    float idx = 0, idy = 0, idz = 0, oodx = 0, oody = 0, oodz = 0, mint = 0, tbest = 0, bu = 0, bv = 0;
+    bool exhausted = false;
+
+    for (;;) {
+        // ---- refill idle lanes ------------------------------------------------------------
+        if (!exhausted) {
+            const unsigned idleMask = __ballot_sync(0xffffffffu, !active);
+            if (idleMask) {
+                unsigned base = 0;
+                const int leader = __ffs(idleMask) - 1;
+                if ((int) lane == leader) base = atomicAdd(workCounter, (unsigned) __popc(idleMask));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (base >= nRays) exhausted = true;
+                else if (!active) {
+                    const uint32_t i = base + __popc(idleMask & ltMask);
+                    float maxt;
+                    if (i < nRays && io.load(i, o, d, mint, maxt)) {
+                        const float big = 1e30f;
+                        idx = fabsf(d.x) > 1e-30f ? 1.0f / d.x : copysignf(big, d.x);
+                        idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);
+                        idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);
+                        oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz;
+                        rayIdx = i; tbest = maxt; best = kNoHit; sp = 0; cur = 0; active = true;
+                    }
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- traverse until too few lanes are left ------------------------------------------
+        for (;;) {
+            while (active && cur >= 0) {                       // inner nodes
+                const float4 *n = nodes + 4 * (size_t) cur;
+                const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+                const float lx0 = __fmaf_rn(n0.x, idx, -oodx), lx1 = __fmaf_rn(n0.y, idx, -oodx);
+                const float ly0 = __fmaf_rn(n0.z, idy, -oody), ly1 = __fmaf_rn(n0.w, idy, -oody);
+                const float lz0 = __fmaf_rn(n2.x, idz, -oodz), lz1 = __fmaf_rn(n2.y, idz, -oodz);
+                const float rx0 = __fmaf_rn(n1.x, idx, -oodx), rx1 = __fmaf_rn(n1.y, idx, -oodx);
+                const float ry0 = __fmaf_rn(n1.z, idy, -oody), ry1 = __fmaf_rn(n1.w, idy, -oody);
+                const float rz0 = __fmaf_rn(n2.z, idz, -oodz), rz1 = __fmaf_rn(n2.w, idz, -oodz);
+                const float lmin = fmaxf(fmaxf(fminf(lx0, lx1), fminf(ly0, ly1)), fmaxf(fminf(lz0, lz1), mint));
+                const float lmax = fminf(fminf(fmaxf(lx0, lx1), fmaxf(ly0, ly1)), fminf(fmaxf(lz0, lz1), tbest));
+                const float rmin = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), mint));
+                const float rmax = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), tbest));
+                const bool hl = lmin <= lmax, hr = rmin <= rmax;
+                int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
+                if (hl && hr) {
+                    if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
+                    stack[sp++] = cr;
+                    cur = cl;
+                } else if (hl) cur = cl;
+                else if (hr) cur = cr;
+                else if (sp > 0) cur = stack[--sp];
+                else active = false;                           // stack empty: the ray is done
+            }
+            if (active) {                                      // leaf
+                const uint32_t code = ~(uint32_t) cur;
+                const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+                for (uint32_t k = 0; k < cnt; ++k) {
+                    const float4 *tp = leafTris + 3 * (size_t) (first + k);
+                    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                    float u, v, t;
+                    if (rayTriangle(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, d, mint, tbest, u, v, t)) {
+                        const uint32_t gid = __float_as_uint(a.w);
+                        if (ANY_HIT) { best = gid; tbest = t; bu = u; bv = v; break; }
+                        if (t < tbest || best == kNoHit || gid > best) { tbest = t; best = gid; bu = u; bv = v; }
+                    }
+                }
+                if (ANY_HIT && best != kNoHit) active = false;
+                else if (sp > 0) cur = stack[--sp];
+                else active = false;
+            }
+            if (!active && rayIdx != 0xffffffffu) {
+                io.store(rayIdx, best, best == kNoHit ? 0.f : tbest, bu, bv);
+                rayIdx = 0xffffffffu;
+            }
+            const unsigned am = __ballot_sync(0xffffffffu, active);
+            if (!am || (!exhausted && __popc(am) < kFetchThreshold)) break;
+        }
+    }
+}
+
+} // namespace ng
