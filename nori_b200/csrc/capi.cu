@@ -32,7 +32,7 @@ struct nori_gpu_ctx {
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 21;
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
-    uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr; size_t tileDoneCap = 0;
+    uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
 };
 
@@ -71,7 +71,7 @@ void freePool(nori_gpu_ctx *c) {
     if (!c->havePool) return;
     Pool &p = c->pool;
     cudaFree(p.rayO); cudaFree(p.rayD); cudaFree(p.hit); cudaFree(p.thr); cudaFree(p.rad); cudaFree(p.rng); cudaFree(p.meta);
-    cudaFree(p.pos); cudaFree(p.sortQueue); cudaFree(p.shadow);
+    cudaFree(p.pos); cudaFree(p.shadow);
     c->havePool = false;
 }
 
@@ -84,7 +84,7 @@ int ensurePool(nori_gpu_ctx *ctx) {
     CK(cudaMalloc((void **) &p.rayO, n * 16)); CK(cudaMalloc((void **) &p.rayD, n * 16)); CK(cudaMalloc((void **) &p.hit, n * 16));
     CK(cudaMalloc((void **) &p.thr, n * 16)); CK(cudaMalloc((void **) &p.rad, n * 16)); CK(cudaMalloc((void **) &p.rng, n * 16));
     CK(cudaMalloc((void **) &p.meta, n * 16)); CK(cudaMalloc((void **) &p.pos, n * 8));
-    CK(cudaMalloc((void **) &p.sortQueue, n * 4 * kNumKeys)); CK(cudaMalloc((void **) &p.shadow, n * 48));
+    CK(cudaMalloc((void **) &p.shadow, n * 48));
     ctx->havePool = true;
     return 0;
 }
@@ -138,7 +138,7 @@ void nori_gpu_destroy(nori_gpu_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     freeScene(ctx); freePool(ctx);
     cudaFree(ctx->d_block); cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
-    cudaFree(ctx->recA); cudaFree(ctx->recB); cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive);
+    cudaFree(ctx->recA); cudaFree(ctx->recB); cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive); cudaFree(ctx->readyTiles);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -246,6 +246,7 @@ int nori_gpu_set_camera(nori_gpu_ctx *ctx, const NoriGpuCameraDesc *cam) {
     ctx->cam.width = cam->width; ctx->cam.height = cam->height;
     ctx->cam.nearClip = cam->near_clip; ctx->cam.farClip = cam->far_clip;
     ctx->cam.invW = 1.0f / (float) cam->width; ctx->cam.invH = 1.0f / (float) cam->height;   // perspective.cpp:38
+    ctx->cam.origin = mulPoint(ctx->cam.c2w, mk(0, 0, 0));
     ctx->haveCamera = true;
     return NORI_GPU_OK;
 }
@@ -324,18 +325,19 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     }
     const size_t tdNeed = (size_t) rp.ring * rp.numTiles;
     if (tdNeed > ctx->tileDoneCap) {
-        cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive); ctx->tileDone = ctx->tileGen = ctx->tileArrive = nullptr;
+        cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive); cudaFree(ctx->readyTiles); ctx->tileDone = ctx->tileGen = ctx->tileArrive = ctx->readyTiles = nullptr;
+        CK(cudaMalloc((void **) &ctx->readyTiles, tdNeed * sizeof(uint32_t)));
         CK(cudaMalloc((void **) &ctx->tileArrive, tdNeed * sizeof(uint32_t)));
         CK(cudaMalloc((void **) &ctx->tileDone, tdNeed * sizeof(uint32_t))); CK(cudaMalloc((void **) &ctx->tileGen, tdNeed * sizeof(uint32_t)));
         ctx->tileDoneCap = tdNeed;
     }
-    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.poolCapacity = ctx->pool.capacity;
+    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.readyTiles = ctx->readyTiles; rp.poolCapacity = ctx->pool.capacity;
     CK(cudaMemsetAsync(ctx->tileDone, 0, tdNeed * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(ctx->tileGen, 0, tdNeed * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(ctx->tileArrive, 0, tdNeed * sizeof(uint32_t), st));
     if (!list) CK(cudaMemsetAsync(ctx->recA, 0xff, recNeed * sizeof(float4), st));        // NaN position = no sample recorded
     CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), st));
-    CK(cudaMemsetAsync(ctx->pool.meta, 0, (size_t) ctx->pool.capacity * sizeof(uint4), st));
+    enqueuePoolInit(ctx->pool, ctx->d_counters, st);
     if (d->clear && !list) CK(cudaMemsetAsync(ctx->d_block, 0, ctx->blockFloats * sizeof(float), st));
 
     const DeviceScene sc = deviceScene(ctx);

@@ -29,7 +29,6 @@ struct Pool {
     ulonglong2 *rng;     // pcg32 state, inc
     uint4 *meta;         // pixel index, sample index, flags | depth | ring slot << 24, record index
     float2 *pos;         // pixelSample handed to ImageBlock::put
-    uint32_t *sortQueue; // kNumKeys x capacity slot indices, by material key of the hit
     float4 *shadow;      // 3 x capacity: (o, maxt) (d, bits(slot)) (contribution, -)
 };
 
@@ -43,6 +42,8 @@ struct Counters {
     unsigned int slotPass[kMaxRing];        // pass currently held by a ring slot
     unsigned int forcePass;                 // pass whose tiles are splatted now although samples are still in flight
     unsigned int lateSamples;               // samples that finished after their pass was closed (direct splat)
+    unsigned int readyCount;                // entries of RenderParams::readyTiles (tiles splatted this iteration)
+    unsigned int passHint;                  // pass containing the next sample index to be issued
     unsigned int traceCursor[2];            // next ray of the persistent traversal kernels (closest, shadow)
 };
 
@@ -62,6 +63,7 @@ struct RenderParams {
     float4 *recA; float *recB;
     uint32_t *tileDone;                      // ring x numTiles: finished samples of the pass held by the slot
     uint32_t *tileGen;                       // ring x numTiles: passes already splatted for this (slot, tile)
+    uint32_t *readyTiles;                    // ring x numTiles: (slot * numTiles + tile) entries ready to splat
     uint32_t *tileArrive;                    // ring x numTiles: k_splat CTAs of the tile that finished (reset by the last)
     uint32_t poolCapacity;
     float *block;                            // (H+2b) x (W+2b) x RGBW accumulator
@@ -69,6 +71,9 @@ struct RenderParams {
 };
 
 struct StageTimes { float generate, traceClosest, shade, traceShadow, splat; };
+
+/// Marks every slot of the pool empty (start of a render).
+void enqueuePoolInit(const Pool &pool, Counters *d_counters, cudaStream_t st);
 
 /// One wavefront iteration, enqueued on `st`. Returns the number of kernel launches.
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,

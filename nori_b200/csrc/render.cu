@@ -42,8 +42,10 @@ __global__ void k_prepare(Counters *c, RenderParams rp) {
     c->shadowRays += c->shadowCount; c->shadowCount = 0;
     c->iterations++;
     c->traceCursor[0] = 0; c->traceCursor[1] = 0;
+    c->readyCount = 0;
     // lanes that drew an index at or past the previous limit discarded it: hand those indices out again
     if (c->issue > c->issueLimit) c->issue = c->issueLimit;
+    c->passHint = rp.listPixel ? 0u : (unsigned) (c->issue / rp.passSlots);   // pass of the next index to hand out
     unsigned cp = c->completedPasses;
     while (cp < rp.numPasses && c->tilesSplatted[cp % rp.ring] >= rp.numTiles * (cp / rp.ring + 1)) ++cp;
     c->completedPasses = cp;
@@ -83,9 +85,11 @@ __device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Count
     }
 }
 
-__global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+__global__ void __launch_bounds__(256, 6) k_finishRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;      // capacity is a multiple of 256
     uint4 meta = pool.meta[i];
+    const float4 rad = pool.rad[i];               // loaded up front (all lanes): one memory round trip, not two
+    const float2 oldPos = pool.pos[i];
     const bool dead = !(meta.z & kFlagAlive);
     const int W = sc.cam.width, H = sc.cam.height;
 
@@ -93,18 +97,16 @@ __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, 
     const bool fin = dead && (meta.z & kFlagHasSample);
     bool late = false;
     if (fin) {
-        float4 rad = pool.rad[i];
         V3 L = mk(rad.x, rad.y, rad.z);
         if (meta.z & kFlagMulT) { float4 t = pool.thr[i]; L = mk(t.x, t.y, t.z) * L; }
         const uint32_t slot = meta.z >> 24;
-        float2 ps = pool.pos[i];
         late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
         if (late) {
-            splatDirect(sc, rp, c, ps, L);
+            splatDirect(sc, rp, c, oldPos, L);
             atomicAdd(&c->lateSamples, 1u);
         } else {
             const size_t r = (size_t) slot * rp.passSlots + meta.w;
-            rp.recA[r] = make_float4(ps.x, ps.y, L.x, L.y);
+            rp.recA[r] = make_float4(oldPos.x, oldPos.y, L.x, L.y);
             rp.recB[r] = L.z;
         }
     }
@@ -129,6 +131,7 @@ __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, 
 
     // ---- draw the next camera sample into the free slot ------------------------------------
     const unsigned long long limit = c->issueLimit;
+    const uint32_t passHint = c->passHint;
     const bool want = dead && *(volatile unsigned long long *) &c->issue < limit;
     bool need = want;
     uint32_t x = 0, y = 0, sampleK = 0, rec = 0, slot = 0;
@@ -157,7 +160,11 @@ __global__ void __launch_bounds__(256) k_finishRegen(DeviceScene sc, Pool pool, 
                     x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g; slot = 0;
                     need = false;
                 } else {
-                    uint32_t pass = (uint32_t) (g / rp.passSlots), j = (uint32_t) (g - (unsigned long long) pass * rp.passSlots);
+                    // g lies in the hinted pass or just after it (a pass holds several pools): no 64-bit division
+                    uint32_t pass = passHint;
+                    unsigned long long j64 = g - (unsigned long long) pass * rp.passSlots;
+                    while (j64 >= rp.passSlots) { j64 -= rp.passSlots; ++pass; }
+                    const uint32_t j = (uint32_t) j64;
                     uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
                     uint32_t tile = j / (1024u * Kp), r = j - tile * (1024u * Kp);
                     tilePixel(r & 1023u, lx, ly);
@@ -219,34 +226,6 @@ struct ClosestIO {
 __global__ void __launch_bounds__(128, 8) k_traceClosest(DeviceScene sc, Pool pool, Counters *c) {
     ClosestIO io; io.pool = pool;
     tracePersistent<false>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io);
-}
-
-/// Material-sorted queues for the shade stage: slot indices grouped by the BSDF of the surface hit
-/// (or "miss"), slot order preserved inside a group; five atomics per CTA.
-__global__ void __launch_bounds__(256) k_sortByMaterial(DeviceScene sc, Pool pool, Counters *c) {
-    __shared__ unsigned sCnt[8][kNumKeys], sBase[kNumKeys];
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const unsigned warp = threadIdx.x >> 5;
-    int key = -1;
-    if (pool.meta[i].z & kFlagAlive) {
-        const uint32_t gid = __float_as_uint(pool.hit[i].w);
-        key = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
-    }
-    unsigned rank = 0;
-#pragma unroll
-    for (int k = 0; k < kNumKeys; ++k) {
-        const unsigned m = __ballot_sync(0xffffffffu, key == k);
-        if (key == k) rank = __popc(m & lanemaskLt());
-        if (laneId() == 0) sCnt[warp][k] = __popc(m);
-    }
-    __syncthreads();
-    if (threadIdx.x < kNumKeys) {
-        unsigned tot = 0;
-        for (int w = 0; w < 8; ++w) { unsigned n = sCnt[w][threadIdx.x]; sCnt[w][threadIdx.x] = tot; tot += n; }
-        sBase[threadIdx.x] = tot ? atomicAdd(&c->sortCount[threadIdx.x], tot) : 0u;
-    }
-    __syncthreads();
-    if (key >= 0) pool.sortQueue[(size_t) key * pool.capacity + sBase[key] + sCnt[warp][key] + rank] = i;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -448,24 +427,49 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
     return true;
 }
 
+/// The shade stage. A CTA owns 256 consecutive path slots (their state is read and written fully
+/// coalesced) and sorts them by the BSDF of the surface hit in shared memory before shading, so
+/// that warps run one material's code; finished slots sort to the end. Shadow rays leave through
+/// a compacted queue (one atomic per CTA).
 template <int INTEGRATOR>
 __global__ void __launch_bounds__(256) k_shade(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
-    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    // locate this thread's entry in the concatenation of the material queues
-    int key = -1; uint32_t idx = g;
-    {
-        uint32_t acc = 0;
-#pragma unroll
-        for (int k = 0; k < kNumKeys; ++k) {
-            uint32_t n = c->sortCount[k];
-            if (key < 0 && g < acc + n) { key = k; idx = g - acc; }
-            acc += n;
-        }
+    constexpr int NK = kNumKeys + 1;                         // + "no live path in this slot"
+    __shared__ unsigned sCnt[8][NK], sOff[NK + 1], sWarpShadow[8], sShadowBase;
+    __shared__ unsigned short sPerm[256];
+    const unsigned tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t blockBase = blockIdx.x * blockDim.x;
+    // ---- CTA-local counting sort by material key -----------------------------------------
+    int key0 = kNumKeys;
+    if (pool.meta[blockBase + tid].z & kFlagAlive) {
+        const uint32_t gid = __float_as_uint(pool.hit[blockBase + tid].w);
+        key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
     }
+    unsigned rank = 0;
+#pragma unroll
+    for (int k = 0; k < NK; ++k) {
+        const unsigned m = __ballot_sync(0xffffffffu, key0 == k);
+        if (key0 == k) rank = __popc(m & lanemaskLt());
+        if (laneId() == 0) sCnt[warp][k] = __popc(m);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned acc = 0;
+        for (int k = 0; k < NK; ++k) {
+            sOff[k] = acc;
+            for (int w = 0; w < 8; ++w) { unsigned n = sCnt[w][k]; sCnt[w][k] = acc; acc += n; }
+        }
+        sOff[NK] = acc;
+        const unsigned alive = sOff[kNumKeys];
+        if (alive) atomicAdd(&c->sortCount[0], alive);       // closest rays traced = live slots
+    }
+    __syncthreads();
+    sPerm[sCnt[warp][key0] + rank] = (unsigned short) tid;
+    __syncthreads();
+    const uint32_t slot = blockBase + sPerm[tid];
+    const bool live = tid < sOff[kNumKeys];
+
     ShadowOut sh; sh.cast = false;
-    uint32_t slot = 0;
-    if (key >= 0) {
-        slot = pool.sortQueue[(size_t) key * pool.capacity + idx];
+    if (live) {
         const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
         const ulonglong2 rs = pool.rng[slot];
         uint4 meta = pool.meta[slot];
@@ -485,10 +489,18 @@ __global__ void __launch_bounds__(256) k_shade(DeviceScene sc, Pool pool, Render
         meta.z = flags;
         pool.meta[slot] = meta;
     }
-    // shadow-ray queue (compacted)
-    const uint32_t q = warpAppend(&c->shadowCount, sh.cast);
+    // ---- shadow-ray queue (compacted) ------------------------------------------------------
+    const unsigned sm = __ballot_sync(0xffffffffu, sh.cast);
+    if (laneId() == 0) sWarpShadow[warp] = __popc(sm);
+    __syncthreads();
+    if (tid == 0) {
+        unsigned acc = 0;
+        for (int w = 0; w < 8; ++w) { unsigned n = sWarpShadow[w]; sWarpShadow[w] = acc; acc += n; }
+        sShadowBase = acc ? atomicAdd(&c->shadowCount, acc) : 0u;
+    }
+    __syncthreads();
     if (sh.cast) {
-        float4 *e = pool.shadow + 3 * (size_t) q;
+        float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(sm & lanemaskLt()));
         e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
         e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
         e[2] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, 0.f);
@@ -526,25 +538,42 @@ __global__ void __launch_bounds__(128, 8) k_traceShadow(DeviceScene sc, Pool poo
 /// `result.put(block)` (src/block.cpp:105-114) into the full-frame accumulator.
 constexpr int kSplatSide = kTile + 2 * kMaxBorder;
 constexpr int kSplatSplit = 8;      // CTAs sharing one tile (each takes the samples k = z, z + Z, ...)
+/// Which (ring slot, tile) pairs are splatted in this iteration: complete tiles, and every pending
+/// tile of a pass that is being closed early. One thread per pair; the splat kernels then run
+/// only over this list with a grid sized to the machine.
+__global__ void k_splatPlan(DeviceScene sc, RenderParams rp, Counters *c) {
+    const uint32_t ti = blockIdx.x * blockDim.x + threadIdx.x;
+    bool ready = false;
+    if (ti < (uint32_t) rp.ring * rp.numTiles) {
+        const uint32_t slot = ti / rp.numTiles, tile = ti - slot * rp.numTiles;
+        const uint32_t pass = c->slotPass[slot];
+        if (pass < rp.numPasses && rp.tileGen[ti] == pass / (uint32_t) rp.ring) {
+            const int ox = (int) (tile % (uint32_t) rp.tilesX) * kTile, oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
+            const int tw = min(sc.cam.width - ox, kTile), th = min(sc.cam.height - oy, kTile);
+            const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
+            ready = pass == c->forcePass || rp.tileDone[ti] == (uint32_t) (tw * th) * Kp;
+        }
+    }
+    const uint32_t q = warpAppend(&c->readyCount, ready);
+    if (ready) rp.readyTiles[q] = ti;
+}
+
 __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, Counters *c) {
     __shared__ float plane[4][kSplatSide * kSplatSide];
     __shared__ float sTable[33];
     __shared__ unsigned sDropped;
-    const uint32_t tile = blockIdx.x, slot = blockIdx.y, z = blockIdx.z, Z = gridDim.z;
+    const uint32_t Z = min((uint32_t) kSplatSplit, rp.K);
+    for (uint32_t work = blockIdx.x; work < c->readyCount * Z; work += gridDim.x) {
+    const uint32_t tiq = rp.readyTiles[work / Z], z = work % Z;
+    const uint32_t slot = tiq / rp.numTiles, tile = tiq - slot * rp.numTiles;
     const uint32_t pass = c->slotPass[slot];
-    if (pass >= rp.numPasses) return;
     const int W = sc.cam.width, H = sc.cam.height, b = sc.filter.border;
     const int ox = (int) (tile % (uint32_t) rp.tilesX) * kTile, oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
     const int tw = min(W - ox, kTile), th = min(H - oy, kTile);
     const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
     const uint32_t ti = slot * rp.numTiles + tile;
-    // All Z CTAs of a tile take the same decision: the bookkeeping below is only changed by the
-    // last of them to arrive.
-    if (rp.tileGen[ti] != pass / (uint32_t) rp.ring) return;                     // this pass of the tile is already in the block
-    const bool force = pass == c->forcePass;
-    if (!force && rp.tileDone[ti] != (uint32_t) (tw * th) * Kp) return;
-
     const int cols = tw + 2 * b, rows = th + 2 * b;
+    __syncthreads();                                                            // shared tile is reused across work items
     if (z < Kp) {
         for (int k = threadIdx.x; k < cols * rows; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
         if (threadIdx.x < 33) sTable[threadIdx.x] = sc.filter.table[threadIdx.x];
@@ -601,12 +630,128 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
             atomicAdd(&c->tilesSplatted[slot], 1u);
         }
     }
+    }
+}
+
+/// The same stage for filters whose border is at most 2 pixels (all of the reference's: gaussian
+/// and mitchell radius 2, tent 1, box 0.5): one thread per PIXEL of a 16x16 quadrant of the tile
+/// walks the K samples of its pixel and accumulates their (2B+1)^2 footprint in registers; only
+/// then does it touch the shared-memory ImageBlock (one atomic per cell and channel per pass
+/// instead of one per sample), which the CTA finally adds to the full-frame block.
+template <int B>
+__global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams rp, Counters *c) {
+    constexpr int WN = 2 * B + 1, Q = 16, SIDE = Q + 2 * B;
+    __shared__ float plane[4][SIDE * SIDE];
+    __shared__ float sTable[33];
+    __shared__ unsigned sDropped;
+    for (uint32_t work = blockIdx.x; work < c->readyCount * 4u; work += gridDim.x) {
+    const uint32_t tiq = rp.readyTiles[work >> 2], z = work & 3u;
+    const uint32_t slot = tiq / rp.numTiles, tile = tiq - slot * rp.numTiles;
+    const uint32_t pass = c->slotPass[slot];
+    const int W = sc.cam.width, H = sc.cam.height;
+    const int ox = (int) (tile % (uint32_t) rp.tilesX) * kTile, oy = (int) (tile / (uint32_t) rp.tilesX) * kTile;
+    const int tw = min(W - ox, kTile), th = min(H - oy, kTile);
+    const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
+    const uint32_t ti = slot * rp.numTiles + tile;
+    __syncthreads();                                                            // shared tile is reused across work items
+    const int qx = (int) (z & 1u), qy = (int) (z >> 1);
+    if (qx * Q < tw && qy * Q < th) {
+        for (int k = threadIdx.x; k < SIDE * SIDE; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
+        if (threadIdx.x < 33) sTable[threadIdx.x] = sc.filter.table[threadIdx.x];
+        if (threadIdx.x == 0) sDropped = 0;
+        __syncthreads();
+        // thread -> record slot of its pixel (inverse of tilePixel: warps are 8x4 pixel patches)
+        const uint32_t wi = threadIdx.x >> 5;
+        const uint32_t wq = (wi & 1u) + 2u * (uint32_t) qx + 4u * ((wi >> 1) + 4u * (uint32_t) qy);
+        const uint32_t pix = wq * 32u + (threadIdx.x & 31u);
+        int lx, ly; tilePixel(pix, lx, ly);
+        const int tx = lx - qx * Q, ty = ly - qy * Q;              // position inside the quadrant
+        float acc[WN][WN][4];
+#pragma unroll
+        for (int i = 0; i < WN; ++i)
+#pragma unroll
+            for (int j = 0; j < WN; ++j) { acc[i][j][0] = 0.f; acc[i][j][1] = 0.f; acc[i][j][2] = 0.f; acc[i][j][3] = 0.f; }
+        const bool inside = lx < tw && ly < th;
+        if (inside) {
+            const float radius = sc.filter.radius, lookup = sc.filter.lookupFactor;
+            const int cols = tw + 2 * B, rows = th + 2 * B;
+            const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp + pix;
+            unsigned dropped = 0;
+#pragma unroll 2
+            for (uint32_t k = 0; k < Kp; ++k) {
+                const size_t r = base + (size_t) k * 1024u;
+                const float4 a = rp.recA[r];
+                if (isnan(a.x)) continue;                                        // still in flight (forced close)
+                const V3 val = mk(a.z, a.w, rp.recB[r]);
+                rp.recA[r].x = __int_as_float(0x7fc00000);                       // consumed
+                if (!isValidColor(val)) { ++dropped; continue; }                 // block.cpp:75-79
+                const float px = a.x - 0.5f - (float) (ox - B), py = a.y - 0.5f - (float) (oy - B);   // block.cpp:82-85
+                const int x0 = max((int) ceilf(px - radius), 0), y0 = max((int) ceilf(py - radius), 0);
+                const int x1 = min((int) floorf(px + radius), cols - 1), y1 = min((int) floorf(py + radius), rows - 1);
+                float wx[WN], wy[WN];
+#pragma unroll
+                for (int j = 0; j < WN; ++j) {
+                    const int x = lx + j, y = ly + j;                            // window cell = pixel + B - B + j
+                    wx[j] = (x >= x0 && x <= x1) ? sTable[min((int) (fabsf((float) x - px) * lookup), 32)] : 0.f;
+                    wy[j] = (y >= y0 && y <= y1) ? sTable[min((int) (fabsf((float) y - py) * lookup), 32)] : 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < WN; ++i)
+#pragma unroll
+                    for (int j = 0; j < WN; ++j) {
+                        acc[i][j][0] += val.x * wx[j] * wy[i];                   // block.cpp:100-102
+                        acc[i][j][1] += val.y * wx[j] * wy[i];
+                        acc[i][j][2] += val.z * wx[j] * wy[i];
+                        acc[i][j][3] += 1.0f * wx[j] * wy[i];
+                    }
+            }
+            if (dropped) atomicAdd(&sDropped, dropped);
+#pragma unroll
+            for (int i = 0; i < WN; ++i)
+#pragma unroll
+                for (int j = 0; j < WN; ++j) {
+                    const int cell = (ty + i) * SIDE + tx + j;
+                    if (acc[i][j][3] != 0.f) {
+                        atomicAdd(&plane[0][cell], acc[i][j][0]); atomicAdd(&plane[1][cell], acc[i][j][1]);
+                        atomicAdd(&plane[2][cell], acc[i][j][2]); atomicAdd(&plane[3][cell], acc[i][j][3]);
+                    }
+                }
+        }
+        __syncthreads();
+        // quadrant cell (x, y) is full-frame cell (ox + 16 qx + x, oy + 16 qy + y)
+        for (int k = threadIdx.x; k < SIDE * SIDE; k += blockDim.x) {
+            const float4 v = make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]);
+            if (v.w == 0.f) continue;
+            const int x = k % SIDE, y = k / SIDE;
+            float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + qy * Q + y) * rp.blockCols + (ox + qx * Q + x);
+            atomicAdd(dst, v);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && sDropped) atomicAdd(&c->dropped, (unsigned long long) sDropped);
+    }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(rp.tileArrive + ti, 1u) == 3u) {                            // last quadrant of this tile
+            rp.tileArrive[ti] = 0;
+            rp.tileDone[ti] = 0;
+            rp.tileGen[ti] = pass / (uint32_t) rp.ring + 1;
+            __threadfence();
+            atomicAdd(&c->tilesSplatted[slot], 1u);
+        }
+    }
+    }
 }
 
 // ------------------------------------------------------------------------------------------
 template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
     k_shade<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
+
+__global__ void k_poolInit(Pool pool, Counters *c) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    pool.meta[i] = make_uint4(0, 0, 0, 0);
+}
+void enqueuePoolInit(const Pool &pool, Counters *c, cudaStream_t st) { k_poolInit<<<pool.capacity / 256, 256, 0, st>>>(pool, c); }
 
 /// One CTA slot per resident block: 8 CTAs of 128 threads per SM (launch bounds of the trace kernels).
 static unsigned persistentGrid() {
@@ -624,7 +769,6 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     if (ev) cudaEventRecord(ev[1], st);
     k_traceClosest<<<persistentGrid(), 128, 0, st>>>(sc, pool, c); ++launches;
     if (ev) cudaEventRecord(ev[2], st);
-    k_sortByMaterial<<<grid, 256, 0, st>>>(sc, pool, c); ++launches;
     switch (rp.integrator) {
     case NORI_INT_NORMALS: launchShade<NORI_INT_NORMALS>(sc, pool, rp, c, st); break;
     case NORI_INT_PATH_MATS: launchShade<NORI_INT_PATH_MATS>(sc, pool, rp, c, st); break;
@@ -639,7 +783,17 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     if (ev) cudaEventRecord(ev[3], st);
     if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<persistentGrid(), 128, 0, st>>>(sc, pool, c); ++launches; }
     if (ev) cudaEventRecord(ev[4], st);
-    if (!rp.listPixel) { k_splat<<<dim3(rp.numTiles, rp.ring, min((uint32_t) kSplatSplit, rp.K)), 256, 0, st>>>(sc, rp, c); ++launches; }
+    if (!rp.listPixel) {
+        k_splatPlan<<<((uint32_t) rp.ring * rp.numTiles + 255u) / 256u, 256, 0, st>>>(sc, rp, c); ++launches;
+        const unsigned g = persistentGrid() / 4u;          // 2 CTAs of 256 threads per SM
+        switch (sc.filter.border) {
+        case 0: k_splatPixel<0><<<g, 256, 0, st>>>(sc, rp, c); break;
+        case 1: k_splatPixel<1><<<g, 256, 0, st>>>(sc, rp, c); break;
+        case 2: k_splatPixel<2><<<g, 256, 0, st>>>(sc, rp, c); break;
+        default: k_splat<<<g, 256, 0, st>>>(sc, rp, c); break;
+        }
+        ++launches;
+    }
     if (ev) cudaEventRecord(ev[5], st);
     return launches;
 }

@@ -31,6 +31,7 @@ struct Camera {
     float s2c[16], c2w[16];
     float invW, invH, nearClip, farClip;
     int width, height;
+    V3 origin;                   // cameraToWorld * (0,0,0), constant over samples (perspective.cpp:100)
 };
 
 /// ImageBlock filter state (src/block.cpp:31-39)
@@ -83,7 +84,7 @@ NG_HD Ray sampleRay(const Camera &c, V2 samplePosition) {
     V3 d = normalized(nearP);
     float invZ = 1.0f / d.z;
     Ray ray;
-    ray.o = mulPoint(c.c2w, mk(0, 0, 0));
+    ray.o = c.origin;
     ray.d = mulVector(c.c2w, d);
     ray.mint = c.nearClip * invZ;
     ray.maxt = c.farClip * invZ;
