@@ -69,12 +69,13 @@ NG_HD V3 mulPoint(const float *m, V3 p) {
         r[i] = ((m[4 * i + 0] * p.x + m[4 * i + 1] * p.y) + m[4 * i + 2] * p.z) + m[4 * i + 3] * 1.0f;
     return mk(r[0] / r[3], r[1] / r[3], r[2] / r[3]);
 }
-/// Transform * Vector3f (transform.h:66-68)
+/// Transform * Vector3f (transform.h:66-68): coefficient-wise 3x3 product, Eigen's unrolled
+/// reduction x0 + (x1 + x2) (Redux.h:94-103) — pinned by tests/golden/ref_vectors.npz (bunny, table).
 NG_HD V3 mulVector(const float *m, V3 v) {
     float r[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i)
-        r[i] = (m[4 * i + 0] * v.x + m[4 * i + 1] * v.y) + m[4 * i + 2] * v.z;
+        r[i] = m[4 * i + 0] * v.x + (m[4 * i + 1] * v.y + m[4 * i + 2] * v.z);
     return mk(r[0], r[1], r[2]);
 }
 

@@ -44,11 +44,13 @@ inline V3 mulPoint(const float *m, V3 p) {
         r[i] = ((m[4 * i + 0] * p.x + m[4 * i + 1] * p.y) + m[4 * i + 2] * p.z) + m[4 * i + 3] * 1.0f;
     return mk(r[0] / r[3], r[1] / r[3], r[2] / r[3]);
 }
-/// Transform * Vector3f (transform.h:66-68): topLeftCorner<3,3>() * v.
+/// Transform * Vector3f (transform.h:66-68): topLeftCorner<3,3>() * v. Eigen evaluates this small
+/// product coefficient-wise with the unrolled fixed-size reduction x0 + (x1 + x2) (Redux.h:94-103),
+/// like dot() — pinned against the compiled reference on a rotated camera (bunny, table).
 inline V3 mulVector(const float *m, V3 v) {
     float r[3];
     for (int i = 0; i < 3; ++i)
-        r[i] = (m[4 * i + 0] * v.x + m[4 * i + 1] * v.y) + m[4 * i + 2] * v.z;
+        r[i] = m[4 * i + 0] * v.x + (m[4 * i + 1] * v.y + m[4 * i + 2] * v.z);
     return mk(r[0], r[1], r[2]);
 }
 
