@@ -16,6 +16,7 @@
 // ships no Integrator subclass: SURVEY.md F3), including the order in which a path consumes its
 // random numbers, so that a camera sample yields the same radiance on both sides.
 #include "engine.h"
+#include <cstdlib>
 #include "traverse_persistent.cuh"
 
 namespace ng {
@@ -223,9 +224,9 @@ struct ClosestIO {
 };
 
 /// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
-__global__ void __launch_bounds__(128, 8) k_traceClosest(DeviceScene sc, Pool pool, Counters *c) {
+__global__ void __launch_bounds__(128, 8) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ClosestIO io; io.pool = pool;
-    tracePersistent<false>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io);
+    tracePersistent<false>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -527,9 +528,9 @@ struct ShadowIO {
 };
 
 /// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
-__global__ void __launch_bounds__(128, 8) k_traceShadow(DeviceScene sc, Pool pool, Counters *c) {
+__global__ void __launch_bounds__(128, 8) k_traceShadow(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ShadowIO io; io.pool = pool;
-    tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io);
+    tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -760,6 +761,19 @@ static unsigned persistentGrid() {
     return g;
 }
 
+/// Tunables of the traversal kernels (environment overrides are for parameter sweeps only).
+struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; };
+static const Tune &tune() {
+    static Tune t = [] {
+        Tune v = {kFetchThreshold, kFetchThreshold, 8u};
+        if (const char *s = getenv("NORI_GPU_FETCH")) v.fetchClosest = v.fetchShadow = atoi(s);
+        if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = atoi(s);
+        if (const char *s = getenv("NORI_GPU_TRACE_CTAS")) v.ctasPerSm = (unsigned) atoi(s);
+        return v;
+    }();
+    return t;
+}
+
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st, cudaEvent_t *ev) {
     const uint32_t grid = pool.capacity / 256;
     int launches = 0;
@@ -767,7 +781,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     k_prepare<<<1, 1, 0, st>>>(c, rp); ++launches;
     k_finishRegen<<<grid, 256, 0, st>>>(sc, pool, rp, c); ++launches;
     if (ev) cudaEventRecord(ev[1], st);
-    k_traceClosest<<<persistentGrid(), 128, 0, st>>>(sc, pool, c); ++launches;
+    k_traceClosest<<<persistentGrid() * tune().ctasPerSm / 8u, 128, 0, st>>>(sc, pool, c, tune().fetchClosest); ++launches;
     if (ev) cudaEventRecord(ev[2], st);
     switch (rp.integrator) {
     case NORI_INT_NORMALS: launchShade<NORI_INT_NORMALS>(sc, pool, rp, c, st); break;
@@ -781,7 +795,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     }
     ++launches;
     if (ev) cudaEventRecord(ev[3], st);
-    if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<persistentGrid(), 128, 0, st>>>(sc, pool, c); ++launches; }
+    if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<persistentGrid() * tune().ctasPerSm / 8u, 128, 0, st>>>(sc, pool, c, tune().fetchShadow); ++launches; }
     if (ev) cudaEventRecord(ev[4], st);
     if (!rp.listPixel) {
         k_splatPlan<<<((uint32_t) rp.ring * rp.numTiles + 255u) / 256u, 256, 0, st>>>(sc, rp, c); ++launches;

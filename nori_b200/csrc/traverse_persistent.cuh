@@ -15,15 +15,16 @@
 
 namespace ng {
 
-constexpr int kFetchThreshold = 20;   // refill when fewer than this many lanes still traverse
+constexpr int kFetchThreshold = 20;   // default: refill when fewer than this many lanes still traverse
 
 template <bool ANY_HIT, class IO>
 NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
-                          unsigned int *workCounter, IO &io) {
+                          unsigned int *workCounter, IO &io, int fetchThreshold = kFetchThreshold) {
     const unsigned lane = threadIdx.x & 31u;
     unsigned ltMask; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(ltMask));
     int stack[kStackSize];
-    int sp = 0, cur = 0;
+    constexpr int kDone = 0x7fffffff;                          // no node left for this lane
+    int sp = 0, cur = kDone, leaf = 0;                         // leaf: postponed leaf link (< 0) or 0
     bool active = false;
     uint32_t rayIdx = 0xffffffffu, best = kNoHit;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
@@ -49,7 +50,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                         idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);
                         idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);
                         oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz;
-                        rayIdx = i; tbest = maxt; best = kNoHit; sp = 0; cur = 0; active = true;
+                        rayIdx = i; tbest = maxt; best = kNoHit; sp = 0; cur = 0; leaf = 0; active = true;
                     }
                 }
             }
@@ -59,33 +60,44 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
             continue;
         }
         // ---- traverse until too few lanes are left ------------------------------------------
+        // Speculative while-while: a lane that reaches a leaf postpones it (`leaf`) and keeps
+        // descending, so the node loop runs with (nearly) all lanes until every lane holds a leaf
+        // or has emptied its stack; only then are the postponed leaves intersected. The slab test
+        // of a speculating lane uses its not-yet-tightened tbest: conservative, never wrong.
         for (;;) {
-            while (active && cur >= 0) {                       // inner nodes
-                const float4 *n = nodes + 4 * (size_t) cur;
-                const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
-                const float lx0 = __fmaf_rn(n0.x, idx, -oodx), lx1 = __fmaf_rn(n0.y, idx, -oodx);
-                const float ly0 = __fmaf_rn(n0.z, idy, -oody), ly1 = __fmaf_rn(n0.w, idy, -oody);
-                const float lz0 = __fmaf_rn(n2.x, idz, -oodz), lz1 = __fmaf_rn(n2.y, idz, -oodz);
-                const float rx0 = __fmaf_rn(n1.x, idx, -oodx), rx1 = __fmaf_rn(n1.y, idx, -oodx);
-                const float ry0 = __fmaf_rn(n1.z, idy, -oody), ry1 = __fmaf_rn(n1.w, idy, -oody);
-                const float rz0 = __fmaf_rn(n2.z, idz, -oodz), rz1 = __fmaf_rn(n2.w, idz, -oodz);
-                const float lmin = fmaxf(fmaxf(fminf(lx0, lx1), fminf(ly0, ly1)), fmaxf(fminf(lz0, lz1), mint));
-                const float lmax = fminf(fminf(fmaxf(lx0, lx1), fmaxf(ly0, ly1)), fminf(fmaxf(lz0, lz1), tbest));
-                const float rmin = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), mint));
-                const float rmax = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), tbest));
-                const bool hl = lmin <= lmax, hr = rmin <= rmax;
-                int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
-                if (hl && hr) {
-                    if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
-                    stack[sp++] = cr;
-                    cur = cl;
-                } else if (hl) cur = cl;
-                else if (hr) cur = cr;
-                else if (sp > 0) cur = stack[--sp];
-                else active = false;                           // stack empty: the ray is done
+            for (;;) {                                         // inner nodes (warp-uniform loop)
+                if (cur >= 0 && cur != kDone) {
+                    const float4 *n = nodes + 4 * (size_t) cur;
+                    const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+                    const float lx0 = __fmaf_rn(n0.x, idx, -oodx), lx1 = __fmaf_rn(n0.y, idx, -oodx);
+                    const float ly0 = __fmaf_rn(n0.z, idy, -oody), ly1 = __fmaf_rn(n0.w, idy, -oody);
+                    const float lz0 = __fmaf_rn(n2.x, idz, -oodz), lz1 = __fmaf_rn(n2.y, idz, -oodz);
+                    const float rx0 = __fmaf_rn(n1.x, idx, -oodx), rx1 = __fmaf_rn(n1.y, idx, -oodx);
+                    const float ry0 = __fmaf_rn(n1.z, idy, -oody), ry1 = __fmaf_rn(n1.w, idy, -oody);
+                    const float rz0 = __fmaf_rn(n2.z, idz, -oodz), rz1 = __fmaf_rn(n2.w, idz, -oodz);
+                    const float lmin = fmaxf(fmaxf(fminf(lx0, lx1), fminf(ly0, ly1)), fmaxf(fminf(lz0, lz1), mint));
+                    const float lmax = fminf(fminf(fmaxf(lx0, lx1), fmaxf(ly0, ly1)), fminf(fmaxf(lz0, lz1), tbest));
+                    const float rmin = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), mint));
+                    const float rmax = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), tbest));
+                    const bool hl = lmin <= lmax, hr = rmin <= rmax;
+                    int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
+                    if (hl && hr) {
+                        if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
+                        stack[sp++] = cr;
+                        cur = cl;
+                    } else if (hl) cur = cl;
+                    else if (hr) cur = cr;
+                    else cur = sp > 0 ? stack[--sp] : kDone;
+                    if (cur < 0 && leaf == 0) {                // first leaf: postpone, keep descending
+                        leaf = cur;
+                        cur = sp > 0 ? stack[--sp] : kDone;
+                    }
+                }
+                const bool searching = leaf == 0 && cur >= 0 && cur != kDone;
+                if (!__any_sync(0xffffffffu, searching)) break;
             }
-            if (active) {                                      // leaf
-                const uint32_t code = ~(uint32_t) cur;
+            while (leaf < 0) {                                 // postponed leaves
+                const uint32_t code = ~(uint32_t) leaf;
                 const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
                 for (uint32_t k = 0; k < cnt; ++k) {
                     const float4 *tp = leafTris + 3 * (size_t) (first + k);
@@ -97,16 +109,16 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                         if (t < tbest || best == kNoHit || gid > best) { tbest = t; best = gid; bu = u; bv = v; }
                     }
                 }
-                if (ANY_HIT && best != kNoHit) active = false;
-                else if (sp > 0) cur = stack[--sp];
-                else active = false;
+                leaf = 0;
+                if (ANY_HIT && best != kNoHit) { cur = kDone; sp = 0; }
+                else if (cur < 0) { leaf = cur; cur = sp > 0 ? stack[--sp] : kDone; }   // a second leaf was reached meanwhile
             }
-            if (!active && rayIdx != 0xffffffffu) {
+            if (active && cur == kDone) {
+                active = false;
                 io.store(rayIdx, best, best == kNoHit ? 0.f : tbest, bu, bv);
-                rayIdx = 0xffffffffu;
             }
             const unsigned am = __ballot_sync(0xffffffffu, active);
-            if (!am || (!exhausted && __popc(am) < kFetchThreshold)) break;
+            if (!am || (!exhausted && __popc(am) < fetchThreshold)) break;
         }
     }
 }

@@ -229,11 +229,23 @@ inline void Accel::build(const Scene *s, int leafSize) {
     struct Job { uint32_t node, lo, hi; };
     std::vector<Job> todo; Job j0 = {0, 0, n}; todo.push_back(j0);
     const int NB = 16;
+    // Node boxes are stored grown by a scene-relative delta so that the slab test can never cull a
+    // triangle the Moeller-Trumbore test would report (its t may round an ulp outside the exact
+    // box): the BVH must return what the reference's brute-force loop returns.
+    float delta = 0.0f;
+    {
+        BBox all; for (uint32_t g = 0; g < n; ++g) all.expandBy(tb[g]);
+        V3 e = all.max - all.min;
+        float diag = std::sqrt(dot(e, e)), maxAbs = 0.0f;
+        for (int k = 0; k < 3; ++k) maxAbs = std::max(maxAbs, std::max(std::abs(all.min[k]), std::abs(all.max[k])));
+        delta = 4e-6f * std::max(diag, maxAbs);
+    }
     while (!todo.empty()) {
         Job j = todo.back(); todo.pop_back();
         BBox box, cbox;
         for (uint32_t i = j.lo; i < j.hi; ++i) { box.expandBy(tb[refs[i]]); cbox.expandBy(tc[refs[i]]); }
         nodes[j.node].box = box;
+        nodes[j.node].box.min = box.min - mk(delta, delta, delta); nodes[j.node].box.max = box.max + mk(delta, delta, delta);
         uint32_t cnt = j.hi - j.lo;
         bool leaf = cnt <= (uint32_t) leafSize;
         int bestAxis = -1, bestBin = -1; float bestCost = kInf;

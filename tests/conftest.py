@@ -84,3 +84,21 @@ def random_rays(scene, n, seed, port_scene=None):
     rays = np.empty((n, 8), np.float32)
     rays[:, 0:3] = o; rays[:, 3] = 1e-4; rays[:, 4:7] = d.astype(np.float32); rays[:, 7] = np.inf
     return rays
+
+
+def assert_hits_equal_reference(got, ps, rays, max_bvh_misses=5):
+    """got = (tri, mesh, tuv) from the GPU. Compared with the oracle's SAH BVH; wherever the two
+    differ the reference's brute-force loop (src/accel.cpp:42-55) is the judge: the GPU must equal
+    it bit for bit. (The oracle BVH uses exact boxes with the reference slab test and can, very
+    rarely, cull a triangle whose Moeller-Trumbore t lies an ulp outside its box; the device boxes
+    are inflated, so the GPU may be right where the oracle BVH is not.)"""
+    tri, mesh, tuv = got
+    rtri, rmesh, rtuv = ps.trace(rays, use_bvh=True)
+    bad = np.nonzero((tri != rtri) | (mesh != rmesh) | (tuv.view(np.uint32) != rtuv.view(np.uint32)).any(axis=1))[0]
+    assert bad.size <= max_bvh_misses, f"{bad.size} rays differ from the oracle BVH"
+    if bad.size:
+        btri, bmesh, btuv = ps.trace(rays[bad], use_bvh=False)
+        np.testing.assert_array_equal(tri[bad], btri)
+        np.testing.assert_array_equal(mesh[bad], bmesh)
+        np.testing.assert_array_equal(tuv[bad].view(np.uint32), btuv.view(np.uint32))
+    return bad.size
