@@ -3,14 +3,14 @@
 // ImageBlock::put) as a fixed pool of path slots advanced by one bounce per iteration:
 //
 //   k_prepare      (1 thread)  statistics, ring bookkeeping, sample issue limit
-//   k_finishRegen  (slot)      record finished camera samples; draw new ones in place
-//                              (Sampler stream + PerspectiveCamera::sampleRay)
-//   k_traceClosest (slot)      Accel::rayIntersect(ray, its, false); queue the slot by material
-//   k_shade        (queue)     one Li loop body per path: emitter, next-event estimation (queues a
-//                              shadow ray), BSDF sample, Russian roulette — material-sorted
+//   k_traceClosest (slot)      Accel::rayIntersect(ray, its, false) for every live path
+//   k_shadeRegen   (slot)      one Li loop body per path (emitter, next-event estimation -> shadow
+//                              queue, BSDF sample, Russian roulette), material-sorted per CTA; paths
+//                              that end write their sample record and their slot draws the next
+//                              camera sample in place (Sampler stream + PerspectiveCamera::sampleRay)
 //   k_traceShadow  (queue)     Accel::rayIntersect(ray, its, true); add unoccluded contributions
-//   k_splat        (tile)      ImageBlock::put for all samples of a finished 32x32 tile, accumulated
-//                              in shared memory, then added to the full-frame block
+//   k_splatPlan / k_splatPixel ImageBlock::put for all samples of a finished 32x32 tile, accumulated
+//                              in registers and shared memory, then added to the full-frame block
 //
 // Integrator semantics follow oracle/noracle_integrators.h statement for statement (the reference
 // ships no Integrator subclass: SURVEY.md F3), including the order in which a path consumes its
@@ -86,129 +86,6 @@ __device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Count
     }
 }
 
-__global__ void __launch_bounds__(256, 6) k_finishRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;      // capacity is a multiple of 256
-    uint4 meta = pool.meta[i];
-    const float4 rad = pool.rad[i];               // loaded up front (all lanes): one memory round trip, not two
-    const float2 oldPos = pool.pos[i];
-    const bool dead = !(meta.z & kFlagAlive);
-    const int W = sc.cam.width, H = sc.cam.height;
-
-    // ---- record a finished camera sample -------------------------------------------------
-    const bool fin = dead && (meta.z & kFlagHasSample);
-    bool late = false;
-    if (fin) {
-        V3 L = mk(rad.x, rad.y, rad.z);
-        if (meta.z & kFlagMulT) { float4 t = pool.thr[i]; L = mk(t.x, t.y, t.z) * L; }
-        const uint32_t slot = meta.z >> 24;
-        late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
-        if (late) {
-            splatDirect(sc, rp, c, oldPos, L);
-            atomicAdd(&c->lateSamples, 1u);
-        } else {
-            const size_t r = (size_t) slot * rp.passSlots + meta.w;
-            rp.recA[r] = make_float4(oldPos.x, oldPos.y, L.x, L.y);
-            rp.recB[r] = L.z;
-        }
-    }
-    if (!rp.listPixel) {
-        // one atomic per (ring slot, tile) present in the warp
-        uint32_t tile = 0xffffffffu;
-        if (fin && !late) {
-            uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
-            tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
-        }
-        unsigned peers = __match_any_sync(0xffffffffu, tile);
-        if (fin && !late && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
-    }
-    // one atomic per CTA for the finished-sample count and for the sample indices drawn below
-    __shared__ unsigned long long sBase;
-    __shared__ unsigned sWarp[8], sTotal;
-    const unsigned warp = threadIdx.x >> 5;
-    {
-        const int nfin = __syncthreads_count(fin);
-        if (threadIdx.x == 0 && nfin) atomicAdd(&c->finished, (unsigned long long) nfin);
-    }
-
-    // ---- draw the next camera sample into the free slot ------------------------------------
-    const unsigned long long limit = c->issueLimit;
-    const uint32_t passHint = c->passHint;
-    const bool want = dead && *(volatile unsigned long long *) &c->issue < limit;
-    bool need = want;
-    uint32_t x = 0, y = 0, sampleK = 0, rec = 0, slot = 0;
-    int lx = 0, ly = 0, ox = 0, oy = 0;
-    for (;;) {
-        const unsigned m = __ballot_sync(0xffffffffu, need);
-        if (laneId() == 0) sWarp[warp] = __popc(m);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned tot = 0;
-            for (int w = 0; w < 8; ++w) { unsigned n = sWarp[w]; sWarp[w] = tot; tot += n; }
-            sTotal = tot;
-            if (tot) sBase = atomicAdd(&c->issue, (unsigned long long) tot);
-        }
-        __syncthreads();
-        const unsigned tot = sTotal;
-        const unsigned long long base = sBase;
-        const unsigned off = sWarp[warp];
-        __syncthreads();
-        if (!tot || base >= limit) break;
-        if (need) {
-            unsigned long long g = base + off + __popc(m & lanemaskLt());
-            if (g < limit) {
-                if (rp.listPixel) {
-                    uint32_t p = rp.listPixel[g];
-                    x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g; slot = 0;
-                    need = false;
-                } else {
-                    // g lies in the hinted pass or just after it (a pass holds several pools): no 64-bit division
-                    uint32_t pass = passHint;
-                    unsigned long long j64 = g - (unsigned long long) pass * rp.passSlots;
-                    while (j64 >= rp.passSlots) { j64 -= rp.passSlots; ++pass; }
-                    const uint32_t j = (uint32_t) j64;
-                    uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
-                    uint32_t tile = j / (1024u * Kp), r = j - tile * (1024u * Kp);
-                    tilePixel(r & 1023u, lx, ly);
-                    uint32_t tyi = tile / (uint32_t) rp.tilesX, txi = tile - tyi * (uint32_t) rp.tilesX;
-                    ox = (int) txi * kTile; oy = (int) tyi * kTile;
-                    x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
-                    if (tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H) {
-                        sampleK = pass * rp.K + (r >> 10); rec = j; slot = pass % (uint32_t) rp.ring;
-                        need = false;
-                    }
-                }
-            }
-        }
-    }
-    if (!dead) return;
-    if (!want || need) {                          // nothing left to issue: the slot stays empty
-        if (meta.z != 0) { meta.z = 0; pool.meta[i] = meta; }
-        return;
-    }
-    Pcg32 rng;
-    const uint32_t sampleIndex = rp.sampleFirst + sampleK;
-    if (rp.streamMode == NORI_STREAM_PER_SAMPLE || rp.listPixel) {
-        rng.seed((uint64_t) y * (uint64_t) W + x, (uint64_t) sampleIndex);
-    } else {
-        // src/independent.cpp:48-53: seed(offset.x, offset.y); renderBlock (src/main.cpp:49-66)
-        // consumes 4 values per camera sample in (y, x, sample) order when Li draws none.
-        const int bw = min(W - ox, kTile);
-        rng.seed((uint64_t) (int64_t) ox, (uint64_t) (int64_t) oy);
-        rng.advance(4ll * (((long long) ly * bw + lx) * (long long) rp.sampleCount + sampleK));
-    }
-    V2 r2 = rng.next2D();
-    V2 ps; ps.x = (float) x + r2.x; ps.y = (float) y + r2.y;      // src/main.cpp:52
-    rng.next2D();                                                // apertureSample (main.cpp:53)
-    Ray ray = sampleRay(sc.cam, ps);
-    pool.rayO[i] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
-    pool.rayD[i] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
-    pool.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
-    pool.rad[i] = make_float4(0.f, 0.f, 0.f, 1.f);
-    pool.rng[i] = make_ulonglong2(rng.state, rng.inc);
-    pool.pos[i] = make_float2(ps.x, ps.y);
-    pool.meta[i] = make_uint4(y * (uint32_t) W + x, sampleIndex, kFlagAlive | kFlagDiscrete | (slot << 24), rec);
-}
-
 // ------------------------------------------------------------------------------------------
 struct ClosestIO {
     Pool pool;
@@ -224,7 +101,8 @@ struct ClosestIO {
 };
 
 /// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
-__global__ void __launch_bounds__(128, 8) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ClosestIO io; io.pool = pool;
     tracePersistent<false>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold);
 }
@@ -428,22 +306,66 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
     return true;
 }
 
-/// The shade stage. A CTA owns 256 consecutive path slots (their state is read and written fully
-/// coalesced) and sorts them by the BSDF of the surface hit in shared memory before shading, so
-/// that warps run one material's code; finished slots sort to the end. Shadow rays leave through
-/// a compacted queue (one atomic per CTA).
+constexpr uint32_t kShadowToRecord = 0x80000000u;          // shadow-queue target is a sample record, not a path slot
+struct ShadowIO {
+    Pool pool; float4 *recA; float *recB;
+    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        const float4 a = pool.shadow[3 * (size_t) i], b = pool.shadow[3 * (size_t) i + 1];
+        o = mk(a.x, a.y, a.z); d = mk(b.x, b.y, b.z); mint = kEpsilon; maxt = a.w;
+        return true;
+    }
+    /// Unoccluded: the light sample's contribution joins the path's radiance (one shadow ray per
+    /// path and iteration, so no two lanes touch the same slot) or, when the path ended at this
+    /// vertex and its slot was handed to a new camera sample, the sample record it left behind.
+    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float, float, float) const {
+        if (gid != kNoHit) return;
+        const float4 b = pool.shadow[3 * (size_t) i + 1], k = pool.shadow[3 * (size_t) i + 2];
+        const uint32_t target = __float_as_uint(b.w);
+        if (target & kShadowToRecord) {
+            const size_t r = target & ~kShadowToRecord;
+            float4 a = recA[r];
+            a.z = a.z + k.x; a.w = a.w + k.y;
+            recA[r] = a;
+            recB[r] = recB[r] + k.z;
+        } else {
+            float4 r = pool.rad[target];
+            r.x = r.x + k.x; r.y = r.y + k.y; r.z = r.z + k.z;
+            pool.rad[target] = r;
+        }
+    }
+};
+
+/// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool pool, float4 *recA, float *recB, Counters *c, int fetchThreshold) {
+    ShadowIO io; io.pool = pool; io.recA = recA; io.recB = recB;
+    tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
+}
+
+// ------------------------------------------------------------------------------------------
+/// Shade + record + regenerate in one pass over the pool (replaces k_finishRegen + k_shade).
+/// A CTA owns 256 consecutive path slots, sorts them in shared memory by what has to happen to
+/// them (BSDF of the surface hit / ray escaped / no live path) so that warps run one code path,
+/// shades the live ones, writes the sample record of every path that ended, and hands the freed
+/// slots to new camera samples (CTA-compacted: full warps, consecutive sample indices, one atomic
+/// per CTA). A path that ends at a vertex which still has a shadow ray in flight leaves its record
+/// behind and lets the shadow kernel add the light sample there (kShadowToRecord); only the cases
+/// the record cannot express (value = T * L, late samples) park the slot until the next iteration.
 template <int INTEGRATOR>
-__global__ void __launch_bounds__(256) k_shade(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+__global__ void __launch_bounds__(256) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
     constexpr int NK = kNumKeys + 1;                         // + "no live path in this slot"
-    __shared__ unsigned sCnt[8][NK], sOff[NK + 1], sWarpShadow[8], sShadowBase;
-    __shared__ unsigned short sPerm[256];
+    __shared__ unsigned sCnt[8][NK], sOff[NK + 1], sWarpShadow[8], sWarpRegen[8], sShadowBase, sRegenTotal;
+    __shared__ unsigned long long sIssueBase;
+    __shared__ unsigned short sPerm[256], sRegen[256];
     const unsigned tid = threadIdx.x, warp = tid >> 5;
     const uint32_t blockBase = blockIdx.x * blockDim.x;
-    // ---- CTA-local counting sort by material key -----------------------------------------
+    const int W = sc.cam.width, H = sc.cam.height;
+    // ---- CTA-local counting sort by what the slot needs -----------------------------------
     int key0 = kNumKeys;
-    if (pool.meta[blockBase + tid].z & kFlagAlive) {
+    {
+        const uint32_t flags0 = pool.meta[blockBase + tid].z;
         const uint32_t gid = __float_as_uint(pool.hit[blockBase + tid].w);
-        key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
+        if (flags0 & kFlagAlive) key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
     }
     unsigned rank = 0;
 #pragma unroll
@@ -469,68 +391,184 @@ __global__ void __launch_bounds__(256) k_shade(DeviceScene sc, Pool pool, Render
     const uint32_t slot = blockBase + sPerm[tid];
     const bool live = tid < sOff[kNumKeys];
 
+    // ---- shade the live paths; collect what ended -----------------------------------------
     ShadowOut sh; sh.cast = false;
+    uint32_t shadowTarget = slot;
+    bool fin = false, freeSlot = false, wasEmpty = false;
+    V3 finL = mk(0, 0, 0);
+    uint4 meta = pool.meta[slot];
     if (live) {
         const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
         const ulonglong2 rs = pool.rng[slot];
-        uint4 meta = pool.meta[slot];
         Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
         Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
         V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
         float bsdfPdf = th.w, eta = ra.w;
         uint32_t flags = meta.z;
-        bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
+        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
         if (cont) {
             pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
             pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
             pool.rng[slot] = make_ulonglong2(rng.state, rng.inc);
-        } else flags = (flags & ~kFlagAlive) | kFlagHasSample;
-        pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
-        pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
-        meta.z = flags;
-        pool.meta[slot] = meta;
+            pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
+            pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
+            meta.z = flags;
+            pool.meta[slot] = meta;
+        } else {
+            const bool mulT = flags & kFlagMulT;
+            const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
+            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+            if (!sh.cast) { fin = true; freeSlot = true; finL = mulT ? T * L : L; }
+            else if (!mulT && !late && r < (size_t) kShadowToRecord) {
+                fin = true; freeSlot = true; finL = L;
+                shadowTarget = kShadowToRecord | (uint32_t) r;
+            } else {                                          // park: finished by the next iteration's pass
+                pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
+                pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
+                meta.z = (flags & ~kFlagAlive) | kFlagHasSample;
+                pool.meta[slot] = meta;
+            }
+        }
+    } else {
+        freeSlot = true;
+        if (meta.z & kFlagHasSample) {
+            const float4 ra = pool.rad[slot];
+            finL = mk(ra.x, ra.y, ra.z);
+            if (meta.z & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
+            fin = true;
+        } else wasEmpty = meta.z == 0;
     }
-    // ---- shadow-ray queue (compacted) ------------------------------------------------------
-    const unsigned sm = __ballot_sync(0xffffffffu, sh.cast);
-    if (laneId() == 0) sWarpShadow[warp] = __popc(sm);
-    __syncthreads();
+    // ---- record the camera samples that ended (src/main.cpp:59-62 -> block.put) ---------------
+    bool counted = false;
+    if (fin) {
+        const float2 ps = pool.pos[slot];
+        const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
+        if (late) {
+            splatDirect(sc, rp, c, ps, finL);
+            atomicAdd(&c->lateSamples, 1u);
+        } else {
+            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+            rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
+            rp.recB[r] = finL.z;
+            counted = !rp.listPixel;
+        }
+    }
+    {   // one atomic per (ring slot, tile) present in the warp
+        uint32_t tile = 0xffffffffu;
+        if (counted) {
+            const uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
+            tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
+        }
+        if (__any_sync(0xffffffffu, counted)) {
+            const unsigned peers = __match_any_sync(0xffffffffu, tile);
+            if (counted && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
+        }
+    }
+    // ---- compaction: shadow queue entries and free slots (one atomic each per CTA) ------------
+    const unsigned mShadow = __ballot_sync(0xffffffffu, sh.cast), mFree = __ballot_sync(0xffffffffu, freeSlot);
+    if (laneId() == 0) { sWarpShadow[warp] = __popc(mShadow); sWarpRegen[warp] = __popc(mFree); }
+    const int nfin = __syncthreads_count(fin);
     if (tid == 0) {
-        unsigned acc = 0;
-        for (int w = 0; w < 8; ++w) { unsigned n = sWarpShadow[w]; sWarpShadow[w] = acc; acc += n; }
-        sShadowBase = acc ? atomicAdd(&c->shadowCount, acc) : 0u;
+        unsigned accS = 0, accR = 0;
+        for (int w = 0; w < 8; ++w) {
+            unsigned n = sWarpShadow[w]; sWarpShadow[w] = accS; accS += n;
+            n = sWarpRegen[w]; sWarpRegen[w] = accR; accR += n;
+        }
+        sShadowBase = accS ? atomicAdd(&c->shadowCount, accS) : 0u;
+        sRegenTotal = accR;
+        if (nfin) atomicAdd(&c->finished, (unsigned long long) nfin);
     }
     __syncthreads();
     if (sh.cast) {
-        float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(sm & lanemaskLt()));
+        float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()));
         e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
-        e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
+        e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(shadowTarget));
         e[2] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, 0.f);
     }
-}
+    if (freeSlot) sRegen[sWarpRegen[warp] + __popc(mFree & lanemaskLt())] = (unsigned short) (sPerm[tid] | (wasEmpty ? 0x8000u : 0u));
+    const unsigned nFree = sRegenTotal;
+    __syncthreads();
+    if (nFree == 0) return;
 
-struct ShadowIO {
-    Pool pool;
-    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
-        const float4 a = pool.shadow[3 * (size_t) i], b = pool.shadow[3 * (size_t) i + 1];
-        o = mk(a.x, a.y, a.z); d = mk(b.x, b.y, b.z); mint = kEpsilon; maxt = a.w;
-        return true;
+    // ---- draw the next camera samples into the free slots (threads 0 .. nFree-1) -------------
+    const unsigned long long limit = c->issueLimit;
+    const uint32_t passHint = c->passHint;
+    const bool mine = tid < nFree;
+    bool need = mine && *(volatile unsigned long long *) &c->issue < limit;
+    const bool want = need;
+    uint32_t x = 0, y = 0, sampleK = 0, rec = 0, ring = 0;
+    int lx = 0, ly = 0, ox = 0, oy = 0;
+    for (;;) {
+        const unsigned m = __ballot_sync(0xffffffffu, need);
+        if (laneId() == 0) sWarpRegen[warp] = __popc(m);
+        __syncthreads();
+        if (tid == 0) {
+            unsigned tot = 0;
+            for (int w = 0; w < 8; ++w) { unsigned n = sWarpRegen[w]; sWarpRegen[w] = tot; tot += n; }
+            sRegenTotal = tot;
+            if (tot) sIssueBase = atomicAdd(&c->issue, (unsigned long long) tot);
+        }
+        __syncthreads();
+        const unsigned tot = sRegenTotal;
+        const unsigned long long base = sIssueBase;
+        if (!tot || base >= limit) break;
+        if (need) {
+            const unsigned long long g = base + sWarpRegen[warp] + __popc(m & lanemaskLt());
+            if (g < limit) {
+                if (rp.listPixel) {
+                    const uint32_t p = rp.listPixel[g];
+                    x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g; ring = 0;
+                    need = false;
+                } else {
+                    // g lies in the hinted pass or just after it (a pass holds several pools): no 64-bit division
+                    uint32_t pass = passHint;
+                    unsigned long long j64 = g - (unsigned long long) pass * rp.passSlots;
+                    while (j64 >= rp.passSlots) { j64 -= rp.passSlots; ++pass; }
+                    const uint32_t j = (uint32_t) j64;
+                    const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
+                    const uint32_t tile = j / (1024u * Kp), r = j - tile * (1024u * Kp);
+                    tilePixel(r & 1023u, lx, ly);
+                    const uint32_t tyi = tile / (uint32_t) rp.tilesX, txi = tile - tyi * (uint32_t) rp.tilesX;
+                    ox = (int) txi * kTile; oy = (int) tyi * kTile;
+                    x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
+                    if (tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H) {
+                        sampleK = pass * rp.K + (r >> 10); rec = j; ring = pass % (uint32_t) rp.ring;
+                        need = false;
+                    }
+                }
+            }
+        }
+        if (!__syncthreads_or(need)) break;
     }
-    /// Unoccluded: the light sample's contribution joins the path's radiance (one shadow ray per
-    /// path and iteration, so no two lanes touch the same slot).
-    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float, float, float) const {
-        if (gid != kNoHit) return;
-        const float4 b = pool.shadow[3 * (size_t) i + 1], k = pool.shadow[3 * (size_t) i + 2];
-        const uint32_t slot = __float_as_uint(b.w);
-        float4 r = pool.rad[slot];
-        r.x = r.x + k.x; r.y = r.y + k.y; r.z = r.z + k.z;
-        pool.rad[slot] = r;
+    if (!mine) return;
+    const unsigned short entry = sRegen[tid];
+    const uint32_t dst = blockBase + (entry & 0x7fffu);
+    if (!want || need) {                          // nothing left to issue: the slot stays empty
+        if (!(entry & 0x8000u)) pool.meta[dst] = make_uint4(0, 0, 0, 0);
+        return;
     }
-};
-
-/// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
-__global__ void __launch_bounds__(128, 8) k_traceShadow(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
-    ShadowIO io; io.pool = pool;
-    tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
+    Pcg32 rng;
+    const uint32_t sampleIndex = rp.sampleFirst + sampleK;
+    if (rp.streamMode == NORI_STREAM_PER_SAMPLE || rp.listPixel) {
+        rng.seed((uint64_t) y * (uint64_t) W + x, (uint64_t) sampleIndex);
+    } else {
+        // src/independent.cpp:48-53: seed(offset.x, offset.y); renderBlock (src/main.cpp:49-66)
+        // consumes 4 values per camera sample in (y, x, sample) order when Li draws none.
+        const int bw = min(W - ox, kTile);
+        rng.seed((uint64_t) (int64_t) ox, (uint64_t) (int64_t) oy);
+        rng.advance(4ll * (((long long) ly * bw + lx) * (long long) rp.sampleCount + sampleK));
+    }
+    const V2 r2 = rng.next2D();
+    V2 ps; ps.x = (float) x + r2.x; ps.y = (float) y + r2.y;      // src/main.cpp:52
+    rng.next2D();                                                // apertureSample (main.cpp:53)
+    const Ray ray = sampleRay(sc.cam, ps);
+    pool.rayO[dst] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
+    pool.rayD[dst] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
+    pool.thr[dst] = make_float4(1.f, 1.f, 1.f, 0.f);
+    pool.rad[dst] = make_float4(0.f, 0.f, 0.f, 1.f);
+    pool.rng[dst] = make_ulonglong2(rng.state, rng.inc);
+    pool.pos[dst] = make_float2(ps.x, ps.y);
+    pool.meta[dst] = make_uint4(y * (uint32_t) W + x, sampleIndex, kFlagAlive | kFlagDiscrete | (ring << 24), rec);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -745,7 +783,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 
 // ------------------------------------------------------------------------------------------
 template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
-    k_shade<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
+    k_shadeRegen<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
 
 __global__ void k_poolInit(Pool pool, Counters *c) {
@@ -768,6 +806,7 @@ static const Tune &tune() {
         Tune v = {kFetchThreshold, kFetchThreshold, 8u};
         if (const char *s = getenv("NORI_GPU_FETCH")) v.fetchClosest = v.fetchShadow = atoi(s);
         if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = atoi(s);
+        if (const char *s = getenv("NORI_GPU_NODE_EXIT")) { v.fetchClosest |= atoi(s) << 8; v.fetchShadow |= atoi(s) << 8; }
         if (const char *s = getenv("NORI_GPU_TRACE_CTAS")) v.ctasPerSm = (unsigned) atoi(s);
         return v;
     }();
@@ -775,13 +814,17 @@ static const Tune &tune() {
 }
 
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st, cudaEvent_t *ev) {
-    const uint32_t grid = pool.capacity / 256;
     int launches = 0;
     if (ev) cudaEventRecord(ev[0], st);
     k_prepare<<<1, 1, 0, st>>>(c, rp); ++launches;
-    k_finishRegen<<<grid, 256, 0, st>>>(sc, pool, rp, c); ++launches;
     if (ev) cudaEventRecord(ev[1], st);
-    k_traceClosest<<<persistentGrid() * tune().ctasPerSm / 8u, 128, 0, st>>>(sc, pool, c, tune().fetchClosest); ++launches;
+    {
+        const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        if (b == 10) k_traceClosest<10><<<g, 128, 0, st>>>(sc, pool, c, tune().fetchClosest);
+        else if (b == 12) k_traceClosest<12><<<g, 128, 0, st>>>(sc, pool, c, tune().fetchClosest);
+        else k_traceClosest<8><<<g, 128, 0, st>>>(sc, pool, c, tune().fetchClosest);
+        ++launches;
+    }
     if (ev) cudaEventRecord(ev[2], st);
     switch (rp.integrator) {
     case NORI_INT_NORMALS: launchShade<NORI_INT_NORMALS>(sc, pool, rp, c, st); break;
@@ -795,7 +838,13 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     }
     ++launches;
     if (ev) cudaEventRecord(ev[3], st);
-    if (rp.integrator != NORI_INT_NORMALS) { k_traceShadow<<<persistentGrid() * tune().ctasPerSm / 8u, 128, 0, st>>>(sc, pool, c, tune().fetchShadow); ++launches; }
+    if (rp.integrator != NORI_INT_NORMALS) {
+        const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
+        else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
+        else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
+        ++launches;
+    }
     if (ev) cudaEventRecord(ev[4], st);
     if (!rp.listPixel) {
         k_splatPlan<<<((uint32_t) rp.ring * rp.numTiles + 255u) / 256u, 256, 0, st>>>(sc, rp, c); ++launches;

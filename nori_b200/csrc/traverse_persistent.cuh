@@ -19,7 +19,9 @@ constexpr int kFetchThreshold = 20;   // default: refill when fewer than this ma
 
 template <bool ANY_HIT, class IO>
 NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
-                          unsigned int *workCounter, IO &io, int fetchThreshold = kFetchThreshold) {
+                          unsigned int *workCounter, IO &io, int tuning = kFetchThreshold) {
+    const int fetchThreshold = tuning & 0xff;                  // refill when fewer lanes than this still hold a ray
+    const int nodeExit = (tuning >> 8) & 0xff;                 // leave the node loop when fewer lanes than this still descend
     const unsigned lane = threadIdx.x & 31u;
     unsigned ltMask; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(ltMask));
     int stack[kStackSize];
@@ -94,7 +96,8 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                     }
                 }
                 const bool searching = leaf == 0 && cur >= 0 && cur != kDone;
-                if (!__any_sync(0xffffffffu, searching)) break;
+                const unsigned sm = __ballot_sync(0xffffffffu, searching);
+                if (__popc(sm) <= nodeExit) break;
             }
             while (leaf < 0) {                                 // postponed leaves
                 const uint32_t code = ~(uint32_t) leaf;
@@ -124,3 +127,4 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
 }
 
 } // namespace ng
+
