@@ -342,209 +342,38 @@ __global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool 
     tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
 }
 
-// ------------------------------------------------------------------------------------------
-/// Shade + record + regenerate in one pass over the pool (replaces k_finishRegen + k_shade).
-/// A CTA owns 256 consecutive path slots, sorts them in shared memory by what has to happen to
-/// them (BSDF of the surface hit / ray escaped / no live path) so that warps run one code path,
-/// shades the live ones, writes the sample record of every path that ended, and hands the freed
-/// slots to new camera samples (CTA-compacted: full warps, consecutive sample indices, one atomic
-/// per CTA). A path that ends at a vertex which still has a shadow ray in flight leaves its record
-/// behind and lets the shadow kernel add the light sample there (kShadowToRecord); only the cases
-/// the record cannot express (value = T * L, late samples) park the slot until the next iteration.
-template <int INTEGRATOR>
-__global__ void __launch_bounds__(256) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
-    constexpr int NK = kNumKeys + 1;                         // + "no live path in this slot"
-    __shared__ unsigned sCnt[8][NK], sOff[NK + 1], sWarpShadow[8], sWarpRegen[8], sShadowBase, sRegenTotal;
-    __shared__ unsigned long long sIssueBase;
-    __shared__ unsigned short sPerm[256], sRegen[256];
-    const unsigned tid = threadIdx.x, warp = tid >> 5;
-    const uint32_t blockBase = blockIdx.x * blockDim.x;
+/// Hands path slot `dst` to camera sample index g of the issue order (pass, tile, sample, pixel):
+/// Sampler stream + PerspectiveCamera::sampleRay (src/main.cpp:49-56). Indices past `limit` or in
+/// the padding of a border tile leave the slot empty; it draws again next iteration.
+__device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, uint32_t dst,
+                                          unsigned long long g, unsigned long long limit, uint32_t passHint, bool wasEmpty) {
     const int W = sc.cam.width, H = sc.cam.height;
-    // ---- CTA-local counting sort by what the slot needs -----------------------------------
-    int key0 = kNumKeys;
-    {
-        const uint32_t flags0 = pool.meta[blockBase + tid].z;
-        const uint32_t gid = __float_as_uint(pool.hit[blockBase + tid].w);
-        if (flags0 & kFlagAlive) key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
-    }
-    unsigned rank = 0;
-#pragma unroll
-    for (int k = 0; k < NK; ++k) {
-        const unsigned m = __ballot_sync(0xffffffffu, key0 == k);
-        if (key0 == k) rank = __popc(m & lanemaskLt());
-        if (laneId() == 0) sCnt[warp][k] = __popc(m);
-    }
-    __syncthreads();
-    if (tid == 0) {
-        unsigned acc = 0;
-        for (int k = 0; k < NK; ++k) {
-            sOff[k] = acc;
-            for (int w = 0; w < 8; ++w) { unsigned n = sCnt[w][k]; sCnt[w][k] = acc; acc += n; }
-        }
-        sOff[NK] = acc;
-        const unsigned alive = sOff[kNumKeys];
-        if (alive) atomicAdd(&c->sortCount[0], alive);       // closest rays traced = live slots
-    }
-    __syncthreads();
-    sPerm[sCnt[warp][key0] + rank] = (unsigned short) tid;
-    __syncthreads();
-    const uint32_t slot = blockBase + sPerm[tid];
-    const bool live = tid < sOff[kNumKeys];
-
-    // ---- shade the live paths; collect what ended -----------------------------------------
-    ShadowOut sh; sh.cast = false;
-    uint32_t shadowTarget = slot;
-    bool fin = false, freeSlot = false, wasEmpty = false;
-    V3 finL = mk(0, 0, 0);
-    uint4 meta = pool.meta[slot];
-    if (live) {
-        const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
-        const ulonglong2 rs = pool.rng[slot];
-        Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
-        Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
-        V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
-        float bsdfPdf = th.w, eta = ra.w;
-        uint32_t flags = meta.z;
-        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
-        if (cont) {
-            pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
-            pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
-            pool.rng[slot] = make_ulonglong2(rng.state, rng.inc);
-            pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
-            pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
-            meta.z = flags;
-            pool.meta[slot] = meta;
-        } else {
-            const bool mulT = flags & kFlagMulT;
-            const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
-            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
-            if (!sh.cast) { fin = true; freeSlot = true; finL = mulT ? T * L : L; }
-            else if (!mulT && !late && r < (size_t) kShadowToRecord) {
-                fin = true; freeSlot = true; finL = L;
-                shadowTarget = kShadowToRecord | (uint32_t) r;
-            } else {                                          // park: finished by the next iteration's pass
-                pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
-                pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
-                meta.z = (flags & ~kFlagAlive) | kFlagHasSample;
-                pool.meta[slot] = meta;
-            }
-        }
-    } else {
-        freeSlot = true;
-        if (meta.z & kFlagHasSample) {
-            const float4 ra = pool.rad[slot];
-            finL = mk(ra.x, ra.y, ra.z);
-            if (meta.z & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
-            fin = true;
-        } else wasEmpty = meta.z == 0;
-    }
-    // ---- record the camera samples that ended (src/main.cpp:59-62 -> block.put) ---------------
-    bool counted = false;
-    if (fin) {
-        const float2 ps = pool.pos[slot];
-        const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < c->completedPasses;
-        if (late) {
-            splatDirect(sc, rp, c, ps, finL);
-            atomicAdd(&c->lateSamples, 1u);
-        } else {
-            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
-            rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
-            rp.recB[r] = finL.z;
-            counted = !rp.listPixel;
-        }
-    }
-    {   // one atomic per (ring slot, tile) present in the warp
-        uint32_t tile = 0xffffffffu;
-        if (counted) {
-            const uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
-            tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
-        }
-        if (__any_sync(0xffffffffu, counted)) {
-            const unsigned peers = __match_any_sync(0xffffffffu, tile);
-            if (counted && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
-        }
-    }
-    // ---- compaction: shadow queue entries and free slots (one atomic each per CTA) ------------
-    const unsigned mShadow = __ballot_sync(0xffffffffu, sh.cast), mFree = __ballot_sync(0xffffffffu, freeSlot);
-    if (laneId() == 0) { sWarpShadow[warp] = __popc(mShadow); sWarpRegen[warp] = __popc(mFree); }
-    const int nfin = __syncthreads_count(fin);
-    if (tid == 0) {
-        unsigned accS = 0, accR = 0;
-        for (int w = 0; w < 8; ++w) {
-            unsigned n = sWarpShadow[w]; sWarpShadow[w] = accS; accS += n;
-            n = sWarpRegen[w]; sWarpRegen[w] = accR; accR += n;
-        }
-        sShadowBase = accS ? atomicAdd(&c->shadowCount, accS) : 0u;
-        sRegenTotal = accR;
-        if (nfin) atomicAdd(&c->finished, (unsigned long long) nfin);
-    }
-    __syncthreads();
-    if (sh.cast) {
-        float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()));
-        e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
-        e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(shadowTarget));
-        e[2] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, 0.f);
-    }
-    if (freeSlot) sRegen[sWarpRegen[warp] + __popc(mFree & lanemaskLt())] = (unsigned short) (sPerm[tid] | (wasEmpty ? 0x8000u : 0u));
-    const unsigned nFree = sRegenTotal;
-    __syncthreads();
-    if (nFree == 0) return;
-
-    // ---- draw the next camera samples into the free slots (threads 0 .. nFree-1) -------------
-    const unsigned long long limit = c->issueLimit;
-    const uint32_t passHint = c->passHint;
-    const bool mine = tid < nFree;
-    bool need = mine && *(volatile unsigned long long *) &c->issue < limit;
-    const bool want = need;
     uint32_t x = 0, y = 0, sampleK = 0, rec = 0, ring = 0;
     int lx = 0, ly = 0, ox = 0, oy = 0;
-    for (;;) {
-        const unsigned m = __ballot_sync(0xffffffffu, need);
-        if (laneId() == 0) sWarpRegen[warp] = __popc(m);
-        __syncthreads();
-        if (tid == 0) {
-            unsigned tot = 0;
-            for (int w = 0; w < 8; ++w) { unsigned n = sWarpRegen[w]; sWarpRegen[w] = tot; tot += n; }
-            sRegenTotal = tot;
-            if (tot) sIssueBase = atomicAdd(&c->issue, (unsigned long long) tot);
+    bool ok = false;
+    if (g < limit) {
+        if (rp.listPixel) {
+            const uint32_t p = rp.listPixel[g];
+            x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g;
+            ok = true;
+        } else {
+            // g lies in the hinted pass or just after it (a pass holds several pools): no 64-bit division
+            uint32_t pass = passHint;
+            unsigned long long j64 = g - (unsigned long long) pass * rp.passSlots;
+            while (j64 >= rp.passSlots) { j64 -= rp.passSlots; ++pass; }
+            const uint32_t j = (uint32_t) j64;
+            const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
+            const uint32_t tile = j / (1024u * Kp), r = j - tile * (1024u * Kp);
+            tilePixel(r & 1023u, lx, ly);
+            const uint32_t tyi = tile / (uint32_t) rp.tilesX, txi = tile - tyi * (uint32_t) rp.tilesX;
+            ox = (int) txi * kTile; oy = (int) tyi * kTile;
+            x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
+            sampleK = pass * rp.K + (r >> 10); rec = j; ring = pass % (uint32_t) rp.ring;
+            ok = tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H;
         }
-        __syncthreads();
-        const unsigned tot = sRegenTotal;
-        const unsigned long long base = sIssueBase;
-        if (!tot || base >= limit) break;
-        if (need) {
-            const unsigned long long g = base + sWarpRegen[warp] + __popc(m & lanemaskLt());
-            if (g < limit) {
-                if (rp.listPixel) {
-                    const uint32_t p = rp.listPixel[g];
-                    x = p % (uint32_t) W; y = p / (uint32_t) W; sampleK = rp.listSample[g]; rec = (uint32_t) g; ring = 0;
-                    need = false;
-                } else {
-                    // g lies in the hinted pass or just after it (a pass holds several pools): no 64-bit division
-                    uint32_t pass = passHint;
-                    unsigned long long j64 = g - (unsigned long long) pass * rp.passSlots;
-                    while (j64 >= rp.passSlots) { j64 -= rp.passSlots; ++pass; }
-                    const uint32_t j = (uint32_t) j64;
-                    const uint32_t Kp = pass == rp.numPasses - 1 ? rp.Klast : rp.K;
-                    const uint32_t tile = j / (1024u * Kp), r = j - tile * (1024u * Kp);
-                    tilePixel(r & 1023u, lx, ly);
-                    const uint32_t tyi = tile / (uint32_t) rp.tilesX, txi = tile - tyi * (uint32_t) rp.tilesX;
-                    ox = (int) txi * kTile; oy = (int) tyi * kTile;
-                    x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
-                    if (tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H) {
-                        sampleK = pass * rp.K + (r >> 10); rec = j; ring = pass % (uint32_t) rp.ring;
-                        need = false;
-                    }
-                }
-            }
-        }
-        if (!__syncthreads_or(need)) break;
     }
-    if (!mine) return;
-    const unsigned short entry = sRegen[tid];
-    const uint32_t dst = blockBase + (entry & 0x7fffu);
-    if (!want || need) {                          // nothing left to issue: the slot stays empty
-        if (!(entry & 0x8000u)) pool.meta[dst] = make_uint4(0, 0, 0, 0);
+    if (!ok) {
+        if (!wasEmpty) pool.meta[dst] = make_uint4(0, 0, 0, 0);
         return;
     }
     Pcg32 rng;
@@ -569,6 +398,157 @@ __global__ void __launch_bounds__(256) k_shadeRegen(DeviceScene sc, Pool pool, R
     pool.rng[dst] = make_ulonglong2(rng.state, rng.inc);
     pool.pos[dst] = make_float2(ps.x, ps.y);
     pool.meta[dst] = make_uint4(y * (uint32_t) W + x, sampleIndex, kFlagAlive | kFlagDiscrete | (ring << 24), rec);
+}
+
+// ------------------------------------------------------------------------------------------
+/// Shade + record + regenerate in one pass over the pool. A CTA owns 256 consecutive path slots
+/// and sorts them in shared memory by what has to happen to them: BSDF of the surface hit (keys
+/// 0-3), ray escaped (4), no live path (5), so that warps run one code path.
+///   * Slots of keys 4 and 5 are free as soon as their sample is recorded: their warps draw new
+///     camera samples (consecutive indices, full warps) while the other warps still shade.
+///   * Slots whose path ends at a surface are recorded and regenerated in place after the shade
+///     step. If the last vertex still has a shadow ray in flight, the record is left behind and
+///     the shadow kernel adds the light sample there (kShadowToRecord); only what the record
+///     cannot express (value = T * L, late samples) parks the slot until the next iteration.
+/// One atomic per CTA each for: sample indices (twice), shadow queue space, finished count.
+template <int INTEGRATOR>
+__global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+    constexpr int NK = kNumKeys + 1;
+    __shared__ unsigned sCnt[8][NK], sOff[NK + 1], sWarpShadow[8], sWarpRegen[8], sShadowBase;
+    __shared__ unsigned long long sIssueA, sIssueB;
+    __shared__ unsigned short sPerm[256];
+    const unsigned tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t blockBase = blockIdx.x * blockDim.x;
+    const int W = sc.cam.width;
+    const unsigned long long limit = c->issueLimit;
+    const uint32_t passHint = c->passHint, completedPasses = c->completedPasses;
+    // ---- CTA-local counting sort by what the slot needs -----------------------------------
+    int key0 = kNumKeys;
+    {
+        const uint32_t flags0 = pool.meta[blockBase + tid].z;
+        const uint32_t gid = __float_as_uint(pool.hit[blockBase + tid].w);
+        if (flags0 & kFlagAlive) key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
+    }
+    unsigned rank = 0;
+#pragma unroll
+    for (int k = 0; k < NK; ++k) {
+        const unsigned m = __ballot_sync(0xffffffffu, key0 == k);
+        if (key0 == k) rank = __popc(m & lanemaskLt());
+        if (laneId() == 0) sCnt[warp][k] = __popc(m);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned acc = 0;
+        for (int k = 0; k < NK; ++k) {
+            sOff[k] = acc;
+            for (int w = 0; w < 8; ++w) { unsigned n = sCnt[w][k]; sCnt[w][k] = acc; acc += n; }
+        }
+        sOff[NK] = acc;
+        const unsigned alive = sOff[kNumKeys];
+        if (alive) atomicAdd(&c->sortCount[0], alive);       // closest rays traced = live slots
+        const unsigned nA = 256u - sOff[kKeyMiss];
+        sIssueA = (nA && *(volatile unsigned long long *) &c->issue < limit) ? atomicAdd(&c->issue, (unsigned long long) nA) : ~0ull;
+    }
+    __syncthreads();
+    sPerm[sCnt[warp][key0] + rank] = (unsigned short) tid;
+    __syncthreads();
+    const uint32_t slot = blockBase + sPerm[tid];
+    const unsigned aBegin = sOff[kKeyMiss];
+
+    ShadowOut sh; sh.cast = false;
+    uint32_t shadowTarget = slot;
+    bool fin = false, needB = false;
+    V3 finL = mk(0, 0, 0);
+    uint4 meta = pool.meta[slot];
+    if (tid < aBegin) {
+        // ---- a surface was hit: one Li loop body ----------------------------------------------
+        const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
+        const ulonglong2 rs = pool.rng[slot];
+        Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
+        Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
+        V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
+        float bsdfPdf = th.w, eta = ra.w;
+        uint32_t flags = meta.z;
+        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
+        if (cont) {
+            pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
+            pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
+            pool.rng[slot] = make_ulonglong2(rng.state, rng.inc);
+            pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
+            pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
+            meta.z = flags;
+            pool.meta[slot] = meta;
+        } else {
+            const bool mulT = flags & kFlagMulT;
+            const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < completedPasses;
+            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+            if (!sh.cast) { fin = true; needB = true; finL = mulT ? T * L : L; }
+            else if (!mulT && !late && r < (size_t) kShadowToRecord) {
+                fin = true; needB = true; finL = L;
+                shadowTarget = kShadowToRecord | (uint32_t) r;
+            } else {                                          // park: recorded by the next iteration's pass
+                pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
+                pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
+                meta.z = (flags & ~kFlagAlive) | kFlagHasSample;
+                pool.meta[slot] = meta;
+            }
+        }
+    } else if (meta.z & (kFlagAlive | kFlagHasSample)) {
+        // ---- ray escaped (Li returns what the path gathered) or a parked sample -----------------
+        const float4 ra = pool.rad[slot];
+        finL = mk(ra.x, ra.y, ra.z);
+        if (meta.z & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
+        fin = true;
+    }
+    // ---- record the camera samples that ended (src/main.cpp:59-62 -> block.put) ---------------
+    bool counted = false;
+    if (fin) {
+        const float2 ps = pool.pos[slot];
+        const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < completedPasses;
+        if (late) {
+            splatDirect(sc, rp, c, ps, finL);
+            atomicAdd(&c->lateSamples, 1u);
+        } else {
+            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+            rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
+            rp.recB[r] = finL.z;
+            counted = !rp.listPixel;
+        }
+    }
+    if (__any_sync(0xffffffffu, counted)) {       // one atomic per (ring slot, tile) present in the warp
+        uint32_t tile = 0xffffffffu;
+        if (counted) {
+            const uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
+            tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
+        }
+        const unsigned peers = __match_any_sync(0xffffffffu, tile);
+        if (counted && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
+    }
+    // ---- free slots known up front draw their next sample while other warps still shade ------
+    if (tid >= aBegin) regenSlot(sc, pool, rp, slot, sIssueA == ~0ull ? ~0ull : sIssueA + (tid - aBegin), limit, passHint, meta.z == 0);
+
+    // ---- compaction: shadow queue entries, slots freed by the shade step ----------------------
+    const unsigned mShadow = __ballot_sync(0xffffffffu, sh.cast), mB = __ballot_sync(0xffffffffu, needB);
+    if (laneId() == 0) { sWarpShadow[warp] = __popc(mShadow); sWarpRegen[warp] = __popc(mB); }
+    const int nfin = __syncthreads_count(fin);
+    if (tid == 0) {
+        unsigned accS = 0, accR = 0;
+        for (int w = 0; w < 8; ++w) {
+            unsigned n = sWarpShadow[w]; sWarpShadow[w] = accS; accS += n;
+            n = sWarpRegen[w]; sWarpRegen[w] = accR; accR += n;
+        }
+        sShadowBase = accS ? atomicAdd(&c->shadowCount, accS) : 0u;
+        sIssueB = (accR && *(volatile unsigned long long *) &c->issue < limit) ? atomicAdd(&c->issue, (unsigned long long) accR) : ~0ull;
+        if (nfin) atomicAdd(&c->finished, (unsigned long long) nfin);
+    }
+    __syncthreads();
+    if (sh.cast) {
+        float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()));
+        e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
+        e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(shadowTarget));
+        e[2] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, 0.f);
+    }
+    if (needB) regenSlot(sc, pool, rp, slot, sIssueB == ~0ull ? ~0ull : sIssueB + sWarpRegen[warp] + __popc(mB & lanemaskLt()), limit, passHint, false);
 }
 
 // ------------------------------------------------------------------------------------------
