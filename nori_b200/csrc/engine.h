@@ -27,7 +27,7 @@ struct Pool {
     float4 *thr;         // throughput rgb, BSDF pdf of the last sampled direction
     float4 *rad;         // radiance rgb, eta product
     ulonglong2 *rng;     // pcg32 state, inc
-    uint4 *meta;         // pixel index, sample index, flags | depth | ring slot << 24, record index
+    uint4 *meta;         // ring slot * numTiles + tile, sample index, flags | depth | ring slot << 24, record index
     float2 *pos;         // pixelSample handed to ImageBlock::put
     float4 *shadow;      // 3 x capacity: (o, maxt) (d, bits(slot)) (contribution, -)
 };

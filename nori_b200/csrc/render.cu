@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool 
 __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, uint32_t dst,
                                           unsigned long long g, unsigned long long limit, uint32_t passHint, bool wasEmpty) {
     const int W = sc.cam.width, H = sc.cam.height;
-    uint32_t x = 0, y = 0, sampleK = 0, rec = 0, ring = 0;
+    uint32_t x = 0, y = 0, sampleK = 0, rec = 0, ring = 0, tileSlot = 0;
     int lx = 0, ly = 0, ox = 0, oy = 0;
     bool ok = false;
     if (g < limit) {
@@ -369,6 +369,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
             ox = (int) txi * kTile; oy = (int) tyi * kTile;
             x = (uint32_t) (ox + lx); y = (uint32_t) (oy + ly);
             sampleK = pass * rp.K + (r >> 10); rec = j; ring = pass % (uint32_t) rp.ring;
+            tileSlot = ring * rp.numTiles + tile;
             ok = tile < rp.numTiles && x < (uint32_t) W && y < (uint32_t) H;
         }
     }
@@ -397,7 +398,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
     pool.rad[dst] = make_float4(0.f, 0.f, 0.f, 1.f);
     pool.rng[dst] = make_ulonglong2(rng.state, rng.inc);
     pool.pos[dst] = make_float2(ps.x, ps.y);
-    pool.meta[dst] = make_uint4(y * (uint32_t) W + x, sampleIndex, kFlagAlive | kFlagDiscrete | (ring << 24), rec);
+    pool.meta[dst] = make_uint4(tileSlot, sampleIndex, kFlagAlive | kFlagDiscrete | (ring << 24), rec);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -419,9 +420,8 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     __shared__ unsigned short sPerm[256];
     const unsigned tid = threadIdx.x, warp = tid >> 5;
     const uint32_t blockBase = blockIdx.x * blockDim.x;
-    const int W = sc.cam.width;
     const unsigned long long limit = c->issueLimit;
-    const uint32_t passHint = c->passHint, completedPasses = c->completedPasses;
+    const uint32_t passHint = c->passHint, lateBelow = c->completedPasses * rp.K;   // samples of closed passes are late
     // ---- CTA-local counting sort by what the slot needs -----------------------------------
     int key0 = kNumKeys;
     {
@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
             pool.meta[slot] = meta;
         } else {
             const bool mulT = flags & kFlagMulT;
-            const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < completedPasses;
+            const bool late = !rp.listPixel && meta.y - rp.sampleFirst < lateBelow;
             const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
             if (!sh.cast) { fin = true; needB = true; finL = mulT ? T * L : L; }
             else if (!mulT && !late && r < (size_t) kShadowToRecord) {
@@ -504,7 +504,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     bool counted = false;
     if (fin) {
         const float2 ps = pool.pos[slot];
-        const bool late = !rp.listPixel && (meta.y - rp.sampleFirst) / rp.K < completedPasses;
+        const bool late = !rp.listPixel && meta.y - rp.sampleFirst < lateBelow;
         if (late) {
             splatDirect(sc, rp, c, ps, finL);
             atomicAdd(&c->lateSamples, 1u);
@@ -516,11 +516,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
         }
     }
     if (__any_sync(0xffffffffu, counted)) {       // one atomic per (ring slot, tile) present in the warp
-        uint32_t tile = 0xffffffffu;
-        if (counted) {
-            const uint32_t x = meta.x % (uint32_t) W, y = meta.x / (uint32_t) W;
-            tile = (meta.z >> 24) * rp.numTiles + (y / kTile) * rp.tilesX + (x / kTile);
-        }
+        const uint32_t tile = counted ? meta.x : 0xffffffffu;
         const unsigned peers = __match_any_sync(0xffffffffu, tile);
         if (counted && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
     }
