@@ -29,7 +29,7 @@ struct nori_gpu_ctx {
     // accumulator
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
-    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 21;
+    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 22;   // 4 Mi path slots (sweep: profiles/r01_sweeps.md)
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
@@ -354,9 +354,11 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     bool done = false;
     const bool debug = getenv("NORI_GPU_DEBUG") != nullptr;
     uint64_t guard = 0;
+    bool drainedBefore = false;
+    Pool pool = ctx->pool;                       // .capacity shrinks in the tail of the render (enqueueCompaction)
     while (!done) {
         for (int k = 0; k < batch; ++k)
-            launches += (uint64_t) enqueueIteration(sc, ctx->pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 6 * k : nullptr);
+            launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 6 * k : nullptr);
         CK(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(evCopy, st));
         CK(cudaEventSynchronize(evCopy));
@@ -374,6 +376,16 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         const Counters &hc = *ctx->h_counters;
         if (debug) fprintf(stderr, "[nori_gpu] it=%llu issue=%llu/%llu limit=%llu finished=%llu/%llu passes=%u/%u splat=[%u %u %u %u]\n", (unsigned long long) hc.iterations, (unsigned long long) hc.issue, (unsigned long long) rp.totalIssue, (unsigned long long) hc.issueLimit, (unsigned long long) hc.finished, (unsigned long long) totalSamples, hc.completedPasses, rp.numPasses, hc.tilesSplatted[0], hc.tilesSplatted[1], hc.tilesSplatted[2], hc.tilesSplatted[3]);
         done = hc.finished >= totalSamples && (list || hc.completedPasses >= rp.numPasses);
+        // Tail: every camera sample has been handed out and the pool drains. Pack the surviving
+        // paths into the front of the pool so that the kernels stop scanning empty slots.
+        // (liveLast bounds the occupied slots only once a whole batch has run without regeneration.)
+        const bool drained = hc.issue >= rp.totalIssue;
+        if (!done && drained && drainedBefore && pool.capacity > 4096u && 2ull * hc.liveLast <= pool.capacity) {
+            const uint32_t newCap = std::max(4096u, (hc.liveLast + 255u) / 256u * 256u);
+            launches += (uint64_t) enqueueCompaction(pool, newCap, ctx->d_counters, st);
+            pool.capacity = newCap;
+        }
+        drainedBefore = drained;
         if (++guard > 4000000ull) { ctx->err = "render: wavefront did not terminate (internal error)"; return NORI_GPU_ECUDA; }
     }
     CK(cudaEventRecord(e1, st));

@@ -45,6 +45,8 @@ struct Counters {
     unsigned int readyCount;                // entries of RenderParams::readyTiles (tiles splatted this iteration)
     unsigned int passHint;                  // pass containing the next sample index to be issued
     unsigned int traceCursor[2];            // next ray of the persistent traversal kernels (closest, shadow)
+    unsigned int liveLast;                  // live paths shaded by the previous iteration
+    unsigned int compactCount[2];           // k_compactScan: free slots below / occupied slots above the new pool size
 };
 
 struct RenderParams {
@@ -74,6 +76,11 @@ struct StageTimes { float generate, traceClosest, shade, traceShadow, splat; };
 
 /// Marks every slot of the pool empty (start of a render).
 void enqueuePoolInit(const Pool &pool, Counters *d_counters, cudaStream_t st);
+
+/// Tail of a render (no camera sample left to hand out): moves the occupied slots at or above
+/// `newCapacity` into free slots below it, so that the following iterations run over
+/// `newCapacity` slots only. `pool.capacity` is the size the pool was run with so far.
+int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *d_counters, cudaStream_t st);
 
 /// One wavefront iteration, enqueued on `st`. Returns the number of kernel launches.
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,

@@ -39,7 +39,7 @@ __device__ __forceinline__ uint32_t warpAppend(unsigned int *counter, bool pred)
 __global__ void k_prepare(Counters *c, RenderParams rp) {
     unsigned rays = 0;
     for (int k = 0; k < kNumKeys; ++k) { rays += c->sortCount[k]; c->sortCount[k] = 0; }
-    c->closestRays += rays; c->segments += rays;
+    c->closestRays += rays; c->segments += rays; c->liveLast = rays;
     c->shadowRays += c->shadowCount; c->shadowCount = 0;
     c->iterations++;
     c->traceCursor[0] = 0; c->traceCursor[1] = 0;
@@ -760,6 +760,34 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 // ------------------------------------------------------------------------------------------
 template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
     k_shadeRegen<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
+}
+
+/// Tail compaction, step 1: list the free slots below `newCap` and the occupied ones at or above it
+/// (lists live in the idle shadow queue: [0, cap) and [cap, 2 cap) as uint32).
+__global__ void k_compactScan(Pool pool, uint32_t newCap, Counters *c) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t *freeList = reinterpret_cast<uint32_t *>(pool.shadow), *liveList = freeList + pool.capacity;
+    const bool occupied = i < pool.capacity && (pool.meta[i].z & (kFlagAlive | kFlagHasSample));
+    const bool isFree = i < newCap && !occupied, isLive = i >= newCap && occupied;
+    const uint32_t qf = warpAppend(&c->compactCount[0], isFree), ql = warpAppend(&c->compactCount[1], isLive);
+    if (isFree) freeList[qf] = i;
+    if (isLive) liveList[ql] = i;
+}
+/// Step 2: move the k-th listed path into the k-th listed free slot.
+__global__ void k_compactMove(Pool pool, Counters *c) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= c->compactCount[1]) return;
+    const uint32_t *freeList = reinterpret_cast<const uint32_t *>(pool.shadow), *liveList = freeList + pool.capacity;
+    const uint32_t src = liveList[k], dst = freeList[k];
+    pool.rayO[dst] = pool.rayO[src]; pool.rayD[dst] = pool.rayD[src]; pool.thr[dst] = pool.thr[src]; pool.rad[dst] = pool.rad[src];
+    pool.rng[dst] = pool.rng[src]; pool.pos[dst] = pool.pos[src]; pool.meta[dst] = pool.meta[src];
+    pool.meta[src] = make_uint4(0, 0, 0, 0);
+}
+int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *c, cudaStream_t st) {
+    cudaMemsetAsync(&c->compactCount[0], 0, 2 * sizeof(unsigned int), st);
+    k_compactScan<<<pool.capacity / 256, 256, 0, st>>>(pool, newCapacity, c);
+    k_compactMove<<<(pool.capacity - newCapacity + 255u) / 256u, 256, 0, st>>>(pool, c);
+    return 2;
 }
 
 __global__ void k_poolInit(Pool pool, Counters *c) {
