@@ -229,7 +229,8 @@ def run_gpu(args):
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("k_traceClosest_dram_bytes_per_launch")
+        tj = json.load(open(tp))
+        traffic = next((v for k, v in tj.items() if k.startswith("k_traceClosest") and k.endswith("_dram_bytes_per_launch")), None)
     cpu_v, cpu_kind, cores, cpu_s = cpu_reference(scene, args.ref_spp) if world == 1 and not args.no_cpu else (None, None, None, None)
     line = {
         "metric": METRIC, "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -237,7 +238,7 @@ def run_gpu(args):
         "config": {"workload": f"cbox path_mis 800x600 {spp}spp per GPU (BASELINE configs[1], C2)", "scene": SCENE, "triangles": scene.n_triangles,
                    "spp_per_gpu": spp, "sampler": "pcg32 per-sample streams", "partition": "sample-index ranges, one NCCL reduce of the ImageBlock per step",
                    "l2": "256 MiB flush buffer written between steps; path pool + sample records (> 400 MB) exceed L2, BVH+geometry (0.25 MB) are cache-resident by nature of the scene",
-                   "pool_paths": args.pool or 1 << 21, "accel": accel},
+                   "pool_paths": args.pool or 1 << 22, "accel": accel},
         "e2e": {"value": samples_per_step / (e2e_ms / 1e3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "includes": "scene upload, accel build, render, NCCL reduce, ImageBlock download"},
         "gpu_launches": int(tot["kernel_launches"]),
@@ -245,7 +246,8 @@ def run_gpu(args):
         "roofline": {"kernel": "k_traceClosest", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": alg["closest"]["bytes_per_ray"],
                      "rays_per_launch": tot["closest_rays"] / launches_closest, "avg_launch_ms": avg_launch_ms,
-                     "note": "algorithmic bytes are served by L1/L2 (scene is cache-resident); see DESIGN.md"},
+                     "traffic_capture": "ncu --set full of one steady-state launch at 2 Mi path slots (profiles/r01_kernels.md): ray records in/out only",
+                     "note": "algorithmic bytes are served by L1 (BVH + triangles of this scene are 0.17 MB): the kernel is issue-bound, not HBM-bound; see DESIGN.md and profiles/r01_trace.md"},
         "stages_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
         "Mrays_per_s": rays * world / (dev_ms / 1e3) / 1e6, "Gsegments_per_s": tot["segments"] * world / (dev_ms / 1e3) / 1e9,
         "segments_per_sample": tot["segments"] / max(tot["camera_samples"], 1), "reduce_ms_per_step": red_total / args.steps,

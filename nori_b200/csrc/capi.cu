@@ -29,7 +29,7 @@ struct nori_gpu_ctx {
     // accumulator
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
-    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 22;   // 4 Mi path slots (sweep: profiles/r01_sweeps.md)
+    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 22;   // 4 Mi path slots (sweep: profiles/r01_pipeline.md)
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;

@@ -2,7 +2,7 @@
 // scheme of Aila & Laine): a warp keeps its 32 lanes busy by refilling lanes whose ray has
 // terminated from a global work counter as soon as enough of them are idle, instead of idling
 // until the slowest ray of the warp is done (ncu on the one-ray-per-thread kernel: 6.4 of 32
-// lanes active per issued instruction, profiles/r01_trace_before.md).
+// lanes active per issued instruction, profiles/r01_trace.md).
 //
 // Same node layout, slab and Moeller-Trumbore arithmetic and tie rule as traverse() in
 // traverse.cuh, i.e. the result is the triangle the reference's brute-force loop reports
