@@ -1,7 +1,8 @@
-"""Builds nori_b200/libnori_b200.so (the C-ABI engine, include/nori_gpu.h) with nvcc for sm_100a.
+"""Builds nori_b200/libnori_b200.so (the C-ABI engine, include/nori_gpu.h) with nvcc for sm_100a and
+nori_b200/bin/nori_b200 (the C++ host front end above the C ABI, nori_b200/host) with g++.
 
-In-tree build: the .so travels with the repo snapshot to the GPU box. nvcc cross-compiles
-without a GPU. `python -m nori_b200.build [--force]`.
+In-tree build: the binaries travel with the repo snapshot to the GPU box. nvcc cross-compiles
+without a GPU. `python -m nori_b200.build [--force] [-v]`.
 """
 from __future__ import annotations
 
@@ -13,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnori_b200.so")
 SOURCES = ["capi.cu", "render.cu", "operators.cu", "bvh.cu"]
-HEADERS = ["engine.h", "bvh.h", "nmath.cuh", "scene.cuh", "traverse.cuh", os.path.join("..", "..", "include", "nori_gpu.h")]
+HEADERS = ["engine.h", "bvh.h", "nmath.cuh", "scene.cuh", "traverse.cuh", "traverse_persistent.cuh", os.path.join("..", "..", "include", "nori_gpu.h")]
 # -fmad=false: the arithmetic order written in nmath.cuh is the order executed (bit parity with
 # the x86-64 reference build, which has no FMA). Division and sqrt stay IEEE (nvcc defaults).
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
@@ -59,5 +60,44 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+HOST = os.path.join(HERE, "host")
+HOST_BIN = os.path.join(HERE, "bin", "nori_b200")
+HOST_SOURCES = ["common.cpp", "object.cpp", "xml.cpp", "parser.cpp", "plugins.cpp", "mesh.cpp", "scene.cpp", "bitmap.cpp", "main.cpp"]
+# No FMA contraction and no fast-math: matrices and filter tables must carry the values the
+# reference's x86-64 build computes.
+HOST_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-Wall", "-Wextra", "-Wno-unused-parameter",
+              "-I", HOST, "-I", os.path.join(HERE, "..", "include")]
+
+
+def build_host(force: bool = False, verbose: bool = False) -> str:
+    """g++ build of the host front end; links against libnori_b200.so next to it ($ORIGIN rpath)."""
+    objdir = os.path.join(HERE, "build", "host")
+    os.makedirs(objdir, exist_ok=True)
+    os.makedirs(os.path.dirname(HOST_BIN), exist_ok=True)
+    hdrs = [os.path.join(HOST, "nori", h) for h in os.listdir(os.path.join(HOST, "nori"))] + [os.path.join(HOST, "src", "xml.h"),
+            os.path.join(HERE, "..", "include", "nori_gpu.h")]
+    cxx = os.environ.get("CXX", "g++")
+    objs, procs = [], []
+    for s in HOST_SOURCES:
+        src, obj = os.path.join(HOST, "src", s), os.path.join(objdir, s.replace(".cpp", ".o"))
+        objs.append(obj)
+        if force or _stale(obj, [src] + hdrs):
+            procs.append((s, subprocess.Popen([cxx] + HOST_FLAGS + ["-c", src, "-o", obj], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    failed = False
+    for s, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0 or (verbose and out.strip()):
+            sys.stderr.write(f"--- g++ {s}\n{out}\n")
+        failed |= p.returncode != 0
+    if failed:
+        raise RuntimeError("g++ failed building the host front end")
+    if force or procs or _stale(HOST_BIN, objs + [LIB]):
+        subprocess.check_call([cxx, "-o", HOST_BIN] + objs + ["-L", HERE, "-lnori_b200", "-Wl,-rpath,$ORIGIN/..", "-lpthread", "-ldl"])
+    return HOST_BIN
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    force, verbose = "--force" in sys.argv, "-v" in sys.argv
+    print(build(force=force, verbose=verbose))
+    print(build_host(force=force, verbose=verbose))
+

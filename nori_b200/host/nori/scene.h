@@ -1,0 +1,218 @@
+// nori/scene.h — the scene-graph classes of the host layer: same class names, XML names,
+// properties and defaults as the reference; the numerical work behind their operators is done by
+// libnori_b200.so (include/nori_gpu.h).
+//
+// Reference: include/nori/{scene,mesh,bsdf,emitter,camera,rfilter,sampler,integrator,block,bitmap}.h
+#pragma once
+#include "object.h"
+#include <memory>
+
+struct nori_gpu_ctx;
+
+NORI_NAMESPACE_BEGIN
+
+class Mesh; class BSDF; class Emitter; class Scene; class Sampler;
+
+// ---- reconstruction filters (include/nori/rfilter.h:34-52, src/rfilter.cpp) ---------------------
+#define NORI_FILTER_RESOLUTION 32
+class ReconstructionFilter : public NoriObject {
+public:
+    float getRadius() const { return m_radius; }
+    virtual float eval(float x) const = 0;
+    EClassType getClassType() const override { return EReconstructionFilter; }
+protected:
+    float m_radius = 0;
+};
+
+// ---- BSDFs (include/nori/bsdf.h:29-112) ---------------------------------------------------------
+enum EMeasure { EUnknownMeasure = 0, ESolidAngle, EDiscrete };
+
+struct BSDFQueryRecord {
+    Vector3f wi, wo;
+    float eta = 1.0f;
+    EMeasure measure = EUnknownMeasure;
+    explicit BSDFQueryRecord(const Vector3f &wi_) : wi(wi_) {}
+    BSDFQueryRecord(const Vector3f &wi_, const Vector3f &wo_, EMeasure m) : wi(wi_), wo(wo_), measure(m) {}
+};
+
+class BSDF : public NoriObject {
+public:
+    /// Device-evaluated (nori_gpu_bsdf_sample / nori_gpu_bsdf_eval_pdf); arguments as in the reference.
+    Color3f sample(BSDFQueryRecord &bRec, const Point2f &sample) const;
+    Color3f eval(const BSDFQueryRecord &bRec) const;
+    float pdf(const BSDFQueryRecord &bRec) const;
+    virtual bool isDiffuse() const { return false; }
+    EClassType getClassType() const override { return EBSDF; }
+    /// Tagged POD view for NoriGpuMeshDesc: NORI_BSDF_* and {albedo|kd rgb, alpha, intIOR, extIOR}
+    virtual void describe(int &type, float params[6]) const = 0;
+};
+
+// ---- emitters (include/nori/emitter.h:28-36 is an empty base; `area` is defined by the scenes) ---
+class Emitter : public NoriObject {
+public:
+    EClassType getClassType() const override { return EEmitter; }
+    virtual Color3f getRadiance() const = 0;
+};
+
+// ---- meshes (include/nori/mesh.h:35-178) ----------------------------------------------------------
+struct Intersection {
+    Point3f p; float t = 0; Point2f uv;
+    Vector3f shS, shT, shN, geoS, geoT, geoN;      // shading and geometric frames
+    const Mesh *mesh = nullptr;
+};
+
+class Mesh : public NoriObject {
+public:
+    ~Mesh() override;
+    uint32_t getTriangleCount() const { return (uint32_t) (m_F.size() / 3); }
+    uint32_t getVertexCount() const { return (uint32_t) (m_V.size() / 3); }
+    /// 3 x nV positions, column-major (== nV consecutive xyz triples), as Mesh::m_V
+    const std::vector<float> &getVertexPositions() const { return m_V; }
+    const std::vector<float> &getVertexNormals() const { return m_N; }
+    const std::vector<float> &getVertexTexCoords() const { return m_UV; }
+    const std::vector<uint32_t> &getIndices() const { return m_F; }
+    bool isEmitter() const { return m_emitter != nullptr; }
+    const Emitter *getEmitter() const { return m_emitter; }
+    const BSDF *getBSDF() const { return m_bsdf; }
+    const std::string &getName() const { return m_name; }
+    void getBoundingBox(Point3f &lo, Point3f &hi) const { lo = m_lo; hi = m_hi; }
+    void addChild(NoriObject *child) override;
+    void activate() override;                        // default diffuse BSDF (src/mesh.cpp:35-41)
+    std::string toString() const override;
+    EClassType getClassType() const override { return EMesh; }
+protected:
+    std::string m_name;
+    std::vector<float> m_V, m_N, m_UV;
+    std::vector<uint32_t> m_F;
+    BSDF *m_bsdf = nullptr;
+    Emitter *m_emitter = nullptr;
+    Point3f m_lo = Point3f(INFINITY), m_hi = Point3f(-INFINITY);
+};
+
+// ---- camera (include/nori/camera.h:34-72, src/perspective.cpp) -------------------------------------
+class Camera : public NoriObject {
+public:
+    const Vector2i &getOutputSize() const { return m_outputSize; }
+    const ReconstructionFilter *getReconstructionFilter() const { return m_rfilter; }
+    EClassType getClassType() const override { return ECamera; }
+    /// State after activate(): the two matrices and clip planes NoriGpuCameraDesc carries
+    virtual void describe(float sampleToCamera[16], float cameraToWorld[16], float &nearClip, float &farClip, float &fov) const = 0;
+protected:
+    Vector2i m_outputSize;
+    ReconstructionFilter *m_rfilter = nullptr;
+};
+
+// ---- sampler (include/nori/sampler.h:45-104, src/independent.cpp) ------------------------------------
+class Sampler : public NoriObject {
+public:
+    size_t getSampleCount() const { return m_sampleCount; }
+    EClassType getClassType() const override { return ESampler; }
+protected:
+    size_t m_sampleCount = 1;
+};
+
+// ---- integrators (include/nori/integrator.h:30-66; the reference ships no subclass) ----------------
+class Integrator : public NoriObject {
+public:
+    EClassType getClassType() const override { return EIntegrator; }
+    virtual void preprocess(const Scene *) {}
+    /// NORI_INT_* of include/nori_gpu.h
+    virtual int gpuType() const = 0;
+    /// Extra parameters some integrators carry (`simple`: position, energy)
+    virtual void describe(float lightPos[3], float lightEnergy[3]) const { for (int i = 0; i < 3; ++i) lightPos[i] = lightEnergy[i] = 0; }
+    /// Path termination: Russian roulette from bounce `rrStart` with survival min(max(T) eta^2, rrMax);
+    /// maxDepth 0 = unbounded (properties rrStart / rrMax / maxDepth, as oracle/ref/plugins.cpp)
+    int rrStart() const { return m_rrStart; }
+    float rrMax() const { return m_rrMax; }
+    int maxDepth() const { return m_maxDepth; }
+protected:
+    void readTermination(const PropertyList &p) {
+        m_rrStart = p.getInteger("rrStart", 3); m_rrMax = p.getFloat("rrMax", 0.99f); m_maxDepth = p.getInteger("maxDepth", 0);
+    }
+    int m_rrStart = 3; float m_rrMax = 0.99f; int m_maxDepth = 0;
+};
+
+// ---- image block and bitmap (include/nori/block.h:44-113, include/nori/bitmap.h:30-58) ---------------
+/// Interleaved RGB float image; saveEXR / savePNG as src/bitmap.cpp:81-134.
+class Bitmap {
+public:
+    Bitmap(int width = 0, int height = 0) : m_width(width), m_height(height), m_data((size_t) width * height * 3, 0.0f) {}
+    int cols() const { return m_width; }
+    int rows() const { return m_height; }
+    float *data() { return m_data.data(); }
+    const float *data() const { return m_data.data(); }
+    Color3f coeff(int y, int x) const { const float *p = &m_data[3 * ((size_t) y * m_width + x)]; return Color3f(p[0], p[1], p[2]); }
+    /// 3-channel FLOAT scanline OpenEXR, uncompressed; appends ".exr" like the reference
+    void saveEXR(const std::string &filename) const;
+    /// 8-bit sRGB PNG (Color3f::toSRGB, clamp); appends ".png"
+    void savePNG(const std::string &filename) const;
+private:
+    int m_width, m_height;
+    std::vector<float> m_data;
+};
+
+/// The full-frame accumulator as the device keeps it: (H + 2b) x (W + 2b) x RGBW, row-major.
+class ImageBlock {
+public:
+    ImageBlock(const Vector2i &size, const ReconstructionFilter *filter);
+    const Vector2i &getSize() const { return m_size; }
+    int getBorderSize() const { return m_border; }
+    int rows() const { return m_size.y + 2 * m_border; }
+    int cols() const { return m_size.x + 2 * m_border; }
+    float *data() { return m_data.data(); }
+    const float *data() const { return m_data.data(); }
+    /// 33-entry filter table and radius exactly as src/block.cpp:31-39 builds them
+    const float *filterTable() const { return m_table; }
+    float filterRadius() const { return m_radius; }
+    /// rgb / w per pixel, border cropped (src/block.cpp:57-63, include/nori/color.h:112-117)
+    std::unique_ptr<Bitmap> toBitmap() const;
+private:
+    Vector2i m_size; int m_border = 0; float m_radius = 0; float m_table[NORI_FILTER_RESOLUTION + 1];
+    std::vector<float> m_data;
+};
+
+// ---- scene (include/nori/scene.h:34-127, src/scene.cpp) -----------------------------------------------
+class Scene : public NoriObject {
+public:
+    explicit Scene(const PropertyList &);
+    ~Scene() override;
+    const Integrator *getIntegrator() const { return m_integrator; }
+    const Camera *getCamera() const { return m_camera; }
+    const Sampler *getSampler() const { return m_sampler; }
+    const std::vector<Mesh *> &getMeshes() const { return m_meshes; }
+    /// Accel::rayIntersect through the device BVH (one ray; batches go through nori_gpu_trace)
+    bool rayIntersect(const Ray3f &ray, Intersection &its) const;
+    bool rayIntersect(const Ray3f &ray) const;
+    void addChild(NoriObject *obj) override;
+    void activate() override;
+    std::string toString() const override;
+    EClassType getClassType() const override { return EScene; }
+    /// Device context holding this scene (created and filled on first use). Throws NoriException
+    /// when no CUDA device or libnori_b200.so is available: there is no CPU path.
+    nori_gpu_ctx *gpu(int device = 0) const;
+private:
+    std::vector<Mesh *> m_meshes;
+    Integrator *m_integrator = nullptr;
+    Sampler *m_sampler = nullptr;
+    Camera *m_camera = nullptr;
+    mutable nori_gpu_ctx *m_ctx = nullptr;
+};
+
+/// Statistics nori_gpu_render reports (subset printed by the command line tool)
+struct RenderReport { double ms = 0, msamples = 0, mrays = 0, gsegments = 0; uint64_t dropped = 0, launches = 0; };
+
+/// Replacement for the reference's render() block loop (src/main.cpp:86-127): the whole frame,
+/// samples [sampleFirst, sampleLast) of every pixel, into `result`.
+void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report);
+
+/// Search path for files named in scene descriptions (the reference prepends the scene's directory)
+class FileResolver {
+public:
+    void prepend(const std::string &dir) { m_paths.insert(m_paths.begin(), dir); }
+    std::string resolve(const std::string &name) const;
+private:
+    std::vector<std::string> m_paths;
+};
+FileResolver *getFileResolver();
+
+NORI_NAMESPACE_END

@@ -1,0 +1,118 @@
+// main.cpp — `nori_b200 scene.xml`: the headless counterpart of the reference's `nori scene.xml`
+// (src/main.cpp:153-213): parse the scene description, render it on the GPU through the C ABI, write
+// <scene>.exr and <scene>.png next to the scene file.
+//
+//   nori_b200 [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] scene.xml
+//   nori_b200 --dump FILE scene.xml     parse only; write the flattened descriptors (tests; no GPU)
+#include <nori/scene.h>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <memory>
+
+using namespace nori;
+
+namespace {
+
+template <class T> void put(std::ofstream &os, const T &v) { os.write((const char *) &v, sizeof(T)); }
+template <class T> void putArray(std::ofstream &os, const T *p, size_t n) { os.write((const char *) p, (std::streamsize) (n * sizeof(T))); }
+
+/// Everything that crosses the C ABI for this scene, as one little-endian binary file
+/// (layout read by tests/test_host_cpp.py).
+void dumpScene(const Scene *scene, const std::string &path) {
+    std::ofstream os(path, std::ios::binary);
+    if (os.fail()) throw NoriException("Unable to open \"%s\" for writing", path);
+    os.write("NB2DUMP1", 8);
+    const Camera *cam = scene->getCamera();
+    float s2c[16], c2w[16], nearClip, farClip, fov;
+    cam->describe(s2c, c2w, nearClip, farClip, fov);
+    put<int32_t>(os, (int32_t) scene->getMeshes().size());
+    put<int32_t>(os, cam->getOutputSize().x); put<int32_t>(os, cam->getOutputSize().y);
+    put(os, nearClip); put(os, farClip); put(os, fov);
+    putArray(os, s2c, 16); putArray(os, c2w, 16);
+    const ImageBlock block(cam->getOutputSize(), cam->getReconstructionFilter());
+    put(os, block.filterRadius()); putArray(os, block.filterTable(), NORI_FILTER_RESOLUTION + 1);
+    const Integrator *in = scene->getIntegrator();
+    float lp[3], le[3];
+    in->describe(lp, le);
+    put<int32_t>(os, in->gpuType()); put<int32_t>(os, in->rrStart()); put<int32_t>(os, in->maxDepth());
+    put<int32_t>(os, (int32_t) scene->getSampler()->getSampleCount());
+    put(os, in->rrMax()); putArray(os, lp, 3); putArray(os, le, 3);
+    for (const Mesh *m : scene->getMeshes()) {
+        put<uint32_t>(os, m->getVertexCount()); put<uint32_t>(os, m->getTriangleCount());
+        put<uint32_t>(os, m->getVertexNormals().empty() ? 0u : 1u); put<uint32_t>(os, m->getVertexTexCoords().empty() ? 0u : 1u);
+        int type; float params[6];
+        m->getBSDF()->describe(type, params);
+        put<int32_t>(os, type); putArray(os, params, 6);
+        put<int32_t>(os, m->isEmitter() ? 1 : 0);
+        const Color3f r = m->isEmitter() ? m->getEmitter()->getRadiance() : Color3f(0.0f);
+        put(os, r.r); put(os, r.g); put(os, r.b);
+        putArray(os, m->getVertexPositions().data(), m->getVertexPositions().size());
+        putArray(os, m->getVertexNormals().data(), m->getVertexNormals().size());
+        putArray(os, m->getVertexTexCoords().data(), m->getVertexTexCoords().size());
+        putArray(os, m->getIndices().data(), m->getIndices().size());
+    }
+}
+
+void render(const Scene *scene, const std::string &outName, int device, int sppOverride, long first, long last, bool png) {
+    const Camera *camera = scene->getCamera();
+    const uint32_t spp = sppOverride > 0 ? (uint32_t) sppOverride : (uint32_t) scene->getSampler()->getSampleCount();
+    const uint32_t s0 = first >= 0 ? (uint32_t) first : 0u, s1 = last >= 0 ? (uint32_t) last : spp;
+    if (s1 <= s0) throw NoriException("empty sample range [%d, %d)", (int) s0, (int) s1);
+    ImageBlock result(camera->getOutputSize(), camera->getReconstructionFilter());
+    scene->gpu(device);                                       // upload + Accel::build (Scene::activate does this in the reference)
+    std::cout << "Rendering .. " << std::flush;
+    RenderReport rep;
+    renderGpu(scene, result, s0, s1, device, &rep);
+    std::cout << "done. (took " << timeString(rep.ms) << ": " << rep.msamples << " Msamples/s, " << rep.mrays << " Mrays/s, "
+              << rep.gsegments << " Gsegments/s";
+    if (rep.dropped) std::cout << ", " << rep.dropped << " invalid samples dropped";
+    std::cout << ")" << std::endl;
+    std::unique_ptr<Bitmap> bitmap = result.toBitmap();
+    bitmap->saveEXR(outName);
+    if (png) bitmap->savePNG(outName);
+}
+
+} // namespace
+
+int main(int argc, char **argv) {
+    std::string sceneFile, dumpFile, outName;
+    int device = 0, spp = 0; long first = -1, last = -1; bool png = true;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto value = [&](const char *what) -> std::string {
+            if (i + 1 >= argc) { std::cerr << "Missing value for " << what << std::endl; exit(-1); }
+            return argv[++i];
+        };
+        if (a == "--device") device = atoi(value("--device").c_str());
+        else if (a == "--spp") spp = atoi(value("--spp").c_str());
+        else if (a == "--first") first = atol(value("--first").c_str());
+        else if (a == "--last") last = atol(value("--last").c_str());
+        else if (a == "--out") outName = value("--out");
+        else if (a == "--dump") dumpFile = value("--dump");
+        else if (a == "--no-png") png = false;
+        else if (!a.empty() && a[0] == '-') { std::cerr << "Unknown option " << a << std::endl; return -1; }
+        else sceneFile = a;
+    }
+    if (sceneFile.empty()) {
+        std::cerr << "Syntax: " << argv[0] << " [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--dump FILE] <scene.xml>" << std::endl;
+        return -1;
+    }
+    try {
+        const size_t slash = sceneFile.find_last_of('/');
+        getFileResolver()->prepend(slash == std::string::npos ? std::string(".") : sceneFile.substr(0, slash));
+        std::unique_ptr<NoriObject> root(loadFromXML(sceneFile));
+        if (root->getClassType() != NoriObject::EScene) return 0;      // e.g. a <test>: nothing to render
+        const Scene *scene = static_cast<const Scene *>(root.get());
+        if (!dumpFile.empty()) { dumpScene(scene, dumpFile); return 0; }
+        if (outName.empty()) {
+            const size_t dot = sceneFile.find_last_of('.');
+            outName = dot == std::string::npos || (slash != std::string::npos && dot < slash) ? sceneFile : sceneFile.substr(0, dot);
+        }
+        render(scene, outName, device, spp, first, last, png);
+    } catch (const std::exception &e) {
+        std::cerr << "Fatal error: " << e.what() << std::endl;
+        return -1;
+    }
+    return 0;
+}

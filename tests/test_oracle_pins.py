@@ -123,7 +123,7 @@ REF_TEST_SCENES = [
 
 @pytest.mark.ref
 @pytest.mark.parametrize("rel", REF_TEST_SCENES)
-def test_reference_fixture_scenes_pass(ref, rel):
+def test_reference_fixture_scenes_pass(ref, rel, tmp_path, monkeypatch):
     """ChiSquareTest::activate / StudentsTTest::activate (src/chi2test.cpp:93, src/ttest.cpp:103) throw
     when a test fails; loadFromXML runs them. They drive the restated plugins (microfacet, area
     emitter, path_ems/mats/mis, whitted) with the references' golden values (0.207067..., 2/5 furnace...)."""
@@ -131,4 +131,5 @@ def test_reference_fixture_scenes_pass(ref, rel):
     path = os.path.join(REFERENCE_ROOT, rel)
     if not os.path.exists(path):
         pytest.skip("reference tree absent")
+    monkeypatch.chdir(tmp_path)                  # chi2test writes chi2test_<n>.m into the working directory
     ref.load_xml(path)
