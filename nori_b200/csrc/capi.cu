@@ -496,7 +496,7 @@ int nori_gpu_trace(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint
     CK(cudaSetDevice(ctx->device));
     DevBuf<float4> dr, dh; CK(dr.alloc(2 * (size_t) n)); CK(dh.alloc(n));
     CK(cudaMemcpyAsync(dr.p, rays, (size_t) n * 32, cudaMemcpyHostToDevice, ctx->stream));
-    launchTrace(deviceScene(ctx), dr.p, n, shadow != 0, dh.p, ctx->stream);
+    launchTrace(deviceScene(ctx), dr.p, n, shadow != 0, dh.p, &ctx->d_counters->traceCursor[0], ctx->stream);
     std::vector<float4> h(n);
     CK(cudaMemcpyAsync(h.data(), dh.p, (size_t) n * 16, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
@@ -510,7 +510,7 @@ int nori_gpu_trace_device(nori_gpu_ctx *ctx, const void *d_rays, int n, int shad
     CK(cudaSetDevice(ctx->device));
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     CK(cudaEventRecord(e0, ctx->stream));
-    launchTrace(deviceScene(ctx), (const float4 *) d_rays, n, shadow != 0, (float4 *) d_hits, ctx->stream);
+    launchTrace(deviceScene(ctx), (const float4 *) d_rays, n, shadow != 0, (float4 *) d_hits, &ctx->d_counters->traceCursor[0], ctx->stream);
     CK(cudaEventRecord(e1, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
     float t = 0; cudaEventElapsedTime(&t, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);

@@ -87,7 +87,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
                      cudaEvent_t *stageEvents /* 6 or nullptr */);
 
 // raw operators (operators.cu); all pointers are device pointers
-void launchTrace(const DeviceScene &sc, const float4 *rays /* 2 per ray */, int n, bool shadow, float4 *hits, cudaStream_t st);
+void launchTrace(const DeviceScene &sc, const float4 *rays /* 2 per ray */, int n, bool shadow, float4 *hits, unsigned int *cursor /* device scratch */, cudaStream_t st);
 void launchTraceCount(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned long long *counts2, cudaStream_t st);
 void launchIntersect(const DeviceScene &sc, const float4 *rays, int n, float *out24, int *valid, cudaStream_t st);
 void launchCameraRays(const DeviceScene &sc, const float2 *ps, int n, float4 *rays, cudaStream_t st);

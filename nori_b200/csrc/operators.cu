@@ -3,7 +3,7 @@
 // They run the same device functions as the wavefront renderer (traverse.cuh, nmath.cuh,
 // scene.cuh) and exist for parity tests, the chi2/t-test harness and Mrays/s measurements.
 #include "engine.h"
-#include "traverse.cuh"
+#include "traverse_persistent.cuh"
 
 namespace ng {
 
@@ -29,10 +29,31 @@ __global__ void __launch_bounds__(256) k_trace(DeviceScene sc, const float4 *__r
     }
 }
 
-void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, cudaStream_t st) {
+/// The same operator on the renderer's traversal kernel (persistent warps, dynamic ray fetch).
+struct RayArrayIO {
+    const float4 *rays; float4 *hits;
+    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        const float4 ro = __ldg(rays + 2 * (size_t) i), rd = __ldg(rays + 2 * (size_t) i + 1);
+        o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float t, float u, float v) const {
+        hits[i] = gid == kNoHit ? make_float4(0.f, 0.f, 0.f, __uint_as_float(gid)) : make_float4(t, u, v, __uint_as_float(gid));
+    }
+};
+template <bool SHADOW>
+__global__ void __launch_bounds__(128, 8) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
+    RayArrayIO io; io.rays = rays; io.hits = hits;
+    tracePersistent<SHADOW>(sc.nodes, sc.leafTris, (uint32_t) n, cursor, io);
+}
+
+void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned int *cursor, cudaStream_t st) {
     if (n <= 0) return;
-    if (shadow) k_trace<true, false><<<gridFor(n), 256, 0, st>>>(sc, rays, n, hits, nullptr);
-    else k_trace<false, false><<<gridFor(n), 256, 0, st>>>(sc, rays, n, hits, nullptr);
+    static unsigned grid = 0;
+    if (!grid) { int dev = 0, sms = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); grid = (unsigned) sms * 8u; }
+    cudaMemsetAsync(cursor, 0, sizeof(unsigned int), st);
+    if (shadow) k_tracePersistent<true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
+    else k_tracePersistent<false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
 }
 void launchTraceCount(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned long long *counts2, cudaStream_t st) {
     if (n <= 0) return;
