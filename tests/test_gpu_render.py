@@ -101,3 +101,58 @@ def test_small_pool_and_odd_sizes(gpu_scene, scenes):
     finally:
         e.set_pool_size(1 << 21)
         e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+
+
+# ---- the other reconstruction filters and integrators -----------------------------
+import os
+HOST_GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "host")
+
+
+@pytest.fixture(scope="module")
+def own_engine():
+    """A context of its own, so that loading other scenes does not disturb the session's scene cache."""
+    from nori_b200.gpu import Engine
+    e = Engine(0)
+    yield e
+    e.close()
+
+
+@pytest.mark.parametrize("name,border,kernel", [
+    ("whitted_box", 0, "k_splatPixel<0>: box filter, radius 0.5; whitted + dielectric"),
+    ("simple_tent", 1, "k_splatPixel<1>: tent filter, radius 1; simple integrator, 96x160 frame"),
+    ("all_tags", 1, "k_splatPixel<1>: mitchell radius 1.5; path_mis with rrStart 5 / rrMax 0.95 / maxDepth 12, microfacet"),
+    ("defaults", 2, "k_splatPixel<2>: default gaussian; normals; 1280x720 default camera"),
+])
+def test_filters_and_integrators_vs_oracle(own_engine, port, name, border, kernel):
+    """Scenes of tests/golden/host (descriptors produced by the reference's parser): every filter
+    radius class of the splat stage and the integrators the Cornell-box fixtures do not use."""
+    from nori_b200.scene import FlatScene
+    s = FlatScene.load(os.path.join(HOST_GOLDEN, name + ".npz"))
+    assert s.border == border
+    spp = 3
+    own_engine.load_scene(s)
+    ps = port.scene(s); ps.set_integrator(s.integrator)
+    want, wstats = ps.render(mode=1, sample_first=0, sample_last=spp)
+    got, stats = own_engine.render(sample_first=0, sample_last=spp)
+    assert got.shape == want.shape == s.block_shape()
+    assert stats["camera_samples"] == s.width * s.height * spp and stats["dropped"] == int(wstats[3])
+    np.testing.assert_allclose(got[..., 3], want[..., 3], rtol=1e-5, atol=1e-6)          # filter weights: same positions, same table
+    if border:
+        assert rel_mse(to_bitmap(got, border), to_bitmap(want, border)) <= 2e-3
+    else:
+        assert rel_mse(got[..., :3], want[..., :3]) <= 2e-3
+
+
+def test_wide_filter_takes_the_generic_splat_kernel(own_engine, port):
+    """A gaussian of radius 3.2 (border 3) is beyond the register-accumulating kernels: k_splat."""
+    from nori_b200.scene import FlatScene
+    s = FlatScene.load(os.path.join(HOST_GOLDEN, "simple_tent.npz"))
+    table, border = port.filter_table(0, 3.2, 0.8, 0.0)                                   # gaussian, stddev 0.8
+    s.filter_radius, s.filter_table = 3.2, table
+    assert border == 3 == s.border
+    own_engine.load_scene(s)
+    ps = port.scene(s); ps.set_integrator(s.integrator)
+    want, _ = ps.render(mode=1, sample_first=0, sample_last=2)
+    got, _ = own_engine.render(sample_first=0, sample_last=2)
+    np.testing.assert_allclose(got[..., 3], want[..., 3], rtol=1e-5, atol=1e-6)
+    assert rel_mse(to_bitmap(got, 3), to_bitmap(want, 3)) <= 2e-3

@@ -149,7 +149,7 @@ def read_png(path):
 
 
 @pytest.mark.gpu
-def test_cli_renders_scene_and_writes_exr_png(tmp_path, engine):
+def test_cli_renders_scene_and_writes_exr_png(tmp_path):
     xml = os.path.join(HOST, "all_tags.xml")
     out = str(tmp_path / "img")
     r = subprocess.run([HOST_BIN, "--out", out, "--spp", "16", xml], capture_output=True, text=True, timeout=300)
@@ -159,11 +159,14 @@ def test_cli_renders_scene_and_writes_exr_png(tmp_path, engine):
     flat = FlatScene.load(os.path.join(HOST, "all_tags.npz"))
     assert img.shape == (flat.height, flat.width, 3)
     # the same render through the Python binding of the same C ABI: same samples, same kernels
+    from nori_b200.gpu import Engine
+    engine = Engine(0)
     engine.load_scene(flat)
     block, _ = engine.render(sample_first=0, sample_last=16)       # integrator and termination come from the scene
     b = flat.border
     rgbw = block[b:b + flat.height, b:b + flat.width]
     want = np.where(rgbw[..., 3:] != 0, rgbw[..., :3] / np.where(rgbw[..., 3:] != 0, rgbw[..., 3:], 1), 0).astype(np.float32)
+    engine.close()
     np.testing.assert_allclose(img, want, rtol=2e-4, atol=1e-5)              # float atomics: summation order only
     assert np.isfinite(img).all() and img.mean() > 1e-3
     png = read_png(out + ".png")
