@@ -341,11 +341,11 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     if (d->clear && !list) CK(cudaMemsetAsync(ctx->d_block, 0, ctx->blockFloats * sizeof(float), st));
 
     const DeviceScene sc = deviceScene(ctx);
-    // Stage events (profiling): 6 per iteration of a batch, read back after the batch's one
+    // Stage events (profiling): 4 per iteration of a batch, read back after the batch's one
     // synchronisation, so that profiling does not change how the kernels are queued.
     const int batch = 8;
     cudaEvent_t e0, e1, evCopy;
-    std::vector<cudaEvent_t> stage(ctx->profiling ? 6 * batch : 0);
+    std::vector<cudaEvent_t> stage(ctx->profiling ? 4 * batch : 0);
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreateWithFlags(&evCopy, cudaEventDisableTiming));
     for (auto &e : stage) CK(cudaEventCreate(&e));
     StageTimes tm = {0, 0, 0, 0, 0};
@@ -358,19 +358,17 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     Pool pool = ctx->pool;                       // .capacity shrinks in the tail of the render (enqueueCompaction)
     while (!done) {
         for (int k = 0; k < batch; ++k)
-            launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 6 * k : nullptr);
+            launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 4 * k : nullptr);
         CK(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(evCopy, st));
         CK(cudaEventSynchronize(evCopy));
         CK(cudaGetLastError());
         if (ctx->profiling) {
             for (int k = 0; k < batch; ++k) {
-                cudaEvent_t *ev = stage.data() + 6 * k; float ms;
-                cudaEventElapsedTime(&ms, ev[0], ev[1]); tm.generate += ms;
-                cudaEventElapsedTime(&ms, ev[1], ev[2]); tm.traceClosest += ms;
-                cudaEventElapsedTime(&ms, ev[2], ev[3]); tm.shade += ms;
-                cudaEventElapsedTime(&ms, ev[3], ev[4]); tm.traceShadow += ms;
-                cudaEventElapsedTime(&ms, ev[4], ev[5]); tm.splat += ms;
+                cudaEvent_t *ev = stage.data() + 4 * k; float ms;
+                cudaEventElapsedTime(&ms, ev[0], ev[1]); tm.traceClosest += ms;    // splat of the previous iteration runs under it
+                cudaEventElapsedTime(&ms, ev[1], ev[2]); tm.shade += ms;           // k_prepare + k_shadeRegen
+                cudaEventElapsedTime(&ms, ev[2], ev[3]); tm.traceShadow += ms;
             }
         }
         const Counters &hc = *ctx->h_counters;

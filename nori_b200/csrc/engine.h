@@ -84,7 +84,7 @@ int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *d_counte
 
 /// One wavefront iteration, enqueued on `st`. Returns the number of kernel launches.
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,
-                     cudaEvent_t *stageEvents /* 6 or nullptr */);
+                     cudaEvent_t *stageEvents /* 4 or nullptr */);
 
 // raw operators (operators.cu); all pointers are device pointers
 void launchTrace(const DeviceScene &sc, const float4 *rays /* 2 per ray */, int n, bool shadow, float4 *hits, unsigned int *cursor /* device scratch */, cudaStream_t st);

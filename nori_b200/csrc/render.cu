@@ -42,7 +42,7 @@ __global__ void k_prepare(Counters *c, RenderParams rp) {
     c->closestRays += rays; c->segments += rays; c->liveLast = rays;
     c->shadowRays += c->shadowCount; c->shadowCount = 0;
     c->iterations++;
-    c->traceCursor[0] = 0; c->traceCursor[1] = 0;
+    c->traceCursor[0] = 0; c->traceCursor[1] = 0;      // [0]: for the NEXT iteration's closest-hit pass (it runs before k_prepare)
     c->readyCount = 0;
     // lanes that drew an index at or past the previous limit discarded it: hand those indices out again
     if (c->issue > c->issueLimit) c->issue = c->issueLimit;
@@ -574,6 +574,7 @@ __global__ void k_splatPlan(DeviceScene sc, RenderParams rp, Counters *c) {
 }
 
 __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, Counters *c) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");     // see k_splatPixel
     __shared__ float plane[4][kSplatSide * kSplatSide];
     __shared__ float sTable[33];
     __shared__ unsigned sDropped;
@@ -655,6 +656,9 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
 /// instead of one per sample), which the CTA finally adds to the full-frame block.
 template <int B>
 __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams rp, Counters *c) {
+    // Programmatic dependent launch: the closest-hit pass queued behind this kernel does not read
+    // anything the splat writes, so it may start filling the SMs this grid leaves free right away.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     constexpr int WN = 2 * B + 1, Q = 16, SIDE = Q + 2 * B;
     __shared__ float plane[4][SIDE * SIDE];
     __shared__ float sTable[33];
@@ -793,6 +797,10 @@ int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *c, cudaS
 __global__ void k_poolInit(Pool pool, Counters *c) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     pool.meta[i] = make_uint4(0, 0, 0, 0);
+    if (i == 0) {                                   // what k_prepare would have left: the first splat pass runs before it
+        c->forcePass = 0xffffffffu;
+        for (int s = 0; s < kMaxRing; ++s) c->slotPass[s] = (unsigned) s;
+    }
 }
 void enqueuePoolInit(const Pool &pool, Counters *c, cudaStream_t st) { k_poolInit<<<pool.capacity / 256, 256, 0, st>>>(pool, c); }
 
@@ -804,10 +812,11 @@ static unsigned persistentGrid() {
 }
 
 /// Tunables of the traversal kernels (environment overrides are for parameter sweeps only).
-struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; };
+struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; bool overlapSplat; };
 static const Tune &tune() {
     static Tune t = [] {
-        Tune v = {kFetchThreshold, kFetchThreshold, 8u};
+        Tune v = {kFetchThreshold, kFetchThreshold, 8u, true};
+        if (getenv("NORI_GPU_NO_OVERLAP")) v.overlapSplat = false;
         if (const char *s = getenv("NORI_GPU_FETCH")) v.fetchClosest = v.fetchShadow = atoi(s);
         if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = atoi(s);
         if (const char *s = getenv("NORI_GPU_NODE_EXIT")) { v.fetchClosest |= atoi(s) << 8; v.fetchShadow |= atoi(s) << 8; }
@@ -817,19 +826,51 @@ static const Tune &tune() {
     return t;
 }
 
+/// Launches `kernel` so that it may begin while the kernel queued before it on `st` is still running
+/// (programmatic stream serialisation): only for kernels that do not consume that kernel's output.
+template <class... Params, class... Args>
+static void launchOverlapped(void (*kernel)(Params...), unsigned grid, unsigned block, cudaStream_t st, bool overlap, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = overlap ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
+// One iteration. The splat of the PREVIOUS iteration's finished tiles is queued first and the
+// closest-hit traversal directly behind it as a programmatic dependent launch: the traversal touches
+// only the path pool, the splat only sample records, tile counters and the frame, so the traversal's
+// CTAs start on the SMs the (few, register-heavy) splat CTAs leave free instead of waiting for them.
+// k_prepare is a normal launch: it starts when both are complete.
+// ev (profiling): [0] begin [1] splat(i-1) + trace end [2] shade end [3] shadow end.
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st, cudaEvent_t *ev) {
     int launches = 0;
+    const bool splat = !rp.listPixel;
     if (ev) cudaEventRecord(ev[0], st);
-    k_prepare<<<1, 1, 0, st>>>(c, rp); ++launches;
-    if (ev) cudaEventRecord(ev[1], st);
-    {
-        const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
-        if (b == 10) k_traceClosest<10><<<g, 128, 0, st>>>(sc, pool, c, tune().fetchClosest);
-        else if (b == 12) k_traceClosest<12><<<g, 128, 0, st>>>(sc, pool, c, tune().fetchClosest);
-        else k_traceClosest<8><<<g, 128, 0, st>>>(sc, pool, c, tune().fetchClosest);
+    if (splat) {
+        k_splatPlan<<<((uint32_t) rp.ring * rp.numTiles + 255u) / 256u, 256, 0, st>>>(sc, rp, c); ++launches;
+        const unsigned g = persistentGrid() / 8u;          // one resident CTA per SM (248 registers x 256 threads): a single wave, so
+                                                           // that every CTA reaches launch_dependents at once
+        switch (sc.filter.border) {
+        case 0: k_splatPixel<0><<<g, 256, 0, st>>>(sc, rp, c); break;
+        case 1: k_splatPixel<1><<<g, 256, 0, st>>>(sc, rp, c); break;
+        case 2: k_splatPixel<2><<<g, 256, 0, st>>>(sc, rp, c); break;
+        default: k_splat<<<g, 256, 0, st>>>(sc, rp, c); break;
+        }
         ++launches;
     }
-    if (ev) cudaEventRecord(ev[2], st);
+    {
+        const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const bool overlap = splat && tune().overlapSplat;
+        if (b == 10) launchOverlapped(k_traceClosest<10>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (b == 12) launchOverlapped(k_traceClosest<12>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else launchOverlapped(k_traceClosest<8>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        ++launches;
+    }
+    if (ev) cudaEventRecord(ev[1], st);
+    k_prepare<<<1, 1, 0, st>>>(c, rp); ++launches;
     switch (rp.integrator) {
     case NORI_INT_NORMALS: launchShade<NORI_INT_NORMALS>(sc, pool, rp, c, st); break;
     case NORI_INT_PATH_MATS: launchShade<NORI_INT_PATH_MATS>(sc, pool, rp, c, st); break;
@@ -841,7 +882,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     default: launchShade<NORI_INT_AO>(sc, pool, rp, c, st); break;
     }
     ++launches;
-    if (ev) cudaEventRecord(ev[3], st);
+    if (ev) cudaEventRecord(ev[2], st);
     if (rp.integrator != NORI_INT_NORMALS) {
         const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
         if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
@@ -849,19 +890,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
         ++launches;
     }
-    if (ev) cudaEventRecord(ev[4], st);
-    if (!rp.listPixel) {
-        k_splatPlan<<<((uint32_t) rp.ring * rp.numTiles + 255u) / 256u, 256, 0, st>>>(sc, rp, c); ++launches;
-        const unsigned g = persistentGrid() / 4u;          // 2 CTAs of 256 threads per SM
-        switch (sc.filter.border) {
-        case 0: k_splatPixel<0><<<g, 256, 0, st>>>(sc, rp, c); break;
-        case 1: k_splatPixel<1><<<g, 256, 0, st>>>(sc, rp, c); break;
-        case 2: k_splatPixel<2><<<g, 256, 0, st>>>(sc, rp, c); break;
-        default: k_splat<<<g, 256, 0, st>>>(sc, rp, c); break;
-        }
-        ++launches;
-    }
-    if (ev) cudaEventRecord(ev[5], st);
+    if (ev) cudaEventRecord(ev[3], st);
     return launches;
 }
 
