@@ -354,7 +354,8 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     bool done = false;
     const bool debug = getenv("NORI_GPU_DEBUG") != nullptr;
     uint64_t guard = 0;
-    bool drainedBefore = false;
+    bool drainedBefore = false, tailDone = false;
+    const uint32_t kTailPaths = getenv("NORI_GPU_TAIL") ? (uint32_t) atoi(getenv("NORI_GPU_TAIL")) : 262144u;   // sweep: profiles/r01_pipeline.md
     Pool pool = ctx->pool;                       // .capacity shrinks in the tail of the render (enqueueCompaction)
     while (!done) {
         for (int k = 0; k < batch; ++k)
@@ -382,6 +383,9 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
             const uint32_t newCap = std::max(4096u, (hc.liveLast + 255u) / 256u * 256u);
             launches += (uint64_t) enqueueCompaction(pool, newCap, ctx->d_counters, st);
             pool.capacity = newCap;
+            // A few thousand paths left: one launch follows each of them to its end (k_finishTail)
+            // instead of one launch-bound wavefront iteration per bounce of the longest path.
+            if (newCap <= kTailPaths && !tailDone) { launches += (uint64_t) enqueueFinishTail(sc, pool, rp, ctx->d_counters, st); tailDone = true; }
         }
         drainedBefore = drained;
         if (++guard > 4000000ull) { ctx->err = "render: wavefront did not terminate (internal error)"; return NORI_GPU_ECUDA; }

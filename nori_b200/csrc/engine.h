@@ -82,6 +82,9 @@ void enqueuePoolInit(const Pool &pool, Counters *d_counters, cudaStream_t st);
 /// `newCapacity` slots only. `pool.capacity` is the size the pool was run with so far.
 int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *d_counters, cudaStream_t st);
 
+/// Follows every path still in `pool` (capacity = the compacted size) to its end in one launch.
+int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st);
+
 /// One wavefront iteration, enqueued on `st`. Returns the number of kernel launches.
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,
                      cudaEvent_t *stageEvents /* 4 or nullptr */);

@@ -766,6 +766,75 @@ template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool
     k_shadeRegen<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
 
+// ------------------------------------------------------------------------------------------
+/// The last paths of a frame: with Russian roulette capped near 1 a handful of paths live for hundreds
+/// of bounces, and a wavefront iteration (six launches) per bounce is launch-bound long before that.
+/// Once the pool has drained to a few thousand paths, ONE launch follows every remaining path to its
+/// end, one thread per path: the same traverse() / shadeVertex() steps in the same order, so each
+/// sample gets the value the wavefront would have produced.
+template <int INTEGRATOR>
+__global__ void __launch_bounds__(128) k_finishTail(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= pool.capacity) return;
+    uint4 meta = pool.meta[slot];
+    if (!(meta.z & (kFlagAlive | kFlagHasSample))) return;
+    const float4 th = pool.thr[slot], ra = pool.rad[slot];
+    V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
+    uint32_t flags = meta.z;
+    unsigned closest = 0, shadows = 0;
+    if (flags & kFlagAlive) {
+        const float4 ro = pool.rayO[slot], rd = pool.rayD[slot];
+        const ulonglong2 rs = pool.rng[slot];
+        Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
+        Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
+        float bsdfPdf = th.w, eta = ra.w;
+        for (;;) {
+            float t, u, v;
+            const uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, ray.o, ray.d, ray.mint, ray.maxt, t, u, v);
+            ++closest;
+            ShadowOut sh;
+            const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh);
+            if (sh.cast) {
+                float st, su, sv;
+                ++shadows;
+                if (traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv) == kNoHit) L = L + sh.contrib;
+            }
+            if (!cont) break;
+        }
+    }
+    const V3 finL = (flags & kFlagMulT) ? T * L : L;
+    const float2 ps = pool.pos[slot];
+    const bool late = !rp.listPixel && meta.y - rp.sampleFirst < c->completedPasses * rp.K;
+    if (late) {
+        splatDirect(sc, rp, c, ps, finL);
+        atomicAdd(&c->lateSamples, 1u);
+    } else {
+        const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+        rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
+        rp.recB[r] = finL.z;
+        if (!rp.listPixel) atomicAdd(rp.tileDone + meta.x, 1u);
+    }
+    pool.meta[slot] = make_uint4(0, 0, 0, 0);
+    atomicAdd(&c->finished, 1ull);
+    if (closest) { atomicAdd(&c->closestRays, (unsigned long long) closest); atomicAdd(&c->segments, (unsigned long long) closest); }
+    if (shadows) atomicAdd(&c->shadowRays, (unsigned long long) shadows);
+}
+
+int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
+    const unsigned g = (pool.capacity + 127u) / 128u;
+    switch (rp.integrator) {
+    case NORI_INT_NORMALS: k_finishTail<NORI_INT_NORMALS><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    case NORI_INT_PATH_MATS: k_finishTail<NORI_INT_PATH_MATS><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    case NORI_INT_PATH_EMS: k_finishTail<NORI_INT_PATH_EMS><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    case NORI_INT_PATH_MIS: k_finishTail<NORI_INT_PATH_MIS><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    case NORI_INT_WHITTED: k_finishTail<NORI_INT_WHITTED><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    case NORI_INT_PRIMARY_SHADOW: k_finishTail<NORI_INT_PRIMARY_SHADOW><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    case NORI_INT_SIMPLE: k_finishTail<NORI_INT_SIMPLE><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    default: k_finishTail<NORI_INT_AO><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
+    }
+    return 1;
+}
+
 /// Tail compaction, step 1: list the free slots below `newCap` and the occupied ones at or above it
 /// (lists live in the idle shadow queue: [0, cap) and [cap, 2 cap) as uint32).
 __global__ void k_compactScan(Pool pool, uint32_t newCap, Counters *c) {
