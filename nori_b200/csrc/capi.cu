@@ -29,7 +29,7 @@ struct nori_gpu_ctx {
     // accumulator
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
-    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 22;   // 4 Mi path slots (sweep: profiles/r01_pipeline.md)
+    Pool pool; bool havePool = false; uint32_t poolSize = 1u << 23;   // 8 Mi path slots (sweep: profiles/r01_pipeline.md)
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
@@ -304,13 +304,17 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     rp.tilesX = (W + kTile - 1) / kTile; rp.tilesY = (H + kTile - 1) / kTile; rp.numTiles = (uint32_t) (rp.tilesX * rp.tilesY);
     rp.block = ctx->d_block; rp.blockCols = W + 2 * ctx->filter.border; rp.blockRows = H + 2 * ctx->filter.border;
     uint64_t totalSamples;
+    // Slots used by this render: never more than there are camera samples (small frames, sample lists)
+    const uint64_t wanted = list ? (uint64_t) listCount : (uint64_t) W * H * (d->sample_last - d->sample_first);
+    Pool pool = ctx->pool;                       // .capacity also shrinks in the tail of the render (enqueueCompaction)
+    pool.capacity = (uint32_t) std::min<uint64_t>(ctx->pool.capacity, std::max<uint64_t>(4096, (wanted + 255) / 256 * 256));
     if (list) {
         rp.K = rp.Klast = 1; rp.numPasses = 1; rp.passSlots = listCount; rp.totalIssue = listCount; rp.ring = 1;
         rp.listPixel = d_listPixel; rp.listSample = d_listSample; totalSamples = listCount;
     } else {
         // pass = K samples of every pixel; sized to a few pool refills so stragglers never stall the ring
         const uint64_t slotsPerSpp = (uint64_t) rp.numTiles * 1024u;
-        uint32_t K = (uint32_t) std::max<uint64_t>(1, (4ull * ctx->pool.capacity + slotsPerSpp - 1) / slotsPerSpp);
+        uint32_t K = (uint32_t) std::max<uint64_t>(1, (4ull * pool.capacity + slotsPerSpp - 1) / slotsPerSpp);
         K = std::min(K, rp.sampleCount);
         rp.K = K; rp.numPasses = (rp.sampleCount + K - 1) / K; rp.Klast = rp.sampleCount - (rp.numPasses - 1) * K;
         rp.passSlots = slotsPerSpp * K; rp.ring = kMaxRing;
@@ -331,13 +335,13 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         CK(cudaMalloc((void **) &ctx->tileDone, tdNeed * sizeof(uint32_t))); CK(cudaMalloc((void **) &ctx->tileGen, tdNeed * sizeof(uint32_t)));
         ctx->tileDoneCap = tdNeed;
     }
-    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.readyTiles = ctx->readyTiles; rp.poolCapacity = ctx->pool.capacity;
+    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.readyTiles = ctx->readyTiles; rp.poolCapacity = pool.capacity;
     CK(cudaMemsetAsync(ctx->tileDone, 0, tdNeed * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(ctx->tileGen, 0, tdNeed * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(ctx->tileArrive, 0, tdNeed * sizeof(uint32_t), st));
     if (!list) CK(cudaMemsetAsync(ctx->recA, 0xff, recNeed * sizeof(float4), st));        // NaN position = no sample recorded
     CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), st));
-    enqueuePoolInit(ctx->pool, ctx->d_counters, st);
+    enqueuePoolInit(pool, ctx->d_counters, st);
     if (d->clear && !list) CK(cudaMemsetAsync(ctx->d_block, 0, ctx->blockFloats * sizeof(float), st));
 
     const DeviceScene sc = deviceScene(ctx);
@@ -356,7 +360,6 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     uint64_t guard = 0;
     bool drainedBefore = false, tailDone = false;
     const uint32_t kTailPaths = getenv("NORI_GPU_TAIL") ? (uint32_t) atoi(getenv("NORI_GPU_TAIL")) : 262144u;   // sweep: profiles/r01_pipeline.md
-    Pool pool = ctx->pool;                       // .capacity shrinks in the tail of the render (enqueueCompaction)
     while (!done) {
         for (int k = 0; k < batch; ++k)
             launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 4 * k : nullptr);
