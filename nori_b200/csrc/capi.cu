@@ -70,7 +70,7 @@ void freeScene(nori_gpu_ctx *c) {
 void freePool(nori_gpu_ctx *c) {
     if (!c->havePool) return;
     Pool &p = c->pool;
-    cudaFree(p.rayO); cudaFree(p.rayD); cudaFree(p.hit); cudaFree(p.thr); cudaFree(p.rad); cudaFree(p.rng); cudaFree(p.meta);
+    cudaFree(p.rayO); cudaFree(p.rayD); cudaFree(p.hit); cudaFree(p.thr); cudaFree(p.rad); cudaFree(p.state); cudaFree(p.info);
     cudaFree(p.pos); cudaFree(p.shadow);
     c->havePool = false;
 }
@@ -82,8 +82,8 @@ int ensurePool(nori_gpu_ctx *ctx) {
     memset(&p, 0, sizeof(p));
     p.capacity = ctx->poolSize;
     CK(cudaMalloc((void **) &p.rayO, n * 16)); CK(cudaMalloc((void **) &p.rayD, n * 16)); CK(cudaMalloc((void **) &p.hit, n * 16));
-    CK(cudaMalloc((void **) &p.thr, n * 16)); CK(cudaMalloc((void **) &p.rad, n * 16)); CK(cudaMalloc((void **) &p.rng, n * 16));
-    CK(cudaMalloc((void **) &p.meta, n * 16)); CK(cudaMalloc((void **) &p.pos, n * 8));
+    CK(cudaMalloc((void **) &p.thr, n * 16)); CK(cudaMalloc((void **) &p.rad, n * 16)); CK(cudaMalloc((void **) &p.state, n * 16));
+    CK(cudaMalloc((void **) &p.info, n * 16)); CK(cudaMalloc((void **) &p.pos, n * 8));
     CK(cudaMalloc((void **) &p.shadow, n * 48));
     ctx->havePool = true;
     return 0;
@@ -284,6 +284,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     REQUIRE(ctx->haveBvh && ctx->haveCamera && ctx->haveFilter, "render: scene, camera, filter and accel must be set first");
     REQUIRE(d->integrator >= NORI_INT_NORMALS && d->integrator <= NORI_INT_AO, "render: unknown integrator");
     REQUIRE(list || d->sample_last > d->sample_first, "render: empty sample range");
+    REQUIRE(list || d->sample_last <= 0x7fffffffu, "render: sample indices must stay below 2^31 (pcg32 stream ids are kept in 32 bits)");
     if (d->intersect_mode != NORI_ISECT_REFERENCE_MT) { ctx->err = "render: only NORI_ISECT_REFERENCE_MT is implemented"; return NORI_GPU_EUNSUPPORTED; }
     if (!list && d->stream_mode == NORI_STREAM_BLOCK && d->integrator != NORI_INT_NORMALS && d->integrator != NORI_INT_SIMPLE) {
         ctx->err = "render: NORI_STREAM_BLOCK (one serial PCG32 stream per block) is only reproducible for integrators that draw no random numbers (normals, simple)";
@@ -421,6 +422,7 @@ int nori_gpu_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuRen
 int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const uint32_t *pixel, const uint32_t *sample, float *rgb, float *pos) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(desc && n > 0 && pixel && sample && rgb, "sample_radiance: bad arguments");
+    for (int i = 0; i < n; ++i) REQUIRE(sample[i] <= 0x7fffffffu, "sample_radiance: sample indices must stay below 2^31");
     CK(cudaSetDevice(ctx->device));
     DevBuf<uint32_t> dp, ds;
     CK(dp.alloc(n)); CK(ds.alloc(n));

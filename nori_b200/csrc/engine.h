@@ -6,7 +6,7 @@
 
 namespace ng {
 
-// meta.z bits of a path slot
+// Pool::state.w bits of a path slot
 constexpr uint32_t kFlagAlive = 1u << 16;       // has a ray in flight
 constexpr uint32_t kFlagHasSample = 1u << 17;   // finished camera sample waiting to be recorded
 constexpr uint32_t kFlagDiscrete = 1u << 18;    // last bounce was a discrete BSDF (or the camera)
@@ -26,8 +26,8 @@ struct Pool {
     float4 *hit;         // t, u, v, bits(global triangle id | kNoHit)
     float4 *thr;         // throughput rgb, BSDF pdf of the last sampled direction
     float4 *rad;         // radiance rgb, eta product
-    ulonglong2 *rng;     // pcg32 state, inc
-    uint4 *meta;         // ring slot * numTiles + tile, sample index, flags | depth | ring slot << 24, record index
+    uint4 *state;        // pcg32 state lo, hi, pcg32 inc (32 bits), flags | depth | ring slot << 24   (read and written every bounce)
+    uint4 *info;         // ring slot * numTiles + tile, sample index, record index, -   (written when the path starts, read when it ends)
     float2 *pos;         // pixelSample handed to ImageBlock::put
     float4 *shadow;      // 3 x capacity: (o, maxt) (d, bits(slot)) (contribution, -)
 };

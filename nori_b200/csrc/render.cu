@@ -60,6 +60,16 @@ __global__ void k_prepare(Counters *c, RenderParams rp) {
     c->forcePass = (!rp.listPixel && cp < rp.numPasses && limit < rp.totalIssue && c->issue + rp.poolCapacity > limit) ? cp : 0xffffffffu;
 }
 
+/// Pool::state = the sampler stream of a path and its flags in one 16-byte word. pcg32's increment is
+/// (initseq << 1) | 1 with initseq a sample index or a tile offset: 32 bits are enough (checked on the host).
+__device__ __forceinline__ uint4 packState(const Pcg32 &rng, uint32_t flags) {
+    return make_uint4((uint32_t) rng.state, (uint32_t) (rng.state >> 32), (uint32_t) rng.inc, flags);
+}
+__device__ __forceinline__ Pcg32 unpackRng(const uint4 &st) {
+    Pcg32 r; r.state = (uint64_t) st.x | ((uint64_t) st.y << 32); r.inc = (uint64_t) st.z;
+    return r;
+}
+
 /// Pixel of slot r (< 1024) inside a tile: warps cover 8x4 pixel patches (coherent primary rays).
 __device__ __forceinline__ void tilePixel(uint32_t pix, int &lx, int &ly) {
     uint32_t w = pix >> 5, l = pix & 31u;
@@ -90,7 +100,7 @@ __device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Count
 struct ClosestIO {
     Pool pool;
     __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
-        if (!(pool.meta[i].z & kFlagAlive)) return false;
+        if (!(pool.state[i].w & kFlagAlive)) return false;
         const float4 ro = pool.rayO[i], rd = pool.rayD[i];
         o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
         return true;
@@ -374,7 +384,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
         }
     }
     if (!ok) {
-        if (!wasEmpty) pool.meta[dst] = make_uint4(0, 0, 0, 0);
+        if (!wasEmpty) pool.state[dst] = make_uint4(0, 0, 0, 0);
         return;
     }
     Pcg32 rng;
@@ -396,9 +406,9 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
     pool.rayD[dst] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
     pool.thr[dst] = make_float4(1.f, 1.f, 1.f, 0.f);
     pool.rad[dst] = make_float4(0.f, 0.f, 0.f, 1.f);
-    pool.rng[dst] = make_ulonglong2(rng.state, rng.inc);
     pool.pos[dst] = make_float2(ps.x, ps.y);
-    pool.meta[dst] = make_uint4(tileSlot, sampleIndex, kFlagAlive | kFlagDiscrete | (ring << 24), rec);
+    pool.state[dst] = packState(rng, kFlagAlive | kFlagDiscrete | (ring << 24));
+    pool.info[dst] = make_uint4(tileSlot, sampleIndex, rec, 0u);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -425,7 +435,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     // ---- CTA-local counting sort by what the slot needs -----------------------------------
     int key0 = kNumKeys;
     {
-        const uint32_t flags0 = pool.meta[blockBase + tid].z;
+        const uint32_t flags0 = pool.state[blockBase + tid].w;
         const uint32_t gid = __float_as_uint(pool.hit[blockBase + tid].w);
         if (flags0 & kFlagAlive) key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
     }
@@ -459,29 +469,28 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     uint32_t shadowTarget = slot;
     bool fin = false, needB = false;
     V3 finL = mk(0, 0, 0);
-    uint4 meta = pool.meta[slot];
+    const uint4 st = pool.state[slot];
+    uint4 info = make_uint4(0, 0, 0, 0);                     // read only when a camera sample ends
     if (tid < aBegin) {
         // ---- a surface was hit: one Li loop body ----------------------------------------------
         const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
-        const ulonglong2 rs = pool.rng[slot];
         Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
-        Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
+        Pcg32 rng = unpackRng(st);
         V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
         float bsdfPdf = th.w, eta = ra.w;
-        uint32_t flags = meta.z;
+        uint32_t flags = st.w;
         const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
         if (cont) {
             pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
             pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
-            pool.rng[slot] = make_ulonglong2(rng.state, rng.inc);
             pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
             pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
-            meta.z = flags;
-            pool.meta[slot] = meta;
+            pool.state[slot] = packState(rng, flags);
         } else {
+            info = pool.info[slot];
             const bool mulT = flags & kFlagMulT;
-            const bool late = !rp.listPixel && meta.y - rp.sampleFirst < lateBelow;
-            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+            const bool late = !rp.listPixel && info.y - rp.sampleFirst < lateBelow;
+            const size_t r = (size_t) (st.w >> 24) * rp.passSlots + info.z;
             if (!sh.cast) { fin = true; needB = true; finL = mulT ? T * L : L; }
             else if (!mulT && !late && r < (size_t) kShadowToRecord) {
                 fin = true; needB = true; finL = L;
@@ -489,39 +498,39 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
             } else {                                          // park: recorded by the next iteration's pass
                 pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
                 pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
-                meta.z = (flags & ~kFlagAlive) | kFlagHasSample;
-                pool.meta[slot] = meta;
+                pool.state[slot] = packState(rng, (flags & ~kFlagAlive) | kFlagHasSample);
             }
         }
-    } else if (meta.z & (kFlagAlive | kFlagHasSample)) {
+    } else if (st.w & (kFlagAlive | kFlagHasSample)) {
+        info = pool.info[slot];
         // ---- ray escaped (Li returns what the path gathered) or a parked sample -----------------
         const float4 ra = pool.rad[slot];
         finL = mk(ra.x, ra.y, ra.z);
-        if (meta.z & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
+        if (st.w & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
         fin = true;
     }
     // ---- record the camera samples that ended (src/main.cpp:59-62 -> block.put) ---------------
     bool counted = false;
     if (fin) {
         const float2 ps = pool.pos[slot];
-        const bool late = !rp.listPixel && meta.y - rp.sampleFirst < lateBelow;
+        const bool late = !rp.listPixel && info.y - rp.sampleFirst < lateBelow;
         if (late) {
             splatDirect(sc, rp, c, ps, finL);
             atomicAdd(&c->lateSamples, 1u);
         } else {
-            const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+            const size_t r = (size_t) (st.w >> 24) * rp.passSlots + info.z;
             rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
             rp.recB[r] = finL.z;
             counted = !rp.listPixel;
         }
     }
     if (__any_sync(0xffffffffu, counted)) {       // one atomic per (ring slot, tile) present in the warp
-        const uint32_t tile = counted ? meta.x : 0xffffffffu;
+        const uint32_t tile = counted ? info.x : 0xffffffffu;
         const unsigned peers = __match_any_sync(0xffffffffu, tile);
         if (counted && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
     }
     // ---- free slots known up front draw their next sample while other warps still shade ------
-    if (tid >= aBegin) regenSlot(sc, pool, rp, slot, sIssueA == ~0ull ? ~0ull : sIssueA + (tid - aBegin), limit, passHint, meta.z == 0);
+    if (tid >= aBegin) regenSlot(sc, pool, rp, slot, sIssueA == ~0ull ? ~0ull : sIssueA + (tid - aBegin), limit, passHint, st.w == 0);
 
     // ---- compaction: shadow queue entries, slots freed by the shade step ----------------------
     const unsigned mShadow = __ballot_sync(0xffffffffu, sh.cast), mB = __ballot_sync(0xffffffffu, needB);
@@ -776,17 +785,17 @@ template <int INTEGRATOR>
 __global__ void __launch_bounds__(128) k_finishTail(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= pool.capacity) return;
-    uint4 meta = pool.meta[slot];
-    if (!(meta.z & (kFlagAlive | kFlagHasSample))) return;
+    const uint4 st = pool.state[slot];
+    if (!(st.w & (kFlagAlive | kFlagHasSample))) return;
+    const uint4 info = pool.info[slot];
     const float4 th = pool.thr[slot], ra = pool.rad[slot];
     V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
-    uint32_t flags = meta.z;
+    uint32_t flags = st.w;
     unsigned closest = 0, shadows = 0;
     if (flags & kFlagAlive) {
         const float4 ro = pool.rayO[slot], rd = pool.rayD[slot];
-        const ulonglong2 rs = pool.rng[slot];
         Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
-        Pcg32 rng; rng.state = rs.x; rng.inc = rs.y;
+        Pcg32 rng = unpackRng(st);
         float bsdfPdf = th.w, eta = ra.w;
         for (;;) {
             float t, u, v;
@@ -804,17 +813,17 @@ __global__ void __launch_bounds__(128) k_finishTail(DeviceScene sc, Pool pool, R
     }
     const V3 finL = (flags & kFlagMulT) ? T * L : L;
     const float2 ps = pool.pos[slot];
-    const bool late = !rp.listPixel && meta.y - rp.sampleFirst < c->completedPasses * rp.K;
+    const bool late = !rp.listPixel && info.y - rp.sampleFirst < c->completedPasses * rp.K;
     if (late) {
         splatDirect(sc, rp, c, ps, finL);
         atomicAdd(&c->lateSamples, 1u);
     } else {
-        const size_t r = (size_t) (meta.z >> 24) * rp.passSlots + meta.w;
+        const size_t r = (size_t) (st.w >> 24) * rp.passSlots + info.z;
         rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
         rp.recB[r] = finL.z;
-        if (!rp.listPixel) atomicAdd(rp.tileDone + meta.x, 1u);
+        if (!rp.listPixel) atomicAdd(rp.tileDone + info.x, 1u);
     }
-    pool.meta[slot] = make_uint4(0, 0, 0, 0);
+    pool.state[slot] = make_uint4(0, 0, 0, 0);
     atomicAdd(&c->finished, 1ull);
     if (closest) { atomicAdd(&c->closestRays, (unsigned long long) closest); atomicAdd(&c->segments, (unsigned long long) closest); }
     if (shadows) atomicAdd(&c->shadowRays, (unsigned long long) shadows);
@@ -840,7 +849,7 @@ int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParam
 __global__ void k_compactScan(Pool pool, uint32_t newCap, Counters *c) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t *freeList = reinterpret_cast<uint32_t *>(pool.shadow), *liveList = freeList + pool.capacity;
-    const bool occupied = i < pool.capacity && (pool.meta[i].z & (kFlagAlive | kFlagHasSample));
+    const bool occupied = i < pool.capacity && (pool.state[i].w & (kFlagAlive | kFlagHasSample));
     const bool isFree = i < newCap && !occupied, isLive = i >= newCap && occupied;
     const uint32_t qf = warpAppend(&c->compactCount[0], isFree), ql = warpAppend(&c->compactCount[1], isLive);
     if (isFree) freeList[qf] = i;
@@ -853,8 +862,8 @@ __global__ void k_compactMove(Pool pool, Counters *c) {
     const uint32_t *freeList = reinterpret_cast<const uint32_t *>(pool.shadow), *liveList = freeList + pool.capacity;
     const uint32_t src = liveList[k], dst = freeList[k];
     pool.rayO[dst] = pool.rayO[src]; pool.rayD[dst] = pool.rayD[src]; pool.thr[dst] = pool.thr[src]; pool.rad[dst] = pool.rad[src];
-    pool.rng[dst] = pool.rng[src]; pool.pos[dst] = pool.pos[src]; pool.meta[dst] = pool.meta[src];
-    pool.meta[src] = make_uint4(0, 0, 0, 0);
+    pool.info[dst] = pool.info[src]; pool.pos[dst] = pool.pos[src]; pool.state[dst] = pool.state[src];
+    pool.state[src] = make_uint4(0, 0, 0, 0);
 }
 int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *c, cudaStream_t st) {
     cudaMemsetAsync(&c->compactCount[0], 0, 2 * sizeof(unsigned int), st);
@@ -865,7 +874,7 @@ int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *c, cudaS
 
 __global__ void k_poolInit(Pool pool, Counters *c) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    pool.meta[i] = make_uint4(0, 0, 0, 0);
+    pool.state[i] = make_uint4(0, 0, 0, 0);
     if (i == 0) {                                   // what k_prepare would have left: the first splat pass runs before it
         c->forcePass = 0xffffffffu;
         for (int s = 0; s < kMaxRing; ++s) c->slotPass[s] = (unsigned) s;
