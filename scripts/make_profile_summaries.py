@@ -25,11 +25,13 @@ def launches():
         if r["Metric Name"] != "gpu__time_duration.sum": continue
         v = float(r["Metric Value"].replace(",", ""))
         v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(r["Metric Unit"], 1.0)
+        if "at::" in r["Kernel Name"]: continue            # bench.py's L2 flush (torch), not a kernel of this library
         a = agg.setdefault(short(r["Kernel Name"]), [0, 0.0]); a[0] += 1; a[1] += v
     tot = sum(a[1] for a in agg.values())
     out = ["# %s: launch list of `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu`" % tag, "",
-           "`ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 600` (steady state of the",
-           "wavefront loop; times are cold-cache and serialised, so read the SHARES). Raw list: `%s_launches.csv`." % tag, "",
+           "`ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 400` (steady state of the wavefront",
+           "loop, the tail of one frame and the start of the next; 8 Mi path slots; times are cold-cache and serialised,",
+           "so read the SHARES). Raw list: `%s_launches.csv`." % tag, "",
            "| kernel | launches | total us | avg us | share |", "|---|---:|---:|---:|---:|"]
     for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
         out.append("| `%s` | %d | %.1f | %.1f | %.1f %% |" % (k, n, t, t / n, 100 * t / tot))
@@ -57,7 +59,7 @@ def kernels():
     per = collections.OrderedDict()
     for d in data: per.setdefault(short(d[ix["Kernel Name"]]), []).append(d)
     md = ["# %s: `ncu --set full` counters (per launch, averaged over the captured launches)" % tag, "",
-          "Command: `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu`, `-s 120 -c 8`, cbox path_mis.", ""]
+          "Command: `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu`, `-s 60 -c 8`, cbox path_mis, 8 Mi path slots", "(about 5.4 M live rays per launch).", ""]
     names = list(per)
     md += ["| counter | " + " | ".join("`%s`" % n for n in names) + " |", "|---|" + "---:|" * len(names)]
     table = {}
@@ -78,7 +80,7 @@ def kernels():
         v = table[key][n]; unit = u[ix[key]].lower()
         return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(unit, 1)
     traffic = {"source": "profiles/%s_kernels.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)" % tag,
-               "workload": "cbox path_mis 800x600, 2 Mi path slots, steady state"}
+               "workload": "cbox path_mis 800x600, 8 Mi path slots, steady state (about 5.4 M live rays per launch)"}
     for n in names:
         traffic[n + "_dram_bytes_per_launch"] = to_bytes("dram__bytes_read.sum", n) + to_bytes("dram__bytes_write.sum", n)
     json.dump(traffic, open(os.path.join(PR, "traffic.json"), "w"), indent=1)
