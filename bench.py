@@ -300,7 +300,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--spp", type=int, default=1024)
-    ap.add_argument("--ref-spp", type=int, default=16, help="spp of the bounded CPU sample")
+    ap.add_argument("--ref-spp", type=int, default=96, help="spp of the bounded CPU sample")
     ap.add_argument("--pool", type=int, default=0)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
