@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnori_b200.so")
 SOURCES = ["capi.cu", "render.cu", "operators.cu", "bvh.cu"]
-HEADERS = ["engine.h", "bvh.h", "nmath.cuh", "scene.cuh", "traverse.cuh", "traverse_persistent.cuh", os.path.join("..", "..", "include", "nori_gpu.h")]
+HEADERS = ["engine.h", "bvh.h", "check.cuh", "nmath.cuh", "scene.cuh", "traverse.cuh", "traverse_persistent.cuh", os.path.join("..", "..", "include", "nori_gpu.h")]
 # -fmad=false: the arithmetic order written in nmath.cuh is the order executed (bit parity with
 # the x86-64 reference build, which has no FMA). Division and sqrt stay IEEE (nvcc defaults).
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
@@ -36,8 +36,15 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    objdir = os.path.join(HERE, "build")
+LIB_CHECKED = os.path.join(HERE, "libnori_b200_checked.so")
+
+
+def build(force: bool = False, verbose: bool = False, checked: bool = False) -> str:
+    """checked=True: the same sources with -DNORI_GPU_CHECKED (csrc/check.cuh: every pool / record / queue /
+    frame index range-checked on the device) -> libnori_b200_checked.so, loaded when NORI_GPU_LIB names it."""
+    objdir = os.path.join(HERE, "build_checked" if checked else "build")
+    lib = LIB_CHECKED if checked else LIB
+    flags = NVCC_FLAGS + (["-DNORI_GPU_CHECKED"] if checked else [])
     os.makedirs(objdir, exist_ok=True)
     hdrs = [os.path.join(CSRC, h) for h in HEADERS]
     objs, procs = [], []
@@ -45,7 +52,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         src, obj = os.path.join(CSRC, s), os.path.join(objdir, s.replace(".cu", ".o"))
         objs.append(obj)
         if force or _stale(obj, [src] + hdrs):
-            cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+            cmd = [_nvcc()] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
             procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for s, p in procs:
@@ -55,9 +62,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed building libnori_b200.so")
-    if force or procs or _stale(LIB, objs):
-        subprocess.check_call([_nvcc(), "-shared", "-o", LIB] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"])
-    return LIB
+    if force or procs or _stale(lib, objs):
+        subprocess.check_call([_nvcc(), "-shared", "-o", lib] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"])
+    return lib
 
 
 HOST = os.path.join(HERE, "host")
@@ -99,5 +106,7 @@ def build_host(force: bool = False, verbose: bool = False) -> str:
 if __name__ == "__main__":
     force, verbose = "--force" in sys.argv, "-v" in sys.argv
     print(build(force=force, verbose=verbose))
+    if "--checked" in sys.argv or os.environ.get("NORI_GPU_CHECKED"):
+        print(build(force=force, verbose=verbose, checked=True))
     print(build_host(force=force, verbose=verbose))
 

@@ -39,6 +39,16 @@ struct nori_gpu_ctx {
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + " failed: " + cudaGetErrorString(e_); return NORI_GPU_ECUDA; } } while (0)
 #define REQUIRE(cond, msg) do { if (!(cond)) { ctx->err = (msg); return NORI_GPU_EINVAL; } } while (0)
 
+/// Checked build only (csrc/check.cuh): turns range-check violations counted by the kernels into an error.
+static int reportChecks(nori_gpu_ctx *ctx, const char *what) {
+    unsigned lineR = 0, lineO = 0;
+    const unsigned nR = renderChecks(&lineR), nO = operatorChecks(&lineO);
+    if (!nR && !nO) return NORI_GPU_OK;
+    ctx->err = std::string(what) + ": device range check failed (" + std::to_string(nR) + " at render.cu/traverse:" + std::to_string(lineR) +
+               ", " + std::to_string(nO) + " at operators.cu/traverse:" + std::to_string(lineO) + ")";
+    return NORI_GPU_ECUDA;
+}
+
 namespace {
 
 template <class T> struct DevBuf {          // scoped device scratch
@@ -336,7 +346,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         CK(cudaMalloc((void **) &ctx->tileDone, tdNeed * sizeof(uint32_t))); CK(cudaMalloc((void **) &ctx->tileGen, tdNeed * sizeof(uint32_t)));
         ctx->tileDoneCap = tdNeed;
     }
-    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.readyTiles = ctx->readyTiles; rp.poolCapacity = pool.capacity;
+    rp.recA = ctx->recA; rp.recB = ctx->recB; rp.tileDone = ctx->tileDone; rp.tileGen = ctx->tileGen; rp.tileArrive = ctx->tileArrive; rp.readyTiles = ctx->readyTiles; rp.poolCapacity = pool.capacity; rp.recCount = recNeed;
     CK(cudaMemsetAsync(ctx->tileDone, 0, tdNeed * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(ctx->tileGen, 0, tdNeed * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(ctx->tileArrive, 0, tdNeed * sizeof(uint32_t), st));
@@ -397,6 +407,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     CK(cudaEventRecord(e1, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
+    if (int r = reportChecks(ctx, "render")) return r;
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(evCopy); for (auto &e : stage) cudaEventDestroy(e);
     if (out) {
@@ -507,6 +518,7 @@ int nori_gpu_trace(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint
     std::vector<float4> h(n);
     CK(cudaMemcpyAsync(h.data(), dh.p, (size_t) n * 16, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    if (int r = reportChecks(ctx, "trace")) return r;
     splitHits(h, ctx, n, tri_id, mesh_id, tuv);
     return NORI_GPU_OK;
 }
@@ -538,6 +550,7 @@ int nori_gpu_trace_count(nori_gpu_ctx *ctx, const float *rays, int n, int shadow
     unsigned long long h[2];
     CK(cudaMemcpyAsync(h, dc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    if (int r = reportChecks(ctx, "trace_count")) return r;
     counts[0] = h[0]; counts[1] = h[1];
     return NORI_GPU_OK;
 }
@@ -640,6 +653,7 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
     unsigned long long hd = 0;
     CK(cudaMemcpyAsync(rgbw, db.p, cells * 16, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(&hd, dd.p, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (int r = reportChecks(ctx, "splat")) return r;
     if (dropped) *dropped = hd;
     return NORI_GPU_OK;
 }

@@ -62,7 +62,7 @@ struct RenderParams {
     // explicit sample list (nori_gpu_sample_radiance)
     const uint32_t *listPixel, *listSample;
     // sample records of the passes in flight
-    float4 *recA; float *recB;
+    float4 *recA; float *recB; size_t recCount;   // ring * passSlots records
     uint32_t *tileDone;                      // ring x numTiles: finished samples of the pass held by the slot
     uint32_t *tileGen;                       // ring x numTiles: passes already splatted for this (slot, tile)
     uint32_t *readyTiles;                    // ring x numTiles: (slot * numTiles + tile) entries ready to splat
@@ -88,6 +88,10 @@ int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParam
 /// One wavefront iteration, enqueued on `st`. Returns the number of kernel launches.
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,
                      cudaEvent_t *stageEvents /* 4 or nullptr */);
+
+/// Checked build (check.cuh): violations counted by the kernels of render.cu / operators.cu since the last call.
+unsigned renderChecks(unsigned *line);
+unsigned operatorChecks(unsigned *line);
 
 // raw operators (operators.cu); all pointers are device pointers
 void launchTrace(const DeviceScene &sc, const float4 *rays /* 2 per ray */, int n, bool shadow, float4 *hits, unsigned int *cursor /* device scratch */, cudaStream_t st);

@@ -31,19 +31,21 @@ __global__ void __launch_bounds__(256) k_trace(DeviceScene sc, const float4 *__r
 
 /// The same operator on the renderer's traversal kernel (persistent warps, dynamic ray fetch).
 struct RayArrayIO {
-    const float4 *rays; float4 *hits;
+    const float4 *rays; float4 *hits; uint32_t n;
     __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        NG_CHECK(i < n);
         const float4 ro = __ldg(rays + 2 * (size_t) i), rd = __ldg(rays + 2 * (size_t) i + 1);
         o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float t, float u, float v) const {
+        NG_CHECK(i < n);
         hits[i] = gid == kNoHit ? make_float4(0.f, 0.f, 0.f, __uint_as_float(gid)) : make_float4(t, u, v, __uint_as_float(gid));
     }
 };
 template <bool SHADOW>
 __global__ void __launch_bounds__(128, 8) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
-    RayArrayIO io; io.rays = rays; io.hits = hits;
+    RayArrayIO io; io.rays = rays; io.hits = hits; io.n = (uint32_t) n;
     tracePersistent<SHADOW>(sc.nodes, sc.leafTris, (uint32_t) n, cursor, io);
 }
 
@@ -169,6 +171,7 @@ __global__ void k_splatList(DeviceScene sc, int n, const float2 *__restrict__ po
         float wy = sc.filter.table[(int) (fabsf((float) y - py) * lookup)];
         for (int x = x0; x <= x1; ++x) {
             float wx = sc.filter.table[(int) (fabsf((float) x - px) * lookup)];
+            NG_CHECK((int) (fabsf((float) y - py) * lookup) <= 32 && (int) (fabsf((float) x - px) * lookup) <= 32 && y < rows && x < cols);
             float *p = block + ((size_t) y * cols + x) * 4;
             atomicAdd(p, val.x * wx * wy); atomicAdd(p + 1, val.y * wx * wy); atomicAdd(p + 2, val.z * wx * wy); atomicAdd(p + 3, 1.0f * wx * wy);
         }
@@ -221,5 +224,7 @@ __global__ void k_toBitmap(const float4 *__restrict__ block, int W, int H, int b
 void launchToBitmap(const float *block, int W, int H, int border, float *rgb, cudaStream_t st) {
     k_toBitmap<<<gridFor(W * H), 256, 0, st>>>(reinterpret_cast<const float4 *>(block), W, H, border, rgb);
 }
+
+unsigned operatorChecks(unsigned *line) { return fetchChecks(line); }
 
 } // namespace ng

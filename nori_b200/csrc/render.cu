@@ -100,12 +100,14 @@ __device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Count
 struct ClosestIO {
     Pool pool;
     __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        NG_CHECK(i < pool.capacity);
         if (!(pool.state[i].w & kFlagAlive)) return false;
         const float4 ro = pool.rayO[i], rd = pool.rayD[i];
         o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float t, float u, float v) const {
+        NG_CHECK(i < pool.capacity);
         pool.hit[i] = make_float4(t, u, v, __uint_as_float(gid));
     }
 };
@@ -318,8 +320,9 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
 
 constexpr uint32_t kShadowToRecord = 0x80000000u;          // shadow-queue target is a sample record, not a path slot
 struct ShadowIO {
-    Pool pool; float4 *recA; float *recB;
+    Pool pool; float4 *recA; float *recB; size_t recCount;
     __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        NG_CHECK(i < pool.capacity);
         const float4 a = pool.shadow[3 * (size_t) i], b = pool.shadow[3 * (size_t) i + 1];
         o = mk(a.x, a.y, a.z); d = mk(b.x, b.y, b.z); mint = kEpsilon; maxt = a.w;
         return true;
@@ -333,11 +336,13 @@ struct ShadowIO {
         const uint32_t target = __float_as_uint(b.w);
         if (target & kShadowToRecord) {
             const size_t r = target & ~kShadowToRecord;
+            NG_CHECK(r < recCount);
             float4 a = recA[r];
             a.z = a.z + k.x; a.w = a.w + k.y;
             recA[r] = a;
             recB[r] = recB[r] + k.z;
         } else {
+            NG_CHECK(target < pool.capacity);
             float4 r = pool.rad[target];
             r.x = r.x + k.x; r.y = r.y + k.y; r.z = r.z + k.z;
             pool.rad[target] = r;
@@ -347,8 +352,8 @@ struct ShadowIO {
 
 /// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
 template <int MINB>
-__global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool pool, float4 *recA, float *recB, Counters *c, int fetchThreshold) {
-    ShadowIO io; io.pool = pool; io.recA = recA; io.recB = recB;
+__global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool pool, float4 *recA, float *recB, size_t recCount, Counters *c, int fetchThreshold) {
+    ShadowIO io; io.pool = pool; io.recA = recA; io.recB = recB; io.recCount = recCount;
     tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
 }
 
@@ -387,6 +392,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
         if (!wasEmpty) pool.state[dst] = make_uint4(0, 0, 0, 0);
         return;
     }
+    NG_CHECK(dst < pool.capacity && (rp.listPixel || (tileSlot < (uint32_t) rp.ring * rp.numTiles && rec < rp.passSlots)));
     Pcg32 rng;
     const uint32_t sampleIndex = rp.sampleFirst + sampleK;
     if (rp.streamMode == NORI_STREAM_PER_SAMPLE || rp.listPixel) {
@@ -460,6 +466,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
         sIssueA = (nA && *(volatile unsigned long long *) &c->issue < limit) ? atomicAdd(&c->issue, (unsigned long long) nA) : ~0ull;
     }
     __syncthreads();
+    NG_CHECK(sCnt[warp][key0] + rank < 256u);
     sPerm[sCnt[warp][key0] + rank] = (unsigned short) tid;
     __syncthreads();
     const uint32_t slot = blockBase + sPerm[tid];
@@ -519,6 +526,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
             atomicAdd(&c->lateSamples, 1u);
         } else {
             const size_t r = (size_t) (st.w >> 24) * rp.passSlots + info.z;
+            NG_CHECK(r < rp.recCount && (rp.listPixel || info.x < (uint32_t) rp.ring * rp.numTiles));
             rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
             rp.recB[r] = finL.z;
             counted = !rp.listPixel;
@@ -548,6 +556,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     }
     __syncthreads();
     if (sh.cast) {
+        NG_CHECK(sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()) < pool.capacity);
         float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()));
         e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
         e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(shadowTarget));
@@ -579,6 +588,7 @@ __global__ void k_splatPlan(DeviceScene sc, RenderParams rp, Counters *c) {
         }
     }
     const uint32_t q = warpAppend(&c->readyCount, ready);
+    NG_CHECK(!ready || q < (uint32_t) rp.ring * rp.numTiles);
     if (ready) rp.readyTiles[q] = ti;
 }
 
@@ -590,6 +600,7 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
     const uint32_t Z = min((uint32_t) kSplatSplit, rp.K);
     for (uint32_t work = blockIdx.x; work < c->readyCount * Z; work += gridDim.x) {
     const uint32_t tiq = rp.readyTiles[work / Z], z = work % Z;
+    NG_CHECK(tiq < (uint32_t) rp.ring * rp.numTiles);
     const uint32_t slot = tiq / rp.numTiles, tile = tiq - slot * rp.numTiles;
     const uint32_t pass = c->slotPass[slot];
     const int W = sc.cam.width, H = sc.cam.height, b = sc.filter.border;
@@ -611,6 +622,7 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
                 int lx, ly; tilePixel(pix, lx, ly);
                 if (lx >= tw || ly >= th) continue;
                 const size_t r = base + k * 1024u + pix;
+                NG_CHECK(r < rp.recCount);
                 const float4 a = rp.recA[r];
                 if (isnan(a.x)) continue;                                        // sample still in flight (forced close)
                 const V3 val = mk(a.z, a.w, rp.recB[r]);
@@ -624,6 +636,7 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
                     for (int x = x0; x <= x1; ++x) {
                         const float wx = sTable[(int) (fabsf((float) x - px) * lookup)];
                         const int cell = y * cols + x;
+                        NG_CHECK(cell >= 0 && cell < kSplatSide * kSplatSide && (int) (fabsf((float) x - px) * lookup) <= 32 && (int) (fabsf((float) y - py) * lookup) <= 32);
                         atomicAdd(&plane[0][cell], val.x * wx * wy);             // block.cpp:100-102
                         atomicAdd(&plane[1][cell], val.y * wx * wy);
                         atomicAdd(&plane[2][cell], val.z * wx * wy);
@@ -639,6 +652,7 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
             const int x = k % cols, y = k / cols;
             const float4 v = make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]);
             if (v.w == 0.f && v.x == 0.f && v.y == 0.f && v.z == 0.f) continue;
+            NG_CHECK(oy + y < rp.blockRows && ox + x < rp.blockCols);
             float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + y) * rp.blockCols + (ox + x);
             atomicAdd(dst, v);
         }
@@ -674,6 +688,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
     __shared__ unsigned sDropped;
     for (uint32_t work = blockIdx.x; work < c->readyCount * 4u; work += gridDim.x) {
     const uint32_t tiq = rp.readyTiles[work >> 2], z = work & 3u;
+    NG_CHECK(tiq < (uint32_t) rp.ring * rp.numTiles);
     const uint32_t slot = tiq / rp.numTiles, tile = tiq - slot * rp.numTiles;
     const uint32_t pass = c->slotPass[slot];
     const int W = sc.cam.width, H = sc.cam.height;
@@ -708,6 +723,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 #pragma unroll 2
             for (uint32_t k = 0; k < Kp; ++k) {
                 const size_t r = base + (size_t) k * 1024u;
+                NG_CHECK(r < rp.recCount);
                 const float4 a = rp.recA[r];
                 if (isnan(a.x)) continue;                                        // still in flight (forced close)
                 const V3 val = mk(a.z, a.w, rp.recB[r]);
@@ -739,6 +755,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 #pragma unroll
                 for (int j = 0; j < WN; ++j) {
                     const int cell = (ty + i) * SIDE + tx + j;
+                    NG_CHECK(cell >= 0 && cell < SIDE * SIDE);
                     if (acc[i][j][3] != 0.f) {
                         atomicAdd(&plane[0][cell], acc[i][j][0]); atomicAdd(&plane[1][cell], acc[i][j][1]);
                         atomicAdd(&plane[2][cell], acc[i][j][2]); atomicAdd(&plane[3][cell], acc[i][j][3]);
@@ -751,6 +768,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
             const float4 v = make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]);
             if (v.w == 0.f) continue;
             const int x = k % SIDE, y = k / SIDE;
+            NG_CHECK(oy + qy * Q + y < rp.blockRows && ox + qx * Q + x < rp.blockCols);
             float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + qy * Q + y) * rp.blockCols + (ox + qx * Q + x);
             atomicAdd(dst, v);
         }
@@ -819,6 +837,7 @@ __global__ void __launch_bounds__(128) k_finishTail(DeviceScene sc, Pool pool, R
         atomicAdd(&c->lateSamples, 1u);
     } else {
         const size_t r = (size_t) (st.w >> 24) * rp.passSlots + info.z;
+        NG_CHECK(r < rp.recCount && (rp.listPixel || info.x < (uint32_t) rp.ring * rp.numTiles));
         rp.recA[r] = make_float4(ps.x, ps.y, finL.x, finL.y);
         rp.recB[r] = finL.z;
         if (!rp.listPixel) atomicAdd(rp.tileDone + info.x, 1u);
@@ -852,6 +871,7 @@ __global__ void k_compactScan(Pool pool, uint32_t newCap, Counters *c) {
     const bool occupied = i < pool.capacity && (pool.state[i].w & (kFlagAlive | kFlagHasSample));
     const bool isFree = i < newCap && !occupied, isLive = i >= newCap && occupied;
     const uint32_t qf = warpAppend(&c->compactCount[0], isFree), ql = warpAppend(&c->compactCount[1], isLive);
+    NG_CHECK((!isFree || qf < pool.capacity) && (!isLive || ql < pool.capacity));
     if (isFree) freeList[qf] = i;
     if (isLive) liveList[ql] = i;
 }
@@ -860,7 +880,9 @@ __global__ void k_compactMove(Pool pool, Counters *c) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= c->compactCount[1]) return;
     const uint32_t *freeList = reinterpret_cast<const uint32_t *>(pool.shadow), *liveList = freeList + pool.capacity;
+    NG_CHECK(k < c->compactCount[0]);                 // a free slot below the new size for every path above it
     const uint32_t src = liveList[k], dst = freeList[k];
+    NG_CHECK(src < pool.capacity && dst < pool.capacity && (pool.state[src].w & (kFlagAlive | kFlagHasSample)) && !(pool.state[dst].w & (kFlagAlive | kFlagHasSample)));
     pool.rayO[dst] = pool.rayO[src]; pool.rayD[dst] = pool.rayD[src]; pool.thr[dst] = pool.thr[src]; pool.rad[dst] = pool.rad[src];
     pool.info[dst] = pool.info[src]; pool.pos[dst] = pool.pos[src]; pool.state[dst] = pool.state[src];
     pool.state[src] = make_uint4(0, 0, 0, 0);
@@ -963,13 +985,15 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     if (ev) cudaEventRecord(ev[2], st);
     if (rp.integrator != NORI_INT_NORMALS) {
         const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
-        if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
-        else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
-        else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, c, tune().fetchShadow);
+        if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         ++launches;
     }
     if (ev) cudaEventRecord(ev[3], st);
     return launches;
 }
+
+unsigned renderChecks(unsigned *line) { return fetchChecks(line); }
 
 } // namespace ng

@@ -17,6 +17,7 @@
 // only); the triangle test does not.
 #pragma once
 #include "scene.cuh"
+#include "check.cuh"
 
 namespace ng {
 
@@ -60,6 +61,7 @@ NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restric
             int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
             if (hl && hr) {
                 if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
+                NG_CHECK(sp < kStackSize);
                 stack[sp++] = cr;
                 cur = cl;
             } else if (hl) cur = cl;

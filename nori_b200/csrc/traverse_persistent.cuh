@@ -85,6 +85,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                     int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
                         if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
+                        NG_CHECK(sp < kStackSize);
                         stack[sp++] = cr;
                         cur = cl;
                     } else if (hl) cur = cl;

@@ -18,7 +18,8 @@ import numpy as np
 from .scene import FlatScene
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnori_b200.so")
+# NORI_GPU_LIB: another build of the SAME engine (the range-checked one, libnori_b200_checked.so); never a different implementation
+LIB_PATH = os.path.join(HERE, os.path.basename(os.environ.get("NORI_GPU_LIB", "libnori_b200.so")))
 
 EXPORTS = [
     "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",

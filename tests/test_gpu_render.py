@@ -156,3 +156,17 @@ def test_wide_filter_takes_the_generic_splat_kernel(own_engine, port):
     got, _ = own_engine.render(sample_first=0, sample_last=2)
     np.testing.assert_allclose(got[..., 3], want[..., 3], rtol=1e-5, atol=1e-6)
     assert rel_mse(to_bitmap(got, 3), to_bitmap(want, 3)) <= 2e-3
+
+
+@pytest.mark.gpu
+def test_range_checked_build_sees_no_violation():
+    """csrc/check.cuh: the engine compiled with -DNORI_GPU_CHECKED tests every pool / shadow-queue / record /
+    tile-counter / traversal-stack / frame index on the device and turns a violation into an error.
+    scripts/sanitize.py drives every kernel family with tiny pools (ring wrap, compaction, finish-tail)."""
+    import subprocess, sys
+    from nori_b200.build import build
+    build(checked=True)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, NORI_GPU_LIB="libnori_b200_checked.so")
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "sanitize.py"), "4"], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "sanitize pass complete" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
