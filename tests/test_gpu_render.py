@@ -163,7 +163,7 @@ def test_range_checked_build_sees_no_violation():
     """csrc/check.cuh: the engine compiled with -DNORI_GPU_CHECKED tests every pool / shadow-queue / record /
     tile-counter / traversal-stack / frame index on the device and turns a violation into an error.
     scripts/sanitize.py drives every kernel family with tiny pools (ring wrap, compaction, finish-tail)."""
-    import subprocess, sys
+    import os, subprocess, sys
     from nori_b200.build import build
     build(checked=True)
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
