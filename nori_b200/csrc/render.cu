@@ -431,10 +431,11 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
 template <int INTEGRATOR>
 __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
     constexpr int NK = kNumKeys + 1;
-    __shared__ unsigned sCnt[8][NK], sOff[NK + 1], sWarpShadow[8], sWarpRegen[8], sShadowBase;
+    static_assert(NK == 6, "the warp scan below covers 6 keys x 8 warps = 48 counts in two registers per lane");
+    __shared__ unsigned sCnt[8][NK], sWarpShadow[8], sWarpRegen[8], sShadowBase;
     __shared__ unsigned long long sIssueA, sIssueB;
-    __shared__ unsigned short sPerm[256];
-    const unsigned tid = threadIdx.x, warp = tid >> 5;
+    __shared__ unsigned short sPerm[256], sRegen[256];
+    const unsigned tid = threadIdx.x, warp = tid >> 5, lane = laneId();
     const uint32_t blockBase = blockIdx.x * blockDim.x;
     const unsigned long long limit = c->issueLimit;
     const uint32_t passHint = c->passHint, lateBelow = c->completedPasses * rp.K;   // samples of closed passes are late
@@ -450,27 +451,40 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     for (int k = 0; k < NK; ++k) {
         const unsigned m = __ballot_sync(0xffffffffu, key0 == k);
         if (key0 == k) rank = __popc(m & lanemaskLt());
-        if (laneId() == 0) sCnt[warp][k] = __popc(m);
+        if (lane == 0) sCnt[warp][k] = __popc(m);
     }
     __syncthreads();
-    if (tid == 0) {
-        unsigned acc = 0;
-        for (int k = 0; k < NK; ++k) {
-            sOff[k] = acc;
-            for (int w = 0; w < 8; ++w) { unsigned n = sCnt[w][k]; sCnt[w][k] = acc; acc += n; }
+    // Every warp scans the 48 (key-major, warp-minor) counts itself: entry i = key * 8 + warp sits in
+    // lane i & 31 of e0 (keys 0-3) or e1 (keys 4, 5). No serial section and no second barrier.
+    unsigned aBegin, alive;
+    {
+        const unsigned v0 = sCnt[lane & 7u][lane >> 3], v1 = lane < 16u ? sCnt[lane & 7u][4u + (lane >> 3)] : 0u;
+        unsigned s0 = v0, s1 = v1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned t0 = __shfl_up_sync(0xffffffffu, s0, d), t1 = __shfl_up_sync(0xffffffffu, s1, d);
+            if ((int) lane >= d) { s0 += t0; s1 += t1; }
         }
-        sOff[NK] = acc;
-        const unsigned alive = sOff[kNumKeys];
-        if (alive) atomicAdd(&c->sortCount[0], alive);       // closest rays traced = live slots
-        const unsigned nA = 256u - sOff[kKeyMiss];
-        sIssueA = (nA && *(volatile unsigned long long *) &c->issue < limit) ? atomicAdd(&c->issue, (unsigned long long) nA) : ~0ull;
+        s1 += __shfl_sync(0xffffffffu, s0, 31);
+        const unsigned e0 = s0 - v0, e1 = s1 - v1;                 // exclusive prefixes
+        const int i = key0 * 8 + (int) warp;
+        const unsigned x0 = __shfl_sync(0xffffffffu, e0, i & 31), x1 = __shfl_sync(0xffffffffu, e1, i & 31);
+        aBegin = __shfl_sync(0xffffffffu, e1, 0);                  // first slot of key kKeyMiss
+        alive = __shfl_sync(0xffffffffu, e1, 8);                   // first slot of key kNumKeys = live paths of this CTA
+        const unsigned dst = (i < 32 ? x0 : x1) + rank;
+        NG_CHECK(dst < 256u);
+        sPerm[dst] = (unsigned short) tid;
     }
+    // Sample indices for the slots known free up front: requested now, consumed after the shade step,
+    // so that the round trip of the atomic hides behind it. (Indices past the limit are discarded by
+    // regenSlot and handed out again: k_prepare clamps the counter.)
+    // The last thread of the CTA is one of those free slots whenever there is any (they sort to the end).
+    const unsigned nA = 256u - aBegin;
+    if (tid == 0 && alive) atomicAdd(&c->sortCount[0], alive);   // closest rays traced = live slots
+    if (tid == 255u && nA) sIssueA = atomicAdd(&c->issue, (unsigned long long) nA);
     __syncthreads();
-    NG_CHECK(sCnt[warp][key0] + rank < 256u);
-    sPerm[sCnt[warp][key0] + rank] = (unsigned short) tid;
-    __syncthreads();
-    const uint32_t slot = blockBase + sPerm[tid];
-    const unsigned aBegin = sOff[kKeyMiss];
+    const unsigned local = sPerm[tid];
+    const uint32_t slot = blockBase + local;
 
     ShadowOut sh; sh.cast = false;
     uint32_t shadowTarget = slot;
@@ -508,13 +522,16 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
                 pool.state[slot] = packState(rng, (flags & ~kFlagAlive) | kFlagHasSample);
             }
         }
-    } else if (st.w & (kFlagAlive | kFlagHasSample)) {
-        info = pool.info[slot];
-        // ---- ray escaped (Li returns what the path gathered) or a parked sample -----------------
-        const float4 ra = pool.rad[slot];
-        finL = mk(ra.x, ra.y, ra.z);
-        if (st.w & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
-        fin = true;
+    } else {
+        sRegen[tid - aBegin] = (unsigned short) (local | (st.w == 0 ? 0x8000u : 0u));   // free slot: regenerated below
+        if (st.w & (kFlagAlive | kFlagHasSample)) {
+            info = pool.info[slot];
+            // ---- ray escaped (Li returns what the path gathered) or a parked sample -----------------
+            const float4 ra = pool.rad[slot];
+            finL = mk(ra.x, ra.y, ra.z);
+            if (st.w & kFlagMulT) { const float4 t = pool.thr[slot]; finL = mk(t.x, t.y, t.z) * finL; }
+            fin = true;
+        }
     }
     // ---- record the camera samples that ended (src/main.cpp:59-62 -> block.put) ---------------
     bool counted = false;
@@ -535,34 +552,41 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     if (__any_sync(0xffffffffu, counted)) {       // one atomic per (ring slot, tile) present in the warp
         const uint32_t tile = counted ? info.x : 0xffffffffu;
         const unsigned peers = __match_any_sync(0xffffffffu, tile);
-        if (counted && (int) laneId() == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
+        if (counted && (int) lane == __ffs(peers) - 1) atomicAdd(rp.tileDone + tile, (unsigned) __popc(peers));
     }
-    // ---- free slots known up front draw their next sample while other warps still shade ------
-    if (tid >= aBegin) regenSlot(sc, pool, rp, slot, sIssueA == ~0ull ? ~0ull : sIssueA + (tid - aBegin), limit, passHint, st.w == 0);
 
     // ---- compaction: shadow queue entries, slots freed by the shade step ----------------------
     const unsigned mShadow = __ballot_sync(0xffffffffu, sh.cast), mB = __ballot_sync(0xffffffffu, needB);
-    if (laneId() == 0) { sWarpShadow[warp] = __popc(mShadow); sWarpRegen[warp] = __popc(mB); }
+    if (lane == 0) { sWarpShadow[warp] = __popc(mShadow); sWarpRegen[warp] = __popc(mB); }
     const int nfin = __syncthreads_count(fin);
+    unsigned preS = 0, preR = 0, totS = 0, totR = 0;
+#pragma unroll
+    for (unsigned w = 0; w < 8; ++w) {
+        const unsigned a = sWarpShadow[w], b = sWarpRegen[w];
+        if (w < warp) { preS += a; preR += b; }
+        totS += a; totR += b;
+    }
     if (tid == 0) {
-        unsigned accS = 0, accR = 0;
-        for (int w = 0; w < 8; ++w) {
-            unsigned n = sWarpShadow[w]; sWarpShadow[w] = accS; accS += n;
-            n = sWarpRegen[w]; sWarpRegen[w] = accR; accR += n;
-        }
-        sShadowBase = accS ? atomicAdd(&c->shadowCount, accS) : 0u;
-        sIssueB = (accR && *(volatile unsigned long long *) &c->issue < limit) ? atomicAdd(&c->issue, (unsigned long long) accR) : ~0ull;
+        sShadowBase = totS ? atomicAdd(&c->shadowCount, totS) : 0u;
+        sIssueB = totR ? atomicAdd(&c->issue, (unsigned long long) totR) : ~0ull;
         if (nfin) atomicAdd(&c->finished, (unsigned long long) nfin);
     }
+    if (needB) sRegen[nA + preR + __popc(mB & lanemaskLt())] = (unsigned short) local;
     __syncthreads();
     if (sh.cast) {
-        NG_CHECK(sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()) < pool.capacity);
-        float4 *e = pool.shadow + 3 * (size_t) (sShadowBase + sWarpShadow[warp] + __popc(mShadow & lanemaskLt()));
+        const uint32_t q = sShadowBase + preS + __popc(mShadow & lanemaskLt());
+        NG_CHECK(q < pool.capacity);
+        float4 *e = pool.shadow + 3 * (size_t) q;
         e[0] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.maxt);
         e[1] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(shadowTarget));
         e[2] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, 0.f);
     }
-    if (needB) regenSlot(sc, pool, rp, slot, sIssueB == ~0ull ? ~0ull : sIssueB + sWarpRegen[warp] + __popc(mB & lanemaskLt()), limit, passHint, false);
+    // ---- every free slot of the CTA draws its next camera sample: one dense list, full warps ----
+    if (tid < nA + totR) {
+        const unsigned e = sRegen[tid];
+        const unsigned long long g = tid < nA ? sIssueA + tid : (sIssueB == ~0ull ? ~0ull : sIssueB + (tid - nA));
+        regenSlot(sc, pool, rp, blockBase + (e & 0x7fffu), g, limit, passHint, (e & 0x8000u) != 0u);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
