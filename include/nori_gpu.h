@@ -51,7 +51,9 @@ enum {
  *        any partitioning of the work over GPUs. */
 enum { NORI_STREAM_BLOCK = 0, NORI_STREAM_PER_SAMPLE = 1 };
 
-/* Ray-triangle test: REFERENCE_MT reproduces src/mesh.cpp:51-88 operation for operation. */
+/* Ray-triangle test: REFERENCE_MT reproduces src/mesh.cpp:51-88 operation for operation (the parity mode).
+ * WATERTIGHT: Woop/Benthin/Wald 2013 — a ray never slips between two triangles sharing an edge or a
+ * vertex (Moeller-Trumbore can); not in the reference, specified by oracle/noracle_math.h. */
 enum { NORI_ISECT_REFERENCE_MT = 0, NORI_ISECT_WATERTIGHT = 1 };
 
 /* One Mesh (include/nori/mesh.h:172-175): column-major Eigen buffers == C arrays below. */
@@ -133,6 +135,9 @@ int nori_gpu_block_device_ptr(nori_gpu_ctx *ctx, void **dptr, uint64_t *n_floats
 int nori_gpu_block_dims(const nori_gpu_ctx *ctx, int *rows, int *cols, int *border);
 int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on);   /* per-stage CUDA-event timing (serialises stages) */
 int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n_paths);
+/* Mesh::rayIntersect variant (src/mesh.cpp:51-88) used by the raw operators below (trace, trace_device,
+ * trace_count, intersect): NORI_ISECT_*. nori_gpu_render takes it from NoriGpuRenderDesc::intersect_mode. */
+int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode);
 
 /* ---- raw operators (parity and Mrays/s) ----------------------------------------------------- */
 /* Accel::rayIntersect (src/accel.cpp:35-55). rays: n x 8 [o.xyz, mint, d.xyz, maxt] (HOST memory).

@@ -34,6 +34,7 @@ struct nori_gpu_ctx {
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
+    int isectMode = NORI_ISECT_REFERENCE_MT;   // used by the raw operators; nori_gpu_render takes it from its descriptor
 };
 
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + " failed: " + cudaGetErrorString(e_); return NORI_GPU_ECUDA; } } while (0)
@@ -65,7 +66,7 @@ DeviceScene deviceScene(const nori_gpu_ctx *c) {
     s.nMeshes = (int) c->meshes.size(); s.nEmitters = (int) c->emitters.size();
     s.nTris = c->nTris; s.nVerts = c->nVerts;
     s.nodes = c->bvh.nodes; s.leafTris = c->bvh.leafTris; s.nNodes = c->bvh.nNodes;
-    s.cam = c->cam; s.filter = c->filter;
+    s.cam = c->cam; s.filter = c->filter; s.isectMode = c->isectMode;
     return s;
 }
 
@@ -295,7 +296,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     REQUIRE(d->integrator >= NORI_INT_NORMALS && d->integrator <= NORI_INT_AO, "render: unknown integrator");
     REQUIRE(list || d->sample_last > d->sample_first, "render: empty sample range");
     REQUIRE(list || d->sample_last <= 0x7fffffffu, "render: sample indices must stay below 2^31 (pcg32 stream ids are kept in 32 bits)");
-    if (d->intersect_mode != NORI_ISECT_REFERENCE_MT) { ctx->err = "render: only NORI_ISECT_REFERENCE_MT is implemented"; return NORI_GPU_EUNSUPPORTED; }
+    REQUIRE(d->intersect_mode == NORI_ISECT_REFERENCE_MT || d->intersect_mode == NORI_ISECT_WATERTIGHT, "render: unknown intersect_mode");
     if (!list && d->stream_mode == NORI_STREAM_BLOCK && d->integrator != NORI_INT_NORMALS && d->integrator != NORI_INT_SIMPLE) {
         ctx->err = "render: NORI_STREAM_BLOCK (one serial PCG32 stream per block) is only reproducible for integrators that draw no random numbers (normals, simple)";
         return NORI_GPU_EUNSUPPORTED;
@@ -355,7 +356,8 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     enqueuePoolInit(pool, ctx->d_counters, st);
     if (d->clear && !list) CK(cudaMemsetAsync(ctx->d_block, 0, ctx->blockFloats * sizeof(float), st));
 
-    const DeviceScene sc = deviceScene(ctx);
+    DeviceScene sc = deviceScene(ctx);
+    sc.isectMode = d->intersect_mode;
     // Stage events (profiling): 4 per iteration of a batch, read back after the batch's one
     // synchronisation, so that profiling does not change how the kernels are queued.
     const int batch = 8;
@@ -446,6 +448,13 @@ int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, i
         rgb[3 * i] = a[i].z; rgb[3 * i + 1] = a[i].w; rgb[3 * i + 2] = b[i];
         if (pos) { pos[2 * i] = a[i].x; pos[2 * i + 1] = a[i].y; }
     }
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(mode == NORI_ISECT_REFERENCE_MT || mode == NORI_ISECT_WATERTIGHT, "set_intersect_mode: unknown mode");
+    ctx->isectMode = mode;
     return NORI_GPU_OK;
 }
 

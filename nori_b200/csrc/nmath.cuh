@@ -166,6 +166,48 @@ NG_HD bool rayTriangle(V3 p0, V3 p1, V3 p2, V3 o, V3 d, float mint, float maxt, 
     return t >= mint && t <= maxt;
 }
 
+/// NORI_ISECT_WATERTIGHT: the watertight test of Woop, Benthin, Wald (JCGT 2(1), 2013) — the reference
+/// only has Moeller-Trumbore, which lets a ray slip between two triangles sharing an edge. Statement for
+/// statement oracle/noracle_math.h:rayTriangleWatertight (no FMA contraction: -fmad=false), so the
+/// edge functions of a shared edge are exact negations of each other on its two triangles.
+/// Same hit convention as rayTriangle: u = weight of p1, v = weight of p2, mint <= t <= maxt.
+struct WtRay { int kx, ky, kz; float Sx, Sy, Sz; };
+NG_HD float comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+NG_HD WtRay wtSetup(V3 d) {
+    WtRay w;
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    w.kz = ax > ay ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    w.kx = w.kz + 1; if (w.kx == 3) w.kx = 0;
+    w.ky = w.kx + 1; if (w.ky == 3) w.ky = 0;
+    if (comp(d, w.kz) < 0.0f) { const int tmp = w.kx; w.kx = w.ky; w.ky = tmp; }
+    const float dz = comp(d, w.kz);
+    w.Sx = comp(d, w.kx) / dz; w.Sy = comp(d, w.ky) / dz; w.Sz = 1.0f / dz;
+    return w;
+}
+NG_HD bool rayTriangleWatertight(V3 p0, V3 p1, V3 p2, V3 o, const WtRay &w, float mint, float maxt, float &u, float &v, float &t) {
+    const V3 A = p0 - o, B = p1 - o, C = p2 - o;
+    const float Akz = comp(A, w.kz), Bkz = comp(B, w.kz), Ckz = comp(C, w.kz);
+    const float Ax = comp(A, w.kx) - w.Sx * Akz, Ay = comp(A, w.ky) - w.Sy * Akz;
+    const float Bx = comp(B, w.kx) - w.Sx * Bkz, By = comp(B, w.ky) - w.Sy * Bkz;
+    const float Cx = comp(C, w.kx) - w.Sx * Ckz, Cy = comp(C, w.ky) - w.Sy * Ckz;
+    float U = Cx * By - Cy * Bx, V = Ax * Cy - Ay * Cx, W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        U = (float) ((double) Cx * (double) By - (double) Cy * (double) Bx);
+        V = (float) ((double) Ax * (double) Cy - (double) Ay * (double) Cx);
+        W = (float) ((double) Bx * (double) Ay - (double) By * (double) Ax);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+    const float det = (U + V) + W;
+    if (det == 0.0f) return false;
+    const float Az = w.Sz * Akz, Bz = w.Sz * Bkz, Cz = w.Sz * Ckz;
+    const float T = (U * Az + V * Bz) + W * Cz;
+    const float rcpDet = 1.0f / det;
+    t = T * rcpDet;
+    if (!(t >= mint && t <= maxt)) return false;
+    u = V * rcpDet; v = W * rcpDet;
+    return true;
+}
+
 // ---- warps (include/nori/warp.h:30-69; the reference's src/warp.cpp:33-79 throws: course spec) -
 NG_HD float tent1(float xi) { return xi < 0.5f ? sqrtf(2.0f * xi) - 1.0f : 1.0f - sqrtf(2.0f - 2.0f * xi); }
 NG_HD V2 squareToTent(V2 s) { V2 r; r.x = tent1(s.x); r.y = tent1(s.y); return r; }

@@ -18,7 +18,7 @@ __global__ void __launch_bounds__(256) k_trace(DeviceScene sc, const float4 *__r
     if (i < n) {
         const float4 ro = __ldg(rays + 2 * (size_t) i), rd = __ldg(rays + 2 * (size_t) i + 1);
         float t = 0.f, u = 0.f, v = 0.f;
-        uint32_t gid = traverse<SHADOW, COUNT>(sc.nodes, sc.leafTris, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), ro.w, rd.w, t, u, v, &ts);
+        uint32_t gid = traverse<SHADOW, COUNT>(sc.nodes, sc.leafTris, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), ro.w, rd.w, t, u, v, &ts, sc.isectMode == NORI_ISECT_WATERTIGHT);
         if (gid == kNoHit) { t = 0.f; u = 0.f; v = 0.f; }
         hits[i] = make_float4(t, u, v, __uint_as_float(gid));
     }
@@ -43,10 +43,10 @@ struct RayArrayIO {
         hits[i] = gid == kNoHit ? make_float4(0.f, 0.f, 0.f, __uint_as_float(gid)) : make_float4(t, u, v, __uint_as_float(gid));
     }
 };
-template <bool SHADOW>
+template <bool SHADOW, bool WT>
 __global__ void __launch_bounds__(128, 8) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
     RayArrayIO io; io.rays = rays; io.hits = hits; io.n = (uint32_t) n;
-    tracePersistent<SHADOW>(sc.nodes, sc.leafTris, (uint32_t) n, cursor, io);
+    tracePersistent<SHADOW, WT>(sc.nodes, sc.leafTris, (uint32_t) n, cursor, io);
 }
 
 void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned int *cursor, cudaStream_t st) {
@@ -54,8 +54,9 @@ void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, 
     static unsigned grid = 0;
     if (!grid) { int dev = 0, sms = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); grid = (unsigned) sms * 8u; }
     cudaMemsetAsync(cursor, 0, sizeof(unsigned int), st);
-    if (shadow) k_tracePersistent<true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
-    else k_tracePersistent<false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
+    const bool wt = sc.isectMode == NORI_ISECT_WATERTIGHT;
+    if (shadow) { if (wt) k_tracePersistent<true, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); else k_tracePersistent<true, false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); }
+    else { if (wt) k_tracePersistent<false, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); else k_tracePersistent<false, false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); }
 }
 void launchTraceCount(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned long long *counts2, cudaStream_t st) {
     if (n <= 0) return;
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__(256) k_intersect(DeviceScene sc, const float4 
     if (i >= n) return;
     const float4 ro = __ldg(rays + 2 * (size_t) i), rd = __ldg(rays + 2 * (size_t) i + 1);
     float t, u, v;
-    uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), ro.w, rd.w, t, u, v);
+    uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), ro.w, rd.w, t, u, v, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT);
     float *o = out + 24 * (size_t) i;
     valid[i] = gid != kNoHit;
     if (gid == kNoHit) { for (int k = 0; k < 24; ++k) o[k] = 0.f; return; }

@@ -113,10 +113,10 @@ struct ClosestIO {
 };
 
 /// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
-template <int MINB>
+template <int MINB, bool WT = false>
 __global__ void __launch_bounds__(128, MINB) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ClosestIO io; io.pool = pool;
-    tracePersistent<false>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold);
+    tracePersistent<false, WT>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -351,10 +351,10 @@ struct ShadowIO {
 };
 
 /// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
-template <int MINB>
+template <int MINB, bool WT = false>
 __global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool pool, float4 *recA, float *recB, size_t recCount, Counters *c, int fetchThreshold) {
     ShadowIO io; io.pool = pool; io.recA = recA; io.recB = recB; io.recCount = recCount;
-    tracePersistent<true>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
+    tracePersistent<true, WT>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
 }
 
 /// Hands path slot `dst` to camera sample index g of the issue order (pass, tile, sample, pixel):
@@ -841,14 +841,14 @@ __global__ void __launch_bounds__(128) k_finishTail(DeviceScene sc, Pool pool, R
         float bsdfPdf = th.w, eta = ra.w;
         for (;;) {
             float t, u, v;
-            const uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, ray.o, ray.d, ray.mint, ray.maxt, t, u, v);
+            const uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, ray.o, ray.d, ray.mint, ray.maxt, t, u, v, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT);
             ++closest;
             ShadowOut sh;
             const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh);
             if (sh.cast) {
                 float st, su, sv;
                 ++shadows;
-                if (traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv) == kNoHit) L = L + sh.contrib;
+                if (traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT) == kNoHit) L = L + sh.contrib;
             }
             if (!cont) break;
         }
@@ -986,9 +986,10 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         ++launches;
     }
     {
-        const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const unsigned b = sc.isectMode == NORI_ISECT_WATERTIGHT ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
         const bool overlap = splat && tune().overlapSplat;
-        if (b == 10) launchOverlapped(k_traceClosest<10>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        if (sc.isectMode == NORI_ISECT_WATERTIGHT) launchOverlapped(k_traceClosest<8, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (b == 10) launchOverlapped(k_traceClosest<10>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 12) launchOverlapped(k_traceClosest<12>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else launchOverlapped(k_traceClosest<8>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         ++launches;
@@ -1008,8 +1009,9 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     ++launches;
     if (ev) cudaEventRecord(ev[2], st);
     if (rp.integrator != NORI_INT_NORMALS) {
-        const unsigned b = tune().ctasPerSm, g = persistentGrid() * b / 8u;
-        if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        const unsigned b = sc.isectMode == NORI_ISECT_WATERTIGHT ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        if (sc.isectMode == NORI_ISECT_WATERTIGHT) k_traceShadow<8, true><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         ++launches;

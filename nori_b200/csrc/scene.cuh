@@ -56,6 +56,7 @@ struct DeviceScene {
     const float4 *nodes;         // 4 x float4 per node
     const float4 *leafTris;      // 3 x float4 per triangle slot: (p0, gid) (p1, -) (p2, -)
     uint32_t nNodes;
+    int isectMode;               // NORI_ISECT_*: ray-triangle test used by every traversal (0 = the reference's Moeller-Trumbore)
     Camera cam;
     FilterTab filter;
 };

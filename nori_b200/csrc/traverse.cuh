@@ -29,7 +29,9 @@ struct TraceStats { uint32_t nodes, tris; };
 template <bool ANY_HIT, bool COUNT = false>
 NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris,
                        V3 o, V3 d, float mint, float maxt, float &tOut, float &uOut, float &vOut,
-                       TraceStats *stats = nullptr) {
+                       TraceStats *stats = nullptr, bool watertight = false) {
+    WtRay wt = {0, 1, 2, 0.f, 0.f, 0.f};
+    if (watertight) wt = wtSetup(d);
     const float big = 1e30f;
     const float idx = fabsf(d.x) > 1e-30f ? 1.0f / d.x : copysignf(big, d.x);
     const float idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);
@@ -78,7 +80,9 @@ NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restric
                 const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
                 if (COUNT) stats->tris++;
                 float u, v, t;
-                if (rayTriangle(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, d, mint, tbest, u, v, t)) {
+                const bool hit = watertight ? rayTriangleWatertight(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, wt, mint, tbest, u, v, t)
+                                            : rayTriangle(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, d, mint, tbest, u, v, t);
+                if (hit) {
                     const uint32_t gid = __float_as_uint(a.w);
                     if (ANY_HIT) { tOut = t; uOut = u; vOut = v; return gid; }
                     if (t < tbest || best == kNoHit || gid > best) {

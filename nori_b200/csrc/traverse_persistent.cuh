@@ -17,7 +17,7 @@ namespace ng {
 
 constexpr int kFetchThreshold = 20;   // default: refill when fewer than this many lanes still traverse
 
-template <bool ANY_HIT, class IO>
+template <bool ANY_HIT, bool WT = false, class IO>
 NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
                           unsigned int *workCounter, IO &io, int tuning = kFetchThreshold) {
     const int fetchThreshold = tuning & 0xff;                  // refill when fewer lanes than this still hold a ray
@@ -32,6 +32,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
     float idx = 0, idy = 0, idz = 0, oodx = 0, oody = 0, oodz = 0, mint = 0, tbest = 0, bu = 0, bv = 0;
     bool exhausted = false;
+    WtRay wt = {0, 1, 2, 0.f, 0.f, 0.f};                      // NORI_ISECT_WATERTIGHT only (WT): per-ray shear
 
     for (;;) {
         // ---- refill idle lanes ------------------------------------------------------------
@@ -52,6 +53,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                         idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);
                         idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);
                         oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz;
+                        if (WT) wt = wtSetup(d);
                         rayIdx = i; tbest = maxt; best = kNoHit; sp = 0; cur = 0; leaf = 0; active = true;
                     }
                 }
@@ -107,7 +109,9 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                     const float4 *tp = leafTris + 3 * (size_t) (first + k);
                     const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
                     float u, v, t;
-                    if (rayTriangle(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, d, mint, tbest, u, v, t)) {
+                    const bool hit = WT ? rayTriangleWatertight(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, wt, mint, tbest, u, v, t)
+                                        : rayTriangle(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, d, mint, tbest, u, v, t);
+                    if (hit) {
                         const uint32_t gid = __float_as_uint(a.w);
                         if (ANY_HIT) { best = gid; tbest = t; bu = u; bv = v; break; }
                         if (t < tbest || best == kNoHit || gid > best) { tbest = t; best = gid; bu = u; bv = v; }

@@ -25,7 +25,7 @@ EXPORTS = [
     "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",
     "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel",
     "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_block_device_ptr",
-    "nori_gpu_block_dims", "nori_gpu_set_profiling", "nori_gpu_set_pool_size",
+    "nori_gpu_block_dims", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance",
@@ -99,6 +99,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_block_dims.argtypes = [vp, C.POINTER(ip), C.POINTER(ip), C.POINTER(ip)]
     L.nori_gpu_set_profiling.argtypes = [vp, ip]
     L.nori_gpu_set_pool_size.argtypes = [vp, C.c_uint32]
+    L.nori_gpu_set_intersect_mode.argtypes = [vp, ip]
     L.nori_gpu_trace.argtypes = [vp, vp, ip, ip, vp, vp, vp]
     L.nori_gpu_trace_device.argtypes = [vp, vp, ip, ip, vp, C.POINTER(C.c_float)]
     L.nori_gpu_trace_count.argtypes = [vp, vp, ip, ip, vp]
@@ -209,22 +210,22 @@ class Engine:
         return p.value, n.value
 
     # ---- render --------------------------------------------------------------------------
-    def render_desc(self, integrator=None, stream_mode=1, sample_first=0, sample_last=None, clear=True) -> RenderDesc:
+    def render_desc(self, integrator=None, stream_mode=1, sample_first=0, sample_last=None, clear=True, intersect_mode=0) -> RenderDesc:
         s = self.scene
         d = RenderDesc()
         d.integrator = int(s.integrator if integrator is None else integrator)
         d.stream_mode = int(stream_mode)
         d.sample_first = int(sample_first)
         d.sample_last = int(s.sample_count if sample_last is None else sample_last)
-        d.rr_start, d.rr_max, d.max_depth, d.intersect_mode = int(s.rr_start), float(s.rr_max), int(s.max_depth), 0
+        d.rr_start, d.rr_max, d.max_depth, d.intersect_mode = int(s.rr_start), float(s.rr_max), int(s.max_depth), int(intersect_mode)
         d.light_pos = (C.c_float * 3)(*[float(x) for x in s.light_pos])
         d.light_energy = (C.c_float * 3)(*[float(x) for x in s.light_energy])
         d.clear, d.deterministic = int(clear), 0
         return d
 
-    def render(self, integrator=None, stream_mode=1, sample_first=0, sample_last=None, clear=True, download=True):
+    def render(self, integrator=None, stream_mode=1, sample_first=0, sample_last=None, clear=True, download=True, intersect_mode=0):
         """render(): all samples [first, last) of every pixel. Returns (ImageBlock data, stats)."""
-        d = self.render_desc(integrator, stream_mode, sample_first, sample_last, clear)
+        d = self.render_desc(integrator, stream_mode, sample_first, sample_last, clear, intersect_mode)
         st = RenderStats()
         self._ck(self.L.nori_gpu_render(self.h, C.byref(d), C.byref(st)))
         return (self.download_block() if download else None), st.as_dict()
@@ -241,11 +242,15 @@ class Engine:
         self._ck(self.L.nori_gpu_download_bitmap(self.h, _p(out)))
         return out
 
-    def sample_radiance(self, pixel, sample, integrator=None):
+    def set_intersect_mode(self, mode: int):
+        """Ray-triangle test of the raw operators: 0 = the reference's Moeller-Trumbore, 1 = watertight."""
+        self._ck(self.L.nori_gpu_set_intersect_mode(self.h, int(mode)))
+
+    def sample_radiance(self, pixel, sample, integrator=None, intersect_mode=0):
         pixel = np.ascontiguousarray(pixel, np.uint32); sample = np.ascontiguousarray(sample, np.uint32)
         n = pixel.shape[0]
         rgb = np.empty((n, 3), np.float32); pos = np.empty((n, 2), np.float32)
-        d = self.render_desc(integrator)
+        d = self.render_desc(integrator, intersect_mode=intersect_mode)
         self._ck(self.L.nori_gpu_sample_radiance(self.h, C.byref(d), n, _p(pixel), _p(sample), _p(rgb), _p(pos)))
         return rgb, pos
 

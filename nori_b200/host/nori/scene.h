@@ -125,11 +125,14 @@ public:
     int rrStart() const { return m_rrStart; }
     float rrMax() const { return m_rrMax; }
     int maxDepth() const { return m_maxDepth; }
+    /// NORI_ISECT_* (property `watertight`, default false = the reference's Moeller-Trumbore, src/mesh.cpp:51-88)
+    int intersectMode() const { return m_watertight ? 1 : 0; }
 protected:
     void readTermination(const PropertyList &p) {
         m_rrStart = p.getInteger("rrStart", 3); m_rrMax = p.getFloat("rrMax", 0.99f); m_maxDepth = p.getInteger("maxDepth", 0);
+        m_watertight = p.getBoolean("watertight", false);
     }
-    int m_rrStart = 3; float m_rrMax = 0.99f; int m_maxDepth = 0;
+    int m_rrStart = 3; float m_rrMax = 0.99f; int m_maxDepth = 0; bool m_watertight = false;
 };
 
 // ---- image block and bitmap (include/nori/block.h:44-113, include/nori/bitmap.h:30-58) ---------------

@@ -210,7 +210,7 @@ void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uin
     d.stream_mode = NORI_STREAM_PER_SAMPLE;
     d.sample_first = sampleFirst; d.sample_last = sampleLast;
     d.rr_start = integrator->rrStart(); d.rr_max = integrator->rrMax(); d.max_depth = integrator->maxDepth();
-    d.intersect_mode = NORI_ISECT_REFERENCE_MT;
+    d.intersect_mode = integrator->intersectMode();
     d.clear = 1;
     integrator->describe(d.light_pos, d.light_energy);
     NoriGpuRenderStats st;

@@ -74,6 +74,7 @@ void noracle_scene_set_integrator(void *s_, int type, int rrStart, float rrMax, 
 
 void noracle_scene_activate(void *s_, int useBvh) { ((Scene *) s_)->activate(useBvh != 0); }
 void noracle_scene_set_use_bvh(void *s_, int useBvh) { ((Scene *) s_)->accel.useBvh = useBvh != 0; }
+void noracle_scene_set_intersect_mode(void *s_, int mode) { ((Scene *) s_)->accel.isectMode = mode; }
 uint32_t noracle_scene_triangle_count(void *s_) { return (uint32_t) ((Scene *) s_)->accel.triMesh.size(); }
 uint32_t noracle_scene_bvh_node_count(void *s_) { return (uint32_t) ((Scene *) s_)->accel.nodes.size(); }
 

@@ -205,6 +205,55 @@ inline bool rayTriangle(V3 p0, V3 p1, V3 p2, const Ray &ray, float &u, float &v,
     return t >= ray.mint && t <= ray.maxt;
 }
 
+// ---------------------------------------------------------------------------------------
+// SPEC (no reference code): watertight ray-triangle test, the second intersection mode the ABI
+// offers (NORI_ISECT_WATERTIGHT). The reference only has Moeller-Trumbore (src/mesh.cpp:51-88),
+// which can let a ray slip between two triangles sharing an edge. Restated from Woop, Benthin,
+// Wald, "Watertight Ray/Triangle Intersection", JCGT 2(1), 2013, section 3 + appendix A:
+// shear the triangle into a ray space whose z axis is the ray's dominant direction, evaluate the
+// three 2D edge functions, recompute them in double precision when one of them is exactly zero.
+// The edge functions of a shared edge are exact negations of each other on the two triangles
+// (no FMA contraction), so a ray is never "outside" both. Same hit convention as mesh.cpp:
+// u = weight of p1, v = weight of p2, accept iff mint <= t <= maxt (inclusive), no culling.
+// Parity: unpinned by the reference (oracle <-> GPU bit-exactness and the watertightness
+// property on shared edges / vertices are what the tests check).
+// ---------------------------------------------------------------------------------------
+struct WtRay { int kx, ky, kz; float Sx, Sy, Sz; };
+inline WtRay wtSetup(V3 d) {
+    WtRay w;
+    float ax = std::abs(d.x), ay = std::abs(d.y), az = std::abs(d.z);
+    w.kz = ax > ay ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    w.kx = w.kz + 1; if (w.kx == 3) w.kx = 0;
+    w.ky = w.kx + 1; if (w.ky == 3) w.ky = 0;
+    if (d[w.kz] < 0.0f) { int tmp = w.kx; w.kx = w.ky; w.ky = tmp; }   // keep the winding
+    float dz = d[w.kz];
+    w.Sx = d[w.kx] / dz; w.Sy = d[w.ky] / dz; w.Sz = 1.0f / dz;
+    return w;
+}
+inline bool rayTriangleWatertight(V3 p0, V3 p1, V3 p2, const Ray &ray, float &u, float &v, float &t) {
+    const WtRay w = wtSetup(ray.d);
+    const V3 A = p0 - ray.o, B = p1 - ray.o, C = p2 - ray.o;
+    const float Ax = A[w.kx] - w.Sx * A[w.kz], Ay = A[w.ky] - w.Sy * A[w.kz];
+    const float Bx = B[w.kx] - w.Sx * B[w.kz], By = B[w.ky] - w.Sy * B[w.kz];
+    const float Cx = C[w.kx] - w.Sx * C[w.kz], Cy = C[w.ky] - w.Sy * C[w.kz];
+    float U = Cx * By - Cy * Bx, V = Ax * Cy - Ay * Cx, W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        U = (float) ((double) Cx * (double) By - (double) Cy * (double) Bx);
+        V = (float) ((double) Ax * (double) Cy - (double) Ay * (double) Cx);
+        W = (float) ((double) Bx * (double) Ay - (double) By * (double) Ax);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+    const float det = (U + V) + W;
+    if (det == 0.0f) return false;
+    const float Az = w.Sz * A[w.kz], Bz = w.Sz * B[w.kz], Cz = w.Sz * C[w.kz];
+    const float T = (U * Az + V * Bz) + W * Cz;
+    const float rcpDet = 1.0f / det;
+    t = T * rcpDet;
+    if (!(t >= ray.mint && t <= ray.maxt)) return false;
+    u = V * rcpDet; v = W * rcpDet;
+    return true;
+}
+
 struct BBox {
     V3 min, max;
     BBox() { reset(); }

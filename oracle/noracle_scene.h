@@ -86,9 +86,10 @@ struct Accel {
     std::vector<uint32_t> refs;                // BVH leaf order -> global triangle id
     std::vector<BvhNode> nodes;
     bool useBvh;
+    int isectMode;                             // 0: Moeller-Trumbore of src/mesh.cpp:51-88; 1: watertight (noracle_math.h)
     mutable TraversalCounters *counters;       // optional (single-threaded callers only)
     mutable TraversalCounters *shadowCounters; // optional: shadow rays counted apart from closest-hit rays
-    Accel() : scene(0), useBvh(true), counters(0), shadowCounters(0), active(0) {}
+    Accel() : scene(0), useBvh(true), isectMode(0), counters(0), shadowCounters(0), active(0) {}
     void build(const Scene *s, int leafSize = 4);
     mutable TraversalCounters *active;         // counter set of the ray being traced
     bool testTri(uint32_t gid, const Ray &ray, float &u, float &v, float &t) const;
@@ -155,6 +156,7 @@ inline bool Accel::testTri(uint32_t gid, const Ray &ray, float &u, float &v, flo
     const MeshData &m = scene->meshes[triMesh[gid]];
     uint32_t f = triLocal[gid];
     if (active) active->triTests++;
+    if (isectMode == 1) return rayTriangleWatertight(m.pos(m.F[3 * f]), m.pos(m.F[3 * f + 1]), m.pos(m.F[3 * f + 2]), ray, u, v, t);
     return rayTriangle(m.pos(m.F[3 * f]), m.pos(m.F[3 * f + 1]), m.pos(m.F[3 * f + 2]), ray, u, v, t);
 }
 

@@ -83,6 +83,10 @@ class PortScene:
         self.L.noracle_scene_set_integrator(self.h, integrator, s.rr_start, C.c_float(s.rr_max), s.max_depth,
                                             _f32(s.light_pos), _f32(s.light_energy))
 
+    def set_intersect_mode(self, mode: int):
+        """0: Moeller-Trumbore (src/mesh.cpp:51-88), 1: watertight (noracle_math.h)."""
+        self.L.noracle_scene_set_intersect_mode(self.h, int(mode))
+
     def camera_rays(self, pixel_samples):
         ps = _f32(pixel_samples, (-1, 2)); out = np.empty((ps.shape[0], 8), np.float32)
         self.L.noracle_camera_rays(self.h, ps.shape[0], ps, out)
@@ -140,6 +144,7 @@ class Port:
         L.noracle_scene_set_integrator.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_int, _f32p, _f32p]
         L.noracle_scene_activate.argtypes = [C.c_void_p, C.c_int]
         L.noracle_scene_set_use_bvh.argtypes = [C.c_void_p, C.c_int]
+        L.noracle_scene_set_intersect_mode.argtypes = [C.c_void_p, C.c_int]
         L.noracle_pcg32_uints.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int, _u32p]
         L.noracle_pcg32_floats.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int, _f32p]
         L.noracle_camera_rays.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p]

@@ -69,6 +69,7 @@ def gpu_scene(engine):
             engine.load_scene(load_scene(name))
             state["name"] = name
         return engine
+    load.invalidate = lambda: state.update(name=None)    # for tests that load a scene of their own into `engine`
     return load
 
 
