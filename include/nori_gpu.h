@@ -163,6 +163,9 @@ int nori_gpu_bsdf_eval_pdf(nori_gpu_ctx *ctx, int bsdf_type, const float params[
 /* Warp::squareTo* and *Pdf (include/nori/warp.h:30-69); ids in src/warptest.cpp:91-94 order:
  * 0 square 1 tent 2 disk 3 uniform_sphere 4 uniform_hemisphere 5 cosine_hemisphere 6 beckmann */
 int nori_gpu_warp(nori_gpu_ctx *ctx, int warp_id, float param, int n, const float *xi, float *out3, float *pdf);
+/* Warp::squareTo*Pdf (include/nori/warp.h:33-69) evaluated at n given points (n x 3; the 2D warps read x, y):
+ * the density the chi^2 tests integrate over their cells (src/warptest.cpp:121-155). */
+int nori_gpu_warp_pdf(nori_gpu_ctx *ctx, int warp_id, float param, int n, const float *points3, float *pdf);
 /* pcg32 (ext/pcg32/pcg32.h:55-112,140-161): seed, advance, n x nextUInt */
 int nori_gpu_pcg32(nori_gpu_ctx *ctx, uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out);
 /* ImageBlock::put(pos, value) (src/block.cpp:74-103) for n samples into a zeroed full-frame block

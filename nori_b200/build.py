@@ -69,7 +69,7 @@ def build(force: bool = False, verbose: bool = False, checked: bool = False) -> 
 
 HOST = os.path.join(HERE, "host")
 HOST_BIN = os.path.join(HERE, "bin", "nori_b200")
-HOST_SOURCES = ["common.cpp", "object.cpp", "xml.cpp", "parser.cpp", "plugins.cpp", "mesh.cpp", "scene.cpp", "bitmap.cpp", "main.cpp"]
+HOST_SOURCES = ["common.cpp", "object.cpp", "xml.cpp", "parser.cpp", "plugins.cpp", "mesh.cpp", "scene.cpp", "bitmap.cpp", "tests.cpp", "main.cpp"]
 # No FMA contraction and no fast-math: matrices and filter tables must carry the values the
 # reference's x86-64 build computes.
 HOST_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-Wall", "-Wextra", "-Wno-unused-parameter",
@@ -81,7 +81,7 @@ def build_host(force: bool = False, verbose: bool = False) -> str:
     objdir = os.path.join(HERE, "build", "host")
     os.makedirs(objdir, exist_ok=True)
     os.makedirs(os.path.dirname(HOST_BIN), exist_ok=True)
-    hdrs = [os.path.join(HOST, "nori", h) for h in os.listdir(os.path.join(HOST, "nori"))] + [os.path.join(HOST, "src", "xml.h"),
+    hdrs = [os.path.join(HOST, "nori", h) for h in sorted(os.listdir(os.path.join(HOST, "nori")))] + [os.path.join(HOST, "src", "xml.h"),
             os.path.join(HERE, "..", "include", "nori_gpu.h")]
     cxx = os.environ.get("CXX", "g++")
     objs, procs = [], []

@@ -636,6 +636,19 @@ int nori_gpu_warp(nori_gpu_ctx *ctx, int warp_id, float param, int n, const floa
     return NORI_GPU_OK;
 }
 
+int nori_gpu_warp_pdf(nori_gpu_ctx *ctx, int warp_id, float param, int n, const float *points3, float *pdf) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(warp_id >= 0 && warp_id <= 6 && n > 0 && points3 && pdf, "warp_pdf: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float> dp, dpdf; CK(dp.alloc(3 * (size_t) n)); CK(dpdf.alloc(n));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(dp.p, points3, (size_t) n * 12, cudaMemcpyHostToDevice, st));
+    launchWarpPdf(warp_id, param, n, dp.p, dpdf.p, st);
+    CK(cudaMemcpyAsync(pdf, dpdf.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
 int nori_gpu_pcg32(nori_gpu_ctx *ctx, uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(n > 0 && out, "pcg32: bad arguments");

@@ -101,6 +101,7 @@ void launchCameraRays(const DeviceScene &sc, const float2 *ps, int n, float4 *ra
 void launchBsdfSample(Bsdf b, int n, const float *wi, const float *xi, float *wo, float *weight, float *pdf, float *eta, int *measure, cudaStream_t st);
 void launchBsdfEvalPdf(Bsdf b, int n, const float *wi, const float *wo, float *f, float *pdf, cudaStream_t st);
 void launchWarp(int id, float param, int n, const float *xi, float *out3, float *pdf, cudaStream_t st);
+void launchWarpPdf(int id, float param, int n, const float *pts3, float *pdf, cudaStream_t st);
 void launchPcg32(uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out, cudaStream_t st);
 void launchSplatList(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
 void launchSplatOrdered(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);

@@ -144,6 +144,28 @@ void launchWarp(int id, float param, int n, const float *xi, float *out3, float 
     if (n > 0) k_warp<<<gridFor(n), 256, 0, st>>>(id, param, n, xi, out3, pdf);
 }
 
+/// Warp::squareTo*Pdf (include/nori/warp.h:33-69) at given points (2D warps read x, y only).
+__global__ void k_warpPdf(int id, float param, int n, const float *__restrict__ pts3, float *pdf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 v = mk(pts3[3 * i], pts3[3 * i + 1], pts3[3 * i + 2]);
+    V2 q; q.x = v.x; q.y = v.y;
+    float p;
+    switch (id) {
+    case 0: p = (q.x >= 0 && q.x <= 1 && q.y >= 0 && q.y <= 1) ? 1.0f : 0.0f; break;
+    case 1: p = squareToTentPdf(q); break;
+    case 2: p = squareToUniformDiskPdf(q); break;
+    case 3: p = squareToUniformSpherePdf(v); break;
+    case 4: p = squareToUniformHemispherePdf(v); break;
+    case 5: p = squareToCosineHemispherePdf(v); break;
+    default: p = squareToBeckmannPdf(v, param); break;
+    }
+    pdf[i] = p;
+}
+void launchWarpPdf(int id, float param, int n, const float *pts3, float *pdf, cudaStream_t st) {
+    if (n > 0) k_warpPdf<<<gridFor(n), 256, 0, st>>>(id, param, n, pts3, pdf);
+}
+
 /// Thread i produces the (advance + i)-th output of the stream through pcg32::advance.
 __global__ void k_pcg32(uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

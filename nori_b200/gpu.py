@@ -27,7 +27,7 @@ EXPORTS = [
     "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_block_device_ptr",
     "nori_gpu_block_dims", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
-    "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_pcg32", "nori_gpu_splat",
+    "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance",
 ]
 
@@ -108,6 +108,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_bsdf_sample.argtypes = [vp, ip, vp, ip, vp, vp, vp, vp, vp, vp, vp]
     L.nori_gpu_bsdf_eval_pdf.argtypes = [vp, ip, vp, ip, vp, vp, vp, vp]
     L.nori_gpu_warp.argtypes = [vp, ip, C.c_float, ip, vp, vp, vp]
+    L.nori_gpu_warp_pdf.argtypes = [vp, ip, C.c_float, ip, vp, vp]
     L.nori_gpu_pcg32.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int64, ip, vp]
     L.nori_gpu_splat.argtypes = [vp, ip, vp, vp, ip, vp, C.POINTER(C.c_uint64)]
     L.nori_gpu_sample_radiance.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp, vp]
@@ -300,6 +301,12 @@ class Engine:
         out = np.empty((n, 3), np.float32); pdf = np.empty(n, np.float32)
         self._ck(self.L.nori_gpu_warp(self.h, int(wid), C.c_float(param), n, _p(xi), _p(out), _p(pdf)))
         return out, pdf
+
+    def warp_pdf(self, wid, points3, param=0.0):
+        pts = _f32(points3, (-1, 3)); n = pts.shape[0]
+        pdf = np.empty(n, np.float32)
+        self._ck(self.L.nori_gpu_warp_pdf(self.h, int(wid), C.c_float(param), n, _p(pts), _p(pdf)))
+        return pdf
 
     def pcg32_uints(self, initstate, initseq, n, advance=0):
         out = np.empty(n, np.uint32)

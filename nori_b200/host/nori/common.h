@@ -105,6 +105,37 @@ std::vector<std::string> tokenize(const std::string &s, const std::string &delim
 std::string indent(const std::string &s, int amount = 2);
 std::string timeString(double ms, bool precise = false);
 std::string memString(size_t size, bool precise = false);
+/// Unit vector from spherical coordinates (src/common.cpp:244-252)
+inline Vector3f sphericalDirection(float theta, float phi) {
+    float sinTheta, cosTheta, sinPhi, cosPhi;
+    sincosf(theta, &sinTheta, &cosTheta); sincosf(phi, &sinPhi, &cosPhi);
+    return Vector3f(sinTheta * cosPhi, sinTheta * sinPhi, cosTheta);
+}
+
+/// PCG32 (XSH-RR 64/32, O'Neill 2014), the generator behind the reference's `independent` sampler and
+/// its test plugins (ext/pcg32/pcg32.h:40-112): default stream, nextUInt, nextFloat by the
+/// exponent-bits trick. The device has its own copy (csrc/nmath.cuh); this one drives the <test> plugins.
+struct Pcg32 {
+    uint64_t state = 0x853c49e6748fea9bULL, inc = 0xda3e39cb94b95bdbULL;
+    Pcg32() {}
+    Pcg32(uint64_t initstate, uint64_t initseq) { seed(initstate, initseq); }
+    void seed(uint64_t initstate, uint64_t initseq) {
+        state = 0; inc = (initseq << 1) | 1u;
+        nextUInt(); state += initstate; nextUInt();
+    }
+    uint32_t nextUInt() {
+        const uint64_t old = state;
+        state = old * 0x5851f42d4c957f2dULL + inc;
+        const uint32_t xorshifted = (uint32_t) (((old >> 18u) ^ old) >> 27u), rot = (uint32_t) (old >> 59u);
+        return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+    }
+    float nextFloat() {
+        union { uint32_t u; float f; } x;
+        x.u = (nextUInt() >> 9) | 0x3f800000u;
+        return x.f - 1.0f;
+    }
+};
+
 inline float degToRad(float v) { return v * (3.14159265358979323846f / 180.0f); }
 
 NORI_NAMESPACE_END

@@ -201,12 +201,21 @@ private:
     mutable nori_gpu_ctx *m_ctx = nullptr;
 };
 
+/// Device context for operators that need no scene (BSDF::sample/eval/pdf, Warp::*): created on first use.
+nori_gpu_ctx *operatorContext();
+/// Turns a non-zero return of the C ABI into a NoriException carrying nori_gpu_last_error().
+void gpuCheck(nori_gpu_ctx *ctx, int rc, const char *what);
+
 /// Statistics nori_gpu_render reports (subset printed by the command line tool)
 struct RenderReport { double ms = 0, msamples = 0, mrays = 0, gsegments = 0; uint64_t dropped = 0, launches = 0; };
 
 /// Replacement for the reference's render() block loop (src/main.cpp:86-127): the whole frame,
 /// samples [sampleFirst, sampleLast) of every pixel, into `result`.
 void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report);
+
+/// Integrator::Li for n individual camera samples (pixel index y * width + x, sample index) with the
+/// per-sample streams of the render path: rgb n x 3. Used by the scene t-tests (src/ttest.cpp:136-176).
+void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const uint32_t *sample, float *rgb, int device = 0);
 
 /// Search path for files named in scene descriptions (the reference prepends the scene's directory)
 class FileResolver {

@@ -4,6 +4,8 @@
 //
 //   nori_b200 [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] scene.xml
 //   nori_b200 --dump FILE scene.xml     parse only; write the flattened descriptors (tests; no GPU)
+//   nori_b200 test.xml                  a <test> root (chi2test, ttest, warptest) runs in activate(), as in the reference
+//   nori_b200 --warptest NAME [P [P2]]  the reference's `warptest NAME P P2` command line mode (src/warptest.cpp:979-1006)
 #include <nori/scene.h>
 #include <cstring>
 #include <fstream>
@@ -91,6 +93,20 @@ int main(int argc, char **argv) {
         else if (a == "--out") outName = value("--out");
         else if (a == "--dump") dumpFile = value("--dump");
         else if (a == "--no-png") png = false;
+        else if (a == "--warptest") {
+            try {
+                PropertyList list;
+                list.setString("warp", value("--warptest"));
+                if (i + 1 < argc) list.setFloat("param", toFloat(argv[++i]));
+                if (i + 1 < argc) list.setFloat("param2", toFloat(argv[++i]));
+                std::unique_ptr<NoriObject> test(NoriObjectFactory::createInstance("warptest", list));
+                test->activate();
+                return 0;
+            } catch (const std::exception &e) {
+                std::cout << e.what() << std::endl;
+                return 1;
+            }
+        }
         else if (!a.empty() && a[0] == '-') { std::cerr << "Unknown option " << a << std::endl; return -1; }
         else sceneFile = a;
     }

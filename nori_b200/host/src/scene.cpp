@@ -3,6 +3,7 @@
 // toBitmap), src/main.cpp:69-151 (the render() this replaces).
 #include <nori/scene.h>
 #include <nori_gpu.h>
+#include <algorithm>
 #include <cstring>
 #include <fstream>
 #include <iostream>
@@ -21,9 +22,10 @@ std::string FileResolver::resolve(const std::string &name) const {
 FileResolver *getFileResolver() { static FileResolver *r = new FileResolver(); return r; }
 
 // ---- errors: C codes -> NoriException ----------------------------------------------------------------
-static void check(nori_gpu_ctx *ctx, int rc, const char *what) {
+void gpuCheck(nori_gpu_ctx *ctx, int rc, const char *what) {
     if (rc != NORI_GPU_OK) throw NoriException("%s: %s", what, nori_gpu_last_error(ctx));
 }
+static void check(nori_gpu_ctx *ctx, int rc, const char *what) { gpuCheck(ctx, rc, what); }
 
 // ---- Scene -------------------------------------------------------------------------------------------
 Scene::Scene(const PropertyList &) {}
@@ -134,7 +136,7 @@ bool Scene::rayIntersect(const Ray3f &ray) const {
 }
 
 // ---- BSDF operators: evaluated by the device code the renderer uses ------------------------------------
-static nori_gpu_ctx *operatorContext() {
+nori_gpu_ctx *operatorContext() {
     static nori_gpu_ctx *ctx = nullptr;
     if (!ctx && nori_gpu_create(&ctx, 0) != NORI_GPU_OK)
         throw NoriException("nori_gpu_create: %s (nori_b200 has no CPU path)", nori_gpu_last_error(nullptr));
@@ -201,9 +203,9 @@ std::unique_ptr<Bitmap> ImageBlock::toBitmap() const {
 }
 
 // ---- render ------------------------------------------------------------------------------------------------
-void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report) {
-    nori_gpu_ctx *ctx = scene->gpu(device);
+static NoriGpuRenderDesc renderDesc(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast) {
     const Integrator *integrator = scene->getIntegrator();
+    if (!integrator) throw NoriException("No integrator was specified!");
     NoriGpuRenderDesc d;
     memset(&d, 0, sizeof(d));
     d.integrator = integrator->gpuType();
@@ -213,6 +215,21 @@ void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uin
     d.intersect_mode = integrator->intersectMode();
     d.clear = 1;
     integrator->describe(d.light_pos, d.light_energy);
+    return d;
+}
+
+void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const uint32_t *sample, float *rgb, int device) {
+    nori_gpu_ctx *ctx = scene->gpu(device);
+    const NoriGpuRenderDesc d = renderDesc(scene, 0, 1);
+    // a path pool sized to the request (the default pool is sized for full-frame renders)
+    const uint32_t slots = (uint32_t) std::min<uint64_t>(1u << 20, std::max<uint64_t>(4096, ((uint64_t) n + 255) / 256 * 256));
+    check(ctx, nori_gpu_set_pool_size(ctx, slots), "nori_gpu_set_pool_size");
+    check(ctx, nori_gpu_sample_radiance(ctx, &d, n, pixel, sample, rgb, nullptr), "nori_gpu_sample_radiance");
+}
+
+void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report) {
+    nori_gpu_ctx *ctx = scene->gpu(device);
+    const NoriGpuRenderDesc d = renderDesc(scene, sampleFirst, sampleLast);
     NoriGpuRenderStats st;
     check(ctx, nori_gpu_render(ctx, &d, &st), "nori_gpu_render");           // replaces tbb::parallel_for(range, map)
     int rows = 0, cols = 0, border = 0;
