@@ -129,6 +129,13 @@ int nori_gpu_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuRen
 int nori_gpu_download_block(nori_gpu_ctx *ctx, float *rgbw);
 /* ImageBlock::toBitmap (src/block.cpp:57-63): H x W x RGB, rgb/w, border cropped */
 int nori_gpu_download_bitmap(nori_gpu_ctx *ctx, float *rgb);
+/* toBitmap + the 8-bit path of Bitmap::savePNG (src/bitmap.cpp:117-127): Color3f::toSRGB (src/common.cpp:178-192),
+ * x 255, clamp, truncate — H x W x RGB8, tonemapped on the device (what the reference's preview shows, src/gui.cpp:64-78). */
+int nori_gpu_download_srgb8(nori_gpu_ctx *ctx, uint8_t *rgb8);
+/* Checkpoint / resume and merging of partial results: sets the accumulated ImageBlock (layout of
+ * nori_gpu_download_block) or, with accumulate = 1, adds to it — ImageBlock::put(ImageBlock &), src/block.cpp:105-114.
+ * A render continues on top of it with NoriGpuRenderDesc::clear = 0 and the next sample range. */
+int nori_gpu_upload_block(nori_gpu_ctx *ctx, const float *rgbw, int accumulate);
 /* Device-side access for the cross-GPU sum of ImageBlocks (`result.put(block)`, block.cpp:105-114):
  * the accumulator is a device array of block_floats() floats that NCCL reduces in place. */
 int nori_gpu_block_device_ptr(nori_gpu_ctx *ctx, void **dptr, uint64_t *n_floats);

@@ -498,6 +498,36 @@ int nori_gpu_download_bitmap(nori_gpu_ctx *ctx, float *rgb) {
     return NORI_GPU_OK;
 }
 
+int nori_gpu_download_srgb8(nori_gpu_ctx *ctx, uint8_t *rgb8) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(rgb8 && ctx->d_block, "download_srgb8: nothing rendered");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = (size_t) ctx->cam.width * ctx->cam.height * 3;
+    DevBuf<uint8_t> d; CK(d.alloc(n));
+    launchToSRGB8(ctx->d_block, ctx->cam.width, ctx->cam.height, ctx->filter.border, d.p, ctx->stream);
+    CK(cudaMemcpyAsync(rgb8, d.p, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_upload_block(nori_gpu_ctx *ctx, const float *rgbw, int accumulate) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(rgbw, "upload_block: null block");
+    REQUIRE(ctx->haveCamera && ctx->haveFilter, "upload_block: camera and filter must be set first");
+    CK(cudaSetDevice(ctx->device));
+    if (int r = ensureBlock(ctx)) return r;
+    if (!accumulate) {
+        CK(cudaMemcpyAsync(ctx->d_block, rgbw, ctx->blockFloats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+        DevBuf<float> d; CK(d.alloc(ctx->blockFloats));
+        CK(cudaMemcpyAsync(d.p, rgbw, ctx->blockFloats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        launchAddBlock(ctx->d_block, d.p, ctx->blockFloats, ctx->stream);
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Raw operators. Host arrays in, host arrays out; the work itself runs on the device.
 #define NEED_SCENE() REQUIRE(ctx->haveBvh, "operator needs an uploaded scene with a built accel")

@@ -106,5 +106,7 @@ void launchPcg32(uint64_t initstate, uint64_t initseq, int64_t advance, int n, u
 void launchSplatList(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
 void launchSplatOrdered(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
 void launchToBitmap(const float *block, int W, int H, int border, float *rgb, cudaStream_t st);
+void launchToSRGB8(const float *block, int W, int H, int border, uint8_t *rgb8, cudaStream_t st);
+void launchAddBlock(float *dst, const float *src, size_t nFloats, cudaStream_t st);
 
 } // namespace ng

@@ -248,6 +248,35 @@ void launchToBitmap(const float *block, int W, int H, int border, float *rgb, cu
     k_toBitmap<<<gridFor(W * H), 256, 0, st>>>(reinterpret_cast<const float4 *>(block), W, H, border, rgb);
 }
 
+/// toBitmap followed by the PNG path of Bitmap::savePNG (src/bitmap.cpp:117-127): Color3f::toSRGB
+/// (src/common.cpp:178-192), scale by 255, clamp to [0, 255], truncate.
+__device__ __forceinline__ float toSRGB1(float v) { return v <= 0.0031308f ? 12.92f * v : (1.0f + 0.055f) * powf(v, 1.0f / 2.4f) - 0.055f; }
+__global__ void k_toSRGB8(const float4 *__restrict__ block, int W, int H, int border, uint8_t *__restrict__ rgb8) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= W * H) return;
+    int x = i % W, y = i / W;
+    float4 c = block[(size_t) (y + border) * (W + 2 * border) + x + border];
+    float v[3] = {0.f, 0.f, 0.f};
+    if (c.w != 0.f) { v[0] = c.x / c.w; v[1] = c.y / c.w; v[2] = c.z / c.w; }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) rgb8[3 * (size_t) i + k] = (uint8_t) fminf(fmaxf(255.f * toSRGB1(v[k]), 0.f), 255.f);
+}
+void launchToSRGB8(const float *block, int W, int H, int border, uint8_t *rgb8, cudaStream_t st) {
+    k_toSRGB8<<<gridFor(W * H), 256, 0, st>>>(reinterpret_cast<const float4 *>(block), W, H, border, rgb8);
+}
+
+/// ImageBlock::put(ImageBlock &) (src/block.cpp:105-114) for two full-frame blocks: dst += src.
+__global__ void k_addBlock(float4 *__restrict__ dst, const float4 *__restrict__ src, size_t n) {
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = dst[i], b = src[i];
+    dst[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+void launchAddBlock(float *dst, const float *src, size_t nFloats, cudaStream_t st) {
+    const size_t n = nFloats / 4;
+    if (n) k_addBlock<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<float4 *>(dst), reinterpret_cast<const float4 *>(src), n);
+}
+
 unsigned operatorChecks(unsigned *line) { return fetchChecks(line); }
 
 } // namespace ng

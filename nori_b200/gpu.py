@@ -24,7 +24,7 @@ LIB_PATH = os.path.join(HERE, os.path.basename(os.environ.get("NORI_GPU_LIB", "l
 EXPORTS = [
     "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",
     "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel",
-    "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_block_device_ptr",
+    "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_download_srgb8", "nori_gpu_upload_block", "nori_gpu_block_device_ptr",
     "nori_gpu_block_dims", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
@@ -95,6 +95,8 @@ def load_library() -> C.CDLL:
     L.nori_gpu_render.argtypes = [vp, C.POINTER(RenderDesc), C.POINTER(RenderStats)]
     L.nori_gpu_download_block.argtypes = [vp, vp]
     L.nori_gpu_download_bitmap.argtypes = [vp, vp]
+    L.nori_gpu_download_srgb8.argtypes = [vp, vp]
+    L.nori_gpu_upload_block.argtypes = [vp, vp, ip]
     L.nori_gpu_block_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
     L.nori_gpu_block_dims.argtypes = [vp, C.POINTER(ip), C.POINTER(ip), C.POINTER(ip)]
     L.nori_gpu_set_profiling.argtypes = [vp, ip]
@@ -246,6 +248,21 @@ class Engine:
     def set_intersect_mode(self, mode: int):
         """Ray-triangle test of the raw operators: 0 = the reference's Moeller-Trumbore, 1 = watertight."""
         self._ck(self.L.nori_gpu_set_intersect_mode(self.h, int(mode)))
+
+    def download_srgb8(self):
+        """ImageBlock::toBitmap + Color3f::toSRGB + 8-bit quantisation on the device (Bitmap::savePNG's pixels)."""
+        w, h = self._wh
+        out = np.empty((h, w, 3), np.uint8)
+        self._ck(self.L.nori_gpu_download_srgb8(self.h, _p(out)))
+        return out
+
+    def upload_block(self, rgbw, accumulate=False):
+        """Restore (or add to) the accumulated ImageBlock: checkpoint / resume, merging partial renders."""
+        a = _f32(rgbw)
+        r, c, _ = self.block_dims()
+        if a.size != r * c * 4:
+            raise NoriGpuError(f"upload_block: expected {r}x{c}x4 floats")
+        self._ck(self.L.nori_gpu_upload_block(self.h, _p(a), int(accumulate)))
 
     def sample_radiance(self, pixel, sample, integrator=None, intersect_mode=0):
         pixel = np.ascontiguousarray(pixel, np.uint32); sample = np.ascontiguousarray(sample, np.uint32)

@@ -211,7 +211,13 @@ struct RenderReport { double ms = 0, msamples = 0, mrays = 0, gsegments = 0; uin
 
 /// Replacement for the reference's render() block loop (src/main.cpp:86-127): the whole frame,
 /// samples [sampleFirst, sampleLast) of every pixel, into `result`.
-void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report);
+/// `resumeFrom`: an ImageBlock holding the samples rendered so far (a checkpoint); the new samples are added to it
+/// on the device (nori_gpu_upload_block + NoriGpuRenderDesc::clear = 0).
+void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report,
+               const ImageBlock *resumeFrom = nullptr);
+/// Checkpoint file of an ImageBlock (RGBW accumulator + the sample range it holds): raw little-endian.
+void saveCheckpoint(const std::string &path, const ImageBlock &block, uint32_t sampleFirst, uint32_t sampleLast);
+void loadCheckpoint(const std::string &path, ImageBlock &block, uint32_t &sampleFirst, uint32_t &sampleLast);
 
 /// Integrator::Li for n individual camera samples (pixel index y * width + x, sample index) with the
 /// per-sample streams of the render path: rgb n x 3. Used by the scene t-tests (src/ttest.cpp:136-176).

@@ -3,6 +3,8 @@
 // <scene>.exr and <scene>.png next to the scene file.
 //
 //   nori_b200 [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] scene.xml
+//   nori_b200 --first 0 --last 64 --checkpoint part.blk scene.xml      render a sample range, keep the accumulator
+//   nori_b200 --resume part.blk --last 256 scene.xml                   continue from it (samples [64, 256) are added)
 //   nori_b200 --dump FILE scene.xml     parse only; write the flattened descriptors (tests; no GPU)
 //   nori_b200 test.xml                  a <test> root (chi2test, ttest, warptest) runs in activate(), as in the reference
 //   nori_b200 --warptest NAME [P [P2]]  the reference's `warptest NAME P P2` command line mode (src/warptest.cpp:979-1006)
@@ -56,16 +58,26 @@ void dumpScene(const Scene *scene, const std::string &path) {
     }
 }
 
-void render(const Scene *scene, const std::string &outName, int device, int sppOverride, long first, long last, bool png) {
+void render(const Scene *scene, const std::string &outName, int device, int sppOverride, long first, long last, bool png,
+            const std::string &resumeFile, const std::string &checkpointFile) {
     const Camera *camera = scene->getCamera();
     const uint32_t spp = sppOverride > 0 ? (uint32_t) sppOverride : (uint32_t) scene->getSampler()->getSampleCount();
-    const uint32_t s0 = first >= 0 ? (uint32_t) first : 0u, s1 = last >= 0 ? (uint32_t) last : spp;
-    if (s1 <= s0) throw NoriException("empty sample range [%d, %d)", (int) s0, (int) s1);
+    uint32_t s0 = first >= 0 ? (uint32_t) first : 0u, s1 = last >= 0 ? (uint32_t) last : spp, held0 = 0;
     ImageBlock result(camera->getOutputSize(), camera->getReconstructionFilter());
+    std::unique_ptr<ImageBlock> held;
+    if (!resumeFile.empty()) {                                // continue after the samples the checkpoint holds
+        held.reset(new ImageBlock(camera->getOutputSize(), camera->getReconstructionFilter()));
+        uint32_t heldLast = 0;
+        loadCheckpoint(resumeFile, *held, held0, heldLast);
+        if (first >= 0 && (uint32_t) first != heldLast) throw NoriException("the checkpoint ends at sample %d; cannot resume at %d", (int) heldLast, (int) first);
+        s0 = heldLast;
+    }
+    if (s1 <= s0) throw NoriException("empty sample range [%d, %d)", (int) s0, (int) s1);
     scene->gpu(device);                                       // upload + Accel::build (Scene::activate does this in the reference)
     std::cout << "Rendering .. " << std::flush;
     RenderReport rep;
-    renderGpu(scene, result, s0, s1, device, &rep);
+    renderGpu(scene, result, s0, s1, device, &rep, held.get());
+    if (!checkpointFile.empty()) saveCheckpoint(checkpointFile, result, held ? held0 : s0, s1);
     std::cout << "done. (took " << timeString(rep.ms) << ": " << rep.msamples << " Msamples/s, " << rep.mrays << " Mrays/s, "
               << rep.gsegments << " Gsegments/s";
     if (rep.dropped) std::cout << ", " << rep.dropped << " invalid samples dropped";
@@ -78,7 +90,7 @@ void render(const Scene *scene, const std::string &outName, int device, int sppO
 } // namespace
 
 int main(int argc, char **argv) {
-    std::string sceneFile, dumpFile, outName;
+    std::string sceneFile, dumpFile, outName, resumeFile, checkpointFile;
     int device = 0, spp = 0; long first = -1, last = -1; bool png = true;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -92,6 +104,8 @@ int main(int argc, char **argv) {
         else if (a == "--last") last = atol(value("--last").c_str());
         else if (a == "--out") outName = value("--out");
         else if (a == "--dump") dumpFile = value("--dump");
+        else if (a == "--resume") resumeFile = value("--resume");
+        else if (a == "--checkpoint") checkpointFile = value("--checkpoint");
         else if (a == "--no-png") png = false;
         else if (a == "--warptest") {
             try {
@@ -111,7 +125,7 @@ int main(int argc, char **argv) {
         else sceneFile = a;
     }
     if (sceneFile.empty()) {
-        std::cerr << "Syntax: " << argv[0] << " [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--dump FILE] <scene.xml>" << std::endl;
+        std::cerr << "Syntax: " << argv[0] << " [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--resume FILE] [--checkpoint FILE] [--dump FILE] <scene.xml>" << std::endl;
         return -1;
     }
     try {
@@ -125,7 +139,7 @@ int main(int argc, char **argv) {
             const size_t dot = sceneFile.find_last_of('.');
             outName = dot == std::string::npos || (slash != std::string::npos && dot < slash) ? sceneFile : sceneFile.substr(0, dot);
         }
-        render(scene, outName, device, spp, first, last, png);
+        render(scene, outName, device, spp, first, last, png, resumeFile, checkpointFile);
     } catch (const std::exception &e) {
         std::cerr << "Fatal error: " << e.what() << std::endl;
         return -1;

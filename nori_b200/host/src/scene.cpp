@@ -227,9 +227,37 @@ void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const u
     check(ctx, nori_gpu_sample_radiance(ctx, &d, n, pixel, sample, rgb, nullptr), "nori_gpu_sample_radiance");
 }
 
-void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report) {
+void saveCheckpoint(const std::string &path, const ImageBlock &block, uint32_t sampleFirst, uint32_t sampleLast) {
+    std::ofstream os(path, std::ios::binary);
+    if (os.fail()) throw NoriException("Unable to open \"%s\" for writing", path);
+    const int32_t dims[3] = {block.rows(), block.cols(), block.getBorderSize()};
+    const uint32_t range[2] = {sampleFirst, sampleLast};
+    os.write("NB2BLK1", 8); os.write((const char *) dims, sizeof(dims)); os.write((const char *) range, sizeof(range));
+    os.write((const char *) block.data(), (std::streamsize) ((size_t) block.rows() * block.cols() * 4 * sizeof(float)));
+}
+
+void loadCheckpoint(const std::string &path, ImageBlock &block, uint32_t &sampleFirst, uint32_t &sampleLast) {
+    std::ifstream is(path, std::ios::binary);
+    char magic[8]; int32_t dims[3]; uint32_t range[2];
+    if (is.fail() || !is.read(magic, 8) || memcmp(magic, "NB2BLK1", 8) != 0 || !is.read((char *) dims, sizeof(dims)) || !is.read((char *) range, sizeof(range)))
+        throw NoriException("\"%s\" is not an ImageBlock checkpoint", path);
+    if (dims[0] != block.rows() || dims[1] != block.cols() || dims[2] != block.getBorderSize())
+        throw NoriException("checkpoint \"%s\" holds a %dx%d block (border %d); the camera needs %dx%d (border %d)", path, dims[1], dims[0], dims[2],
+                            block.cols(), block.rows(), block.getBorderSize());
+    if (!is.read((char *) block.data(), (std::streamsize) ((size_t) block.rows() * block.cols() * 4 * sizeof(float))))
+        throw NoriException("checkpoint \"%s\" is truncated", path);
+    sampleFirst = range[0]; sampleLast = range[1];
+}
+
+void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report,
+               const ImageBlock *resumeFrom) {
     nori_gpu_ctx *ctx = scene->gpu(device);
-    const NoriGpuRenderDesc d = renderDesc(scene, sampleFirst, sampleLast);
+    NoriGpuRenderDesc d = renderDesc(scene, sampleFirst, sampleLast);
+    if (resumeFrom) {
+        if (resumeFrom->rows() != result.rows() || resumeFrom->cols() != result.cols()) throw NoriException("renderGpu: the checkpoint does not match the camera");
+        check(ctx, nori_gpu_upload_block(ctx, resumeFrom->data(), 0), "nori_gpu_upload_block");
+        d.clear = 0;
+    }
     NoriGpuRenderStats st;
     check(ctx, nori_gpu_render(ctx, &d, &st), "nori_gpu_render");           // replaces tbb::parallel_for(range, map)
     int rows = 0, cols = 0, border = 0;

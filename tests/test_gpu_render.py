@@ -170,3 +170,38 @@ def test_range_checked_build_sees_no_violation():
     env = dict(os.environ, NORI_GPU_LIB="libnori_b200_checked.so")
     r = subprocess.run([sys.executable, os.path.join(root, "scripts", "sanitize.py"), "4"], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0 and "sanitize pass complete" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_device_tonemap_matches_bitmap_save_png(gpu_scene, scenes):
+    """nori_gpu_download_srgb8 = ImageBlock::toBitmap + Color3f::toSRGB + the 8-bit quantisation of Bitmap::savePNG
+    (src/bitmap.cpp:117-127, src/common.cpp:178-192) on the device: equal to the host formula on the downloaded
+    bitmap up to one level where device powf and numpy differ in the last ulp."""
+    e = gpu_scene("cbox_mis")
+    e.render(sample_first=0, sample_last=8)
+    img = e.download_bitmap()
+    got = e.download_srgb8()
+    assert got.dtype == np.uint8 and got.shape == img.shape
+    srgb = np.where(img <= np.float32(0.0031308), np.float32(12.92) * img,
+                    np.float32(1.055) * np.power(np.maximum(img, 0), np.float32(1 / 2.4), dtype=np.float32) - np.float32(0.055))
+    want = np.clip(np.float32(255) * srgb, 0, 255).astype(np.uint8)
+    diff = np.abs(got.astype(int) - want.astype(int))
+    assert diff.max() <= 1 and (diff == 0).mean() > 0.999
+    assert got.max() == 255 and got.min() == 0              # the light saturates, the background is black
+
+
+def test_block_upload_resumes_and_merges(gpu_scene, scenes):
+    """Checkpoint / resume through nori_gpu_upload_block: [0,3) then [3,8) with clear=0 on the restored block equals
+    [0,8); accumulate=1 merges two partial blocks (ImageBlock::put(ImageBlock&), src/block.cpp:105-114)."""
+    e = gpu_scene("cbox_mis")
+    whole, _ = e.render(sample_first=0, sample_last=8)
+    first, _ = e.render(sample_first=0, sample_last=3)
+    second, _ = e.render(sample_first=3, sample_last=8)
+    e.render(sample_first=0, sample_last=1)                 # scribble over the accumulator
+    e.upload_block(first)
+    np.testing.assert_array_equal(e.download_block(), first)
+    resumed, _ = e.render(sample_first=3, sample_last=8, clear=False)
+    np.testing.assert_allclose(resumed, whole, rtol=2e-4, atol=2e-4)
+    e.upload_block(first); e.upload_block(second, accumulate=True)
+    np.testing.assert_array_equal(e.download_block(), first + second)
+    with pytest.raises(Exception):
+        e.upload_block(first[:-1])

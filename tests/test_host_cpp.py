@@ -185,3 +185,22 @@ def test_cli_sample_range_and_no_gpu_message(tmp_path):
     env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
     r = subprocess.run([HOST_BIN, "--out", out, xml], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode != 0 and "Fatal error:" in r.stderr and "no CPU path" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_checkpoint_and_resume_equal_one_render(tmp_path):
+    """--checkpoint keeps the RGBW accumulator of a sample range, --resume continues on top of it on the device:
+    [0, 6) + [6, 16) must be the image of [0, 16) (same samples; float atomics: summation order only)."""
+    xml = os.path.join(HOST, "all_tags.xml")
+    whole, part, rest, blk = (str(tmp_path / n) for n in ("whole", "part", "rest", "part.blk"))
+    def run(*args):
+        r = subprocess.run([HOST_BIN, "--no-png"] + list(args) + [xml], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+    run("--out", whole, "--spp", "16")
+    run("--out", part, "--first", "0", "--last", "6", "--checkpoint", blk)
+    run("--out", rest, "--resume", blk, "--last", "16")
+    a, b, c = read_exr(whole + ".exr"), read_exr(rest + ".exr"), read_exr(part + ".exr")
+    np.testing.assert_allclose(b, a, rtol=2e-4, atol=1e-5)
+    assert np.abs(c - a).mean() > 1e-4                       # the 6-sample image alone is a different (noisier) image
+    r = subprocess.run([HOST_BIN, "--resume", blk, "--first", "3", "--last", "16", xml], capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0 and "cannot resume at 3" in r.stderr
