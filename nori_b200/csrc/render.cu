@@ -428,13 +428,13 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
 ///     the shadow kernel adds the light sample there (kShadowToRecord); only what the record
 ///     cannot express (value = T * L, late samples) parks the slot until the next iteration.
 /// One atomic per CTA each for: sample indices (twice), shadow queue space, finished count.
-template <int INTEGRATOR>
-__global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
-    constexpr int NK = kNumKeys + 1;
-    static_assert(NK == 6, "the warp scan below covers 6 keys x 8 warps = 48 counts in two registers per lane");
-    __shared__ unsigned sCnt[8][NK], sWarpShadow[8], sWarpRegen[8], sShadowBase;
+template <int INTEGRATOR, int NT>
+__global__ void __launch_bounds__(NT, 1024 / NT) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+    constexpr int NK = kNumKeys + 1, NW = NT / 32;
+    static_assert(NK * NW <= 64 && (NW == 8 || NW == 4), "the warp scan below keeps the NK x NW sort counts in two registers per lane");
+    __shared__ unsigned sCnt[NW][NK], sWarpShadow[NW], sWarpRegen[NW], sShadowBase;
     __shared__ unsigned long long sIssueA, sIssueB;
-    __shared__ unsigned short sPerm[256], sRegen[256];
+    __shared__ unsigned short sPerm[NT], sRegen[NT];
     const unsigned tid = threadIdx.x, warp = tid >> 5, lane = laneId();
     const uint32_t blockBase = blockIdx.x * blockDim.x;
     const unsigned long long limit = c->issueLimit;
@@ -454,11 +454,13 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
         if (lane == 0) sCnt[warp][k] = __popc(m);
     }
     __syncthreads();
-    // Every warp scans the 48 (key-major, warp-minor) counts itself: entry i = key * 8 + warp sits in
-    // lane i & 31 of e0 (keys 0-3) or e1 (keys 4, 5). No serial section and no second barrier.
+    // Every warp scans the NK x NW (key-major, warp-minor) counts itself: entry i = key * NW + warp sits in
+    // lane i & 31 of e0 (i < 32) or e1. No serial section and no second barrier.
     unsigned aBegin, alive;
     {
-        const unsigned v0 = sCnt[lane & 7u][lane >> 3], v1 = lane < 16u ? sCnt[lane & 7u][4u + (lane >> 3)] : 0u;
+        constexpr unsigned NE = NK * NW;
+        const unsigned i1 = lane + 32u;
+        const unsigned v0 = lane < NE ? sCnt[lane % NW][lane / NW] : 0u, v1 = i1 < NE ? sCnt[i1 % NW][i1 / NW] : 0u;
         unsigned s0 = v0, s1 = v1;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -467,21 +469,23 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
         }
         s1 += __shfl_sync(0xffffffffu, s0, 31);
         const unsigned e0 = s0 - v0, e1 = s1 - v1;                 // exclusive prefixes
-        const int i = key0 * 8 + (int) warp;
-        const unsigned x0 = __shfl_sync(0xffffffffu, e0, i & 31), x1 = __shfl_sync(0xffffffffu, e1, i & 31);
-        aBegin = __shfl_sync(0xffffffffu, e1, 0);                  // first slot of key kKeyMiss
-        alive = __shfl_sync(0xffffffffu, e1, 8);                   // first slot of key kNumKeys = live paths of this CTA
-        const unsigned dst = (i < 32 ? x0 : x1) + rank;
-        NG_CHECK(dst < 256u);
+        auto entry = [&](unsigned i) {                               // exclusive prefix of entry i (i may differ per lane)
+            const unsigned x0 = __shfl_sync(0xffffffffu, e0, i & 31u), x1 = __shfl_sync(0xffffffffu, e1, i & 31u);
+            return i < 32u ? x0 : x1;
+        };
+        const unsigned dst = entry((unsigned) key0 * NW + warp) + rank;
+        aBegin = entry(kKeyMiss * NW);                               // first slot of key kKeyMiss
+        alive = entry(kNumKeys * NW);                                // first slot of key kNumKeys = live paths of this CTA
+        NG_CHECK(dst < (unsigned) NT);
         sPerm[dst] = (unsigned short) tid;
     }
     // Sample indices for the slots known free up front: requested now, consumed after the shade step,
     // so that the round trip of the atomic hides behind it. (Indices past the limit are discarded by
     // regenSlot and handed out again: k_prepare clamps the counter.)
     // The last thread of the CTA is one of those free slots whenever there is any (they sort to the end).
-    const unsigned nA = 256u - aBegin;
+    const unsigned nA = (unsigned) NT - aBegin;
     if (tid == 0 && alive) atomicAdd(&c->sortCount[0], alive);   // closest rays traced = live slots
-    if (tid == 255u && nA) sIssueA = atomicAdd(&c->issue, (unsigned long long) nA);
+    if (tid == (unsigned) NT - 1u && nA) sIssueA = atomicAdd(&c->issue, (unsigned long long) nA);
     __syncthreads();
     const unsigned local = sPerm[tid];
     const uint32_t slot = blockBase + local;
@@ -561,7 +565,7 @@ __global__ void __launch_bounds__(256, 4) k_shadeRegen(DeviceScene sc, Pool pool
     const int nfin = __syncthreads_count(fin);
     unsigned preS = 0, preR = 0, totS = 0, totR = 0;
 #pragma unroll
-    for (unsigned w = 0; w < 8; ++w) {
+    for (unsigned w = 0; w < (unsigned) NW; ++w) {
         const unsigned a = sWarpShadow[w], b = sWarpRegen[w];
         if (w < warp) { preS += a; preR += b; }
         totS += a; totR += b;
@@ -814,7 +818,9 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 
 // ------------------------------------------------------------------------------------------
 template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
-    k_shadeRegen<I><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
+    static const bool small = getenv("NORI_GPU_SHADE_NT") && atoi(getenv("NORI_GPU_SHADE_NT")) == 128;   // sweep: profiles/r01_pipeline.md
+    if (small) k_shadeRegen<I, 128><<<pool.capacity / 128, 128, 0, st>>>(sc, pool, rp, c);
+    else k_shadeRegen<I, 256><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
 
 // ------------------------------------------------------------------------------------------
