@@ -279,7 +279,7 @@ def run_gpu(args):
                      "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": alg["closest"]["bytes_per_ray"],
                      "rays_per_launch": tot["closest_rays"] / launches_closest, "avg_launch_ms": avg_launch_ms,
                      "timing": "CUDA events around k_traceClosest on its stream; the interval also contains the previous iteration's splat kernels, which run concurrently with it (programmatic dependent launch), so `achieved` is a lower bound",
-                     "traffic_capture": "ncu --set full of one steady-state launch at 8 Mi path slots, about 5.4 M live rays (profiles/r01_kernels.md): ray records in/out only",
+                     "traffic_capture": "ncu --set full of one steady-state launch at 8 Mi path slots, about 5.4 M live rays (profiles/r01b_kernels.md): ray records in/out only",
                      "note": "algorithmic bytes are served by L1 (BVH + triangles of this scene are 0.17 MB): the kernel is issue-bound, not HBM-bound; see DESIGN.md and profiles/r01_trace.md"},
         "stages_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
         "Mrays_per_s": rays * world / (dev_ms / 1e3) / 1e6, "Gsegments_per_s": tot["segments"] * world / (dev_ms / 1e3) / 1e9,

@@ -40,7 +40,11 @@ def main():
         eng.trace(rays); eng.trace(rays, shadow=True); eng.trace_count(rays); eng.intersect(rays)
         pix = rng.integers(0, w * h, 500).astype(np.uint32)
         eng.sample_radiance(pix, rng.integers(0, 50, 500).astype(np.uint32))
-        eng.download_bitmap()
+        eng.download_bitmap(); eng.download_srgb8()
+        eng.upload_block(block); eng.upload_block(block2, accumulate=True)
+        if name in ("cbox_mis", "table_mis"):                                  # watertight ray-triangle mode
+            eng.render(sample_first=0, sample_last=2, intersect_mode=1)
+            eng.set_intersect_mode(1); eng.trace(rays); eng.trace(rays, shadow=True); eng.intersect(rays); eng.set_intersect_mode(0)
         if name == "bunny_normals":
             eng.render(stream_mode=0, sample_first=0, sample_last=3)          # block-seeded stream
         pos = (rng.random((4000, 2)) * [w, h]).astype(np.float32)
@@ -55,7 +59,8 @@ def main():
         out = eng.bsdf_sample(bt, p, wi, xi)
         eng.bsdf_eval_pdf(bt, p, wi, out[0])
     for wid in range(7):
-        eng.warp(wid, xi, 0.3)
+        pts, _ = eng.warp(wid, xi, 0.3)
+        eng.warp_pdf(wid, pts, 0.3)
     eng.pcg32_uints(42, 54, 100, advance=1000)
     eng.close()
     print("sanitize pass complete")
