@@ -184,7 +184,18 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
         nV += meshes[i].nV; nF += meshes[i].nF;
     }
     REQUIRE(nF > 0 && nF < (1u << 28), "upload_meshes: triangle count out of range");
-    std::vector<float4> vpos(nV), vnrm(nV); std::vector<float2> vuv(nV); std::vector<uint4> tris(nF);
+    // The Mesh buffers cross the bus as they are (12 + 12 + 8 B per vertex, 12 B per face) and are padded,
+    // concatenated and range-checked on the device (k_packVerts / k_packTris); only the per-mesh records and
+    // the emitters' area tables are put together here.
+    ctx->nTris = (uint32_t) nF; ctx->nVerts = (uint32_t) nV;
+    CK(cudaMalloc((void **) &ctx->d_vpos, nV * sizeof(float4))); CK(cudaMalloc((void **) &ctx->d_vnrm, nV * sizeof(float4)));
+    CK(cudaMalloc((void **) &ctx->d_vuv, nV * sizeof(float2))); CK(cudaMalloc((void **) &ctx->d_tris, nF * sizeof(uint4)));
+    size_t stageFloats = 0, stageIdx = 0;
+    for (int i = 0; i < n; ++i) { stageFloats = std::max(stageFloats, (size_t) meshes[i].nV * 8); stageIdx = std::max(stageIdx, (size_t) meshes[i].nF * 3); }
+    DevBuf<float> stageV[2]; DevBuf<uint32_t> stageF[2]; DevBuf<unsigned int> bad;
+    for (int k = 0; k < (n > 1 ? 2 : 1); ++k) { CK(stageV[k].alloc(std::max<size_t>(1, stageFloats))); CK(stageF[k].alloc(std::max<size_t>(1, stageIdx))); }
+    CK(bad.alloc(1)); CK(cudaMemsetAsync(bad.p, 0, sizeof(unsigned int), ctx->stream));
+    cudaEvent_t stageFree[2] = {nullptr, nullptr};
     std::vector<float> cdf;
     size_t vo = 0, fo = 0;
     for (int i = 0; i < n; ++i) {
@@ -196,15 +207,17 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
         mi.alpha = b.alpha; mi.intIOR = b.intIOR; mi.extIOR = b.extIOR; mi.ks = b.ks;
         mi.emitter = -1; mi.hasN = m.N != nullptr; mi.hasUV = m.UV != nullptr;
         mi.triOffset = (uint32_t) fo; mi.nTris = m.nF; mi.vertOffset = (uint32_t) vo; mi.nVerts = m.nV;
-        for (uint32_t v = 0; v < m.nV; ++v) {
-            vpos[vo + v] = make_float4(m.V[3 * v], m.V[3 * v + 1], m.V[3 * v + 2], 0.f);
-            vnrm[vo + v] = m.N ? make_float4(m.N[3 * v], m.N[3 * v + 1], m.N[3 * v + 2], 0.f) : make_float4(0, 0, 0, 0);
-            vuv[vo + v] = m.UV ? make_float2(m.UV[2 * v], m.UV[2 * v + 1]) : make_float2(0, 0);
-        }
-        for (uint32_t f = 0; f < m.nF; ++f) {
-            uint32_t a = m.F[3 * f], bb = m.F[3 * f + 1], c = m.F[3 * f + 2];
-            REQUIRE(a < m.nV && bb < m.nV && c < m.nV, "upload_meshes: face index out of range");
-            tris[fo + f] = make_uint4((uint32_t) vo + a, (uint32_t) vo + bb, (uint32_t) vo + c, (uint32_t) i);
+        {   // two staging buffers: the copy of mesh i + 1 overlaps the packing of mesh i
+            const int k = i & 1;
+            if (stageFree[k]) CK(cudaEventSynchronize(stageFree[k])); else CK(cudaEventCreateWithFlags(&stageFree[k], cudaEventDisableTiming));
+            float *dV = stageV[k].p, *dN = m.N ? dV + 3 * (size_t) m.nV : nullptr, *dUV = m.UV ? dV + 6 * (size_t) m.nV : nullptr;
+            CK(cudaMemcpyAsync(dV, m.V, (size_t) m.nV * 12, cudaMemcpyHostToDevice, ctx->stream));
+            if (m.N) CK(cudaMemcpyAsync(dN, m.N, (size_t) m.nV * 12, cudaMemcpyHostToDevice, ctx->stream));
+            if (m.UV) CK(cudaMemcpyAsync(dUV, m.UV, (size_t) m.nV * 8, cudaMemcpyHostToDevice, ctx->stream));
+            if (m.nF) CK(cudaMemcpyAsync(stageF[k].p, m.F, (size_t) m.nF * 12, cudaMemcpyHostToDevice, ctx->stream));
+            launchPackMesh(dV, dN, dUV, stageF[k].p, m.nV, m.nF, (uint32_t) vo, (uint32_t) i, ctx->d_vpos + vo, ctx->d_vnrm + vo, ctx->d_vuv + vo,
+                           ctx->d_tris + fo, bad.p, ctx->stream);
+            CK(cudaEventRecord(stageFree[k], ctx->stream));
         }
         if (m.is_emitter) {
             // `area` emitter: DiscretePDF over triangle areas (Mesh::surfaceArea src/mesh.cpp:43-49;
@@ -216,8 +229,10 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
             e.cdfOffset = (uint32_t) cdf.size(); e.nTris = m.nF; e.triOffset = (uint32_t) fo;
             cdf.push_back(0.0f);
             for (uint32_t f = 0; f < m.nF; ++f) {
-                const float4 &A = vpos[vo + m.F[3 * f]], &B = vpos[vo + m.F[3 * f + 1]], &C = vpos[vo + m.F[3 * f + 2]];
-                V3 p0 = mk(A.x, A.y, A.z), p1 = mk(B.x, B.y, B.z), p2 = mk(C.x, C.y, C.z);
+                const uint32_t ia = m.F[3 * (size_t) f], ib = m.F[3 * (size_t) f + 1], ic = m.F[3 * (size_t) f + 2];
+                REQUIRE(ia < m.nV && ib < m.nV && ic < m.nV, "upload_meshes: face index out of range");
+                const float *A = m.V + 3 * (size_t) ia, *B = m.V + 3 * (size_t) ib, *C = m.V + 3 * (size_t) ic;
+                V3 p0 = mk(A[0], A[1], A[2]), p1 = mk(B[0], B[1], B[2]), p2 = mk(C[0], C[1], C[2]);
                 volatile float area = 0.5f * sqrtf(squaredNorm(cross(p1 - p0, p2 - p0)));
                 cdf.push_back(cdf.back() + area);
             }
@@ -234,19 +249,17 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
         ctx->meshes.push_back(mi);
         vo += m.nV; fo += m.nF;
     }
-    ctx->nTris = (uint32_t) nF; ctx->nVerts = (uint32_t) nV;
-    CK(cudaMalloc((void **) &ctx->d_vpos, nV * sizeof(float4))); CK(cudaMalloc((void **) &ctx->d_vnrm, nV * sizeof(float4)));
-    CK(cudaMalloc((void **) &ctx->d_vuv, nV * sizeof(float2))); CK(cudaMalloc((void **) &ctx->d_tris, nF * sizeof(uint4)));
     CK(cudaMalloc((void **) &ctx->d_meshes, ctx->meshes.size() * sizeof(MeshInfo)));
     CK(cudaMalloc((void **) &ctx->d_emitters, std::max<size_t>(1, ctx->emitters.size()) * sizeof(EmitterInfo)));
     CK(cudaMalloc((void **) &ctx->d_cdf, std::max<size_t>(1, cdf.size()) * sizeof(float)));
-    CK(cudaMemcpy(ctx->d_vpos, vpos.data(), nV * sizeof(float4), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->d_vnrm, vnrm.data(), nV * sizeof(float4), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->d_vuv, vuv.data(), nV * sizeof(float2), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->d_tris, tris.data(), nF * sizeof(uint4), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->d_meshes, ctx->meshes.data(), ctx->meshes.size() * sizeof(MeshInfo), cudaMemcpyHostToDevice));
-    if (!ctx->emitters.empty()) CK(cudaMemcpy(ctx->d_emitters, ctx->emitters.data(), ctx->emitters.size() * sizeof(EmitterInfo), cudaMemcpyHostToDevice));
-    if (!cdf.empty()) CK(cudaMemcpy(ctx->d_cdf, cdf.data(), cdf.size() * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpyAsync(ctx->d_meshes, ctx->meshes.data(), ctx->meshes.size() * sizeof(MeshInfo), cudaMemcpyHostToDevice, ctx->stream));
+    if (!ctx->emitters.empty()) CK(cudaMemcpyAsync(ctx->d_emitters, ctx->emitters.data(), ctx->emitters.size() * sizeof(EmitterInfo), cudaMemcpyHostToDevice, ctx->stream));
+    if (!cdf.empty()) CK(cudaMemcpyAsync(ctx->d_cdf, cdf.data(), cdf.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    unsigned int nBad = 0;
+    CK(cudaMemcpyAsync(&nBad, bad.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
+    for (cudaEvent_t e : stageFree) if (e) cudaEventDestroy(e);
+    if (nBad) { freeScene(ctx); ctx->err = "upload_meshes: face index out of range"; return NORI_GPU_EINVAL; }
     return NORI_GPU_OK;
 }
 

@@ -105,6 +105,8 @@ void launchWarpPdf(int id, float param, int n, const float *pts3, float *pdf, cu
 void launchPcg32(uint64_t initstate, uint64_t initseq, int64_t advance, int n, uint32_t *out, cudaStream_t st);
 void launchSplatList(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
 void launchSplatOrdered(const DeviceScene &sc, int n, const float2 *pos, const float *rgb, float *block, unsigned long long *dropped, cudaStream_t st);
+void launchPackMesh(const float *V, const float *N, const float *UV, const uint32_t *F, uint32_t nV, uint32_t nF, uint32_t vertOffset, uint32_t mesh,
+                    float4 *vpos, float4 *vnrm, float2 *vuv, uint4 *tris, unsigned int *badIndex, cudaStream_t st);
 void launchToBitmap(const float *block, int W, int H, int border, float *rgb, cudaStream_t st);
 void launchToSRGB8(const float *block, int W, int H, int border, uint8_t *rgb8, cudaStream_t st);
 void launchAddBlock(float *dst, const float *src, size_t nFloats, cudaStream_t st);

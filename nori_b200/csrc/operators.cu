@@ -234,6 +234,31 @@ void launchSplatOrdered(const DeviceScene &sc, int n, const float2 *pos, const f
     if (n > 0) k_splatOrdered<<<gridFor(cells), 256, 0, st>>>(sc, n, pos, rgb, block, dropped);
 }
 
+/// Scene flattening on the device: the Mesh buffers as the reference keeps them (m_V / m_N 3 x nV, m_UV 2 x nV,
+/// m_F 3 x nF, column-major, include/nori/mesh.h:172-175) arrive as raw copies; these two kernels write the
+/// padded, concatenated arrays the traversal and shading kernels read (16-byte vertex records, global indices).
+__global__ void k_packVerts(const float *__restrict__ V, const float *__restrict__ N, const float *__restrict__ UV, uint32_t nV,
+                            float4 *__restrict__ vpos, float4 *__restrict__ vnrm, float2 *__restrict__ vuv) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nV) return;
+    vpos[v] = make_float4(V[3 * (size_t) v], V[3 * (size_t) v + 1], V[3 * (size_t) v + 2], 0.f);
+    vnrm[v] = N ? make_float4(N[3 * (size_t) v], N[3 * (size_t) v + 1], N[3 * (size_t) v + 2], 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+    vuv[v] = UV ? make_float2(UV[2 * (size_t) v], UV[2 * (size_t) v + 1]) : make_float2(0.f, 0.f);
+}
+__global__ void k_packTris(const uint32_t *__restrict__ F, uint32_t nF, uint32_t nV, uint32_t vertOffset, uint32_t mesh,
+                           uint4 *__restrict__ tris, unsigned int *badIndex) {
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nF) return;
+    const uint32_t a = F[3 * (size_t) f], b = F[3 * (size_t) f + 1], c = F[3 * (size_t) f + 2];
+    if (a >= nV || b >= nV || c >= nV) { atomicAdd(badIndex, 1u); tris[f] = make_uint4(vertOffset, vertOffset, vertOffset, mesh); return; }
+    tris[f] = make_uint4(vertOffset + a, vertOffset + b, vertOffset + c, mesh);
+}
+void launchPackMesh(const float *V, const float *N, const float *UV, const uint32_t *F, uint32_t nV, uint32_t nF, uint32_t vertOffset, uint32_t mesh,
+                    float4 *vpos, float4 *vnrm, float2 *vuv, uint4 *tris, unsigned int *badIndex, cudaStream_t st) {
+    if (nV) k_packVerts<<<gridFor((int) nV), 256, 0, st>>>(V, N, UV, nV, vpos, vnrm, vuv);
+    if (nF) k_packTris<<<gridFor((int) nF), 256, 0, st>>>(F, nF, nV, vertOffset, mesh, tris, badIndex);
+}
+
 /// ImageBlock::toBitmap (src/block.cpp:57-63; Color4f::divideByFilterWeight, color.h:112-117)
 __global__ void k_toBitmap(const float4 *__restrict__ block, int W, int H, int border, float *__restrict__ rgb) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
