@@ -140,6 +140,12 @@ int nori_gpu_upload_block(nori_gpu_ctx *ctx, const float *rgbw, int accumulate);
  * the accumulator is a device array of block_floats() floats that NCCL reduces in place. */
 int nori_gpu_block_device_ptr(nori_gpu_ctx *ctx, void **dptr, uint64_t *n_floats);
 int nori_gpu_block_dims(const nori_gpu_ctx *ctx, int *rows, int *cols, int *border);
+/* The same sum inside ONE process holding a context per GPU: the accumulators of ctxs[0..n) (same camera and
+ * filter, one device each) are summed into ctxs[root] with one ncclReduce over NVLink (libnccl.so.2, resolved at
+ * run time; n == 1 is a no-op). The other contexts keep their own partial block. */
+int nori_gpu_reduce_blocks(nori_gpu_ctx *const *ctxs, int n, int root);
+/* Number of CUDA devices visible to the library (0 without a driver). */
+int nori_gpu_device_count(void);
 int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on);   /* per-stage CUDA-event timing (serialises stages) */
 int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n_paths);
 /* Mesh::rayIntersect variant (src/mesh.cpp:51-88) used by the raw operators below (trace, trace_device,

@@ -8,6 +8,9 @@
 #include <cstdlib>
 #include <cmath>
 #include <algorithm>
+#include <map>
+#include <mutex>
+#include <dlfcn.h>
 
 using namespace ng;
 
@@ -469,6 +472,83 @@ int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode) {
     REQUIRE(mode == NORI_ISECT_REFERENCE_MT || mode == NORI_ISECT_WATERTIGHT, "set_intersect_mode: unknown mode");
     ctx->isectMode = mode;
     return NORI_GPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Cross-device sum of ImageBlocks inside one process: `result.put(block)` (src/block.cpp:105-114) between
+// the contexts of several GPUs as ONE ncclReduce over NVLink / NVSwitch. (One process per GPU — bench.py,
+// torchrun — does the same reduce through torch.distributed on nori_gpu_block_device_ptr.)
+// NCCL is resolved at run time (libnccl.so.2): a single-device build or box never needs it.
+namespace {
+typedef struct ncclComm *ncclComm_t;                  // declarations after nccl.h (NCCL 2.x, stable C ABI)
+struct NcclApi {
+    void *lib = nullptr;
+    int (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Reduce)(const void *, void *, size_t, int /*ncclDataType_t*/, int /*ncclRedOp_t*/, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    std::string error;
+    std::map<std::vector<int>, std::vector<ncclComm_t>> comms;   // one communicator set per device list
+    std::mutex lock;
+};
+constexpr int kNcclFloat32 = 7, kNcclSum = 0;         // nccl.h: ncclFloat32, ncclSum
+
+NcclApi &nccl() {
+    static NcclApi api;
+    if (api.lib || !api.error.empty()) return api;
+    const char *names[] = {getenv("NORI_GPU_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names) { if (nm && (api.lib = dlopen(nm, RTLD_NOW | RTLD_LOCAL))) break; }
+    if (!api.lib) { api.error = std::string("NCCL is not available (") + dlerror() + ")"; return api; }
+    auto sym = [&](const char *n) { void *f = dlsym(api.lib, n); if (!f) api.error = std::string("libnccl lacks ") + n; return f; };
+    api.CommInitAll = (decltype(api.CommInitAll)) sym("ncclCommInitAll");
+    api.CommDestroy = (decltype(api.CommDestroy)) sym("ncclCommDestroy");
+    api.Reduce = (decltype(api.Reduce)) sym("ncclReduce");
+    api.GroupStart = (decltype(api.GroupStart)) sym("ncclGroupStart");
+    api.GroupEnd = (decltype(api.GroupEnd)) sym("ncclGroupEnd");
+    api.GetErrorString = (decltype(api.GetErrorString)) sym("ncclGetErrorString");
+    return api;
+}
+} // namespace
+
+int nori_gpu_reduce_blocks(nori_gpu_ctx *const *ctxs, int n, int root) {
+    if (!ctxs || n < 1 || root < 0 || root >= n || !ctxs[root]) return NORI_GPU_EINVAL;
+    nori_gpu_ctx *ctx = ctxs[root];                   // error messages land on the root context
+    std::vector<int> devs((size_t) n);
+    for (int i = 0; i < n; ++i) {
+        REQUIRE(ctxs[i] && ctxs[i]->d_block, "reduce_blocks: a context has no ImageBlock yet");
+        REQUIRE(ctxs[i]->blockFloats == ctx->blockFloats, "reduce_blocks: the contexts hold ImageBlocks of different sizes");
+        devs[(size_t) i] = ctxs[i]->device;
+        for (int j = 0; j < i; ++j) REQUIRE(ctxs[j]->device != ctxs[i]->device, "reduce_blocks: one context per device");
+    }
+    if (n == 1) return NORI_GPU_OK;
+    NcclApi &api = nccl();
+    if (!api.error.empty()) { ctx->err = "reduce_blocks: " + api.error; return NORI_GPU_EUNSUPPORTED; }
+    std::lock_guard<std::mutex> guard(api.lock);
+#define NCK(call) do { int r_ = (call); if (r_ != 0) { ctx->err = std::string(#call) + " failed: " + api.GetErrorString(r_); return NORI_GPU_ECUDA; } } while (0)
+    auto it = api.comms.find(devs);
+    if (it == api.comms.end()) {
+        std::vector<ncclComm_t> comms((size_t) n);
+        NCK(api.CommInitAll(comms.data(), n, devs.data()));
+        it = api.comms.emplace(devs, comms).first;
+    }
+    for (int i = 0; i < n; ++i) { CK(cudaSetDevice(devs[(size_t) i])); CK(cudaStreamSynchronize(ctxs[i]->stream)); }
+    NCK(api.GroupStart());
+    for (int i = 0; i < n; ++i) {
+        CK(cudaSetDevice(devs[(size_t) i]));
+        NCK(api.Reduce(ctxs[i]->d_block, ctxs[i]->d_block, ctx->blockFloats, kNcclFloat32, kNcclSum, root, it->second[(size_t) i], ctxs[i]->stream));
+    }
+    NCK(api.GroupEnd());
+    for (int i = 0; i < n; ++i) { CK(cudaSetDevice(devs[(size_t) i])); CK(cudaStreamSynchronize(ctxs[i]->stream)); }
+    CK(cudaSetDevice(ctx->device));
+#undef NCK
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_device_count(void) {
+    int n = 0;
+    return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
 }
 
 int nori_gpu_block_dims(const nori_gpu_ctx *ctx, int *rows, int *cols, int *border) {

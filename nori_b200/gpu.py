@@ -25,7 +25,7 @@ EXPORTS = [
     "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",
     "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel",
     "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_download_srgb8", "nori_gpu_upload_block", "nori_gpu_block_device_ptr",
-    "nori_gpu_block_dims", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
+    "nori_gpu_block_dims", "nori_gpu_reduce_blocks", "nori_gpu_device_count", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance",
@@ -100,6 +100,8 @@ def load_library() -> C.CDLL:
     L.nori_gpu_block_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
     L.nori_gpu_block_dims.argtypes = [vp, C.POINTER(ip), C.POINTER(ip), C.POINTER(ip)]
     L.nori_gpu_set_profiling.argtypes = [vp, ip]
+    L.nori_gpu_reduce_blocks.argtypes = [C.POINTER(vp), ip, ip]
+    L.nori_gpu_device_count.argtypes = []
     L.nori_gpu_set_pool_size.argtypes = [vp, C.c_uint32]
     L.nori_gpu_set_intersect_mode.argtypes = [vp, ip]
     L.nori_gpu_trace.argtypes = [vp, vp, ip, ip, vp, vp, vp]
@@ -125,6 +127,19 @@ def _f32(a, shape=None):
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def device_count() -> int:
+    return int(load_library().nori_gpu_device_count())
+
+
+def reduce_blocks(engines, root: int = 0):
+    """Sum the ImageBlocks of several engines (one per GPU, same process) into engines[root]: one ncclReduce."""
+    L = load_library()
+    hs = (C.c_void_p * len(engines))(*[e.h for e in engines])
+    rc = L.nori_gpu_reduce_blocks(hs, len(engines), int(root))
+    if rc != 0:
+        raise NoriGpuError(f"[{rc}] {L.nori_gpu_last_error(engines[root].h).decode()}")
 
 
 class Engine:

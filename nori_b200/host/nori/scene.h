@@ -5,6 +5,7 @@
 // Reference: include/nori/{scene,mesh,bsdf,emitter,camera,rfilter,sampler,integrator,block,bitmap}.h
 #pragma once
 #include "object.h"
+#include <map>
 #include <memory>
 
 struct nori_gpu_ctx;
@@ -198,7 +199,7 @@ private:
     Integrator *m_integrator = nullptr;
     Sampler *m_sampler = nullptr;
     Camera *m_camera = nullptr;
-    mutable nori_gpu_ctx *m_ctx = nullptr;
+    mutable std::map<int, nori_gpu_ctx *> m_ctx;        // device -> context holding this scene
 };
 
 /// Device context for operators that need no scene (BSDF::sample/eval/pdf, Warp::*): created on first use.
@@ -215,6 +216,11 @@ struct RenderReport { double ms = 0, msamples = 0, mrays = 0, gsegments = 0; uin
 /// on the device (nori_gpu_upload_block + NoriGpuRenderDesc::clear = 0).
 void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, int device, RenderReport *report,
                const ImageBlock *resumeFrom = nullptr);
+/// The same over several GPUs of the box: device k renders the k-th contiguous part of [sampleFirst, sampleLast)
+/// (per-sample streams: the union of the parts is the single-GPU sample set) on its own host thread, then ONE
+/// nori_gpu_reduce_blocks (ncclReduce over NVLink) sums the accumulators into the first device's, which is downloaded.
+void renderGpuMulti(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, const std::vector<int> &devices,
+                    RenderReport *report);
 /// Checkpoint file of an ImageBlock (RGBW accumulator + the sample range it holds): raw little-endian.
 void saveCheckpoint(const std::string &path, const ImageBlock &block, uint32_t sampleFirst, uint32_t sampleLast);
 void loadCheckpoint(const std::string &path, ImageBlock &block, uint32_t &sampleFirst, uint32_t &sampleLast);

@@ -3,6 +3,7 @@
 // <scene>.exr and <scene>.png next to the scene file.
 //
 //   nori_b200 [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] scene.xml
+//   nori_b200 --devices 0,1,2,3 scene.xml                              sample ranges over several GPUs, one NCCL reduce
 //   nori_b200 --first 0 --last 64 --checkpoint part.blk scene.xml      render a sample range, keep the accumulator
 //   nori_b200 --resume part.blk --last 256 scene.xml                   continue from it (samples [64, 256) are added)
 //   nori_b200 --dump FILE scene.xml     parse only; write the flattened descriptors (tests; no GPU)
@@ -59,7 +60,7 @@ void dumpScene(const Scene *scene, const std::string &path) {
 }
 
 void render(const Scene *scene, const std::string &outName, int device, int sppOverride, long first, long last, bool png,
-            const std::string &resumeFile, const std::string &checkpointFile) {
+            const std::string &resumeFile, const std::string &checkpointFile, const std::vector<int> &devices) {
     const Camera *camera = scene->getCamera();
     const uint32_t spp = sppOverride > 0 ? (uint32_t) sppOverride : (uint32_t) scene->getSampler()->getSampleCount();
     uint32_t s0 = first >= 0 ? (uint32_t) first : 0u, s1 = last >= 0 ? (uint32_t) last : spp, held0 = 0;
@@ -73,10 +74,16 @@ void render(const Scene *scene, const std::string &outName, int device, int sppO
         s0 = heldLast;
     }
     if (s1 <= s0) throw NoriException("empty sample range [%d, %d)", (int) s0, (int) s1);
-    scene->gpu(device);                                       // upload + Accel::build (Scene::activate does this in the reference)
-    std::cout << "Rendering .. " << std::flush;
     RenderReport rep;
-    renderGpu(scene, result, s0, s1, device, &rep, held.get());
+    if (devices.size() > 1) {
+        if (held) throw NoriException("--resume and --devices cannot be combined");
+        std::cout << "Rendering on " << devices.size() << " GPUs .. " << std::flush;
+        renderGpuMulti(scene, result, s0, s1, devices, &rep);
+    } else {
+        scene->gpu(device);                                   // upload + Accel::build (Scene::activate does this in the reference)
+        std::cout << "Rendering .. " << std::flush;
+        renderGpu(scene, result, s0, s1, device, &rep, held.get());
+    }
     if (!checkpointFile.empty()) saveCheckpoint(checkpointFile, result, held ? held0 : s0, s1);
     std::cout << "done. (took " << timeString(rep.ms) << ": " << rep.msamples << " Msamples/s, " << rep.mrays << " Mrays/s, "
               << rep.gsegments << " Gsegments/s";
@@ -92,6 +99,7 @@ void render(const Scene *scene, const std::string &outName, int device, int sppO
 int main(int argc, char **argv) {
     std::string sceneFile, dumpFile, outName, resumeFile, checkpointFile;
     int device = 0, spp = 0; long first = -1, last = -1; bool png = true;
+    std::vector<int> devices;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto value = [&](const char *what) -> std::string {
@@ -99,6 +107,7 @@ int main(int argc, char **argv) {
             return argv[++i];
         };
         if (a == "--device") device = atoi(value("--device").c_str());
+        else if (a == "--devices") { for (const std::string &t : tokenize(value("--devices"), ",")) devices.push_back(toInt(t)); if (!devices.empty()) device = devices[0]; }
         else if (a == "--spp") spp = atoi(value("--spp").c_str());
         else if (a == "--first") first = atol(value("--first").c_str());
         else if (a == "--last") last = atol(value("--last").c_str());
@@ -125,7 +134,7 @@ int main(int argc, char **argv) {
         else sceneFile = a;
     }
     if (sceneFile.empty()) {
-        std::cerr << "Syntax: " << argv[0] << " [--device N] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--resume FILE] [--checkpoint FILE] [--dump FILE] <scene.xml>" << std::endl;
+        std::cerr << "Syntax: " << argv[0] << " [--device N | --devices A,B,..] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--resume FILE] [--checkpoint FILE] [--dump FILE] <scene.xml>" << std::endl;
         return -1;
     }
     try {
@@ -139,7 +148,7 @@ int main(int argc, char **argv) {
             const size_t dot = sceneFile.find_last_of('.');
             outName = dot == std::string::npos || (slash != std::string::npos && dot < slash) ? sceneFile : sceneFile.substr(0, dot);
         }
-        render(scene, outName, device, spp, first, last, png, resumeFile, checkpointFile);
+        render(scene, outName, device, spp, first, last, png, resumeFile, checkpointFile, devices);
     } catch (const std::exception &e) {
         std::cerr << "Fatal error: " << e.what() << std::endl;
         return -1;

@@ -5,6 +5,8 @@
 #include <nori_gpu.h>
 #include <algorithm>
 #include <cstring>
+#include <mutex>
+#include <thread>
 #include <fstream>
 #include <iostream>
 
@@ -31,7 +33,7 @@ static void check(nori_gpu_ctx *ctx, int rc, const char *what) { gpuCheck(ctx, r
 Scene::Scene(const PropertyList &) {}
 
 Scene::~Scene() {
-    if (m_ctx) nori_gpu_destroy(m_ctx);
+    for (auto &kv : m_ctx) nori_gpu_destroy(kv.second);
     delete m_sampler; delete m_camera; delete m_integrator;
     for (Mesh *m : m_meshes) delete m;                       // (the reference leaks its meshes)
 }
@@ -72,7 +74,12 @@ std::string Scene::toString() const {
 }
 
 nori_gpu_ctx *Scene::gpu(int device) const {
-    if (m_ctx) return m_ctx;
+    static std::mutex lock;                                   // renderGpuMulti: one host thread per device
+    {
+        std::lock_guard<std::mutex> g(lock);
+        auto it = m_ctx.find(device);
+        if (it != m_ctx.end()) return it->second;
+    }
     nori_gpu_ctx *ctx = nullptr;
     if (nori_gpu_create(&ctx, device) != NORI_GPU_OK)
         throw NoriException("nori_gpu_create: %s (nori_b200 has no CPU path)", nori_gpu_last_error(nullptr));
@@ -108,7 +115,8 @@ nori_gpu_ctx *Scene::gpu(int device) const {
         nori_gpu_destroy(ctx);
         throw;
     }
-    m_ctx = ctx;
+    std::lock_guard<std::mutex> g(lock);
+    m_ctx[device] = ctx;
     return ctx;
 }
 
@@ -225,6 +233,42 @@ void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const u
     const uint32_t slots = (uint32_t) std::min<uint64_t>(1u << 20, std::max<uint64_t>(4096, ((uint64_t) n + 255) / 256 * 256));
     check(ctx, nori_gpu_set_pool_size(ctx, slots), "nori_gpu_set_pool_size");
     check(ctx, nori_gpu_sample_radiance(ctx, &d, n, pixel, sample, rgb, nullptr), "nori_gpu_sample_radiance");
+}
+
+void renderGpuMulti(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uint32_t sampleLast, const std::vector<int> &devices,
+                    RenderReport *report) {
+    const int n = (int) devices.size();
+    if (n < 1) throw NoriException("renderGpuMulti: no devices");
+    const uint32_t total = sampleLast - sampleFirst;
+    if ((uint32_t) n > total) throw NoriException("renderGpuMulti: %d devices for %d samples per pixel", n, (int) total);
+    std::vector<nori_gpu_ctx *> ctxs((size_t) n);
+    std::vector<NoriGpuRenderStats> stats((size_t) n);
+    std::vector<std::string> errors((size_t) n);
+    std::vector<std::thread> workers;
+    for (int k = 0; k < n; ++k)
+        workers.emplace_back([&, k]() {
+            try {
+                nori_gpu_ctx *ctx = scene->gpu(devices[(size_t) k]);                      // upload + accel build per device (replicated scene)
+                ctxs[(size_t) k] = ctx;
+                const uint32_t s0 = sampleFirst + (uint32_t) ((uint64_t) total * k / n), s1 = sampleFirst + (uint32_t) ((uint64_t) total * (k + 1) / n);
+                const NoriGpuRenderDesc d = renderDesc(scene, s0, s1);
+                check(ctx, nori_gpu_render(ctx, &d, &stats[(size_t) k]), "nori_gpu_render");
+            } catch (const std::exception &e) { errors[(size_t) k] = e.what(); }
+        });
+    for (std::thread &w : workers) w.join();
+    for (const std::string &e : errors) if (!e.empty()) throw NoriException("%s", e);
+    check(ctxs[0], nori_gpu_reduce_blocks(ctxs.data(), n, 0), "nori_gpu_reduce_blocks");   // result.put(block) across devices
+    check(ctxs[0], nori_gpu_download_block(ctxs[0], result.data()), "nori_gpu_download_block");
+    if (report) {
+        *report = RenderReport();
+        uint64_t samples = 0, rays = 0, segs = 0;
+        for (const NoriGpuRenderStats &st : stats) {
+            report->ms = std::max(report->ms, (double) st.ms_total);                        // devices run side by side
+            samples += st.camera_samples; rays += st.closest_rays + st.shadow_rays; segs += st.segments;
+            report->dropped += st.dropped; report->launches += st.kernel_launches;
+        }
+        if (report->ms > 0) { report->msamples = samples / report->ms / 1e3; report->mrays = rays / report->ms / 1e3; report->gsegments = segs / report->ms / 1e6; }
+    }
 }
 
 void saveCheckpoint(const std::string &path, const ImageBlock &block, uint32_t sampleFirst, uint32_t sampleLast) {

@@ -205,3 +205,35 @@ def test_block_upload_resumes_and_merges(gpu_scene, scenes):
     np.testing.assert_array_equal(e.download_block(), first + second)
     with pytest.raises(Exception):
         e.upload_block(first[:-1])
+
+
+def test_reduce_blocks_in_process(engine, gpu_scene, scenes):
+    """nori_gpu_reduce_blocks: `result.put(block)` across the contexts of several GPUs in ONE process (ncclReduce).
+    With one GPU: n = 1 is a no-op and two contexts on one device are refused. With two or more (gpurun --gpus 2):
+    two sample ranges on two devices sum to the single-device image."""
+    from nori_b200.gpu import Engine, NoriGpuError, device_count, reduce_blocks
+    e = gpu_scene("cbox_mis")
+    whole, _ = e.render(sample_first=0, sample_last=6)
+    reduce_blocks([e])
+    np.testing.assert_array_equal(e.download_block(), whole)
+    other = Engine(0)
+    try:
+        other.load_scene(scenes("cbox_mis")); other.render(sample_first=0, sample_last=1)
+        with pytest.raises(NoriGpuError, match="one context per device"):
+            reduce_blocks([e, other])
+    finally:
+        other.close()
+    if device_count() < 2:
+        return
+    second = Engine(1)
+    try:
+        second.load_scene(scenes("cbox_mis"))
+        a, _ = e.render(sample_first=0, sample_last=3)
+        b, _ = second.render(sample_first=3, sample_last=6)
+        reduce_blocks([e, second], root=0)
+        got = e.download_block()
+        np.testing.assert_allclose(got, a + b, rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(got, whole, rtol=2e-4, atol=2e-4)
+        np.testing.assert_array_equal(second.download_block(), b)      # non-root keeps its partial block
+    finally:
+        second.close()

@@ -204,3 +204,18 @@ def test_cli_checkpoint_and_resume_equal_one_render(tmp_path):
     assert np.abs(c - a).mean() > 1e-4                       # the 6-sample image alone is a different (noisier) image
     r = subprocess.run([HOST_BIN, "--resume", blk, "--first", "3", "--last", "16", xml], capture_output=True, text=True, timeout=300)
     assert r.returncode != 0 and "cannot resume at 3" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_renders_over_several_devices(tmp_path):
+    """--devices A,B: sample ranges on one host thread per GPU + nori_gpu_reduce_blocks (NCCL) = the single-GPU image."""
+    from nori_b200.gpu import device_count
+    if device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    xml = os.path.join(HOST, "all_tags.xml")
+    one, two = str(tmp_path / "one"), str(tmp_path / "two")
+    for out, extra in ((one, []), (two, ["--devices", "0,1"])):
+        r = subprocess.run([HOST_BIN, "--no-png", "--out", out, "--spp", "16"] + extra + [xml], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+    assert "Rendering on 2 GPUs" in r.stdout
+    np.testing.assert_allclose(read_exr(two + ".exr"), read_exr(one + ".exr"), rtol=2e-4, atol=1e-5)
