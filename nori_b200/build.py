@@ -39,6 +39,27 @@ def _stale(target: str, deps) -> bool:
 LIB_CHECKED = os.path.join(HERE, "libnori_b200_checked.so")
 
 
+def build_variant(name: str, defines, verbose: bool = False) -> str:
+    """Experiment builds: the same sources with extra -D flags -> libnori_b200_<name>.so (select with NORI_GPU_LIB)."""
+    objdir = os.path.join(HERE, "build_" + name)
+    lib = os.path.join(HERE, "libnori_b200_%s.so" % name)
+    os.makedirs(objdir, exist_ok=True)
+    objs, procs = [], []
+    for s in SOURCES:
+        src, obj = os.path.join(CSRC, s), os.path.join(objdir, s.replace(".cu", ".o"))
+        objs.append(obj)
+        cmd = [_nvcc()] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for s, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0 or verbose:
+            sys.stderr.write(f"--- nvcc {s}\n{out}\n")
+        if p.returncode != 0:
+            raise RuntimeError("nvcc failed building " + lib)
+    subprocess.check_call([_nvcc(), "-shared", "-o", lib] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"])
+    return lib
+
+
 def build(force: bool = False, verbose: bool = False, checked: bool = False) -> str:
     """checked=True: the same sources with -DNORI_GPU_CHECKED (csrc/check.cuh: every pool / record / queue /
     frame index range-checked on the device) -> libnori_b200_checked.so, loaded when NORI_GPU_LIB names it."""

@@ -15,6 +15,9 @@
 
 namespace ng {
 
+#ifndef NORI_TRACE_SHARED_STACK
+#define NORI_TRACE_SHARED_STACK 0
+#endif
 constexpr int kFetchThreshold = 20;   // default: refill when fewer than this many lanes still traverse
 
 template <bool ANY_HIT, bool WT = false, class IO>
@@ -24,9 +27,25 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
     const int nodeExit = (tuning >> 8) & 0xff;                 // leave the node loop when fewer lanes than this still descend
     const unsigned lane = threadIdx.x & 31u;
     unsigned ltMask; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(ltMask));
-    int stack[kStackSize];
+    // Traversal stack: the first kSharedStack entries of every lane live in shared memory as [entry][thread], so a
+    // push or pop is one conflict-free wavefront whatever the lanes' stack depths are (bank = thread % 32); in
+    // local memory lanes at different depths touch different lines. Deeper entries (rare) overflow to local memory.
+    int sp = 0, cur = 0, leaf = 0;                             // leaf: postponed leaf link (< 0) or 0
+    constexpr int kSharedStack = NORI_TRACE_SHARED_STACK;
+    __shared__ int sStack[kSharedStack > 0 ? kSharedStack : 1][128];
+    int stack[kStackSize - kSharedStack];
+    const unsigned tix = threadIdx.x;
+    auto push = [&](int v) {
+        NG_CHECK(sp < kStackSize);
+        if (kSharedStack > 0 && sp < kSharedStack) sStack[sp][tix] = v; else stack[sp - kSharedStack] = v;
+        ++sp;
+    };
+    auto pop = [&]() -> int {
+        --sp;
+        return (kSharedStack > 0 && sp < kSharedStack) ? sStack[sp][tix] : stack[sp - kSharedStack];
+    };
     constexpr int kDone = 0x7fffffff;                          // no node left for this lane
-    int sp = 0, cur = kDone, leaf = 0;                         // leaf: postponed leaf link (< 0) or 0
+    cur = kDone;
     bool active = false;
     uint32_t rayIdx = 0xffffffffu, best = kNoHit;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
@@ -87,15 +106,14 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                     int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
                         if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
-                        NG_CHECK(sp < kStackSize);
-                        stack[sp++] = cr;
+                        push(cr);
                         cur = cl;
                     } else if (hl) cur = cl;
                     else if (hr) cur = cr;
-                    else cur = sp > 0 ? stack[--sp] : kDone;
+                    else cur = sp > 0 ? pop() : kDone;
                     if (cur < 0 && leaf == 0) {                // first leaf: postpone, keep descending
                         leaf = cur;
-                        cur = sp > 0 ? stack[--sp] : kDone;
+                        cur = sp > 0 ? pop() : kDone;
                     }
                 }
                 const bool searching = leaf == 0 && cur >= 0 && cur != kDone;
@@ -119,7 +137,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                 }
                 leaf = 0;
                 if (ANY_HIT && best != kNoHit) { cur = kDone; sp = 0; }
-                else if (cur < 0) { leaf = cur; cur = sp > 0 ? stack[--sp] : kDone; }   // a second leaf was reached meanwhile
+                else if (cur < 0) { leaf = cur; cur = sp > 0 ? pop() : kDone; }   // a second leaf was reached meanwhile
             }
             if (active && cur == kDone) {
                 active = false;
