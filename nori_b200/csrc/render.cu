@@ -428,15 +428,25 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
 ///     the shadow kernel adds the light sample there (kShadowToRecord); only what the record
 ///     cannot express (value = T * L, late samples) parks the slot until the next iteration.
 /// One atomic per CTA each for: sample indices (twice), shadow queue space, finished count.
+#ifndef NORI_SHADE_THREADS_PER_SM
+#define NORI_SHADE_THREADS_PER_SM 1024      // 64 registers per thread
+#endif
 template <int INTEGRATOR, int NT>
-__global__ void __launch_bounds__(NT, 1024 / NT) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
+__global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
     constexpr int NK = kNumKeys + 1, NW = NT / 32;
     static_assert(NK * NW <= 64 && (NW == 8 || NW == 4), "the warp scan below keeps the NK x NW sort counts in two registers per lane");
     __shared__ unsigned sCnt[NW][NK], sWarpShadow[NW], sWarpRegen[NW], sShadowBase;
     __shared__ unsigned long long sIssueA, sIssueB;
     __shared__ unsigned short sPerm[NT], sRegen[NT];
     const unsigned tid = threadIdx.x, warp = tid >> 5, lane = laneId();
+    // CTAs walk the pool from its END: the closest-hit pass before this kernel fetched slots in ascending order, so
+    // the rays and hit records it touched last are the ones still in L2; and this kernel then finishes at the low
+    // slots, where the next closest-hit pass starts.
+#ifdef NORI_SHADE_ASCENDING
     const uint32_t blockBase = blockIdx.x * blockDim.x;
+#else
+    const uint32_t blockBase = (gridDim.x - 1u - blockIdx.x) * blockDim.x;
+#endif
     const unsigned long long limit = c->issueLimit;
     const uint32_t passHint = c->passHint, lateBelow = c->completedPasses * rp.K;   // samples of closed passes are late
     // ---- CTA-local counting sort by what the slot needs -----------------------------------
