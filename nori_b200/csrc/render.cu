@@ -439,13 +439,13 @@ __global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeReg
     __shared__ unsigned long long sIssueA, sIssueB;
     __shared__ unsigned short sPerm[NT], sRegen[NT];
     const unsigned tid = threadIdx.x, warp = tid >> 5, lane = laneId();
-    // CTAs walk the pool from its END: the closest-hit pass before this kernel fetched slots in ascending order, so
+    // Experiment (-DNORI_SHADE_DESCENDING): CTAs walk the pool from its END: the closest-hit pass before this kernel fetched slots in ascending order, so
     // the rays and hit records it touched last are the ones still in L2; and this kernel then finishes at the low
     // slots, where the next closest-hit pass starts.
-#ifdef NORI_SHADE_ASCENDING
-    const uint32_t blockBase = blockIdx.x * blockDim.x;
-#else
+#ifdef NORI_SHADE_DESCENDING
     const uint32_t blockBase = (gridDim.x - 1u - blockIdx.x) * blockDim.x;
+#else
+    const uint32_t blockBase = blockIdx.x * blockDim.x;
 #endif
     const unsigned long long limit = c->issueLimit;
     const uint32_t passHint = c->passHint, lateBelow = c->completedPasses * rp.K;   // samples of closed passes are late
