@@ -219,3 +219,16 @@ def test_cli_renders_over_several_devices(tmp_path):
         assert r.returncode == 0, r.stderr
     assert "Rendering on 2 GPUs" in r.stdout
     np.testing.assert_allclose(read_exr(two + ".exr"), read_exr(one + ".exr"), rtol=2e-4, atol=1e-5)
+
+
+def test_cli_rejects_a_bad_checkpoint_before_touching_the_device(tmp_path):
+    """--resume reads and validates the checkpoint (magic, block size of this camera) before any GPU work."""
+    xml = os.path.join(HOST, "defaults.xml")
+    bad = tmp_path / "bad.blk"; bad.write_bytes(b"not a block")
+    r = subprocess.run([HOST_BIN, "--resume", str(bad), xml], capture_output=True, text=True, timeout=120)
+    assert r.returncode != 0 and "is not an ImageBlock checkpoint" in r.stderr
+    import struct
+    wrong = tmp_path / "wrong.blk"
+    wrong.write_bytes(b"NB2BLK1\0" + struct.pack("<3i2I", 7, 9, 2, 0, 4) + b"\0" * (7 * 9 * 16))
+    r = subprocess.run([HOST_BIN, "--resume", str(wrong), xml], capture_output=True, text=True, timeout=120)
+    assert r.returncode != 0 and "holds a 9x7 block" in r.stderr
