@@ -48,3 +48,15 @@ for bits in (2, 3, 4, 6):
     time_it(rays[order(bits)], f"bounce rays, sorted: {bits}-bit cell + octant")
 dirkey = np.argsort((np.arctan2(D[:, 1], D[:, 0]) * 8 // np.pi).astype(np.int64) * 64 + (np.arccos(np.clip(D[:, 2], -1, 1)) * 8 // np.pi).astype(np.int64), kind="stable")
 time_it(rays[dirkey], "bounce rays, sorted by direction bins only")
+
+# What a CTA of the shade kernel could do on its own: order the rays of each block of 256 consecutive slots
+octant = ((D[:, 0] < 0).astype(np.int64) | ((D[:, 1] < 0).astype(np.int64) << 1) | ((D[:, 2] < 0).astype(np.int64) << 2))
+base = rays[rng.permutation(m)]; oc = ((base[:, 4] < 0).astype(np.int64) | ((base[:, 5] < 0).astype(np.int64) << 1) | ((base[:, 6] < 0).astype(np.int64) << 2))
+for blk in (256, 1024, 4096):
+    key = (np.arange(m) // blk) * 8 + oc
+    time_it(base[np.argsort(key, kind="stable")], f"random order, octant-sorted within blocks of {blk}")
+q2 = np.clip(((base[:, 0:3] - lo) / (hi - lo + 1e-9) * 4).astype(np.int64), 0, 3)
+cell = q2[:, 0] | (q2[:, 1] << 2) | (q2[:, 2] << 4)
+for blk in (256, 4096):
+    key = (np.arange(m) // blk) * 512 + cell * 8 + oc
+    time_it(base[np.argsort(key, kind="stable")], f"random order, cell+octant-sorted within blocks of {blk}")
