@@ -56,6 +56,12 @@ enum { NORI_STREAM_BLOCK = 0, NORI_STREAM_PER_SAMPLE = 1 };
  * vertex (Moeller-Trumbore can); not in the reference, specified by oracle/noracle_math.h. */
 enum { NORI_ISECT_REFERENCE_MT = 0, NORI_ISECT_WATERTIGHT = 1 };
 
+/* Node layout read by the traversal kernels of nori_gpu_render / nori_gpu_trace*:
+ * FLOAT: 64-byte nodes, two child boxes in single precision (four 16-byte loads per visit).
+ * QUANTISED: 32-byte nodes, child boxes on a 15-bit grid over the scene box, rounded outwards (two loads per visit;
+ * half the node traffic for scenes whose tree does not fit the caches). Same tree, same triangle tests: same hits. */
+enum { NORI_ACCEL_FLOAT = 0, NORI_ACCEL_QUANTISED = 1 };
+
 /* One Mesh (include/nori/mesh.h:172-175): column-major Eigen buffers == C arrays below. */
 typedef struct {
     const float *V;        /* 3 x nV positions (world space; obj.cpp applies toWorld at load) */
@@ -122,6 +128,7 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
 int nori_gpu_set_camera(nori_gpu_ctx *ctx, const NoriGpuCameraDesc *cam);              /* camera.h:56-64 */
 int nori_gpu_set_filter(nori_gpu_ctx *ctx, float radius, const float table33[33]);     /* ImageBlock ctor table, src/block.cpp:31-39 */
 int nori_gpu_build_accel(nori_gpu_ctx *ctx, NoriGpuAccelStats *out);                   /* Accel::build (accel.h:45) — device BVH */
+int nori_gpu_set_accel_layout(nori_gpu_ctx *ctx, int layout);                          /* NORI_ACCEL_*; before or after build_accel */
 
 /* ---- the hot path: replaces render()'s parallel_for (src/main.cpp:93-121) -------------------- */
 int nori_gpu_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuRenderStats *out);

@@ -368,4 +368,48 @@ bool buildBvh(const float4 *d_vpos, const uint4 *d_tris, uint32_t N, const BvhPa
     return true;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Quantised node layout (include/nori_gpu.h: NORI_ACCEL_QUANTISED)
+__global__ void k_quantiseNodes(const float4 *__restrict__ nodes, uint32_t nNodes, double3 lo, double3 invCell, uint4 *__restrict__ q) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nNodes) return;
+    const float4 n0 = nodes[4 * (size_t) i], n1 = nodes[4 * (size_t) i + 1], n2 = nodes[4 * (size_t) i + 2], n3 = nodes[4 * (size_t) i + 3];
+    auto qmin = [](float v, double l, double ic) { const double x = floor(((double) v - l) * ic); return (uint32_t) fmin(fmax(x, 0.0), 32767.0) | 0x8000u; };
+    auto qmax = [](float v, double l, double ic) { const double x = ceil(((double) v - l) * ic); return (uint32_t) fmin(fmax(x, 0.0), 32767.0) | 0x8000u; };
+    auto axis = [&](float mn, float mx, double l, double ic) { return qmin(mn, l, ic) | (qmax(mx, l, ic) << 16); };
+    uint4 a, b;
+    a.x = axis(n0.x, n0.y, lo.x, invCell.x); a.y = axis(n0.z, n0.w, lo.y, invCell.y); a.z = axis(n2.x, n2.y, lo.z, invCell.z); a.w = __float_as_uint(n3.x);
+    b.x = axis(n1.x, n1.y, lo.x, invCell.x); b.y = axis(n1.z, n1.w, lo.y, invCell.y); b.z = axis(n2.z, n2.w, lo.z, invCell.z); b.w = __float_as_uint(n3.y);
+    q[2 * (size_t) i] = a; q[2 * (size_t) i + 1] = b;
+}
+
+bool quantiseNodes(BvhDevice &bvh, float inflate, cudaStream_t st, std::string &err) {
+    if (!bvh.nodes || !bvh.nNodes) { err = "quantiseNodes: no BVH"; return false; }
+    if (bvh.qnodes) return true;
+    double diag2 = 0, maxAbs = 0;
+    for (int k = 0; k < 3; ++k) {
+        diag2 += ((double) bvh.sceneHi[k] - bvh.sceneLo[k]) * ((double) bvh.sceneHi[k] - bvh.sceneLo[k]);
+        maxAbs = std::max(maxAbs, (double) std::max(std::fabs(bvh.sceneLo[k]), std::fabs(bvh.sceneHi[k])));
+    }
+    // the stored child boxes are the exact ones grown by inflate * scale (buildBvh): the grid must contain them
+    const double margin = 4.0 * inflate * std::max(std::sqrt(diag2), maxAbs) + 1e-30;
+    double lo[3], cell[3];
+    for (int k = 0; k < 3; ++k) {
+        const double ext = std::max(((double) bvh.sceneHi[k] - bvh.sceneLo[k]) + 2.0 * margin, 1e-20);
+        lo[k] = (double) bvh.sceneLo[k] - margin - 2.0 * ext / 32760.0;            // two spare cells on either side
+        const float E = (float) (ext * (32768.0 / 32760.0) * (1.0 + 4.0 / 32760.0));
+        // what the traversal reconstructs: qBase + m * qExt with m = 1 + q / 32768, i.e. lo + q * E / 32768
+        bvh.qExt[k] = E; bvh.qBase[k] = (float) lo[k] - E;
+        lo[k] = (double) bvh.qBase[k] + (double) E;                                     // the grid as the FLOATS define it
+        cell[k] = (double) E / 32768.0;
+    }
+    uint4 *q = nullptr;
+    if (cudaMalloc((void **) &q, 2 * (size_t) bvh.nNodes * sizeof(uint4)) != cudaSuccess) { err = "quantiseNodes: out of device memory"; return false; }
+    k_quantiseNodes<<<(bvh.nNodes + 255u) / 256u, 256, 0, st>>>(bvh.nodes, bvh.nNodes, make_double3(lo[0], lo[1], lo[2]),
+                                                                make_double3(1.0 / cell[0], 1.0 / cell[1], 1.0 / cell[2]), q);
+    if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) { cudaFree(q); err = "quantiseNodes: kernel failed"; return false; }
+    bvh.qnodes = q;
+    return true;
+}
+
 } // namespace ng

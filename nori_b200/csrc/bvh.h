@@ -20,11 +20,21 @@ struct BvhDevice {
     float4 *leafTris = nullptr;    // 3 x float4 per triangle, leaf order
     uint32_t nNodes = 0, nTris = 0;
     float sceneLo[3] = {0, 0, 0}, sceneHi[3] = {0, 0, 0};
+    // optional second copy of the nodes, 32 B each: child boxes on a 15-bit grid over the scene box (quantiseNodes)
+    uint4 *qnodes = nullptr;
+    float qBase[3] = {0, 0, 0}, qExt[3] = {1, 1, 1};   // coordinate = qBase + m * qExt, m in [1, 2) (traverse_persistent.cuh)
 };
 
 /// Builds the tree for triangles tris[0..nTris) over vpos. Frees nothing it did not allocate;
 /// the caller owns out.nodes / out.leafTris (cudaFree).
 bool buildBvh(const float4 *d_vpos, const uint4 *d_tris, uint32_t nTris, const BvhParams &p, cudaStream_t stream,
               BvhDevice &out, NoriGpuAccelStats &stats, std::string &err);
+
+/// NORI_ACCEL_QUANTISED: writes bvh.qnodes from bvh.nodes (same topology, same links). Per node
+///   q0 = (L.x | L.y | L.z | linkL), q1 = (R.x | R.y | R.z | linkR), each axis word = lo16 | hi16 << 16,
+///   a 16-bit field = 0x8000 | q with q the 15-bit grid index of the bound, rounded OUTWARDS (the float boxes already
+///   carry the builder's inflation, ~0.1 cell, which covers the 0.004-cell error of the decode),
+/// so that the two bytes drop into a float mantissa (0x3F.. .. .. 00 = 1 + q / 32768) with one PRMT.
+bool quantiseNodes(BvhDevice &bvh, float inflate, cudaStream_t stream, std::string &err);
 
 } // namespace ng

@@ -37,6 +37,7 @@ struct nori_gpu_ctx {
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
+    int accelLayout = NORI_ACCEL_FLOAT;         // node layout the persistent traversal kernels read
     int isectMode = NORI_ISECT_REFERENCE_MT;   // used by the raw operators; nori_gpu_render takes it from its descriptor
 };
 
@@ -70,13 +71,15 @@ DeviceScene deviceScene(const nori_gpu_ctx *c) {
     s.nTris = c->nTris; s.nVerts = c->nVerts;
     s.nodes = c->bvh.nodes; s.leafTris = c->bvh.leafTris; s.nNodes = c->bvh.nNodes;
     s.cam = c->cam; s.filter = c->filter; s.isectMode = c->isectMode;
+    s.qnodes = c->accelLayout == NORI_ACCEL_QUANTISED ? c->bvh.qnodes : nullptr;
+    for (int k = 0; k < 3; ++k) { s.qBase[k] = c->bvh.qBase[k]; s.qExt[k] = c->bvh.qExt[k]; }
     return s;
 }
 
 void freeScene(nori_gpu_ctx *c) {
     cudaFree(c->d_vpos); cudaFree(c->d_vnrm); cudaFree(c->d_vuv); cudaFree(c->d_tris);
     cudaFree(c->d_meshes); cudaFree(c->d_emitters); cudaFree(c->d_cdf);
-    cudaFree(c->bvh.nodes); cudaFree(c->bvh.leafTris);
+    cudaFree(c->bvh.nodes); cudaFree(c->bvh.leafTris); cudaFree(c->bvh.qnodes);
     c->d_vpos = c->d_vnrm = nullptr; c->d_vuv = nullptr; c->d_tris = nullptr; c->d_meshes = nullptr; c->d_emitters = nullptr; c->d_cdf = nullptr;
     c->bvh = BvhDevice(); c->haveBvh = false; c->meshes.clear(); c->emitters.clear(); c->nTris = c->nVerts = 0;
 }
@@ -142,6 +145,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
     if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
     if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
+    if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : NORI_ACCEL_FLOAT;   // sweeps
     *out = ctx;
     return NORI_GPU_OK;
 }
@@ -294,11 +298,21 @@ int nori_gpu_build_accel(nori_gpu_ctx *ctx, NoriGpuAccelStats *out) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(ctx->d_tris, "build_accel: upload meshes first");
     CK(cudaSetDevice(ctx->device));
-    cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.leafTris); ctx->bvh = BvhDevice(); ctx->haveBvh = false;
+    cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.leafTris); cudaFree(ctx->bvh.qnodes); ctx->bvh = BvhDevice(); ctx->haveBvh = false;
     NoriGpuAccelStats st;
     if (!buildBvh(ctx->d_vpos, ctx->d_tris, ctx->nTris, ctx->bvhParams, ctx->stream, ctx->bvh, st, ctx->err)) return NORI_GPU_ECUDA;
     ctx->haveBvh = true;
+    if (ctx->accelLayout == NORI_ACCEL_QUANTISED && !quantiseNodes(ctx->bvh, ctx->bvhParams.inflate, ctx->stream, ctx->err)) return NORI_GPU_ECUDA;
     if (out) *out = st;
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_set_accel_layout(nori_gpu_ctx *ctx, int layout) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(layout == NORI_ACCEL_FLOAT || layout == NORI_ACCEL_QUANTISED, "set_accel_layout: unknown layout");
+    CK(cudaSetDevice(ctx->device));
+    ctx->accelLayout = layout;
+    if (layout == NORI_ACCEL_QUANTISED && ctx->haveBvh && !quantiseNodes(ctx->bvh, ctx->bvhParams.inflate, ctx->stream, ctx->err)) return NORI_GPU_ECUDA;
     return NORI_GPU_OK;
 }
 

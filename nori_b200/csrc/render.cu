@@ -113,10 +113,12 @@ struct ClosestIO {
 };
 
 /// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
-template <int MINB, bool WT = false>
+__device__ __forceinline__ QGrid sceneGrid(const DeviceScene &sc) { QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]}; return g; }
+
+template <int MINB, bool WT = false, bool QN = false>
 __global__ void __launch_bounds__(128, MINB) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ClosestIO io; io.pool = pool;
-    tracePersistent<false, WT>(sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold);
+    tracePersistent<false, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold, sceneGrid(sc));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -351,10 +353,10 @@ struct ShadowIO {
 };
 
 /// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
-template <int MINB, bool WT = false>
+template <int MINB, bool WT = false, bool QN = false>
 __global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool pool, float4 *recA, float *recB, size_t recCount, Counters *c, int fetchThreshold) {
     ShadowIO io; io.pool = pool; io.recA = recA; io.recB = recB; io.recCount = recCount;
-    tracePersistent<true, WT>(sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold);
+    tracePersistent<true, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold, sceneGrid(sc));
 }
 
 /// Hands path slot `dst` to camera sample index g of the issue order (pass, tile, sample, pixel):
@@ -1002,9 +1004,10 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         ++launches;
     }
     {
-        const unsigned b = sc.isectMode == NORI_ISECT_WATERTIGHT ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
         const bool overlap = splat && tune().overlapSplat;
         if (sc.isectMode == NORI_ISECT_WATERTIGHT) launchOverlapped(k_traceClosest<8, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (sc.qnodes) launchOverlapped(k_traceClosest<8, false, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 10) launchOverlapped(k_traceClosest<10>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 12) launchOverlapped(k_traceClosest<12>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else launchOverlapped(k_traceClosest<8>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
@@ -1025,8 +1028,9 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     ++launches;
     if (ev) cudaEventRecord(ev[2], st);
     if (rp.integrator != NORI_INT_NORMALS) {
-        const unsigned b = sc.isectMode == NORI_ISECT_WATERTIGHT ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
         if (sc.isectMode == NORI_ISECT_WATERTIGHT) k_traceShadow<8, true><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (sc.qnodes) k_traceShadow<8, false, true><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);

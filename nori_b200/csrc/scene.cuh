@@ -56,6 +56,8 @@ struct DeviceScene {
     const float4 *nodes;         // 4 x float4 per node
     const float4 *leafTris;      // 3 x float4 per triangle slot: (p0, gid) (p1, -) (p2, -)
     uint32_t nNodes;
+    const uint4 *qnodes;         // quantised copy of the nodes (NORI_ACCEL_QUANTISED) or nullptr; grid: coordinate = qBase + m qExt
+    float qBase[3], qExt[3];
     int isectMode;               // NORI_ISECT_*: ray-triangle test used by every traversal (0 = the reference's Moeller-Trumbore)
     Camera cam;
     FilterTab filter;

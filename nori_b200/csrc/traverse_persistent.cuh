@@ -20,9 +20,17 @@ namespace ng {
 #endif
 constexpr int kFetchThreshold = 20;   // default: refill when fewer than this many lanes still traverse
 
-template <bool ANY_HIT, bool WT = false, class IO>
+/// Grid of the quantised node layout (bvh.h: quantiseNodes): coordinate = base + m * ext, m in [1, 2).
+struct QGrid { float bx, by, bz, ex, ey, ez; };
+
+/// A 16-bit field of a quantised node (0x8000 | q) dropped into a float mantissa: 1 + q / 32768. One PRMT.
+template <bool HIGH> NG_D float qfield(uint32_t w) { return __uint_as_float(__byte_perm(w, 0x3F000000u, HIGH ? 0x7324u : 0x7104u)); }
+
+/// QN: `nodes` holds the 32-byte quantised nodes (two 16-byte loads per visit instead of four); the slab test is the
+/// same fused multiply-add per plane with per-ray constants that fold the grid in: t = m * (ext / d) + (base - o) / d.
+template <bool ANY_HIT, bool WT = false, bool QN = false, class IO>
 NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
-                          unsigned int *workCounter, IO &io, int tuning = kFetchThreshold) {
+                          unsigned int *workCounter, IO &io, int tuning = kFetchThreshold, QGrid grid = QGrid()) {
     const int fetchThreshold = tuning & 0xff;                  // refill when fewer lanes than this still hold a ray
     const int nodeExit = (tuning >> 8) & 0xff;                 // leave the node loop when fewer lanes than this still descend
     const unsigned lane = threadIdx.x & 31u;
@@ -71,7 +79,10 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                         idx = fabsf(d.x) > 1e-30f ? 1.0f / d.x : copysignf(big, d.x);
                         idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);
                         idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);
-                        oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz;
+                        if (QN) {   // plane at m: ((base + m ext) - o) / d = m * (ext / d) - (o - base) / d
+                            oodx = (o.x - grid.bx) * idx; oody = (o.y - grid.by) * idy; oodz = (o.z - grid.bz) * idz;
+                            idx *= grid.ex; idy *= grid.ey; idz *= grid.ez;
+                        } else { oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz; }
                         if (WT) wt = wtSetup(d);
                         rayIdx = i; tbest = maxt; best = kNoHit; sp = 0; cur = 0; leaf = 0; active = true;
                     }
@@ -90,8 +101,20 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
         for (;;) {
             for (;;) {                                         // inner nodes (warp-uniform loop)
                 if (cur >= 0 && cur != kDone) {
-                    const float4 *n = nodes + 4 * (size_t) cur;
-                    const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+                    float4 n0, n1, n2; int cl, cr;
+                    if (QN) {
+                        const uint4 *qn = reinterpret_cast<const uint4 *>(nodes) + 2 * (size_t) cur;
+                        const uint4 a = __ldg(qn), b = __ldg(qn + 1);
+                        n0 = make_float4(qfield<false>(a.x), qfield<true>(a.x), qfield<false>(a.y), qfield<true>(a.y));
+                        n1 = make_float4(qfield<false>(b.x), qfield<true>(b.x), qfield<false>(b.y), qfield<true>(b.y));
+                        n2 = make_float4(qfield<false>(a.z), qfield<true>(a.z), qfield<false>(b.z), qfield<true>(b.z));
+                        cl = (int) a.w; cr = (int) b.w;
+                    } else {
+                        const float4 *n = nodes + 4 * (size_t) cur;
+                        n0 = __ldg(n); n1 = __ldg(n + 1); n2 = __ldg(n + 2);
+                        const float4 n3 = __ldg(n + 3);
+                        cl = __float_as_int(n3.x); cr = __float_as_int(n3.y);
+                    }
                     const float lx0 = __fmaf_rn(n0.x, idx, -oodx), lx1 = __fmaf_rn(n0.y, idx, -oodx);
                     const float ly0 = __fmaf_rn(n0.z, idy, -oody), ly1 = __fmaf_rn(n0.w, idy, -oody);
                     const float lz0 = __fmaf_rn(n2.x, idz, -oodz), lz1 = __fmaf_rn(n2.y, idz, -oodz);
@@ -103,7 +126,6 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                     const float rmin = fmaxf(fmaxf(fminf(rx0, rx1), fminf(ry0, ry1)), fmaxf(fminf(rz0, rz1), mint));
                     const float rmax = fminf(fminf(fmaxf(rx0, rx1), fmaxf(ry0, ry1)), fminf(fmaxf(rz0, rz1), tbest));
                     const bool hl = lmin <= lmax, hr = rmin <= rmax;
-                    int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
                         if (rmin < lmin) { int tmp = cl; cl = cr; cr = tmp; }
                         push(cr);

@@ -23,7 +23,7 @@ LIB_PATH = os.path.join(HERE, os.path.basename(os.environ.get("NORI_GPU_LIB", "l
 
 EXPORTS = [
     "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",
-    "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel",
+    "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel", "nori_gpu_set_accel_layout",
     "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_download_srgb8", "nori_gpu_upload_block", "nori_gpu_block_device_ptr",
     "nori_gpu_block_dims", "nori_gpu_reduce_blocks", "nori_gpu_device_count", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
@@ -92,6 +92,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_set_camera.argtypes = [vp, C.POINTER(CameraDesc)]
     L.nori_gpu_set_filter.argtypes = [vp, C.c_float, vp]
     L.nori_gpu_build_accel.argtypes = [vp, C.POINTER(AccelStats)]
+    L.nori_gpu_set_accel_layout.argtypes = [vp, ip]
     L.nori_gpu_render.argtypes = [vp, C.POINTER(RenderDesc), C.POINTER(RenderStats)]
     L.nori_gpu_download_block.argtypes = [vp, vp]
     L.nori_gpu_download_bitmap.argtypes = [vp, vp]
@@ -259,6 +260,10 @@ class Engine:
         out = np.empty((h, w, 3), np.float32)
         self._ck(self.L.nori_gpu_download_bitmap(self.h, _p(out)))
         return out
+
+    def set_accel_layout(self, layout: int):
+        """0: 64-byte float nodes, 1: 32-byte quantised nodes (NORI_ACCEL_*)."""
+        self._ck(self.L.nori_gpu_set_accel_layout(self.h, int(layout)))
 
     def set_intersect_mode(self, mode: int):
         """Ray-triangle test of the raw operators: 0 = the reference's Moeller-Trumbore, 1 = watertight."""

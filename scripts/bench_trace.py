@@ -2,7 +2,8 @@
 Accel::rayIntersect operator (nori_gpu_trace_device, rays resident in HBM, CUDA events) for coherent
 primary rays, shadow rays towards the light and incoherent bounce rays, with the algorithmic bytes per
 ray (48 + 32 N_box + 36 N_tri, counted by the device BVH: nori_gpu_trace_count) against the measured
-HBM peak.   python scripts/bench_trace.py [c4|c1] [--out profiles/trace_<cfg>.json]"""
+HBM peak.   python scripts/bench_trace.py [c4|c1] [--layout 0|1] [--out profiles/trace_<cfg>.json]
+--layout 1: NORI_ACCEL_QUANTISED (32-byte nodes); the algorithmic bytes stay those of SURVEY 8d (32 B per box test)."""
 import json, os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -23,7 +24,9 @@ def main():
     cfg = sys.argv[1] if len(sys.argv) > 1 and not sys.argv[1].startswith("-") else "c4"
     out = sys.argv[sys.argv.index("--out") + 1] if "--out" in sys.argv else None
     scene = synth.terrain_scene() if cfg == "c4" else synth.ajax_class_scene()
+    layout = int(sys.argv[sys.argv.index("--layout") + 1]) if "--layout" in sys.argv else 0
     eng = Engine(0)
+    eng.set_accel_layout(layout)
     t0 = time.perf_counter(); accel = eng.load_scene(scene); load_s = time.perf_counter() - t0
     W, H = scene.width, scene.height
     rng = np.random.default_rng(7)
@@ -43,7 +46,7 @@ def main():
     v /= np.linalg.norm(v, axis=1, keepdims=True)
     bounce = np.concatenate([P, np.full((len(P), 1), 1e-4, np.float32), v, np.full((len(P), 1), np.inf, np.float32)], 1).astype(np.float32)
     hbm, src = peak()
-    res = {"config": cfg, "triangles": accel["n_triangles"], "accel": accel, "load_and_build_s": load_s, "hbm_peak_gbs": hbm, "peak_source": src, "rays": {}}
+    res = {"config": cfg, "node_layout": "quantised 32 B" if layout else "float 64 B", "triangles": accel["n_triangles"], "accel": accel, "load_and_build_s": load_s, "hbm_peak_gbs": hbm, "peak_source": src, "rays": {}}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     for name, rays, sh in (("primary_closest", primary, False), ("shadow_anyhit", shadow, True), ("bounce_closest", bounce, False)):
         n = len(rays)

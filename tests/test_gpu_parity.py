@@ -154,3 +154,34 @@ def test_splat_reference_order_bit_exact(gpu_scene, port, scenes):
         np.testing.assert_allclose(got2, want, rtol=1e-5, atol=1e-6)
     finally:
         e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+
+
+@pytest.mark.parametrize("name", ["cbox_mis", "bunny_normals", "table_mis"])
+def test_quantised_node_layout_returns_the_same_hits(engine, gpu_scene, port, scenes, name):
+    """NORI_ACCEL_QUANTISED: 32-byte nodes with child boxes on a 15-bit grid, rounded outwards. The tree and the
+    triangle tests are the same, so hit ids and (t,u,v) must equal the float layout's bit for bit — and the
+    reference's brute-force loop."""
+    e = gpu_scene(name); s = scenes(name); ps = port.scene(s)
+    rng = np.random.default_rng(11)
+    prim = ps.camera_rays((rng.random((20000, 2)) * [s.width, s.height]).astype(np.float32))
+    rays = np.concatenate([prim, random_rays(s, 20000, 12)])
+    want = e.trace(rays)
+    sh = rays.copy(); sh[:, 7] = rng.uniform(0.05, 1.5, size=sh.shape[0]).astype(np.float32)
+    want_occ = e.trace(sh, shadow=True)[0] != 0xffffffff
+    e.set_accel_layout(1)
+    try:
+        got = e.trace(rays)
+        for a, b in zip(got, want):
+            np.testing.assert_array_equal(bits(a) if a.dtype == np.float32 else a, bits(b) if b.dtype == np.float32 else b)
+        np.testing.assert_array_equal(e.trace(sh, shadow=True)[0] != 0xffffffff, want_occ)
+        if name != "table_mis":
+            rtri, rmesh, rtuv = ps.trace(rays[:8000], use_bvh=False)
+            np.testing.assert_array_equal(got[0][:8000], rtri); np.testing.assert_array_equal(bits(got[2][:8000]), bits(rtuv))
+        # a render through the quantised layout gives every camera sample the same radiance
+        pixel = rng.integers(0, s.width * s.height, 3000).astype(np.uint32); sample = rng.integers(0, 32, 3000).astype(np.uint32)
+        rgb_q, _ = e.sample_radiance(pixel, sample)
+        e.set_accel_layout(0)
+        rgb_f, _ = e.sample_radiance(pixel, sample)
+        np.testing.assert_array_equal(bits(rgb_q), bits(rgb_f))
+    finally:
+        e.set_accel_layout(0)
