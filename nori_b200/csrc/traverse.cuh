@@ -26,6 +26,20 @@ constexpr int kStackSize = 64;
 
 struct TraceStats { uint32_t nodes, tris; };
 
+/// One 64-byte node as TWO 256-bit loads (sm_100 `ld.global.nc.v8.f32`, SASS LDG.E.256) instead of four 128-bit ones:
+/// the traversal is bound by the L1/TEX pipe (ncu: 82-85 % on every ray type, DRAM 4-6 %), where every lane's load
+/// of its own node costs a tag lookup per instruction; nodes are 64-byte aligned (cudaMalloc + 64 B stride).
+#ifndef NORI_NODE_LOAD_128
+NG_D void loadNode(const float4 *n, float4 &n0, float4 &n1, float4 &n2, float4 &n3) {
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(n0.x), "=f"(n0.y), "=f"(n0.z), "=f"(n0.w), "=f"(n1.x), "=f"(n1.y), "=f"(n1.z), "=f"(n1.w) : "l"(n));
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(n2.x), "=f"(n2.y), "=f"(n2.z), "=f"(n2.w), "=f"(n3.x), "=f"(n3.y), "=f"(n3.z), "=f"(n3.w) : "l"(n + 2));
+}
+#else
+NG_D void loadNode(const float4 *n, float4 &n0, float4 &n1, float4 &n2, float4 &n3) { n0 = __ldg(n); n1 = __ldg(n + 1); n2 = __ldg(n + 2); n3 = __ldg(n + 3); }
+#endif
+
 template <bool ANY_HIT, bool COUNT = false>
 NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris,
                        V3 o, V3 d, float mint, float maxt, float &tOut, float &uOut, float &vOut,
@@ -47,7 +61,7 @@ NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restric
     for (;;) {
         if (cur >= 0) {
             const float4 *n = nodes + 4 * (size_t) cur;
-            const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+            float4 n0, n1, n2, n3; loadNode(n, n0, n1, n2, n3);
             if (COUNT) stats->nodes++;
             const float lx0 = __fmaf_rn(n0.x, idx, -oodx), lx1 = __fmaf_rn(n0.y, idx, -oodx);
             const float ly0 = __fmaf_rn(n0.z, idy, -oody), ly1 = __fmaf_rn(n0.w, idy, -oody);

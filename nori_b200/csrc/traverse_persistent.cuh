@@ -111,8 +111,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                         cl = (int) a.w; cr = (int) b.w;
                     } else {
                         const float4 *n = nodes + 4 * (size_t) cur;
-                        n0 = __ldg(n); n1 = __ldg(n + 1); n2 = __ldg(n + 2);
-                        const float4 n3 = __ldg(n + 3);
+                        float4 n3; loadNode(n, n0, n1, n2, n3);
                         cl = __float_as_int(n3.x); cr = __float_as_int(n3.y);
                     }
                     const float lx0 = __fmaf_rn(n0.x, idx, -oodx), lx1 = __fmaf_rn(n0.y, idx, -oodx);
