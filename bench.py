@@ -280,7 +280,7 @@ def run_gpu(args):
                      "rays_per_launch": tot["closest_rays"] / launches_closest, "avg_launch_ms": avg_launch_ms,
                      "timing": "CUDA events around k_traceClosest on its stream; the interval also contains the previous iteration's splat kernels, which run concurrently with it (programmatic dependent launch), so `achieved` is a lower bound",
                      "traffic_capture": "ncu --set full of one steady-state launch at 8 Mi path slots, about 5.4 M live rays (profiles/r01b_kernels.md): ray records in/out only",
-                     "note": "algorithmic bytes are served by L1 (BVH + triangles of this scene are 0.17 MB): the kernel is issue-bound, not HBM-bound; see DESIGN.md and profiles/r01_trace.md"},
+                     "note": "algorithmic bytes are served by L1 (BVH + triangles of this scene are 0.17 MB): the kernel is bound by instruction issue (70 %) and the L1 LSU data pipe (80 %), not by HBM (ncu: 6 % DRAM); see DESIGN.md and profiles/r01_trace.md"},
         "stages_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
         "Mrays_per_s": rays * world / (dev_ms / 1e3) / 1e6, "Gsegments_per_s": tot["segments"] * world / (dev_ms / 1e3) / 1e9,
         "segments_per_sample": tot["segments"] / max(tot["camera_samples"], 1), "reduce_ms_per_step": red_total / args.steps,
