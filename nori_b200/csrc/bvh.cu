@@ -195,7 +195,8 @@ __global__ void k_walkUp(uint32_t n /*leaves*/, uint32_t total, const float4 *__
         uint4 t = tris[g];
         float4 a = vpos[t.x], b = vpos[t.y], c = vpos[t.z];
         a.w = __uint_as_float(g); b.w = 0.f; c.w = 0.f;
-        leafTris[3 * (size_t) offset] = a; leafTris[3 * (size_t) offset + 1] = b; leafTris[3 * (size_t) offset + 2] = c;
+        leafTris[kTriStride * (size_t) offset] = a; leafTris[kTriStride * (size_t) offset + 1] = b; leafTris[kTriStride * (size_t) offset + 2] = c;
+        if (kTriStride == 4) leafTris[kTriStride * (size_t) offset + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
         effective[x] = 0;
     } else {
         bool eff = !collapsed[x] && !under;
@@ -332,7 +333,7 @@ bool buildBvh(const float4 *d_vpos, const uint4 *d_tris, uint32_t N, const BvhPa
     k_collapse<<<cdiv(N, T), T, 0, st>>>(N, blo, bhi, parent, visit, count, cost, collapsed, prm.maxLeaf, prm.costInner, prm.costTri);
     BVH_CHECK(cudaMemsetAsync(collapsed + root, 0, 1, st));       // the root is always an inner node
     float4 *leafTris = nullptr, *nodes = nullptr;
-    BVH_CHECK(cudaMalloc((void **) &leafTris, 3 * (size_t) N * sizeof(float4)));
+    BVH_CHECK(cudaMalloc((void **) &leafTris, kTriStride * (size_t) N * sizeof(float4)));
     k_walkUp<<<cdiv(total, T), T, 0, st>>>(N, total, blo, bhi, parent, count, collapsed, valsSorted, d_vpos, d_tris, start, effective, leafTris, misc + 2);
     uint32_t nNodes = 1;
     if (N == 1) {

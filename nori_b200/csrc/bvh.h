@@ -7,6 +7,13 @@
 
 namespace ng {
 
+// float4 slots per leaf triangle: 3 = (p0|gid, p1, p2), 48 B, three 128-bit loads; 4 = padded to 64 B, two 256-bit loads
+// (experiment, -DNORI_TRI_STRIDE=4: profiles/r01_trace.md)
+#ifndef NORI_TRI_STRIDE
+#define NORI_TRI_STRIDE 3
+#endif
+constexpr int kTriStride = NORI_TRI_STRIDE;
+
 struct BvhParams {
     int plocRadius = 16;       // PLOC search radius in Morton order
     int maxLeaf = 4;           // triangles per leaf (<= 8: 3 bits in the leaf link)

@@ -17,6 +17,7 @@
 // only); the triangle test does not.
 #pragma once
 #include "scene.cuh"
+#include "bvh.h"
 #include "check.cuh"
 
 namespace ng {
@@ -39,6 +40,11 @@ NG_D void loadNode(const float4 *n, float4 &n0, float4 &n1, float4 &n2, float4 &
 #else
 NG_D void loadNode(const float4 *n, float4 &n0, float4 &n1, float4 &n2, float4 &n3) { n0 = __ldg(n); n1 = __ldg(n + 1); n2 = __ldg(n + 2); n3 = __ldg(n + 3); }
 #endif
+
+NG_D void loadTri(const float4 *tp, float4 &a, float4 &b, float4 &c) {
+    if (kTriStride == 4) { float4 pad; loadNode(tp, a, b, c, pad); }
+    else { a = __ldg(tp); b = __ldg(tp + 1); c = __ldg(tp + 2); }
+}
 
 template <bool ANY_HIT, bool COUNT = false>
 NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris,
@@ -90,8 +96,8 @@ NG_D uint32_t traverse(const float4 *__restrict__ nodes, const float4 *__restric
             const uint32_t code = ~(uint32_t) cur;
             const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
             for (uint32_t i = 0; i < cnt; ++i) {
-                const float4 *tp = leafTris + 3 * (size_t) (first + i);
-                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                const float4 *tp = leafTris + kTriStride * (size_t) (first + i);
+                float4 a, b, c; loadTri(tp, a, b, c);
                 if (COUNT) stats->tris++;
                 float u, v, t;
                 const bool hit = watertight ? rayTriangleWatertight(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, wt, mint, tbest, u, v, t)

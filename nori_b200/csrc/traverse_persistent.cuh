@@ -145,8 +145,8 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                 const uint32_t code = ~(uint32_t) leaf;
                 const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
                 for (uint32_t k = 0; k < cnt; ++k) {
-                    const float4 *tp = leafTris + 3 * (size_t) (first + k);
-                    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                    const float4 *tp = leafTris + kTriStride * (size_t) (first + k);
+                    float4 a, b, c; loadTri(tp, a, b, c);
                     float u, v, t;
                     const bool hit = WT ? rayTriangleWatertight(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, wt, mint, tbest, u, v, t)
                                         : rayTriangle(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), o, d, mint, tbest, u, v, t);
