@@ -191,7 +191,10 @@ struct ShadowOut { bool cast; V3 o, d; float maxt; V3 contrib; };
 /// the path continues (a new ray was written to `ray`).
 template <int INTEGRATOR>
 __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderParams &rp, Ray &ray, uint32_t gid, float t, float u, float v,
-                                            Pcg32 &rng, V3 &T, V3 &L, float &eta, float &bsdfPdf, uint32_t &flags, ShadowOut &sh) {
+                                            Pcg32 &rng, V3 &T, V3 &L, float &eta, float &bsdfPdf, uint32_t &flags, ShadowOut &sh,
+                                            const float4 *lazyOrigin = nullptr) {
+    // lazyOrigin: where the incoming ray's origin can be read when `ray.o` was not loaded. Only the MIS weight of an
+    // emitter hit needs it, so the wavefront shade kernel leaves those 16 bytes per path in memory.
     sh.cast = false;
     if (gid == kNoHit) return false;
     Hit its;
@@ -276,7 +279,9 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
             if (!isZero(Le)) {
                 if (discrete || !useEms) L = L + T * Le;
                 else if (useMats) {
-                    float pl = emitterPdfSolidAngle(em, ray.o, its.p, its.sh.n) / (float) nLights;
+                    V3 rayOrigin = ray.o;
+                    if (lazyOrigin) { const float4 o4 = *lazyOrigin; rayOrigin = mk(o4.x, o4.y, o4.z); }
+                    float pl = emitterPdfSolidAngle(em, rayOrigin, its.p, its.sh.n) / (float) nLights;
                     float wgt = bsdfPdf / (bsdfPdf + pl);
                     L = L + T * Le * wgt;
                 }
@@ -510,13 +515,13 @@ __global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeReg
     uint4 info = make_uint4(0, 0, 0, 0);                     // read only when a camera sample ends
     if (tid < aBegin) {
         // ---- a surface was hit: one Li loop body ----------------------------------------------
-        const float4 ro = pool.rayO[slot], rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
-        Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
+        const float4 rd = pool.rayD[slot], h = pool.hit[slot], th = pool.thr[slot], ra = pool.rad[slot];
+        Ray ray; ray.o = mk(0.f, 0.f, 0.f); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = 0.f; ray.maxt = rd.w;   // origin: see lazyOrigin
         Pcg32 rng = unpackRng(st);
         V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
         float bsdfPdf = th.w, eta = ra.w;
         uint32_t flags = st.w;
-        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh);
+        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh, pool.rayO + slot);
         if (cont) {
             pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
             pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
