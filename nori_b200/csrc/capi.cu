@@ -202,7 +202,8 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
     DevBuf<float> stageV[2]; DevBuf<uint32_t> stageF[2]; DevBuf<unsigned int> bad;
     for (int k = 0; k < (n > 1 ? 2 : 1); ++k) { CK(stageV[k].alloc(std::max<size_t>(1, stageFloats))); CK(stageF[k].alloc(std::max<size_t>(1, stageIdx))); }
     CK(bad.alloc(1)); CK(cudaMemsetAsync(bad.p, 0, sizeof(unsigned int), ctx->stream));
-    cudaEvent_t stageFree[2] = {nullptr, nullptr};
+    struct StageEvents { cudaEvent_t e[2] = {nullptr, nullptr}; ~StageEvents() { for (cudaEvent_t x : e) if (x) cudaEventDestroy(x); } } stageEvents;   // freed on every return path
+    cudaEvent_t *stageFree = stageEvents.e;
     std::vector<float> cdf;
     size_t vo = 0, fo = 0;
     for (int i = 0; i < n; ++i) {
@@ -265,7 +266,6 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
     unsigned int nBad = 0;
     CK(cudaMemcpyAsync(&nBad, bad.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
-    for (cudaEvent_t e : stageFree) if (e) cudaEventDestroy(e);
     if (nBad) { freeScene(ctx); ctx->err = "upload_meshes: face index out of range"; return NORI_GPU_EINVAL; }
     return NORI_GPU_OK;
 }
