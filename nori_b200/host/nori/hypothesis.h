@@ -10,7 +10,9 @@
 //   * adaptive Simpson quadrature with the |S2 - S1| < 15 eps acceptance rule and Richardson
 //     extrapolation, nested for rectangles (hypothesis.h:65-109).
 // The distribution functions are the regularised incomplete gamma and beta functions, evaluated by
-// series / continued fractions (modified Lentz); checked against scipy.stats in tests/test_host_cpp.py.
+// series / continued fractions (modified Lentz). Pinned: verdicts, pooled counts, statistics, p-values and CDF values
+// equal the reference header's (compiled into oracle/_ref) on the seeded cases of tests/golden/hypothesis_ref.json,
+// and the CDFs agree with scipy.stats (tests/test_host_tests.py).
 #pragma once
 #include <algorithm>
 #include <cmath>

@@ -21,6 +21,20 @@ int main(int argc, char **argv) {
     } else if (!strcmp(argv[1], "ttest") && argc == 5) {
         auto r = hypothesis::students_t_test(atof(argv[2]), atof(argv[3]), atof(argv[4]), 100000, 0.01, 5);
         printf("%d\n%s", r.first ? 1 : 0, r.second.c_str());
+    } else if (!strcmp(argv[1], "chi2file") && argc == 3) {
+        // file: nCells sampleCount minExp significance numTests, then nCells obs, then nCells exp
+        FILE *f = fopen(argv[2], "r"); if (!f) return 3;
+        int n, sc, nt; double me, sig;
+        if (fscanf(f, "%d %d %lf %lf %d", &n, &sc, &me, &sig, &nt) != 5) return 3;
+        std::vector<double> obs(n), expd(n);
+        for (double &v : obs) if (fscanf(f, "%lf", &v) != 1) return 3;
+        for (double &v : expd) if (fscanf(f, "%lf", &v) != 1) return 3;
+        fclose(f);
+        auto r = hypothesis::chi2_test(n, obs.data(), expd.data(), sc, me, sig, nt);
+        printf("%d\n%s", r.first ? 1 : 0, r.second.c_str());
+    } else if (!strcmp(argv[1], "ttestn") && argc == 8) {
+        auto r = hypothesis::students_t_test(atof(argv[2]), atof(argv[3]), atof(argv[4]), atoi(argv[5]), atof(argv[6]), atoi(argv[7]));
+        printf("%d\n%s", r.first ? 1 : 0, r.second.c_str());
     } else return 2;
     return 0;
 }

@@ -74,6 +74,50 @@ def test_t_decision_rule(probe):
     assert bad[0] == "0" and "Rejected" in bad[-1]
 
 
+def test_statistics_header_pinned_to_the_reference(probe, tmp_path):
+    """nori/hypothesis.h against tests/golden/hypothesis_ref.json: verdicts, pooled-cell counts, statistics, degrees of
+    freedom, p-values and Sidak levels of the REFERENCE's ext/hypothesis/hypothesis.h (compiled into oracle/_ref,
+    oracle/make_hypothesis_golden.py) on 24 seeded contingency tables and 16 t-tests around the decision boundary."""
+    import json, re
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "hypothesis_ref.json")))
+
+    def numbers(msg):
+        out = {"pooled": None, "statistic": None, "dof": None, "pvalue": None, "alpha": None}
+        m = re.search(r"Pooled (\d+)", msg); out["pooled"] = int(m.group(1)) if m else None
+        m = re.search(r"statistic = ([-\d.e+naif]+) \(d\.o\.f\. = (-?\d+)\)", msg)
+        if m: out["statistic"], out["dof"] = float(m.group(1)), int(m.group(2))
+        m = re.search(r"p-value = ([-\d.e+naif]+), significance level = ([-\d.e+]+)", msg)
+        if m: out["pvalue"], out["alpha"] = float(m.group(1)), float(m.group(2))
+        return out
+
+    def same(got, want, case):
+        assert got["pooled"] == want["pooled"] and got["dof"] == want["dof"], case
+        for k in ("statistic", "pvalue", "alpha"):
+            if want[k] is None:
+                assert got[k] is None, case
+            else:
+                assert got[k] == pytest.approx(want[k], rel=2e-5, abs=1e-12), (k, case)   # both print 6 significant digits
+
+    for i, c in enumerate(gold["chi2"]):
+        f = tmp_path / f"t{i}.txt"
+        f.write_text("%d %d %r %r %d\n%s\n%s\n" % (c["n"], c["sampleCount"], c["minExp"], c["significance"], c["numTests"],
+                                                  " ".join(repr(x) for x in c["obs"]), " ".join(repr(x) for x in c["exp"])))
+        out = probe("chi2file", f)
+        assert int(out.splitlines()[0]) == c["accept"], (i, out, c["message"])
+        same(numbers(out), c, i)
+        if c["statistic"] is None:                             # rejection shortcuts: same reason given
+            assert out.split("\n", 1)[1].split(".")[0][:30] == c["message"].split(".")[0][:30]
+    assert any(c["pooled"] for c in gold["chi2"]) and any(not c["accept"] for c in gold["chi2"])
+    for i, c in enumerate(gold["ttest"]):
+        out = probe("ttestn", repr(c["mean"]), repr(c["variance"]), repr(c["reference"]), c["sampleCount"], c["significance"], c["numTests"])
+        assert int(out.splitlines()[0]) == c["accept"], (i, out, c["message"])
+        same(numbers(out), c, i)
+    for x, dof, want in gold["chi2_cdf"]:
+        assert float(probe("chi2", x, dof)) == pytest.approx(want, rel=1e-9, abs=1e-13)
+    for x, dof, want in gold["t_cdf"]:
+        assert float(probe("t", x, dof)) == pytest.approx(want, rel=2e-9, abs=1e-13)
+
+
 def test_plugins_are_registered_and_fail_loudly_without_a_device():
     """Parsing works anywhere; activate() needs the device (there is no CPU path)."""
     import ctypes
