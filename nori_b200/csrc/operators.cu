@@ -44,7 +44,7 @@ struct RayArrayIO {
     }
 };
 template <bool SHADOW, bool WT, bool QN = false>
-__global__ void __launch_bounds__(128, 8) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
+__global__ void __launch_bounds__(128, 10) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
     RayArrayIO io; io.rays = rays; io.hits = hits; io.n = (uint32_t) n;
     const QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]};
     tracePersistent<SHADOW, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, (uint32_t) n, cursor, io, kFetchThreshold, g);
@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(128, 8) k_tracePersistent(DeviceScene sc, cons
 void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned int *cursor, cudaStream_t st) {
     if (n <= 0) return;
     static unsigned grid = 0;
-    if (!grid) { int dev = 0, sms = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); grid = (unsigned) sms * 8u; }
+    if (!grid) { int dev = 0, sms = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); grid = (unsigned) sms * 10u; }   // 10 resident CTAs per SM (48 registers), as the renderer's trace kernels
     cudaMemsetAsync(cursor, 0, sizeof(unsigned int), st);
     const bool wt = sc.isectMode == NORI_ISECT_WATERTIGHT;
     if (sc.qnodes && !wt) {                                   // quantised node layout

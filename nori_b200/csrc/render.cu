@@ -962,7 +962,7 @@ static unsigned persistentGrid() {
 struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; bool overlapSplat; };
 static const Tune &tune() {
     static Tune t = [] {
-        Tune v = {kFetchThreshold, kFetchThreshold, 8u, true};
+        Tune v = {kFetchThreshold, kFetchThreshold, 10u, true};     // 10 CTAs of 128 threads per SM (48 registers): best since the nodes are fetched with 256-bit loads
         if (getenv("NORI_GPU_NO_OVERLAP")) v.overlapSplat = false;
         if (const char *s = getenv("NORI_GPU_FETCH")) v.fetchClosest = v.fetchShadow = atoi(s);
         if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = atoi(s);
