@@ -1015,6 +1015,8 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         else if (sc.qnodes) launchOverlapped(k_traceClosest<8, false, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 10) launchOverlapped(k_traceClosest<10>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 12) launchOverlapped(k_traceClosest<12>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (b == 9) launchOverlapped(k_traceClosest<9>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (b == 11) launchOverlapped(k_traceClosest<11>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else launchOverlapped(k_traceClosest<8>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         ++launches;
     }
@@ -1038,6 +1040,8 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         else if (sc.qnodes) k_traceShadow<8, false, true><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (b == 9) k_traceShadow<9><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (b == 11) k_traceShadow<11><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else k_traceShadow<8><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         ++launches;
     }
