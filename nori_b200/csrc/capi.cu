@@ -140,12 +140,14 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
         g_createError = cudaGetErrorString(e); delete ctx; return NORI_GPU_ECUDA;
     }
     memset(&ctx->cam, 0, sizeof(ctx->cam)); memset(&ctx->filter, 0, sizeof(ctx->filter)); memset(&ctx->pool, 0, sizeof(ctx->pool));
+#ifdef NORI_GPU_SWEEP   // parameter sweeps (build_variant): the default build reads no tuning from the environment
     if (const char *s = getenv("NORI_GPU_POOL")) ctx->poolSize = std::max(256u, (uint32_t) strtoul(s, nullptr, 10) / 256u * 256u);
     if (const char *s = getenv("NORI_GPU_PLOC_RADIUS")) ctx->bvhParams.plocRadius = atoi(s);
     if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
     if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
     if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
-    if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : NORI_ACCEL_FLOAT;   // sweeps
+    if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : NORI_ACCEL_FLOAT;
+#endif
     *out = ctx;
     return NORI_GPU_OK;
 }
@@ -179,15 +181,20 @@ int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n) {
 
 /// Scene::addChild(EMesh) + Accel::addMesh for every mesh (src/scene.cpp:58-66, accel.cpp:24-29,
 /// without the reference's single-mesh limit), Mesh::addChild(BSDF/Emitter) (mesh.cpp:104-126).
-int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int n) {
-    if (!ctx) return NORI_GPU_EINVAL;
+static int uploadMeshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int n) {
     REQUIRE(meshes && n > 0, "upload_meshes: no meshes");
     CK(cudaSetDevice(ctx->device));
     freeScene(ctx);
+    // Every descriptor is validated before anything is allocated (the face indices of non-emitter meshes are
+    // range-checked on the device while they are packed; that path frees the scene as well).
     size_t nV = 0, nF = 0;
     for (int i = 0; i < n; ++i) {
         REQUIRE(meshes[i].V && meshes[i].F && meshes[i].nV > 0, "upload_meshes: mesh without vertices or faces");
         REQUIRE(meshes[i].bsdf_type >= 0 && meshes[i].bsdf_type <= 3, "upload_meshes: unknown BSDF type");
+        if (meshes[i].is_emitter) {
+            REQUIRE(meshes[i].nF > 0, "upload_meshes: emitter mesh without triangles");
+            for (size_t k = 0; k < 3 * (size_t) meshes[i].nF; ++k) REQUIRE(meshes[i].F[k] < meshes[i].nV, "upload_meshes: face index out of range");
+        }
         nV += meshes[i].nV; nF += meshes[i].nF;
     }
     REQUIRE(nF > 0 && nF < (1u << 28), "upload_meshes: triangle count out of range");
@@ -231,14 +238,12 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
             // `area` emitter: DiscretePDF over triangle areas (Mesh::surfaceArea src/mesh.cpp:43-49;
             // append/normalize include/nori/dpdf.h:57-59,94-108). Sequential float sums on the host
             // so the table equals the reference's bit for bit.
-            REQUIRE(m.nF > 0, "upload_meshes: emitter mesh without triangles");
             EmitterInfo e; memset(&e, 0, sizeof(e));
             e.mesh = i; e.radiance[0] = m.radiance[0]; e.radiance[1] = m.radiance[1]; e.radiance[2] = m.radiance[2];
             e.cdfOffset = (uint32_t) cdf.size(); e.nTris = m.nF; e.triOffset = (uint32_t) fo;
             cdf.push_back(0.0f);
             for (uint32_t f = 0; f < m.nF; ++f) {
                 const uint32_t ia = m.F[3 * (size_t) f], ib = m.F[3 * (size_t) f + 1], ic = m.F[3 * (size_t) f + 2];
-                REQUIRE(ia < m.nV && ib < m.nV && ic < m.nV, "upload_meshes: face index out of range");
                 const float *A = m.V + 3 * (size_t) ia, *B = m.V + 3 * (size_t) ib, *C = m.V + 3 * (size_t) ic;
                 V3 p0 = mk(A[0], A[1], A[2]), p1 = mk(B[0], B[1], B[2]), p2 = mk(C[0], C[1], C[2]);
                 volatile float area = 0.5f * sqrtf(squaredNorm(cross(p1 - p0, p2 - p0)));
@@ -266,8 +271,15 @@ int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int
     unsigned int nBad = 0;
     CK(cudaMemcpyAsync(&nBad, bad.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream)); CK(cudaGetLastError());
-    if (nBad) { freeScene(ctx); ctx->err = "upload_meshes: face index out of range"; return NORI_GPU_EINVAL; }
+    if (nBad) { ctx->err = "upload_meshes: face index out of range"; return NORI_GPU_EINVAL; }
     return NORI_GPU_OK;
+}
+
+int nori_gpu_upload_meshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int n) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    const int r = uploadMeshes(ctx, meshes, n);
+    if (r != NORI_GPU_OK) freeScene(ctx);          // no error return leaves a half-uploaded scene behind
+    return r;
 }
 
 int nori_gpu_set_camera(nori_gpu_ctx *ctx, const NoriGpuCameraDesc *cam) {
@@ -331,6 +343,11 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         ctx->err = "render: NORI_STREAM_BLOCK (one serial PCG32 stream per block) is only reproducible for integrators that draw no random numbers (normals, simple)";
         return NORI_GPU_EUNSUPPORTED;
     }
+    if (!list && d->stream_mode == NORI_STREAM_BLOCK && d->sample_first != 0) {
+        // the block stream is advanced by 4 * (pixel * spp + k): a sub-range would need the total spp, which the descriptor does not carry
+        ctx->err = "render: NORI_STREAM_BLOCK renders the sample range [0, spp) only (sample_first must be 0; shard with NORI_STREAM_PER_SAMPLE)";
+        return NORI_GPU_EUNSUPPORTED;
+    }
     CK(cudaSetDevice(ctx->device));
     if (int r = ensurePool(ctx)) return r;
     if (int r = ensureBlock(ctx)) return r;
@@ -391,18 +408,28 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     // Stage events (profiling): 4 per iteration of a batch, read back after the batch's one
     // synchronisation, so that profiling does not change how the kernels are queued.
     const int batch = 8;
-    cudaEvent_t e0, e1, evCopy;
-    std::vector<cudaEvent_t> stage(ctx->profiling ? 4 * batch : 0);
+    struct Events {                              // destroyed on every return path
+        cudaEvent_t e0 = nullptr, e1 = nullptr, evCopy = nullptr; std::vector<cudaEvent_t> stage;
+        ~Events() { for (cudaEvent_t e : {e0, e1, evCopy}) if (e) cudaEventDestroy(e); for (cudaEvent_t e : stage) if (e) cudaEventDestroy(e); }
+    } evs;
+    evs.stage.assign(ctx->profiling ? 4 * batch : 0, nullptr);
+    cudaEvent_t &e0 = evs.e0, &e1 = evs.e1, &evCopy = evs.evCopy;
+    std::vector<cudaEvent_t> &stage = evs.stage;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreateWithFlags(&evCopy, cudaEventDisableTiming));
     for (auto &e : stage) CK(cudaEventCreate(&e));
     StageTimes tm = {0, 0, 0, 0, 0};
     CK(cudaEventRecord(e0, st));
     uint64_t launches = 0;
     bool done = false;
+#ifdef NORI_GPU_SWEEP
     const bool debug = getenv("NORI_GPU_DEBUG") != nullptr;
+    const uint32_t kTailPaths = getenv("NORI_GPU_TAIL") ? (uint32_t) atoi(getenv("NORI_GPU_TAIL")) : 262144u;   // sweep: profiles/r01_pipeline.md
+#else
+    const bool debug = false;
+    const uint32_t kTailPaths = 262144u;
+#endif
     uint64_t guard = 0;
     bool drainedBefore = false, tailDone = false;
-    const uint32_t kTailPaths = getenv("NORI_GPU_TAIL") ? (uint32_t) atoi(getenv("NORI_GPU_TAIL")) : 262144u;   // sweep: profiles/r01_pipeline.md
     while (!done) {
         for (int k = 0; k < batch; ++k)
             launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 4 * k : nullptr);
@@ -424,7 +451,8 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         // Tail: every camera sample has been handed out and the pool drains. Pack the surviving
         // paths into the front of the pool so that the kernels stop scanning empty slots.
         // (liveLast bounds the occupied slots only once a whole batch has run without regeneration.)
-        const bool drained = hc.issue >= rp.totalIssue;
+        // (issue overshoots its limit transiently: every free slot adds to it before k_prepare clamps it)
+        const bool drained = std::min<unsigned long long>(hc.issue, hc.issueLimit) >= rp.totalIssue;
         if (!done && drained && drainedBefore && pool.capacity > 4096u && 2ull * hc.liveLast <= pool.capacity) {
             const uint32_t newCap = std::max(4096u, (hc.liveLast + 255u) / 256u * 256u);
             launches += (uint64_t) enqueueCompaction(pool, newCap, ctx->d_counters, st);
@@ -441,7 +469,6 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     CK(cudaGetLastError());
     if (int r = reportChecks(ctx, "render")) return r;
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(evCopy); for (auto &e : stage) cudaEventDestroy(e);
     if (out) {
         const Counters &hc = *ctx->h_counters;
         memset(out, 0, sizeof(*out));

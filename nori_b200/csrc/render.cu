@@ -119,6 +119,11 @@ template <int MINB, bool WT = false, bool QN = false>
 __global__ void __launch_bounds__(128, MINB) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ClosestIO io; io.pool = pool;
     tracePersistent<false, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold, sceneGrid(sc));
+    // This grid is a programmatic dependent of the splat kernels (they execute launch_dependents on entry). It must
+    // not COMPLETE before they have: k_prepare, a normal launch behind it, is ordered after this grid only, and it
+    // resets counters the splat still reads. Waiting here, after the last hit is stored, keeps the overlap and makes
+    // stream order transitive again (a no-op when the launch carried no programmatic attribute).
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // ------------------------------------------------------------------------------------------
@@ -835,9 +840,11 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 
 // ------------------------------------------------------------------------------------------
 template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *c, cudaStream_t st) {
+#ifdef NORI_GPU_SWEEP
     static const bool small = getenv("NORI_GPU_SHADE_NT") && atoi(getenv("NORI_GPU_SHADE_NT")) == 128;   // sweep: profiles/r01_pipeline.md
-    if (small) k_shadeRegen<I, 128><<<pool.capacity / 128, 128, 0, st>>>(sc, pool, rp, c);
-    else k_shadeRegen<I, 256><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
+    if (small) { k_shadeRegen<I, 128><<<pool.capacity / 128, 128, 0, st>>>(sc, pool, rp, c); return; }
+#endif
+    k_shadeRegen<I, 256><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -925,7 +932,7 @@ __global__ void k_compactScan(Pool pool, uint32_t newCap, Counters *c) {
 /// Step 2: move the k-th listed path into the k-th listed free slot.
 __global__ void k_compactMove(Pool pool, Counters *c) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= c->compactCount[1]) return;
+    if (k >= c->compactCount[1] || k >= c->compactCount[0]) return;   // never read past either list (the host sizes newCap so that free >= live)
     const uint32_t *freeList = reinterpret_cast<const uint32_t *>(pool.shadow), *liveList = freeList + pool.capacity;
     NG_CHECK(k < c->compactCount[0]);                 // a free slot below the new size for every path above it
     const uint32_t src = liveList[k], dst = freeList[k];
@@ -958,16 +965,18 @@ static unsigned persistentGrid() {
     return g;
 }
 
-/// Tunables of the traversal kernels (environment overrides are for parameter sweeps only).
+/// Tunables of the traversal kernels (environment overrides exist only in -DNORI_GPU_SWEEP builds: build_variant).
 struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; bool overlapSplat; };
 static const Tune &tune() {
     static Tune t = [] {
         Tune v = {kFetchThreshold, kFetchThreshold, 10u, true};     // 10 CTAs of 128 threads per SM (48 registers): best since the nodes are fetched with 256-bit loads
+#ifdef NORI_GPU_SWEEP
         if (getenv("NORI_GPU_NO_OVERLAP")) v.overlapSplat = false;
         if (const char *s = getenv("NORI_GPU_FETCH")) v.fetchClosest = v.fetchShadow = atoi(s);
         if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = atoi(s);
         if (const char *s = getenv("NORI_GPU_NODE_EXIT")) { v.fetchClosest |= atoi(s) << 8; v.fetchShadow |= atoi(s) << 8; }
         if (const char *s = getenv("NORI_GPU_TRACE_CTAS")) v.ctasPerSm = (unsigned) atoi(s);
+#endif
         return v;
     }();
     return t;

@@ -103,6 +103,35 @@ def test_small_pool_and_odd_sizes(gpu_scene, scenes):
         e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
 
 
+def test_tiny_pool_many_tiles_splat_outlasts_trace(gpu_scene, scenes):
+    """Stream ordering of the overlapped launch: with a 4 096-slot pool over 640 tiles the closest-hit pass takes
+    microseconds while the splat of the previous iteration still has whole tiles to go. k_prepare must nevertheless
+    run after BOTH (k_traceClosest ends with griddepcontrol.wait): a prepare that ran under a live splat would
+    reset its tile list and leave tiles partly splatted — the filter-weight channel would then be short."""
+    e = gpu_scene("cbox_mis"); s = scenes("cbox_mis")
+    e.set_camera(s.sample_to_camera, s.camera_to_world, 1024, 640, s.near_clip, s.far_clip)
+    try:
+        e.set_pool_size(1 << 21)
+        want, _ = e.render(sample_first=0, sample_last=3)
+        e.set_pool_size(4096)
+        for _ in range(2):
+            got, st = e.render(sample_first=0, sample_last=3)
+            assert st["camera_samples"] == 1024 * 640 * 3
+            np.testing.assert_allclose(got[..., 3], want[..., 3], rtol=1e-5, atol=1e-6)      # every sample splatted exactly once
+            np.testing.assert_allclose(got, want, rtol=2e-4, atol=1e-5)
+    finally:
+        e.set_pool_size(1 << 21)
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+
+
+def test_block_stream_rejects_sample_subranges(gpu_scene):
+    """NORI_STREAM_BLOCK advances one PCG32 per block by 4 * (pixel * spp + k): a shard [first, last) with first > 0
+    would replay the stream of [0, last - first). Refused, not rendered."""
+    e = gpu_scene("bunny_normals")
+    with pytest.raises(RuntimeError, match="sample_first must be 0"):
+        e.render(stream_mode=0, integrator=NORMALS, sample_first=2, sample_last=4)
+
+
 # ---- the other reconstruction filters and integrators (SURVEY 8f-1) -----------------------------
 import os
 HOST_GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "host")
