@@ -163,6 +163,17 @@ int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode);
 /* Accel::rayIntersect (src/accel.cpp:35-55). rays: n x 8 [o.xyz, mint, d.xyz, maxt] (HOST memory).
  * tri_id: mesh-local triangle index or 0xffffffff; mesh_id likewise; tuv: n x 3 (t,u,v) or NULL. */
 int nori_gpu_trace(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint32_t *tri_id, uint32_t *mesh_id, float *tuv);
+/* NO COUNTERPART IN THE REFERENCE. nori_gpu_trace for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): same
+ * arguments, same results bit for bit, but the call allocates nothing — no cudaMalloc / cudaFree, no allocating
+ * library routine (the error paths alone format a message). All device scratch (staged rays, hit records, the traversal's work cursor, the
+ * split output arrays) lives in one file-scope `static __device__` array of the library, sized for at most
+ * NORI_GPU_TRACE_STATIC_MAX_RAYS rays per call (4.4 MB, held by every GPU that loads the library until exit);
+ * more rays are rejected with NORI_GPU_EINVAL. The array is shared by every context on a device and keeps the last
+ * call's contents (the work cursor is cleared by each call): calls that overlap on one GPU race and must be
+ * serialised by the caller. Always reads the float node layout (same tree, same hits as the quantised one). */
+#define NORI_GPU_TRACE_STATIC_MAX_RAYS 65536
+int nori_gpu_trace_static(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint32_t *tri_id, uint32_t *mesh_id, float *tuv);
 /* Same on DEVICE buffers already resident (no copies): for kernel-only timing. ms = device time. */
 int nori_gpu_trace_device(nori_gpu_ctx *ctx, const void *d_rays, int n, int shadow, void *d_hits /* n x 16 B: t,u,v,gid */, float *ms);
 /* Work counters of the device BVH for n rays: counts[0] = node visits (two child boxes per visit),

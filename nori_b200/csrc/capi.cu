@@ -1,6 +1,7 @@
 // capi.cu — the C ABI of include/nori_gpu.h: context, scene upload, render loop, operators.
 // No CPU path exists here: every entry point either runs CUDA kernels or fails.
 #include "engine.h"
+#include "traverse_persistent.cuh"
 #include <vector>
 #include <string>
 #include <cstring>
@@ -845,3 +846,108 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// nori_gpu_trace_static: Accel::rayIntersect for callers that must not allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc). Everything nori_gpu_trace keeps in cudaMalloc'ed scratch — the device
+// copy of the rays, the hit records, the work cursor of the persistent traversal, the split output arrays — lives in
+// ONE file-scope device array of fixed size. Every GPU that loads the library holds it (4.4 MB) until exit.
+// The array is shared by every context and every call on a device and keeps the previous call's contents: the
+// work cursor is cleared at the start of each call, everything else is overwritten before it is read. Two calls
+// that overlap on one GPU (different streams / host threads) race on it: callers serialise them.
+namespace {
+
+struct TraceStaticScratch {
+    unsigned int cursor; unsigned int pad[63];                  // work counter of tracePersistent; must start at zero
+    float4 rays[2 * NORI_GPU_TRACE_STATIC_MAX_RAYS];            // (o, mint) (d, maxt)
+    float4 hits[NORI_GPU_TRACE_STATIC_MAX_RAYS];                // (t, u, v, bits(gid))
+    uint32_t tri[NORI_GPU_TRACE_STATIC_MAX_RAYS], mesh[NORI_GPU_TRACE_STATIC_MAX_RAYS];
+    float tuv[3 * NORI_GPU_TRACE_STATIC_MAX_RAYS];
+};
+static __device__ __align__(256) unsigned char g_traceStaticScratch[sizeof(TraceStaticScratch)];
+
+/// Device address of the array on the CURRENT device. In host code `g_traceStaticScratch` is only a stand-in for the
+/// symbol, not a device address: it is resolved once per device, with that device current, and cached.
+constexpr int kMaxDevices = 64;
+TraceStaticScratch *g_traceStaticPtr[kMaxDevices];
+std::mutex g_traceStaticLock;
+
+cudaError_t traceStaticScratch(int device, TraceStaticScratch **out) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> guard(g_traceStaticLock);
+    if (!g_traceStaticPtr[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_traceStaticScratch);     // the caller made `device` current
+        if (e != cudaSuccess) return e;
+        g_traceStaticPtr[device] = static_cast<TraceStaticScratch *>(p);
+    }
+    *out = g_traceStaticPtr[device];
+    return cudaSuccess;
+}
+
+struct StaticRayIO {
+    TraceStaticScratch *s; uint32_t n;
+    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
+        NG_CHECK(i < n);
+        const float4 ro = s->rays[2 * (size_t) i], rd = s->rays[2 * (size_t) i + 1];
+        o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float t, float u, float v) const {
+        NG_CHECK(i < n);
+        s->hits[i] = gid == kNoHit ? make_float4(0.f, 0.f, 0.f, __uint_as_float(gid)) : make_float4(t, u, v, __uint_as_float(gid));
+    }
+};
+
+__global__ void k_traceStaticReset(TraceStaticScratch *s) { s->cursor = 0u; }
+
+/// The renderer's traversal kernel (persistent warps, dynamic ray fetch) on the rays staged in the static array.
+template <bool SHADOW, bool WT>
+__global__ void __launch_bounds__(128, 10) k_traceStatic(DeviceScene sc, TraceStaticScratch *s, int n) {
+    StaticRayIO io; io.s = s; io.n = (uint32_t) n;
+    tracePersistent<SHADOW, WT, false>(sc.nodes, sc.leafTris, (uint32_t) n, &s->cursor, io, kFetchThreshold, QGrid());
+}
+
+/// Global triangle id -> (mesh, mesh-local index) and (t, u, v) as the separate arrays the caller receives.
+__global__ void k_traceStaticSplit(DeviceScene sc, TraceStaticScratch *s, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = s->hits[i];
+    const uint32_t gid = __float_as_uint(h.w);
+    uint32_t tri = 0xffffffffu, mesh = 0xffffffffu;
+    if (gid != kNoHit) { mesh = sc.tris[gid].w; tri = gid - sc.meshes[mesh].triOffset; }
+    s->tri[i] = tri; s->mesh[i] = mesh;
+    s->tuv[3 * (size_t) i] = h.x; s->tuv[3 * (size_t) i + 1] = h.y; s->tuv[3 * (size_t) i + 2] = h.z;
+}
+
+} // namespace
+
+extern "C" int nori_gpu_trace_static(nori_gpu_ctx *ctx, const float *rays, int n, int shadow, uint32_t *tri_id, uint32_t *mesh_id, float *tuv) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    NEED_SCENE(); REQUIRE(rays && tri_id && n >= 0, "trace_static: bad arguments");
+    if (n > NORI_GPU_TRACE_STATIC_MAX_RAYS) {
+        ctx->err = "trace_static: " + std::to_string(n) + " rays exceed the static scratch array (NORI_GPU_TRACE_STATIC_MAX_RAYS = " +
+                   std::to_string(NORI_GPU_TRACE_STATIC_MAX_RAYS) + " per call): split the batch or use nori_gpu_trace";
+        return NORI_GPU_EINVAL;
+    }
+    if (n == 0) return NORI_GPU_OK;
+    CK(cudaSetDevice(ctx->device));
+    TraceStaticScratch *s = nullptr;
+    CK(traceStaticScratch(ctx->device, &s));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(s->rays, rays, (size_t) n * 32, cudaMemcpyHostToDevice, st));
+    k_traceStaticReset<<<1, 1, 0, st>>>(s);
+    const DeviceScene sc = deviceScene(ctx);
+    const unsigned grid = (unsigned) ctx->prop.multiProcessorCount * 10u;      // 10 resident CTAs of 128 threads per SM, as launchTrace
+    const bool wt = sc.isectMode == NORI_ISECT_WATERTIGHT;
+    if (shadow) { if (wt) k_traceStatic<true, true><<<grid, 128, 0, st>>>(sc, s, n); else k_traceStatic<true, false><<<grid, 128, 0, st>>>(sc, s, n); }
+    else { if (wt) k_traceStatic<false, true><<<grid, 128, 0, st>>>(sc, s, n); else k_traceStatic<false, false><<<grid, 128, 0, st>>>(sc, s, n); }
+    k_traceStaticSplit<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(sc, s, n);
+    CK(cudaMemcpyAsync(tri_id, s->tri, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    if (mesh_id) CK(cudaMemcpyAsync(mesh_id, s->mesh, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    if (tuv) CK(cudaMemcpyAsync(tuv, s->tuv, (size_t) n * 12, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    unsigned line = 0;
+    if (const unsigned bad = fetchChecks(&line)) { ctx->err = "trace_static: device range check failed (" + std::to_string(bad) + " at capi.cu/traverse:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}

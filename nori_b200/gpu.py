@@ -28,7 +28,7 @@ EXPORTS = [
     "nori_gpu_block_dims", "nori_gpu_reduce_blocks", "nori_gpu_device_count", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
-    "nori_gpu_sample_radiance",
+    "nori_gpu_sample_radiance", "nori_gpu_trace_static",
 ]
 
 
@@ -106,6 +106,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_set_pool_size.argtypes = [vp, C.c_uint32]
     L.nori_gpu_set_intersect_mode.argtypes = [vp, ip]
     L.nori_gpu_trace.argtypes = [vp, vp, ip, ip, vp, vp, vp]
+    L.nori_gpu_trace_static.argtypes = [vp, vp, ip, ip, vp, vp, vp]
     L.nori_gpu_trace_device.argtypes = [vp, vp, ip, ip, vp, C.POINTER(C.c_float)]
     L.nori_gpu_trace_count.argtypes = [vp, vp, ip, ip, vp]
     L.nori_gpu_intersect.argtypes = [vp, vp, ip, vp, vp]
@@ -302,6 +303,15 @@ class Engine:
         rays = _f32(rays, (-1, 8)); n = rays.shape[0]
         tri = np.empty(n, np.uint32); mesh = np.empty(n, np.uint32); tuv = np.empty((n, 3), np.float32)
         self._ck(self.L.nori_gpu_trace(self.h, _p(rays), n, int(shadow), _p(tri), _p(mesh), _p(tuv)))
+        return tri, mesh, tuv
+
+    TRACE_STATIC_MAX_RAYS = 65536
+
+    def trace_static(self, rays, shadow=False):
+        """nori_gpu_trace without any allocation on the library side (static device scratch, <= 65 536 rays per call)."""
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        tri = np.empty(n, np.uint32); mesh = np.empty(n, np.uint32); tuv = np.empty((n, 3), np.float32)
+        self._ck(self.L.nori_gpu_trace_static(self.h, _p(rays), n, int(shadow), _p(tri), _p(mesh), _p(tuv)))
         return tri, mesh, tuv
 
     def trace_count(self, rays, shadow=False):
