@@ -298,6 +298,10 @@ class RefScene:
         sec = self.L.ref_render(self.h, mode, sample_first, sample_last, threads, int(use_bvh), out)
         return out, sec
 
+    def threads_used(self) -> int:
+        """Distinct TBB workers that rendered blocks in the last render() (0 with a library built before this existed)."""
+        return int(self.L.ref_render_threads_used()) if hasattr(self.L, "ref_render_threads_used") else 0
+
 
 class Ref:
     def __init__(self, build: bool = False):

@@ -14,6 +14,8 @@
 #include <cstring>
 #include <chrono>
 #include <thread>
+#include <mutex>
+#include <set>
 
 using namespace nori;
 
@@ -37,6 +39,11 @@ private:
 };
 } // namespace
 
+namespace {
+std::mutex g_workerLock;
+std::set<std::thread::id> g_workers;        // TBB workers that rendered at least one block in the last ref_render
+} // namespace
+
 extern "C" {
 
 /// mode 0: the reference's per-block stream; mode 1: per-sample streams, samples [s0, s1).
@@ -55,6 +62,7 @@ double ref_render(void *o, int mode, uint32_t s0, uint32_t s1, int threads, int 
     result.clear();
     const int W = outputSize.x();
 
+    { std::lock_guard<std::mutex> g(g_workerLock); g_workers.clear(); }
     tbb::task_scheduler_init init(threads > 0 ? threads : tbb::task_scheduler_init::automatic);
     auto t0 = std::chrono::steady_clock::now();
     tbb::blocked_range<int> range(0, blockGenerator.getBlockCount());
@@ -64,6 +72,7 @@ double ref_render(void *o, int mode, uint32_t s0, uint32_t s1, int threads, int 
         StreamSampler streams(s1 - s0);
         std::unique_ptr<Sampler> indep(static_cast<Sampler *>(NoriObjectFactory::createInstance("independent", PropertyList())));
         Sampler &sampler = mode == 1 ? static_cast<Sampler &>(streams) : *indep;
+        { std::lock_guard<std::mutex> g(g_workerLock); g_workers.insert(std::this_thread::get_id()); }
         for (int i = r.begin(); i < r.end(); ++i) {
             blockGenerator.next(block);
             sampler.prepare(block);
@@ -109,5 +118,7 @@ void ref_sample_radiance(void *o, int n, const uint32_t *pixel, const uint32_t *
 }
 
 int ref_hardware_threads() { return (int) std::thread::hardware_concurrency(); }
+/// Distinct threads that took part in the last ref_render (what `cores` of a CPU baseline line should say).
+int ref_render_threads_used() { std::lock_guard<std::mutex> g(g_workerLock); return (int) g_workers.size(); }
 
 } // extern "C"

@@ -60,3 +60,11 @@ cell = q2[:, 0] | (q2[:, 1] << 2) | (q2[:, 2] << 4)
 for blk in (256, 4096):
     key = (np.arange(m) // blk) * 512 + cell * 8 + oc
     time_it(base[np.argsort(key, kind="stable")], f"random order, cell+octant-sorted within blocks of {blk}")
+
+# Global binning by origin cell alone (what per-bin queues filled by the shade kernel would give: no order inside a bin)
+for bits in (1, 2, 3):
+    q = np.clip(((base[:, 0:3] - lo) / (hi - lo + 1e-9) * (1 << bits)).astype(np.int64), 0, (1 << bits) - 1)
+    key = q[:, 0] | (q[:, 1] << bits) | (q[:, 2] << (2 * bits))
+    time_it(base[np.argsort(key, kind="stable")], f"random order, globally binned by {bits}-bit origin cell ({len(np.unique(key))} bins used)")
+    key = key * 8 + oc
+    time_it(base[np.argsort(key, kind="stable")], f"random order, globally binned by {bits}-bit cell + octant ({len(np.unique(key))} bins used)")
