@@ -207,6 +207,54 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
 int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const uint32_t *pixel, const uint32_t *sample,
                              float *rgb, float *pos);
 
+/* ---- path-graph post-process, first slice (the fork's own CUDA tool, src/pbsdf.cu) -------------------- */
+/* One path vertex = the reference's SPoint (include/nori/shadingPoint.h:125-147), same field order, 168 bytes. The reference
+ * only READS such records from .bin dumps written by another renderer (src/pathgraph.cpp:22); here the wavefront tracer's own
+ * paths produce them (nori_gpu_path_vertices). Direction conventions as bsdfeval_device uses them (src/pbsdf.cu:464-468):
+ * wo = unit vector towards the previous vertex (the camera side), wi = sampled continuation towards the next vertex. */
+typedef struct {
+    float pos[3];
+    float wi[3];        /* sampled continuation direction (world); 0 when the path ends here */
+    float wi_d[3];      /* direction of the light sample of next-event estimation (world); 0 if none was drawn */
+    float wo[3];        /* towards the previous vertex (world) */
+    float shN[3], geoN[3];
+    float diffuse[3];   /* albedo (diffuse), kd (microfacet), 0 otherwise */
+    float specular[3];  /* ks (microfacet), 1 (mirror, dielectric), 0 (diffuse) */
+    float eLi[3], eLd[3];   /* radiance fields of the later stages: written as 0 by this slice */
+    float eta[3];       /* intIOR / extIOR (dielectric, microfacet), else 0 */
+    float k[3];         /* conductor absorption: 0 (Nori has no conductor) */
+    float roughness;    /* Beckmann alpha (microfacet), else 0 */
+    float pdf;          /* solid-angle density of wi (0: discrete) */
+    float rrpdf;        /* Russian-roulette survival probability applied after this vertex (1 before roulette starts, 0 if the path ends) */
+    int32_t nidx;       /* 1: the next record is the next vertex of the same path (pbsdf.cu:1408 reads Index + 1), else 0 */
+    int32_t groupIdx;   /* camera sample the vertex belongs to: pixel * spp + k */
+    char bsdf_type;     /* 'd' diffuse, 'c' mirror (conductor, roughness 0), 't' dielectric, 'o' microfacet (opaque rough) */
+} NoriGpuSPoint;
+
+/* hparam (include/nori/shadingPoint.h:18-24): uniform grid of dim cells of size cellsize from minb; k / dk neighbours for the
+ * indirect / direct-light scatter. SPoints::BuildKNN (shadingPoint.h:776-806) derives it from the points' bounding box. */
+typedef struct {
+    int32_t dim[3];
+    float cellsize[3];
+    float minb[3];
+    int32_t k, dk;
+} NoriGpuHashParams;
+
+/* Path vertices of the camera samples [sample_first, sample_last) of every pixel (PER_SAMPLE streams; the same paths
+ * nori_gpu_render traces), in path order, the vertices of one path contiguous. out == NULL: only counts. Returns the number of
+ * vertices in *n_vertices; if it exceeds `capacity` nothing is written and NORI_GPU_EINVAL is returned (call again with room). */
+int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuSPoint *out, uint64_t capacity, uint64_t *n_vertices);
+/* buildHashGridAndFindKNN (src/pbsdf.cu:3173-3235): uniform hash grid over n points + max(k, dk) nearest neighbours of every
+ * point inside the 2x2x2 cell block around it (batchNearestNeighbor, pbsdf.cu:1089-1178). points: n records `stride` bytes
+ * apart whose first 12 bytes are the position (NoriGpuSPoint array: stride 168; packed float3: stride 12), HOST memory.
+ * neighbors: n x max(k, dk) ints (row i = point i; nearest first by (distance, index), the point itself swapped to the front as
+ * the reference does; unused entries -1). knn / dknn: neighbours available for the k / dk consumers (pbsdf.cu:1141-1164).
+ * ms (optional): device time of grid build + search. max(k, dk) <= 200. */
+int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp,
+                           int32_t *neighbors, int32_t *knn, int32_t *dknn, float *ms);
+/* SPoints::BuildKNN's grid (shadingPoint.h:794-801) for a cell count per axis: bounding box of the points, cellsize = extent / dim. */
+int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int n, const int32_t dim[3], int k, int dk, NoriGpuHashParams *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2,6 +2,7 @@
 // No CPU path exists here: every entry point either runs CUDA kernels or fails.
 #include "engine.h"
 #include "traverse_persistent.cuh"
+#include "pathgraph.h"
 #include <vector>
 #include <string>
 #include <cstring>
@@ -846,6 +847,100 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Path-graph post-process, first slice (src/pbsdf.cu): vertex records out of the tracer, hash grid + kNN.
+extern "C" int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, NoriGpuSPoint *out, uint64_t capacity, uint64_t *n_vertices) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(d && n_vertices, "path_vertices: bad arguments");
+    REQUIRE(ctx->haveBvh && ctx->haveCamera, "path_vertices: scene, camera and accel must be set first");
+    REQUIRE(d->sample_last > d->sample_first && d->sample_last <= 0x7fffffffu, "path_vertices: bad sample range");
+    REQUIRE(d->integrator == NORI_INT_PATH_MATS || d->integrator == NORI_INT_PATH_EMS || d->integrator == NORI_INT_PATH_MIS,
+            "path_vertices: the path graph is built from path_mats / path_ems / path_mis paths");
+    CK(cudaSetDevice(ctx->device));
+    const uint32_t spp = d->sample_last - d->sample_first;
+    const unsigned long long nPaths = (unsigned long long) ctx->cam.width * ctx->cam.height * spp;
+    REQUIRE(nPaths < (1ull << 31), "path_vertices: more than 2^31 camera samples in one call");
+    RenderParams rp; memset(&rp, 0, sizeof(rp));
+    rp.integrator = d->integrator; rp.streamMode = NORI_STREAM_PER_SAMPLE; rp.sampleFirst = d->sample_first; rp.sampleCount = spp;
+    rp.rrStart = d->rr_start; rp.rrMax = d->rr_max; rp.maxDepth = d->max_depth;
+    DeviceScene sc = deviceScene(ctx); sc.isectMode = d->intersect_mode;
+    DevBuf<unsigned int> counts; DevBuf<unsigned long long> offsets;
+    CK(counts.alloc(nPaths)); CK(offsets.alloc(nPaths + 1));
+    cudaStream_t st = ctx->stream;
+    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, nullptr, nullptr, st);
+    enqueueScanCounts(counts.p, nPaths, offsets.p, st);
+    unsigned long long total = 0;
+    CK(cudaMemcpyAsync(&total, offsets.p + nPaths, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    *n_vertices = total;
+    if (!out) return NORI_GPU_OK;
+    if (total > capacity) { ctx->err = "path_vertices: " + std::to_string(total) + " vertices do not fit the given capacity of " + std::to_string(capacity); return NORI_GPU_EINVAL; }
+    if (total == 0) return NORI_GPU_OK;
+    DevBuf<NoriGpuSPoint> recs; CK(recs.alloc(total));
+    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, offsets.p, recs.p, st);
+    CK(cudaMemcpyAsync(out, recs.p, total * sizeof(NoriGpuSPoint), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    return NORI_GPU_OK;
+}
+
+extern "C" int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int n, const int32_t dim[3], int k, int dk, NoriGpuHashParams *out) {
+    if (!points || n <= 0 || stride < 12 || !out) return NORI_GPU_EINVAL;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < n; ++i) {
+        float p[3]; memcpy(p, static_cast<const unsigned char *>(points) + (size_t) i * stride, 12);
+        for (int c = 0; c < 3; ++c) { lo[c] = std::min(lo[c], p[c]); hi[c] = std::max(hi[c], p[c]); }
+    }
+    int dm[3];
+    if (dim) { dm[0] = dim[0]; dm[1] = dim[1]; dm[2] = dim[2]; }
+    else {   // PathGraph::computeDimensions (src/pathgraph.cpp:40-50): about n cells for a cubic box, proportional to the extents
+        const float ext[3] = {hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2]};
+        const float longest = std::max(ext[0], std::max(ext[1], ext[2]));
+        const float dd = (float) (std::pow((double) n, 1.0 / 3.0) + 1.0);
+        for (int c = 0; c < 3; ++c) dm[c] = (int) ((longest > 0 ? ext[c] / longest : 0.f) * dd + 1.0f);
+    }
+    for (int c = 0; c < 3; ++c) {
+        if (dm[c] < 1) return NORI_GPU_EINVAL;
+        out->dim[c] = dm[c]; out->minb[c] = lo[c];
+        out->cellsize[c] = (hi[c] - lo[c]) / (float) dm[c];              // SPoints::BuildKNN, include/nori/shadingPoint.h:794
+        if (!(out->cellsize[c] > 0.f)) out->cellsize[c] = 1.0f;          // flat point set: one layer of unit cells
+    }
+    out->k = k; out->dk = dk;
+    return NORI_GPU_OK;
+}
+
+extern "C" int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp,
+                                      int32_t *neighbors, int32_t *knn, int32_t *dknn, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(points && hp && neighbors && knn && dknn && n > 0 && stride >= 12 && stride % 4 == 0, "pathgraph_knn: bad arguments");
+    REQUIRE(hp->k >= 1 && hp->dk >= 1 && hp->dim[0] >= 1 && hp->dim[1] >= 1 && hp->dim[2] >= 1, "pathgraph_knn: bad grid parameters");
+    const unsigned long long cells = (unsigned long long) hp->dim[0] * hp->dim[1] * hp->dim[2];
+    REQUIRE(cells < (1ull << 30), "pathgraph_knn: more than 2^30 grid cells");
+    REQUIRE(hp->cellsize[0] > 0 && hp->cellsize[1] > 0 && hp->cellsize[2] > 0, "pathgraph_knn: cell sizes must be positive");
+    CK(cudaSetDevice(ctx->device));
+    PgParams P;
+    for (int c = 0; c < 3; ++c) { P.minb[c] = hp->minb[c]; P.cell[c] = hp->cellsize[c]; P.dim[c] = hp->dim[c]; }
+    P.k = hp->k; P.dk = hp->dk; P.maxK = std::max(hp->k, hp->dk); P.nCells = (int) cells;
+    REQUIRE(P.maxK <= kPgMaxK, "pathgraph_knn: max(k, dk) above 200 is not supported");
+    DevBuf<unsigned char> pts, scratch; DevBuf<int> nb, dk1, dk2;
+    CK(pts.alloc((size_t) n * stride)); CK(scratch.alloc(pgScratchBytes(n, P.nCells)));
+    CK(nb.alloc((size_t) n * P.maxK)); CK(dk1.alloc(n)); CK(dk2.alloc(n));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(pts.p, points, (size_t) n * stride, cudaMemcpyHostToDevice, st));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    if (!launchPathgraphKnn(pts.p, (size_t) stride, n, P, scratch.p, nb.p, P.maxK, dk1.p, dk2.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    CK(cudaMemcpyAsync(neighbors, nb.p, (size_t) n * P.maxK * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(knn, dk1.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(dknn, dk2.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (ms) cudaEventElapsedTime(ms, e0, e1);
+    unsigned line = 0;
+    if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_knn: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 // nori_gpu_trace_static: Accel::rayIntersect for callers that must not allocate (CUDA graph capture, tight serving

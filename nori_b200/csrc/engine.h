@@ -89,6 +89,12 @@ int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParam
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,
                      cudaEvent_t *stageEvents /* 4 or nullptr */);
 
+/// Path vertices (NoriGpuSPoint records) of nPaths = W * H * spp camera samples: counts (out == nullptr) or records at offsets.
+bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t spp, unsigned long long nPaths, unsigned int *counts,
+                         const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st);
+/// offsets[0..nPaths] = exclusive prefix sums of counts (offsets[nPaths] = total).
+void enqueueScanCounts(const unsigned int *counts, unsigned long long nPaths, unsigned long long *offsets, cudaStream_t st);
+
 /// Checked build (check.cuh): violations counted by the kernels of render.cu / operators.cu since the last call.
 unsigned renderChecks(unsigned *line);
 unsigned operatorChecks(unsigned *line);

@@ -1,0 +1,24 @@
+// pathgraph.h — host-side interface of pathgraph.cu (hash grid + kNN over path vertices; reference src/pbsdf.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+
+namespace ng {
+
+constexpr int kPgMaxK = 200;          // max(k, dk): the per-thread heaps of a 128-thread CTA must fit shared memory (8 * K * 128 bytes)
+
+/// KPara (src/pbsdf.cu:16-24) = hparam (include/nori/shadingPoint.h:18-24) + derived sizes.
+struct PgParams {
+    float minb[3], cell[3];
+    int dim[3];
+    int k, dk, maxK;
+    int nCells;
+};
+
+size_t pgScratchBytes(int n, int nCells);
+bool launchPathgraphKnn(const void *d_pos, size_t strideBytes, int n, const PgParams &P, void *d_scratch, int *d_neighbors, int pitchInts,
+                        int *d_knn, int *d_dknn, cudaStream_t st, std::string &err);
+unsigned pathgraphChecks(unsigned *line);
+
+} // namespace ng

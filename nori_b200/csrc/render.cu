@@ -197,7 +197,7 @@ struct ShadowOut { bool cast; V3 o, d; float maxt; V3 contrib; };
 template <int INTEGRATOR>
 __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderParams &rp, Ray &ray, uint32_t gid, float t, float u, float v,
                                             Pcg32 &rng, V3 &T, V3 &L, float &eta, float &bsdfPdf, uint32_t &flags, ShadowOut &sh,
-                                            const float4 *lazyOrigin = nullptr) {
+                                            const float4 *lazyOrigin = nullptr, float *rrProb = nullptr) {
     // lazyOrigin: where the incoming ray's origin can be read when `ray.o` was not loaded. Only the MIS weight of an
     // emitter hit needs it, so the wavefront shade kernel leaves those 16 bytes per path in memory.
     sh.cast = false;
@@ -324,6 +324,7 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
     flags = (flags & ~(kDepthMask | kFlagDiscrete)) | (depth & kDepthMask) | (nowDiscrete ? kFlagDiscrete : 0u);
     if ((int) depth >= rp.rrStart) {
         float qc = fminf(maxCoeff(T) * eta * eta, rp.rrMax);
+        if (rrProb) *rrProb = qc;
         if (!(rng.next1D() < qc)) return false;
         T = T / qc;
     }
@@ -915,6 +916,117 @@ int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParam
     default: k_finishTail<NORI_INT_AO><<<g, 128, 0, st>>>(sc, pool, rp, c); break;
     }
     return 1;
+}
+
+// ------------------------------------------------------------------------------------------
+/// Path vertices for the path-graph post-process (include/nori_gpu.h: NoriGpuSPoint = the reference's SPoint,
+/// include/nori/shadingPoint.h:125-147). One thread follows one camera sample's path with the same traverse() /
+/// shadeVertex() steps and random numbers as the wavefront, so these are the vertices nori_gpu_render visits.
+/// WRITE = false: counts[g] = surface vertices of path g. WRITE = true: records at offsets[g] + v (path-contiguous).
+template <int INTEGRATOR, bool WRITE>
+__global__ void __launch_bounds__(128) k_pathVertices(DeviceScene sc, RenderParams rp, uint32_t spp, unsigned long long nPaths,
+                                                      unsigned int *__restrict__ counts, const unsigned long long *__restrict__ offsets, NoriGpuSPoint *__restrict__ out) {
+    const unsigned long long g = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nPaths) return;
+    const uint32_t pixel = (uint32_t) (g / spp), k = (uint32_t) (g % spp);
+    const uint32_t x = pixel % (uint32_t) sc.cam.width, y = pixel / (uint32_t) sc.cam.width;
+    Pcg32 rng;
+    rng.seed((uint64_t) y * (uint64_t) sc.cam.width + x, (uint64_t) (rp.sampleFirst + k));
+    const V2 r2 = rng.next2D();
+    V2 ps; ps.x = (float) x + r2.x; ps.y = (float) y + r2.y;
+    rng.next2D();
+    Ray ray = sampleRay(sc.cam, ps);
+    V3 T = mk(1.f, 1.f, 1.f), L = mk(0.f, 0.f, 0.f);
+    float bsdfPdf = 0.f, eta = 1.f;
+    uint32_t flags = kFlagAlive | kFlagDiscrete;
+    unsigned int nv = 0;
+    const unsigned long long base = WRITE ? offsets[g] : 0ull;
+    for (;;) {
+        float t, u, v;
+        const uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, ray.o, ray.d, ray.mint, ray.maxt, t, u, v, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT);
+        if (gid == kNoHit) break;
+        NoriGpuSPoint *rec = nullptr;
+        if (WRITE) {
+            if (nv > 0) out[base + nv - 1].nidx = 1;                       // the previous vertex has a successor on this path
+            rec = out + base + nv;
+            Hit its; fillHit(sc, gid, t, u, v, its);
+            const MeshInfo &m = sc.meshes[its.mesh];
+            NoriGpuSPoint r;
+            r.pos[0] = its.p.x; r.pos[1] = its.p.y; r.pos[2] = its.p.z;
+            r.wi[0] = r.wi[1] = r.wi[2] = 0.f; r.wi_d[0] = r.wi_d[1] = r.wi_d[2] = 0.f;
+            r.wo[0] = -ray.d.x; r.wo[1] = -ray.d.y; r.wo[2] = -ray.d.z;
+            r.shN[0] = its.sh.n.x; r.shN[1] = its.sh.n.y; r.shN[2] = its.sh.n.z;
+            r.geoN[0] = its.geo.n.x; r.geoN[1] = its.geo.n.y; r.geoN[2] = its.geo.n.z;
+            const bool dif = m.bsdfType == NORI_BSDF_DIFFUSE, mic = m.bsdfType == NORI_BSDF_MICROFACET;
+            const float spec = mic ? m.ks : (dif ? 0.f : 1.f), ratio = (m.bsdfType == NORI_BSDF_DIELECTRIC || mic) ? m.intIOR / m.extIOR : 0.f;
+            for (int c = 0; c < 3; ++c) {
+                r.diffuse[c] = (dif || mic) ? m.albedo[c] : 0.f; r.specular[c] = spec;
+                r.eLi[c] = 0.f; r.eLd[c] = 0.f; r.eta[c] = ratio; r.k[c] = 0.f;
+            }
+            r.roughness = mic ? m.alpha : 0.f; r.pdf = 0.f; r.rrpdf = 0.f; r.nidx = 0; r.groupIdx = (int32_t) g;
+            r.bsdf_type = dif ? 'd' : (m.bsdfType == NORI_BSDF_MIRROR ? 'c' : (mic ? 'o' : 't'));
+            *rec = r;
+        }
+        ++nv;
+        ShadowOut sh;
+        float rr = 1.0f;
+        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh, nullptr, &rr);
+        if (WRITE) {
+            if (sh.cast) { rec->wi_d[0] = sh.d.x; rec->wi_d[1] = sh.d.y; rec->wi_d[2] = sh.d.z; }
+            if (cont) { rec->wi[0] = ray.d.x; rec->wi[1] = ray.d.y; rec->wi[2] = ray.d.z; rec->pdf = bsdfPdf; rec->rrpdf = rr; }
+        }
+        if (!cont) break;
+    }
+    if (!WRITE) counts[g] = nv;
+}
+
+bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t spp, unsigned long long nPaths, unsigned int *counts,
+                         const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st) {
+    const unsigned g = (unsigned) ((nPaths + 127ull) / 128ull);
+#define PV(I) do { if (out) k_pathVertices<I, true><<<g, 128, 0, st>>>(sc, rp, spp, nPaths, counts, offsets, out); \
+                   else k_pathVertices<I, false><<<g, 128, 0, st>>>(sc, rp, spp, nPaths, counts, offsets, out); } while (0)
+    switch (rp.integrator) {
+    case NORI_INT_PATH_MATS: PV(NORI_INT_PATH_MATS); break;
+    case NORI_INT_PATH_EMS: PV(NORI_INT_PATH_EMS); break;
+    case NORI_INT_PATH_MIS: PV(NORI_INT_PATH_MIS); break;
+    default: return false;                                   // the path graph is built from path-traced vertices only
+    }
+#undef PV
+    return true;
+}
+
+/// Exclusive prefix sums of the per-path vertex counts (64-bit): one CTA, sequential over tiles (a few million paths).
+__global__ void __launch_bounds__(1024) k_scanCounts(const unsigned int *__restrict__ counts, unsigned long long nPaths, unsigned long long *__restrict__ offsets) {
+    __shared__ unsigned long long sWarp[32];
+    __shared__ unsigned long long sCarry;
+    if (threadIdx.x == 0) sCarry = 0;
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (unsigned long long start = 0; start < nPaths; start += 1024ull) {
+        const unsigned long long i = start + threadIdx.x;
+        const unsigned long long v = i < nPaths ? counts[i] : 0ull;
+        unsigned long long s = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const unsigned long long t = __shfl_up_sync(0xffffffffu, s, d); if ((int) lane >= d) s += t; }
+        if (lane == 31) sWarp[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long w = sWarp[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const unsigned long long t = __shfl_up_sync(0xffffffffu, w, d); if ((int) lane >= d) w += t; }
+            sWarp[lane] = w;
+        }
+        __syncthreads();
+        const unsigned long long carry = sCarry, base = warp ? sWarp[warp - 1] : 0ull;
+        if (i < nPaths) offsets[i] = carry + base + s - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) sCarry = carry + sWarp[31];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) offsets[nPaths] = sCarry;
+}
+void enqueueScanCounts(const unsigned int *counts, unsigned long long nPaths, unsigned long long *offsets, cudaStream_t st) {
+    k_scanCounts<<<1, 1024, 0, st>>>(counts, nPaths, offsets);
 }
 
 /// Tail compaction, step 1: list the free slots below `newCap` and the occupied ones at or above it

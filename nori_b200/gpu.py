@@ -29,6 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
+    "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid",
 ]
 
 
@@ -70,6 +71,17 @@ class AccelStats(C.Structure):
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
+
+class HashParams(C.Structure):
+    """hparam (include/nori/shadingPoint.h:18-24)."""
+    _fields_ = [("dim", C.c_int32 * 3), ("cellsize", C.c_float * 3), ("minb", C.c_float * 3), ("k", C.c_int32), ("dk", C.c_int32)]
+
+
+# NoriGpuSPoint = the reference's SPoint (include/nori/shadingPoint.h:125-147), 168 bytes
+SPOINT_DTYPE = np.dtype([("pos", "<f4", 3), ("wi", "<f4", 3), ("wi_d", "<f4", 3), ("wo", "<f4", 3), ("shN", "<f4", 3), ("geoN", "<f4", 3),
+                         ("diffuse", "<f4", 3), ("specular", "<f4", 3), ("eLi", "<f4", 3), ("eLd", "<f4", 3), ("eta", "<f4", 3), ("k", "<f4", 3),
+                         ("roughness", "<f4"), ("pdf", "<f4"), ("rrpdf", "<f4"), ("nidx", "<i4"), ("groupIdx", "<i4"), ("bsdf_type", "S1"), ("_pad", "V3")])
+assert SPOINT_DTYPE.itemsize == 168
 
 _lib = None
 
@@ -118,6 +130,9 @@ def load_library() -> C.CDLL:
     L.nori_gpu_pcg32.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int64, ip, vp]
     L.nori_gpu_splat.argtypes = [vp, ip, vp, vp, ip, vp, C.POINTER(C.c_uint64)]
     L.nori_gpu_sample_radiance.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp, vp]
+    L.nori_gpu_path_vertices.argtypes = [vp, C.POINTER(RenderDesc), vp, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
+    L.nori_gpu_pathgraph_grid.argtypes = [vp, C.c_uint64, ip, vp, ip, ip, C.POINTER(HashParams)]
     _lib = L
     return L
 
@@ -129,6 +144,18 @@ def _f32(a, shape=None):
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def pathgraph_grid(points, k: int, dk: int, dim=None) -> HashParams:
+    """SPoints::BuildKNN's grid over the bounding box of the points; dim=None: PathGraph::computeDimensions (about n cells)."""
+    pts = points if points.dtype == SPOINT_DTYPE else _f32(points, (-1, 3))
+    pts = np.ascontiguousarray(pts)
+    hp = HashParams()
+    d = None if dim is None else (C.c_int32 * 3)(*[int(x) for x in dim])
+    rc = load_library().nori_gpu_pathgraph_grid(_p(pts), pts.strides[0], pts.shape[0], d, int(k), int(dk), C.byref(hp))
+    if rc != 0:
+        raise NoriGpuError(f"[{rc}] pathgraph_grid: bad arguments")
+    return hp
 
 
 def device_count() -> int:
@@ -292,6 +319,27 @@ class Engine:
         d = self.render_desc(integrator, intersect_mode=intersect_mode)
         self._ck(self.L.nori_gpu_sample_radiance(self.h, C.byref(d), n, _p(pixel), _p(sample), _p(rgb), _p(pos)))
         return rgb, pos
+
+    # ---- path graph (src/pbsdf.cu) -------------------------------------------------------------
+    def path_vertices(self, integrator=None, sample_first=0, sample_last=1):
+        """SPoint records of every surface vertex of the camera samples [first, last) of every pixel, path-contiguous."""
+        d = self.render_desc(integrator, 1, sample_first, sample_last)
+        n = C.c_uint64()
+        self._ck(self.L.nori_gpu_path_vertices(self.h, C.byref(d), None, 0, C.byref(n)))
+        out = np.zeros(int(n.value), SPOINT_DTYPE)
+        if n.value:
+            self._ck(self.L.nori_gpu_path_vertices(self.h, C.byref(d), _p(out), n.value, C.byref(n)))
+        return out
+
+    def pathgraph_knn(self, points, hp: "HashParams"):
+        """buildHashGridAndFindKNN: points = (n, 3) float32 or an SPoint record array. Returns (neighbors, knn, dknn, ms)."""
+        pts = points if points.dtype == SPOINT_DTYPE else _f32(points, (-1, 3))
+        pts = np.ascontiguousarray(pts)
+        n, stride = pts.shape[0], pts.strides[0]
+        mk = max(hp.k, hp.dk)
+        nb = np.empty((n, mk), np.int32); knn = np.empty(n, np.int32); dknn = np.empty(n, np.int32); ms = C.c_float()
+        self._ck(self.L.nori_gpu_pathgraph_knn(self.h, _p(pts), stride, n, C.byref(hp), _p(nb), _p(knn), _p(dknn), C.byref(ms)))
+        return nb, knn, dknn, ms.value
 
     # ---- operators -----------------------------------------------------------------------
     def camera_rays(self, pixel_samples):

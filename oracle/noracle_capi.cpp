@@ -3,6 +3,7 @@
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs ONLY.
 // The product library (libnori_b200.so) never links or loads this file.
 #include "noracle_scene.h"
+#include "noracle_pathgraph.h"
 #include <thread>
 #include <mutex>
 #include <atomic>
@@ -291,6 +292,15 @@ void noracle_render_counted(void *s_, int mode, uint32_t sampleFirst, uint32_t s
     counters6[0] = c0.rays; counters6[1] = c0.boxTests; counters6[2] = c0.triTests;
     counters6[3] = c1.rays; counters6[4] = c1.boxTests; counters6[5] = c1.triTests;
     if (stats3) { stats3[0] = st.closest; stats3[1] = st.shadow; stats3[2] = st.segments; }
+}
+
+/// Path-graph hash grid + kNN (noracle_pathgraph.h). hp = {dim[3]} ints, {cellsize[3], minb[3]} floats, k, dk.
+void noracle_pathgraph_knn(const float *pts, int n, const int *dim, const float *cellsize, const float *minb, int k, int dk,
+                           int32_t *neighbors, int32_t *knn, int32_t *dknn, float *dists) {
+    HashParams h;
+    for (int c = 0; c < 3; ++c) { h.dim[c] = dim[c]; h.cellsize[c] = cellsize[c]; h.minb[c] = minb[c]; }
+    h.k = k; h.dk = dk;
+    pathgraphKnn(pts, n, h, neighbors, knn, dknn, dists);
 }
 
 } // extern "C"

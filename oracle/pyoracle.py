@@ -161,6 +161,14 @@ class Port:
         L.noracle_sample_radiance.argtypes = [C.c_void_p, C.c_int, _u32p, _u32p, _f32p, _f32p, _u64p]
         L.noracle_render.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _f32p, _u64p]
         L.noracle_render_counted.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _u64p, _u64p]
+        L.noracle_pathgraph_knn.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, _f32p]
+
+    def pathgraph_knn(self, pts, dim, cellsize, minb, k, dk):
+        """noracle_pathgraph.h: hash grid + kNN. Returns (neighbors, knn, dknn, dists) rows nearest first, self swapped to the front."""
+        pts = _f32(pts, (-1, 3)); n = pts.shape[0]; mk = max(k, dk)
+        nb = np.empty((n, mk), np.int32); a = np.empty(n, np.int32); b = np.empty(n, np.int32); d = np.empty((n, mk), np.float32)
+        self.L.noracle_pathgraph_knn(pts, n, np.asarray(dim, np.int32), _f32(cellsize), _f32(minb), k, dk, nb, a, b, d)
+        return nb, a, b, d
 
     def scene(self, scene: FlatScene, use_bvh=True) -> PortScene:
         return PortScene(self, scene, use_bvh)
@@ -210,6 +218,31 @@ class Port:
         out = np.empty((H + 2 * b, W + 2 * b, 4), np.float32)
         dropped = self.L.noracle_splat(W, H, radius, _f32(table), pos.shape[0], pos, rgb, out)
         return out, int(dropped)
+
+
+REFCUDA_SO = os.path.join(HERE, "_ref", "libpbsdf_ref.so")
+
+
+class RefCuda:
+    """The reference's own CUDA tool (src/pbsdf.cu compiled unmodified, oracle/Makefile refcuda). Needs a GPU."""
+    def __init__(self):
+        if not os.path.exists(REFCUDA_SO):
+            raise RuntimeError("oracle/_ref/libpbsdf_ref.so missing (run `make -C oracle refcuda` where /root/reference exists)")
+        self.L = C.CDLL(REFCUDA_SO)
+        self.L.refcuda_knn.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, C.POINTER(C.c_double)]
+
+    def knn(self, pts, dim, cellsize, minb, k, dk):
+        """buildHashGridAndFindKNN. Returns (neighbors n x max(k,dk), knn, dknn, seconds)."""
+        pts = _f32(pts, (-1, 3)); n = pts.shape[0]; mk = max(k, dk)
+        nb = np.empty((n, mk), np.int32); a = np.empty(n, np.int32); b = np.empty(n, np.int32); sec = C.c_double()
+        rc = self.L.refcuda_knn(pts, n, np.asarray(dim, np.int32), _f32(cellsize), _f32(minb), k, dk, nb, a, b, C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_knn failed ({rc})")
+        return nb, a, b, sec.value
+
+
+def have_refcuda() -> bool:
+    return os.path.exists(REFCUDA_SO)
 
 
 class RefScene:
