@@ -207,6 +207,12 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
 int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const uint32_t *pixel, const uint32_t *sample,
                              float *rgb, float *pos);
 
+/* Integrator::Li(const Scene *, Sampler *, const Ray3f &) (include/nori/integrator.h:54) for n rays [o.xyz, mint, d.xyz, maxt], each
+ * drawing from its own Sampler: rng_state holds n (pcg32 state, pcg32 inc) pairs (ext/pcg32/pcg32.h:55-57), read before and written
+ * back after the call, so that a host Sampler continues exactly where Li left it (src/ttest.cpp:168-175, src/main.cpp:57-59).
+ * rgb: n x 3 radiance. Uses integrator, rr_*, max_depth, intersect_mode, light_* of the descriptor. */
+int nori_gpu_li(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const float *rays, uint64_t *rng_state, float *rgb);
+
 /* ---- path-graph post-process, first slice (the fork's own CUDA tool, src/pbsdf.cu) -------------------- */
 /* One path vertex = the reference's SPoint (include/nori/shadingPoint.h:125-147), same field order, 168 bytes. The reference
  * only READS such records from .bin dumps written by another renderer (src/pathgraph.cpp:22); here the wavefront tracer's own

@@ -432,15 +432,16 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
 #endif
     uint64_t guard = 0;
     bool drainedBefore = false, tailDone = false;
+    int batchNow = batch;                        // iterations enqueued between two looks at the counters
     while (!done) {
-        for (int k = 0; k < batch; ++k)
+        for (int k = 0; k < batchNow; ++k)
             launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 4 * k : nullptr);
         CK(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(evCopy, st));
         CK(cudaEventSynchronize(evCopy));
         CK(cudaGetLastError());
         if (ctx->profiling) {
-            for (int k = 0; k < batch; ++k) {
+            for (int k = 0; k < batchNow; ++k) {
                 cudaEvent_t *ev = stage.data() + 4 * k; float ms;
                 cudaEventElapsedTime(&ms, ev[0], ev[1]); tm.traceClosest += ms;    // splat of the previous iteration runs under it
                 cudaEventElapsedTime(&ms, ev[1], ev[2]); tm.shade += ms;           // k_prepare + k_shadeRegen
@@ -448,6 +449,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
             }
         }
         const Counters &hc = *ctx->h_counters;
+        if (debug) { float tms = 0; cudaEventRecord(e1, st); cudaEventSynchronize(e1); cudaEventElapsedTime(&tms, e0, e1); fprintf(stderr, "[nori_gpu] t=%.3fms cap=%u live=%u ", tms, pool.capacity, hc.liveLast); }
         if (debug) fprintf(stderr, "[nori_gpu] it=%llu issue=%llu/%llu limit=%llu finished=%llu/%llu passes=%u/%u splat=[%u %u %u %u]\n", (unsigned long long) hc.iterations, (unsigned long long) hc.issue, (unsigned long long) rp.totalIssue, (unsigned long long) hc.issueLimit, (unsigned long long) hc.finished, (unsigned long long) totalSamples, hc.completedPasses, rp.numPasses, hc.tilesSplatted[0], hc.tilesSplatted[1], hc.tilesSplatted[2], hc.tilesSplatted[3]);
         done = hc.finished >= totalSamples && (list || hc.completedPasses >= rp.numPasses);
         // Tail: every camera sample has been handed out and the pool drains. Pack the surviving
@@ -464,6 +466,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
             if (newCap <= kTailPaths && !tailDone) { launches += (uint64_t) enqueueFinishTail(sc, pool, rp, ctx->d_counters, st); tailDone = true; }
         }
         drainedBefore = drained;
+        if (drained) batchNow = 2;               // the pool empties within a few bounces: look (and compact) more often than every 8 iterations
         if (++guard > 4000000ull) { ctx->err = "render: wavefront did not terminate (internal error)"; return NORI_GPU_ECUDA; }
     }
     CK(cudaEventRecord(e1, st));
@@ -507,6 +510,31 @@ int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, i
         rgb[3 * i] = a[i].z; rgb[3 * i + 1] = a[i].w; rgb[3 * i + 2] = b[i];
         if (pos) { pos[2 * i] = a[i].x; pos[2 * i + 1] = a[i].y; }
     }
+    return NORI_GPU_OK;
+}
+
+int nori_gpu_li(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, int n, const float *rays, uint64_t *rng_state, float *rgb) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(d && n > 0 && rays && rng_state && rgb, "li: bad arguments");
+    REQUIRE(ctx->haveBvh, "li: scene and accel must be set first");
+    REQUIRE(d->integrator >= NORI_INT_NORMALS && d->integrator <= NORI_INT_AO, "li: unknown integrator");
+    REQUIRE(d->intersect_mode == NORI_ISECT_REFERENCE_MT || d->intersect_mode == NORI_ISECT_WATERTIGHT, "li: unknown intersect_mode");
+    CK(cudaSetDevice(ctx->device));
+    RenderParams rp; memset(&rp, 0, sizeof(rp));
+    rp.integrator = d->integrator; rp.rrStart = d->rr_start; rp.rrMax = d->rr_max; rp.maxDepth = d->max_depth;
+    rp.lightPos = mk(d->light_pos[0], d->light_pos[1], d->light_pos[2]);
+    rp.lightEnergy = mk(d->light_energy[0], d->light_energy[1], d->light_energy[2]);
+    DeviceScene sc = deviceScene(ctx); sc.isectMode = d->intersect_mode;
+    DevBuf<float4> dr; DevBuf<unsigned long long> ds; DevBuf<float> dc;
+    CK(dr.alloc(2 * (size_t) n)); CK(ds.alloc(2 * (size_t) n)); CK(dc.alloc(3 * (size_t) n));
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(dr.p, rays, (size_t) n * 32, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ds.p, rng_state, (size_t) n * 16, cudaMemcpyHostToDevice, st));
+    enqueueLi(sc, rp, n, dr.p, ds.p, dc.p, st);
+    CK(cudaMemcpyAsync(rgb, dc.p, (size_t) n * 12, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(rng_state, ds.p, (size_t) n * 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (int r = reportChecks(ctx, "li")) return r;
     return NORI_GPU_OK;
 }
 

@@ -89,6 +89,9 @@ int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParam
 int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams &rp, Counters *d_counters, cudaStream_t st,
                      cudaEvent_t *stageEvents /* 4 or nullptr */);
 
+/// Integrator::Li for n rays (2 float4 each) with per-ray pcg32 (state, inc) pairs read and written back; rgb n x 3.
+void enqueueLi(const DeviceScene &sc, const RenderParams &rp, int n, const float4 *rays, unsigned long long *rngState, float *rgb, cudaStream_t st);
+
 /// Path vertices (NoriGpuSPoint records) of nPaths = W * H * spp camera samples: counts (out == nullptr) or records at offsets.
 bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t spp, unsigned long long nPaths, unsigned int *counts,
                          const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st);

@@ -919,6 +919,50 @@ int enqueueFinishTail(const DeviceScene &sc, const Pool &pool, const RenderParam
 }
 
 // ------------------------------------------------------------------------------------------
+/// Integrator::Li(scene, sampler, ray) (include/nori/integrator.h:54) for n given rays, each with the state of the Sampler
+/// (pcg32: state, inc) it draws from; the advanced state is written back, so the caller's sampler continues exactly where
+/// a CPU Li would have left it (src/ttest.cpp:168-175 draws the next ray from the same sampler).
+template <int INTEGRATOR>
+__global__ void __launch_bounds__(128) k_li(DeviceScene sc, RenderParams rp, int n, const float4 *__restrict__ rays, unsigned long long *__restrict__ rngState, float *__restrict__ rgb) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 ro = rays[2 * (size_t) i], rd = rays[2 * (size_t) i + 1];
+    Ray ray; ray.o = mk(ro.x, ro.y, ro.z); ray.d = mk(rd.x, rd.y, rd.z); ray.mint = ro.w; ray.maxt = rd.w;
+    Pcg32 rng; rng.state = rngState[2 * (size_t) i]; rng.inc = rngState[2 * (size_t) i + 1];
+    V3 T = mk(1.f, 1.f, 1.f), L = mk(0.f, 0.f, 0.f);
+    float bsdfPdf = 0.f, eta = 1.f;
+    uint32_t flags = kFlagAlive | kFlagDiscrete;
+    for (;;) {
+        float t, u, v;
+        const uint32_t gid = traverse<false>(sc.nodes, sc.leafTris, ray.o, ray.d, ray.mint, ray.maxt, t, u, v, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT);
+        ShadowOut sh;
+        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh);
+        if (sh.cast) {
+            float st, su, sv;
+            if (traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT) == kNoHit) L = L + sh.contrib;
+        }
+        if (!cont) break;
+    }
+    const V3 finL = (flags & kFlagMulT) ? T * L : L;
+    rgb[3 * (size_t) i] = finL.x; rgb[3 * (size_t) i + 1] = finL.y; rgb[3 * (size_t) i + 2] = finL.z;
+    rngState[2 * (size_t) i] = rng.state; rngState[2 * (size_t) i + 1] = rng.inc;
+}
+
+void enqueueLi(const DeviceScene &sc, const RenderParams &rp, int n, const float4 *rays, unsigned long long *rngState, float *rgb, cudaStream_t st) {
+    const unsigned g = (unsigned) ((n + 127) / 128);
+    switch (rp.integrator) {
+    case NORI_INT_NORMALS: k_li<NORI_INT_NORMALS><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    case NORI_INT_PATH_MATS: k_li<NORI_INT_PATH_MATS><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    case NORI_INT_PATH_EMS: k_li<NORI_INT_PATH_EMS><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    case NORI_INT_PATH_MIS: k_li<NORI_INT_PATH_MIS><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    case NORI_INT_WHITTED: k_li<NORI_INT_WHITTED><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    case NORI_INT_PRIMARY_SHADOW: k_li<NORI_INT_PRIMARY_SHADOW><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    case NORI_INT_SIMPLE: k_li<NORI_INT_SIMPLE><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    default: k_li<NORI_INT_AO><<<g, 128, 0, st>>>(sc, rp, n, rays, rngState, rgb); break;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 /// Path vertices for the path-graph post-process (include/nori_gpu.h: NoriGpuSPoint = the reference's SPoint,
 /// include/nori/shadingPoint.h:125-147). One thread follows one camera sample's path with the same traverse() /
 /// shadeVertex() steps and random numbers as the wavefront, so these are the vertices nori_gpu_render visits.

@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid",
+    "nori_gpu_li", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid",
 ]
 
 
@@ -130,6 +130,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_pcg32.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int64, ip, vp]
     L.nori_gpu_splat.argtypes = [vp, ip, vp, vp, ip, vp, C.POINTER(C.c_uint64)]
     L.nori_gpu_sample_radiance.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp, vp]
+    L.nori_gpu_li.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp]
     L.nori_gpu_path_vertices.argtypes = [vp, C.POINTER(RenderDesc), vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_grid.argtypes = [vp, C.c_uint64, ip, vp, ip, ip, C.POINTER(HashParams)]
@@ -319,6 +320,15 @@ class Engine:
         d = self.render_desc(integrator, intersect_mode=intersect_mode)
         self._ck(self.L.nori_gpu_sample_radiance(self.h, C.byref(d), n, _p(pixel), _p(sample), _p(rgb), _p(pos)))
         return rgb, pos
+
+    def li(self, rays, rng_state, integrator=None, intersect_mode=0):
+        """Integrator::Li for n rays, each with its sampler's (pcg32 state, inc). Returns (rgb n x 3, advanced states n x 2 uint64)."""
+        rays = _f32(rays, (-1, 8)); n = rays.shape[0]
+        st = np.array(rng_state, np.uint64).reshape(n, 2).copy()
+        rgb = np.empty((n, 3), np.float32)
+        d = self.render_desc(integrator, intersect_mode=intersect_mode)
+        self._ck(self.L.nori_gpu_li(self.h, C.byref(d), n, _p(rays), _p(st), _p(rgb)))
+        return rgb, st
 
     # ---- path graph (src/pbsdf.cu) -------------------------------------------------------------
     def path_vertices(self, integrator=None, sample_first=0, sample_last=1):

@@ -46,6 +46,7 @@ private:
 // ---- small fixed-size vectors (plain float, no SIMD: every operation rounds once, in the order written)
 struct Vector2f { float x = 0, y = 0; Vector2f() {} Vector2f(float x_, float y_) : x(x_), y(y_) {} };
 struct Vector2i { int x = 0, y = 0; Vector2i() {} Vector2i(int x_, int y_) : x(x_), y(y_) {} };
+typedef Vector2i Point2i;
 struct Vector3f {
     float x = 0, y = 0, z = 0;
     Vector3f() {}

@@ -16,6 +16,7 @@ class Mesh; class BSDF; class Emitter; class Scene; class Sampler;
 
 // ---- reconstruction filters (include/nori/rfilter.h:34-52, src/rfilter.cpp) ---------------------
 #define NORI_FILTER_RESOLUTION 32
+#define NORI_BLOCK_SIZE 32          /* include/nori/block.h:29 */
 class ReconstructionFilter : public NoriObject {
 public:
     float getRadius() const { return m_radius; }
@@ -96,6 +97,8 @@ public:
     const Vector2i &getOutputSize() const { return m_outputSize; }
     const ReconstructionFilter *getReconstructionFilter() const { return m_rfilter; }
     EClassType getClassType() const override { return ECamera; }
+    /// include/nori/camera.h:56-58 — importance-sample a ray through the film position `samplePosition` (pixels)
+    virtual Color3f sampleRay(Ray3f &ray, const Point2f &samplePosition, const Point2f &apertureSample) const = 0;
     /// State after activate(): the two matrices and clip planes NoriGpuCameraDesc carries
     virtual void describe(float sampleToCamera[16], float cameraToWorld[16], float &nearClip, float &farClip, float &fov) const = 0;
 protected:
@@ -104,10 +107,23 @@ protected:
 };
 
 // ---- sampler (include/nori/sampler.h:45-104, src/independent.cpp) ------------------------------------
+class ImageBlock;
 class Sampler : public NoriObject {
 public:
-    size_t getSampleCount() const { return m_sampleCount; }
+    /// Exact copy, random number state included (one per worker in the reference: src/main.cpp:102)
+    virtual std::unique_ptr<Sampler> clone() const = 0;
+    /// Deterministic re-seed for a new image block (src/independent.cpp:48-53: pcg32::seed(offset.x, offset.y))
+    virtual void prepare(const ImageBlock &block) = 0;
+    virtual void generate() = 0;
+    virtual void advance() = 0;
+    virtual float next1D() = 0;
+    virtual Point2f next2D() = 0;
+    virtual size_t getSampleCount() const { return m_sampleCount; }
     EClassType getClassType() const override { return ESampler; }
+    /// Device bridge: the pcg32 (state, inc) the sampler draws from, so that Integrator::Li can continue the SAME stream on the
+    /// GPU and hand it back advanced. A sampler without such a state returns false (Li then throws).
+    virtual bool getStreamState(uint64_t &state, uint64_t &inc) const { (void) state; (void) inc; return false; }
+    virtual void setStreamState(uint64_t state, uint64_t inc) { (void) state; (void) inc; }
 protected:
     size_t m_sampleCount = 1;
 };
@@ -117,6 +133,11 @@ class Integrator : public NoriObject {
 public:
     EClassType getClassType() const override { return EIntegrator; }
     virtual void preprocess(const Scene *) {}
+    /// include/nori/integrator.h:54 — radiance arriving along `ray`, drawing from `sampler`. One ray through the device
+    /// operator nori_gpu_li: the sampler's pcg32 state goes in and comes back advanced by exactly the numbers the path drew,
+    /// so a loop written against the reference (src/main.cpp:49-62, src/ttest.cpp:168-175) produces the same sequence of
+    /// values as the CPU integrator would. (Batches: sampleRadianceGpu / renderGpu.)
+    virtual Color3f Li(const Scene *scene, Sampler *sampler, const Ray3f &ray) const;
     /// NORI_INT_* of include/nori_gpu.h
     virtual int gpuType() const = 0;
     /// Extra parameters some integrators carry (`simple`: position, energy)
@@ -160,6 +181,9 @@ class ImageBlock {
 public:
     ImageBlock(const Vector2i &size, const ReconstructionFilter *filter);
     const Vector2i &getSize() const { return m_size; }
+    /// Offset of the block inside the frame (include/nori/block.h:62-66); Sampler::prepare seeds from it
+    const Point2i &getOffset() const { return m_offset; }
+    void setOffset(const Point2i &offset) { m_offset = offset; }
     int getBorderSize() const { return m_border; }
     int rows() const { return m_size.y + 2 * m_border; }
     int cols() const { return m_size.x + 2 * m_border; }
@@ -171,7 +195,7 @@ public:
     /// rgb / w per pixel, border cropped (src/block.cpp:57-63, include/nori/color.h:112-117)
     std::unique_ptr<Bitmap> toBitmap() const;
 private:
-    Vector2i m_size; int m_border = 0; float m_radius = 0; float m_table[NORI_FILTER_RESOLUTION + 1];
+    Vector2i m_size; Point2i m_offset; int m_border = 0; float m_radius = 0; float m_table[NORI_FILTER_RESOLUTION + 1];
     std::vector<float> m_data;
 };
 

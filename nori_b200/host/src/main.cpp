@@ -8,6 +8,9 @@
 //   nori_b200 --resume part.blk --last 256 scene.xml                   continue from it (samples [64, 256) are added)
 //   nori_b200 --dump FILE scene.xml     parse only; write the flattened descriptors (tests; no GPU)
 //   nori_b200 test.xml                  a <test> root (chi2test, ttest, warptest) runs in activate(), as in the reference
+//   nori_b200 --li-stream FILE [--spp N] scene.xml   the reference's renderBlock loop (src/main.cpp:38-67) written against the
+//                                       plugin contracts: Sampler::prepare / next2D, Camera::sampleRay, Integrator::Li (one ray per
+//                                       call through nori_gpu_li); writes (pixelSample.xy, rgb) float32 x 5 per camera sample
 //   nori_b200 --warptest NAME [P [P2]]  the reference's `warptest NAME P P2` command line mode (src/warptest.cpp:979-1006)
 #include <nori/scene.h>
 #include <cstring>
@@ -94,10 +97,44 @@ void render(const Scene *scene, const std::string &outName, int device, int sppO
     if (png) bitmap->savePNG(outName);
 }
 
+/// renderBlock (src/main.cpp:38-67) for every 32 x 32 block of the frame, exactly as a reference plugin user writes it: one
+/// `independent` sampler re-seeded per block from the block offset, four numbers per camera sample, then whatever Li draws.
+/// This is the reference's own sample stream for ANY integrator (the wavefront path offers it for normals / simple only): the
+/// serial dependence between consecutive samples is carried by the Sampler, whose pcg32 state travels through nori_gpu_li.
+void liStream(const Scene *scene, const std::string &path, int sppOverride) {
+    const Camera *camera = scene->getCamera();
+    const Integrator *integrator = scene->getIntegrator();
+    const Vector2i size = camera->getOutputSize();
+    const uint32_t spp = sppOverride > 0 ? (uint32_t) sppOverride : (uint32_t) scene->getSampler()->getSampleCount();
+    std::unique_ptr<Sampler> sampler(scene->getSampler()->clone());
+    std::ofstream os(path, std::ios::binary);
+    if (os.fail()) throw NoriException("Unable to open \"%s\" for writing", path);
+    scene->gpu(0);
+    for (int oy = 0; oy < size.y; oy += NORI_BLOCK_SIZE)
+        for (int ox = 0; ox < size.x; ox += NORI_BLOCK_SIZE) {
+            ImageBlock block(Vector2i(std::min(NORI_BLOCK_SIZE, size.x - ox), std::min(NORI_BLOCK_SIZE, size.y - oy)), camera->getReconstructionFilter());
+            block.setOffset(Point2i(ox, oy));
+            sampler->prepare(block);
+            for (int y = 0; y < block.getSize().y; ++y)
+                for (int x = 0; x < block.getSize().x; ++x)
+                    for (uint32_t i = 0; i < spp; ++i) {
+                        const Point2f r = sampler->next2D();
+                        const Point2f pixelSample((float) (x + ox) + r.x, (float) (y + oy) + r.y);
+                        const Point2f apertureSample = sampler->next2D();
+                        Ray3f ray;
+                        Color3f value = camera->sampleRay(ray, pixelSample, apertureSample);
+                        const Color3f li = integrator->Li(scene, sampler.get(), ray);
+                        value = Color3f(value.r * li.r, value.g * li.g, value.b * li.b);
+                        const float rec[5] = {pixelSample.x, pixelSample.y, value.r, value.g, value.b};
+                        putArray(os, rec, 5);
+                    }
+        }
+}
+
 } // namespace
 
 int main(int argc, char **argv) {
-    std::string sceneFile, dumpFile, outName, resumeFile, checkpointFile;
+    std::string sceneFile, dumpFile, outName, resumeFile, checkpointFile, liFile;
     int device = 0, spp = 0; long first = -1, last = -1; bool png = true;
     std::vector<int> devices;
     for (int i = 1; i < argc; ++i) {
@@ -113,6 +150,7 @@ int main(int argc, char **argv) {
         else if (a == "--last") last = atol(value("--last").c_str());
         else if (a == "--out") outName = value("--out");
         else if (a == "--dump") dumpFile = value("--dump");
+        else if (a == "--li-stream") liFile = value("--li-stream");
         else if (a == "--resume") resumeFile = value("--resume");
         else if (a == "--checkpoint") checkpointFile = value("--checkpoint");
         else if (a == "--no-png") png = false;
@@ -144,6 +182,7 @@ int main(int argc, char **argv) {
         if (root->getClassType() != NoriObject::EScene) return 0;      // e.g. a <test>: nothing to render
         const Scene *scene = static_cast<const Scene *>(root.get());
         if (!dumpFile.empty()) { dumpScene(scene, dumpFile); return 0; }
+        if (!liFile.empty()) { liStream(scene, liFile, spp); return 0; }
         if (outName.empty()) {
             const size_t dot = sceneFile.find_last_of('.');
             outName = dot == std::string::npos || (slash != std::string::npos && dot < slash) ? sceneFile : sceneFile.substr(0, dot);

@@ -173,6 +173,19 @@ public:
         m_rfilter = static_cast<ReconstructionFilter *>(obj);
     }
 
+    /// src/perspective.cpp:88-109, in the evaluation orders the compiled reference uses (the device's sampleRay, csrc/scene.cuh)
+    Color3f sampleRay(Ray3f &ray, const Point2f &samplePosition, const Point2f &) const override {
+        const float invW = 1.0f / (float) m_outputSize.x, invH = 1.0f / (float) m_outputSize.y;
+        const Point3f nearP = m_sampleToCamera.applyPoint(Point3f(samplePosition.x * invW, samplePosition.y * invH, 0.0f));
+        const Vector3f d = Vector3f(nearP.x, nearP.y, nearP.z).normalized();
+        const float invZ = 1.0f / d.z;
+        ray.o = m_cameraToWorld.applyPoint(Point3f(0, 0, 0));
+        ray.d = m_cameraToWorld.applyVector(d);
+        ray.mint = m_nearClip * invZ;
+        ray.maxt = m_farClip * invZ;
+        return Color3f(1.0f);
+    }
+
     void describe(float s2c[16], float c2w[16], float &nearClip, float &farClip, float &fov) const override {
         m_sampleToCamera.getMatrix().toRowMajor(s2c);
         m_cameraToWorld.getMatrix().toRowMajor(c2w);

@@ -131,10 +131,30 @@ private:
 };
 
 // ---- sampler -----------------------------------------------------------------------------------------------
+/// src/independent.cpp:33-77: independent samples from one pcg32 per sampler instance.
 class Independent : public Sampler {
 public:
     explicit Independent(const PropertyList &p) { m_sampleCount = (size_t) p.getInteger("sampleCount", 1); }
+    std::unique_ptr<Sampler> clone() const override {
+        std::unique_ptr<Independent> cloned(new Independent());
+        cloned->m_sampleCount = m_sampleCount;
+        cloned->m_random = m_random;
+        return std::unique_ptr<Sampler>(cloned.release());
+    }
+    void prepare(const ImageBlock &block) override { m_random.seed((uint64_t) (int64_t) block.getOffset().x, (uint64_t) (int64_t) block.getOffset().y); }
+    void generate() override {}
+    void advance() override {}
+    float next1D() override { return m_random.nextFloat(); }
+    /// The reference writes Point2f(m_random.nextFloat(), m_random.nextFloat()): x86-64 g++ evaluates the arguments right to left,
+    /// so y is drawn first (pinned against the compiled reference: tests/golden/ref_vectors.npz, sampler_next2d).
+    Point2f next2D() override { const float y = m_random.nextFloat(); const float x = m_random.nextFloat(); return Point2f(x, y); }
+    bool getStreamState(uint64_t &state, uint64_t &inc) const override { state = m_random.state; inc = m_random.inc; return true; }
+    void setStreamState(uint64_t state, uint64_t inc) override { m_random.state = state; m_random.inc = inc; }
     std::string toString() const override { return fmt("Independent[sampleCount=%d]", (int) m_sampleCount); }
+protected:
+    Independent() {}
+private:
+    Pcg32 m_random;
 };
 
 // ---- integrators ---------------------------------------------------------------------------------------------

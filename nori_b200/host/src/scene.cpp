@@ -226,6 +226,20 @@ static NoriGpuRenderDesc renderDesc(const Scene *scene, uint32_t sampleFirst, ui
     return d;
 }
 
+Color3f Integrator::Li(const Scene *scene, Sampler *sampler, const Ray3f &ray) const {
+    if (!scene || !sampler) throw NoriException("Integrator::Li: scene and sampler are required");
+    if (scene->getIntegrator() != this) throw NoriException("Integrator::Li: the device evaluates the scene's own integrator");
+    uint64_t st[2];
+    if (!sampler->getStreamState(st[0], st[1])) throw NoriException("Integrator::Li: this sampler has no pcg32 stream the device could continue");
+    nori_gpu_ctx *ctx = scene->gpu(0);
+    const NoriGpuRenderDesc d = renderDesc(scene, 0, 1);
+    const float r[8] = {ray.o.x, ray.o.y, ray.o.z, ray.mint, ray.d.x, ray.d.y, ray.d.z, ray.maxt};
+    float rgb[3];
+    check(ctx, nori_gpu_li(ctx, &d, 1, r, st, rgb), "nori_gpu_li");
+    sampler->setStreamState(st[0], st[1]);
+    return Color3f(rgb[0], rgb[1], rgb[2]);
+}
+
 void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const uint32_t *sample, float *rgb, int device) {
     nori_gpu_ctx *ctx = scene->gpu(device);
     const NoriGpuRenderDesc d = renderDesc(scene, 0, 1);

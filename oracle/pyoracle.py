@@ -331,6 +331,16 @@ class RefScene:
         sec = self.L.ref_render(self.h, mode, sample_first, sample_last, threads, int(use_bvh), out)
         return out, sec
 
+    def bridge_render(self, shape, libnori_b200: str, sample_first=0, sample_last=1, device=0):
+        """tests/ref_bridge.cpp: this scene (objects of the reference's own parser) rendered by libnori_b200.so through the C ABI."""
+        out = np.empty(shape, np.float32)
+        self.L.ref_bridge_render.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.c_uint32, _f32p, C.c_void_p]
+        self.L.ref_bridge_error.restype = C.c_char_p
+        rc = self.L.ref_bridge_render(self.h, libnori_b200.encode(), device, sample_first, sample_last, out, None)
+        if rc != 0:
+            raise RuntimeError(f"ref_bridge_render failed ({rc}): {self.L.ref_bridge_error().decode()}")
+        return out
+
     def threads_used(self) -> int:
         """Distinct TBB workers that rendered blocks in the last render() (0 with a library built before this existed)."""
         return int(self.L.ref_render_threads_used()) if hasattr(self.L, "ref_render_threads_used") else 0

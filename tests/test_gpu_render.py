@@ -48,7 +48,7 @@ def to_bitmap(block, border):
     return np.where(w != 0, rgb / np.where(w != 0, w, 1), 0)
 
 
-@pytest.mark.parametrize("name,spp,tol", [("cbox_mis", 4, 2e-3), ("bunny_normals", 2, 1e-9)])
+@pytest.mark.parametrize("name,spp,tol", [("cbox_mis", 4, 2e-3), ("bunny_normals", 2, 1e-9), ("table_mis", 2, 2e-3), ("veach_mis", 2, 2e-3)])
 def test_render_image_vs_oracle(gpu_scene, port, scenes, name, spp, tol):
     """Whole frame, same per-sample streams on both sides: the ImageBlocks agree up to summation
     order and the rare chaotic sample; relative MSE of the bitmap <= tol (eps 1e-2)."""
@@ -65,6 +65,31 @@ def test_render_image_vs_oracle(gpu_scene, port, scenes, name, spp, tol):
     assert abs(stats["closest_rays"] - int(wstats[0])) <= 0.002 * int(wstats[0])
     assert abs(stats["shadow_rays"] - int(wstats[1])) <= 0.002 * max(int(wstats[1]), 1)
     np.testing.assert_allclose(e.download_bitmap(), to_bitmap(got, b), rtol=1e-6, atol=1e-7)
+
+
+def test_render_converges_to_an_independently_seeded_cpu_render(gpu_scene, port, scenes):
+    """Convergence, not sample-for-sample agreement: the GPU renders samples [0, n) of every pixel, the CPU oracle renders
+    DISJOINT sample indices [5000, 5000 + n) (other PCG32 streams: an independent estimate of the same image). The relative
+    MSE between two independent n-sample estimates is the sum of their variances, i.e. it must fall like 1/n: from 64 to
+    256 spp by about 4x (accepted: at least 2.5x), and it must be small in absolute terms at 256 spp (<= 4e-2, eps 1e-2; the CPU-vs-CPU
+    value of two independent 64-spp renders is 7e-2).
+    200 x 150 Cornell box, path_mis (glass + mirror + area light)."""
+    import os
+    e = gpu_scene("cbox_mis"); s = scenes("cbox_mis")
+    from bench import resize_camera
+    small = resize_camera(s, 200, 150)
+    e.set_camera(small.sample_to_camera, small.camera_to_world, 200, 150, s.near_clip, s.far_clip)
+    try:
+        ps = port.scene(small); ps.set_integrator(small.integrator)
+        errs = []
+        for n in (64, 256):
+            want, _ = ps.render(mode=1, sample_first=5000, sample_last=5000 + n, threads=os.cpu_count() or 1)
+            got, st = e.render(sample_first=0, sample_last=n)
+            assert st["camera_samples"] == 200 * 150 * n
+            errs.append(rel_mse(to_bitmap(got, s.border), to_bitmap(want, s.border)))
+        assert errs[1] <= 4e-2 and errs[0] >= 2.5 * errs[1], errs
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
 
 
 def test_render_reference_block_stream_normals(gpu_scene, port, scenes):
@@ -252,8 +277,16 @@ def test_reduce_blocks_in_process(engine, gpu_scene, scenes):
             reduce_blocks([e, other])
     finally:
         other.close()
+
+
+def test_reduce_blocks_across_two_devices(engine, gpu_scene, scenes):
+    """The NCCL part of nori_gpu_reduce_blocks: two sample ranges on two devices sum to the single-device image.
+    Needs two GPUs (`gpurun --gpus 2`; the log of that run is profiles/r02_two_gpu_tests.log); skipped, not passed, on one."""
+    from nori_b200.gpu import Engine, device_count, reduce_blocks
     if device_count() < 2:
-        return
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    e = gpu_scene("cbox_mis")
+    whole, _ = e.render(sample_first=0, sample_last=6)
     second = Engine(1)
     try:
         second.load_scene(scenes("cbox_mis"))

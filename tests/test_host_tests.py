@@ -168,6 +168,15 @@ def test_ttest_furnace_scenes(tmp_path):
 
 
 @pytest.mark.gpu
+def test_ttest_glass_furnace_on_device_samples(tmp_path):
+    """The dielectric pin (closed furnace seen through a glass sphere: 1 / (1 - a) whatever the eta^2 bookkeeping, provided it is
+    consistent) on DEVICE-generated samples; tests/test_oracle_pins.py runs the same file through the reference's own t-test on the CPU."""
+    r = run_case("ttest-furnace-glass.xml", tmp_path)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr
+    assert "Passed 6/6 tests." in r.stdout
+
+
+@pytest.mark.gpu
 def test_ttest_rejects_a_wrong_reference_value(tmp_path):
     r = run_case("ttest-furnace-wrong.xml", tmp_path)
     assert r.returncode != 0 and "***** Rejected *****" in r.stdout and "Passed 0/1 tests." in r.stdout

@@ -136,6 +136,20 @@ def test_reference_fixture_scenes_pass(ref, rel, tmp_path, monkeypatch):
 
 
 @pytest.mark.ref
+def test_glass_furnace_passes_the_reference_ttest(ref, tmp_path, monkeypatch):
+    """A dielectric pin that does not rest on this repository's conventions: a closed furnace (emittance 1, albedo a) with a glass
+    sphere between camera and wall must still show 1 / (1 - a) in every direction. Run by the REFERENCE's own StudentsTTest
+    (src/ttest.cpp:147-194) on the restated dielectric + integrators, for path_ems / path_mats / path_mis and a = 0.5, 0.8
+    (tests/golden/host/tests/ttest-furnace-glass.xml; the same file runs on device samples in tests/test_host_tests.py)."""
+    monkeypatch.chdir(tmp_path)
+    fd = os.dup(1); null = os.open(os.devnull, os.O_WRONLY); os.dup2(null, 1)       # the test report goes to stdout: keep the log short
+    try:
+        ref.load_xml(os.path.join(os.path.dirname(__file__), "golden", "host", "tests", "ttest-furnace-glass.xml"))   # throws when a test is rejected
+    finally:
+        os.dup2(fd, 1); os.close(fd); os.close(null)
+
+
+@pytest.mark.ref
 def test_exported_scene_reloads_identically_in_the_compiled_reference(ref, tmp_path):
     """oracle/export_xml.py (how bench.py feeds the compiled reference on machines without its scene
     files): a FlatScene written as XML + OBJ and parsed by the reference's own parser / OBJ loader /
