@@ -207,6 +207,18 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
 int nori_gpu_sample_radiance(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int n, const uint32_t *pixel, const uint32_t *sample,
                              float *rgb, float *pos);
 
+/* ---- the step before the path: OBJ corner de-duplication on the device (src/obj.cpp:32-48, 96-117, 136-161) ------------------- */
+/* The loader's OBJVertex hash map and vertex gather for one mesh. corners: n_corners x 3 = the (p, uv, n) index triples of the `f`
+ * lines in file order, 1-based as written (quads already split as obj.cpp:101-107 does; uv / n entries are ignored when the file has
+ * no vt / vn lines); positions / texcoords / normals: the file's v / vt / vn arrays (toWorld already applied, obj.cpp:66-84).
+ * Outputs, bit-equal to what the reference's loader builds: F (n_corners vertex ids, handed out in order of FIRST USE), V (3 floats
+ * per unique corner), N, UV (NULL exactly when the file has no vn / vt); the caller provides room for n_corners vertices.
+ * Corners naming a non-existent v / vt / vn are an error (the reference's .at() throws). ms (optional): device time of the sort,
+ * scan and gather. All arrays in HOST memory. */
+int nori_gpu_obj_dedup(nori_gpu_ctx *ctx, const uint32_t *corners, uint32_t n_corners, const float *positions, uint32_t n_positions,
+                       const float *texcoords, uint32_t n_texcoords, const float *normals, uint32_t n_normals,
+                       uint32_t *F, float *V, float *N, float *UV, uint32_t *n_vertices, float *ms);
+
 /* Integrator::Li(const Scene *, Sampler *, const Ray3f &) (include/nori/integrator.h:54) for n rays [o.xyz, mint, d.xyz, maxt], each
  * drawing from its own Sampler: rng_state holds n (pcg32 state, pcg32 inc) pairs (ext/pcg32/pcg32.h:55-57), read before and written
  * back after the call, so that a host Sampler continues exactly where Li left it (src/ttest.cpp:168-175, src/main.cpp:57-59).

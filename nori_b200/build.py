@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnori_b200.so")
-SOURCES = ["capi.cu", "render.cu", "operators.cu", "bvh.cu", "pathgraph.cu"]
+SOURCES = ["capi.cu", "render.cu", "operators.cu", "bvh.cu", "pathgraph.cu", "objdedup.cu"]
 HEADERS = ["engine.h", "bvh.h", "check.cuh", "nmath.cuh", "scene.cuh", "traverse.cuh", "traverse_persistent.cuh", "pathgraph.h", os.path.join("..", "..", "include", "nori_gpu.h")]
 # -fmad=false: the arithmetic order written in nmath.cuh is the order executed (bit parity with
 # the x86-64 reference build, which has no FMA). Division and sqrt stay IEEE (nvcc defaults).

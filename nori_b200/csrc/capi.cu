@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <map>
 #include <mutex>
+#include <thread>
 #include <dlfcn.h>
 
 using namespace ng;
@@ -36,6 +37,16 @@ struct nori_gpu_ctx {
     // wavefront pool
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 23;   // 8 Mi path slots (sweep: profiles/r01_pipeline.md)
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
+    // host -> device staging for large pageable arrays (stagedCopy): kUploadWorkers host threads x 2 pinned buffers each (sweep on the GPU box, C4 240 MB: 4 x 8 MB 19.3 ms, 8 x 4 MB 13.4 ms, 8 x 8 15.8, 12 x 4 14.4, 8 x 2 15.1, 16 x 2 18.3; plain pageable copies 26 ms)
+#ifndef NORI_UPLOAD_WORKERS
+#define NORI_UPLOAD_WORKERS 8
+#endif
+#ifndef NORI_UPLOAD_CHUNK_MB
+#define NORI_UPLOAD_CHUNK_MB 4
+#endif
+    static constexpr int kUploadWorkers = NORI_UPLOAD_WORKERS; static constexpr size_t kUploadChunk = (size_t) NORI_UPLOAD_CHUNK_MB << 20;
+    void *upBuf[kUploadWorkers][2] = {}; cudaEvent_t upEv[kUploadWorkers][2] = {}; cudaStream_t upStream[kUploadWorkers] = {};
+    cudaEvent_t upDone[kUploadWorkers] = {}, upGate = nullptr; bool haveUpload = false;
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
@@ -108,6 +119,52 @@ int ensurePool(nori_gpu_ctx *ctx) {
     return 0;
 }
 
+/// Host -> device copy of a large PAGEABLE array at pinned-memory speed. A plain cudaMemcpyAsync from pageable memory goes
+/// through one driver staging buffer at ~9 GB/s (C4's 240 MB took 26 ms). Here kUploadWorkers host threads each copy
+/// their 8 MB chunks into two pinned buffers of their own and queue the DMA on their own stream, so that the CPU copies of
+/// several chunks and the DMA of the previous ones overlap; ctx->stream then waits for all of them. Small arrays take the plain path.
+int stagedCopy(nori_gpu_ctx *ctx, void *dst, const void *src, size_t bytes) {
+    constexpr int W = nori_gpu_ctx::kUploadWorkers; constexpr size_t C = nori_gpu_ctx::kUploadChunk;
+    if (bytes < 4 * C) { CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream)); return 0; }
+    if (!ctx->haveUpload) {
+        for (int w = 0; w < W; ++w) {
+            CK(cudaStreamCreateWithFlags(&ctx->upStream[w], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&ctx->upDone[w], cudaEventDisableTiming));
+            for (int b = 0; b < 2; ++b) { CK(cudaHostAlloc(&ctx->upBuf[w][b], C, cudaHostAllocDefault)); CK(cudaEventCreateWithFlags(&ctx->upEv[w][b], cudaEventDisableTiming)); }
+        }
+        CK(cudaEventCreateWithFlags(&ctx->upGate, cudaEventDisableTiming));
+        ctx->haveUpload = true;
+    }
+    // the staging streams must not run ahead of work already queued on ctx->stream that still reads or writes dst
+    CK(cudaEventRecord(ctx->upGate, ctx->stream));
+    for (int w = 0; w < W; ++w) CK(cudaStreamWaitEvent(ctx->upStream[w], ctx->upGate, 0));
+    const size_t nChunks = (bytes + C - 1) / C;
+    cudaError_t errs[W];
+    std::thread workers[W];
+    for (int w = 0; w < W; ++w)
+        workers[w] = std::thread([=, &errs]() {
+            cudaError_t e = cudaSetDevice(ctx->device);
+            int turn = 0;
+            for (size_t c = (size_t) w; c < nChunks && e == cudaSuccess; c += W, ++turn) {
+                const int b = turn & 1;
+                const size_t off = c * C, n = std::min(C, bytes - off);
+                e = cudaEventSynchronize(ctx->upEv[w][b]);        // the DMA that last read this buffer (this call or an earlier one) is done
+                if (e != cudaSuccess) break;
+                memcpy(ctx->upBuf[w][b], static_cast<const unsigned char *>(src) + off, n);
+                e = cudaMemcpyAsync(static_cast<unsigned char *>(dst) + off, ctx->upBuf[w][b], n, cudaMemcpyHostToDevice, ctx->upStream[w]);
+                if (e == cudaSuccess) e = cudaEventRecord(ctx->upEv[w][b], ctx->upStream[w]);
+            }
+            errs[w] = e;
+        });
+    for (int w = 0; w < W; ++w) workers[w].join();
+    for (int w = 0; w < W; ++w) CK(errs[w]);
+    for (int w = 0; w < W; ++w) {                 // everything queued behind this call on ctx->stream sees the data
+        CK(cudaEventRecord(ctx->upDone[w], ctx->upStream[w]));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->upDone[w], 0));
+    }
+    return 0;
+}
+
 int ensureBlock(nori_gpu_ctx *ctx) {
     size_t need = (size_t) (ctx->cam.width + 2 * ctx->filter.border) * (ctx->cam.height + 2 * ctx->filter.border) * 4;
     if (ctx->d_block && ctx->blockFloats == need) return 0;
@@ -160,6 +217,12 @@ void nori_gpu_destroy(nori_gpu_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     freeScene(ctx); freePool(ctx);
     cudaFree(ctx->d_block); cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
+    if (ctx->haveUpload)
+        for (int w = 0; w < nori_gpu_ctx::kUploadWorkers; ++w) {
+            for (int b = 0; b < 2; ++b) { cudaFreeHost(ctx->upBuf[w][b]); cudaEventDestroy(ctx->upEv[w][b]); }
+            cudaStreamDestroy(ctx->upStream[w]); cudaEventDestroy(ctx->upDone[w]);
+        }
+    if (ctx->haveUpload) cudaEventDestroy(ctx->upGate);
     cudaFree(ctx->recA); cudaFree(ctx->recB); cudaFree(ctx->tileDone); cudaFree(ctx->tileGen); cudaFree(ctx->tileArrive); cudaFree(ctx->readyTiles);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -228,10 +291,10 @@ static int uploadMeshes(nori_gpu_ctx *ctx, const NoriGpuMeshDesc *meshes, int n)
             const int k = i & 1;
             if (stageFree[k]) CK(cudaEventSynchronize(stageFree[k])); else CK(cudaEventCreateWithFlags(&stageFree[k], cudaEventDisableTiming));
             float *dV = stageV[k].p, *dN = m.N ? dV + 3 * (size_t) m.nV : nullptr, *dUV = m.UV ? dV + 6 * (size_t) m.nV : nullptr;
-            CK(cudaMemcpyAsync(dV, m.V, (size_t) m.nV * 12, cudaMemcpyHostToDevice, ctx->stream));
-            if (m.N) CK(cudaMemcpyAsync(dN, m.N, (size_t) m.nV * 12, cudaMemcpyHostToDevice, ctx->stream));
-            if (m.UV) CK(cudaMemcpyAsync(dUV, m.UV, (size_t) m.nV * 8, cudaMemcpyHostToDevice, ctx->stream));
-            if (m.nF) CK(cudaMemcpyAsync(stageF[k].p, m.F, (size_t) m.nF * 12, cudaMemcpyHostToDevice, ctx->stream));
+            if (int r = stagedCopy(ctx, dV, m.V, (size_t) m.nV * 12)) return r;
+            if (m.N) if (int r = stagedCopy(ctx, dN, m.N, (size_t) m.nV * 12)) return r;
+            if (m.UV) if (int r = stagedCopy(ctx, dUV, m.UV, (size_t) m.nV * 8)) return r;
+            if (m.nF) if (int r = stagedCopy(ctx, stageF[k].p, m.F, (size_t) m.nF * 12)) return r;
             launchPackMesh(dV, dN, dUV, stageF[k].p, m.nV, m.nF, (uint32_t) vo, (uint32_t) i, ctx->d_vpos + vo, ctx->d_vnrm + vo, ctx->d_vuv + vo,
                            ctx->d_tris + fo, bad.p, ctx->stream);
             CK(cudaEventRecord(stageFree[k], ctx->stream));
@@ -875,6 +938,43 @@ int nori_gpu_splat(nori_gpu_ctx *ctx, int n, const float *pos, const float *rgb,
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// The step before the path: OBJ corner de-duplication on the device (objdedup.cu).
+extern "C" int nori_gpu_obj_dedup(nori_gpu_ctx *ctx, const uint32_t *corners, uint32_t n_corners, const float *positions, uint32_t n_positions,
+                                  const float *texcoords, uint32_t n_texcoords, const float *normals, uint32_t n_normals,
+                                  uint32_t *F, float *V, float *N, float *UV, uint32_t *n_vertices, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(corners && n_corners > 0 && n_corners % 3 == 0 && positions && n_positions > 0 && F && V && n_vertices, "obj_dedup: bad arguments");
+    REQUIRE((n_texcoords == 0) == (UV == nullptr) && (n_normals == 0) == (N == nullptr), "obj_dedup: UV / N outputs must be given exactly when the file has vt / vn lines");
+    REQUIRE((n_texcoords == 0 || texcoords) && (n_normals == 0 || normals), "obj_dedup: missing texcoord / normal array");
+    REQUIRE(n_corners < (1u << 31), "obj_dedup: too many corners");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = n_corners;
+    DevBuf<uint32_t> dC, dF; DevBuf<float> dP, dT, dNr, dV, dN, dUV;
+    CK(dC.alloc(3 * n)); CK(dF.alloc(n)); CK(dP.alloc(3 * (size_t) n_positions)); CK(dV.alloc(3 * n));
+    if (n_texcoords) { CK(dT.alloc(2 * (size_t) n_texcoords)); CK(dUV.alloc(2 * n)); }
+    if (n_normals) { CK(dNr.alloc(3 * (size_t) n_normals)); CK(dN.alloc(3 * n)); }
+    cudaStream_t st = ctx->stream;
+    if (int r = stagedCopy(ctx, dC.p, corners, 12 * n)) return r;
+    if (int r = stagedCopy(ctx, dP.p, positions, 12 * (size_t) n_positions)) return r;
+    if (n_texcoords) if (int r = stagedCopy(ctx, dT.p, texcoords, 8 * (size_t) n_texcoords)) return r;
+    if (n_normals) if (int r = stagedCopy(ctx, dNr.p, normals, 12 * (size_t) n_normals)) return r;
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    uint32_t nV = 0;
+    if (!objDedup(dC.p, n_corners, dP.p, n_positions, dT.p, n_texcoords, dNr.p, n_normals, dF.p, dV.p, dN.p, dUV.p, &nV, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    CK(cudaMemcpyAsync(F, dF.p, 4 * n, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(V, dV.p, 12 * (size_t) nV, cudaMemcpyDeviceToHost, st));
+    if (n_normals) CK(cudaMemcpyAsync(N, dN.p, 12 * (size_t) nV, cudaMemcpyDeviceToHost, st));
+    if (n_texcoords) CK(cudaMemcpyAsync(UV, dUV.p, 8 * (size_t) nV, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    *n_vertices = nV;
+    if (ms) cudaEventElapsedTime(ms, e0, e1);
+    return NORI_GPU_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 // Path-graph post-process, first slice (src/pbsdf.cu): vertex records out of the tracer, hash grid + kNN.

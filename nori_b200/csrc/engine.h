@@ -98,6 +98,10 @@ bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t
 /// offsets[0..nPaths] = exclusive prefix sums of counts (offsets[nPaths] = total).
 void enqueueScanCounts(const unsigned int *counts, unsigned long long nPaths, unsigned long long *offsets, cudaStream_t st);
 
+/// OBJ corner de-duplication in first-use order + vertex gather (objdedup.cu; src/obj.cpp:96-161). Device pointers.
+bool objDedup(const uint32_t *corners, uint32_t n, const float *pos, uint32_t nP, const float *tex, uint32_t nT, const float *nrm, uint32_t nN,
+              uint32_t *F, float *V, float *N, float *UV, uint32_t *nVertsOut, cudaStream_t st, std::string &err);
+
 /// Checked build (check.cuh): violations counted by the kernels of render.cu / operators.cu since the last call.
 unsigned renderChecks(unsigned *line);
 unsigned operatorChecks(unsigned *line);

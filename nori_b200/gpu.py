@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid",
 ]
 
 
@@ -130,6 +130,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_pcg32.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int64, ip, vp]
     L.nori_gpu_splat.argtypes = [vp, ip, vp, vp, ip, vp, C.POINTER(C.c_uint64)]
     L.nori_gpu_sample_radiance.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp, vp]
+    L.nori_gpu_obj_dedup.argtypes = [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32, vp, vp, vp, vp, C.POINTER(C.c_uint32), C.POINTER(C.c_float)]
     L.nori_gpu_li.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp]
     L.nori_gpu_path_vertices.argtypes = [vp, C.POINTER(RenderDesc), vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
@@ -320,6 +321,19 @@ class Engine:
         d = self.render_desc(integrator, intersect_mode=intersect_mode)
         self._ck(self.L.nori_gpu_sample_radiance(self.h, C.byref(d), n, _p(pixel), _p(sample), _p(rgb), _p(pos)))
         return rgb, pos
+
+    def obj_dedup(self, corners, positions, texcoords=None, normals=None):
+        """The OBJ loader's corner de-duplication (first-use order) + vertex gather. corners: (n, 3) uint32 (p, uv, n), 1-based.
+        Returns (F (n/3, 3), V, N or None, UV or None, device ms)."""
+        c = np.ascontiguousarray(corners, np.uint32).reshape(-1, 3); n = c.shape[0]
+        P = _f32(positions, (-1, 3)); T = None if texcoords is None else _f32(texcoords, (-1, 2)); Nr = None if normals is None else _f32(normals, (-1, 3))
+        F = np.empty(n, np.uint32); V = np.empty((n, 3), np.float32)
+        N = None if Nr is None else np.empty((n, 3), np.float32); UV = None if T is None else np.empty((n, 2), np.float32)
+        nv, ms = C.c_uint32(), C.c_float()
+        self._ck(self.L.nori_gpu_obj_dedup(self.h, _p(c), n, _p(P), P.shape[0], _p(T), 0 if T is None else T.shape[0], _p(Nr), 0 if Nr is None else Nr.shape[0],
+                                           _p(F), _p(V), _p(N), _p(UV), C.byref(nv), C.byref(ms)))
+        k = nv.value
+        return F.reshape(-1, 3), V[:k].copy(), None if N is None else N[:k].copy(), None if UV is None else UV[:k].copy(), ms.value
 
     def li(self, rays, rng_state, integrator=None, intersect_mode=0):
         """Integrator::Li for n rays, each with its sampler's (pcg32 state, inc). Returns (rgb n x 3, advanced states n x 2 uint64)."""

@@ -226,6 +226,11 @@ private:
     mutable std::map<int, nori_gpu_ctx *> m_ctx;        // device -> context holding this scene
 };
 
+/// `--device-dedup`: the OBJ loader hands corner de-duplication and the vertex gather (src/obj.cpp:96-161) to the device
+/// (nori_gpu_obj_dedup) instead of its host hash map; same m_F / m_V / m_N / m_UV. An explicit choice of the caller, never automatic.
+bool deviceObjDedup();
+void setDeviceObjDedup(bool on);
+
 /// Device context for operators that need no scene (BSDF::sample/eval/pdf, Warp::*): created on first use.
 nori_gpu_ctx *operatorContext();
 /// Turns a non-zero return of the C ABI into a NoriException carrying nori_gpu_last_error().

@@ -6,6 +6,7 @@
 //   nori_b200 --devices 0,1,2,3 scene.xml                              sample ranges over several GPUs, one NCCL reduce
 //   nori_b200 --first 0 --last 64 --checkpoint part.blk scene.xml      render a sample range, keep the accumulator
 //   nori_b200 --resume part.blk --last 256 scene.xml                   continue from it (samples [64, 256) are added)
+//   nori_b200 --device-dedup ...        OBJ corner de-duplication + vertex gather on the GPU (nori_gpu_obj_dedup) instead of the loader's hash map
 //   nori_b200 --dump FILE scene.xml     parse only; write the flattened descriptors (tests; no GPU)
 //   nori_b200 test.xml                  a <test> root (chi2test, ttest, warptest) runs in activate(), as in the reference
 //   nori_b200 --li-stream FILE [--spp N] scene.xml   the reference's renderBlock loop (src/main.cpp:38-67) written against the
@@ -154,6 +155,7 @@ int main(int argc, char **argv) {
         else if (a == "--resume") resumeFile = value("--resume");
         else if (a == "--checkpoint") checkpointFile = value("--checkpoint");
         else if (a == "--no-png") png = false;
+        else if (a == "--device-dedup") setDeviceObjDedup(true);
         else if (a == "--warptest") {
             try {
                 PropertyList list;

@@ -1,6 +1,7 @@
 // mesh.cpp — Mesh base class, the Wavefront OBJ loader ("obj") and the perspective camera.
 // Reference: src/mesh.cpp:28-41,104-146; src/obj.cpp:30-173; src/perspective.cpp:33-86.
 #include <nori/scene.h>
+#include <nori_gpu.h>
 #include <chrono>
 #include <fstream>
 #include <iostream>
@@ -76,6 +77,8 @@ public:
         std::vector<Point3f> positions; std::vector<Point2f> texcoords; std::vector<Normal3f> normals;
         std::vector<ObjCorner> corners;                      // unique corners in order of first use
         std::unordered_map<ObjCorner, uint32_t, ObjCornerHash> cornerIndex;
+        const bool onDevice = deviceObjDedup();              // --device-dedup: the hash map below becomes one nori_gpu_obj_dedup call
+        std::vector<uint32_t> cornerList;                    // (p, uv, n) of every face corner in file order
         std::string lineStr;
         while (std::getline(is, lineStr)) {
             std::istringstream line(lineStr);
@@ -102,6 +105,10 @@ public:
                     quad[3] = ObjCorner(v[3]); quad[4] = quad[0]; quad[5] = quad[2];
                     count = 6;
                 }
+                if (onDevice) {
+                    for (int i = 0; i < count; ++i) { cornerList.push_back(quad[i].p); cornerList.push_back(quad[i].uv); cornerList.push_back(quad[i].n); }
+                    continue;
+                }
                 for (int i = 0; i < count; ++i) {
                     auto it = cornerIndex.find(quad[i]);
                     if (it == cornerIndex.end()) {
@@ -113,19 +120,38 @@ public:
                 }
             }
         }
-        m_V.resize(3 * corners.size());
+        if (onDevice) {
+            if (cornerList.empty()) throw NoriException("OBJ file \"%s\" has no faces", path);
+            const size_t n = cornerList.size() / 3;
+            std::vector<float> P(3 * positions.size()), T(2 * texcoords.size()), Nr(3 * normals.size());
+            for (size_t i = 0; i < positions.size(); ++i) { P[3 * i] = positions[i].x; P[3 * i + 1] = positions[i].y; P[3 * i + 2] = positions[i].z; }
+            for (size_t i = 0; i < texcoords.size(); ++i) { T[2 * i] = texcoords[i].x; T[2 * i + 1] = texcoords[i].y; }
+            for (size_t i = 0; i < normals.size(); ++i) { Nr[3 * i] = normals[i].x; Nr[3 * i + 1] = normals[i].y; Nr[3 * i + 2] = normals[i].z; }
+            m_F.resize(n); m_V.resize(3 * n);
+            if (!normals.empty()) m_N.resize(3 * n);
+            if (!texcoords.empty()) m_UV.resize(2 * n);
+            uint32_t nV = 0;
+            nori_gpu_ctx *ctx = operatorContext();
+            gpuCheck(ctx, nori_gpu_obj_dedup(ctx, cornerList.data(), (uint32_t) n, P.data(), (uint32_t) positions.size(), T.empty() ? nullptr : T.data(), (uint32_t) texcoords.size(),
+                                             Nr.empty() ? nullptr : Nr.data(), (uint32_t) normals.size(), m_F.data(), m_V.data(), m_N.empty() ? nullptr : m_N.data(),
+                                             m_UV.empty() ? nullptr : m_UV.data(), &nV, nullptr), "nori_gpu_obj_dedup");
+            m_V.resize(3 * (size_t) nV);
+            if (!m_N.empty()) m_N.resize(3 * (size_t) nV);
+            if (!m_UV.empty()) m_UV.resize(2 * (size_t) nV);
+        }
+        if (!onDevice) m_V.resize(3 * corners.size());
         for (size_t i = 0; i < corners.size(); ++i) {
             const Point3f &p = positions.at(corners[i].p - 1);
             m_V[3 * i] = p.x; m_V[3 * i + 1] = p.y; m_V[3 * i + 2] = p.z;
         }
-        if (!normals.empty()) {
+        if (!onDevice && !normals.empty()) {
             m_N.resize(3 * corners.size());
             for (size_t i = 0; i < corners.size(); ++i) {
                 const Normal3f &n = normals.at(corners[i].n - 1);
                 m_N[3 * i] = n.x; m_N[3 * i + 1] = n.y; m_N[3 * i + 2] = n.z;
             }
         }
-        if (!texcoords.empty()) {
+        if (!onDevice && !texcoords.empty()) {
             m_UV.resize(2 * corners.size());
             for (size_t i = 0; i < corners.size(); ++i) {
                 const Point2f &t = texcoords.at(corners[i].uv - 1);

@@ -144,6 +144,10 @@ bool Scene::rayIntersect(const Ray3f &ray) const {
 }
 
 // ---- BSDF operators: evaluated by the device code the renderer uses ------------------------------------
+static bool g_deviceObjDedup = false;
+bool deviceObjDedup() { return g_deviceObjDedup; }
+void setDeviceObjDedup(bool on) { g_deviceObjDedup = on; }
+
 nori_gpu_ctx *operatorContext() {
     static nori_gpu_ctx *ctx = nullptr;
     if (!ctx && nori_gpu_create(&ctx, 0) != NORI_GPU_OK)
