@@ -209,6 +209,9 @@ def run_gpu(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        with _QuietStdout():                       # NCCL announces its version on stdout when the communicator comes up: stdout carries one JSON line only
+            dist.barrier()
+            torch.cuda.synchronize()
 
     scene = load_scene()
     spp = args.spp

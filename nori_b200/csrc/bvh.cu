@@ -146,6 +146,53 @@ __global__ void k_plocMerge(const uint32_t *__restrict__ cluster, const uint32_t
     } else out[pos] = cluster[i];
 }
 
+/// Optional refinement of the PLOC tree (BvhParams::rotationPasses): tree rotations after Kensler 2008, bottom-up. At an inner
+/// node X = (A, B) with B = (B0, B1) the subtree A may change places with B0 or B1 (and symmetrically for A's children) when that
+/// shrinks the surface area of the child that is rebuilt — X's own box, hence everything above it, stays as it is. The second
+/// thread to arrive at a node processes it (as k_collapse): both subtrees are complete and nobody else touches them.
+__global__ void k_rotate(uint32_t n, float4 *__restrict__ blo, float4 *__restrict__ bhi, int *__restrict__ parent, uint32_t *__restrict__ visit, uint32_t *__restrict__ nRotations) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int cur = parent[i];
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(visit + cur, 1u) == 0) return;
+        __threadfence();
+        const int c[2] = {__float_as_int(blo[cur].w), __float_as_int(bhi[cur].w)};
+        float bestDelta = 0.f; int bestSide = -1, bestKeep = 0;
+        for (int s = 0; s < 2; ++s) {
+            const int inner = c[s], other = c[1 - s];
+            if (inner < (int) n) continue;                                   // a leaf has no children to trade
+            const float4 ilo = blo[inner], ihi = bhi[inner], olo = blo[other], ohi = bhi[other];
+            const float aOld = boxArea(make_float3(ilo.x, ilo.y, ilo.z), make_float3(ihi.x, ihi.y, ihi.z));
+            const int g[2] = {__float_as_int(ilo.w), __float_as_int(ihi.w)};
+            for (int keep = 0; keep < 2; ++keep) {                            // `keep` stays below `inner`, the other grandchild moves up
+                const float4 klo = blo[g[keep]], khi = bhi[g[keep]];
+                const float a = boxArea(make_float3(fminf(klo.x, olo.x), fminf(klo.y, olo.y), fminf(klo.z, olo.z)),
+                                        make_float3(fmaxf(khi.x, ohi.x), fmaxf(khi.y, ohi.y), fmaxf(khi.z, ohi.z)));
+                const float d = a - aOld;
+                if (d < bestDelta) { bestDelta = d; bestSide = s; bestKeep = keep; }
+            }
+        }
+        if (bestSide >= 0) {
+            const int inner = c[bestSide], other = c[1 - bestSide];
+            const float4 ilo = blo[inner], ihi = bhi[inner];
+            const int g[2] = {__float_as_int(ilo.w), __float_as_int(ihi.w)};
+            const int keep = g[bestKeep], up = g[1 - bestKeep];
+            const float4 klo = blo[keep], khi = bhi[keep], olo = blo[other], ohi = bhi[other];
+            // inner = (keep, other); cur = (inner, up) on the sides they had
+            blo[inner] = make_float4(fminf(klo.x, olo.x), fminf(klo.y, olo.y), fminf(klo.z, olo.z), __int_as_float(keep));
+            bhi[inner] = make_float4(fmaxf(khi.x, ohi.x), fmaxf(khi.y, ohi.y), fmaxf(khi.z, ohi.z), __int_as_float(other));
+            parent[other] = inner; parent[up] = cur;
+            float4 plo = blo[cur], phi = bhi[cur];
+            if (bestSide == 0) phi.w = __int_as_float(up); else plo.w = __int_as_float(up);
+            blo[cur] = plo; bhi[cur] = phi;
+            atomicAdd(nRotations, 1u);
+        }
+        cur = parent[cur];
+    }
+}
+
 /// Bottom-up SAH pass: subtree triangle counts, SAH cost, and the leaf-collapse decision.
 /// The second thread to arrive at a node processes it (both children are then complete).
 __global__ void k_collapse(uint32_t n, const float4 *__restrict__ blo, const float4 *__restrict__ bhi, const int *__restrict__ parent,
@@ -325,6 +372,13 @@ bool buildBvh(const float4 *d_vpos, const uint4 *d_tris, uint32_t N, const BvhPa
     }
     if (nextNode != total) { err = "PLOC node count mismatch (internal error)"; return false; }
     const uint32_t root = total - 1;
+
+    // 3b. optional rotations (off by default: measured, profiles/r02_notes.md)
+    for (int pass = 0; pass < prm.rotationPasses; ++pass) {
+        BVH_CHECK(cudaMemsetAsync(visit, 0, total * sizeof(uint32_t), st));
+        BVH_CHECK(cudaMemsetAsync(misc, 0, 4 * sizeof(uint32_t), st));
+        k_rotate<<<cdiv(N, T), T, 0, st>>>(N, blo, bhi, parent, visit, misc + 3);
+    }
 
     // 4. SAH collapse, DFS layout, emission
     BVH_CHECK(cudaMemsetAsync(visit, 0, total * sizeof(uint32_t), st));

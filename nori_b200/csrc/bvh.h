@@ -19,6 +19,7 @@ struct BvhParams {
     int maxLeaf = 4;           // triangles per leaf (<= 8: 3 bits in the leaf link)
     float costInner = 1.0f;    // SAH: one node visit (two child boxes)
     float costTri = 1.0f;      // SAH: one Moeller-Trumbore test
+    int rotationPasses = 0;    // bottom-up tree-rotation passes over the PLOC tree before the leaf collapse (k_rotate)
     float inflate = 4e-6f;     // child boxes grow by inflate * max(scene diagonal, max |coordinate|): ~60 float ulps
 };
 

@@ -203,6 +203,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     if (const char *s = getenv("NORI_GPU_POOL")) ctx->poolSize = std::max(256u, (uint32_t) strtoul(s, nullptr, 10) / 256u * 256u);
     if (const char *s = getenv("NORI_GPU_PLOC_RADIUS")) ctx->bvhParams.plocRadius = atoi(s);
     if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
+    if (const char *s = getenv("NORI_GPU_ROTATIONS")) ctx->bvhParams.rotationPasses = atoi(s);
     if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
     if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
     if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : NORI_ACCEL_FLOAT;
