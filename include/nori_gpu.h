@@ -244,7 +244,7 @@ typedef struct {
     float roughness;    /* Beckmann alpha (microfacet), else 0 */
     float pdf;          /* solid-angle density of wi (0: discrete) */
     float rrpdf;        /* Russian-roulette survival probability applied after this vertex (1 before roulette starts, 0 if the path ends) */
-    int32_t nidx;       /* 1: the next record is the next vertex of the same path (pbsdf.cu:1408 reads Index + 1), else 0 */
+    int32_t nidx;       /* record index of the next vertex of the same path (= own index + 1: pbsdf.cu:1408 reads Index + 1, :1749 compares nidx with an index), 0: the path ends here */
     int32_t groupIdx;   /* camera sample the vertex belongs to: pixel * spp + k */
     char bsdf_type;     /* 'd' diffuse, 'c' mirror (conductor, roughness 0), 't' dielectric, 'o' microfacet (opaque rough) */
 } NoriGpuSPoint;

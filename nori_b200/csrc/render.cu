@@ -991,7 +991,7 @@ __global__ void __launch_bounds__(128) k_pathVertices(DeviceScene sc, RenderPara
         if (gid == kNoHit) break;
         NoriGpuSPoint *rec = nullptr;
         if (WRITE) {
-            if (nv > 0) out[base + nv - 1].nidx = 1;                       // the previous vertex has a successor on this path
+            if (nv > 0) out[base + nv - 1].nidx = (int32_t) (base + nv);   // the previous vertex has a successor: its record index (pbsdf.cu:1749 compares nidx with an index)
             rec = out + base + nv;
             Hit its; fillHit(sc, gid, t, u, v, its);
             const MeshInfo &m = sc.meshes[its.mesh];

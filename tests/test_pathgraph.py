@@ -132,7 +132,8 @@ def test_gpu_path_vertices_and_their_graph(gpu_scene, scenes, port):
     first = np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]])
     assert (np.diff(v["groupIdx"]) >= 0).all()                        # path-contiguous, in camera-sample order
     # every non-last vertex of a path points at its successor
-    nxt = np.nonzero(v["nidx"][:-1] == 1)[0]
+    nxt = np.nonzero(v["nidx"][:-1] > 0)[0]
+    assert (v["nidx"][nxt] == nxt + 1).all()                          # nidx = record index of the successor
     assert (v["groupIdx"][nxt + 1] == v["groupIdx"][nxt]).all() and (~first[nxt + 1]).all()
     seg = v["pos"][nxt + 1] - v["pos"][nxt]
     length = np.linalg.norm(seg, axis=1)
