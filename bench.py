@@ -66,31 +66,58 @@ def measured_peak():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region."""
+    """SM clock + throttle reasons DURING a timed region. NVML in-process (nvidia_ml_py: a query takes ~1 ms, sampled every 50 ms,
+    so that even a 0.3 s region gets several samples); falls back to polling nvidia-smi (one query can take a second on an 8-GPU box)."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}   # nvml.h nvmlClocksEventReason*
+    _nvml = None
 
     def __init__(self, gpu: int):
         super().__init__(daemon=True)
-        self.gpu, self.rows, self.stop_flag = gpu, [], threading.Event()
+        self.gpu, self.sm, self.mx, self.reasons, self.stop_flag, self.source = gpu, [], [], set(), threading.Event(), "nvidia-smi"
+        self.handle = None
+        try:
+            import pynvml
+            if ClockSampler._nvml is None:
+                pynvml.nvmlInit(); ClockSampler._nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(gpu)
+            self.source = "nvml"
+        except Exception:
+            self.handle = None
+
+    def _sample_nvml(self):
+        n = ClockSampler._nvml
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        self.mx.append(float(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(n, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        mask = int(get(self.handle))
+        self.reasons |= {k for k, bit in self.BITS.items() if mask & bit}
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        r = [x.strip() for x in out.split(",")] if out else []
+        if r and r[0].replace(".", "").isdigit():
+            self.sm.append(float(r[0]))
+        if len(r) > 1 and r[1].replace(".", "").isdigit():
+            self.mx.append(float(r[1]))
+        self.reasons |= {n for i, n in enumerate(self.NAMES) if len(r) > 2 + i and r[2 + i].lower().startswith("active")}
 
     def run(self):
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                self._sample_nvml() if self.handle is not None else self._sample_smi()
             except Exception:
-                pass
-            self.stop_flag.wait(0.2)
+                if self.handle is not None:
+                    self.handle, self.source = None, "nvidia-smi"         # NVML refused: poll nvidia-smi instead
+            self.stop_flag.wait(0.05 if self.handle is not None else 0.2)
 
     def summary(self):
         self.stop_flag.set()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+        self.join(timeout=6)
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": [n for n in self.NAMES if n in self.reasons], "samples": len(self.sm), "source": self.source}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -448,6 +475,7 @@ def to_bitmap(block, border):
 # ------------------------------------------------------------------------------------------------
 def timed_render(eng, scene, spp, warm_spp, gpu):
     """Loads `scene`, one warm-up render, one timed render under a clock sampler. Device time from the call's own CUDA events."""
+    t0 = time.perf_counter(); eng.load_scene(scene); first_ms = (time.perf_counter() - t0) * 1e3     # incl. first-use allocations (pinned staging ring)
     t0 = time.perf_counter(); accel = eng.load_scene(scene); load_ms = (time.perf_counter() - t0) * 1e3
     eng.set_profiling(True)
     eng.render(sample_first=0, sample_last=warm_spp, download=False)
@@ -462,7 +490,7 @@ def timed_render(eng, scene, spp, warm_spp, gpu):
             "Gsegments_per_s": st["segments"] / ms / 1e6, "segments_per_sample": st["segments"] / max(st["camera_samples"], 1),
             "stages_ms": {"closest+splat": st["ms_trace_closest"], "shade": st["ms_shade"], "shadow": st["ms_trace_shadow"]},
             "iterations": st["iterations"], "gpu_launches": st["kernel_launches"], "triangles": accel["n_triangles"], "nodes": accel["n_nodes"],
-            "build_ms_device": accel["build_ms"], "upload_and_build_ms_wall": load_ms, "sah_cost": accel["sah_cost"], "clocks": clocks}
+            "build_ms_device": accel["build_ms"], "upload_and_build_ms_wall": load_ms, "upload_and_build_ms_wall_first_call": first_ms, "sah_cost": accel["sah_cost"], "clocks": clocks}
 
 
 def measure_configs(eng, torch, gpu, hbm):

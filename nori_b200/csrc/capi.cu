@@ -36,7 +36,7 @@ struct nori_gpu_ctx {
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 23;   // 8 Mi path slots (sweep: profiles/r01_pipeline.md)
-    Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirror
+    Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirrors: two (one per batch in flight)
     // host -> device staging for large pageable arrays (stagedCopy): kUploadWorkers host threads x 2 pinned buffers each (sweep on the GPU box, C4 240 MB: 4 x 8 MB 19.3 ms, 8 x 4 MB 13.4 ms, 8 x 8 15.8, 12 x 4 14.4, 8 x 2 15.1, 16 x 2 18.3; plain pageable copies 26 ms)
 #ifndef NORI_UPLOAD_WORKERS
 #define NORI_UPLOAD_WORKERS 8
@@ -195,7 +195,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     cudaGetDeviceProperties(&ctx->prop, device_id);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaMalloc((void **) &ctx->d_counters, sizeof(Counters))) != cudaSuccess ||
-        (e = cudaMallocHost((void **) &ctx->h_counters, sizeof(Counters))) != cudaSuccess) {
+        (e = cudaMallocHost((void **) &ctx->h_counters, 2 * sizeof(Counters))) != cudaSuccess) {
         g_createError = cudaGetErrorString(e); delete ctx; return NORI_GPU_ECUDA;
     }
     memset(&ctx->cam, 0, sizeof(ctx->cam)); memset(&ctx->filter, 0, sizeof(ctx->filter)); memset(&ctx->pool, 0, sizeof(ctx->pool));
@@ -474,14 +474,19 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     // Stage events (profiling): 4 per iteration of a batch, read back after the batch's one
     // synchronisation, so that profiling does not change how the kernels are queued.
     const int batch = 8;
+    // Two batches are kept in flight while camera samples are still being handed out: the host reads the counters of batch k
+    // while batch k + 1 already runs, so the device never idles for the round trip (26 of them per 1024-spp frame, ~0.27 ms each).
+    // Nothing the host decides in that phase depends on the counters. Once every sample has been issued (tail: compaction,
+    // k_finishTail, termination) the loop falls back to one batch of 2 iterations at a time.
     struct Events {                              // destroyed on every return path
-        cudaEvent_t e0 = nullptr, e1 = nullptr, evCopy = nullptr; std::vector<cudaEvent_t> stage;
-        ~Events() { for (cudaEvent_t e : {e0, e1, evCopy}) if (e) cudaEventDestroy(e); for (cudaEvent_t e : stage) if (e) cudaEventDestroy(e); }
+        cudaEvent_t e0 = nullptr, e1 = nullptr, evCopy[2] = {nullptr, nullptr}; std::vector<cudaEvent_t> stage;
+        ~Events() { for (cudaEvent_t e : {e0, e1, evCopy[0], evCopy[1]}) if (e) cudaEventDestroy(e); for (cudaEvent_t e : stage) if (e) cudaEventDestroy(e); }
     } evs;
-    evs.stage.assign(ctx->profiling ? 4 * batch : 0, nullptr);
-    cudaEvent_t &e0 = evs.e0, &e1 = evs.e1, &evCopy = evs.evCopy;
+    evs.stage.assign(ctx->profiling ? 2 * 4 * batch : 0, nullptr);
+    cudaEvent_t &e0 = evs.e0, &e1 = evs.e1;
     std::vector<cudaEvent_t> &stage = evs.stage;
-    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreateWithFlags(&evCopy, cudaEventDisableTiming));
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (cudaEvent_t &e : evs.evCopy) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : stage) CK(cudaEventCreate(&e));
     StageTimes tm = {0, 0, 0, 0, 0};
     CK(cudaEventRecord(e0, st));
@@ -490,29 +495,41 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
 #ifdef NORI_GPU_SWEEP
     const bool debug = getenv("NORI_GPU_DEBUG") != nullptr;
     const uint32_t kTailPaths = getenv("NORI_GPU_TAIL") ? (uint32_t) atoi(getenv("NORI_GPU_TAIL")) : 262144u;   // sweep: profiles/r01_pipeline.md
+    const int depthSteady = getenv("NORI_GPU_NO_PIPELINE") ? 1 : 2;
 #else
     const bool debug = false;
     const uint32_t kTailPaths = 262144u;
+    const int depthSteady = 2;
 #endif
     uint64_t guard = 0;
-    bool drainedBefore = false, tailDone = false;
-    int batchNow = batch;                        // iterations enqueued between two looks at the counters
+    bool drainedBefore = false, tailDone = false, drainedSeen = false;
+    int batchNow = batch;                        // iterations per batch
+    int inFlight = 0, head = 0, sizes[2] = {0, 0};   // ring of batches whose counters have not been looked at yet: [head, head + inFlight)
+    const Counters *last = ctx->h_counters;
     while (!done) {
-        for (int k = 0; k < batchNow; ++k)
-            launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 4 * k : nullptr);
-        CK(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-        CK(cudaEventRecord(evCopy, st));
-        CK(cudaEventSynchronize(evCopy));
+        const int depth = drainedSeen ? 1 : depthSteady;
+        while (inFlight < depth) {
+            const int b = (head + inFlight) & 1;
+            for (int k = 0; k < batchNow; ++k)
+                launches += (uint64_t) enqueueIteration(sc, pool, rp, ctx->d_counters, st, ctx->profiling ? stage.data() + 4 * (b * batch + k) : nullptr);
+            CK(cudaMemcpyAsync(ctx->h_counters + b, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+            CK(cudaEventRecord(evs.evCopy[b], st));
+            sizes[b] = batchNow; ++inFlight;
+        }
+        const int b = head;
+        CK(cudaEventSynchronize(evs.evCopy[b]));
         CK(cudaGetLastError());
+        head ^= 1; --inFlight;
         if (ctx->profiling) {
-            for (int k = 0; k < batchNow; ++k) {
-                cudaEvent_t *ev = stage.data() + 4 * k; float ms;
+            for (int k = 0; k < sizes[b]; ++k) {
+                cudaEvent_t *ev = stage.data() + 4 * (b * batch + k); float ms;
                 cudaEventElapsedTime(&ms, ev[0], ev[1]); tm.traceClosest += ms;    // splat of the previous iteration runs under it
                 cudaEventElapsedTime(&ms, ev[1], ev[2]); tm.shade += ms;           // k_prepare + k_shadeRegen
                 cudaEventElapsedTime(&ms, ev[2], ev[3]); tm.traceShadow += ms;
             }
         }
-        const Counters &hc = *ctx->h_counters;
+        const Counters &hc = ctx->h_counters[b];
+        last = &hc;
         if (debug) { float tms = 0; cudaEventRecord(e1, st); cudaEventSynchronize(e1); cudaEventElapsedTime(&tms, e0, e1); fprintf(stderr, "[nori_gpu] t=%.3fms cap=%u live=%u ", tms, pool.capacity, hc.liveLast); }
         if (debug) fprintf(stderr, "[nori_gpu] it=%llu issue=%llu/%llu limit=%llu finished=%llu/%llu passes=%u/%u splat=[%u %u %u %u]\n", (unsigned long long) hc.iterations, (unsigned long long) hc.issue, (unsigned long long) rp.totalIssue, (unsigned long long) hc.issueLimit, (unsigned long long) hc.finished, (unsigned long long) totalSamples, hc.completedPasses, rp.numPasses, hc.tilesSplatted[0], hc.tilesSplatted[1], hc.tilesSplatted[2], hc.tilesSplatted[3]);
         done = hc.finished >= totalSamples && (list || hc.completedPasses >= rp.numPasses);
@@ -521,7 +538,11 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         // (liveLast bounds the occupied slots only once a whole batch has run without regeneration.)
         // (issue overshoots its limit transiently: every free slot adds to it before k_prepare clamps it)
         const bool drained = std::min<unsigned long long>(hc.issue, hc.issueLimit) >= rp.totalIssue;
-        if (!done && drained && drainedBefore && pool.capacity > 4096u && 2ull * hc.liveLast <= pool.capacity) {
+        if (drained && !drainedSeen) {           // first sight of the tail: from here on the counters steer the loop, no look-ahead
+            drainedSeen = true; batchNow = 2;
+            if (inFlight) { drainedBefore = true; continue; }   // the batch already queued behind this one ran without regeneration: examine it before anything is decided
+        }
+        if (!done && drained && drainedBefore && inFlight == 0 && pool.capacity > 4096u && 2ull * hc.liveLast <= pool.capacity) {
             const uint32_t newCap = std::max(4096u, (hc.liveLast + 255u) / 256u * 256u);
             launches += (uint64_t) enqueueCompaction(pool, newCap, ctx->d_counters, st);
             pool.capacity = newCap;
@@ -530,8 +551,12 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
             if (newCap <= kTailPaths && !tailDone) { launches += (uint64_t) enqueueFinishTail(sc, pool, rp, ctx->d_counters, st); tailDone = true; }
         }
         drainedBefore = drained;
-        if (drained) batchNow = 2;               // the pool empties within a few bounces: look (and compact) more often than every 8 iterations
         if (++guard > 4000000ull) { ctx->err = "render: wavefront did not terminate (internal error)"; return NORI_GPU_ECUDA; }
+    }
+    while (inFlight) {                           // a look-ahead batch still queued when the end was seen: its counters are the final ones
+        const int b2 = head;
+        CK(cudaEventSynchronize(evs.evCopy[b2]));
+        last = ctx->h_counters + b2; head ^= 1; --inFlight;
     }
     CK(cudaEventRecord(e1, st));
     CK(cudaStreamSynchronize(st));
@@ -539,7 +564,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     if (int r = reportChecks(ctx, "render")) return r;
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     if (out) {
-        const Counters &hc = *ctx->h_counters;
+        const Counters &hc = *last;
         memset(out, 0, sizeof(*out));
         uint64_t rays = hc.closestRays, shadows = hc.shadowRays + hc.shadowCount;
         for (int k = 0; k < kNumKeys; ++k) rays += hc.sortCount[k];

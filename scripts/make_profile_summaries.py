@@ -28,7 +28,7 @@ def launches():
         if "at::" in r["Kernel Name"]: continue            # bench.py's L2 flush (torch), not a kernel of this library
         a = agg.setdefault(short(r["Kernel Name"]), [0, 0.0]); a[0] += 1; a[1] += v
     tot = sum(a[1] for a in agg.values())
-    out = ["# %s: launch list of `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu`" % tag, "",
+    out = ["# %s: launch list of `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu --no-configs`" % tag, "",
            "`ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 400` (steady state of the wavefront",
            "loop, the tail of one frame and the start of the next; 8 Mi path slots; times are cold-cache and serialised,",
            "so read the SHARES). Raw list: `%s_launches.csv`." % tag, "",
@@ -59,7 +59,7 @@ def kernels():
     per = collections.OrderedDict()
     for d in data: per.setdefault(short(d[ix["Kernel Name"]]), []).append(d)
     md = ["# %s: `ncu --set full` counters (per launch, averaged over the captured launches)" % tag, "",
-          "Command: `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu`, `-s 60 -c 8`, cbox path_mis, 8 Mi path slots", "(about 5.4 M live rays per launch).", ""]
+          "Command: `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu --no-configs`, `-k regex:k_trace|k_shade|k_splatPixel -s 60 -c 8`, cbox path_mis, 8 Mi path slots", "(about 5.4 M live rays per launch).", ""]
     names = list(per)
     md += ["| counter | " + " | ".join("`%s`" % n for n in names) + " |", "|---|" + "---:|" * len(names)]
     table = {}

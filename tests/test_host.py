@@ -62,3 +62,28 @@ def test_two_rank_reduce_equals_single_render(port, tmp_path):
     s = load_scene("cbox_mis"); s.width, s.height = 48, 36
     want, _ = port.scene(s).render(mode=1, sample_first=0, sample_last=6, threads=1)
     np.testing.assert_allclose(np.load(out), want, rtol=1e-5, atol=1e-6)
+
+
+# ---- bench.py host logic (round 2) -------------------------------------------------------------------------------------
+def test_bench_helpers():
+    """bench.py pieces that need no GPU: the camera resize reproduces PerspectiveCamera::activate for the fixture's own size
+    (so the C5 frame is the same camera at 3840x2160), rel-MSE / toBitmap, the host CPU record, and the issue model the roofline reads."""
+    import json, os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import bench
+    s = bench.load_scene()
+    same = bench.resize_camera(s, s.width, s.height)
+    np.testing.assert_allclose(same.sample_to_camera, s.sample_to_camera, rtol=2e-6, atol=1e-7)
+    big = bench.resize_camera(s, 3840, 2160)
+    assert (big.width, big.height) == (3840, 2160) and big.block_shape() == (2164, 3844, 4)
+    blk = np.zeros((8, 8, 4), np.float32); blk[..., :3] = 2.0; blk[..., 3] = 4.0; blk[3, 3, 3] = 0.0
+    bmp = bench.to_bitmap(blk, 2)
+    assert bmp.shape == (4, 4, 3) and bmp[0, 0, 0] == 0.5 and bmp[1, 1, 0] == 0.0          # rgb / w, zero weight -> 0
+    assert bench.rel_mse(bmp, bmp) == 0.0 and bench.rel_mse(bmp + 0.1, bmp) > 0
+    info = bench.host_cpu_info()
+    assert info["logical_cpus"] >= 1
+    im = json.load(open(os.path.join(root, "profiles", "issue_model.json")))
+    k = im["kernels"]["k_traceClosest"]
+    assert 50 < k["warp_inst_per_ray"] < 400 and 1 <= k["lanes_per_inst"] <= 32 and k["dram_bytes_per_ray"] > 0
+    assert {"k_shadeRegen", "k_traceShadow"} <= set(im["kernels"])
