@@ -728,6 +728,15 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
 /// walks the K samples of its pixel and accumulates their (2B+1)^2 footprint in registers; only
 /// then does it touch the shared-memory ImageBlock (one atomic per cell and channel per pass
 /// instead of one per sample), which the CTA finally adds to the full-frame block.
+/// A tile is shared by 4 quadrants x kSplatSlices sample slices (slice z takes the samples k = z, z + S, ... of every pixel).
+/// Measured (profiles/r02_notes.md): more slices make the step SLOWER (closest + splat stage 202.0 / 204.3 / 207.3 / 213.4 ms for
+/// S = 1 / 2 / 4 / 8). A splat CTA holds 248 registers x 256 threads = the whole register file of its SM, so no traversal CTA can
+/// share the SM with it: what the splat costs the overlapped traversal is the SM-time it occupies, and spreading the same work
+/// over more SMs for a shorter time only adds the per-CTA set-up and flush. S = 1 stays.
+#ifndef NORI_SPLAT_SLICES
+#define NORI_SPLAT_SLICES 1
+#endif
+constexpr uint32_t kSplatSlices = NORI_SPLAT_SLICES;
 template <int B>
 __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams rp, Counters *c) {
     // Programmatic dependent launch: the closest-hit pass queued behind this kernel does not read
@@ -737,8 +746,8 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
     __shared__ float plane[4][SIDE * SIDE];
     __shared__ float sTable[33];
     __shared__ unsigned sDropped;
-    for (uint32_t work = blockIdx.x; work < c->readyCount * 4u; work += gridDim.x) {
-    const uint32_t tiq = rp.readyTiles[work >> 2], z = work & 3u;
+    for (uint32_t work = blockIdx.x; work < c->readyCount * 4u * kSplatSlices; work += gridDim.x) {
+    const uint32_t tiq = rp.readyTiles[work / (4u * kSplatSlices)], z = (work / kSplatSlices) & 3u, slice = work % kSplatSlices;
     NG_CHECK(tiq < (uint32_t) rp.ring * rp.numTiles);
     const uint32_t slot = tiq / rp.numTiles, tile = tiq - slot * rp.numTiles;
     const uint32_t pass = c->slotPass[slot];
@@ -772,7 +781,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
             const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp + pix;
             unsigned dropped = 0;
 #pragma unroll 2
-            for (uint32_t k = 0; k < Kp; ++k) {
+            for (uint32_t k = slice; k < Kp; k += kSplatSlices) {
                 const size_t r = base + (size_t) k * 1024u;
                 NG_CHECK(r < rp.recCount);
                 const float4 a = rp.recA[r];
@@ -828,7 +837,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
     }
     if (threadIdx.x == 0) {
         __threadfence();
-        if (atomicAdd(rp.tileArrive + ti, 1u) == 3u) {                            // last quadrant of this tile
+        if (atomicAdd(rp.tileArrive + ti, 1u) == 4u * kSplatSlices - 1u) {        // last quadrant and slice of this tile
             rp.tileArrive[ti] = 0;
             rp.tileDone[ti] = 0;
             rp.tileGen[ti] = pass / (uint32_t) rp.ring + 1;
