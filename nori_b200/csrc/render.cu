@@ -18,6 +18,7 @@
 #include "engine.h"
 #include <cstdlib>
 #include "traverse_persistent.cuh"
+#include <cuda_pipeline.h>
 
 namespace ng {
 
@@ -737,17 +738,35 @@ __global__ void __launch_bounds__(256) k_splat(DeviceScene sc, RenderParams rp, 
 #define NORI_SPLAT_SLICES 1
 #endif
 constexpr uint32_t kSplatSlices = NORI_SPLAT_SLICES;
-template <int B>
-__global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams rp, Counters *c) {
+#ifndef NORI_SPLAT_THREADS
+#define NORI_SPLAT_THREADS 256
+#endif
+constexpr int kSplatThreads = NORI_SPLAT_THREADS;
+template <int B, int NT>
+__global__ void __launch_bounds__(NT) k_splatPixel(DeviceScene sc, RenderParams rp, Counters *c) {
     // Programmatic dependent launch: the closest-hit pass queued behind this kernel does not read
     // anything the splat writes, so it may start filling the SMs this grid leaves free right away.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    constexpr int WN = 2 * B + 1, Q = 16, SIDE = Q + 2 * B;
-    __shared__ float plane[4][SIDE * SIDE];
+    // NT threads = a 16 x QH block of the tile (NT = 256: a quadrant; NT = 128: half a quadrant, 8 CTAs per tile, half the
+    // registers per CTA so that traversal CTAs can share the SM with it)
+    constexpr int WN = 2 * B + 1, Q = 16, QH = NT / 16, SIDE = Q + 2 * B, SIDEH = QH + 2 * B;
+    constexpr uint32_t NSUB = 1024u / NT;
+    static_assert(NT == 256 || NT == 128, "one thread per pixel of a 16 x 16 or 16 x 8 block");
+    __shared__ float plane[4][SIDE * SIDEH];
     __shared__ float sTable[33];
     __shared__ unsigned sDropped;
-    for (uint32_t work = blockIdx.x; work < c->readyCount * 4u * kSplatSlices; work += gridDim.x) {
-    const uint32_t tiq = rp.readyTiles[work / (4u * kSplatSlices)], z = (work / kSplatSlices) & 3u, slice = work % kSplatSlices;
+    // Per-thread ring of sample records, filled with cp.async kSplatAhead - 1 samples ahead of the one being splatted: the kernel
+    // runs 8 warps per SM (248 registers) and used to wait for every record load in turn (20 bytes per sample, latency-bound).
+    // Each thread reads back only what it copied itself: no barrier, just its own async-copy groups. [stage][thread]: conflict-free.
+#ifndef NORI_SPLAT_AHEAD
+#define NORI_SPLAT_AHEAD 4
+#endif
+    constexpr uint32_t kSplatAhead = NORI_SPLAT_AHEAD;
+    static_assert((kSplatAhead & (kSplatAhead - 1)) == 0, "ring size must be a power of two");
+    __shared__ float4 sRecA[kSplatAhead > 1 ? kSplatAhead : 1][NT];
+    __shared__ float sRecB[kSplatAhead > 1 ? kSplatAhead : 1][NT];
+    for (uint32_t work = blockIdx.x; work < c->readyCount * NSUB * kSplatSlices; work += gridDim.x) {
+    const uint32_t tiq = rp.readyTiles[work / (NSUB * kSplatSlices)], z = (work / kSplatSlices) % NSUB, slice = work % kSplatSlices;
     NG_CHECK(tiq < (uint32_t) rp.ring * rp.numTiles);
     const uint32_t slot = tiq / rp.numTiles, tile = tiq - slot * rp.numTiles;
     const uint32_t pass = c->slotPass[slot];
@@ -758,17 +777,17 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
     const uint32_t ti = slot * rp.numTiles + tile;
     __syncthreads();                                                            // shared tile is reused across work items
     const int qx = (int) (z & 1u), qy = (int) (z >> 1);
-    if (qx * Q < tw && qy * Q < th) {
-        for (int k = threadIdx.x; k < SIDE * SIDE; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
+    if (qx * Q < tw && qy * QH < th) {
+        for (int k = threadIdx.x; k < SIDE * SIDEH; k += blockDim.x) { plane[0][k] = 0.f; plane[1][k] = 0.f; plane[2][k] = 0.f; plane[3][k] = 0.f; }
         if (threadIdx.x < 33) sTable[threadIdx.x] = sc.filter.table[threadIdx.x];
         if (threadIdx.x == 0) sDropped = 0;
         __syncthreads();
         // thread -> record slot of its pixel (inverse of tilePixel: warps are 8x4 pixel patches)
         const uint32_t wi = threadIdx.x >> 5;
-        const uint32_t wq = (wi & 1u) + 2u * (uint32_t) qx + 4u * ((wi >> 1) + 4u * (uint32_t) qy);
+        const uint32_t wq = (wi & 1u) + 2u * (uint32_t) qx + 4u * ((wi >> 1) + (uint32_t) (QH / 4) * (uint32_t) qy);   // 8 x 4 pixel patches: 4 across, 8 down the tile
         const uint32_t pix = wq * 32u + (threadIdx.x & 31u);
         int lx, ly; tilePixel(pix, lx, ly);
-        const int tx = lx - qx * Q, ty = ly - qy * Q;              // position inside the quadrant
+        const int tx = lx - qx * Q, ty = ly - qy * QH;              // position inside the quadrant
         float acc[WN][WN][4];
 #pragma unroll
         for (int i = 0; i < WN; ++i)
@@ -780,13 +799,29 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
             const int cols = tw + 2 * B, rows = th + 2 * B;
             const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp + pix;
             unsigned dropped = 0;
+            const uint32_t nK = Kp > slice ? (Kp - slice + kSplatSlices - 1u) / kSplatSlices : 0u;      // samples of this slice: k = slice + j * S
+            auto fetch = [&](uint32_t j) {
+                const size_t r = base + (size_t) (slice + j * kSplatSlices) * 1024u;
+                __pipeline_memcpy_async(&sRecA[j & (kSplatAhead - 1u)][threadIdx.x], rp.recA + r, 16);
+                __pipeline_memcpy_async(&sRecB[j & (kSplatAhead - 1u)][threadIdx.x], rp.recB + r, 4);
+            };
+            if (kSplatAhead > 1) {
+                for (uint32_t j = 0; j + 1u < kSplatAhead; ++j) { if (j < nK) fetch(j); __pipeline_commit(); }
+            }
 #pragma unroll 2
-            for (uint32_t k = slice; k < Kp; k += kSplatSlices) {
+            for (uint32_t j = 0; j < nK; ++j) {
+                const uint32_t k = slice + j * kSplatSlices;
                 const size_t r = base + (size_t) k * 1024u;
                 NG_CHECK(r < rp.recCount);
-                const float4 a = rp.recA[r];
+                float4 a; float recb;
+                if (kSplatAhead > 1) {
+                    if (j + kSplatAhead - 1u < nK) fetch(j + kSplatAhead - 1u);
+                    __pipeline_commit();
+                    __pipeline_wait_prior(kSplatAhead - 1u);                     // the group that carried sample j has landed
+                    a = sRecA[j & (kSplatAhead - 1u)][threadIdx.x]; recb = sRecB[j & (kSplatAhead - 1u)][threadIdx.x];
+                } else { a = rp.recA[r]; recb = rp.recB[r]; }
                 if (isnan(a.x)) continue;                                        // still in flight (forced close)
-                const V3 val = mk(a.z, a.w, rp.recB[r]);
+                const V3 val = mk(a.z, a.w, recb);
                 rp.recA[r].x = __int_as_float(0x7fc00000);                       // consumed
                 if (!isValidColor(val)) { ++dropped; continue; }                 // block.cpp:75-79
                 const float px = a.x - 0.5f - (float) (ox - B), py = a.y - 0.5f - (float) (oy - B);   // block.cpp:82-85
@@ -815,7 +850,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
 #pragma unroll
                 for (int j = 0; j < WN; ++j) {
                     const int cell = (ty + i) * SIDE + tx + j;
-                    NG_CHECK(cell >= 0 && cell < SIDE * SIDE);
+                    NG_CHECK(cell >= 0 && cell < SIDE * SIDEH);
                     if (acc[i][j][3] != 0.f) {
                         atomicAdd(&plane[0][cell], acc[i][j][0]); atomicAdd(&plane[1][cell], acc[i][j][1]);
                         atomicAdd(&plane[2][cell], acc[i][j][2]); atomicAdd(&plane[3][cell], acc[i][j][3]);
@@ -823,13 +858,13 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
                 }
         }
         __syncthreads();
-        // quadrant cell (x, y) is full-frame cell (ox + 16 qx + x, oy + 16 qy + y)
-        for (int k = threadIdx.x; k < SIDE * SIDE; k += blockDim.x) {
+        // block cell (x, y) is full-frame cell (ox + 16 qx + x, oy + QH qy + y)
+        for (int k = threadIdx.x; k < SIDE * SIDEH; k += blockDim.x) {
             const float4 v = make_float4(plane[0][k], plane[1][k], plane[2][k], plane[3][k]);
             if (v.w == 0.f) continue;
             const int x = k % SIDE, y = k / SIDE;
-            NG_CHECK(oy + qy * Q + y < rp.blockRows && ox + qx * Q + x < rp.blockCols);
-            float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + qy * Q + y) * rp.blockCols + (ox + qx * Q + x);
+            NG_CHECK(oy + qy * QH + y < rp.blockRows && ox + qx * Q + x < rp.blockCols);
+            float4 *dst = reinterpret_cast<float4 *>(rp.block) + (size_t) (oy + qy * QH + y) * rp.blockCols + (ox + qx * Q + x);
             atomicAdd(dst, v);
         }
         __syncthreads();
@@ -837,7 +872,7 @@ __global__ void __launch_bounds__(256) k_splatPixel(DeviceScene sc, RenderParams
     }
     if (threadIdx.x == 0) {
         __threadfence();
-        if (atomicAdd(rp.tileArrive + ti, 1u) == 4u * kSplatSlices - 1u) {        // last quadrant and slice of this tile
+        if (atomicAdd(rp.tileArrive + ti, 1u) == NSUB * kSplatSlices - 1u) {     // last block and slice of this tile
             rp.tileArrive[ti] = 0;
             rp.tileDone[ti] = 0;
             rp.tileGen[ti] = pass / (uint32_t) rp.ring + 1;
@@ -1175,9 +1210,9 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         const unsigned g = persistentGrid() / 8u;          // one resident CTA per SM (248 registers x 256 threads): a single wave, so
                                                            // that every CTA reaches launch_dependents at once
         switch (sc.filter.border) {
-        case 0: k_splatPixel<0><<<g, 256, 0, st>>>(sc, rp, c); break;
-        case 1: k_splatPixel<1><<<g, 256, 0, st>>>(sc, rp, c); break;
-        case 2: k_splatPixel<2><<<g, 256, 0, st>>>(sc, rp, c); break;
+        case 0: k_splatPixel<0, kSplatThreads><<<g, kSplatThreads, 0, st>>>(sc, rp, c); break;
+        case 1: k_splatPixel<1, kSplatThreads><<<g, kSplatThreads, 0, st>>>(sc, rp, c); break;
+        case 2: k_splatPixel<2, kSplatThreads><<<g, kSplatThreads, 0, st>>>(sc, rp, c); break;
         default: k_splat<<<g, 256, 0, st>>>(sc, rp, c); break;
         }
         ++launches;
