@@ -155,6 +155,12 @@ int nori_gpu_reduce_blocks(nori_gpu_ctx *const *ctxs, int n, int root);
 int nori_gpu_device_count(void);
 int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on);   /* per-stage CUDA-event timing (serialises stages) */
 int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n_paths);
+/* Ray binning of the wavefront renderer (default on): after every shade pass the path slots are counting-sorted by
+ * (origin cell of the scene box, two direction signs) and the next closest-hit pass walks them in that order, so that the
+ * lanes of a warp traverse neighbouring rays. Changes which lane traces which ray, never a result: images are identical with
+ * it on or off. No counterpart in the reference (its render loop, src/main.cpp:57-100, traces one ray at a time per thread).
+ * Pools beyond 16 Mi slots render without it. */
+int nori_gpu_set_ray_binning(nori_gpu_ctx *ctx, int on);
 /* Mesh::rayIntersect variant (src/mesh.cpp:51-88) used by the raw operators below (trace, trace_device,
  * trace_count, intersect): NORI_ISECT_*. nori_gpu_render takes it from NoriGpuRenderDesc::intersect_mode. */
 int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode);

@@ -50,6 +50,7 @@ struct nori_gpu_ctx {
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
+    bool rayBins = true;                        // bounce rays binned by origin cell + direction signs between shade and the next closest-hit pass (nori_gpu_set_ray_binning)
     int accelLayout = NORI_ACCEL_FLOAT;         // node layout the persistent traversal kernels read
     int isectMode = NORI_ISECT_REFERENCE_MT;   // used by the raw operators; nori_gpu_render takes it from its descriptor
 };
@@ -102,11 +103,14 @@ void freePool(nori_gpu_ctx *c) {
     Pool &p = c->pool;
     cudaFree(p.rayO); cudaFree(p.rayD); cudaFree(p.hit); cudaFree(p.thr); cudaFree(p.rad); cudaFree(p.state); cudaFree(p.info);
     cudaFree(p.pos); cudaFree(p.shadow);
+    cudaFree(p.key); cudaFree(p.order); cudaFree(p.sortTmp);
     c->havePool = false;
 }
 
 int ensurePool(nori_gpu_ctx *ctx) {
-    if (ctx->havePool && ctx->pool.capacity == ctx->poolSize) return 0;
+    // the sort word keeps the slot number in 24 bits: pools beyond 16 Mi slots render without binning
+    const bool bins = ctx->rayBins && ctx->poolSize <= kBinSlotMask + 1u;
+    if (ctx->havePool && ctx->pool.capacity == ctx->poolSize && (ctx->pool.order != nullptr) == bins) return 0;
     freePool(ctx);
     Pool &p = ctx->pool; const size_t n = ctx->poolSize;
     memset(&p, 0, sizeof(p));
@@ -115,6 +119,11 @@ int ensurePool(nori_gpu_ctx *ctx) {
     CK(cudaMalloc((void **) &p.thr, n * 16)); CK(cudaMalloc((void **) &p.rad, n * 16)); CK(cudaMalloc((void **) &p.state, n * 16));
     CK(cudaMalloc((void **) &p.info, n * 16)); CK(cudaMalloc((void **) &p.pos, n * 8));
     CK(cudaMalloc((void **) &p.shadow, n * 48));
+    if (bins) {
+        CK(cudaMalloc((void **) &p.key, n * 4)); CK(cudaMalloc((void **) &p.order, n * 4));
+        p.sortTmpBytes = binSortTmpBytes(ctx->poolSize);
+        CK(cudaMalloc(&p.sortTmp, p.sortTmpBytes));
+    }
     ctx->havePool = true;
     return 0;
 }
@@ -204,6 +213,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     if (const char *s = getenv("NORI_GPU_PLOC_RADIUS")) ctx->bvhParams.plocRadius = atoi(s);
     if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
     if (const char *s = getenv("NORI_GPU_ROTATIONS")) ctx->bvhParams.rotationPasses = atoi(s);
+    if (const char *s = getenv("NORI_GPU_BINS")) ctx->rayBins = atoi(s) != 0;
     if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
     if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
     if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : NORI_ACCEL_FLOAT;
@@ -432,6 +442,10 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     // Slots used by this render: never more than there are camera samples (small frames, sample lists)
     const uint64_t wanted = list ? (uint64_t) listCount : (uint64_t) W * H * (d->sample_last - d->sample_first);
     Pool pool = ctx->pool;                       // .capacity also shrinks in the tail of the render (enqueueCompaction)
+    for (int k = 0; k < 3; ++k) {
+        const float ext = ctx->bvh.sceneHi[k] - ctx->bvh.sceneLo[k];
+        pool.binLo[k] = ctx->bvh.sceneLo[k]; pool.binInv[k] = ext > 0.f ? 4.0f / ext : 0.f;
+    }
     pool.capacity = (uint32_t) std::min<uint64_t>(ctx->pool.capacity, std::max<uint64_t>(4096, (wanted + 255) / 256 * 256));
     if (list) {
         rp.K = rp.Klast = 1; rp.numPasses = 1; rp.passSlots = listCount; rp.totalIssue = listCount; rp.ring = 1;
@@ -546,6 +560,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
             const uint32_t newCap = std::max(4096u, (hc.liveLast + 255u) / 256u * 256u);
             launches += (uint64_t) enqueueCompaction(pool, newCap, ctx->d_counters, st);
             pool.capacity = newCap;
+            enqueueIdentityOrder(pool, newCap, st);         // paths changed slots: the next closest-hit pass walks the pool in slot order
             // A few thousand paths left: one launch follows each of them to its end (k_finishTail)
             // instead of one launch-bound wavefront iteration per bounce of the longest path.
             if (newCap <= kTailPaths && !tailDone) { launches += (uint64_t) enqueueFinishTail(sc, pool, rp, ctx->d_counters, st); tailDone = true; }
@@ -627,6 +642,11 @@ int nori_gpu_li(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, int n, const floa
     return NORI_GPU_OK;
 }
 
+int nori_gpu_set_ray_binning(nori_gpu_ctx *ctx, int on) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    ctx->rayBins = on != 0;          // takes effect at the next render (ensurePool reallocates the two index arrays)
+    return NORI_GPU_OK;
+}
 int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(mode == NORI_ISECT_REFERENCE_MT || mode == NORI_ISECT_WATERTIGHT, "set_intersect_mode: unknown mode");

@@ -30,7 +30,13 @@ struct Pool {
     uint4 *info;         // ring slot * numTiles + tile, sample index, record index, -   (written when the path starts, read when it ends)
     float2 *pos;         // pixelSample handed to ImageBlock::put
     float4 *shadow;      // 3 x capacity: (o, maxt) (d, bits(slot)) (contribution, -)
+    // Ray binning (off unless `order` is set): the shade kernel writes (bin << 24 | slot) per slot — bin = origin cell, 2 bits per
+    // axis of the scene box, + two direction sign bits; fresh camera rays and empty slots in bins of their own —, ONE 8-bit radix
+    // pass over those words orders the slot numbers by bin, and the closest-hit pass walks `order` instead of the pool.
+    uint32_t *key, *order; void *sortTmp; size_t sortTmpBytes;
+    float binLo[3], binInv[3];
 };
+constexpr uint32_t kBinFresh = 0xfeu, kBinEmpty = 0xffu, kBinSlotMask = 0x00ffffffu;
 
 struct Counters {
     unsigned long long issue, issueLimit, finished;
@@ -73,6 +79,11 @@ struct RenderParams {
 };
 
 struct StageTimes { float generate, traceClosest, shade, traceShadow, splat; };
+
+/// order[i] = i for i < n (ray binning: after the tail compaction moved paths between slots).
+void enqueueIdentityOrder(const Pool &pool, uint32_t n, cudaStream_t st);
+/// Bytes of scratch the per-iteration radix pass needs for n slots.
+size_t binSortTmpBytes(uint32_t n);
 
 /// Marks every slot of the pool empty (start of a render).
 void enqueuePoolInit(const Pool &pool, Counters *d_counters, cudaStream_t st);

@@ -71,6 +71,24 @@ __device__ __forceinline__ Pcg32 unpackRng(const uint4 &st) {
     return r;
 }
 
+/// Sort word of a bounce ray: bin (2 bits of origin cell per axis of the scene box, two direction sign bits) << 24 | slot.
+#ifndef NORI_BIN_DIRS
+#define NORI_BIN_DIRS 0      // which two direction signs: 0 = (x, y), 1 = (x, z), 2 = (y, z)
+#endif
+__device__ __forceinline__ uint32_t binWord(const Pool &pool, const Ray &ray, uint32_t slot) {
+    const int cx = min(max((int) ((ray.o.x - pool.binLo[0]) * pool.binInv[0]), 0), 3);
+    const int cy = min(max((int) ((ray.o.y - pool.binLo[1]) * pool.binInv[1]), 0), 3);
+    const int cz = min(max((int) ((ray.o.z - pool.binLo[2]) * pool.binInv[2]), 0), 3);
+#if NORI_BIN_DIRS >= 3      // 3 / 4: the full direction octant, paid for with one bit of the z / y cell
+    const int cell = NORI_BIN_DIRS == 3 ? (cx | (cy << 2) | ((cz >> 1) << 4)) : (cx | (cz << 2) | ((cy >> 1) << 4));
+    const uint32_t bin = min((uint32_t) ((cell << 3) | (ray.d.x < 0.f ? 1 : 0) | (ray.d.y < 0.f ? 2 : 0) | (ray.d.z < 0.f ? 4 : 0)), 0xfdu);
+#else
+    const float da = NORI_BIN_DIRS == 2 ? ray.d.y : ray.d.x, db = NORI_BIN_DIRS == 0 ? ray.d.y : ray.d.z;
+    const uint32_t bin = min((uint32_t) (((cx | (cy << 2) | (cz << 4)) << 2) | (da < 0.f ? 1 : 0) | (db < 0.f ? 2 : 0)), 0xfdu);
+#endif
+    return (bin << 24) | slot;
+}
+
 /// Pixel of slot r (< 1024) inside a tile: warps cover 8x4 pixel patches (coherent primary rays).
 __device__ __forceinline__ void tilePixel(uint32_t pix, int &lx, int &ly) {
     uint32_t w = pix >> 5, l = pix & 31u;
@@ -100,15 +118,17 @@ __device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Count
 // ------------------------------------------------------------------------------------------
 struct ClosestIO {
     Pool pool;
-    __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
-        NG_CHECK(i < pool.capacity);
+    __device__ __forceinline__ bool load(uint32_t k, V3 &o, V3 &d, float &mint, float &maxt) const {
+        NG_CHECK(k < pool.capacity);
+        const uint32_t i = pool.order ? (pool.order[k] & kBinSlotMask) : k;
         if (!(pool.state[i].w & kFlagAlive)) return false;
         const float4 ro = pool.rayO[i], rd = pool.rayD[i];
         o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
         return true;
     }
-    __device__ __forceinline__ void store(uint32_t i, uint32_t gid, float t, float u, float v) const {
-        NG_CHECK(i < pool.capacity);
+    __device__ __forceinline__ void store(uint32_t k, uint32_t gid, float t, float u, float v) const {
+        NG_CHECK(k < pool.capacity);
+        const uint32_t i = pool.order ? (pool.order[k] & kBinSlotMask) : k;
         pool.hit[i] = make_float4(t, u, v, __uint_as_float(gid));
     }
 };
@@ -403,7 +423,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
         }
     }
     if (!ok) {
-        if (!wasEmpty) pool.state[dst] = make_uint4(0, 0, 0, 0);
+        if (!wasEmpty) { pool.state[dst] = make_uint4(0, 0, 0, 0); if (pool.order) pool.key[dst] = (kBinEmpty << 24) | dst; }
         return;
     }
     NG_CHECK(dst < pool.capacity && (rp.listPixel || (tileSlot < (uint32_t) rp.ring * rp.numTiles && rec < rp.passSlots)));
@@ -429,6 +449,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
     pool.pos[dst] = make_float2(ps.x, ps.y);
     pool.state[dst] = packState(rng, kFlagAlive | kFlagDiscrete | (ring << 24));
     pool.info[dst] = make_uint4(tileSlot, sampleIndex, rec, 0u);
+    if (pool.order) pool.key[dst] = (kBinFresh << 24) | dst;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -535,7 +556,9 @@ __global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeReg
             pool.thr[slot] = make_float4(T.x, T.y, T.z, bsdfPdf);
             pool.rad[slot] = make_float4(L.x, L.y, L.z, eta);
             pool.state[slot] = packState(rng, flags);
+            if (pool.order) pool.key[slot] = binWord(pool, ray, slot);
         } else {
+            if (pool.order) pool.key[slot] = (kBinEmpty << 24) | slot;   // ended or parked; a regeneration later in this kernel overwrites it
             info = pool.info[slot];
             const bool mulT = flags & kFlagMulT;
             const bool late = !rp.listPixel && info.y - rp.sampleFirst < lateBelow;
@@ -1151,10 +1174,109 @@ int enqueueCompaction(const Pool &pool, uint32_t newCapacity, Counters *c, cudaS
 __global__ void k_poolInit(Pool pool, Counters *c) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     pool.state[i] = make_uint4(0, 0, 0, 0);
+    if (pool.order) { pool.key[i] = (kBinEmpty << 24) | i; pool.order[i] = i; }
     if (i == 0) {                                   // what k_prepare would have left: the first splat pass runs before it
         c->forcePass = 0xffffffffu;
         for (int s = 0; s < kMaxRing; ++s) c->slotPass[s] = (unsigned) s;
     }
+}
+__global__ void k_identityOrder(Pool pool, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) pool.order[i] = i;
+}
+void enqueueIdentityOrder(const Pool &pool, uint32_t n, cudaStream_t st) { if (pool.order && n) k_identityOrder<<<(n + 255u) / 256u, 256, 0, st>>>(pool, n); }
+// ---- ray binning: a counting sort of the (bin << 24 | slot) words by bin, specialised for 256 bins -----------------------------
+// Three small kernels instead of a general radix pass (cub::DeviceRadixSort::SortKeys over bits 24..31: profiles/r02_notes.md).
+// One CTA per chunk of kBinChunk consecutive words:
+//   k_binCount    shared-memory histogram of the chunk -> counts[bin][chunk]            (no global atomics)
+//   k_binScan     one warp per bin: exclusive offsets over the chunks (in place), totals[bin] behind the matrix
+//   k_binScatter  the chunk again, sorted by bin inside shared memory first, so that consecutive threads write consecutive words
+//                 of a (bin, chunk) run (a word stored straight to its place costs a 32-byte sector per lane: 3x slower).
+//                 The lanes of a warp that hold fresh camera rays take one range of the cursor and keep their order, so the
+//                 primary rays of one pixel patch stay neighbours; inside the other bins the order is whatever the
+//                 shared-memory atomics make it, which only decides which lanes trace which rays.
+constexpr int kBinChunk = 8192, kBinThreads = 512, kBins = 256;
+
+__global__ void __launch_bounds__(kBinThreads) k_binCount(const uint32_t *__restrict__ key, uint32_t n, uint32_t nChunks, uint32_t *__restrict__ counts) {
+    __shared__ unsigned int hist[kBins];
+    for (int b = threadIdx.x; b < kBins; b += kBinThreads) hist[b] = 0;
+    __syncthreads();
+    const uint32_t lo = blockIdx.x * kBinChunk, hi = min(n, lo + kBinChunk);
+    uint32_t k[kBinChunk / kBinThreads];
+#pragma unroll
+    for (int j = 0; j < kBinChunk / kBinThreads; ++j) { const uint32_t i = lo + j * kBinThreads + threadIdx.x; k[j] = i < hi ? key[i] : 0u; }
+#pragma unroll
+    for (int j = 0; j < kBinChunk / kBinThreads; ++j) if (lo + j * kBinThreads + threadIdx.x < hi) atomicAdd(&hist[k[j] >> 24], 1u);
+    __syncthreads();
+    for (int b = threadIdx.x; b < kBins; b += kBinThreads) counts[b * nChunks + blockIdx.x] = hist[b];
+}
+__device__ __forceinline__ unsigned int warpInclusive(unsigned int v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+    return v;
+}
+__global__ void __launch_bounds__(256) k_binScan(uint32_t *__restrict__ counts /* in: counts, out: offsets; then totals[kBins] */, uint32_t nChunks) {
+    const int bin = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    uint32_t *row = counts + (size_t) bin * nChunks;
+    unsigned int carry = 0;
+#pragma unroll 4
+    for (uint32_t c0 = 0; c0 < nChunks; c0 += 32) {
+        const uint32_t c = c0 + lane;
+        const unsigned int v = c < nChunks ? row[c] : 0u, incl = warpInclusive(v, lane);
+        if (c < nChunks) row[c] = carry + incl - v;
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) counts[(size_t) kBins * nChunks + bin] = carry;
+}
+__global__ void __launch_bounds__(kBinThreads) k_binScatter(const uint32_t *__restrict__ key, uint32_t n, uint32_t nChunks, const uint32_t *__restrict__ offsets, uint32_t *__restrict__ order) {
+    __shared__ uint32_t stage[kBinChunk];
+    __shared__ unsigned int cursor[kBins], shift[kBins], wsumA[kBins / 32], wsumB[kBins / 32];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t chunk = blockIdx.x, lo = chunk * kBinChunk, hi = min(n, lo + kBinChunk);
+    uint32_t k[kBinChunk / kBinThreads];
+#pragma unroll
+    for (int j = 0; j < kBinChunk / kBinThreads; ++j) { const uint32_t i = lo + j * kBinThreads + tid; k[j] = i < hi ? key[i] : 0u; }
+    // two exclusive scans over the bins: the totals (where a bin starts in the output) and this chunk's counts (where it starts in stage[])
+    unsigned int tot = 0, cnt = 0, goff = 0, inclA = 0, inclB = 0;
+    if (tid < kBins) {
+        tot = offsets[(size_t) kBins * nChunks + tid];
+        goff = offsets[(size_t) tid * nChunks + chunk];
+        cnt = (chunk + 1 < nChunks ? offsets[(size_t) tid * nChunks + chunk + 1] : tot) - goff;
+        inclA = warpInclusive(tot, lane); inclB = warpInclusive(cnt, lane);
+        if (lane == 31) { wsumA[tid >> 5] = inclA; wsumB[tid >> 5] = inclB; }
+    }
+    __syncthreads();
+    if (tid < kBins) {
+        unsigned int preA = 0, preB = 0;
+        for (int w = 0; w < (tid >> 5); ++w) { preA += wsumA[w]; preB += wsumB[w]; }
+        const unsigned int lstart = preB + inclB - cnt;                    // where the bin starts in stage[]
+        cursor[tid] = lstart;
+        shift[tid] = preA + inclA - tot + goff - lstart;                    // stage[] index -> output index (mod 2^32)
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kBinChunk / kBinThreads; ++j) {
+        const bool valid = lo + j * kBinThreads + tid < hi;
+        const uint32_t bin = k[j] >> 24;
+        const unsigned int fresh = __ballot_sync(0xffffffffu, valid && bin == kBinFresh);
+        unsigned int baseF = 0;
+        if (lane == 0 && fresh) baseF = atomicAdd(&cursor[kBinFresh], (unsigned int) __popc(fresh));
+        baseF = __shfl_sync(0xffffffffu, baseF, 0);
+        if (valid) stage[bin == kBinFresh ? baseF + __popc(fresh & ((1u << lane) - 1u)) : atomicAdd(&cursor[bin], 1u)] = k[j];
+    }
+    __syncthreads();
+    for (uint32_t t = tid; t < hi - lo; t += kBinThreads) {
+        const uint32_t w = stage[t], bin = w >> 24;
+        order[shift[bin] + t] = w;
+    }
+}
+size_t binSortTmpBytes(uint32_t n) { return (size_t) ((n + kBinChunk - 1) / kBinChunk + 1) * kBins * sizeof(uint32_t); }
+static void enqueueBinSort(const Pool &pool, cudaStream_t st) {
+    uint32_t *counts = static_cast<uint32_t *>(pool.sortTmp);
+    const uint32_t n = pool.capacity, nChunks = (n + kBinChunk - 1) / kBinChunk;
+    k_binCount<<<nChunks, kBinThreads, 0, st>>>(pool.key, n, nChunks, counts);
+    k_binScan<<<kBins / 8, 256, 0, st>>>(counts, nChunks);
+    k_binScatter<<<nChunks, kBinThreads, 0, st>>>(pool.key, n, nChunks, counts, pool.order);
 }
 void enqueuePoolInit(const Pool &pool, Counters *c, cudaStream_t st) { k_poolInit<<<pool.capacity / 256, 256, 0, st>>>(pool, c); }
 
@@ -1242,6 +1364,10 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     default: launchShade<NORI_INT_AO>(sc, pool, rp, c, st); break;
     }
     ++launches;
+    if (pool.order) {                               // one 8-bit radix pass over (bin << 24 | slot): slot numbers ordered by bin for the next closest-hit pass
+        enqueueBinSort(pool, st);
+        launches += 3;
+    }
     if (ev) cudaEventRecord(ev[2], st);
     if (rp.integrator != NORI_INT_NORMALS) {
         const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;

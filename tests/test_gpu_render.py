@@ -128,6 +128,26 @@ def test_small_pool_and_odd_sizes(gpu_scene, scenes):
         e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
 
 
+def test_ray_binning_never_changes_the_image(gpu_scene, scenes):
+    """nori_gpu_set_ray_binning: the counting sort of the slots between bounces only decides which lane traces which ray.
+    Same samples -> the same hits, radiance and splats (up to the summation order inside a pixel, as between two pool sizes):
+    on the default pool, on a pool small enough for tail compaction to kick in, and switched back on (the index arrays are
+    reallocated)."""
+    e = gpu_scene("cbox_mis"); s = scenes("cbox_mis")
+    try:
+        imgs = []
+        for on, pool in ((True, 1 << 21), (False, 1 << 21), (True, 4096), (False, 4096), (True, 1 << 21)):
+            e.set_ray_binning(on); e.set_pool_size(pool)
+            block, st = e.render(sample_first=0, sample_last=6)
+            assert st["camera_samples"] == 6 * s.width * s.height
+            imgs.append(block)
+        for b in imgs[1:]:
+            np.testing.assert_allclose(b[..., 3], imgs[0][..., 3], rtol=1e-5, atol=1e-6)
+            np.testing.assert_allclose(b, imgs[0], rtol=2e-4, atol=1e-5)
+    finally:
+        e.set_ray_binning(True); e.set_pool_size(1 << 21)
+
+
 def test_tiny_pool_many_tiles_splat_outlasts_trace(gpu_scene, scenes):
     """Stream ordering of the overlapped launch: with a 4 096-slot pool over 640 tiles the closest-hit pass takes
     microseconds while the splat of the previous iteration still has whole tiles to go. k_prepare must nevertheless
