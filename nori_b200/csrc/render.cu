@@ -822,7 +822,11 @@ __global__ void __launch_bounds__(NT) k_splatPixel(DeviceScene sc, RenderParams 
             const int cols = tw + 2 * B, rows = th + 2 * B;
             const size_t base = (size_t) slot * rp.passSlots + (size_t) tile * 1024u * Kp + pix;
             unsigned dropped = 0;
+#ifdef NORI_SPLAT_SKIP          // timing experiment: what the stage costs without the sample loop (images are wrong)
+            const uint32_t nK = 0u;
+#else
             const uint32_t nK = Kp > slice ? (Kp - slice + kSplatSlices - 1u) / kSplatSlices : 0u;      // samples of this slice: k = slice + j * S
+#endif
             auto fetch = [&](uint32_t j) {
                 const size_t r = base + (size_t) (slice + j * kSplatSlices) * 1024u;
                 __pipeline_memcpy_async(&sRecA[j & (kSplatAhead - 1u)][threadIdx.x], rp.recA + r, 16);
