@@ -244,7 +244,9 @@ typedef struct {
     float shN[3], geoN[3];
     float diffuse[3];   /* albedo (diffuse), kd (microfacet), 0 otherwise */
     float specular[3];  /* ks (microfacet), 1 (mirror, dielectric), 0 (diffuse) */
-    float eLi[3], eLd[3];   /* radiance fields of the later stages: written as 0 by this slice */
+    float eLi[3], eLd[3];   /* eLd: what the path estimator credits to this vertex itself (emission seen from the previous vertex with its MIS
+                             * weight + the light sample if unoccluded) as radiance leaving towards wo; eLi: the same for the whole path
+                             * suffix from this vertex on (eLi of a path's first vertex = the camera sample's radiance) */
     float eta[3];       /* intIOR / extIOR (dielectric, microfacet), else 0 */
     float k[3];         /* conductor absorption: 0 (Nori has no conductor) */
     float roughness;    /* Beckmann alpha (microfacet), else 0 */
@@ -278,6 +280,27 @@ int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uint64_t strid
                            int32_t *neighbors, int32_t *knn, int32_t *dknn, float *ms);
 /* SPoints::BuildKNN's grid (shadingPoint.h:794-801) for a cell count per axis: bounding box of the points, cellsize = extent / dim. */
 int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int n, const int32_t dim[3], int k, int dk, NoriGpuHashParams *out);
+/* computeScatterAllOnGPURecord (src/pbsdf.cu:2317-2368), the second slice of the tool: the marginal density of every vertex's
+ * continuation direction over its neighbourhood (allGPUPdfMarginal, :1738-1756), then `iterations` passes of
+ *   blur[it] = radiance scattered over the k-nearest-neighbour graph (allGPUScatterRadiance, :1398-1431: vertex i hands
+ *              temp[i + 1] * bsdf_j(wi_i) / pdfmarginal[i] to each neighbour j);
+ *   temp     = eLi, or blur[it] + eLd once it >= 1 (updateRadiance, :2185-2194, called with the loop index: passes 0 and 1
+ *              therefore scatter the same temp = eLi, :2344-2356);
+ *   mc[it]   = the vertex's own one-sample estimate temp[i + 1] * bsdf_i(wi_i) / (pdf_i(wi_i) * rrpdf_i) with that updated temp
+ *              (lastRun, :1497-1526).
+ * bsdf / pdf are the TOOL's evaluations from the record fields (bsdfeval_device / pdf_device, :464-628: clamped dot products,
+ * its own microfacet and conductor models), not Nori's BSDF plugins. points: n records (HOST); neighbors: n rows of row_ints
+ * ints, the first knn[i] of row i are read (what nori_gpu_pathgraph_knn returns); pdfmarginal: n floats or NULL; blur, mc:
+ * iterations x n x 3 floats. The scatter sums are atomic, here as in the reference: equal up to the order of float additions.
+ * ms: device time without the copies. */
+int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
+                               const int32_t *knn, int iterations, float *pdfmarginal, float *blur, float *mc, float *ms);
+/* The tool's whole pipeline in one call, as SPoints::BuildKNN + the scatter driver run it (include/nori/shadingPoint.h:776-806,
+ * 484-503): hash grid + kNN over the records' positions, then the scatter stage on the rows the search left ON THE DEVICE (the k
+ * consumer's count knn[i] of each row, as shadingPoint.h:500 passes cu_knn). Same results as nori_gpu_pathgraph_knn followed by
+ * nori_gpu_pathgraph_scatter without the round trip of the n x max(k, dk) rows through host memory. ms[0]: search, ms[1]: scatter. */
+int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
+                              float *pdfmarginal, float *blur, float *mc, float ms[2]);
 
 #ifdef __cplusplus
 }

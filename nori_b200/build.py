@@ -13,8 +13,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnori_b200.so")
-SOURCES = ["capi.cu", "render.cu", "operators.cu", "bvh.cu", "pathgraph.cu", "objdedup.cu"]
-HEADERS = ["engine.h", "bvh.h", "check.cuh", "nmath.cuh", "scene.cuh", "traverse.cuh", "traverse_persistent.cuh", "pathgraph.h", os.path.join("..", "..", "include", "nori_gpu.h")]
+SOURCES = ["capi.cu", "render.cu", "operators.cu", "bvh.cu", "pathgraph.cu", "pathgraph_scatter.cu", "objdedup.cu"]
+HEADERS = ["engine.h", "bvh.h", "check.cuh", "nmath.cuh", "scene.cuh", "traverse.cuh", "traverse_persistent.cuh", "pathgraph.h", "pathgraph_bsdf.cuh", os.path.join("..", "..", "include", "nori_gpu.h")]
 # -fmad=false: the arithmetic order written in nmath.cuh is the order executed (bit parity with
 # the x86-64 reference build, which has no FMA). Division and sqrt stay IEEE (nvcc defaults).
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",

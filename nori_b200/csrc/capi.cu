@@ -1116,6 +1116,86 @@ extern "C" int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uin
     return NORI_GPU_OK;
 }
 
+namespace {
+/// Device side of the scatter stage shared by the two entry points: rows already on the device and validated.
+int pathgraphScatterOnDevice(nori_gpu_ctx *ctx, const NoriGpuSPoint *d_sps, int n, const int *d_nb, int rowInts, const int *d_knn, int iterations,
+                             float *pdfmarginal, float *blur, float *mc, float *ms) {
+    DevBuf<unsigned char> scratch; DevBuf<float> pm, db, dm;
+    CK(scratch.alloc(pgScatterScratchBytes(n))); CK(pm.alloc(n));
+    const size_t resultFloats = (size_t) std::max(iterations, 1) * 3 * (size_t) n;
+    CK(db.alloc(resultFloats)); CK(dm.alloc(resultFloats));
+    cudaStream_t st = ctx->stream;
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    if (!launchPathgraphScatter(d_sps, n, d_nb, rowInts, d_knn, iterations, scratch.p, pm.p, db.p, dm.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    if (pdfmarginal) CK(cudaMemcpyAsync(pdfmarginal, pm.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    if (iterations > 0) {
+        CK(cudaMemcpyAsync(blur, db.p, (size_t) iterations * 3 * n * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(mc, dm.p, (size_t) iterations * 3 * n * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (ms) cudaEventElapsedTime(ms, e0, e1);
+    unsigned line = 0;
+    if (const unsigned bad = pathgraphScatterChecks(&line)) { ctx->err = "pathgraph_scatter: device range check failed (" + std::to_string(bad) + " at pathgraph_scatter.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
+}
+
+extern "C" int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
+                                          const int32_t *knn, int iterations, float *pdfmarginal, float *blur, float *mc, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(points && neighbors && knn && n > 0 && row_ints >= 1 && iterations >= 0, "pathgraph_scatter: bad arguments");
+    REQUIRE(iterations == 0 || (blur && mc), "pathgraph_scatter: blur and mc must hold iterations x n x 3 floats");
+    REQUIRE(iterations <= 64, "pathgraph_scatter: more than 64 iterations");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<NoriGpuSPoint> sps; DevBuf<int> nb, kn, flag;
+    CK(sps.alloc(n)); CK(nb.alloc((size_t) n * row_ints)); CK(kn.alloc(n)); CK(flag.alloc(1));
+    cudaStream_t st = ctx->stream;
+    if (int rc = stagedCopy(ctx, sps.p, points, (size_t) n * sizeof(NoriGpuSPoint))) return rc;
+    if (int rc = stagedCopy(ctx, nb.p, neighbors, (size_t) n * row_ints * 4)) return rc;
+    CK(cudaMemcpyAsync(kn.p, knn, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    // the kernels trust the rows: checked once, on the device copy
+    launchPathgraphValidate(nb.p, row_ints, row_ints, kn.p, n, flag.p, st);
+    int bad = 0;
+    CK(cudaMemcpyAsync(&bad, flag.p, sizeof(int), cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
+    REQUIRE(!(bad & 1), "pathgraph_scatter: knn[i] outside [0, row_ints]");
+    REQUIRE(!(bad & 2), "pathgraph_scatter: neighbour index outside [0, n)");
+    return pathgraphScatterOnDevice(ctx, sps.p, n, nb.p, row_ints, kn.p, iterations, pdfmarginal, blur, mc, ms);
+}
+
+extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
+                                         float *pdfmarginal, float *blur, float *mc, float ms[2]) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(points && hp && n > 0 && iterations >= 0 && iterations <= 64, "pathgraph_filter: bad arguments");
+    REQUIRE(iterations == 0 || (blur && mc), "pathgraph_filter: blur and mc must hold iterations x n x 3 floats");
+    REQUIRE(hp->k >= 1 && hp->dk >= 1 && hp->dim[0] >= 1 && hp->dim[1] >= 1 && hp->dim[2] >= 1, "pathgraph_filter: bad grid parameters");
+    const unsigned long long cells = (unsigned long long) hp->dim[0] * hp->dim[1] * hp->dim[2];
+    REQUIRE(cells < (1ull << 30), "pathgraph_filter: more than 2^30 grid cells");
+    REQUIRE(hp->cellsize[0] > 0 && hp->cellsize[1] > 0 && hp->cellsize[2] > 0, "pathgraph_filter: cell sizes must be positive");
+    CK(cudaSetDevice(ctx->device));
+    PgParams P;
+    for (int c = 0; c < 3; ++c) { P.minb[c] = hp->minb[c]; P.cell[c] = hp->cellsize[c]; P.dim[c] = hp->dim[c]; }
+    P.k = hp->k; P.dk = hp->dk; P.maxK = std::max(hp->k, hp->dk); P.nCells = (int) cells;
+    REQUIRE(P.maxK <= kPgMaxK, "pathgraph_filter: max(k, dk) above 200 is not supported");
+    DevBuf<NoriGpuSPoint> sps; DevBuf<unsigned char> scratch; DevBuf<int> nb, dk1, dk2;
+    CK(sps.alloc(n)); CK(scratch.alloc(pgScratchBytes(n, P.nCells))); CK(nb.alloc((size_t) n * P.maxK)); CK(dk1.alloc(n)); CK(dk2.alloc(n));
+    cudaStream_t st = ctx->stream;
+    if (int rc = stagedCopy(ctx, sps.p, points, (size_t) n * sizeof(NoriGpuSPoint))) return rc;
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    if (!launchPathgraphKnn(sps.p, sizeof(NoriGpuSPoint), n, P, scratch.p, nb.p, P.maxK, dk1.p, dk2.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    float msScatter = 0.f;
+    if (int rc = pathgraphScatterOnDevice(ctx, sps.p, n, nb.p, P.maxK, dk1.p, iterations, pdfmarginal, blur, mc, &msScatter)) return rc;
+    if (ms) { cudaEventElapsedTime(&ms[0], e0, e1); ms[1] = msScatter; }
+    unsigned line = 0;
+    if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_filter: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // nori_gpu_trace_static: Accel::rayIntersect for callers that must not allocate (CUDA graph capture, tight serving
 // loops, harnesses that forbid cudaMalloc). Everything nori_gpu_trace keeps in cudaMalloc'ed scratch — the device

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
+#include "../../include/nori_gpu.h"
 
 namespace ng {
 
@@ -20,5 +21,12 @@ size_t pgScratchBytes(int n, int nCells);
 bool launchPathgraphKnn(const void *d_pos, size_t strideBytes, int n, const PgParams &P, void *d_scratch, int *d_neighbors, int pitchInts,
                         int *d_knn, int *d_dknn, cudaStream_t st, std::string &err);
 unsigned pathgraphChecks(unsigned *line);
+
+/// pathgraph_scatter.cu: marginal densities + iterated radiance scatter over the kNN graph (src/pbsdf.cu:2317-2368).
+size_t pgScatterScratchBytes(int n);
+bool launchPathgraphScatter(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
+                            void *d_scratch, float *d_pdfmarginal, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
+void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
+unsigned pathgraphScatterChecks(unsigned *line);
 
 } // namespace ng

@@ -1085,14 +1085,35 @@ __global__ void __launch_bounds__(128) k_pathVertices(DeviceScene sc, RenderPara
         ++nv;
         ShadowOut sh;
         float rr = 1.0f;
+        const V3 Tb = T, Lb = L;                                     // throughput up to this vertex, radiance credited before it
         const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh, nullptr, &rr);
         if (WRITE) {
-            if (sh.cast) { rec->wi_d[0] = sh.d.x; rec->wi_d[1] = sh.d.y; rec->wi_d[2] = sh.d.z; }
+            if (sh.cast) {
+                rec->wi_d[0] = sh.d.x; rec->wi_d[1] = sh.d.y; rec->wi_d[2] = sh.d.z;
+                float st, su, sv;                                    // the light sample counts if its shadow ray is free (as k_li)
+                if (traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT) == kNoHit) L = L + sh.contrib;
+            }
             if (cont) { rec->wi[0] = ray.d.x; rec->wi[1] = ray.d.y; rec->wi[2] = ray.d.z; rec->pdf = bsdfPdf; rec->rrpdf = rr; }
+            // eLd: what the estimator credits to this vertex itself (emission seen from the previous vertex with its MIS weight +
+            // the light sample), as radiance leaving towards wo = the credited amount / the throughput up to here. eLi holds that
+            // throughput until the path has ended (the pass below turns it into the radiance of the whole path suffix).
+            const V3 dL = L - Lb;
+            rec->eLd[0] = Tb.x > 0.f ? dL.x / Tb.x : 0.f; rec->eLd[1] = Tb.y > 0.f ? dL.y / Tb.y : 0.f; rec->eLd[2] = Tb.z > 0.f ? dL.z / Tb.z : 0.f;
+            rec->eLi[0] = Tb.x; rec->eLi[1] = Tb.y; rec->eLi[2] = Tb.z;
         }
         if (!cont) break;
     }
-    if (!WRITE) counts[g] = nv;
+    if (WRITE) {
+        // eLi[j] = sum over the vertices m >= j of what the path credits to m, over the throughput up to j: the path's own
+        // estimate of the radiance leaving vertex j towards wo (eLi of a path's first vertex = the sample's radiance).
+        V3 acc = mk(0.f, 0.f, 0.f);
+        for (unsigned int j = nv; j-- > 0;) {
+            NoriGpuSPoint *rec = out + base + j;
+            const V3 Tj = mk(rec->eLi[0], rec->eLi[1], rec->eLi[2]);
+            acc = acc + mk(rec->eLd[0], rec->eLd[1], rec->eLd[2]) * Tj;
+            rec->eLi[0] = Tj.x > 0.f ? acc.x / Tj.x : 0.f; rec->eLi[1] = Tj.y > 0.f ? acc.y / Tj.y : 0.f; rec->eLi[2] = Tj.z > 0.f ? acc.z / Tj.z : 0.f;
+        }
+    } else counts[g] = nv;
 }
 
 bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t spp, unsigned long long nPaths, unsigned int *counts,

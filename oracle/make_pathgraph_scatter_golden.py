@@ -1,0 +1,80 @@
+"""Golden vectors of the path-graph scatter stage from the REFERENCE's own CUDA code (oracle/_ref/libpbsdf_ref.so = src/pbsdf.cu
+compiled unmodified). Needs a GPU: run on the GPU box, the result comes back through gpurun_out/ and is committed as
+tests/golden/pathgraph_scatter_ref.npz.   python oracle/make_pathgraph_scatter_golden.py [out.npz]
+
+Two parts: (eval_*) pdf_device / bsdfeval_device at synthetic records of all four material tags, one direction each; (sc_*)
+computeScatterAllOnGPURecord + allGPUPdfMarginal on path-vertex records. The records of the second part are INPUT only: they
+are whole paths of the table scene (diffuse + microfacet vertices) taken from nori_gpu_path_vertices, their neighbour rows come
+from the reference's own buildHashGridAndFindKNN."""
+import os, sys
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.pyoracle import RefCuda
+from nori_b200.gpu import SPOINT_DTYPE
+
+
+def unit(v):
+    return (v / np.linalg.norm(v, axis=-1, keepdims=True)).astype(np.float32)
+
+
+def synthetic_records(n, seed):
+    """Records that reach every branch of the tool's evaluations: four tags, grazing and below-surface directions, shading
+    normals that differ from the geometric ones, roughness from near-specular to rough, eta / k of metals and glass."""
+    rng = np.random.default_rng(seed)
+    s = np.zeros(n, SPOINT_DTYPE)
+    s["pos"] = rng.random((n, 3))
+    s["geoN"] = unit(rng.normal(size=(n, 3)))
+    s["shN"] = unit(s["geoN"] + 0.2 * rng.normal(size=(n, 3)))
+    s["wo"] = unit(s["shN"] + rng.normal(size=(n, 3)) * rng.choice([0.3, 1.0, 3.0], size=(n, 1)))
+    s["wi"] = unit(s["shN"] + rng.normal(size=(n, 3)) * rng.choice([0.3, 1.0, 3.0], size=(n, 1)))
+    s["diffuse"] = rng.random((n, 3)); s["specular"] = rng.random((n, 3))
+    s["roughness"] = rng.choice([0.02, 0.1, 0.3, 0.7], size=n) * (0.5 + rng.random(n))
+    s["eta"] = np.where(rng.random((n, 1)) < 0.5, 1.5, 0.2 + 2.0 * rng.random((n, 3)))
+    s["k"] = 1.0 + 3.0 * rng.random((n, 3))
+    s["rrpdf"] = rng.choice([1.0, 0.95, 0.5], size=n); s["pdf"] = rng.random(n)
+    s["bsdf_type"] = rng.choice(np.array([b"d", b"o", b"c", b"t"]), size=n, p=[0.35, 0.3, 0.3, 0.05])
+    # a few exact mirror configurations for the 't' branch as the tool builds them (components of wo negated: src/pbsdf.cu:450-454)
+    t = np.nonzero(s["bsdf_type"] == b"t")[0][::2]
+    s["wi"][t] = s["wo"][t] * np.array([-1, -1, 1], np.float32)
+    return s
+
+
+def main():
+    out = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "pathgraph_scatter_ref.npz")
+    ref = RefCuda()
+    res = {}
+    ev = synthetic_records(6000, 11)
+    pdf, f = ref.eval(ev, ev["wi"])
+    res["eval_sps"] = ev.view(np.uint8).reshape(len(ev), 168); res["eval_pdf"] = pdf; res["eval_bsdf"] = f
+
+    from nori_b200.gpu import Engine
+    from nori_b200.scene import FlatScene
+    s = FlatScene.load(os.path.join(ROOT, "tests", "golden", "scenes", "table_mis.npz"))
+    e = Engine(0); e.load_scene(s)
+    e.set_camera(s.sample_to_camera, s.camera_to_world, 96, 72, s.near_clip, s.far_clip)
+    v = e.path_vertices(sample_first=0, sample_last=1)
+    keep = v["bsdf_type"] != b"t"                       # the tool prints a line per dielectric evaluation: whole paths without glass only
+    bad_groups = np.unique(v["groupIdx"][~keep])
+    v = v[~np.isin(v["groupIdx"], bad_groups)]
+    # re-link: nidx = index of the successor inside the filtered array
+    nxt = np.nonzero(v["nidx"] > 0)[0]
+    v["nidx"][nxt] = nxt + 1
+    v = v[:7000]
+    last = np.nonzero(v["nidx"] == 0)[0][-1]
+    v = np.ascontiguousarray(v[:last + 1])             # whole paths only
+    pts = np.ascontiguousarray(v["pos"])
+    lo, hi = pts.min(0), pts.max(0); dim = np.array([4, 4, 4], np.int32)
+    cs = ((hi - lo) / dim).astype(np.float32)
+    k = 12
+    nb, knn, dknn, _ = ref.knn(pts, dim, cs, lo.astype(np.float32), k, k)
+    it = 3
+    pm, blur, mc, sec = ref.scatter(v, nb, knn, it)
+    res["sc_sps"] = v.view(np.uint8).reshape(len(v), 168); res["sc_nb"] = nb; res["sc_knn"] = knn
+    res["sc_pm"] = pm; res["sc_blur"] = blur; res["sc_mc"] = mc
+    np.savez_compressed(out, **res)
+    print("wrote", out, len(v), "records", {t: int((v["bsdf_type"] == t).sum()) for t in np.unique(v["bsdf_type"])}, "nan rows", int(np.isnan(blur).any(-1).sum()))
+
+
+if __name__ == "__main__":
+    main()

@@ -4,6 +4,7 @@
 // The product library (libnori_b200.so) never links or loads this file.
 #include "noracle_scene.h"
 #include "noracle_pathgraph.h"
+#include "noracle_pathgraph_scatter.h"
 #include <thread>
 #include <mutex>
 #include <atomic>
@@ -301,6 +302,17 @@ void noracle_pathgraph_knn(const float *pts, int n, const int *dim, const float 
     for (int c = 0; c < 3; ++c) { h.dim[c] = dim[c]; h.cellsize[c] = cellsize[c]; h.minb[c] = minb[c]; }
     h.k = k; h.dk = dk;
     pathgraphKnn(pts, n, h, neighbors, knn, dknn, dists);
+}
+
+/// Path-graph marginal densities + radiance scatter (noracle_pathgraph_scatter.h). sps: n SPoint records of 168 bytes.
+void noracle_pathgraph_scatter(const void *sps, int n, const int32_t *neighbors, int row_ints, const int32_t *knn, int iterations,
+                               int sequential, float *pdfmarginal, float *blur, float *mc) {
+    pathgraphScatter(static_cast<const SPointRec *>(sps), n, neighbors, row_ints, knn, iterations, sequential != 0, pdfmarginal, blur, mc);
+}
+/// The tool's evaluations at one vertex each: pdf[i] = pdf_device(sps[i], wi[i]), bsdf[i] = bsdfeval_device(sps[i], wi[i]).
+void noracle_pathgraph_eval(const void *sps, int n, const float *wi, float *pdf, float *bsdf) {
+    const SPointRec *p = static_cast<const SPointRec *>(sps);
+    for (int i = 0; i < n; ++i) { pdf[i] = pgs::pdfAt(p[i], wi + 3 * (size_t) i); pgs::bsdfAt(p[i], wi + 3 * (size_t) i, bsdf + 3 * (size_t) i); }
 }
 
 } // extern "C"

@@ -162,6 +162,8 @@ class Port:
         L.noracle_render.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _f32p, _u64p]
         L.noracle_render_counted.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, _u64p, _u64p]
         L.noracle_pathgraph_knn.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, _f32p]
+        L.noracle_pathgraph_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p]
+        L.noracle_pathgraph_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
 
     def pathgraph_knn(self, pts, dim, cellsize, minb, k, dk):
         """noracle_pathgraph.h: hash grid + kNN. Returns (neighbors, knn, dknn, dists) rows nearest first, self swapped to the front."""
@@ -169,6 +171,23 @@ class Port:
         nb = np.empty((n, mk), np.int32); a = np.empty(n, np.int32); b = np.empty(n, np.int32); d = np.empty((n, mk), np.float32)
         self.L.noracle_pathgraph_knn(pts, n, np.asarray(dim, np.int32), _f32(cellsize), _f32(minb), k, dk, nb, a, b, d)
         return nb, a, b, d
+
+    def pathgraph_scatter(self, sps, neighbors, knn, iterations, sequential=False):
+        """noracle_pathgraph_scatter.h: (pdfmarginal, blur (it, n, 3), mc (it, n, 3)). sequential: the marginal sums in list order
+        (the reference's single thread) instead of the product's lane order."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168
+        nb = np.ascontiguousarray(neighbors, np.int32); kn = np.ascontiguousarray(knn, np.int32)
+        pm = np.empty(n, np.float32); blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
+        self.L.noracle_pathgraph_scatter(sps.ctypes.data_as(C.c_void_p), n, nb, nb.shape[1], kn, iterations, int(sequential), pm, blur.reshape(-1), mc.reshape(-1))
+        return pm, blur[:iterations], mc[:iterations]
+
+    def pathgraph_eval(self, sps, wi):
+        """pdf_device / bsdfeval_device restated: (pdf (n,), bsdf (n, 3)) of record i for direction wi[i]."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]; wi = _f32(wi, (-1, 3))
+        pdf = np.empty(n, np.float32); f = np.empty((n, 3), np.float32)
+        self.L.noracle_pathgraph_eval(sps.ctypes.data_as(C.c_void_p), n, wi, pdf, f.reshape(-1))
+        return pdf, f
 
     def scene(self, scene: FlatScene, use_bvh=True) -> PortScene:
         return PortScene(self, scene, use_bvh)
@@ -230,6 +249,8 @@ class RefCuda:
             raise RuntimeError("oracle/_ref/libpbsdf_ref.so missing (run `make -C oracle refcuda` where /root/reference exists)")
         self.L = C.CDLL(REFCUDA_SO)
         self.L.refcuda_knn.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, C.POINTER(C.c_double)]
+        self.L.refcuda_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
+        self.L.refcuda_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
 
     def knn(self, pts, dim, cellsize, minb, k, dk):
         """buildHashGridAndFindKNN. Returns (neighbors n x max(k,dk), knn, dknn, seconds)."""
@@ -239,6 +260,27 @@ class RefCuda:
         if rc != 0:
             raise RuntimeError(f"refcuda_knn failed ({rc})")
         return nb, a, b, sec.value
+
+
+    def scatter(self, sps, neighbors, knn, iterations):
+        """computeScatterAllOnGPURecord + allGPUPdfMarginal: (pdfmarginal, blur (it, n, 3), mc (it, n, 3), seconds)."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168
+        nb = np.ascontiguousarray(neighbors, np.int32); kn = np.ascontiguousarray(knn, np.int32)
+        pm = np.empty(n, np.float32); blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32); sec = C.c_double()
+        rc = self.L.refcuda_scatter(sps.ctypes.data_as(C.c_void_p), n, nb, nb.shape[1], kn, iterations, pm, blur.reshape(-1), mc.reshape(-1), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_scatter failed ({rc})")
+        return pm, blur[:iterations], mc[:iterations], sec.value
+
+    def eval(self, sps, wi):
+        """pdf_device / bsdfeval_device of the compiled reference: (pdf (n,), bsdf (n, 3))."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]; wi = _f32(wi, (-1, 3))
+        pdf = np.empty(n, np.float32); f = np.empty((n, 3), np.float32)
+        rc = self.L.refcuda_eval(sps.ctypes.data_as(C.c_void_p), n, wi, pdf, f.reshape(-1))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_eval failed ({rc})")
+        return pdf, f
 
 
 def have_refcuda() -> bool:

@@ -38,3 +38,71 @@ extern "C" int refcuda_knn(const float *pos, int n, const int *dim, const float 
     cudaFree(cu_sps); cudaFree(cu_neighbors); cudaFree(cu_knn); cudaFree(cu_dknn);
     return e == cudaSuccess ? 0 : -3;
 }
+
+// ---- second slice: marginal densities + radiance scatter ---------------------------------------------------------------------
+// The reference's kernels, device functions and __constant__ parameters are reached across translation units (the Makefile
+// compiles with -rdc=true); nothing of them is restated here.
+extern __global__ void allGPUPdfMarginal(const SPoint *sps, const int *neighbors, const int *knn, float *pdfmarginal);   // src/pbsdf.cu:1738
+extern __device__ void pdf_device(const SPoint sp, const float *wi, float *pdf);                                         // src/pbsdf.cu:562
+extern __device__ void bsdfeval_device(const SPoint sp, const float *wi, float *bsdf, bool t);                          // src/pbsdf.cu:464
+
+namespace {
+__global__ void glueEval(const SPoint *sps, int n, const float *wi, float *pdf, float *bsdf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float p = 0.0f, f[3] = {0.0f, 0.0f, 0.0f};           // what every caller in pbsdf.cu passes in
+    pdf_device(sps[i], wi + 3 * (size_t) i, &p);
+    bsdfeval_device(sps[i], wi + 3 * (size_t) i, f, false);
+    pdf[i] = p; bsdf[3 * (size_t) i] = f[0]; bsdf[3 * (size_t) i + 1] = f[1]; bsdf[3 * (size_t) i + 2] = f[2];
+}
+}
+
+/// pdf_device / bsdfeval_device (src/pbsdf.cu:464-628) at n records, one direction each.
+extern "C" int refcuda_eval(const void *sps, int n, const float *wi, float *pdf, float *bsdf) {
+    SPoint *cu_sps = nullptr; float *cu_wi = nullptr, *cu_pdf = nullptr, *cu_bsdf = nullptr;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) return -1;
+    cudaMalloc((void **) &cu_wi, 12 * (size_t) n); cudaMalloc((void **) &cu_pdf, 4 * (size_t) n); cudaMalloc((void **) &cu_bsdf, 12 * (size_t) n);
+    cudaMemcpy(cu_sps, sps, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMemcpy(cu_wi, wi, 12 * (size_t) n, cudaMemcpyHostToDevice);
+    glueEval<<<(n + 127) / 128, 128>>>(cu_sps, n, cu_wi, cu_pdf, cu_bsdf);
+    cudaError_t e = cudaDeviceSynchronize();
+    cudaMemcpy(pdf, cu_pdf, 4 * (size_t) n, cudaMemcpyDeviceToHost); cudaMemcpy(bsdf, cu_bsdf, 12 * (size_t) n, cudaMemcpyDeviceToHost);
+    cudaFree(cu_sps); cudaFree(cu_wi); cudaFree(cu_pdf); cudaFree(cu_bsdf);
+    return e == cudaSuccess ? 0 : -3;
+}
+
+/// computeScatterAllOnGPURecord (src/pbsdf.cu:2317-2368) on n records and their neighbour rows (row_ints ints each, knn[i] used),
+/// then allGPUPdfMarginal once more into a buffer of this glue (the driver frees its own before returning; the __constant__
+/// sizes it set are still in place). blur / mc: iterations x n x 3 floats. seconds: wall time of the reference's driver alone
+/// (it synchronises and copies its results to the host inside, as the tool does).
+extern "C" int refcuda_scatter(const void *sps, int n, const int *neighbors, int row_ints, const int *knn, int iterations,
+                               float *pdfmarginal, float *blur, float *mc, double *seconds) {
+    SPoint *cu_sps = nullptr; int *cu_neighbors = nullptr, *cu_knn = nullptr; float *cu_pm = nullptr; size_t pitch_n = 0;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) return -1;
+    cudaMemcpy(cu_sps, sps, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    if (cudaMallocPitch((void **) &cu_neighbors, &pitch_n, row_ints * sizeof(int), n) != cudaSuccess) return -2;
+    cudaMemcpy2D(cu_neighbors, pitch_n, neighbors, row_ints * sizeof(int), row_ints * sizeof(int), n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_knn, sizeof(int) * (size_t) n); cudaMemcpy(cu_knn, knn, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_pm, sizeof(float) * (size_t) n);
+    ResultSpace ret;
+    for (int i = 0; i < iterations; ++i) {
+        ret.blur_results.push_back((val3f *) malloc(sizeof(val3f) * (size_t) n));
+        ret.mc_results.push_back((val3f *) malloc(sizeof(val3f) * (size_t) n));
+    }
+    cudaDeviceSynchronize();
+    auto t0 = std::chrono::steady_clock::now();
+    computeScatterAllOnGPURecord(cu_sps, cu_neighbors, cu_knn, n, iterations, row_ints, ret, pitch_n);
+    cudaDeviceSynchronize();
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    allGPUPdfMarginal<<<n / 512 + 1, 512>>>(cu_sps, cu_neighbors, cu_knn, cu_pm);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (pdfmarginal) cudaMemcpy(pdfmarginal, cu_pm, sizeof(float) * (size_t) n, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < iterations; ++i) {
+        static_assert(sizeof(val3f) == 12, "val3f is three floats");
+        std::memcpy(blur + (size_t) i * 3 * n, ret.blur_results[i], sizeof(val3f) * (size_t) n);
+        std::memcpy(mc + (size_t) i * 3 * n, ret.mc_results[i], sizeof(val3f) * (size_t) n);
+        free(ret.blur_results[i]); free(ret.mc_results[i]);
+    }
+    cudaFree(cu_sps); cudaFree(cu_neighbors); cudaFree(cu_knn); cudaFree(cu_pm);
+    return e == cudaSuccess ? 0 : -3;
+}

@@ -17,6 +17,45 @@ def arg(name, default):
     return type(default)(sys.argv[sys.argv.index(name) + 1]) if name in sys.argv else default
 
 
+def scatter_leg(spp, k, iterations):
+    """Second slice (marginal densities + iterated radiance scatter) on the veach scene's path vertices (diffuse + microfacet:
+    the reference prints a line per dielectric evaluation, so scenes with glass would time its printf)."""
+    s = FlatScene.load(os.path.join(ROOT, "tests", "golden", "scenes", "veach_mis.npz"))
+    e = Engine(0); e.load_scene(s)
+    v = e.path_vertices(sample_first=0, sample_last=spp)
+    hp = pathgraph_grid(v, k, k)
+    nb, knn, dknn, _ = e.pathgraph_knn(v, hp)
+    ms, wall = [], []
+    for _ in range(4):
+        t0 = time.perf_counter(); pm, blur, mc, t = e.pathgraph_scatter(v, nb, knn, iterations); wall.append(time.perf_counter() - t0); ms.append(t)
+    mine, mine_wall = float(np.median(ms[1:])), float(np.median(wall[1:]))
+    fwall = []
+    for _ in range(4):
+        t0 = time.perf_counter(); fpm, fblur, fmc, fms = e.pathgraph_filter(v, hp, iterations); fwall.append(time.perf_counter() - t0)
+    filter_wall = float(np.median(fwall[1:]))
+    evals = float(knn.sum()) * (1 + iterations) + len(v) * 2.0 * iterations          # pdf per edge once, bsdf per edge per pass, lastRun
+    out = {"workload": f"path vertices of veach path_mis {s.width}x{s.height}, {spp} spp: {len(v)} vertices, k = {k} ({float(knn.mean()):.1f} used), {iterations} iterations",
+           "vertices": int(len(v)), "edges": int(knn.sum()), "iterations": iterations,
+           "nori_b200": {"ms_device": mine, "ms_call_wall": mine_wall * 1e3, "Gevals_per_s_device": evals / mine / 1e6,
+                         "filter_call_wall_ms": filter_wall * 1e3, "filter_device_ms": [float(fms[0]), float(fms[1])],
+                         "filter": "nori_gpu_pathgraph_filter: kNN + scatter in one call from the host records (H2D of 168 B per vertex, rows never leave the device, D2H of the result rows)",
+                         "timing": "ms_device: CUDA events around pack + marginal + iterations x (scatter, update, lastRun), records resident; ms_call_wall: the whole nori_gpu_pathgraph_scatter call from host buffers (H2D of records and rows, D2H of all result rows)"}}
+    if have_refcuda():
+        ref = RefCuda()
+        secs = []
+        for _ in range(3):
+            rpm, rblur, rmc, sec = ref.scatter(v, nb, knn, iterations)
+            secs.append(sec)
+        r = float(np.median(secs[1:]))
+        scale = np.abs(rblur[-1]).max(-1, keepdims=True) + 1e-3
+        out["reference_pbsdf_cu"] = {"ms": r * 1e3, "timing": "wall clock around computeScatterAllOnGPURecord (src/pbsdf.cu:2317-2368), same GPU, records and rows resident; includes its per-iteration synchronisation and D2H copies of the result rows"}
+        out["speedup_vs_reference_device"] = r * 1e3 / mine
+        out["speedup_vs_reference_call"] = r / mine_wall
+        out["max_rel_row_error_last_blur"] = float((np.abs(blur[-1] - rblur[-1]) / scale).max())
+        out["max_rel_error_pdfmarginal"] = float((np.abs(pm - rpm) / np.maximum(np.abs(rpm), 1e-20)).max())
+    return out
+
+
 def main():
     spp, k, out = arg("--spp", 2), arg("--k", 16), arg("--out", "")
     s = FlatScene.load(os.path.join(ROOT, "tests", "golden", "scenes", "cbox_mis.npz"))
@@ -45,6 +84,7 @@ def main():
         res["speedup_vs_reference_kernels"] = r * 1e3 / mine
         res["rows_identical_as_sets_sampled"] = same
         res["counts_equal"] = bool((knn == rknn).all() and (dknn == rdknn).all())
+    res["scatter"] = scatter_leg(arg("--scatter-spp", 2), k, arg("--iterations", 3))
     print(json.dumps(res))
     if out:
         json.dump(res, open(out, "w"), indent=1)

@@ -1,0 +1,261 @@
+"""Path-graph post-process, second slice (reference src/pbsdf.cu:464-628, 1398-1431, 1497-1526, 1738-1756,
+2185-2194, 2317-2368): the tool's own BSDF / density evaluations at a recorded vertex, the marginal densities over the
+k-nearest-neighbour graph and the iterated radiance scatter.
+CPU: the oracle restatement (oracle/noracle_pathgraph_scatter.h) against vectors produced by the reference's own CUDA code on
+the GPU box (tests/golden/pathgraph_scatter_ref.npz, oracle/make_pathgraph_scatter_golden.py) and against closed forms.
+GPU: the sm_100a kernels through the C ABI against the oracle (marginal densities and first mc rows to the bit) and against the
+compiled reference running on the same GPU; the eLi / eLd fields of nori_gpu_path_vertices against the renderer's own radiance.
+
+Tolerances. The reference is compiled with nvcc's default -fmad=true, the oracle and the product without contraction, and the
+reference's scatter adds with float atomics in no fixed order: rows agree to RTOL = 2e-4 of the row's largest component
+(+ 1e-6 absolute); the deterministic quantities (evaluations, marginal densities, mc rows) to 2e-5."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+REF_NPZ = os.path.join(GOLDEN, "pathgraph_scatter_ref.npz")
+RTOL_SUM, RTOL_DET = 2e-4, 2e-5
+
+
+def spoint_dtype():
+    from nori_b200.gpu import SPOINT_DTYPE
+    return SPOINT_DTYPE
+
+
+def records(raw):
+    return np.ascontiguousarray(raw).view(spoint_dtype()).reshape(-1)
+
+
+def close_rows(got, want, rtol, what):
+    """Rows (n, 3) equal up to rtol of the row's largest component; NaN / inf patterns must coincide."""
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    np.testing.assert_array_equal(np.isfinite(got), np.isfinite(want), err_msg=what + ": non-finite pattern")
+    fin = np.isfinite(want).all(-1)
+    scale = np.abs(want[fin]).max(-1, keepdims=True)
+    err = np.abs(got[fin] - want[fin]) / (scale + 1e-6 / rtol)
+    assert err.max(initial=0.0) <= rtol, f"{what}: max relative row error {err.max():.3g} at row {np.nonzero(fin)[0][err.max(-1).argmax()]}"
+
+
+def unit(v):
+    return (v / np.linalg.norm(v, axis=-1, keepdims=True)).astype(np.float32)
+
+
+# ---- CPU: the oracle ---------------------------------------------------------------------------------------------------
+def test_oracle_eval_closed_forms(port):
+    """Diffuse vertices: pdf = cos / pi, bsdf = albedo * cos / pi with the cosine CLAMPED into [0, 1] (src/pbsdf.cu:257-264);
+    directions below the shading or the geometric side evaluate to 0; an unknown tag evaluates to 0."""
+    rng = np.random.default_rng(3)
+    n = 2000
+    s = np.zeros(n, spoint_dtype())
+    s["shN"] = unit(rng.normal(size=(n, 3))); s["geoN"] = s["shN"]
+    s["wo"] = unit(s["shN"] + 0.7 * rng.normal(size=(n, 3)))
+    wi = unit(rng.normal(size=(n, 3)))
+    s["diffuse"] = rng.random((n, 3)); s["rrpdf"] = 1; s["bsdf_type"] = b"d"
+    pdf, f = port.pathgraph_eval(s, wi)
+    cos_i = (wi * s["shN"]).sum(1); cos_o = (s["wo"] * s["shN"]).sum(1)
+    lit = (cos_i > 0) & (cos_o > 0)
+    assert lit.sum() > 300 and (~lit).sum() > 300
+    np.testing.assert_allclose(pdf[lit], np.minimum(cos_i[lit], 1) / np.pi, rtol=1e-5)
+    np.testing.assert_allclose(f[lit], s["diffuse"][lit] * (np.minimum(cos_i[lit], 1) / np.pi)[:, None], rtol=1e-5)
+    assert (pdf[~lit] == 0).all() and (f[~lit] == 0).all()
+    s["bsdf_type"] = b"x"
+    pdf, f = port.pathgraph_eval(s, wi)
+    assert (pdf == 0).all() and (f == 0).all()
+
+
+def test_oracle_eval_vs_reference_vectors(port):
+    """pdf_device / bsdfeval_device of the compiled reference (run on the GPU box) at 6 000 synthetic records of all four tags."""
+    z = np.load(REF_NPZ)
+    s = records(z["eval_sps"])
+    pdf, f = port.pathgraph_eval(s, s["wi"])
+    tags = {t: int((s["bsdf_type"] == t).sum()) for t in (b"d", b"o", b"c", b"t")}
+    assert min(tags.values()) > 100
+    want_pdf, want_f = z["eval_pdf"], z["eval_bsdf"]
+    np.testing.assert_array_equal(want_pdf == 0, pdf == 0)             # the same branches taken
+    np.testing.assert_allclose(pdf, want_pdf, rtol=RTOL_DET, atol=1e-30)
+    close_rows(f, want_f, RTOL_DET, "bsdf")
+    for t in tags:                                                      # every tag contributes non-zero values
+        assert (want_pdf[s["bsdf_type"] == t] > 0).sum() > 20, t
+
+
+def test_oracle_scatter_vs_reference_vectors(port):
+    """computeScatterAllOnGPURecord + allGPUPdfMarginal of the compiled reference on ~7 000 path vertices (whole paths of the
+    table scene: diffuse and microfacet) with the reference's own neighbour rows, three iterations."""
+    z = np.load(REF_NPZ)
+    s = records(z["sc_sps"]); nb, knn = z["sc_nb"], z["sc_knn"]
+    assert {b"d", b"o"} <= set(np.unique(s["bsdf_type"]).tolist())
+    it = z["sc_blur"].shape[0]
+    pm, blur, mc = port.pathgraph_scatter(s, nb, knn, it, sequential=True)
+    np.testing.assert_allclose(pm, z["sc_pm"], rtol=RTOL_DET, atol=1e-30)
+    assert (z["sc_pm"] > 0).mean() > 0.5
+    for i in range(it):
+        close_rows(blur[i], z["sc_blur"][i], RTOL_SUM, f"blur[{i}]")
+        close_rows(mc[i], z["sc_mc"][i], RTOL_SUM if i else RTOL_DET, f"mc[{i}]")
+    assert np.abs(z["sc_blur"][0]).sum() > 0 and np.abs(z["sc_mc"][2]).sum() > 0
+    # passes 0 and 1 scatter the same temp = eLi (the reference's update passes its loop index, src/pbsdf.cu:2344-2356)
+    close_rows(z["sc_blur"][1], z["sc_blur"][0], RTOL_SUM, "reference blur[1] vs blur[0]")
+    np.testing.assert_array_equal(blur[1], blur[0])
+    # the lane order of the product's warps changes the marginal sums by rounding only
+    pm_lane, _, _ = port.pathgraph_scatter(s, nb, knn, 0, sequential=False)
+    np.testing.assert_allclose(pm_lane, pm, rtol=2e-6, atol=1e-30)
+
+
+def test_oracle_mc_row_is_the_paths_own_estimate(port):
+    """lastRun on diffuse vertices: bsdf / pdf = albedo, so mc[0][i] = eLi[i + 1] * albedo / rrpdf — with records whose eLi obeys
+    the path recursion eLi[i] = eLd[i] + albedo * eLi[i + 1] / rrpdf this reads mc[0] + eLd = eLi."""
+    rng = np.random.default_rng(9)
+    paths, length = 300, 5
+    n = paths * length
+    s = np.zeros(n, spoint_dtype())
+    s["shN"] = unit(rng.normal(size=(n, 3))); s["geoN"] = s["shN"]
+    s["wo"] = unit(s["shN"] + 0.5 * rng.normal(size=(n, 3))); s["wi"] = unit(s["shN"] + 0.5 * rng.normal(size=(n, 3)))
+    s["diffuse"] = 0.2 + 0.6 * rng.random((n, 3)); s["rrpdf"] = rng.choice([1.0, 0.9], size=n); s["bsdf_type"] = b"d"
+    s["eLd"] = rng.random((n, 3)); s["pos"] = rng.random((n, 3))
+    idx = np.arange(n)
+    inner = idx % length != length - 1
+    s["nidx"][inner] = idx[inner] + 1
+    s["wi"][~inner] = 0; s["rrpdf"][~inner] = 0
+    eli = s["eLd"].astype(np.float64).copy()
+    for j in range(length - 2, -1, -1):
+        rows = idx[idx % length == j]
+        eli[rows] += s["diffuse"][rows] * eli[rows + 1] / s["rrpdf"][rows, None]
+    s["eLi"] = eli
+    nb = np.tile(idx[:, None], (1, 4)).astype(np.int32); nb[:, 1:] = (idx[:, None] + np.array([7, 13, 29])) % n
+    knn = np.full(n, 4, np.int32)
+    pm, blur, mc = port.pathgraph_scatter(s, nb, knn, 1)
+    lit = inner & ((s["wi"] * s["shN"]).sum(1) > 0) & ((s["wo"] * s["shN"]).sum(1) > 0)
+    assert lit.sum() > n // 2
+    np.testing.assert_allclose(mc[0][lit] + s["eLd"][lit], s["eLi"][lit], rtol=1e-5)
+    assert (mc[0][~inner] == 0).all()
+
+
+# ---- GPU: the kernels ---------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_gpu_scatter_vs_oracle_on_reference_vectors(engine, port):
+    """The fixture's records through nori_gpu_pathgraph_scatter: marginal densities and the first mc rows equal the oracle's
+    (same operations in the same order) to the bit; everything that went through the scatter's atomics to rounding; and all of
+    it agrees with what the compiled reference produced on the GPU box."""
+    z = np.load(REF_NPZ)
+    s = records(z["sc_sps"]); nb, knn = z["sc_nb"], z["sc_knn"]
+    it = z["sc_blur"].shape[0]
+    pm, blur, mc, ms = engine.pathgraph_scatter(s, nb, knn, it)
+    wpm, wblur, wmc = port.pathgraph_scatter(s, nb, knn, it, sequential=False)
+    np.testing.assert_array_equal(pm.view(np.uint32), wpm.view(np.uint32))
+    np.testing.assert_array_equal(mc[0].view(np.uint32), wmc[0].view(np.uint32))
+    for i in range(it):
+        close_rows(blur[i], wblur[i], RTOL_SUM, f"blur[{i}] vs oracle")
+        close_rows(mc[i], wmc[i], RTOL_SUM, f"mc[{i}] vs oracle")
+        close_rows(blur[i], z["sc_blur"][i], RTOL_SUM, f"blur[{i}] vs reference")
+        close_rows(mc[i], z["sc_mc"][i], RTOL_SUM, f"mc[{i}] vs reference")
+    np.testing.assert_allclose(pm, z["sc_pm"], rtol=RTOL_DET, atol=1e-30)
+
+
+@pytest.mark.gpu
+def test_gpu_scatter_all_tags_vs_oracle(engine, port):
+    """Synthetic records of all four tags (the fixture's eval set, given paths of four vertices and random neighbour rows): the
+    kernels' evaluations agree with the oracle's to the bit wherever no atomic is involved."""
+    z = np.load(REF_NPZ)
+    s = records(z["eval_sps"]).copy()
+    n = len(s); idx = np.arange(n)
+    inner = idx % 4 != 3
+    s["nidx"] = 0; s["nidx"][inner] = idx[inner] + 1
+    rng = np.random.default_rng(21)
+    s["eLi"] = rng.random((n, 3)); s["eLd"] = rng.random((n, 3))
+    k = 40                                                              # more than one lane round
+    nb = rng.integers(0, n, size=(n, k)).astype(np.int32); nb[:, 0] = idx
+    knn = rng.integers(1, k + 1, size=n).astype(np.int32)
+    pm, blur, mc, _ = engine.pathgraph_scatter(s, nb, knn, 2)
+    wpm, wblur, wmc = port.pathgraph_scatter(s, nb, knn, 2, sequential=False)
+    np.testing.assert_array_equal(pm.view(np.uint32), wpm.view(np.uint32))
+    np.testing.assert_array_equal(mc[0].view(np.uint32), wmc[0].view(np.uint32))
+    for i in range(2):
+        close_rows(blur[i], wblur[i], RTOL_SUM, f"blur[{i}]")
+    assert (pm > 0).mean() > 0.3 and np.abs(blur[0]).sum() > 0
+
+
+@pytest.mark.gpu
+def test_gpu_scatter_vs_compiled_reference_cuda(gpu_scene, scenes, port):
+    """The reference's own kernels (src/pbsdf.cu compiled unmodified, oracle/_ref/libpbsdf_ref.so) on the same GPU, same records
+    (path vertices of the veach scene: diffuse and microfacet plates under four lights), same neighbour rows."""
+    from oracle.pyoracle import RefCuda, have_refcuda
+    from nori_b200.gpu import pathgraph_grid
+    if not have_refcuda():
+        pytest.skip("oracle/_ref/libpbsdf_ref.so not built (needs /root/reference at build time)")
+    e = gpu_scene("veach_mis"); s = scenes("veach_mis")
+    e.set_camera(s.sample_to_camera, s.camera_to_world, 256, 160, s.near_clip, s.far_clip)
+    try:
+        v = e.path_vertices(sample_first=0, sample_last=2)
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+    assert len(v) > 100_000 and set(np.unique(v["bsdf_type"]).tolist()) <= {b"d", b"o"}
+    hp = pathgraph_grid(v, 16, 16)
+    nb, knn, dknn, _ = e.pathgraph_knn(v, hp)
+    pm, blur, mc, ms = e.pathgraph_scatter(v, nb, knn, 3)
+    rpm, rblur, rmc, sec = RefCuda().scatter(v, nb, knn, 3)
+    np.testing.assert_allclose(pm, rpm, rtol=RTOL_DET, atol=1e-30)
+    for i in range(3):
+        close_rows(blur[i], rblur[i], RTOL_SUM, f"blur[{i}]")
+        close_rows(mc[i], rmc[i], RTOL_SUM, f"mc[{i}]")
+    assert np.abs(rblur[2]).sum() > 0 and (rpm > 0).mean() > 0.3
+
+
+@pytest.mark.gpu
+def test_gpu_path_vertices_carry_the_paths_radiance(gpu_scene, scenes, port):
+    """eLi / eLd of nori_gpu_path_vertices: eLi of a path's first vertex is the radiance nori_gpu_sample_radiance returns for
+    that camera sample; along a path eLi[i] = eLd[i] + w_i * eLi[i + 1] with w_i = the sampling weight of the continuation, which
+    at diffuse vertices is albedo / rrpdf — the same statement lastRun makes: mc[0] + eLd = eLi there."""
+    e = gpu_scene("cbox_mis"); s = scenes("cbox_mis")
+    e.set_camera(s.sample_to_camera, s.camera_to_world, 160, 120, s.near_clip, s.far_clip)
+    try:
+        v = e.path_vertices(sample_first=0, sample_last=2)
+        first = np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]])
+        g = v["groupIdx"][first]
+        rad, _ = e.sample_radiance(g // 2, g % 2)
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+    np.testing.assert_allclose(v["eLi"][first], rad, rtol=2e-4, atol=1e-5)
+    assert (v["eLd"] >= 0).all() and (np.abs(v["eLi"]).sum(1) > 0).mean() > 0.5
+    idx = np.arange(len(v))
+    nb = idx[:, None].astype(np.int32).copy(); knn = np.ones(len(v), np.int32)
+    pm, blur, mc, _ = e.pathgraph_scatter(v, nb, knn, 1)
+    dif = (v["bsdf_type"] == b"d") & (v["nidx"] > 0) & (np.abs(mc[0]).sum(1) > 0)
+    assert dif.sum() > 10_000
+    np.testing.assert_allclose(mc[0][dif] + v["eLd"][dif], v["eLi"][dif], rtol=5e-4, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_gpu_filter_equals_knn_then_scatter(gpu_scene, scenes):
+    """nori_gpu_pathgraph_filter = the two stages back to back with the rows kept on the device: same marginal densities and mc[0]
+    rows to the bit (no atomics involved), the scattered rows to rounding."""
+    from nori_b200.gpu import pathgraph_grid
+    e = gpu_scene("table_mis"); s = scenes("table_mis")
+    e.set_camera(s.sample_to_camera, s.camera_to_world, 200, 150, s.near_clip, s.far_clip)
+    try:
+        v = e.path_vertices(sample_first=0, sample_last=1)
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+    hp = pathgraph_grid(v, 10, 14)                                      # k < dk: the scatter must read the k consumer's counts
+    nb, knn, dknn, _ = e.pathgraph_knn(v, hp)
+    pm, blur, mc, _ = e.pathgraph_scatter(v, nb, knn, 2)
+    fpm, fblur, fmc, ms = e.pathgraph_filter(v, hp, 2)
+    np.testing.assert_array_equal(fpm.view(np.uint32), pm.view(np.uint32))
+    np.testing.assert_array_equal(fmc[0].view(np.uint32), mc[0].view(np.uint32))
+    for i in range(2):
+        close_rows(fblur[i], blur[i], RTOL_SUM, f"blur[{i}]")
+    assert ms[0] > 0 and ms[1] > 0
+
+
+@pytest.mark.gpu
+def test_gpu_scatter_rejects_bad_rows(engine):
+    z = np.load(REF_NPZ)
+    s = records(z["sc_sps"])[:64].copy(); s["nidx"][63] = 0
+    nb = np.zeros((64, 4), np.int32); knn = np.full(64, 4, np.int32)
+    nb[5, 2] = 64
+    with pytest.raises(RuntimeError, match="neighbour index outside"):
+        engine.pathgraph_scatter(s, nb, knn, 1)
+    nb[5, 2] = 0; knn[7] = 5
+    with pytest.raises(RuntimeError, match="knn"):
+        engine.pathgraph_scatter(s, nb, knn, 1)
