@@ -2,6 +2,7 @@
 // Reference: src/scene.cpp:26-100 (child bookkeeping, defaults), src/block.cpp:27-63 (filter table,
 // toBitmap), src/main.cpp:69-151 (the render() this replaces).
 #include <nori/scene.h>
+#include <chrono>
 #include <nori_gpu.h>
 #include <algorithm>
 #include <cstring>
@@ -333,6 +334,50 @@ void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uin
         report->gsegments = st.ms_total > 0 ? st.segments / st.ms_total / 1e6 : 0;
         report->dropped = st.dropped; report->launches = st.kernel_launches;
     }
+}
+
+PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, int device) {
+    if (sampleLast <= sampleFirst) throw NoriException("pathGraphGpu: empty sample range");
+    if (k < 1 || iterations < 1) throw NoriException("pathGraphGpu: k and the number of iterations must be positive");
+    nori_gpu_ctx *ctx = scene->gpu(device);
+    const NoriGpuRenderDesc d = renderDesc(scene, sampleFirst, sampleLast);
+    const uint32_t spp = sampleLast - sampleFirst;
+    const Vector2i size = scene->getCamera()->getOutputSize();
+    PathGraphImages out;
+    auto t0 = std::chrono::steady_clock::now();
+    uint64_t n = 0;
+    check(ctx, nori_gpu_path_vertices(ctx, &d, nullptr, 0, &n), "nori_gpu_path_vertices");
+    if (n == 0) throw NoriException("pathGraphGpu: no camera sample hit a surface");
+    if (n > 0x7fffffffull) throw NoriException("pathGraphGpu: more than 2^31 path vertices; render fewer samples per call");
+    std::vector<NoriGpuSPoint> v((size_t) n);
+    check(ctx, nori_gpu_path_vertices(ctx, &d, v.data(), n, &n), "nori_gpu_path_vertices");
+    out.vertices = n;
+    out.msVertices = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    NoriGpuHashParams hp;
+    check(ctx, nori_gpu_pathgraph_grid(v.data(), sizeof(NoriGpuSPoint), (int) n, nullptr, k, k, &hp), "nori_gpu_pathgraph_grid");   // PathGraph::computeDimensions
+    std::vector<float> blur((size_t) iterations * 3 * n), mc((size_t) iterations * 3 * n);
+    float ms[2] = {0, 0};
+    check(ctx, nori_gpu_pathgraph_filter(ctx, v.data(), (int) n, &hp, iterations, nullptr, blur.data(), mc.data(), ms), "nori_gpu_pathgraph_filter");
+    out.msKnn = ms[0]; out.msScatter = ms[1];
+    Bitmap *imgs[5];
+    std::unique_ptr<Bitmap> *slots[5] = {&out.full, &out.indirect, &out.pt, &out.blur, &out.init};
+    for (int i = 0; i < 5; ++i) { slots[i]->reset(new Bitmap(size.x, size.y)); imgs[i] = slots[i]->get(); }
+    const float *lastMc = mc.data() + (size_t) (iterations - 1) * 3 * n, *lastBlur = blur.data() + (size_t) (iterations - 1) * 3 * n;
+    const float inv = 1.0f / (float) spp;
+    for (uint64_t i = 0; i < n; ++i) {
+        if (i > 0 && v[i - 1].groupIdx == v[i].groupIdx) continue;          // first vertex of each path only
+        const uint32_t pixel = (uint32_t) v[i].groupIdx / spp;
+        if (pixel >= (uint32_t) (size.x * size.y)) throw NoriException("pathGraphGpu: vertex record outside the frame");
+        for (int c = 0; c < 3; ++c) {
+            const float eLd = v[i].eLd[c], eLi = v[i].eLi[c], m = lastMc[3 * i + c], b = lastBlur[3 * i + c];
+            imgs[0]->data()[3 * (size_t) pixel + c] += (eLd + m) * inv;
+            imgs[1]->data()[3 * (size_t) pixel + c] += m * inv;
+            imgs[2]->data()[3 * (size_t) pixel + c] += (eLi - eLd) * inv;
+            imgs[3]->data()[3 * (size_t) pixel + c] += b * inv;
+            imgs[4]->data()[3 * (size_t) pixel + c] += eLd * inv;
+        }
+    }
+    return out;
 }
 
 NORI_NAMESPACE_END

@@ -232,3 +232,39 @@ def test_cli_rejects_a_bad_checkpoint_before_touching_the_device(tmp_path):
     wrong.write_bytes(b"NB2BLK1\0" + struct.pack("<3i2I", 7, 9, 2, 0, 4) + b"\0" * (7 * 9 * 16))
     r = subprocess.run([HOST_BIN, "--resume", str(wrong), xml], capture_output=True, text=True, timeout=120)
     assert r.returncode != 0 and "holds a 9x7 block" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_pathgraph_tool_writes_the_reference_tools_images(tmp_path):
+    """`nori_b200 --pathgraph K ITER`: the fork's `pg` tool in its "knn" mode (src/cluster.cpp:156-253) on the scene's own paths.
+    Images as the tool composes them from each path's first vertex (src/cluster.cpp:23-107): with one pass, mc = the vertex's own
+    estimate, so on diffuse first hits full = eLd + mc equals eLi = init + pt (the path tracer's value of that sample); the
+    blurred estimate has the same overall brightness."""
+    xml = os.path.join(HOST, "all_tags.xml")
+    out = str(tmp_path / "pg")
+    r = subprocess.run([HOST_BIN, "--out", out, "--spp", "1", "--pathgraph", "12", "1", xml], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Path graph: 1 spp, k = 12, 1 iterations" in r.stdout and "vertices in" in r.stdout and "scatter" in r.stdout, r.stdout
+    full, ind, pt, blur, init = (read_exr(out + s + ".exr") for s in ("_k-12_full", "_k-12_indirect", "_k-12_indirect_pt", "_k-12_indirect_blur", "_Le_init"))
+    flat = FlatScene.load(os.path.join(HOST, "all_tags.npz"))
+    assert full.shape == (flat.height, flat.width, 3)
+    for img in (full, ind, pt, blur, init):
+        assert np.isfinite(img).all() and (img >= 0).all()
+    np.testing.assert_allclose(full, init + ind, rtol=1e-5, atol=1e-6)
+    # the same pipeline through the Python binding of the same C ABI, composed as src/cluster.cpp:23-107 does
+    from nori_b200.gpu import Engine, pathgraph_grid
+    engine = Engine(0)
+    engine.load_scene(flat)
+    v = engine.path_vertices(sample_first=0, sample_last=1)
+    pm, wblur, wmc, _ = engine.pathgraph_filter(v, pathgraph_grid(v, 12, 12), 1)
+    engine.close()
+    first = np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]])
+    pix = v["groupIdx"][first]
+    def image(rows):
+        img = np.zeros((flat.height * flat.width, 3), np.float32); img[pix] = rows[first]
+        return img.reshape(flat.height, flat.width, 3)
+    np.testing.assert_array_equal(init, image(v["eLd"]))
+    np.testing.assert_array_equal(pt, image(v["eLi"] - v["eLd"]))
+    np.testing.assert_array_equal(ind, image(wmc[0]))                 # no atomics on the way to mc[0]
+    np.testing.assert_allclose(blur, image(wblur[0]), rtol=2e-4, atol=1e-6)
+    assert init.mean() > 1e-3 and blur.mean() > 0 and first.sum() > 0.2 * flat.height * flat.width
