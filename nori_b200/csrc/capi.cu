@@ -560,7 +560,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
             const uint32_t newCap = std::max(4096u, (hc.liveLast + 255u) / 256u * 256u);
             launches += (uint64_t) enqueueCompaction(pool, newCap, ctx->d_counters, st);
             pool.capacity = newCap;
-            enqueueIdentityOrder(pool, newCap, st);         // paths changed slots: the next closest-hit pass walks the pool in slot order
+            enqueueIdentityOrder(pool, newCap, ctx->d_counters, st);         // paths changed slots: the next closest-hit pass walks the pool in slot order
             // A few thousand paths left: one launch follows each of them to its end (k_finishTail)
             // instead of one launch-bound wavefront iteration per bounce of the longest path.
             if (newCap <= kTailPaths && !tailDone) { launches += (uint64_t) enqueueFinishTail(sc, pool, rp, ctx->d_counters, st); tailDone = true; }

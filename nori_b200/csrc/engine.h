@@ -53,6 +53,7 @@ struct Counters {
     unsigned int traceCursor[2];            // next ray of the persistent traversal kernels (closest, shadow)
     unsigned int liveLast;                  // live paths shaded by the previous iteration
     unsigned int compactCount[2];           // k_compactScan: free slots below / occupied slots above the new pool size
+    unsigned int traceLimit, orderSorted;   // ray binning: entries of Pool::order the closest-hit pass walks; 1 if the bin sort wrote them (live slots first)
 };
 
 struct RenderParams {
@@ -81,7 +82,7 @@ struct RenderParams {
 struct StageTimes { float generate, traceClosest, shade, traceShadow, splat; };
 
 /// order[i] = i for i < n (ray binning: after the tail compaction moved paths between slots).
-void enqueueIdentityOrder(const Pool &pool, uint32_t n, cudaStream_t st);
+void enqueueIdentityOrder(const Pool &pool, uint32_t n, Counters *c, cudaStream_t st);
 /// Bytes of scratch the per-iteration radix pass needs for n slots.
 size_t binSortTmpBytes(uint32_t n);
 

@@ -118,28 +118,36 @@ __device__ void splatDirect(const DeviceScene &sc, const RenderParams &rp, Count
 // ------------------------------------------------------------------------------------------
 struct ClosestIO {
     Pool pool;
-    __device__ __forceinline__ bool load(uint32_t k, V3 &o, V3 &d, float &mint, float &maxt) const {
+    bool sorted;        // the order list was written by the bin sort of this iteration: entries below Counters::traceLimit are live slots
+    /// slot: in = k, out = the path slot the k-th entry of the order list names (the handle store() gets back)
+    __device__ __forceinline__ bool load(uint32_t k, uint32_t &slot, V3 &o, V3 &d, float &mint, float &maxt) const {
         NG_CHECK(k < pool.capacity);
         const uint32_t i = pool.order ? (pool.order[k] & kBinSlotMask) : k;
-        if (!(pool.state[i].w & kFlagAlive)) return false;
+        NG_CHECK(i < pool.capacity);
+        // a sorted list holds the live slots first (fresh and bounce bins), the empty ones behind traceLimit: no need to ask
+        if (!sorted) { if (!(pool.state[i].w & kFlagAlive)) return false; }
+        else NG_CHECK(pool.state[i].w & kFlagAlive);
         const float4 ro = pool.rayO[i], rd = pool.rayD[i];
         o = mk(ro.x, ro.y, ro.z); d = mk(rd.x, rd.y, rd.z); mint = ro.w; maxt = rd.w;
+        slot = i;
         return true;
     }
-    __device__ __forceinline__ void store(uint32_t k, uint32_t gid, float t, float u, float v) const {
-        NG_CHECK(k < pool.capacity);
-        const uint32_t i = pool.order ? (pool.order[k] & kBinSlotMask) : k;
-        pool.hit[i] = make_float4(t, u, v, __uint_as_float(gid));
+    __device__ __forceinline__ void store(uint32_t slot, uint32_t gid, float t, float u, float v) const {
+        NG_CHECK(slot < pool.capacity);
+        pool.hit[slot] = make_float4(t, u, v, __uint_as_float(gid));
     }
 };
+
+template <> struct IoIndirect<ClosestIO> { static constexpr bool value = true; };
 
 /// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
 __device__ __forceinline__ QGrid sceneGrid(const DeviceScene &sc) { QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]}; return g; }
 
 template <int MINB, bool WT = false, bool QN = false>
 __global__ void __launch_bounds__(128, MINB) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
-    ClosestIO io; io.pool = pool;
-    tracePersistent<false, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, pool.capacity, &c->traceCursor[0], io, fetchThreshold, sceneGrid(sc));
+    ClosestIO io; io.pool = pool; io.sorted = pool.order && c->orderSorted;
+    const uint32_t nRays = pool.order ? min(c->traceLimit, pool.capacity) : pool.capacity;
+    tracePersistent<false, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, nRays, &c->traceCursor[0], io, fetchThreshold, sceneGrid(sc));
     // This grid is a programmatic dependent of the splat kernels (they execute launch_dependents on entry). It must
     // not COMPLETE before they have: k_prepare, a normal launch behind it, is ordered after this grid only, and it
     // resets counters the splat still reads. Waiting here, after the last hit is stored, keeps the overlap and makes
@@ -423,7 +431,8 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
         }
     }
     if (!ok) {
-        if (!wasEmpty) { pool.state[dst] = make_uint4(0, 0, 0, 0); if (pool.order) pool.key[dst] = (kBinEmpty << 24) | dst; }
+        if (!wasEmpty) pool.state[dst] = make_uint4(0, 0, 0, 0);
+        if (pool.order) pool.key[dst] = (kBinEmpty << 24) | dst;      // whatever the slot held before (a path moved away by the tail compaction keeps its word): empty slots sort last
         return;
     }
     NG_CHECK(dst < pool.capacity && (rp.listPixel || (tileSlot < (uint32_t) rp.ring * rp.numTiles && rec < rp.passSlots)));
@@ -1201,15 +1210,17 @@ __global__ void k_poolInit(Pool pool, Counters *c) {
     pool.state[i] = make_uint4(0, 0, 0, 0);
     if (pool.order) { pool.key[i] = (kBinEmpty << 24) | i; pool.order[i] = i; }
     if (i == 0) {                                   // what k_prepare would have left: the first splat pass runs before it
+        c->traceLimit = pool.capacity; c->orderSorted = 0;
         c->forcePass = 0xffffffffu;
         for (int s = 0; s < kMaxRing; ++s) c->slotPass[s] = (unsigned) s;
     }
 }
-__global__ void k_identityOrder(Pool pool, uint32_t n) {
+__global__ void k_identityOrder(Pool pool, uint32_t n, Counters *c) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) pool.order[i] = i;
+    if (i == 0) { c->traceLimit = n; c->orderSorted = 0; }     // slot order: the closest-hit pass asks every slot whether it is alive
 }
-void enqueueIdentityOrder(const Pool &pool, uint32_t n, cudaStream_t st) { if (pool.order && n) k_identityOrder<<<(n + 255u) / 256u, 256, 0, st>>>(pool, n); }
+void enqueueIdentityOrder(const Pool &pool, uint32_t n, Counters *c, cudaStream_t st) { if (pool.order && n) k_identityOrder<<<(n + 255u) / 256u, 256, 0, st>>>(pool, n, c); }
 // ---- ray binning: a counting sort of the (bin << 24 | slot) words by bin, specialised for 256 bins -----------------------------
 // Three small kernels instead of a general radix pass (cub::DeviceRadixSort::SortKeys over bits 24..31: profiles/r02_notes.md).
 // One CTA per chunk of kBinChunk consecutive words:
@@ -1222,7 +1233,7 @@ void enqueueIdentityOrder(const Pool &pool, uint32_t n, cudaStream_t st) { if (p
 //                 shared-memory atomics make it, which only decides which lanes trace which rays.
 constexpr int kBinChunk = 8192, kBinThreads = 512, kBins = 256;
 
-__global__ void __launch_bounds__(kBinThreads) k_binCount(const uint32_t *__restrict__ key, uint32_t n, uint32_t nChunks, uint32_t *__restrict__ counts) {
+__global__ void __launch_bounds__(kBinThreads) k_binCount(const uint32_t *__restrict__ key, uint32_t n, uint32_t nChunks, uint32_t *__restrict__ counts, const uint4 *__restrict__ state) {
     __shared__ unsigned int hist[kBins];
     for (int b = threadIdx.x; b < kBins; b += kBinThreads) hist[b] = 0;
     __syncthreads();
@@ -1231,7 +1242,12 @@ __global__ void __launch_bounds__(kBinThreads) k_binCount(const uint32_t *__rest
 #pragma unroll
     for (int j = 0; j < kBinChunk / kBinThreads; ++j) { const uint32_t i = lo + j * kBinThreads + threadIdx.x; k[j] = i < hi ? key[i] : 0u; }
 #pragma unroll
-    for (int j = 0; j < kBinChunk / kBinThreads; ++j) if (lo + j * kBinThreads + threadIdx.x < hi) atomicAdd(&hist[k[j] >> 24], 1u);
+    for (int j = 0; j < kBinChunk / kBinThreads; ++j) if (lo + j * kBinThreads + threadIdx.x < hi) {
+        atomicAdd(&hist[k[j] >> 24], 1u);
+        // the closest-hit pass trusts the sorted list: a word is in the empty bin exactly if its slot holds no live path
+        NG_CHECK((k[j] & kBinSlotMask) == lo + j * kBinThreads + threadIdx.x);
+        NG_CHECK(((k[j] >> 24) == kBinEmpty) == !(state[k[j] & kBinSlotMask].w & kFlagAlive));
+    }
     __syncthreads();
     for (int b = threadIdx.x; b < kBins; b += kBinThreads) counts[b * nChunks + blockIdx.x] = hist[b];
 }
@@ -1240,7 +1256,7 @@ __device__ __forceinline__ unsigned int warpInclusive(unsigned int v, int lane) 
     for (int d = 1; d < 32; d <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
     return v;
 }
-__global__ void __launch_bounds__(256) k_binScan(uint32_t *__restrict__ counts /* in: counts, out: offsets; then totals[kBins] */, uint32_t nChunks) {
+__global__ void __launch_bounds__(256) k_binScan(uint32_t *__restrict__ counts /* in: counts, out: offsets; then totals[kBins] */, uint32_t nChunks, uint32_t n, Counters *c) {
     const int bin = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     uint32_t *row = counts + (size_t) bin * nChunks;
     unsigned int carry = 0;
@@ -1251,7 +1267,11 @@ __global__ void __launch_bounds__(256) k_binScan(uint32_t *__restrict__ counts /
         if (c < nChunks) row[c] = carry + incl - v;
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (lane == 0) counts[(size_t) kBins * nChunks + bin] = carry;
+    if (lane == 0) {
+        counts[(size_t) kBins * nChunks + bin] = carry;
+        // the empty slots sort last: the next closest-hit pass stops in front of them and trusts the list (ClosestIO::sorted)
+        if (bin == (int) kBinEmpty) { c->traceLimit = n - carry; c->orderSorted = 1; }
+    }
 }
 __global__ void __launch_bounds__(kBinThreads) k_binScatter(const uint32_t *__restrict__ key, uint32_t n, uint32_t nChunks, const uint32_t *__restrict__ offsets, uint32_t *__restrict__ order) {
     __shared__ uint32_t stage[kBinChunk];
@@ -1296,11 +1316,11 @@ __global__ void __launch_bounds__(kBinThreads) k_binScatter(const uint32_t *__re
     }
 }
 size_t binSortTmpBytes(uint32_t n) { return (size_t) ((n + kBinChunk - 1) / kBinChunk + 1) * kBins * sizeof(uint32_t); }
-static void enqueueBinSort(const Pool &pool, cudaStream_t st) {
+static void enqueueBinSort(const Pool &pool, Counters *c, cudaStream_t st) {
     uint32_t *counts = static_cast<uint32_t *>(pool.sortTmp);
     const uint32_t n = pool.capacity, nChunks = (n + kBinChunk - 1) / kBinChunk;
-    k_binCount<<<nChunks, kBinThreads, 0, st>>>(pool.key, n, nChunks, counts);
-    k_binScan<<<kBins / 8, 256, 0, st>>>(counts, nChunks);
+    k_binCount<<<nChunks, kBinThreads, 0, st>>>(pool.key, n, nChunks, counts, pool.state);
+    k_binScan<<<kBins / 8, 256, 0, st>>>(counts, nChunks, n, c);
     k_binScatter<<<nChunks, kBinThreads, 0, st>>>(pool.key, n, nChunks, counts, pool.order);
 }
 void enqueuePoolInit(const Pool &pool, Counters *c, cudaStream_t st) { k_poolInit<<<pool.capacity / 256, 256, 0, st>>>(pool, c); }
@@ -1390,7 +1410,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     }
     ++launches;
     if (pool.order) {                               // one 8-bit radix pass over (bin << 24 | slot): slot numbers ordered by bin for the next closest-hit pass
-        enqueueBinSort(pool, st);
+        enqueueBinSort(pool, c, st);
         launches += 3;
     }
     if (ev) cudaEventRecord(ev[2], st);

@@ -26,6 +26,10 @@ struct QGrid { float bx, by, bz, ex, ey, ez; };
 /// A 16-bit field of a quantised node (0x8000 | q) dropped into a float mantissa: 1 + q / 32768. One PRMT.
 template <bool HIGH> NG_D float qfield(uint32_t w) { return __uint_as_float(__byte_perm(w, 0x3F000000u, HIGH ? 0x7324u : 0x7104u)); }
 
+/// IO types whose load() turns the ray number into another handle for store() (the renderer's ClosestIO: the path slot the
+/// sorted order list names) specialise this to true and take the handle as load()'s second argument.
+template <class IO> struct IoIndirect { static constexpr bool value = false; };
+
 /// QN: `nodes` holds the 32-byte quantised nodes (two 16-byte loads per visit instead of four); the slab test is the
 /// same fused multiply-add per plane with per-ray constants that fold the grid in: t = m * (ext / d) + (base - o) / d.
 template <bool ANY_HIT, bool WT = false, bool QN = false, class IO>
@@ -55,7 +59,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
     constexpr int kDone = 0x7fffffff;                          // no node left for this lane
     cur = kDone;
     bool active = false;
-    uint32_t rayIdx = 0xffffffffu, best = kNoHit;
+    uint32_t rayIdx = 0xffffffffu, best = kNoHit;              // rayIdx: the handle io.load returned for io.store (path slot or ray number)
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
     float idx = 0, idy = 0, idz = 0, oodx = 0, oody = 0, oodz = 0, mint = 0, tbest = 0, bu = 0, bv = 0;
     bool exhausted = false;
@@ -74,18 +78,27 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                 else if (!active) {
                     const uint32_t i = base + __popc(idleMask & ltMask);
                     float maxt;
-                    if (i < nRays && io.load(i, o, d, mint, maxt)) {
-                        const float big = 1e30f;
-                        idx = fabsf(d.x) > 1e-30f ? 1.0f / d.x : copysignf(big, d.x);
-                        idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);
-                        idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);
-                        if (QN) {   // plane at m: ((base + m ext) - o) / d = m * (ext / d) - (o - base) / d
-                            oodx = (o.x - grid.bx) * idx; oody = (o.y - grid.by) * idy; oodz = (o.z - grid.bz) * idz;
-                            idx *= grid.ex; idy *= grid.ey; idz *= grid.ez;
-                        } else { oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz; }
-                        if (WT) wt = wtSetup(d);
-                        rayIdx = i; tbest = maxt; best = kNoHit; sp = 0; cur = 0; leaf = 0; active = true;
+                    // (two copies of the same few lines: the register allocation of the 48-register kernels is at its limit, and a shared
+                    // `handle` variable alone costs the any-hit kernel a 16-byte spill)
+#define NG_START_RAY(HANDLE) do {                                                                                        \
+                        const float big = 1e30f;                                                                         \
+                        idx = fabsf(d.x) > 1e-30f ? 1.0f / d.x : copysignf(big, d.x);                                    \
+                        idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);                                    \
+                        idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);                                    \
+                        if (QN) {   /* plane at m: ((base + m ext) - o) / d = m * (ext / d) - (o - base) / d */          \
+                            oodx = (o.x - grid.bx) * idx; oody = (o.y - grid.by) * idy; oodz = (o.z - grid.bz) * idz;    \
+                            idx *= grid.ex; idy *= grid.ey; idz *= grid.ez;                                              \
+                        } else { oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz; }                                 \
+                        if (WT) wt = wtSetup(d);                                                                         \
+                        rayIdx = (HANDLE); tbest = maxt; best = kNoHit; sp = 0; cur = 0; leaf = 0; active = true;        \
+                    } while (0)
+                    if constexpr (IoIndirect<IO>::value) {      // load() names the handle store() gets back (the path slot)
+                        uint32_t handle;
+                        if (i < nRays && io.load(i, handle, o, d, mint, maxt)) NG_START_RAY(handle);
+                    } else {
+                        if (i < nRays && io.load(i, o, d, mint, maxt)) NG_START_RAY(i);
                     }
+#undef NG_START_RAY
                 }
             }
         }

@@ -2,7 +2,7 @@
 
 On the GPU box, the whole render under ncu with four cheap counters (one replay pass per kernel):
     ncu --metrics smsp__inst_executed.sum,smsp__thread_inst_executed.sum,dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum \
-        --clock-control none -k regex:'k_trace|k_shade' --csv --log-file gpurun_out/<tag>_issue.csv python scripts/issue_model.py run <tag>
+        --clock-control none -k regex:'k_trace|k_shade|k_bin' --csv --log-file gpurun_out/<tag>_issue.csv python scripts/issue_model.py run <tag>
 `run` renders the Cornell box (path_mis, 800x600, 64 spp, 8 Mi path slots) once and writes the render's own counters (closest rays, shadow
 rays) to gpurun_out/<tag>_issue_stats.json. Here, afterwards:
     python scripts/issue_model.py parse <tag>        -> profiles/issue_model.json
@@ -36,7 +36,9 @@ else:
         if m == "gpu__time_duration.sum": v *= {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(u, 1)      # -> ms
         agg[k][m] += v
         if (r["ID"], k) not in seen: seen.add((r["ID"], k)); launches[k] += 1
-    units = {"k_traceClosest": ("closest ray", st["closest_rays"]), "k_shadeRegen": ("path segment shaded", st["closest_rays"]), "k_traceShadow": ("shadow ray", st["shadow_rays"])}
+    units = {"k_traceClosest": ("closest ray", st["closest_rays"]), "k_shadeRegen": ("path segment shaded", st["closest_rays"]), "k_traceShadow": ("shadow ray", st["shadow_rays"]),
+             "k_binCount": ("closest ray (sort of the slots between bounces)", st["closest_rays"]), "k_binScan": ("closest ray (sort of the slots between bounces)", st["closest_rays"]),
+             "k_binScatter": ("closest ray (sort of the slots between bounces)", st["closest_rays"])}
     out = {"source": f"ncu ({tag}): smsp__inst_executed.sum, smsp__thread_inst_executed.sum, dram__bytes_read.sum + dram__bytes_write.sum summed over every launch of one "
                      f"Cornell-box path_mis render (800x600, {SPP} spp, 8 Mi path slots) and divided by that render's own ray counts; raw list profiles/{tag}_issue.csv",
            "sm_count": 148, "render": {k: st[k] for k in ("camera_samples", "closest_rays", "shadow_rays", "iterations")}, "kernels": {}}
