@@ -295,11 +295,22 @@ int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int n, const in
  * ms: device time without the copies. */
 int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
                                const int32_t *knn, int iterations, float *pdfmarginal, float *blur, float *mc, float *ms);
-/* The tool's whole pipeline in one call, as SPoints::BuildKNN + the scatter driver run it (include/nori/shadingPoint.h:776-806,
- * 484-503): hash grid + kNN over the records' positions, then the scatter stage on the rows the search left ON THE DEVICE (the k
- * consumer's count knn[i] of each row, as shadingPoint.h:500 passes cu_knn). Same results as nori_gpu_pathgraph_knn followed by
- * nori_gpu_pathgraph_scatter without the round trip of the n x max(k, dk) rows through host memory. ms[0]: search, ms[1]: scatter. */
-int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
+/* computeMISAllOnGPURecord (src/pbsdf.cu:2922-2965), the variant the `pg` tool runs in its "knn" mode (src/cluster.cpp:223 ->
+ * SPoints::computeMISRadianceAOGWithProcessRecording, shadingPoint.h:504-510): a GATHER instead of a scatter. Once:
+ *   pdfsum[i][a] = sum over i's neighbours b of pdf_b(wi_a) * rrpdf_b   for every neighbour a of i whose path continues
+ *                  (allGPUPdfSum, :1600-1617; k^2 evaluations per vertex);
+ * per pass: blur[it][i] = sum over a of bsdf_i(wi_a) * temp[a + 1] / pdfsum[i][a] (allGPUMISRadiance, :1346-1370), temp = eLi
+ * before the first pass and blur[it] + eLd after each, mc[it] as above (lastRun). No atomics: results are deterministic. */
+int nori_gpu_pathgraph_mis(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
+                           const int32_t *knn, int iterations, float *blur, float *mc, float *ms);
+/* The tool's whole pipeline in one call, as SPoints::BuildKNN + one of the two drivers run it (include/nori/shadingPoint.h:776-806,
+ * 496-510): hash grid + kNN over the records' positions, then the scatter (mode NORI_PG_SCATTER) or the MIS gather (NORI_PG_MIS)
+ * on the rows the search left ON THE DEVICE (the k consumer's count knn[i] of each row, as the reference passes cu_knn). Same
+ * results as nori_gpu_pathgraph_knn followed by nori_gpu_pathgraph_scatter / _mis without the round trip of the n x max(k, dk)
+ * rows through host memory. pdfmarginal (optional) is written in scatter mode only. ms[0]: search, ms[1]: scatter / gather. */
+#define NORI_PG_SCATTER 0
+#define NORI_PG_MIS 1
+int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
                               float *pdfmarginal, float *blur, float *mc, float ms[2]);
 
 #ifdef __cplusplus

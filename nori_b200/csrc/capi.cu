@@ -1118,19 +1118,20 @@ extern "C" int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uin
 
 namespace {
 /// Device side of the scatter stage shared by the two entry points: rows already on the device and validated.
-int pathgraphScatterOnDevice(nori_gpu_ctx *ctx, const NoriGpuSPoint *d_sps, int n, const int *d_nb, int rowInts, const int *d_knn, int iterations,
+int pathgraphScatterOnDevice(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *d_sps, int n, const int *d_nb, int rowInts, const int *d_knn, int iterations,
                              float *pdfmarginal, float *blur, float *mc, float *ms) {
     DevBuf<unsigned char> scratch; DevBuf<float> pm, db, dm;
-    CK(scratch.alloc(pgScatterScratchBytes(n))); CK(pm.alloc(n));
+    CK(scratch.alloc(mode == NORI_PG_MIS ? pgMisScratchBytes(n, rowInts) : pgScatterScratchBytes(n))); CK(pm.alloc(n));
     const size_t resultFloats = (size_t) std::max(iterations, 1) * 3 * (size_t) n;
     CK(db.alloc(resultFloats)); CK(dm.alloc(resultFloats));
     cudaStream_t st = ctx->stream;
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
     CK(cudaEventRecord(e0, st));
-    if (!launchPathgraphScatter(d_sps, n, d_nb, rowInts, d_knn, iterations, scratch.p, pm.p, db.p, dm.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    if (mode == NORI_PG_MIS) { if (!launchPathgraphMis(d_sps, n, d_nb, rowInts, d_knn, iterations, scratch.p, db.p, dm.p, st, ctx->err)) return NORI_GPU_EINVAL; }
+    else if (!launchPathgraphScatter(d_sps, n, d_nb, rowInts, d_knn, iterations, scratch.p, pm.p, db.p, dm.p, st, ctx->err)) return NORI_GPU_EINVAL;
     CK(cudaEventRecord(e1, st));
-    if (pdfmarginal) CK(cudaMemcpyAsync(pdfmarginal, pm.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    if (pdfmarginal && mode != NORI_PG_MIS) CK(cudaMemcpyAsync(pdfmarginal, pm.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
     if (iterations > 0) {
         CK(cudaMemcpyAsync(blur, db.p, (size_t) iterations * 3 * n * 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(mc, dm.p, (size_t) iterations * 3 * n * 4, cudaMemcpyDeviceToHost, st));
@@ -1143,8 +1144,9 @@ int pathgraphScatterOnDevice(nori_gpu_ctx *ctx, const NoriGpuSPoint *d_sps, int 
 }
 }
 
-extern "C" int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
-                                          const int32_t *knn, int iterations, float *pdfmarginal, float *blur, float *mc, float *ms) {
+namespace {
+int pathgraphFromHostRows(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
+                          const int32_t *knn, int iterations, float *pdfmarginal, float *blur, float *mc, float *ms) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(points && neighbors && knn && n > 0 && row_ints >= 1 && iterations >= 0, "pathgraph_scatter: bad arguments");
     REQUIRE(iterations == 0 || (blur && mc), "pathgraph_scatter: blur and mc must hold iterations x n x 3 floats");
@@ -1162,12 +1164,23 @@ extern "C" int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint
     CK(cudaMemcpyAsync(&bad, flag.p, sizeof(int), cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
     REQUIRE(!(bad & 1), "pathgraph_scatter: knn[i] outside [0, row_ints]");
     REQUIRE(!(bad & 2), "pathgraph_scatter: neighbour index outside [0, n)");
-    return pathgraphScatterOnDevice(ctx, sps.p, n, nb.p, row_ints, kn.p, iterations, pdfmarginal, blur, mc, ms);
+    return pathgraphScatterOnDevice(ctx, mode, sps.p, n, nb.p, row_ints, kn.p, iterations, pdfmarginal, blur, mc, ms);
+}
 }
 
-extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
+extern "C" int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
+                                          const int32_t *knn, int iterations, float *pdfmarginal, float *blur, float *mc, float *ms) {
+    return pathgraphFromHostRows(ctx, NORI_PG_SCATTER, points, n, neighbors, row_ints, knn, iterations, pdfmarginal, blur, mc, ms);
+}
+extern "C" int nori_gpu_pathgraph_mis(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
+                                      const int32_t *knn, int iterations, float *blur, float *mc, float *ms) {
+    return pathgraphFromHostRows(ctx, NORI_PG_MIS, points, n, neighbors, row_ints, knn, iterations, nullptr, blur, mc, ms);
+}
+
+extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
                                          float *pdfmarginal, float *blur, float *mc, float ms[2]) {
     if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(mode == NORI_PG_SCATTER || mode == NORI_PG_MIS, "pathgraph_filter: unknown mode");
     REQUIRE(points && hp && n > 0 && iterations >= 0 && iterations <= 64, "pathgraph_filter: bad arguments");
     REQUIRE(iterations == 0 || (blur && mc), "pathgraph_filter: blur and mc must hold iterations x n x 3 floats");
     REQUIRE(hp->k >= 1 && hp->dk >= 1 && hp->dim[0] >= 1 && hp->dim[1] >= 1 && hp->dim[2] >= 1, "pathgraph_filter: bad grid parameters");
@@ -1189,7 +1202,7 @@ extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, const NoriGpuSPoint 
     if (!launchPathgraphKnn(sps.p, sizeof(NoriGpuSPoint), n, P, scratch.p, nb.p, P.maxK, dk1.p, dk2.p, st, ctx->err)) return NORI_GPU_EINVAL;
     CK(cudaEventRecord(e1, st));
     float msScatter = 0.f;
-    if (int rc = pathgraphScatterOnDevice(ctx, sps.p, n, nb.p, P.maxK, dk1.p, iterations, pdfmarginal, blur, mc, &msScatter)) return rc;
+    if (int rc = pathgraphScatterOnDevice(ctx, mode, sps.p, n, nb.p, P.maxK, dk1.p, iterations, pdfmarginal, blur, mc, &msScatter)) return rc;
     if (ms) { cudaEventElapsedTime(&ms[0], e0, e1); ms[1] = msScatter; }
     unsigned line = 0;
     if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_filter: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }

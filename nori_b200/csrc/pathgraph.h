@@ -26,6 +26,9 @@ unsigned pathgraphChecks(unsigned *line);
 size_t pgScatterScratchBytes(int n);
 bool launchPathgraphScatter(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
                             void *d_scratch, float *d_pdfmarginal, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
+size_t pgMisScratchBytes(int n, int rowInts);
+bool launchPathgraphMis(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
+                        void *d_scratch, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
 unsigned pathgraphScatterChecks(unsigned *line);
 

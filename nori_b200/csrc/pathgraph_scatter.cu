@@ -151,6 +151,97 @@ __global__ void k_pgUnpack(const float4 *__restrict__ src, float *__restrict__ d
     dst[3 * (size_t) i] = v.x; dst[3 * (size_t) i + 1] = v.y; dst[3 * (size_t) i + 2] = v.z;
 }
 
+/// allGPUPdfSum (src/pbsdf.cu:1600-1617): pdfsum[i][a] = sum over i's neighbours b of pdf_b(wi_a) * rrpdf_b, for every neighbour a of i
+/// whose path continues (nidx > 0, rrpdf > 1e-7): the density with which ANY vertex of the neighbourhood would have produced a's
+/// direction — the denominator of the tool's MIS-style gather. k^2 evaluations per vertex: a warp per vertex, the outer loop
+/// over a is warp-uniform, the lanes take the b (for k <= 32 each lane keeps "its" neighbour's record in registers for the whole
+/// loop); sums in the same fixed order as the marginal densities (lane-strided, then a butterfly). Entries of neighbours that
+/// do not continue stay 0 (the array is cleared first, as the reference does).
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgPdfSum(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                            const int *__restrict__ neighbors, int pitchInts, const int *__restrict__ knn, int n,
+                                                            int rowInts, float *__restrict__ pdfsum) {
+    const int i = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int k = knn[i];
+    const int *row = neighbors + (size_t) i * pitchInts;
+    PgVertex mine; mine.type = 0; mine.rrpdf = 0.f;
+    if (k <= 32) {
+        // One neighbour record per lane, kept in registers for the whole loop. Rows of at most 16 (8) entries split the warp into
+        // 2 (4) groups that work on different a at the same time; a group's butterfly adds the same terms in the same order as the
+        // whole warp's would (the other lanes hold zeros), so the grouping does not change a bit of the result.
+        const int G = k <= 8 ? 8 : (k <= 16 ? 16 : 32), group = lane / G, l = lane % G, groups = 32 / G;
+        if (l < k) { const int jb = row[l]; NG_CHECK(jb >= 0 && jb < n); pgLoadA(A, jb, mine); pgLoadB(B, jb, mine); }
+        for (int a0 = 0; a0 < k; a0 += groups) {
+            const int a = a0 + group;
+            float sum = 0.0f;
+            bool want = false;
+            if (a < k) {
+                const int ja = row[a];
+                NG_CHECK(ja >= 0 && ja < n);
+                const float4 a1 = __ldg(A + 4 * (size_t) ja + 1), a3 = __ldg(A + 4 * (size_t) ja + 3);
+                want = __float_as_int(a3.w) > 0 && a1.w > 1e-7f;
+                if (want && l < k) {
+                    const float4 w4 = __ldg(wiAll + ja);
+                    const float wi[3] = {w4.x, w4.y, w4.z};
+                    sum += pgPdf(mine, wi) * mine.rrpdf;
+                }
+            }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) { const float t = __shfl_xor_sync(0xffffffffu, sum, d); if (d < G) sum += t; }
+            if (want && l == 0) pdfsum[(size_t) i * rowInts + a] = sum;
+        }
+        return;
+    }
+    for (int a = 0; a < k; ++a) {
+        const int ja = row[a];
+        NG_CHECK(ja >= 0 && ja < n);
+        const float4 a1 = __ldg(A + 4 * (size_t) ja + 1), a3 = __ldg(A + 4 * (size_t) ja + 3);
+        if (!(__float_as_int(a3.w) > 0 && a1.w > 1e-7f)) continue;
+        const float4 w4 = __ldg(wiAll + ja);
+        const float wi[3] = {w4.x, w4.y, w4.z};
+        float sum = 0.0f;
+        for (int b = lane; b < k; b += 32) {
+            const int jb = row[b];
+            NG_CHECK(jb >= 0 && jb < n);
+            PgVertex v; pgLoadA(A, jb, v); pgLoadB(B, jb, v);
+            sum += pgPdf(v, wi) * v.rrpdf;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+        if (lane == 0) pdfsum[(size_t) i * rowInts + a] = sum;
+    }
+}
+
+/// allGPUMISRadiance (src/pbsdf.cu:1346-1370): vertex i GATHERS from its neighbours a: bsdf_i(wi_a) * temp[a + 1] / pdfsum[i][a].
+/// No atomics: lane l adds its neighbours l, l + 32, ... in order, then a butterfly per channel.
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgMisGather(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                               const float *__restrict__ pdfsum, int rowInts, const int *__restrict__ neighbors, int pitchInts,
+                                                               const int *__restrict__ knn, int n, const float4 *__restrict__ temp, float4 *__restrict__ radiance) {
+    const int i = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int k = knn[i];
+    const int *row = neighbors + (size_t) i * pitchInts;
+    PgVertex self; pgLoadA(A, i, self); pgLoadB(B, i, self);
+    float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+    for (int a = lane; a < k; a += 32) {
+        const int ja = row[a];
+        NG_CHECK(ja >= 0 && ja < n);
+        const float4 a1 = __ldg(A + 4 * (size_t) ja + 1), a3 = __ldg(A + 4 * (size_t) ja + 3);
+        const float ps = pdfsum[(size_t) i * rowInts + a];
+        if (!(__float_as_int(a3.w) > 0 && ps > 0.0f && a1.w > 1e-7f) || ja + 1 >= n) continue;
+        const float4 w4 = __ldg(wiAll + ja), src = temp[ja + 1];
+        const float wi[3] = {w4.x, w4.y, w4.z};
+        float f[3]; pgBsdf(self, wi, f);
+        const float inv = (float) (1.0 / (double) ps);
+        r0 += (f[0] * src.x) * inv; r1 += (f[1] * src.y) * inv; r2 += (f[2] * src.z) * inv;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        r0 += __shfl_xor_sync(0xffffffffu, r0, d); r1 += __shfl_xor_sync(0xffffffffu, r1, d); r2 += __shfl_xor_sync(0xffffffffu, r2, d);
+    }
+    if (lane == 0) radiance[i] = make_float4(r0, r1, r2, 0.f);
+}
+
 /// The neighbour rows are trusted by the kernels above: every knn[i] in [0, rowInts] and every used entry in [0, n), else flag = 1.
 __global__ void k_pgValidate(const int *__restrict__ neighbors, int pitchInts, int rowInts, const int *__restrict__ knn, int n, int *__restrict__ flag) {
     const int i = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -195,6 +286,34 @@ bool launchPathgraphScatter(const NoriGpuSPoint *d_sps, int n, const int *d_neig
     }
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("pathgraph_scatter: ") + cudaGetErrorString(e); return false; }
+    return true;
+}
+
+size_t pgMisScratchBytes(int n, int rowInts) { return pgScatterScratchBytes(n) + (size_t) n * rowInts * sizeof(float); }
+
+/// computeMISAllOnGPURecord (src/pbsdf.cu:2922-2965), what the `pg` tool runs in its "knn" mode (src/cluster.cpp:223,
+/// SPoints::computeMISRadianceAOGWithProcessRecording): pdfsum once, then per pass gather -> blur[it], temp = radiance + eLd
+/// (the update gets it + 1 here, so only the initial temp is eLi), lastRun -> mc[it].
+bool launchPathgraphMis(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
+                        void *d_scratch, float *d_blur, float *d_mc, cudaStream_t st, std::string &err) {
+    if (n <= 0 || iterations < 0 || pitchInts < 1) { err = "pathgraph_mis: bad sizes"; return false; }
+    float4 *A = static_cast<float4 *>(d_scratch), *B = A + 4 * (size_t) n, *wi = B + 3 * (size_t) n, *eLi = wi + n, *eLd = eLi + n, *temp = eLd + n, *radiance = temp + n;
+    float *pdfsum = reinterpret_cast<float *>(radiance + n);
+    const unsigned gt = (unsigned) ((n + 255) / 256), gw = (unsigned) ((n + kPgWarps - 1) / kPgWarps);
+    k_pgPack<<<gt, 256, 0, st>>>(d_sps, n, A, B, wi, eLi, eLd);
+    cudaMemsetAsync(pdfsum, 0, (size_t) n * pitchInts * sizeof(float), st);
+    k_pgPdfSum<<<gw, kPgWarps * 32, 0, st>>>(A, B, wi, d_neighbors, pitchInts, d_knn, n, pitchInts, pdfsum);
+    cudaMemsetAsync(radiance, 0, (size_t) n * sizeof(float4), st);
+    k_pgUpdate<<<gt, 256, 0, st>>>(eLi, eLd, radiance, temp, n, 0);
+    for (int it = 0; it < iterations; ++it) {
+        k_pgMisGather<<<gw, kPgWarps * 32, 0, st>>>(A, B, wi, pdfsum, pitchInts, d_neighbors, pitchInts, d_knn, n, temp, radiance);
+        k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_blur + (size_t) it * 3 * n, n);
+        k_pgUpdate<<<gt, 256, 0, st>>>(eLi, eLd, radiance, temp, n, it + 1);
+        k_pgLastRun<<<gt, 256, 0, st>>>(A, B, wi, temp, radiance, n);
+        k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_mc + (size_t) it * 3 * n, n);
+    }
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("pathgraph_mis: ") + cudaGetErrorString(e); return false; }
     return true;
 }
 

@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_filter",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter",
 ]
 
 
@@ -137,7 +137,8 @@ def load_library() -> C.CDLL:
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_grid.argtypes = [vp, C.c_uint64, ip, vp, ip, ip, C.POINTER(HashParams)]
     L.nori_gpu_pathgraph_scatter.argtypes = [vp, vp, ip, vp, ip, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
-    L.nori_gpu_pathgraph_filter.argtypes = [vp, vp, ip, C.POINTER(HashParams), ip, vp, vp, vp, vp]
+    L.nori_gpu_pathgraph_filter.argtypes = [vp, ip, vp, ip, C.POINTER(HashParams), ip, vp, vp, vp, vp]
+    L.nori_gpu_pathgraph_mis.argtypes = [vp, vp, ip, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
     _lib = L
     return L
 
@@ -382,13 +383,24 @@ class Engine:
         self._ck(self.L.nori_gpu_pathgraph_scatter(self.h, _p(pts), n, _p(nb), nb.shape[1], _p(kn), int(iterations), _p(pm), _p(blur), _p(mc), C.byref(ms)))
         return pm, blur, mc, ms.value
 
-    def pathgraph_filter(self, points, hp: "HashParams", iterations: int):
-        """kNN + scatter in one call, the rows staying on the device: (pdfmarginal, blur, mc, (ms_knn, ms_scatter))."""
+    def pathgraph_mis(self, points, neighbors, knn, iterations: int):
+        """computeMISAllOnGPURecord (the pg tool's knn mode): SPoint records + the kNN rows -> (blur (it, n, 3), mc (it, n, 3), ms)."""
         assert points.dtype == SPOINT_DTYPE
         pts = np.ascontiguousarray(points); n = pts.shape[0]
-        pm = np.empty(n, np.float32); blur = np.empty((iterations, n, 3), np.float32); mc = np.empty((iterations, n, 3), np.float32)
+        nb = np.ascontiguousarray(neighbors, np.int32); kn = np.ascontiguousarray(knn, np.int32)
+        assert nb.ndim == 2 and nb.shape[0] == n and kn.shape == (n,)
+        blur = np.empty((iterations, n, 3), np.float32); mc = np.empty((iterations, n, 3), np.float32); ms = C.c_float()
+        self._ck(self.L.nori_gpu_pathgraph_mis(self.h, _p(pts), n, _p(nb), nb.shape[1], _p(kn), int(iterations), _p(blur), _p(mc), C.byref(ms)))
+        return blur, mc, ms.value
+
+    def pathgraph_filter(self, points, hp: "HashParams", iterations: int, mode: str = "scatter"):
+        """kNN + scatter ("scatter") or MIS gather ("mis") in one call, the rows staying on the device:
+        (pdfmarginal (scatter mode; zeros otherwise), blur, mc, (ms_knn, ms_stage))."""
+        assert points.dtype == SPOINT_DTYPE
+        pts = np.ascontiguousarray(points); n = pts.shape[0]
+        pm = np.zeros(n, np.float32); blur = np.empty((iterations, n, 3), np.float32); mc = np.empty((iterations, n, 3), np.float32)
         ms = (C.c_float * 2)()
-        self._ck(self.L.nori_gpu_pathgraph_filter(self.h, _p(pts), n, C.byref(hp), int(iterations), _p(pm), _p(blur), _p(mc), ms))
+        self._ck(self.L.nori_gpu_pathgraph_filter(self.h, {"scatter": 0, "mis": 1}[mode], _p(pts), n, C.byref(hp), int(iterations), _p(pm), _p(blur), _p(mc), ms))
         return pm, blur, mc, (ms[0], ms[1])
 
     # ---- operators -----------------------------------------------------------------------

@@ -261,14 +261,15 @@ void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const u
 /// The fork's path-graph tool (`pg`, src/cluster.cpp:156-253, mode "knn") on the tracer's own paths instead of another renderer's
 /// dumps: path vertices of the camera samples [sampleFirst, sampleLast) of every pixel (nori_gpu_path_vertices), grid as
 /// PathGraph::computeDimensions sizes it (nori_gpu_pathgraph_grid), kNN + marginal densities + `iterations` scatter passes
-/// (nori_gpu_pathgraph_filter), then the images writeFullLight / writeIndirectLight / writeFullinit compose from each path's
+/// (nori_gpu_pathgraph_filter; mis = true: the MIS gather the tool's "knn" mode runs, computeMISAllOnGPURecord; false: the
+/// scatter driver computeScatterAllOnGPURecord), then the images writeFullLight / writeIndirectLight / writeFullinit compose from each path's
 /// FIRST vertex (src/cluster.cpp:23-107): full = eLd + mc, indirect = mc, pt = eLi - eLd, blur, init = eLd, all of the last
 /// pass. With several samples per pixel the reference's loop keeps the last path of a pixel; here they are averaged.
 struct PathGraphImages {
     std::unique_ptr<Bitmap> full, indirect, pt, blur, init;
     uint64_t vertices = 0; double msVertices = 0, msKnn = 0, msScatter = 0;
 };
-PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, int device = 0);
+PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, bool mis = true, int device = 0);
 
 /// Search path for files named in scene descriptions (the reference prepends the scene's directory)
 class FileResolver {

@@ -336,7 +336,7 @@ void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uin
     }
 }
 
-PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, int device) {
+PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, bool mis, int device) {
     if (sampleLast <= sampleFirst) throw NoriException("pathGraphGpu: empty sample range");
     if (k < 1 || iterations < 1) throw NoriException("pathGraphGpu: k and the number of iterations must be positive");
     nori_gpu_ctx *ctx = scene->gpu(device);
@@ -357,7 +357,7 @@ PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t 
     check(ctx, nori_gpu_pathgraph_grid(v.data(), sizeof(NoriGpuSPoint), (int) n, nullptr, k, k, &hp), "nori_gpu_pathgraph_grid");   // PathGraph::computeDimensions
     std::vector<float> blur((size_t) iterations * 3 * n), mc((size_t) iterations * 3 * n);
     float ms[2] = {0, 0};
-    check(ctx, nori_gpu_pathgraph_filter(ctx, v.data(), (int) n, &hp, iterations, nullptr, blur.data(), mc.data(), ms), "nori_gpu_pathgraph_filter");
+    check(ctx, nori_gpu_pathgraph_filter(ctx, mis ? NORI_PG_MIS : NORI_PG_SCATTER, v.data(), (int) n, &hp, iterations, nullptr, blur.data(), mc.data(), ms), "nori_gpu_pathgraph_filter");
     out.msKnn = ms[0]; out.msScatter = ms[1];
     Bitmap *imgs[5];
     std::unique_ptr<Bitmap> *slots[5] = {&out.full, &out.indirect, &out.pt, &out.blur, &out.init};

@@ -3,7 +3,7 @@ compiled unmodified). Needs a GPU: run on the GPU box, the result comes back thr
 tests/golden/pathgraph_scatter_ref.npz.   python oracle/make_pathgraph_scatter_golden.py [out.npz]
 
 Two parts: (eval_*) pdf_device / bsdfeval_device at synthetic records of all four material tags, one direction each; (sc_*)
-computeScatterAllOnGPURecord + allGPUPdfMarginal on path-vertex records. The records of the second part are INPUT only: they
+computeScatterAllOnGPURecord + allGPUPdfMarginal and (mis_*) computeMISAllOnGPURecord on path-vertex records. The records of the second part are INPUT only: they
 are whole paths of the table scene (diffuse + microfacet vertices) taken from nori_gpu_path_vertices, their neighbour rows come
 from the reference's own buildHashGridAndFindKNN."""
 import os, sys
@@ -72,6 +72,8 @@ def main():
     pm, blur, mc, sec = ref.scatter(v, nb, knn, it)
     res["sc_sps"] = v.view(np.uint8).reshape(len(v), 168); res["sc_nb"] = nb; res["sc_knn"] = knn
     res["sc_pm"] = pm; res["sc_blur"] = blur; res["sc_mc"] = mc
+    mblur, mmc, _ = ref.mis(v, nb, knn, it)                 # computeMISAllOnGPURecord on the same records and rows
+    res["mis_blur"] = mblur; res["mis_mc"] = mmc
     np.savez_compressed(out, **res)
     print("wrote", out, len(v), "records", {t: int((v["bsdf_type"] == t).sum()) for t in np.unique(v["bsdf_type"])}, "nan rows", int(np.isnan(blur).any(-1).sum()))
 

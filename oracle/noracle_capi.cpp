@@ -309,6 +309,11 @@ void noracle_pathgraph_scatter(const void *sps, int n, const int32_t *neighbors,
                                int sequential, float *pdfmarginal, float *blur, float *mc) {
     pathgraphScatter(static_cast<const SPointRec *>(sps), n, neighbors, row_ints, knn, iterations, sequential != 0, pdfmarginal, blur, mc);
 }
+/// The MIS gather variant (computeMISAllOnGPURecord).
+void noracle_pathgraph_mis(const void *sps, int n, const int32_t *neighbors, int row_ints, const int32_t *knn, int iterations,
+                           int sequential, float *blur, float *mc) {
+    pathgraphMis(static_cast<const SPointRec *>(sps), n, neighbors, row_ints, knn, iterations, sequential != 0, blur, mc);
+}
 /// The tool's evaluations at one vertex each: pdf[i] = pdf_device(sps[i], wi[i]), bsdf[i] = bsdfeval_device(sps[i], wi[i]).
 void noracle_pathgraph_eval(const void *sps, int n, const float *wi, float *pdf, float *bsdf) {
     const SPointRec *p = static_cast<const SPointRec *>(sps);

@@ -4,6 +4,7 @@
 //   bsdfeval_device / pdf_device                                                           src/pbsdf.cu:464-628
 //   allGPUPdfMarginal / allGPUScatterRadiance / lastRun / updateRadiance                   src/pbsdf.cu:1738-1756, 1398-1431, 1497-1526, 2185-2194
 //   computeScatterAllOnGPURecord (the sequence of the passes)                              src/pbsdf.cu:2317-2368
+//   allGPUPdfSum / allGPUMISRadiance / computeMISAllOnGPURecord (the MIS gather variant)   src/pbsdf.cu:1600-1617, 1346-1370, 2922-2965
 // Float / double mixing is written out where the reference's literals (1.0, 4.0, M_PI, M_1_PI) promote an expression to double.
 // The reference is compiled by nvcc with -fmad=true, this file with -ffp-contract=off: agreement with the reference is to
 // rounding (tests: rtol 2e-4 on the radiance rows, which also covers the undefined order of its float atomics), agreement with
@@ -227,6 +228,70 @@ inline void pathgraphScatter(const SPointRec *sps, int n, const int32_t *neighbo
         std::memcpy(blur + (size_t) it * 3 * n, rad.data(), sizeof(float) * 3 * (size_t) n);
         for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c)
             temp[3 * (size_t) i + c] = it == 0 ? sps[i].eLi[c] : rad[3 * (size_t) i + c] + sps[i].eLd[c];
+        float *out = mc + (size_t) it * 3 * n;
+        for (int i = 0; i < n; ++i) {
+            out[3 * (size_t) i] = out[3 * (size_t) i + 1] = out[3 * (size_t) i + 2] = 0.0f;
+            const SPointRec &sp = sps[i];
+            const float spdf = pdfAt(sp, sp.wi);
+            if (spdf > 0.0f && sp.nidx > 0 && i + 1 < n) {
+                const float inv = (float) (1.0 / (double) (spdf * sp.rrpdf));
+                float f[3]; bsdfAt(sp, sp.wi, f);
+                for (int c = 0; c < 3; ++c) out[3 * (size_t) i + c] = (temp[3 * (size_t) (i + 1) + c] * f[c]) * inv;
+            }
+        }
+    }
+}
+
+/// computeMISAllOnGPURecord (src/pbsdf.cu:2922-2965): allGPUPdfSum (:1600-1617), then per pass allGPUMISRadiance (:1346-1370),
+/// updateRadiance with it + 1, lastRun. Sums in lane order + butterfly (the product's warp) or, `sequential`, in list order (the
+/// reference's single thread).
+inline void pathgraphMis(const SPointRec *sps, int n, const int32_t *neighbors, int rowInts, const int32_t *knn, int iterations,
+                         bool sequential, float *blur, float *mc) {
+    using namespace pgs;
+    std::vector<float> pdfsum((size_t) n * rowInts, 0.0f), temp(3 * (size_t) n), rad(3 * (size_t) n);
+    auto butterfly = [](float *lane) {
+        for (int d = 16; d > 0; d >>= 1) { float nxt[32]; for (int l = 0; l < 32; ++l) nxt[l] = lane[l] + lane[l ^ d]; std::memcpy(lane, nxt, sizeof nxt); }
+        return lane[0];
+    };
+    for (int i = 0; i < n; ++i) {
+        const int32_t *row = neighbors + (size_t) i * rowInts; const int k = knn[i];
+        for (int a = 0; a < k; ++a) {
+            const SPointRec &spa = sps[row[a]];
+            if (!(spa.nidx > 0 && spa.rrpdf > 1e-7f)) continue;
+            if (sequential) {
+                float s = 0.0f;
+                for (int b = 0; b < k; ++b) s += pdfAt(sps[row[b]], spa.wi) * sps[row[b]].rrpdf;
+                pdfsum[(size_t) i * rowInts + a] = s;
+            } else {
+                float lane[32];
+                for (int l = 0; l < 32; ++l) { float s = 0.0f; for (int b = l; b < k; b += 32) s += pdfAt(sps[row[b]], spa.wi) * sps[row[b]].rrpdf; lane[l] = s; }
+                pdfsum[(size_t) i * rowInts + a] = butterfly(lane);
+            }
+        }
+    }
+    for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) temp[3 * (size_t) i + c] = sps[i].eLi[c];
+    for (int it = 0; it < iterations; ++it) {
+        for (int i = 0; i < n; ++i) {
+            const int32_t *row = neighbors + (size_t) i * rowInts; const int k = knn[i];
+            float lanes[3][32];
+            for (int c = 0; c < 3; ++c) for (int l = 0; l < 32; ++l) lanes[c][l] = 0.0f;
+            float seq[3] = {0.0f, 0.0f, 0.0f};
+            for (int a = 0; a < k; ++a) {
+                const int ja = row[a];
+                const SPointRec &spa = sps[ja];
+                const float ps = pdfsum[(size_t) i * rowInts + a];
+                if (!(spa.nidx > 0 && ps > 0.0f && spa.rrpdf > 1e-7f) || ja + 1 >= n) continue;
+                float f[3]; bsdfAt(sps[i], spa.wi, f);
+                const float inv = (float) (1.0 / (double) ps);
+                for (int c = 0; c < 3; ++c) {
+                    const float term = (f[c] * temp[3 * (size_t) (ja + 1) + c]) * inv;
+                    seq[c] += term; lanes[c][a & 31] += term;          // lane a % 32 adds its neighbours in order
+                }
+            }
+            for (int c = 0; c < 3; ++c) rad[3 * (size_t) i + c] = sequential ? seq[c] : butterfly(lanes[c]);
+        }
+        std::memcpy(blur + (size_t) it * 3 * n, rad.data(), sizeof(float) * 3 * (size_t) n);
+        for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) temp[3 * (size_t) i + c] = rad[3 * (size_t) i + c] + sps[i].eLd[c];
         float *out = mc + (size_t) it * 3 * n;
         for (int i = 0; i < n; ++i) {
             out[3 * (size_t) i] = out[3 * (size_t) i + 1] = out[3 * (size_t) i + 2] = 0.0f;

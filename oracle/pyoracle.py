@@ -164,6 +164,7 @@ class Port:
         L.noracle_pathgraph_knn.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, _f32p]
         L.noracle_pathgraph_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
+        L.noracle_pathgraph_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p]
 
     def pathgraph_knn(self, pts, dim, cellsize, minb, k, dk):
         """noracle_pathgraph.h: hash grid + kNN. Returns (neighbors, knn, dknn, dists) rows nearest first, self swapped to the front."""
@@ -181,6 +182,15 @@ class Port:
         pm = np.empty(n, np.float32); blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
         self.L.noracle_pathgraph_scatter(sps.ctypes.data_as(C.c_void_p), n, nb, nb.shape[1], kn, iterations, int(sequential), pm, blur.reshape(-1), mc.reshape(-1))
         return pm, blur[:iterations], mc[:iterations]
+
+    def pathgraph_mis(self, sps, neighbors, knn, iterations, sequential=False):
+        """computeMISAllOnGPURecord restated: (blur (it, n, 3), mc (it, n, 3))."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168
+        nb = np.ascontiguousarray(neighbors, np.int32); kn = np.ascontiguousarray(knn, np.int32)
+        blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
+        self.L.noracle_pathgraph_mis(sps.ctypes.data_as(C.c_void_p), n, nb, nb.shape[1], kn, iterations, int(sequential), blur.reshape(-1), mc.reshape(-1))
+        return blur[:iterations], mc[:iterations]
 
     def pathgraph_eval(self, sps, wi):
         """pdf_device / bsdfeval_device restated: (pdf (n,), bsdf (n, 3)) of record i for direction wi[i]."""
@@ -251,6 +261,7 @@ class RefCuda:
         self.L.refcuda_knn.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, C.POINTER(C.c_double)]
         self.L.refcuda_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         self.L.refcuda_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
+        self.L.refcuda_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_double)]
 
     def knn(self, pts, dim, cellsize, minb, k, dk):
         """buildHashGridAndFindKNN. Returns (neighbors n x max(k,dk), knn, dknn, seconds)."""
@@ -272,6 +283,17 @@ class RefCuda:
         if rc != 0:
             raise RuntimeError(f"refcuda_scatter failed ({rc})")
         return pm, blur[:iterations], mc[:iterations], sec.value
+
+    def mis(self, sps, neighbors, knn, iterations):
+        """computeMISAllOnGPURecord of the compiled reference: (blur (it, n, 3), mc (it, n, 3), seconds)."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168
+        nb = np.ascontiguousarray(neighbors, np.int32); kn = np.ascontiguousarray(knn, np.int32)
+        blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32); sec = C.c_double()
+        rc = self.L.refcuda_mis(sps.ctypes.data_as(C.c_void_p), n, nb, nb.shape[1], kn, iterations, blur.reshape(-1), mc.reshape(-1), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_mis failed ({rc})")
+        return blur[:iterations], mc[:iterations], sec.value
 
     def eval(self, sps, wi):
         """pdf_device / bsdfeval_device of the compiled reference: (pdf (n,), bsdf (n, 3))."""

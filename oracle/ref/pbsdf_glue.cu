@@ -106,3 +106,32 @@ extern "C" int refcuda_scatter(const void *sps, int n, const int *neighbors, int
     cudaFree(cu_sps); cudaFree(cu_neighbors); cudaFree(cu_knn); cudaFree(cu_pm);
     return e == cudaSuccess ? 0 : -3;
 }
+
+/// computeMISAllOnGPURecord (src/pbsdf.cu:2922-2965; what the `pg` tool's "knn" mode runs) on n records and their neighbour rows.
+/// blur / mc: iterations x n x 3 floats. seconds: wall time of the reference's driver alone.
+extern "C" int refcuda_mis(const void *sps, int n, const int *neighbors, int row_ints, const int *knn, int iterations,
+                           float *blur, float *mc, double *seconds) {
+    SPoint *cu_sps = nullptr; int *cu_neighbors = nullptr, *cu_knn = nullptr; size_t pitch_n = 0;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) return -1;
+    cudaMemcpy(cu_sps, sps, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    if (cudaMallocPitch((void **) &cu_neighbors, &pitch_n, row_ints * sizeof(int), n) != cudaSuccess) return -2;
+    cudaMemcpy2D(cu_neighbors, pitch_n, neighbors, row_ints * sizeof(int), row_ints * sizeof(int), n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_knn, sizeof(int) * (size_t) n); cudaMemcpy(cu_knn, knn, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice);
+    ResultSpace ret;
+    for (int i = 0; i < iterations; ++i) {
+        ret.blur_results.push_back((val3f *) malloc(sizeof(val3f) * (size_t) n));
+        ret.mc_results.push_back((val3f *) malloc(sizeof(val3f) * (size_t) n));
+    }
+    cudaDeviceSynchronize();
+    auto t0 = std::chrono::steady_clock::now();
+    computeMISAllOnGPURecord(cu_sps, cu_neighbors, cu_knn, n, iterations, row_ints, ret, pitch_n);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (int i = 0; i < iterations; ++i) {
+        std::memcpy(blur + (size_t) i * 3 * n, ret.blur_results[i], sizeof(val3f) * (size_t) n);
+        std::memcpy(mc + (size_t) i * 3 * n, ret.mc_results[i], sizeof(val3f) * (size_t) n);
+        free(ret.blur_results[i]); free(ret.mc_results[i]);
+    }
+    cudaFree(cu_sps); cudaFree(cu_neighbors); cudaFree(cu_knn);
+    return e == cudaSuccess ? 0 : -3;
+}

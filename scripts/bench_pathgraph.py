@@ -33,6 +33,10 @@ def scatter_leg(spp, k, iterations):
     for _ in range(4):
         t0 = time.perf_counter(); fpm, fblur, fmc, fms = e.pathgraph_filter(v, hp, iterations); fwall.append(time.perf_counter() - t0)
     filter_wall = float(np.median(fwall[1:]))
+    mms = []
+    for _ in range(3):
+        mblur, mmc, t = e.pathgraph_mis(v, nb, knn, iterations); mms.append(t)
+    mis_ms = float(np.median(mms[1:]))
     evals = float(knn.sum()) * (1 + iterations) + len(v) * 2.0 * iterations          # pdf per edge once, bsdf per edge per pass, lastRun
     out = {"workload": f"path vertices of veach path_mis {s.width}x{s.height}, {spp} spp: {len(v)} vertices, k = {k} ({float(knn.mean()):.1f} used), {iterations} iterations",
            "vertices": int(len(v)), "edges": int(knn.sum()), "iterations": iterations,
@@ -40,8 +44,16 @@ def scatter_leg(spp, k, iterations):
                          "filter_call_wall_ms": filter_wall * 1e3, "filter_device_ms": [float(fms[0]), float(fms[1])],
                          "filter": "nori_gpu_pathgraph_filter: kNN + scatter in one call from the host records (H2D of 168 B per vertex, rows never leave the device, D2H of the result rows)",
                          "timing": "ms_device: CUDA events around pack + marginal + iterations x (scatter, update, lastRun), records resident; ms_call_wall: the whole nori_gpu_pathgraph_scatter call from host buffers (H2D of records and rows, D2H of all result rows)"}}
+    out["mis"] = {"what": "computeMISAllOnGPURecord (the pg tool's knn mode): pdfsum (k^2 evaluations per vertex) + iterations x (gather, update, lastRun)",
+                  "nori_b200_ms_device": mis_ms, "Gevals_per_s_device": (float((knn.astype(np.float64) ** 2).sum()) + float(knn.sum()) * iterations) / mis_ms / 1e6}
     if have_refcuda():
         ref = RefCuda()
+        msec = []
+        for _ in range(2):
+            rmblur, rmmc, sec = ref.mis(v, nb, knn, iterations); msec.append(sec)
+        out["mis"]["reference_ms"] = float(msec[-1]) * 1e3
+        out["mis"]["speedup_vs_reference_device"] = float(msec[-1]) * 1e3 / mis_ms
+        out["mis"]["max_rel_row_error_last_blur"] = float((np.abs(mblur[-1] - rmblur[-1]) / (np.abs(rmblur[-1]).max(-1, keepdims=True) + 1e-3)).max())
         secs = []
         for _ in range(3):
             rpm, rblur, rmc, sec = ref.scatter(v, nb, knn, iterations)

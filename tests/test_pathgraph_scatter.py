@@ -103,6 +103,23 @@ def test_oracle_scatter_vs_reference_vectors(port):
     np.testing.assert_allclose(pm_lane, pm, rtol=2e-6, atol=1e-30)
 
 
+def test_oracle_mis_gather_vs_reference_vectors(port):
+    """computeMISAllOnGPURecord of the compiled reference (what the `pg` tool's "knn" mode runs: allGPUPdfSum + allGPUMISRadiance)
+    on the fixture's records and rows. A gather without atomics: the reference is deterministic here, so everything agrees to the
+    rounding of its fused multiply-adds."""
+    z = np.load(REF_NPZ)
+    s = records(z["sc_sps"]); nb, knn = z["sc_nb"], z["sc_knn"]
+    it = z["mis_blur"].shape[0]
+    blur, mc = port.pathgraph_mis(s, nb, knn, it, sequential=True)
+    for i in range(it):
+        close_rows(blur[i], z["mis_blur"][i], RTOL_DET * 2, f"mis blur[{i}]")
+        close_rows(mc[i], z["mis_mc"][i], RTOL_DET * 2, f"mis mc[{i}]")
+    assert np.abs(z["mis_blur"][0]).sum() > 0 and not np.allclose(z["mis_blur"][0], z["sc_blur"][0])
+    # the lane order of the product's warps changes the sums by rounding only
+    lblur, lmc = port.pathgraph_mis(s, nb, knn, it, sequential=False)
+    close_rows(lblur[it - 1], blur[it - 1], 1e-5, "lane order vs list order")
+
+
 def test_oracle_mc_row_is_the_paths_own_estimate(port):
     """lastRun on diffuse vertices: bsdf / pdf = albedo, so mc[0][i] = eLi[i + 1] * albedo / rrpdf — with records whose eLi obeys
     the path recursion eLi[i] = eLd[i] + albedo * eLi[i + 1] / rrpdf this reads mc[0] + eLd = eLi."""
@@ -154,6 +171,37 @@ def test_gpu_scatter_vs_oracle_on_reference_vectors(engine, port):
 
 
 @pytest.mark.gpu
+def test_gpu_mis_gather_vs_oracle_and_reference(engine, port):
+    """nori_gpu_pathgraph_mis on the fixture's records: no atomics anywhere, so EVERY row of every pass equals the oracle's
+    (same operations, same summation order) to the bit — also on synthetic records of all four tags with rows longer than a
+    warp —, and agrees with the compiled reference's vectors to rounding."""
+    z = np.load(REF_NPZ)
+    s = records(z["sc_sps"]); nb, knn = z["sc_nb"], z["sc_knn"]
+    it = z["mis_blur"].shape[0]
+    blur, mc, ms = engine.pathgraph_mis(s, nb, knn, it)
+    wblur, wmc = port.pathgraph_mis(s, nb, knn, it, sequential=False)
+    np.testing.assert_array_equal(blur.view(np.uint32), wblur.view(np.uint32))
+    np.testing.assert_array_equal(mc.view(np.uint32), wmc.view(np.uint32))
+    for i in range(it):
+        close_rows(blur[i], z["mis_blur"][i], RTOL_DET * 2, f"mis blur[{i}] vs reference")
+        close_rows(mc[i], z["mis_mc"][i], RTOL_DET * 2, f"mis mc[{i}] vs reference")
+    t = records(z["eval_sps"])[:3000].copy()
+    n = len(t); idx = np.arange(n)
+    inner = idx % 4 != 3
+    t["nidx"] = 0; t["nidx"][inner] = idx[inner] + 1
+    rng = np.random.default_rng(5)
+    t["eLi"] = rng.random((n, 3)); t["eLd"] = rng.random((n, 3))
+    k = 45
+    tnb = rng.integers(0, n, size=(n, k)).astype(np.int32); tnb[:, 0] = idx
+    tknn = rng.integers(1, k + 1, size=n).astype(np.int32)
+    blur, mc, _ = engine.pathgraph_mis(t, tnb, tknn, 2)
+    wblur, wmc = port.pathgraph_mis(t, tnb, tknn, 2, sequential=False)
+    np.testing.assert_array_equal(blur.view(np.uint32), wblur.view(np.uint32))
+    np.testing.assert_array_equal(mc.view(np.uint32), wmc.view(np.uint32))
+    assert np.isfinite(blur).all() and np.abs(blur[1]).sum() > 0
+
+
+@pytest.mark.gpu
 def test_gpu_scatter_all_tags_vs_oracle(engine, port):
     """Synthetic records of all four tags (the fixture's eval set, given paths of four vertices and random neighbour rows): the
     kernels' evaluations agree with the oracle's to the bit wherever no atomic is involved."""
@@ -200,6 +248,13 @@ def test_gpu_scatter_vs_compiled_reference_cuda(gpu_scene, scenes, port):
         close_rows(blur[i], rblur[i], RTOL_SUM, f"blur[{i}]")
         close_rows(mc[i], rmc[i], RTOL_SUM, f"mc[{i}]")
     assert np.abs(rblur[2]).sum() > 0 and (rpm > 0).mean() > 0.3
+    mblur, mmc, _ = e.pathgraph_mis(v, nb, knn, 2)
+    rmblur, rmmc, _ = RefCuda().mis(v, nb, knn, 2)
+    for i in range(2):
+        close_rows(mblur[i], rmblur[i], RTOL_DET * 2, f"mis blur[{i}]")
+        close_rows(mmc[i], rmmc[i], RTOL_DET * 2, f"mis mc[{i}]")
+    fpm, fblur, fmc, _ = e.pathgraph_filter(v, hp, 2, mode="mis")
+    np.testing.assert_array_equal(fblur.view(np.uint32), mblur.view(np.uint32))       # same rows, same kernels: deterministic
 
 
 @pytest.mark.gpu
