@@ -59,8 +59,11 @@ enum { NORI_ISECT_REFERENCE_MT = 0, NORI_ISECT_WATERTIGHT = 1 };
 /* Node layout read by the traversal kernels of nori_gpu_render / nori_gpu_trace*:
  * FLOAT: 64-byte nodes, two child boxes in single precision (four 16-byte loads per visit).
  * QUANTISED: 32-byte nodes, child boxes on a 15-bit grid over the scene box, rounded outwards (two loads per visit;
- * half the node traffic for scenes whose tree does not fit the caches). Same tree, same triangle tests: same hits. */
-enum { NORI_ACCEL_FLOAT = 0, NORI_ACCEL_QUANTISED = 1 };
+ * half the node traffic for scenes whose tree does not fit the caches). Same tree, same triangle tests: same hits.
+ * WIDE4: the same tree collapsed on the device into 4-wide nodes of 128 bytes (four child boxes in single precision, half as many
+ * dependent node fetches per ray). Same leaves, same triangle tests: same closest hits; any-hit rays agree on occlusion.
+ * Measured no faster than FLOAT on this hardware (profiles/r02_notes.md); FLOAT is the default. */
+enum { NORI_ACCEL_FLOAT = 0, NORI_ACCEL_QUANTISED = 1, NORI_ACCEL_WIDE4 = 2 };
 
 /* One Mesh (include/nori/mesh.h:172-175): column-major Eigen buffers == C arrays below. */
 typedef struct {

@@ -467,4 +467,78 @@ bool quantiseNodes(BvhDevice &bvh, float inflate, cudaStream_t st, std::string &
     return true;
 }
 
+// ---------------------------------------------------------------------------------------------
+// 4-wide node layout (include/nori_gpu.h: NORI_ACCEL_WIDE4): the binary tree collapsed top-down. A wide node is rooted at a
+// binary inner node; its children start as that node's two and, while fewer than four, the inner child with the largest
+// surface area is replaced by its own two (the greedy collapse of Wald et al. 2008 / Dammertz et al. 2008). One launch per
+// level of the wide tree: a job = (binary node, wide node index); every inner child found gets the next wide index and becomes
+// a job of the next level.
+//   wide node = 8 x float4 (128 B, four 256-bit loads): lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4] link[4] -,
+//   link as in the binary tree (>= 0: wide node index, < 0: leaf code), kWideEmpty for an unused child.
+__device__ __forceinline__ float wideArea(const float *b) {          // b = lo.xyz hi.xyz
+    const float dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+__device__ __forceinline__ void wideChildren(const float4 *__restrict__ nodes, uint32_t bin, float (*box)[6], int *link, int a, int b) {
+    const float4 n0 = nodes[4 * (size_t) bin], n1 = nodes[4 * (size_t) bin + 1], n2 = nodes[4 * (size_t) bin + 2], n3 = nodes[4 * (size_t) bin + 3];
+    box[a][0] = n0.x; box[a][3] = n0.y; box[a][1] = n0.z; box[a][4] = n0.w; box[a][2] = n2.x; box[a][5] = n2.y; link[a] = __float_as_int(n3.x);
+    box[b][0] = n1.x; box[b][3] = n1.y; box[b][1] = n1.z; box[b][4] = n1.w; box[b][2] = n2.z; box[b][5] = n2.w; link[b] = __float_as_int(n3.y);
+}
+__global__ void k_wideLevel(const float4 *__restrict__ nodes, const uint2 *__restrict__ jobsIn, uint32_t nIn, uint2 *__restrict__ jobsOut,
+                            uint32_t *__restrict__ counters /* [0] next wide index, [1] jobs written */, float4 *__restrict__ wnodes) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nIn) return;
+    const uint2 job = jobsIn[t];
+    float box[4][6]; int link[4]; int cnt = 2;
+    wideChildren(nodes, job.x, box, link, 0, 1);
+    while (cnt < 4) {
+        int pick = -1; float best = -1.0f;
+        for (int c = 0; c < cnt; ++c) if (link[c] >= 0) { const float a = wideArea(box[c]); if (a > best) { best = a; pick = c; } }
+        if (pick < 0) break;
+        wideChildren(nodes, (uint32_t) link[pick], box, link, pick, cnt);
+        ++cnt;
+    }
+    for (int c = 0; c < cnt; ++c) if (link[c] >= 0) {
+        const uint32_t w = atomicAdd(&counters[0], 1u), pos = atomicAdd(&counters[1], 1u);
+        jobsOut[pos] = make_uint2((uint32_t) link[c], w);
+        link[c] = (int) w;
+    }
+    for (int c = cnt; c < 4; ++c) { for (int k = 0; k < 6; ++k) box[c][k] = 0.0f; link[c] = kWideEmpty; }
+    float4 *o = wnodes + 8 * (size_t) job.y;
+    for (int k = 0; k < 3; ++k) {
+        o[2 * k] = make_float4(box[0][k], box[1][k], box[2][k], box[3][k]);
+        o[2 * k + 1] = make_float4(box[0][3 + k], box[1][3 + k], box[2][3 + k], box[3][3 + k]);
+    }
+    o[6] = make_float4(__int_as_float(link[0]), __int_as_float(link[1]), __int_as_float(link[2]), __int_as_float(link[3]));
+    o[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+bool wideNodes(BvhDevice &bvh, cudaStream_t st, std::string &err) {
+    if (!bvh.nodes || !bvh.nNodes) { err = "wideNodes: no BVH"; return false; }
+    if (bvh.wnodes) return true;
+    const uint32_t n = bvh.nNodes;
+    float4 *w = nullptr; uint2 *jobs[2] = {nullptr, nullptr}; uint32_t *counters = nullptr;
+    auto fail = [&](const char *what) { cudaFree(w); cudaFree(jobs[0]); cudaFree(jobs[1]); cudaFree(counters); err = what; return false; };
+    if (cudaMalloc((void **) &w, 8 * (size_t) n * sizeof(float4)) != cudaSuccess || cudaMalloc((void **) &jobs[0], (size_t) n * sizeof(uint2)) != cudaSuccess ||
+        cudaMalloc((void **) &jobs[1], (size_t) n * sizeof(uint2)) != cudaSuccess || cudaMalloc((void **) &counters, 2 * sizeof(uint32_t)) != cudaSuccess)
+        return fail("wideNodes: out of device memory");
+    const uint2 root = make_uint2(0u, 0u);
+    uint32_t hc[2] = {1u, 0u}, nIn = 1, depth = 0;
+    if (cudaMemcpyAsync(jobs[0], &root, sizeof(root), cudaMemcpyHostToDevice, st) != cudaSuccess) return fail("wideNodes: copy failed");
+    while (nIn) {
+        hc[1] = 0;
+        if (cudaMemcpyAsync(counters, hc, sizeof(hc), cudaMemcpyHostToDevice, st) != cudaSuccess) return fail("wideNodes: copy failed");
+        k_wideLevel<<<(nIn + 127u) / 128u, 128, 0, st>>>(bvh.nodes, jobs[depth & 1], nIn, jobs[(depth + 1) & 1], counters, w);
+        if (cudaMemcpyAsync(hc, counters, sizeof(hc), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
+            return fail("wideNodes: kernel failed");
+        nIn = hc[1]; ++depth;
+        if (hc[0] > n || depth > 4096) return fail("wideNodes: the binary tree is not a tree (internal error)");
+    }
+    // a visit pushes at most three entries: the traversal's stack (kWideStackSize) must hold 3 per level
+    if (3u * depth + 1u > (uint32_t) kWideStackSize) return fail("wideNodes: the collapsed tree is too deep for the traversal stack");
+    cudaFree(jobs[0]); cudaFree(jobs[1]); cudaFree(counters);
+    bvh.wnodes = w; bvh.nWide = hc[0]; bvh.wideDepth = depth;
+    return true;
+}
+
 } // namespace ng

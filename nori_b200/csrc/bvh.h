@@ -31,6 +31,9 @@ struct BvhDevice {
     // optional second copy of the nodes, 32 B each: child boxes on a 15-bit grid over the scene box (quantiseNodes)
     uint4 *qnodes = nullptr;
     float qBase[3] = {0, 0, 0}, qExt[3] = {1, 1, 1};   // coordinate = qBase + m * qExt, m in [1, 2) (traverse_persistent.cuh)
+    // optional third copy: the tree collapsed to 4-wide nodes, 128 B each (wideNodes)
+    float4 *wnodes = nullptr;
+    uint32_t nWide = 0, wideDepth = 0;
 };
 
 /// Builds the tree for triangles tris[0..nTris) over vpos. Frees nothing it did not allocate;
@@ -44,5 +47,10 @@ bool buildBvh(const float4 *d_vpos, const uint4 *d_tris, uint32_t nTris, const B
 ///   carry the builder's inflation, ~0.1 cell, which covers the 0.004-cell error of the decode),
 /// so that the two bytes drop into a float mantissa (0x3F.. .. .. 00 = 1 + q / 32768) with one PRMT.
 bool quantiseNodes(BvhDevice &bvh, float inflate, cudaStream_t stream, std::string &err);
+
+/// NORI_ACCEL_WIDE4: writes bvh.wnodes, the binary tree collapsed top-down into 4-wide nodes (bvh.cu). Leaves are unchanged.
+constexpr int kWideEmpty = 0x7ffffffe;       // link of an unused child slot
+constexpr int kWideStackSize = 128;          // traversal stack entries of the wide layout (three pushes per visit)
+bool wideNodes(BvhDevice &bvh, cudaStream_t stream, std::string &err);
 
 } // namespace ng

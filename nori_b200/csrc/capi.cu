@@ -86,6 +86,7 @@ DeviceScene deviceScene(const nori_gpu_ctx *c) {
     s.nodes = c->bvh.nodes; s.leafTris = c->bvh.leafTris; s.nNodes = c->bvh.nNodes;
     s.cam = c->cam; s.filter = c->filter; s.isectMode = c->isectMode;
     s.qnodes = c->accelLayout == NORI_ACCEL_QUANTISED ? c->bvh.qnodes : nullptr;
+    s.wnodes = c->accelLayout == NORI_ACCEL_WIDE4 ? c->bvh.wnodes : nullptr;
     for (int k = 0; k < 3; ++k) { s.qBase[k] = c->bvh.qBase[k]; s.qExt[k] = c->bvh.qExt[k]; }
     return s;
 }
@@ -93,7 +94,7 @@ DeviceScene deviceScene(const nori_gpu_ctx *c) {
 void freeScene(nori_gpu_ctx *c) {
     cudaFree(c->d_vpos); cudaFree(c->d_vnrm); cudaFree(c->d_vuv); cudaFree(c->d_tris);
     cudaFree(c->d_meshes); cudaFree(c->d_emitters); cudaFree(c->d_cdf);
-    cudaFree(c->bvh.nodes); cudaFree(c->bvh.leafTris); cudaFree(c->bvh.qnodes);
+    cudaFree(c->bvh.nodes); cudaFree(c->bvh.leafTris); cudaFree(c->bvh.qnodes); cudaFree(c->bvh.wnodes);
     c->d_vpos = c->d_vnrm = nullptr; c->d_vuv = nullptr; c->d_tris = nullptr; c->d_meshes = nullptr; c->d_emitters = nullptr; c->d_cdf = nullptr;
     c->bvh = BvhDevice(); c->haveBvh = false; c->meshes.clear(); c->emitters.clear(); c->nTris = c->nVerts = 0;
 }
@@ -216,7 +217,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     if (const char *s = getenv("NORI_GPU_BINS")) ctx->rayBins = atoi(s) != 0;
     if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
     if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
-    if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : NORI_ACCEL_FLOAT;
+    if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : (atoi(e) == 2 ? NORI_ACCEL_WIDE4 : NORI_ACCEL_FLOAT);
 #endif
     *out = ctx;
     return NORI_GPU_OK;
@@ -386,21 +387,23 @@ int nori_gpu_build_accel(nori_gpu_ctx *ctx, NoriGpuAccelStats *out) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(ctx->d_tris, "build_accel: upload meshes first");
     CK(cudaSetDevice(ctx->device));
-    cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.leafTris); cudaFree(ctx->bvh.qnodes); ctx->bvh = BvhDevice(); ctx->haveBvh = false;
+    cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.leafTris); cudaFree(ctx->bvh.qnodes); cudaFree(ctx->bvh.wnodes); ctx->bvh = BvhDevice(); ctx->haveBvh = false;
     NoriGpuAccelStats st;
     if (!buildBvh(ctx->d_vpos, ctx->d_tris, ctx->nTris, ctx->bvhParams, ctx->stream, ctx->bvh, st, ctx->err)) return NORI_GPU_ECUDA;
     ctx->haveBvh = true;
     if (ctx->accelLayout == NORI_ACCEL_QUANTISED && !quantiseNodes(ctx->bvh, ctx->bvhParams.inflate, ctx->stream, ctx->err)) return NORI_GPU_ECUDA;
+    if (ctx->accelLayout == NORI_ACCEL_WIDE4 && !wideNodes(ctx->bvh, ctx->stream, ctx->err)) return NORI_GPU_ECUDA;
     if (out) *out = st;
     return NORI_GPU_OK;
 }
 
 int nori_gpu_set_accel_layout(nori_gpu_ctx *ctx, int layout) {
     if (!ctx) return NORI_GPU_EINVAL;
-    REQUIRE(layout == NORI_ACCEL_FLOAT || layout == NORI_ACCEL_QUANTISED, "set_accel_layout: unknown layout");
+    REQUIRE(layout == NORI_ACCEL_FLOAT || layout == NORI_ACCEL_QUANTISED || layout == NORI_ACCEL_WIDE4, "set_accel_layout: unknown layout");
     CK(cudaSetDevice(ctx->device));
     ctx->accelLayout = layout;
     if (layout == NORI_ACCEL_QUANTISED && ctx->haveBvh && !quantiseNodes(ctx->bvh, ctx->bvhParams.inflate, ctx->stream, ctx->err)) return NORI_GPU_ECUDA;
+    if (layout == NORI_ACCEL_WIDE4 && ctx->haveBvh && !wideNodes(ctx->bvh, ctx->stream, ctx->err)) return NORI_GPU_ECUDA;
     return NORI_GPU_OK;
 }
 

@@ -43,11 +43,11 @@ struct RayArrayIO {
         hits[i] = gid == kNoHit ? make_float4(0.f, 0.f, 0.f, __uint_as_float(gid)) : make_float4(t, u, v, __uint_as_float(gid));
     }
 };
-template <bool SHADOW, bool WT, bool QN = false>
-__global__ void __launch_bounds__(128, 10) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
+template <bool SHADOW, bool WT, int QN = 0>
+__global__ void __launch_bounds__(128, QN == 2 ? 8 : 10) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
     RayArrayIO io; io.rays = rays; io.hits = hits; io.n = (uint32_t) n;
     const QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]};
-    tracePersistent<SHADOW, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, (uint32_t) n, cursor, io, kFetchThreshold, g);
+    tracePersistent<SHADOW, WT, QN>(QN == 2 ? sc.wnodes : (QN == 1 ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes), sc.leafTris, (uint32_t) n, cursor, io, kFetchThreshold, g);
 }
 
 void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned int *cursor, cudaStream_t st) {
@@ -57,8 +57,13 @@ void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, 
     cudaMemsetAsync(cursor, 0, sizeof(unsigned int), st);
     const bool wt = sc.isectMode == NORI_ISECT_WATERTIGHT;
     if (sc.qnodes && !wt) {                                   // quantised node layout
-        if (shadow) k_tracePersistent<true, false, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
-        else k_tracePersistent<false, false, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
+        if (shadow) k_tracePersistent<true, false, 1><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
+        else k_tracePersistent<false, false, 1><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor);
+        return;
+    }
+    if (sc.wnodes && !wt) {                                   // 4-wide node layout (64 registers: 8 CTAs per SM)
+        if (shadow) k_tracePersistent<true, false, 2><<<grid * 8u / 10u, 128, 0, st>>>(sc, rays, n, hits, cursor);
+        else k_tracePersistent<false, false, 2><<<grid * 8u / 10u, 128, 0, st>>>(sc, rays, n, hits, cursor);
         return;
     }
     if (shadow) { if (wt) k_tracePersistent<true, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); else k_tracePersistent<true, false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); }

@@ -143,11 +143,11 @@ template <> struct IoIndirect<ClosestIO> { static constexpr bool value = true; }
 /// Accel::rayIntersect(ray, its, false) for every live path (persistent warps, dynamic fetch).
 __device__ __forceinline__ QGrid sceneGrid(const DeviceScene &sc) { QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]}; return g; }
 
-template <int MINB, bool WT = false, bool QN = false>
+template <int MINB, bool WT = false, int QN = 0>
 __global__ void __launch_bounds__(128, MINB) k_traceClosest(DeviceScene sc, Pool pool, Counters *c, int fetchThreshold) {
     ClosestIO io; io.pool = pool; io.sorted = pool.order && c->orderSorted;
     const uint32_t nRays = pool.order ? min(c->traceLimit, pool.capacity) : pool.capacity;
-    tracePersistent<false, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, nRays, &c->traceCursor[0], io, fetchThreshold, sceneGrid(sc));
+    tracePersistent<false, WT, QN>(QN == 2 ? sc.wnodes : (QN == 1 ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes), sc.leafTris, nRays, &c->traceCursor[0], io, fetchThreshold, sceneGrid(sc));
     // This grid is a programmatic dependent of the splat kernels (they execute launch_dependents on entry). It must
     // not COMPLETE before they have: k_prepare, a normal launch behind it, is ordered after this grid only, and it
     // resets counters the splat still reads. Waiting here, after the last hit is stored, keeps the overlap and makes
@@ -393,10 +393,10 @@ struct ShadowIO {
 };
 
 /// Accel::rayIntersect(ray, its, true) for the queued shadow rays.
-template <int MINB, bool WT = false, bool QN = false>
+template <int MINB, bool WT = false, int QN = 0>
 __global__ void __launch_bounds__(128, MINB) k_traceShadow(DeviceScene sc, Pool pool, float4 *recA, float *recB, size_t recCount, Counters *c, int fetchThreshold) {
     ShadowIO io; io.pool = pool; io.recA = recA; io.recB = recB; io.recCount = recCount;
-    tracePersistent<true, WT, QN>(QN ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes, sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold, sceneGrid(sc));
+    tracePersistent<true, WT, QN>(QN == 2 ? sc.wnodes : (QN == 1 ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes), sc.leafTris, c->shadowCount, &c->traceCursor[1], io, fetchThreshold, sceneGrid(sc));
 }
 
 /// Hands path slot `dst` to camera sample index g of the issue order (pass, tile, sample, pixel):
@@ -1385,10 +1385,11 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         ++launches;
     }
     {
-        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes || sc.wnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
         const bool overlap = splat && tune().overlapSplat;
         if (sc.isectMode == NORI_ISECT_WATERTIGHT) launchOverlapped(k_traceClosest<8, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
-        else if (sc.qnodes) launchOverlapped(k_traceClosest<8, false, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (sc.qnodes) launchOverlapped(k_traceClosest<8, false, 1>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
+        else if (sc.wnodes) launchOverlapped(k_traceClosest<8, false, 2>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 10) launchOverlapped(k_traceClosest<10>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 12) launchOverlapped(k_traceClosest<12>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (b == 9) launchOverlapped(k_traceClosest<9>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
@@ -1415,9 +1416,10 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
     }
     if (ev) cudaEventRecord(ev[2], st);
     if (rp.integrator != NORI_INT_NORMALS) {
-        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes || sc.wnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
         if (sc.isectMode == NORI_ISECT_WATERTIGHT) k_traceShadow<8, true><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
-        else if (sc.qnodes) k_traceShadow<8, false, true><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (sc.qnodes) k_traceShadow<8, false, 1><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
+        else if (sc.wnodes) k_traceShadow<8, false, 2><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 10) k_traceShadow<10><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 12) k_traceShadow<12><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);
         else if (b == 9) k_traceShadow<9><<<g, 128, 0, st>>>(sc, pool, rp.recA, rp.recB, rp.recCount, c, tune().fetchShadow);

@@ -58,6 +58,7 @@ struct DeviceScene {
     uint32_t nNodes;
     const uint4 *qnodes;         // quantised copy of the nodes (NORI_ACCEL_QUANTISED) or nullptr; grid: coordinate = qBase + m qExt
     float qBase[3], qExt[3];
+    const float4 *wnodes;        // 4-wide copy of the tree (NORI_ACCEL_WIDE4) or nullptr: 8 x float4 per node
     int isectMode;               // NORI_ISECT_*: ray-triangle test used by every traversal (0 = the reference's Moeller-Trumbore)
     Camera cam;
     FilterTab filter;

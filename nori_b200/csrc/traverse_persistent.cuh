@@ -30,9 +30,10 @@ template <bool HIGH> NG_D float qfield(uint32_t w) { return __uint_as_float(__by
 /// sorted order list names) specialise this to true and take the handle as load()'s second argument.
 template <class IO> struct IoIndirect { static constexpr bool value = false; };
 
-/// QN: `nodes` holds the 32-byte quantised nodes (two 16-byte loads per visit instead of four); the slab test is the
+/// QN = 2: `nodes` holds the 4-wide nodes of bvh.cu: wideNodes (128 bytes, four 256-bit loads per visit, up to three pushes).
+/// QN = 1: `nodes` holds the 32-byte quantised nodes (two 16-byte loads per visit instead of four); the slab test is the
 /// same fused multiply-add per plane with per-ray constants that fold the grid in: t = m * (ext / d) + (base - o) / d.
-template <bool ANY_HIT, bool WT = false, bool QN = false, class IO>
+template <bool ANY_HIT, bool WT = false, int QN = 0, class IO>
 NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
                           unsigned int *workCounter, IO &io, int tuning = kFetchThreshold, QGrid grid = QGrid()) {
     const int fetchThreshold = tuning & 0xff;                  // refill when fewer lanes than this still hold a ray
@@ -45,10 +46,11 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
     int sp = 0, cur = 0, leaf = 0;                             // leaf: postponed leaf link (< 0) or 0
     constexpr int kSharedStack = NORI_TRACE_SHARED_STACK;
     __shared__ int sStack[kSharedStack > 0 ? kSharedStack : 1][128];
-    int stack[kStackSize - kSharedStack];
+    constexpr int kStack = QN == 2 ? kWideStackSize : kStackSize;
+    int stack[kStack - kSharedStack];
     const unsigned tix = threadIdx.x;
     auto push = [&](int v) {
-        NG_CHECK(sp < kStackSize);
+        NG_CHECK(sp < kStack);
         if (kSharedStack > 0 && sp < kSharedStack) sStack[sp][tix] = v; else stack[sp - kSharedStack] = v;
         ++sp;
     };
@@ -85,7 +87,7 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
                         idx = fabsf(d.x) > 1e-30f ? 1.0f / d.x : copysignf(big, d.x);                                    \
                         idy = fabsf(d.y) > 1e-30f ? 1.0f / d.y : copysignf(big, d.y);                                    \
                         idz = fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(big, d.z);                                    \
-                        if (QN) {   /* plane at m: ((base + m ext) - o) / d = m * (ext / d) - (o - base) / d */          \
+                        if (QN == 1) {   /* plane at m: ((base + m ext) - o) / d = m * (ext / d) - (o - base) / d */          \
                             oodx = (o.x - grid.bx) * idx; oody = (o.y - grid.by) * idy; oodz = (o.z - grid.bz) * idz;    \
                             idx *= grid.ex; idy *= grid.ey; idz *= grid.ez;                                              \
                         } else { oodx = o.x * idx; oody = o.y * idy; oodz = o.z * idz; }                                 \
@@ -113,9 +115,43 @@ NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__rest
         // of a speculating lane uses its not-yet-tightened tbest: conservative, never wrong.
         for (;;) {
             for (;;) {                                         // inner nodes (warp-uniform loop)
+                if (QN == 2) {
+                    if (cur >= 0 && cur != kDone) {
+                        const float4 *n = nodes + 8 * (size_t) cur;
+                        float4 lox, hix, loy, hiy, loz, hiz, lk, pad;
+                        loadNode(n, lox, hix, loy, hiy);
+                        loadNode(n + 4, loz, hiz, lk, pad);
+                        // slab test of the four children (fused multiply-adds on inflated boxes, as the binary visit)
+                        float key[4]; int link[4];
+#define NG_WIDE_CHILD(C, M)                                                                                              \
+                        {                                                                                                \
+                            const float x0 = __fmaf_rn(lox.M, idx, -oodx), x1 = __fmaf_rn(hix.M, idx, -oodx);            \
+                            const float y0 = __fmaf_rn(loy.M, idy, -oody), y1 = __fmaf_rn(hiy.M, idy, -oody);            \
+                            const float z0 = __fmaf_rn(loz.M, idz, -oodz), z1 = __fmaf_rn(hiz.M, idz, -oodz);            \
+                            const float tmn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), mint));    \
+                            const float tmx = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tbest));   \
+                            link[C] = __float_as_int(lk.M);                                                              \
+                            key[C] = (tmn <= tmx && link[C] != kWideEmpty) ? tmn : INFINITY;                             \
+                        }
+                        NG_WIDE_CHILD(0, x) NG_WIDE_CHILD(1, y) NG_WIDE_CHILD(2, z) NG_WIDE_CHILD(3, w)
+#undef NG_WIDE_CHILD
+                        // nearest first: a five-comparator network on (entry distance, link); misses carry +inf and end up last
+#define NG_WIDE_SWAP(A, B) if (key[B] < key[A]) { const float tk = key[A]; key[A] = key[B]; key[B] = tk; const int tl = link[A]; link[A] = link[B]; link[B] = tl; }
+                        NG_WIDE_SWAP(0, 1) NG_WIDE_SWAP(2, 3) NG_WIDE_SWAP(0, 2) NG_WIDE_SWAP(1, 3) NG_WIDE_SWAP(1, 2)
+#undef NG_WIDE_SWAP
+                        if (key[3] < INFINITY) push(link[3]);
+                        if (key[2] < INFINITY) push(link[2]);
+                        if (key[1] < INFINITY) push(link[1]);
+                        cur = key[0] < INFINITY ? link[0] : (sp > 0 ? pop() : kDone);
+                        if (cur < 0 && leaf == 0) {            // first leaf: postpone, keep descending
+                            leaf = cur;
+                            cur = sp > 0 ? pop() : kDone;
+                        }
+                    }
+                } else
                 if (cur >= 0 && cur != kDone) {
                     float4 n0, n1, n2; int cl, cr;
-                    if (QN) {
+                    if (QN == 1) {
                         const uint4 *qn = reinterpret_cast<const uint4 *>(nodes) + 2 * (size_t) cur;
                         const uint4 a = __ldg(qn), b = __ldg(qn + 1);
                         n0 = make_float4(qfield<false>(a.x), qfield<true>(a.x), qfield<false>(a.y), qfield<true>(a.y));

@@ -3,7 +3,7 @@ Accel::rayIntersect operator (nori_gpu_trace_device, rays resident in HBM, CUDA 
 primary rays, shadow rays towards the light and incoherent bounce rays, with the algorithmic bytes per
 ray (48 + 32 N_box + 36 N_tri, counted by the device BVH: nori_gpu_trace_count) against the measured
 HBM peak.   python scripts/bench_trace.py [c4|c1] [--layout 0|1] [--out profiles/trace_<cfg>.json]
---layout 1: NORI_ACCEL_QUANTISED (32-byte nodes); the algorithmic bytes stay those of SURVEY 8d (32 B per box test)."""
+--layout 1: NORI_ACCEL_QUANTISED (32-byte nodes), 2: NORI_ACCEL_WIDE4 (the tree collapsed to 4-wide nodes; N_box counts stay the binary tree's); the algorithmic bytes stay those of SURVEY 8d (32 B per box test)."""
 import json, os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -46,7 +46,7 @@ def main():
     v /= np.linalg.norm(v, axis=1, keepdims=True)
     bounce = np.concatenate([P, np.full((len(P), 1), 1e-4, np.float32), v, np.full((len(P), 1), np.inf, np.float32)], 1).astype(np.float32)
     hbm, src = peak()
-    res = {"config": cfg, "node_layout": "quantised 32 B" if layout else "float 64 B", "triangles": accel["n_triangles"], "accel": accel, "load_and_build_s": load_s, "hbm_peak_gbs": hbm, "peak_source": src, "rays": {}}
+    res = {"config": cfg, "node_layout": ["float 64 B", "quantised 32 B", "4-wide float 128 B"][layout], "triangles": accel["n_triangles"], "accel": accel, "load_and_build_s": load_s, "hbm_peak_gbs": hbm, "peak_source": src, "rays": {}}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     for name, rays, sh in (("primary_closest", primary, False), ("shadow_anyhit", shadow, True), ("bounce_closest", bounce, False)):
         n = len(rays)
