@@ -45,6 +45,18 @@ def main():
         if name in ("cbox_mis", "table_mis"):                                  # watertight ray-triangle mode
             eng.render(sample_first=0, sample_last=2, intersect_mode=1)
             eng.set_intersect_mode(1); eng.trace(rays); eng.trace(rays, shadow=True); eng.intersect(rays); eng.set_intersect_mode(0)
+        if name in ("cbox_mis", "table_mis"):                                  # 4-wide node layout; renders without the ray binning
+            eng.set_accel_layout(2); eng.render(sample_first=0, sample_last=2); eng.trace(rays); eng.trace(rays, shadow=True); eng.set_accel_layout(0)
+            eng.set_ray_binning(False); eng.render(sample_first=0, sample_last=2); eng.set_ray_binning(True)
+            eng.trace_static(rays); eng.trace_static(rays, shadow=True)
+        if name in ("cbox_mis", "table_mis", "veach_mis"):                     # path-graph tool: records, grid + kNN, scatter, MIS gather
+            from nori_b200.gpu import pathgraph_grid
+            v = eng.path_vertices(sample_first=0, sample_last=2)
+            hp = pathgraph_grid(v, 9, 35)
+            nb, knn, dknn, _ = eng.pathgraph_knn(v, hp)
+            eng.pathgraph_scatter(v, nb, knn, 2); eng.pathgraph_mis(v, nb, dknn, 2)         # dknn: rows longer than a warp
+            eng.pathgraph_filter(v, hp, 1); eng.pathgraph_filter(v, hp, 1, mode="mis")
+            print("  pathgraph", len(v), "vertices", flush=True)
         if name == "bunny_normals":
             eng.render(stream_mode=0, sample_first=0, sample_last=3)          # block-seeded stream
         pos = (rng.random((4000, 2)) * [w, h]).astype(np.float32)
