@@ -315,6 +315,20 @@ int nori_gpu_pathgraph_mis(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n
 #define NORI_PG_MIS 1
 int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
                               float *pdfmarginal, float *blur, float *mc, float ms[2]);
+/* The `pg` tool end to end on the scene's own paths (src/cluster.cpp:156-253 in its "knn" mode, minus the file I/O), everything
+ * on the device: the path vertices of the camera samples [sample_first, sample_last) of every pixel (nori_gpu_path_vertices; the
+ * 168-byte records never leave the device), their bounding box and the grid PathGraph::computeDimensions derives from it, k
+ * nearest neighbours, `iterations` passes of the scatter (NORI_PG_SCATTER) or the MIS gather (NORI_PG_MIS), and the images
+ * writeFullLight / writeIndirectLight / writeFullinit compose from each path's first vertex (src/cluster.cpp:23-107).
+ * images: 5 x height x width x 3 floats (HOST): full = eLd + mc, indirect = mc, pt = eLi - eLd, blur, init = eLd, all of the last
+ * pass, averaged over a pixel's samples in sample order (the reference keeps the last path of a pixel). */
+typedef struct {
+    uint64_t vertices;
+    float ms_vertices, ms_knn, ms_stage;    /* device time: records + bounding box, grid + search, scatter / gather + images */
+    int32_t dim[3];                         /* grid the search used */
+} NoriGpuPathGraphStats;
+int nori_gpu_pathgraph_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, int mode, int k, int iterations, float *images,
+                              NoriGpuPathGraphStats *stats);
 
 #ifdef __cplusplus
 }

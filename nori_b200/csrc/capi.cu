@@ -1061,13 +1061,9 @@ extern "C" int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc
     return NORI_GPU_OK;
 }
 
-extern "C" int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int n, const int32_t dim[3], int k, int dk, NoriGpuHashParams *out) {
-    if (!points || n <= 0 || stride < 12 || !out) return NORI_GPU_EINVAL;
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    for (int i = 0; i < n; ++i) {
-        float p[3]; memcpy(p, static_cast<const unsigned char *>(points) + (size_t) i * stride, 12);
-        for (int c = 0; c < 3; ++c) { lo[c] = std::min(lo[c], p[c]); hi[c] = std::max(hi[c], p[c]); }
-    }
+namespace {
+/// SPoints::BuildKNN's grid (shadingPoint.h:794-801) over the box [lo, hi] of n points; dim == NULL: PathGraph::computeDimensions.
+int pathgraphGridFromBox(const float lo[3], const float hi[3], int n, const int32_t dim[3], int k, int dk, NoriGpuHashParams *out) {
     int dm[3];
     if (dim) { dm[0] = dim[0]; dm[1] = dim[1]; dm[2] = dim[2]; }
     else {   // PathGraph::computeDimensions (src/pathgraph.cpp:40-50): about n cells for a cubic box, proportional to the extents
@@ -1084,6 +1080,17 @@ extern "C" int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int 
     }
     out->k = k; out->dk = dk;
     return NORI_GPU_OK;
+}
+}
+
+extern "C" int nori_gpu_pathgraph_grid(const void *points, uint64_t stride, int n, const int32_t dim[3], int k, int dk, NoriGpuHashParams *out) {
+    if (!points || n <= 0 || stride < 12 || !out) return NORI_GPU_EINVAL;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < n; ++i) {
+        float p[3]; memcpy(p, static_cast<const unsigned char *>(points) + (size_t) i * stride, 12);
+        for (int c = 0; c < 3; ++c) { lo[c] = std::min(lo[c], p[c]); hi[c] = std::max(hi[c], p[c]); }
+    }
+    return pathgraphGridFromBox(lo, hi, n, dim, k, dk, out);
 }
 
 extern "C" int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp,
@@ -1209,6 +1216,82 @@ extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const Nori
     if (ms) { cudaEventElapsedTime(&ms[0], e0, e1); ms[1] = msScatter; }
     unsigned line = 0;
     if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_filter: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
+
+extern "C" int nori_gpu_pathgraph_render(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, int mode, int k, int iterations, float *images,
+                                         NoriGpuPathGraphStats *stats) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(d && images, "pathgraph_render: bad arguments");
+    REQUIRE(mode == NORI_PG_SCATTER || mode == NORI_PG_MIS, "pathgraph_render: unknown mode");
+    REQUIRE(k >= 1 && k <= kPgMaxK && iterations >= 1 && iterations <= 64, "pathgraph_render: k in [1, 200], iterations in [1, 64]");
+    REQUIRE(ctx->haveBvh && ctx->haveCamera, "pathgraph_render: scene, camera and accel must be set first");
+    REQUIRE(d->sample_last > d->sample_first && d->sample_last <= 0x7fffffffu, "pathgraph_render: bad sample range");
+    REQUIRE(d->integrator == NORI_INT_PATH_MATS || d->integrator == NORI_INT_PATH_EMS || d->integrator == NORI_INT_PATH_MIS,
+            "pathgraph_render: the path graph is built from path_mats / path_ems / path_mis paths");
+    CK(cudaSetDevice(ctx->device));
+    const uint32_t spp = d->sample_last - d->sample_first;
+    const int nPixels = ctx->cam.width * ctx->cam.height;
+    const unsigned long long nPaths = (unsigned long long) nPixels * spp;
+    REQUIRE(nPaths < (1ull << 31), "pathgraph_render: more than 2^31 camera samples in one call");
+    RenderParams rp; memset(&rp, 0, sizeof(rp));
+    rp.integrator = d->integrator; rp.streamMode = NORI_STREAM_PER_SAMPLE; rp.sampleFirst = d->sample_first; rp.sampleCount = spp;
+    rp.rrStart = d->rr_start; rp.rrMax = d->rr_max; rp.maxDepth = d->max_depth;
+    DeviceScene sc = deviceScene(ctx); sc.isectMode = d->intersect_mode;
+    cudaStream_t st = ctx->stream;
+    cudaEvent_t ev[4];
+    for (auto &e : ev) CK(cudaEventCreate(&e));
+    struct Ev { cudaEvent_t *e; ~Ev() { for (int i = 0; i < 4; ++i) cudaEventDestroy(e[i]); } } evGuard{ev};
+    // 1. the paths' vertices, never leaving the device: count, scan, write
+    DevBuf<unsigned int> counts, bounds; DevBuf<unsigned long long> offsets;
+    CK(counts.alloc(nPaths)); CK(offsets.alloc(nPaths + 1)); CK(bounds.alloc(6));
+    CK(cudaEventRecord(ev[0], st));
+    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, nullptr, nullptr, st);
+    enqueueScanCounts(counts.p, nPaths, offsets.p, st);
+    unsigned long long total = 0;
+    CK(cudaMemcpyAsync(&total, offsets.p + nPaths, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    REQUIRE(total > 0, "pathgraph_render: no camera sample hit a surface");
+    REQUIRE(total <= 0x7fffffffull, "pathgraph_render: more than 2^31 path vertices; render fewer samples per call");
+    const int n = (int) total;
+    DevBuf<NoriGpuSPoint> recs; CK(recs.alloc(total));
+    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, offsets.p, recs.p, st);
+    // 2. grid as SPoints::BuildKNN / PathGraph::computeDimensions size it, from the records' bounding box
+    launchPathgraphBounds(recs.p, n, bounds.p, st);
+    unsigned int hb[6];
+    CK(cudaMemcpyAsync(hb, bounds.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ev[1], st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    float lo[3], hi[3];
+    for (int c = 0; c < 3; ++c) { lo[c] = pathgraphOrderedToFloat(hb[c]); hi[c] = pathgraphOrderedToFloat(hb[3 + c]); }
+    NoriGpuHashParams hp;
+    REQUIRE(pathgraphGridFromBox(lo, hi, n, nullptr, k, k, &hp) == NORI_GPU_OK, "pathgraph_render: degenerate vertex set");
+    PgParams P;
+    for (int c = 0; c < 3; ++c) { P.minb[c] = hp.minb[c]; P.cell[c] = hp.cellsize[c]; P.dim[c] = hp.dim[c]; }
+    const unsigned long long cells = (unsigned long long) hp.dim[0] * hp.dim[1] * hp.dim[2];
+    REQUIRE(cells < (1ull << 30), "pathgraph_render: more than 2^30 grid cells");
+    P.k = k; P.dk = k; P.maxK = k; P.nCells = (int) cells;
+    // 3. neighbours, 4. scatter or MIS gather, 5. images: all on the records where they lie
+    DevBuf<unsigned char> scratch, stage; DevBuf<int> nb, dk1, dk2; DevBuf<float> pm, db, dm, img;
+    CK(scratch.alloc(pgScratchBytes(n, P.nCells))); CK(nb.alloc((size_t) n * k)); CK(dk1.alloc(n)); CK(dk2.alloc(n));
+    if (!launchPathgraphKnn(recs.p, sizeof(NoriGpuSPoint), n, P, scratch.p, nb.p, k, dk1.p, dk2.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(ev[2], st));
+    CK(stage.alloc(mode == NORI_PG_MIS ? pgMisScratchBytes(n, k) : pgScatterScratchBytes(n))); CK(pm.alloc(n));
+    CK(db.alloc((size_t) iterations * 3 * n)); CK(dm.alloc((size_t) iterations * 3 * n)); CK(img.alloc((size_t) 5 * nPixels * 3));
+    if (mode == NORI_PG_MIS) { if (!launchPathgraphMis(recs.p, n, nb.p, k, dk1.p, iterations, stage.p, db.p, dm.p, st, ctx->err)) return NORI_GPU_EINVAL; }
+    else if (!launchPathgraphScatter(recs.p, n, nb.p, k, dk1.p, iterations, stage.p, pm.p, db.p, dm.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    launchPathgraphCompose(recs.p, offsets.p, counts.p, db.p + (size_t) (iterations - 1) * 3 * n, dm.p + (size_t) (iterations - 1) * 3 * n, nPixels, spp, img.p, st);
+    CK(cudaEventRecord(ev[3], st));
+    CK(cudaMemcpyAsync(images, img.p, (size_t) 5 * nPixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (stats) {
+        stats->vertices = total;
+        cudaEventElapsedTime(&stats->ms_vertices, ev[0], ev[1]); cudaEventElapsedTime(&stats->ms_knn, ev[1], ev[2]); cudaEventElapsedTime(&stats->ms_stage, ev[2], ev[3]);
+        for (int c = 0; c < 3; ++c) stats->dim[c] = hp.dim[c];
+    }
+    unsigned line = 0;
+    if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_render: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    if (const unsigned bad = pathgraphScatterChecks(&line)) { ctx->err = "pathgraph_render: device range check failed (" + std::to_string(bad) + " at pathgraph_scatter.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
     return NORI_GPU_OK;
 }
 

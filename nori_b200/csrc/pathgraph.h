@@ -30,6 +30,11 @@ size_t pgMisScratchBytes(int n, int rowInts);
 bool launchPathgraphMis(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
                         void *d_scratch, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
+/// Whole pipeline on the device (nori_gpu_pathgraph_render): bounding box of the records, image composition from first vertices.
+void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bounds6, cudaStream_t st);
+float pathgraphOrderedToFloat(unsigned int ordered);
+void launchPathgraphCompose(const NoriGpuSPoint *d_sps, const unsigned long long *d_offsets, const unsigned int *d_counts, const float *d_blur, const float *d_mc,
+                            int nPixels, unsigned int spp, float *d_images, cudaStream_t st);
 unsigned pathgraphScatterChecks(unsigned *line);
 
 } // namespace ng

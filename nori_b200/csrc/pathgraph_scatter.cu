@@ -15,6 +15,8 @@
 //   * the marginal sums are taken in a fixed order (lane l adds neighbours l, l + 32, ... in turn, then a butterfly over the
 //     lanes), so they do not depend on scheduling; the reference adds them in list order in one thread. The scatter sums are
 //     atomic in both: their order is not defined by either implementation.
+#include <algorithm>
+#include <cstring>
 #include "engine.h"
 #include "check.cuh"
 #include "pathgraph.h"
@@ -257,6 +259,56 @@ __global__ void k_pgValidate(const int *__restrict__ neighbors, int pitchInts, i
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st) {
     cudaMemsetAsync(d_flag, 0, sizeof(int), st);
     k_pgValidate<<<(unsigned) ((n + kPgWarps - 1) / kPgWarps), kPgWarps * 32, 0, st>>>(d_neighbors, pitchInts, rowInts, d_knn, n, d_flag);
+}
+
+namespace {
+
+/// Bounding box of the record positions (SPoints::BuildKNN reads it off the loaded set, shadingPoint.h:786-793): block-wise
+/// min / max, then one ordered-integer atomic per block and coordinate (floats compare like their sign-fixed bit patterns).
+__device__ __forceinline__ unsigned int pgOrdered(float f) { const unsigned int u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__global__ void __launch_bounds__(256) k_pgBounds(const NoriGpuSPoint *__restrict__ sps, int n, unsigned int *__restrict__ bounds /* lo.xyz (min), hi.xyz (max), ordered */) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        for (int c = 0; c < 3; ++c) { const float p = sps[i].pos[c]; lo[c] = fminf(lo[c], p); hi[c] = fmaxf(hi[c], p); }
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) { lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], d)); hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], d)); }
+        if ((threadIdx.x & 31) == 0) { atomicMin(bounds + c, pgOrdered(lo[c])); atomicMax(bounds + 3 + c, pgOrdered(hi[c])); }
+    }
+}
+
+/// The images the tool composes from each path's FIRST vertex (src/cluster.cpp:23-107): full = eLd + mc, indirect = mc, pt = eLi - eLd,
+/// blur, init = eLd, averaged over the pixel's samples in sample order (one thread per pixel: no atomics, a fixed order).
+/// offsets[g] / counts[g]: first record and number of records of camera sample g = pixel * spp + k (the vertex pass's own scan).
+__global__ void k_pgCompose(const NoriGpuSPoint *__restrict__ sps, const unsigned long long *__restrict__ offsets, const unsigned int *__restrict__ counts,
+                            const float *__restrict__ blur, const float *__restrict__ mc, int nPixels, unsigned int spp, float *__restrict__ images) {
+    const int pixel = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pixel >= nPixels) return;
+    float acc[5][3] = {};
+    const float inv = 1.0f / (float) spp;
+    for (unsigned int k = 0; k < spp; ++k) {
+        const unsigned long long g = (unsigned long long) pixel * spp + k;
+        if (!counts[g]) continue;
+        const unsigned long long i = offsets[g];
+        for (int c = 0; c < 3; ++c) {
+            const float eLd = sps[i].eLd[c], eLi = sps[i].eLi[c], m = mc[3 * i + c], b = blur[3 * i + c];
+            acc[0][c] += (eLd + m) * inv; acc[1][c] += m * inv; acc[2][c] += (eLi - eLd) * inv; acc[3][c] += b * inv; acc[4][c] += eLd * inv;
+        }
+    }
+    for (int im = 0; im < 5; ++im) for (int c = 0; c < 3; ++c) images[((size_t) im * nPixels + pixel) * 3 + c] = acc[im][c];
+}
+
+} // namespace
+
+void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bounds6, cudaStream_t st) {
+    const unsigned int init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    cudaMemcpyAsync(d_bounds6, init, sizeof(init), cudaMemcpyHostToDevice, st);
+    k_pgBounds<<<(unsigned) std::min((n + 255) / 256, 148 * 8), 256, 0, st>>>(d_sps, n, d_bounds6);
+}
+float pathgraphOrderedToFloat(unsigned int u) { const unsigned int b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; float f; memcpy(&f, &b, 4); return f; }
+void launchPathgraphCompose(const NoriGpuSPoint *d_sps, const unsigned long long *d_offsets, const unsigned int *d_counts, const float *d_blur, const float *d_mc,
+                            int nPixels, unsigned int spp, float *d_images, cudaStream_t st) {
+    k_pgCompose<<<(unsigned) ((nPixels + 127) / 128), 128, 0, st>>>(d_sps, d_offsets, d_counts, d_blur, d_mc, nPixels, spp, d_images);
 }
 
 size_t pgScatterScratchBytes(int n) {

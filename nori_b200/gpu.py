@@ -29,12 +29,16 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
 ]
 
 
 class NoriGpuError(RuntimeError):
     """Raised for every non-zero return of the C ABI (the C++ wrapper's NoriException)."""
+
+
+class PathGraphStats(C.Structure):
+    _fields_ = [("vertices", C.c_uint64), ("ms_vertices", C.c_float), ("ms_knn", C.c_float), ("ms_stage", C.c_float), ("dim", C.c_int32 * 3)]
 
 
 class MeshDesc(C.Structure):
@@ -138,6 +142,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_pathgraph_grid.argtypes = [vp, C.c_uint64, ip, vp, ip, ip, C.POINTER(HashParams)]
     L.nori_gpu_pathgraph_scatter.argtypes = [vp, vp, ip, vp, ip, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_filter.argtypes = [vp, ip, vp, ip, C.POINTER(HashParams), ip, vp, vp, vp, vp]
+    L.nori_gpu_pathgraph_render.argtypes = [vp, C.POINTER(RenderDesc), ip, ip, ip, vp, C.POINTER(PathGraphStats)]
     L.nori_gpu_pathgraph_mis.argtypes = [vp, vp, ip, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
     _lib = L
     return L
@@ -382,6 +387,15 @@ class Engine:
         pm = np.empty(n, np.float32); blur = np.empty((iterations, n, 3), np.float32); mc = np.empty((iterations, n, 3), np.float32); ms = C.c_float()
         self._ck(self.L.nori_gpu_pathgraph_scatter(self.h, _p(pts), n, _p(nb), nb.shape[1], _p(kn), int(iterations), _p(pm), _p(blur), _p(mc), C.byref(ms)))
         return pm, blur, mc, ms.value
+
+    def pathgraph_render(self, k: int, iterations: int, mode: str = "mis", integrator=None, sample_first=0, sample_last=1):
+        """The pg tool end to end on the device: {"full", "indirect", "pt", "blur", "init"} images (H, W, 3) + stats."""
+        d = self.render_desc(integrator, 1, sample_first, sample_last)
+        W, H = self._wh
+        img = np.empty((5, H, W, 3), np.float32); st = PathGraphStats()
+        self._ck(self.L.nori_gpu_pathgraph_render(self.h, C.byref(d), {"scatter": 0, "mis": 1}[mode], int(k), int(iterations), _p(img), C.byref(st)))
+        out = dict(zip(("full", "indirect", "pt", "blur", "init"), img))
+        return out, {"vertices": int(st.vertices), "ms_vertices": st.ms_vertices, "ms_knn": st.ms_knn, "ms_stage": st.ms_stage, "dim": list(st.dim)}
 
     def pathgraph_mis(self, points, neighbors, knn, iterations: int):
         """computeMISAllOnGPURecord (the pg tool's knn mode): SPoint records + the kNN rows -> (blur (it, n, 3), mc (it, n, 3), ms)."""

@@ -259,9 +259,8 @@ void loadCheckpoint(const std::string &path, ImageBlock &block, uint32_t &sample
 void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const uint32_t *sample, float *rgb, int device = 0);
 
 /// The fork's path-graph tool (`pg`, src/cluster.cpp:156-253, mode "knn") on the tracer's own paths instead of another renderer's
-/// dumps: path vertices of the camera samples [sampleFirst, sampleLast) of every pixel (nori_gpu_path_vertices), grid as
-/// PathGraph::computeDimensions sizes it (nori_gpu_pathgraph_grid), kNN + marginal densities + `iterations` scatter passes
-/// (nori_gpu_pathgraph_filter; mis = true: the MIS gather the tool's "knn" mode runs, computeMISAllOnGPURecord; false: the
+/// dumps, in ONE device call (nori_gpu_pathgraph_render): path vertices of the camera samples [sampleFirst, sampleLast) of every
+/// pixel, grid as PathGraph::computeDimensions sizes it, kNN + `iterations` passes (mis = true: the MIS gather the tool's "knn" mode runs, computeMISAllOnGPURecord; false: the
 /// scatter driver computeScatterAllOnGPURecord), then the images writeFullLight / writeIndirectLight / writeFullinit compose from each path's
 /// FIRST vertex (src/cluster.cpp:23-107): full = eLd + mc, indirect = mc, pt = eLi - eLd, blur, init = eLd, all of the last
 /// pass. With several samples per pixel the reference's loop keeps the last path of a pixel; here they are averaged.

@@ -341,41 +341,18 @@ PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t 
     if (k < 1 || iterations < 1) throw NoriException("pathGraphGpu: k and the number of iterations must be positive");
     nori_gpu_ctx *ctx = scene->gpu(device);
     const NoriGpuRenderDesc d = renderDesc(scene, sampleFirst, sampleLast);
-    const uint32_t spp = sampleLast - sampleFirst;
     const Vector2i size = scene->getCamera()->getOutputSize();
+    const size_t plane = (size_t) size.x * size.y * 3;
+    std::vector<float> images(5 * plane);
+    NoriGpuPathGraphStats st;
+    // records, grid, neighbours, scatter / gather and the five images in one call: nothing but the images leaves the device
+    check(ctx, nori_gpu_pathgraph_render(ctx, &d, mis ? NORI_PG_MIS : NORI_PG_SCATTER, k, iterations, images.data(), &st), "nori_gpu_pathgraph_render");
     PathGraphImages out;
-    auto t0 = std::chrono::steady_clock::now();
-    uint64_t n = 0;
-    check(ctx, nori_gpu_path_vertices(ctx, &d, nullptr, 0, &n), "nori_gpu_path_vertices");
-    if (n == 0) throw NoriException("pathGraphGpu: no camera sample hit a surface");
-    if (n > 0x7fffffffull) throw NoriException("pathGraphGpu: more than 2^31 path vertices; render fewer samples per call");
-    std::vector<NoriGpuSPoint> v((size_t) n);
-    check(ctx, nori_gpu_path_vertices(ctx, &d, v.data(), n, &n), "nori_gpu_path_vertices");
-    out.vertices = n;
-    out.msVertices = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    NoriGpuHashParams hp;
-    check(ctx, nori_gpu_pathgraph_grid(v.data(), sizeof(NoriGpuSPoint), (int) n, nullptr, k, k, &hp), "nori_gpu_pathgraph_grid");   // PathGraph::computeDimensions
-    std::vector<float> blur((size_t) iterations * 3 * n), mc((size_t) iterations * 3 * n);
-    float ms[2] = {0, 0};
-    check(ctx, nori_gpu_pathgraph_filter(ctx, mis ? NORI_PG_MIS : NORI_PG_SCATTER, v.data(), (int) n, &hp, iterations, nullptr, blur.data(), mc.data(), ms), "nori_gpu_pathgraph_filter");
-    out.msKnn = ms[0]; out.msScatter = ms[1];
-    Bitmap *imgs[5];
+    out.vertices = st.vertices; out.msVertices = st.ms_vertices; out.msKnn = st.ms_knn; out.msScatter = st.ms_stage;
     std::unique_ptr<Bitmap> *slots[5] = {&out.full, &out.indirect, &out.pt, &out.blur, &out.init};
-    for (int i = 0; i < 5; ++i) { slots[i]->reset(new Bitmap(size.x, size.y)); imgs[i] = slots[i]->get(); }
-    const float *lastMc = mc.data() + (size_t) (iterations - 1) * 3 * n, *lastBlur = blur.data() + (size_t) (iterations - 1) * 3 * n;
-    const float inv = 1.0f / (float) spp;
-    for (uint64_t i = 0; i < n; ++i) {
-        if (i > 0 && v[i - 1].groupIdx == v[i].groupIdx) continue;          // first vertex of each path only
-        const uint32_t pixel = (uint32_t) v[i].groupIdx / spp;
-        if (pixel >= (uint32_t) (size.x * size.y)) throw NoriException("pathGraphGpu: vertex record outside the frame");
-        for (int c = 0; c < 3; ++c) {
-            const float eLd = v[i].eLd[c], eLi = v[i].eLi[c], m = lastMc[3 * i + c], b = lastBlur[3 * i + c];
-            imgs[0]->data()[3 * (size_t) pixel + c] += (eLd + m) * inv;
-            imgs[1]->data()[3 * (size_t) pixel + c] += m * inv;
-            imgs[2]->data()[3 * (size_t) pixel + c] += (eLi - eLd) * inv;
-            imgs[3]->data()[3 * (size_t) pixel + c] += b * inv;
-            imgs[4]->data()[3 * (size_t) pixel + c] += eLd * inv;
-        }
+    for (int i = 0; i < 5; ++i) {
+        slots[i]->reset(new Bitmap(size.x, size.y));
+        std::copy(images.begin() + (std::ptrdiff_t) (i * plane), images.begin() + (std::ptrdiff_t) ((i + 1) * plane), (*slots[i])->data());
     }
     return out;
 }

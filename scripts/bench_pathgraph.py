@@ -44,6 +44,14 @@ def scatter_leg(spp, k, iterations):
                          "filter_call_wall_ms": filter_wall * 1e3, "filter_device_ms": [float(fms[0]), float(fms[1])],
                          "filter": "nori_gpu_pathgraph_filter: kNN + scatter in one call from the host records (H2D of 168 B per vertex, rows never leave the device, D2H of the result rows)",
                          "timing": "ms_device: CUDA events around pack + marginal + iterations x (scatter, update, lastRun), records resident; ms_call_wall: the whole nori_gpu_pathgraph_scatter call from host buffers (H2D of records and rows, D2H of all result rows)"}}
+    t0 = time.perf_counter(); img, rst = e.pathgraph_render(k, iterations, mode="mis", sample_first=0, sample_last=spp); t_first = time.perf_counter() - t0
+    t0 = time.perf_counter(); img, rst = e.pathgraph_render(k, iterations, mode="mis", sample_first=0, sample_last=spp); t_render = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    v2 = e.path_vertices(sample_first=0, sample_last=spp); hp2 = pathgraph_grid(v2, k, k); e.pathgraph_filter(v2, hp2, iterations, mode="mis")
+    t_staged = time.perf_counter() - t0
+    out["end_to_end"] = {"what": "the pg tool's knn mode from the loaded scene to the five images on the host (MIS gather)",
+                         "pathgraph_render_wall_ms": t_render * 1e3, "device_ms": [rst["ms_vertices"], rst["ms_knn"], rst["ms_stage"]],
+                         "staged_calls_wall_ms": t_staged * 1e3, "staged": "nori_gpu_path_vertices (records to the host) + nori_gpu_pathgraph_grid + nori_gpu_pathgraph_filter (records back to the device, result rows to the host)"}
     out["mis"] = {"what": "computeMISAllOnGPURecord (the pg tool's knn mode): pdfsum (k^2 evaluations per vertex) + iterations x (gather, update, lastRun)",
                   "nori_b200_ms_device": mis_ms, "Gevals_per_s_device": (float((knn.astype(np.float64) ** 2).sum()) + float(knn.sum()) * iterations) / mis_ms / 1e6}
     if have_refcuda():

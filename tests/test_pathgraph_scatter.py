@@ -304,6 +304,45 @@ def test_gpu_filter_equals_knn_then_scatter(gpu_scene, scenes):
 
 
 @pytest.mark.gpu
+def test_gpu_pathgraph_render_equals_the_stages_one_by_one(gpu_scene, scenes):
+    """nori_gpu_pathgraph_render keeps records, rows and results on the device and returns the five images only: the same images
+    as composing them on the host (src/cluster.cpp:23-107) from nori_gpu_path_vertices + nori_gpu_pathgraph_filter, to the bit in
+    MIS mode (no atomics anywhere), to rounding in the blurred image of scatter mode; two samples per pixel are averaged in
+    sample order."""
+    from nori_b200.gpu import pathgraph_grid
+    e = gpu_scene("veach_mis"); s = scenes("veach_mis")
+    W, H, spp, k = 192, 128, 2, 10
+    e.set_camera(s.sample_to_camera, s.camera_to_world, W, H, s.near_clip, s.far_clip)
+    try:
+        v = e.path_vertices(sample_first=0, sample_last=spp)
+        hp = pathgraph_grid(v, k, k)
+        for mode in ("mis", "scatter"):
+            _, blur, mc, _ = e.pathgraph_filter(v, hp, 2, mode=mode)
+            img, st = e.pathgraph_render(k, 2, mode=mode, sample_first=0, sample_last=spp)
+            assert st["vertices"] == len(v) and st["dim"] == list(hp.dim) and st["ms_knn"] > 0
+            first = np.nonzero(np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]]))[0]
+            g = v["groupIdx"][first]
+            def image(rows):
+                out = np.zeros((H * W, 3), np.float32)
+                for kk in range(spp):                       # sample order, float32 accumulation as the kernel's
+                    sel = g % spp == kk
+                    out[g[sel] // spp] += rows[first[sel]] * np.float32(1.0 / spp)
+                return out.reshape(H, W, 3)
+            np.testing.assert_array_equal(img["init"], image(v["eLd"]))
+            np.testing.assert_array_equal(img["pt"], image(v["eLi"] - v["eLd"]))
+            if mode == "mis":
+                np.testing.assert_array_equal(img["indirect"], image(mc[1]))
+                np.testing.assert_array_equal(img["blur"], image(blur[1]))
+                np.testing.assert_array_equal(img["full"], image(v["eLd"] + mc[1]))
+            else:
+                close_rows(img["blur"].reshape(-1, 3), image(blur[1]).reshape(-1, 3), RTOL_SUM, "blur image")
+                close_rows(img["indirect"].reshape(-1, 3), image(mc[1]).reshape(-1, 3), RTOL_SUM, "indirect image")
+            assert img["full"].mean() > 0 and np.isfinite(img["full"]).all()
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+
+
+@pytest.mark.gpu
 def test_gpu_scatter_rejects_bad_rows(engine):
     z = np.load(REF_NPZ)
     s = records(z["sc_sps"])[:64].copy(); s["nidx"][63] = 0
