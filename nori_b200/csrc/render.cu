@@ -472,6 +472,12 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
 ///     the shadow kernel adds the light sample there (kShadowToRecord); only what the record
 ///     cannot express (value = T * L, late samples) parks the slot until the next iteration.
 /// One atomic per CTA each for: sample indices (twice), shadow queue space, finished count.
+#ifndef NORI_SHADE_PREFETCH
+#define NORI_SHADE_PREFETCH 4
+#endif
+#ifndef NORI_SHADE_PREFETCH_AHEAD
+#define NORI_SHADE_PREFETCH_AHEAD 592       // CTAs: one wave of 4 x 148 (296 and 1184 measure the same)
+#endif
 #ifndef NORI_SHADE_THREADS_PER_SM
 #define NORI_SHADE_THREADS_PER_SM 1024      // 64 registers per thread
 #endif
@@ -496,9 +502,47 @@ __global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeReg
     // ---- CTA-local counting sort by what the slot needs -----------------------------------
     int key0 = kNumKeys;
     {
+#if NORI_SHADE_PREFETCH >= 4      // the first loads of a CTA that starts a few waves later: into L2
+        {
+            const size_t ahead = (size_t) blockBase + tid + (size_t) NORI_SHADE_PREFETCH_AHEAD * NT;
+            if (ahead < pool.capacity) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(pool.state + ahead));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(pool.hit + ahead));
+#if NORI_SHADE_PREFETCH >= 5      // and what its shade step reads
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(pool.rayD + ahead));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(pool.thr + ahead));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(pool.rad + ahead));
+#endif
+            }
+        }
+#endif
         const uint32_t flags0 = pool.state[blockBase + tid].w;
         const uint32_t gid = __float_as_uint(pool.hit[blockBase + tid].w);
-        if (flags0 & kFlagAlive) key0 = gid == kNoHit ? kKeyMiss : sc.meshes[__ldg(&sc.tris[gid].w)].bsdfType;
+#ifndef NORI_SHADE_NO_PREFETCH
+        // What the shade step reads of this slot after the sort (by ANOTHER thread of this CTA, two barriers from here): asked for
+        // now, so that the DRAM round trip runs under the key's dependent loads and the sort instead of after them.
+        if (flags0 & kFlagAlive) {
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pool.rayD + blockBase + tid));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pool.thr + blockBase + tid));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pool.rad + blockBase + tid));
+#if NORI_SHADE_PREFETCH >= 2      // + what a camera sample reads when it ends (a third of the live slots per pass)
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pool.info + blockBase + tid));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pool.pos + blockBase + tid));
+#endif
+        }
+#endif
+        if (flags0 & kFlagAlive) {
+            if (gid == kNoHit) key0 = kKeyMiss;
+            else {
+                const uint4 tri = __ldg(sc.tris + gid);
+#if NORI_SHADE_PREFETCH == 3      // + the triangle's vertices (fillHit): measured, much slower (profiles/r02_notes.md)
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.vpos + tri.x));
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.vpos + tri.y));
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.vpos + tri.z));
+#endif
+                key0 = sc.meshes[tri.w].bsdfType;
+            }
+        }
     }
     unsigned rank = 0;
 #pragma unroll
