@@ -1353,7 +1353,7 @@ __global__ void k_traceStaticReset(TraceStaticScratch *s) { s->cursor = 0u; }
 template <bool SHADOW, bool WT>
 __global__ void __launch_bounds__(128, 10) k_traceStatic(DeviceScene sc, TraceStaticScratch *s, int n) {
     StaticRayIO io; io.s = s; io.n = (uint32_t) n;
-    tracePersistent<SHADOW, WT, false>(sc.nodes, sc.leafTris, (uint32_t) n, &s->cursor, io, kFetchThreshold, QGrid());
+    tracePersistent<SHADOW, WT, false>(sc.nodes, sc.leafTris, (uint32_t) n, &s->cursor, io, kTraceTuning, QGrid());
 }
 
 /// Global triangle id -> (mesh, mesh-local index) and (t, u, v) as the separate arrays the caller receives.

@@ -47,7 +47,7 @@ template <bool SHADOW, bool WT, int QN = 0>
 __global__ void __launch_bounds__(128, QN == 2 ? 8 : 10) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
     RayArrayIO io; io.rays = rays; io.hits = hits; io.n = (uint32_t) n;
     const QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]};
-    tracePersistent<SHADOW, WT, QN>(QN == 2 ? sc.wnodes : (QN == 1 ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes), sc.leafTris, (uint32_t) n, cursor, io, kFetchThreshold, g);
+    tracePersistent<SHADOW, WT, QN>(QN == 2 ? sc.wnodes : (QN == 1 ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes), sc.leafTris, (uint32_t) n, cursor, io, kTraceTuning, g);
 }
 
 void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned int *cursor, cudaStream_t st) {

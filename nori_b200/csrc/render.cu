@@ -1380,12 +1380,14 @@ static unsigned persistentGrid() {
 struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; bool overlapSplat; };
 static const Tune &tune() {
     static Tune t = [] {
-        Tune v = {kFetchThreshold, kFetchThreshold, 10u, true};     // 10 CTAs of 128 threads per SM (48 registers): best since the nodes are fetched with 256-bit loads
+        Tune v = {kTraceTuning, kTraceTuning, 10u, true};     // 10 CTAs of 128 threads per SM (48 registers): best since the nodes are fetched with 256-bit loads
 #ifdef NORI_GPU_SWEEP
         if (getenv("NORI_GPU_NO_OVERLAP")) v.overlapSplat = false;
-        if (const char *s = getenv("NORI_GPU_FETCH")) v.fetchClosest = v.fetchShadow = atoi(s);
-        if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = atoi(s);
-        if (const char *s = getenv("NORI_GPU_NODE_EXIT")) { v.fetchClosest |= atoi(s) << 8; v.fetchShadow |= atoi(s) << 8; }
+        if (const char *s = getenv("NORI_GPU_FETCH")) { v.fetchClosest = (v.fetchClosest & ~0xff) | atoi(s); v.fetchShadow = (v.fetchShadow & ~0xff) | atoi(s); }
+        if (const char *s = getenv("NORI_GPU_FETCH_SHADOW")) v.fetchShadow = (v.fetchShadow & ~0xff) | atoi(s);
+        if (const char *s = getenv("NORI_GPU_NODE_EXIT")) { v.fetchClosest = (v.fetchClosest & 0xff) | atoi(s) << 8; v.fetchShadow = (v.fetchShadow & 0xff) | atoi(s) << 8; }
+        if (const char *s = getenv("NORI_GPU_NODE_EXIT_CLOSEST")) v.fetchClosest = (v.fetchClosest & 0xff) | atoi(s) << 8;
+        if (const char *s = getenv("NORI_GPU_NODE_EXIT_SHADOW")) v.fetchShadow = (v.fetchShadow & 0xff) | atoi(s) << 8;
         if (const char *s = getenv("NORI_GPU_TRACE_CTAS")) v.ctasPerSm = (unsigned) atoi(s);
 #endif
         return v;

@@ -19,6 +19,10 @@ namespace ng {
 #define NORI_TRACE_SHARED_STACK 0
 #endif
 constexpr int kFetchThreshold = 20;   // default: refill when fewer than this many lanes still traverse
+// Leave the inner-node loop for the postponed leaves as soon as at most this many lanes still descend (0: only when none does).
+// Measured with binned rays (profiles/r02_notes.md): cbox closest-hit stage 80.4 -> 77.8 ms, any-hit 34.9 -> 30.9 at 512 spp.
+constexpr int kNodeExit = 3;
+constexpr int kTraceTuning = kFetchThreshold | (kNodeExit << 8);     // the `tuning` argument of tracePersistent
 
 /// Grid of the quantised node layout (bvh.h: quantiseNodes): coordinate = base + m * ext, m in [1, 2).
 struct QGrid { float bx, by, bz, ex, ey, ez; };
@@ -35,7 +39,7 @@ template <class IO> struct IoIndirect { static constexpr bool value = false; };
 /// same fused multiply-add per plane with per-ray constants that fold the grid in: t = m * (ext / d) + (base - o) / d.
 template <bool ANY_HIT, bool WT = false, int QN = 0, class IO>
 NG_D void tracePersistent(const float4 *__restrict__ nodes, const float4 *__restrict__ leafTris, uint32_t nRays,
-                          unsigned int *workCounter, IO &io, int tuning = kFetchThreshold, QGrid grid = QGrid()) {
+                          unsigned int *workCounter, IO &io, int tuning = kTraceTuning, QGrid grid = QGrid()) {
     const int fetchThreshold = tuning & 0xff;                  // refill when fewer lanes than this still hold a ray
     const int nodeExit = (tuning >> 8) & 0xff;                 // leave the node loop when fewer lanes than this still descend
     const unsigned lane = threadIdx.x & 31u;
