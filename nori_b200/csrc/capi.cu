@@ -36,6 +36,7 @@ struct nori_gpu_ctx {
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 23;   // 8 Mi path slots (sweep: profiles/r01_pipeline.md)
+    bool poolAuto = true;                       // no nori_gpu_set_pool_size yet: renders of >= 2^28 camera samples take 16 Mi slots (profiles/r02_notes.md)
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirrors: two (one per batch in flight)
     // host -> device staging for large pageable arrays (stagedCopy): kUploadWorkers host threads x 2 pinned buffers each (sweep on the GPU box, C4 240 MB: 4 x 8 MB 19.3 ms, 8 x 4 MB 13.4 ms, 8 x 8 15.8, 12 x 4 14.4, 8 x 2 15.1, 16 x 2 18.3; plain pageable copies 26 ms)
 #ifndef NORI_UPLOAD_WORKERS
@@ -210,7 +211,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     }
     memset(&ctx->cam, 0, sizeof(ctx->cam)); memset(&ctx->filter, 0, sizeof(ctx->filter)); memset(&ctx->pool, 0, sizeof(ctx->pool));
 #ifdef NORI_GPU_SWEEP   // parameter sweeps (build_variant): the default build reads no tuning from the environment
-    if (const char *s = getenv("NORI_GPU_POOL")) ctx->poolSize = std::max(256u, (uint32_t) strtoul(s, nullptr, 10) / 256u * 256u);
+    if (const char *s = getenv("NORI_GPU_POOL")) { ctx->poolSize = std::max(256u, (uint32_t) strtoul(s, nullptr, 10) / 256u * 256u); ctx->poolAuto = false; }
     if (const char *s = getenv("NORI_GPU_PLOC_RADIUS")) ctx->bvhParams.plocRadius = atoi(s);
     if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
     if (const char *s = getenv("NORI_GPU_ROTATIONS")) ctx->bvhParams.rotationPasses = atoi(s);
@@ -252,7 +253,7 @@ int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on) { if (!ctx) return NORI_GP
 int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(n >= 256, "pool size must be >= 256");
-    ctx->poolSize = n / 256u * 256u;
+    ctx->poolSize = n / 256u * 256u; ctx->poolAuto = false;
     return NORI_GPU_OK;
 }
 
@@ -428,10 +429,12 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         return NORI_GPU_EUNSUPPORTED;
     }
     CK(cudaSetDevice(ctx->device));
+    const int W = ctx->cam.width, H = ctx->cam.height;
+    // Long renders amortise ramp-up and tail over more iterations and gain from a larger wavefront (1024 spp: -2 %), short ones lose (128 spp: +13 %)
+    if (ctx->poolAuto) ctx->poolSize = (!list && (uint64_t) W * H * (d->sample_last - d->sample_first) >= (1ull << 28)) ? (1u << 24) : (1u << 23);
     if (int r = ensurePool(ctx)) return r;
     if (int r = ensureBlock(ctx)) return r;
     cudaStream_t st = ctx->stream;
-    const int W = ctx->cam.width, H = ctx->cam.height;
 
     RenderParams rp; memset(&rp, 0, sizeof(rp));
     rp.integrator = d->integrator; rp.streamMode = d->stream_mode;

@@ -44,7 +44,7 @@ struct RayArrayIO {
     }
 };
 template <bool SHADOW, bool WT, int QN = 0>
-__global__ void __launch_bounds__(128, QN == 2 ? 8 : 10) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
+__global__ void __launch_bounds__(128, QN == 2 ? 8 : (SHADOW ? 10 : 9)) k_tracePersistent(DeviceScene sc, const float4 *__restrict__ rays, int n, float4 *__restrict__ hits, unsigned int *cursor) {
     RayArrayIO io; io.rays = rays; io.hits = hits; io.n = (uint32_t) n;
     const QGrid g = {sc.qBase[0], sc.qBase[1], sc.qBase[2], sc.qExt[0], sc.qExt[1], sc.qExt[2]};
     tracePersistent<SHADOW, WT, QN>(QN == 2 ? sc.wnodes : (QN == 1 ? reinterpret_cast<const float4 *>(sc.qnodes) : sc.nodes), sc.leafTris, (uint32_t) n, cursor, io, kTraceTuning, g);
@@ -66,8 +66,9 @@ void launchTrace(const DeviceScene &sc, const float4 *rays, int n, bool shadow, 
         else k_tracePersistent<false, false, 2><<<grid * 8u / 10u, 128, 0, st>>>(sc, rays, n, hits, cursor);
         return;
     }
+    // closest hit: 9 resident CTAs per SM (56 registers), any hit: 10 (48), as the renderer's kernels
     if (shadow) { if (wt) k_tracePersistent<true, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); else k_tracePersistent<true, false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); }
-    else { if (wt) k_tracePersistent<false, true><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); else k_tracePersistent<false, false><<<grid, 128, 0, st>>>(sc, rays, n, hits, cursor); }
+    else { if (wt) k_tracePersistent<false, true><<<grid * 9u / 10u, 128, 0, st>>>(sc, rays, n, hits, cursor); else k_tracePersistent<false, false><<<grid * 9u / 10u, 128, 0, st>>>(sc, rays, n, hits, cursor); }
 }
 void launchTraceCount(const DeviceScene &sc, const float4 *rays, int n, bool shadow, float4 *hits, unsigned long long *counts2, cudaStream_t st) {
     if (n <= 0) return;

@@ -1377,10 +1377,11 @@ static unsigned persistentGrid() {
 }
 
 /// Tunables of the traversal kernels (environment overrides exist only in -DNORI_GPU_SWEEP builds: build_variant).
-struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm; bool overlapSplat; };
+struct Tune { int fetchClosest, fetchShadow; unsigned ctasPerSm, ctasClosest; bool overlapSplat; };
 static const Tune &tune() {
     static Tune t = [] {
-        Tune v = {kTraceTuning, kTraceTuning, 10u, true};     // 10 CTAs of 128 threads per SM (48 registers): best since the nodes are fetched with 256-bit loads
+        // any-hit: 10 CTAs of 128 threads per SM (48 registers); closest-hit: 9 (56 registers) since the rays are binned (75.4 vs 77.9 ms at 512 spp)
+        Tune v = {kTraceTuning, kTraceTuning, 10u, 9u, true};
 #ifdef NORI_GPU_SWEEP
         if (getenv("NORI_GPU_NO_OVERLAP")) v.overlapSplat = false;
         if (const char *s = getenv("NORI_GPU_FETCH")) { v.fetchClosest = (v.fetchClosest & ~0xff) | atoi(s); v.fetchShadow = (v.fetchShadow & ~0xff) | atoi(s); }
@@ -1388,7 +1389,8 @@ static const Tune &tune() {
         if (const char *s = getenv("NORI_GPU_NODE_EXIT")) { v.fetchClosest = (v.fetchClosest & 0xff) | atoi(s) << 8; v.fetchShadow = (v.fetchShadow & 0xff) | atoi(s) << 8; }
         if (const char *s = getenv("NORI_GPU_NODE_EXIT_CLOSEST")) v.fetchClosest = (v.fetchClosest & 0xff) | atoi(s) << 8;
         if (const char *s = getenv("NORI_GPU_NODE_EXIT_SHADOW")) v.fetchShadow = (v.fetchShadow & 0xff) | atoi(s) << 8;
-        if (const char *s = getenv("NORI_GPU_TRACE_CTAS")) v.ctasPerSm = (unsigned) atoi(s);
+        if (const char *s = getenv("NORI_GPU_TRACE_CTAS")) v.ctasPerSm = v.ctasClosest = (unsigned) atoi(s);
+        if (const char *s = getenv("NORI_GPU_TRACE_CTAS_CLOSEST")) v.ctasClosest = (unsigned) atoi(s);
 #endif
         return v;
     }();
@@ -1431,7 +1433,7 @@ int enqueueIteration(const DeviceScene &sc, const Pool &pool, const RenderParams
         ++launches;
     }
     {
-        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes || sc.wnodes) ? 8u : tune().ctasPerSm, g = persistentGrid() * b / 8u;
+        const unsigned b = (sc.isectMode == NORI_ISECT_WATERTIGHT || sc.qnodes || sc.wnodes) ? 8u : tune().ctasClosest, g = persistentGrid() * b / 8u;
         const bool overlap = splat && tune().overlapSplat;
         if (sc.isectMode == NORI_ISECT_WATERTIGHT) launchOverlapped(k_traceClosest<8, true>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
         else if (sc.qnodes) launchOverlapped(k_traceClosest<8, false, 1>, g, 128, st, overlap, sc, pool, c, tune().fetchClosest);
