@@ -36,7 +36,7 @@ struct nori_gpu_ctx {
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 23;   // 8 Mi path slots (sweep: profiles/r01_pipeline.md)
-    bool poolAuto = true;                       // no nori_gpu_set_pool_size yet: renders of >= 2^28 camera samples take 16 Mi slots (profiles/r02_notes.md)
+    bool poolAuto = true;                       // no nori_gpu_set_pool_size yet: renders of >= 3 * 2^26 (201 M) camera samples take 16 Mi slots (profiles/r02_notes.md)
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirrors: two (one per batch in flight)
     // host -> device staging for large pageable arrays (stagedCopy): kUploadWorkers host threads x 2 pinned buffers each (sweep on the GPU box, C4 240 MB: 4 x 8 MB 19.3 ms, 8 x 4 MB 13.4 ms, 8 x 8 15.8, 12 x 4 14.4, 8 x 2 15.1, 16 x 2 18.3; plain pageable copies 26 ms)
 #ifndef NORI_UPLOAD_WORKERS
@@ -430,8 +430,8 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     }
     CK(cudaSetDevice(ctx->device));
     const int W = ctx->cam.width, H = ctx->cam.height;
-    // Long renders amortise ramp-up and tail over more iterations and gain from a larger wavefront (1024 spp: -2 %), short ones lose (128 spp: +13 %)
-    if (ctx->poolAuto) ctx->poolSize = (!list && (uint64_t) W * H * (d->sample_last - d->sample_first) >= (1ull << 28)) ? (1u << 24) : (1u << 23);
+    // Long renders amortise ramp-up and tail over more iterations and gain from a larger wavefront (1024 spp: -2 %), short ones lose (128 spp: +13 %); 800x600: break-even between 256 and 512 spp
+    if (ctx->poolAuto) ctx->poolSize = (!list && (uint64_t) W * H * (d->sample_last - d->sample_first) >= (3ull << 26)) ? (1u << 24) : (1u << 23);
     if (int r = ensurePool(ctx)) return r;
     if (int r = ensureBlock(ctx)) return r;
     cudaStream_t st = ctx->stream;
