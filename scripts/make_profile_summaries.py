@@ -59,7 +59,7 @@ def kernels():
     per = collections.OrderedDict()
     for d in data: per.setdefault(short(d[ix["Kernel Name"]]), []).append(d)
     md = ["# %s: `ncu --set full` counters (per launch, averaged over the captured launches)" % tag, "",
-          "Command: `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu --no-configs`, `-k regex:k_trace|k_shade|k_splatPixel -s 60 -c 8`, cbox path_mis, 8 Mi path slots", "(about 5.4 M live rays per launch).", ""]
+          "Command: `python bench.py --steps 1 --warmup 3 --spp 128 --no-cpu --no-configs`, `-k regex:k_trace|k_shade|k_splatPixel|k_bin -s 70 -c 14` (r01 / r02: without k_bin, `-s 60 -c 8`), cbox path_mis, 8 Mi path slots (128 spp: below the 16 Mi rule)", "(about 5.4 M live rays per launch).", ""]
     names = list(per)
     md += ["| counter | " + " | ".join("`%s`" % n for n in names) + " |", "|---|" + "---:|" * len(names)]
     table = {}
