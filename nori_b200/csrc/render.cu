@@ -360,11 +360,17 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
     return true;
 }
 
+#ifndef NORI_SHADOW_PREFETCH
+#define NORI_SHADOW_PREFETCH 8192      // any-hit stage 29.06 -> 28.55 ms at 512 spp (65 536: the same); 0 = off
+#endif
 constexpr uint32_t kShadowToRecord = 0x80000000u;          // shadow-queue target is a sample record, not a path slot
 struct ShadowIO {
     Pool pool; float4 *recA; float *recB; size_t recCount;
     __device__ __forceinline__ bool load(uint32_t i, V3 &o, V3 &d, float &mint, float &maxt) const {
         NG_CHECK(i < pool.capacity);
+#if NORI_SHADOW_PREFETCH > 0      // the queue is read front to back: the entry a few thousand places on goes to L2 now
+        if (i + NORI_SHADOW_PREFETCH < pool.capacity) asm volatile("prefetch.global.L2 [%0];" :: "l"(pool.shadow + 3 * (size_t) (i + NORI_SHADOW_PREFETCH)));
+#endif
         const float4 a = pool.shadow[3 * (size_t) i], b = pool.shadow[3 * (size_t) i + 1];
         o = mk(a.x, a.y, a.z); d = mk(b.x, b.y, b.z); mint = kEpsilon; maxt = a.w;
         return true;
