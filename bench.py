@@ -376,8 +376,8 @@ def run_gpu(args):
         "config": {"workload": f"cbox path_mis 800x600 {spp}spp per GPU (BASELINE configs[1], C2)", "scene": SCENE, "triangles": scene.n_triangles,
                    "spp_per_gpu": spp, "sampler": "pcg32 per-sample streams", "partition": "sample-index ranges, one NCCL reduce of the ImageBlock per step",
                    "l2": "256 MiB flush buffer written between steps; path pool + sample records (> 400 MB) exceed L2, BVH+geometry (0.25 MB) are cache-resident by nature of the scene",
-                   "pool_paths": args.pool or (1 << 24 if scene.width * scene.height * spp >= 3 << 26 else 1 << 23),
-                   "pool_rule": "library default: 16 Mi path slots for renders of >= 3 * 2^26 camera samples, 8 Mi below (nori_gpu_set_pool_size overrides)", "accel": accel},
+                   "pool_paths": args.pool or (1 << 24 if scene.width * scene.height * spp >= 3 << 26 else min(1 << 23, max(1 << 21, scene.width * scene.height * spp // 3 // 256 * 256))),
+                   "pool_rule": "library default: 16 Mi path slots for renders of >= 3 * 2^26 camera samples, below that a third of the samples within [2 Mi, 8 Mi] (nori_gpu_set_pool_size overrides)", "accel": accel},
         "e2e": {"value": samples_per_step / (e2e_ms / 1e3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "includes": "scene upload, accel build, render, NCCL reduce, ImageBlock download"},
         "gpu_launches": int(tot["kernel_launches"]),

@@ -157,8 +157,9 @@ int nori_gpu_reduce_blocks(nori_gpu_ctx *const *ctxs, int n, int root);
 /* Number of CUDA devices visible to the library (0 without a driver). */
 int nori_gpu_device_count(void);
 int nori_gpu_set_profiling(nori_gpu_ctx *ctx, int on);   /* per-stage CUDA-event timing (serialises stages) */
-/* Path slots of the wavefront (a multiple of 256). Without this call the library picks 8 Mi, or 16 Mi for renders of at least 3 * 2^26
- * (201 M) camera samples (long renders gain from the larger wavefront, short ones lose to its ramp-up and tail). */
+/* Path slots of the wavefront (a multiple of 256). Without this call the library sizes the pool per render: a third of the render's
+ * camera samples, at least 2 Mi and at most 8 Mi slots, and 16 Mi for renders of at least 3 * 2^26 (201 M) camera samples (long renders
+ * gain from the larger wavefront, short ones lose to its ramp-up and tail). */
 int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n_paths);
 /* Ray binning of the wavefront renderer (default on): after every shade pass the path slots are counting-sorted by
  * (origin cell of the scene box, two direction signs) and the next closest-hit pass walks them in that order, so that the

@@ -36,7 +36,7 @@ struct nori_gpu_ctx {
     float *d_block = nullptr; size_t blockFloats = 0;
     // wavefront pool
     Pool pool; bool havePool = false; uint32_t poolSize = 1u << 23;   // 8 Mi path slots (sweep: profiles/r01_pipeline.md)
-    bool poolAuto = true;                       // no nori_gpu_set_pool_size yet: renders of >= 3 * 2^26 (201 M) camera samples take 16 Mi slots (profiles/r02_notes.md)
+    bool poolAuto = true;                       // no nori_gpu_set_pool_size yet: renders of >= 3 * 2^26 (201 M) camera samples take 16 Mi slots, short ones a third of their samples (2 Mi .. 8 Mi): profiles/r02_notes.md
     Counters *d_counters = nullptr; Counters *h_counters = nullptr;   // pinned mirrors: two (one per batch in flight)
     // host -> device staging for large pageable arrays (stagedCopy): kUploadWorkers host threads x 2 pinned buffers each (sweep on the GPU box, C4 240 MB: 4 x 8 MB 19.3 ms, 8 x 4 MB 13.4 ms, 8 x 8 15.8, 12 x 4 14.4, 8 x 2 15.1, 16 x 2 18.3; plain pageable copies 26 ms)
 #ifndef NORI_UPLOAD_WORKERS
@@ -430,8 +430,15 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
     }
     CK(cudaSetDevice(ctx->device));
     const int W = ctx->cam.width, H = ctx->cam.height;
-    // Long renders amortise ramp-up and tail over more iterations and gain from a larger wavefront (1024 spp: -2 %), short ones lose (128 spp: +13 %); 800x600: break-even between 256 and 512 spp
-    if (ctx->poolAuto) ctx->poolSize = (!list && (uint64_t) W * H * (d->sample_last - d->sample_first) >= (3ull << 26)) ? (1u << 24) : (1u << 23);
+    // Path slots this render works on. Unless the caller fixed the pool size: a third of the render's samples within [2 Mi, 8 Mi] (ramp-up, tail, the
+    // per-iteration sort and the pool initialisation grow with the pool: 7.7 M samples take 11.7 ms on 2 Mi slots, 14.0 on 8 Mi), 16 Mi from 201 M
+    // samples on (1024 spp: -2 %). The allocation only ever grows; a shorter render uses the front of it.
+    uint32_t renderSlots = ctx->poolSize;
+    if (ctx->poolAuto) {
+        const uint64_t total = list ? (uint64_t) listCount : (uint64_t) W * H * (d->sample_last - d->sample_first);
+        renderSlots = (!list && total >= (3ull << 26)) ? (1u << 24) : (uint32_t) std::min<uint64_t>(1u << 23, std::max<uint64_t>(1u << 21, total / 3 / 256 * 256));
+        ctx->poolSize = std::max(ctx->poolSize, renderSlots);
+    }
     if (int r = ensurePool(ctx)) return r;
     if (int r = ensureBlock(ctx)) return r;
     cudaStream_t st = ctx->stream;
@@ -452,7 +459,7 @@ static int runWavefront(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, const uin
         const float ext = ctx->bvh.sceneHi[k] - ctx->bvh.sceneLo[k];
         pool.binLo[k] = ctx->bvh.sceneLo[k]; pool.binInv[k] = ext > 0.f ? 4.0f / ext : 0.f;
     }
-    pool.capacity = (uint32_t) std::min<uint64_t>(ctx->pool.capacity, std::max<uint64_t>(4096, (wanted + 255) / 256 * 256));
+    pool.capacity = (uint32_t) std::min<uint64_t>(std::min(ctx->pool.capacity, renderSlots), std::max<uint64_t>(4096, (wanted + 255) / 256 * 256));
     if (list) {
         rp.K = rp.Klast = 1; rp.numPasses = 1; rp.passSlots = listCount; rp.totalIssue = listCount; rp.ring = 1;
         rp.listPixel = d_listPixel; rp.listSample = d_listSample; totalSamples = listCount;
