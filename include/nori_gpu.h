@@ -263,6 +263,19 @@ typedef struct {
     char bsdf_type;     /* 'd' diffuse, 'c' mirror (conductor, roughness 0), 't' dielectric, 'o' microfacet (opaque rough) */
 } NoriGpuSPoint;
 
+/* One light record per path vertex = the reference's LPoint (include/nori/shadingPoint.h:149-156), same field order, 44 bytes: what the
+ * direct-light scatter of the tool reads beside the SPoint (src/pbsdf.cu:1651-1687, 1881-1897). As the tracer fills them:
+ * L_directsample = radiance of the light sample drawn at this vertex (direction SPoint::wi_d) if its shadow ray is free, else 0;
+ * lightpdf = that sample's solid-angle density; L_bsdfsample = radiance the continuation (SPoint::wi) finds on an emitter at the
+ * next vertex, else 0; bsdfpdf = SPoint::pdf; L_em = radiance this vertex emits towards wo. */
+typedef struct {
+    float L_directsample[3];
+    float L_bsdfsample[3];
+    float L_em[3];
+    float lightpdf;
+    float bsdfpdf;
+} NoriGpuLPoint;
+
 /* hparam (include/nori/shadingPoint.h:18-24): uniform grid of dim cells of size cellsize from minb; k / dk neighbours for the
  * indirect / direct-light scatter. SPoints::BuildKNN (shadingPoint.h:776-806) derives it from the points' bounding box. */
 typedef struct {
@@ -276,6 +289,9 @@ typedef struct {
  * nori_gpu_render traces), in path order, the vertices of one path contiguous. out == NULL: only counts. Returns the number of
  * vertices in *n_vertices; if it exceeds `capacity` nothing is written and NORI_GPU_EINVAL is returned (call again with room). */
 int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuSPoint *out, uint64_t capacity, uint64_t *n_vertices);
+/* The same, with the light record of every vertex beside it (lights: `capacity` records or NULL). */
+int nori_gpu_path_vertices_lights(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *desc, NoriGpuSPoint *out, NoriGpuLPoint *lights, uint64_t capacity,
+                                  uint64_t *n_vertices);
 /* buildHashGridAndFindKNN (src/pbsdf.cu:3173-3235): uniform hash grid over n points + max(k, dk) nearest neighbours of every
  * point inside the 2x2x2 cell block around it (batchNearestNeighbor, pbsdf.cu:1089-1178). points: n records `stride` bytes
  * apart whose first 12 bytes are the position (NoriGpuSPoint array: stride 168; packed float3: stride 12), HOST memory.
@@ -309,6 +325,20 @@ int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, i
  * before the first pass and blur[it] + eLd after each, mc[it] as above (lastRun). No atomics: results are deterministic. */
 int nori_gpu_pathgraph_mis(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
                            const int32_t *knn, int iterations, float *blur, float *mc, float *ms);
+/* computeDirectScatterAllOnGPU (src/pbsdf.cu:2370-2395): the tool's filter for DIRECT light. Per vertex i the marginal densities
+ * (k x lightpdf_i, sum_j pdf_j(wi_i): allGPUDirectPdfMarginal, :1881-1897), then every neighbour j of i receives
+ * L_directsample_i * bsdf_j(wi_d_i) / (k lightpdf_i) + L_bsdfsample_i * bsdf_j(wi_i) / sum_j pdf_j(wi_i) (allGPUDirectScatterRadiance,
+ * :1651-1687), and each vertex its own emission L_em (:813-818). dknn: the dk consumer's counts of nori_gpu_pathgraph_knn.
+ * direct: n x 3 floats. Float atomics, here as in the reference: equal up to the order of the additions. */
+int nori_gpu_pathgraph_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors,
+                              int row_ints, const int32_t *dknn, float *direct, float *ms);
+/* SPoints::computeScatterRadianceAOGWithProcessRecordingAndDirectLightOPT (include/nori/shadingPoint.h:462-476): the direct-light filter
+ * above (result in `direct`, the reference's m_result.blur_direct), then computeScatterAllOnGPURecordWithDirectOpt (src/pbsdf.cu:2488-2540):
+ * the iterated scatter of nori_gpu_pathgraph_scatter with the FILTERED direct light in the place of the vertices' own eLd — after every
+ * pass temp = direct + scattered radiance (updateWithOptDirectRadiance, :2196-2199). knn / dknn: the two consumers' counts of the rows. */
+int nori_gpu_pathgraph_scatter_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors,
+                                      int row_ints, const int32_t *knn, const int32_t *dknn, int iterations, float *direct, float *blur, float *mc,
+                                      float *ms);
 /* The tool's whole pipeline in one call, as SPoints::BuildKNN + one of the two drivers run it (include/nori/shadingPoint.h:776-806,
  * 496-510): hash grid + kNN over the records' positions, then the scatter (mode NORI_PG_SCATTER) or the MIS gather (NORI_PG_MIS)
  * on the rows the search left ON THE DEVICE (the k consumer's count knn[i] of each row, as the reference passes cu_knn). Same

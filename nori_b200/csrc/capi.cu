@@ -1037,7 +1037,8 @@ extern "C" int nori_gpu_obj_dedup(nori_gpu_ctx *ctx, const uint32_t *corners, ui
 
 // ---------------------------------------------------------------------------------------------
 // Path-graph post-process, first slice (src/pbsdf.cu): vertex records out of the tracer, hash grid + kNN.
-extern "C" int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, NoriGpuSPoint *out, uint64_t capacity, uint64_t *n_vertices) {
+extern "C" int nori_gpu_path_vertices_lights(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, NoriGpuSPoint *out, NoriGpuLPoint *lights, uint64_t capacity,
+                                             uint64_t *n_vertices) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(d && n_vertices, "path_vertices: bad arguments");
     REQUIRE(ctx->haveBvh && ctx->haveCamera, "path_vertices: scene, camera and accel must be set first");
@@ -1064,11 +1065,16 @@ extern "C" int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc
     if (!out) return NORI_GPU_OK;
     if (total > capacity) { ctx->err = "path_vertices: " + std::to_string(total) + " vertices do not fit the given capacity of " + std::to_string(capacity); return NORI_GPU_EINVAL; }
     if (total == 0) return NORI_GPU_OK;
-    DevBuf<NoriGpuSPoint> recs; CK(recs.alloc(total));
-    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, offsets.p, recs.p, st);
+    DevBuf<NoriGpuSPoint> recs; DevBuf<NoriGpuLPoint> lrecs; CK(recs.alloc(total));
+    if (lights) CK(lrecs.alloc(total));
+    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, offsets.p, recs.p, st, lights ? lrecs.p : nullptr);
     CK(cudaMemcpyAsync(out, recs.p, total * sizeof(NoriGpuSPoint), cudaMemcpyDeviceToHost, st));
+    if (lights) CK(cudaMemcpyAsync(lights, lrecs.p, total * sizeof(NoriGpuLPoint), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
     return NORI_GPU_OK;
+}
+extern "C" int nori_gpu_path_vertices(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, NoriGpuSPoint *out, uint64_t capacity, uint64_t *n_vertices) {
+    return nori_gpu_path_vertices_lights(ctx, d, out, nullptr, capacity, n_vertices);
 }
 
 namespace {
@@ -1195,6 +1201,69 @@ extern "C" int nori_gpu_pathgraph_scatter(nori_gpu_ctx *ctx, const NoriGpuSPoint
 extern "C" int nori_gpu_pathgraph_mis(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, int n, const int32_t *neighbors, int row_ints,
                                       const int32_t *knn, int iterations, float *blur, float *mc, float *ms) {
     return pathgraphFromHostRows(ctx, NORI_PG_MIS, points, n, neighbors, row_ints, knn, iterations, nullptr, blur, mc, ms);
+}
+
+namespace {
+/// The direct-light filter alone (iterations < 0) or followed by the indirect scatter that uses it (SPoints::
+/// computeScatterRadianceAOGWithProcessRecordingAndDirectLightOPT, include/nori/shadingPoint.h:462-476).
+int pathgraphDirectFromHost(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors, int row_ints,
+                            const int32_t *knn, const int32_t *dknn, int iterations, float *direct, float *blur, float *mc, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    const bool indirect = iterations >= 0;
+    REQUIRE(points && lights && neighbors && dknn && direct && n > 0 && row_ints >= 1, "pathgraph_direct: bad arguments");
+    REQUIRE(!indirect || (knn && iterations <= 64 && (iterations == 0 || (blur && mc))), "pathgraph_direct: knn, blur and mc (iterations x n x 3 floats, <= 64 iterations)");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<NoriGpuSPoint> sps; DevBuf<NoriGpuLPoint> lps; DevBuf<int> nb, kn, dkn, flag; DevBuf<unsigned char> scratch; DevBuf<float> out, pm, db, dm;
+    CK(sps.alloc(n)); CK(lps.alloc(n)); CK(nb.alloc((size_t) n * row_ints)); CK(dkn.alloc(n)); CK(flag.alloc(1));
+    CK(scratch.alloc(std::max(pgDirectScratchBytes(n), pgScatterScratchBytes(n)))); CK(out.alloc((size_t) 3 * n));
+    cudaStream_t st = ctx->stream;
+    if (int rc = stagedCopy(ctx, sps.p, points, (size_t) n * sizeof(NoriGpuSPoint))) return rc;
+    if (int rc = stagedCopy(ctx, lps.p, lights, (size_t) n * sizeof(NoriGpuLPoint))) return rc;
+    if (int rc = stagedCopy(ctx, nb.p, neighbors, (size_t) n * row_ints * 4)) return rc;
+    CK(cudaMemcpyAsync(dkn.p, dknn, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+    launchPathgraphValidate(nb.p, row_ints, row_ints, dkn.p, n, flag.p, st);
+    int bad = 0;
+    CK(cudaMemcpyAsync(&bad, flag.p, sizeof(int), cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
+    REQUIRE(!(bad & 1), "pathgraph_direct: dknn[i] outside [0, row_ints]");
+    REQUIRE(!(bad & 2), "pathgraph_direct: neighbour index outside [0, n)");
+    if (indirect) {
+        CK(kn.alloc(n)); CK(pm.alloc(n));
+        const size_t resultFloats = (size_t) std::max(iterations, 1) * 3 * (size_t) n;
+        CK(db.alloc(resultFloats)); CK(dm.alloc(resultFloats));
+        CK(cudaMemcpyAsync(kn.p, knn, (size_t) n * 4, cudaMemcpyHostToDevice, st));
+        launchPathgraphValidate(nb.p, row_ints, row_ints, kn.p, n, flag.p, st);
+        CK(cudaMemcpyAsync(&bad, flag.p, sizeof(int), cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
+        REQUIRE(!(bad & 1), "pathgraph_direct: knn[i] outside [0, row_ints]");
+        REQUIRE(!(bad & 2), "pathgraph_direct: neighbour index outside [0, n)");
+    }
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    if (!launchPathgraphDirect(sps.p, lps.p, n, nb.p, row_ints, dkn.p, scratch.p, out.p, st, ctx->err)) return NORI_GPU_EINVAL;
+    if (indirect && !launchPathgraphScatter(sps.p, n, nb.p, row_ints, kn.p, iterations, scratch.p, pm.p, db.p, dm.p, st, ctx->err, out.p)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    CK(cudaMemcpyAsync(direct, out.p, (size_t) 3 * n * 4, cudaMemcpyDeviceToHost, st));
+    if (indirect && iterations > 0) {
+        CK(cudaMemcpyAsync(blur, db.p, (size_t) iterations * 3 * n * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(mc, dm.p, (size_t) iterations * 3 * n * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (ms) cudaEventElapsedTime(ms, e0, e1);
+    unsigned line = 0;
+    if (const unsigned b = pathgraphScatterChecks(&line)) { ctx->err = "pathgraph_direct: device range check failed (" + std::to_string(b) + " at pathgraph_scatter.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
+}
+
+extern "C" int nori_gpu_pathgraph_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors,
+                                         int row_ints, const int32_t *dknn, float *direct, float *ms) {
+    return pathgraphDirectFromHost(ctx, points, lights, n, neighbors, row_ints, nullptr, dknn, -1, direct, nullptr, nullptr, ms);
+}
+extern "C" int nori_gpu_pathgraph_scatter_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors,
+                                                 int row_ints, const int32_t *knn, const int32_t *dknn, int iterations, float *direct, float *blur, float *mc,
+                                                 float *ms) {
+    if (ctx) REQUIRE(iterations >= 0, "pathgraph_scatter_direct: iterations < 0");
+    return pathgraphDirectFromHost(ctx, points, lights, n, neighbors, row_ints, knn, dknn, iterations, direct, blur, mc, ms);
 }
 
 extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,

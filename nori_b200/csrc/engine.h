@@ -106,7 +106,7 @@ void enqueueLi(const DeviceScene &sc, const RenderParams &rp, int n, const float
 
 /// Path vertices (NoriGpuSPoint records) of nPaths = W * H * spp camera samples: counts (out == nullptr) or records at offsets.
 bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t spp, unsigned long long nPaths, unsigned int *counts,
-                         const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st);
+                         const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st, NoriGpuLPoint *lights = nullptr);
 /// offsets[0..nPaths] = exclusive prefix sums of counts (offsets[nPaths] = total).
 void enqueueScanCounts(const unsigned int *counts, unsigned long long nPaths, unsigned long long *offsets, cudaStream_t st);
 

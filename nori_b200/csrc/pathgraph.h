@@ -25,10 +25,14 @@ unsigned pathgraphChecks(unsigned *line);
 /// pathgraph_scatter.cu: marginal densities + iterated radiance scatter over the kNN graph (src/pbsdf.cu:2317-2368).
 size_t pgScatterScratchBytes(int n);
 bool launchPathgraphScatter(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
-                            void *d_scratch, float *d_pdfmarginal, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
+                            void *d_scratch, float *d_pdfmarginal, float *d_blur, float *d_mc, cudaStream_t st, std::string &err,
+                            const float *d_direct = nullptr);
 size_t pgMisScratchBytes(int n, int rowInts);
 bool launchPathgraphMis(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
                         void *d_scratch, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
+size_t pgDirectScratchBytes(int n);
+bool launchPathgraphDirect(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_neighbors, int pitchInts, const int *d_knn,
+                           void *d_scratch, float *d_direct, cudaStream_t st, std::string &err);
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
 /// Whole pipeline on the device (nori_gpu_pathgraph_render): bounding box of the records, image composition from first vertices.
 void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bounds6, cudaStream_t st);

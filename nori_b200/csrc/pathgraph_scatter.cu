@@ -125,6 +125,14 @@ __global__ void k_pgUpdate(const float4 *__restrict__ eLi, const float4 *__restr
     else { const float4 r = radiance[i], d = eLd[i]; temp[i] = make_float4(r.x + d.x, r.y + d.y, r.z + d.z, 0.f); }
 }
 
+/// updateWithOptDirectRadiance (src/pbsdf.cu:2196-2199): temp = filtered direct light (n x 3 floats) + radiance, in every pass.
+__global__ void k_pgUpdateDirect(const float *__restrict__ direct, const float4 *__restrict__ radiance, float4 *__restrict__ temp, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 r = radiance[i];
+    temp[i] = make_float4(direct[3 * (size_t) i] + r.x, direct[3 * (size_t) i + 1] + r.y, direct[3 * (size_t) i + 2] + r.z, 0.f);
+}
+
 /// lastRun (src/pbsdf.cu:1497-1526): the plain Monte-Carlo estimate of the same quantity from the vertex's own continuation:
 /// temp[i + 1] * bsdf_i(wi_i) / (pdf_i(wi_i) * rrpdf_i). Writes radiance (the reference adds into a cleared array).
 __global__ void k_pgLastRun(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll, const float4 *__restrict__ temp,
@@ -244,6 +252,73 @@ __global__ void __launch_bounds__(kPgWarps * 32) k_pgMisGather(const float4 *__r
     if (lane == 0) radiance[i] = make_float4(r0, r1, r2, 0.f);
 }
 
+/// Direct-light scatter (computeDirectScatterAllOnGPU, src/pbsdf.cu:2370-2395). allGPUDirectPdfMarginal (:1881-1897):
+/// m.x = the vertex's light-sample density added up once per neighbour (the reference adds the same float k times: so does lane 0),
+/// m.y = sum over the neighbours j of pdf_j(wi_i) — no rrpdf, no exclusion here — in the fixed lane order of the other sums.
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgDirectMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                                    const NoriGpuLPoint *__restrict__ lps, const int *__restrict__ neighbors, int pitchInts,
+                                                                    const int *__restrict__ knn, int n, float2 *__restrict__ marginal) {
+    const int i = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int k = knn[i];
+    const float4 w4 = wiAll[i];
+    const float wi[3] = {w4.x, w4.y, w4.z};
+    const int *row = neighbors + (size_t) i * pitchInts;
+    float sum = 0.0f;
+    for (int t = lane; t < k; t += 32) {
+        const int j = row[t];
+        NG_CHECK(j >= 0 && j < n);
+        PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
+        sum += pgPdf(v, wi);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+    if (lane == 0) {
+        const float lp = lps[i].lightpdf;
+        float x = 0.0f;
+        for (int t = 0; t < k; ++t) x += lp;
+        marginal[i] = make_float2(x, sum);
+    }
+}
+
+/// allGPUDirectScatterRadiance (:1651-1687): vertex i hands its light sample and what its continuation found on an emitter to all its
+/// neighbours, each evaluating its own BSDF for i's two directions; float4 reduction per neighbour as in the indirect scatter.
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgDirectScatter(const float4 *__restrict__ A, const float4 *__restrict__ B, const NoriGpuSPoint *__restrict__ sps,
+                                                                   const NoriGpuLPoint *__restrict__ lps, const float2 *__restrict__ marginal,
+                                                                   const int *__restrict__ neighbors, int pitchInts, const int *__restrict__ knn, int n,
+                                                                   float4 *__restrict__ radiance) {
+    const int i = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const float2 m = marginal[i];
+    const float invL = (float) (1.0 / (double) m.x), invB = (float) (1.0 / (double) m.y);
+    const NoriGpuLPoint lp = lps[i];
+    const float wid[3] = {sps[i].wi_d[0], sps[i].wi_d[1], sps[i].wi_d[2]}, wi[3] = {sps[i].wi[0], sps[i].wi[1], sps[i].wi[2]};
+    const int k = knn[i];
+    const int *row = neighbors + (size_t) i * pitchInts;
+    for (int t = lane; t < k; t += 32) {
+        const int j = row[t];
+        NG_CHECK(j >= 0 && j < n);
+        PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
+        float out[3] = {0.f, 0.f, 0.f};
+        if (m.x > 0.0f) {
+            float f[3]; pgBsdf(v, wid, f);
+            for (int c = 0; c < 3; ++c) out[c] = out[c] + (lp.L_directsample[c] * f[c]) * invL;
+        }
+        if (m.y > 0.0f) {
+            float f[3]; pgBsdf(v, wi, f);
+            for (int c = 0; c < 3; ++c) out[c] = out[c] + (lp.L_bsdfsample[c] * f[c]) * invB;
+        }
+        pgRedAdd(radiance + j, out[0], out[1], out[2]);
+    }
+}
+/// addEmitterToDirectLight (:813-818) + the val3f rows of the result
+__global__ void k_pgDirectFinish(const float4 *__restrict__ radiance, const NoriGpuLPoint *__restrict__ lps, int n, float *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 r = radiance[i];
+    out[3 * (size_t) i] = r.x + lps[i].L_em[0]; out[3 * (size_t) i + 1] = r.y + lps[i].L_em[1]; out[3 * (size_t) i + 2] = r.z + lps[i].L_em[2];
+}
+
 /// The neighbour rows are trusted by the kernels above: every knn[i] in [0, rowInts] and every used entry in [0, n), else flag = 1.
 __global__ void k_pgValidate(const int *__restrict__ neighbors, int pitchInts, int rowInts, const int *__restrict__ knn, int n, int *__restrict__ flag) {
     const int i = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -319,8 +394,10 @@ size_t pgScatterScratchBytes(int n) {
 /// computeScatterAllOnGPURecord (src/pbsdf.cu:2317-2368). d_blur / d_mc: iterations x n x 3 floats (device); d_pdfmarginal: n floats.
 /// Sequence kept as the reference has it, including that its update step after the first scatter passes the LOOP index (0) again,
 /// so pass 1 scatters the same temp = eLi as pass 0 (pbsdf.cu:2344-2356).
+/// d_direct != nullptr: computeScatterAllOnGPURecordWithDirectOpt (:2488-2540) — the same passes with the filtered direct light (n x 3 floats,
+/// launchPathgraphDirect's result) in the place of eLd: temp = direct + radiance after EVERY scatter (updateWithOptDirectRadiance).
 bool launchPathgraphScatter(const NoriGpuSPoint *d_sps, int n, const int *d_neighbors, int pitchInts, const int *d_knn, int iterations,
-                            void *d_scratch, float *d_pdfmarginal, float *d_blur, float *d_mc, cudaStream_t st, std::string &err) {
+                            void *d_scratch, float *d_pdfmarginal, float *d_blur, float *d_mc, cudaStream_t st, std::string &err, const float *d_direct) {
     if (n <= 0 || iterations < 0) { err = "pathgraph_scatter: bad sizes"; return false; }
     float4 *A = static_cast<float4 *>(d_scratch), *B = A + 4 * (size_t) n, *wi = B + 3 * (size_t) n, *eLi = wi + n, *eLd = eLi + n, *temp = eLd + n, *radiance = temp + n;
     const unsigned gt = (unsigned) ((n + 255) / 256), gw = (unsigned) ((n + kPgWarps - 1) / kPgWarps);
@@ -332,7 +409,8 @@ bool launchPathgraphScatter(const NoriGpuSPoint *d_sps, int n, const int *d_neig
         cudaMemsetAsync(radiance, 0, (size_t) n * sizeof(float4), st);
         k_pgScatter<<<gw, kPgWarps * 32, 0, st>>>(A, B, wi, d_pdfmarginal, d_neighbors, pitchInts, d_knn, n, temp, radiance);
         k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_blur + (size_t) it * 3 * n, n);
-        k_pgUpdate<<<gt, 256, 0, st>>>(eLi, eLd, radiance, temp, n, it);
+        if (d_direct) k_pgUpdateDirect<<<gt, 256, 0, st>>>(d_direct, radiance, temp, n);
+        else k_pgUpdate<<<gt, 256, 0, st>>>(eLi, eLd, radiance, temp, n, it);
         k_pgLastRun<<<gt, 256, 0, st>>>(A, B, wi, temp, radiance, n);
         k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_mc + (size_t) it * 3 * n, n);
     }
@@ -366,6 +444,25 @@ bool launchPathgraphMis(const NoriGpuSPoint *d_sps, int n, const int *d_neighbor
     }
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("pathgraph_mis: ") + cudaGetErrorString(e); return false; }
+    return true;
+}
+
+size_t pgDirectScratchBytes(int n) { return (size_t) n * (64 + 48 + 16 + 16 + 16 + 16 + 8); }
+
+/// computeDirectScatterAllOnGPU (src/pbsdf.cu:2370-2395): d_direct = n x 3 floats (device), d_marginal (optional) = n float2.
+bool launchPathgraphDirect(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_neighbors, int pitchInts, const int *d_knn,
+                           void *d_scratch, float *d_direct, cudaStream_t st, std::string &err) {
+    if (n <= 0 || pitchInts < 1) { err = "pathgraph_direct: bad sizes"; return false; }
+    float4 *A = static_cast<float4 *>(d_scratch), *B = A + 4 * (size_t) n, *wi = B + 3 * (size_t) n, *eLi = wi + n, *eLd = eLi + n, *radiance = eLd + n;
+    float2 *marginal = reinterpret_cast<float2 *>(radiance + n);
+    const unsigned gt = (unsigned) ((n + 255) / 256), gw = (unsigned) ((n + kPgWarps - 1) / kPgWarps);
+    k_pgPack<<<gt, 256, 0, st>>>(d_sps, n, A, B, wi, eLi, eLd);
+    k_pgDirectMarginal<<<gw, kPgWarps * 32, 0, st>>>(A, B, wi, d_lps, d_neighbors, pitchInts, d_knn, n, marginal);
+    cudaMemsetAsync(radiance, 0, (size_t) n * sizeof(float4), st);
+    k_pgDirectScatter<<<gw, kPgWarps * 32, 0, st>>>(A, B, d_sps, d_lps, marginal, d_neighbors, pitchInts, d_knn, n, radiance);
+    k_pgDirectFinish<<<gt, 256, 0, st>>>(radiance, d_lps, n, d_direct);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("pathgraph_direct: ") + cudaGetErrorString(e); return false; }
     return true;
 }
 

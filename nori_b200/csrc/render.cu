@@ -223,10 +223,13 @@ struct ShadowOut { bool cast; V3 o, d; float maxt; V3 contrib; };
 
 /// Body of the Li loops of oracle/noracle_integrators.h for ONE path vertex. Returns true while
 /// the path continues (a new ray was written to `ray`).
+/// What the path-graph tool's LPoint records want of a vertex (k_pathVertices only; nullptr everywhere else: the code folds away).
+struct LightOut { V3 Lem, Ldirect; float lightPdf; };
+
 template <int INTEGRATOR>
 __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderParams &rp, Ray &ray, uint32_t gid, float t, float u, float v,
                                             Pcg32 &rng, V3 &T, V3 &L, float &eta, float &bsdfPdf, uint32_t &flags, ShadowOut &sh,
-                                            const float4 *lazyOrigin = nullptr, float *rrProb = nullptr) {
+                                            const float4 *lazyOrigin = nullptr, float *rrProb = nullptr, LightOut *lo = nullptr) {
     // lazyOrigin: where the incoming ray's origin can be read when `ray.o` was not loaded. Only the MIS weight of an
     // emitter hit needs it, so the wavefront shade kernel leaves those 16 bytes per path in memory.
     sh.cast = false;
@@ -310,6 +313,7 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
         const EmitterInfo &em = sc.emitters[mesh.emitter];
         if (dot(its.sh.n, -ray.d) > 0.0f) {
             V3 Le = mk(em.radiance[0], em.radiance[1], em.radiance[2]);
+            if (lo) lo->Lem = Le;
             if (!isZero(Le)) {
                 if (discrete || !useEms) L = L + T * Le;
                 else if (useMats) {
@@ -329,6 +333,7 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
         V2 xi = rng.next2D();
         LightSample ls;
         if (sampleLights(sc, its.p, uu, xi, ls)) {
+            if (lo) { lo->Ldirect = ls.Le; lo->lightPdf = ls.pdf; }
             BsdfQuery q; q.wi = wiLocal; q.wo = its.sh.toLocal(ls.wi); q.eta = 1.0f; q.measure = kSolidAngle;
             V3 f = bsdf.eval(q);
             if (!isZero(f)) {
@@ -1099,7 +1104,8 @@ void enqueueLi(const DeviceScene &sc, const RenderParams &rp, int n, const float
 /// WRITE = false: counts[g] = surface vertices of path g. WRITE = true: records at offsets[g] + v (path-contiguous).
 template <int INTEGRATOR, bool WRITE>
 __global__ void __launch_bounds__(128) k_pathVertices(DeviceScene sc, RenderParams rp, uint32_t spp, unsigned long long nPaths,
-                                                      unsigned int *__restrict__ counts, const unsigned long long *__restrict__ offsets, NoriGpuSPoint *__restrict__ out) {
+                                                      unsigned int *__restrict__ counts, const unsigned long long *__restrict__ offsets, NoriGpuSPoint *__restrict__ out,
+                                                      NoriGpuLPoint *__restrict__ lights) {
     const unsigned long long g = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= nPaths) return;
     const uint32_t pixel = (uint32_t) (g / spp), k = (uint32_t) (g % spp);
@@ -1145,14 +1151,27 @@ __global__ void __launch_bounds__(128) k_pathVertices(DeviceScene sc, RenderPara
         ShadowOut sh;
         float rr = 1.0f;
         const V3 Tb = T, Lb = L;                                     // throughput up to this vertex, radiance credited before it
-        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh, nullptr, &rr);
+        LightOut lo; lo.Lem = mk(0.f, 0.f, 0.f); lo.Ldirect = mk(0.f, 0.f, 0.f); lo.lightPdf = 0.f;
+        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, gid, t, u, v, rng, T, L, eta, bsdfPdf, flags, sh, nullptr, &rr, WRITE ? &lo : nullptr);
         if (WRITE) {
+            bool lit = false;
             if (sh.cast) {
                 rec->wi_d[0] = sh.d.x; rec->wi_d[1] = sh.d.y; rec->wi_d[2] = sh.d.z;
                 float st, su, sv;                                    // the light sample counts if its shadow ray is free (as k_li)
-                if (traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT) == kNoHit) L = L + sh.contrib;
+                lit = traverse<true>(sc.nodes, sc.leafTris, sh.o, sh.d, kEpsilon, sh.maxt, st, su, sv, nullptr, sc.isectMode == NORI_ISECT_WATERTIGHT) == kNoHit;
+                if (lit) L = L + sh.contrib;
             }
-            if (cont) { rec->wi[0] = ray.d.x; rec->wi[1] = ray.d.y; rec->wi[2] = ray.d.z; rec->pdf = bsdfPdf; rec->rrpdf = rr; }
+            if (lights) {                                            // LPoint (include/nori/shadingPoint.h:149-156) of this vertex
+                NoriGpuLPoint lp;
+                const V3 Ld = lit ? lo.Ldirect : mk(0.f, 0.f, 0.f);
+                lp.L_directsample[0] = Ld.x; lp.L_directsample[1] = Ld.y; lp.L_directsample[2] = Ld.z;
+                lp.L_bsdfsample[0] = lp.L_bsdfsample[1] = lp.L_bsdfsample[2] = 0.f;      // known at the next vertex (below)
+                lp.L_em[0] = lo.Lem.x; lp.L_em[1] = lo.Lem.y; lp.L_em[2] = lo.Lem.z;
+                lp.lightpdf = sh.cast ? lo.lightPdf : 0.f; lp.bsdfpdf = 0.f;
+                lights[base + nv - 1] = lp;
+                if (nv > 1) { NoriGpuLPoint *prev = lights + base + nv - 2; prev->L_bsdfsample[0] = lo.Lem.x; prev->L_bsdfsample[1] = lo.Lem.y; prev->L_bsdfsample[2] = lo.Lem.z; }
+            }
+            if (cont) { rec->wi[0] = ray.d.x; rec->wi[1] = ray.d.y; rec->wi[2] = ray.d.z; rec->pdf = bsdfPdf; rec->rrpdf = rr; if (lights) lights[base + nv - 1].bsdfpdf = bsdfPdf; }
             // eLd: what the estimator credits to this vertex itself (emission seen from the previous vertex with its MIS weight +
             // the light sample), as radiance leaving towards wo = the credited amount / the throughput up to here. eLi holds that
             // throughput until the path has ended (the pass below turns it into the radiance of the whole path suffix).
@@ -1176,10 +1195,10 @@ __global__ void __launch_bounds__(128) k_pathVertices(DeviceScene sc, RenderPara
 }
 
 bool enqueuePathVertices(const DeviceScene &sc, const RenderParams &rp, uint32_t spp, unsigned long long nPaths, unsigned int *counts,
-                         const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st) {
+                         const unsigned long long *offsets, NoriGpuSPoint *out, cudaStream_t st, NoriGpuLPoint *lights) {
     const unsigned g = (unsigned) ((nPaths + 127ull) / 128ull);
-#define PV(I) do { if (out) k_pathVertices<I, true><<<g, 128, 0, st>>>(sc, rp, spp, nPaths, counts, offsets, out); \
-                   else k_pathVertices<I, false><<<g, 128, 0, st>>>(sc, rp, spp, nPaths, counts, offsets, out); } while (0)
+#define PV(I) do { if (out) k_pathVertices<I, true><<<g, 128, 0, st>>>(sc, rp, spp, nPaths, counts, offsets, out, lights); \
+                   else k_pathVertices<I, false><<<g, 128, 0, st>>>(sc, rp, spp, nPaths, counts, offsets, out, nullptr); } while (0)
     switch (rp.integrator) {
     case NORI_INT_PATH_MATS: PV(NORI_INT_PATH_MATS); break;
     case NORI_INT_PATH_EMS: PV(NORI_INT_PATH_EMS); break;

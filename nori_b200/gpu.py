@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
 ]
 
 
@@ -86,6 +86,9 @@ SPOINT_DTYPE = np.dtype([("pos", "<f4", 3), ("wi", "<f4", 3), ("wi_d", "<f4", 3)
                          ("diffuse", "<f4", 3), ("specular", "<f4", 3), ("eLi", "<f4", 3), ("eLd", "<f4", 3), ("eta", "<f4", 3), ("k", "<f4", 3),
                          ("roughness", "<f4"), ("pdf", "<f4"), ("rrpdf", "<f4"), ("nidx", "<i4"), ("groupIdx", "<i4"), ("bsdf_type", "S1"), ("_pad", "V3")])
 assert SPOINT_DTYPE.itemsize == 168
+# NoriGpuLPoint = the reference's LPoint (include/nori/shadingPoint.h:148-155), 44 bytes
+LPOINT_DTYPE = np.dtype([("L_directsample", "<f4", 3), ("L_bsdfsample", "<f4", 3), ("L_em", "<f4", 3), ("lightpdf", "<f4"), ("bsdfpdf", "<f4")])
+assert LPOINT_DTYPE.itemsize == 44
 
 _lib = None
 
@@ -138,6 +141,9 @@ def load_library() -> C.CDLL:
     L.nori_gpu_obj_dedup.argtypes = [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32, vp, vp, vp, vp, C.POINTER(C.c_uint32), C.POINTER(C.c_float)]
     L.nori_gpu_li.argtypes = [vp, C.POINTER(RenderDesc), ip, vp, vp, vp]
     L.nori_gpu_path_vertices.argtypes = [vp, C.POINTER(RenderDesc), vp, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.nori_gpu_path_vertices_lights.argtypes = [vp, C.POINTER(RenderDesc), vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.nori_gpu_pathgraph_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
+    L.nori_gpu_pathgraph_scatter_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_grid.argtypes = [vp, C.c_uint64, ip, vp, ip, ip, C.POINTER(HashParams)]
     L.nori_gpu_pathgraph_scatter.argtypes = [vp, vp, ip, vp, ip, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
@@ -358,15 +364,39 @@ class Engine:
         return rgb, st
 
     # ---- path graph (src/pbsdf.cu) -------------------------------------------------------------
-    def path_vertices(self, integrator=None, sample_first=0, sample_last=1):
-        """SPoint records of every surface vertex of the camera samples [first, last) of every pixel, path-contiguous."""
+    def path_vertices(self, integrator=None, sample_first=0, sample_last=1, lights=False):
+        """SPoint records of every surface vertex of the camera samples [first, last) of every pixel, path-contiguous.
+        lights=True: (SPoint records, LPoint records) — the light record of every vertex beside it."""
         d = self.render_desc(integrator, 1, sample_first, sample_last)
         n = C.c_uint64()
         self._ck(self.L.nori_gpu_path_vertices(self.h, C.byref(d), None, 0, C.byref(n)))
         out = np.zeros(int(n.value), SPOINT_DTYPE)
+        lps = np.zeros(int(n.value), LPOINT_DTYPE) if lights else None
         if n.value:
-            self._ck(self.L.nori_gpu_path_vertices(self.h, C.byref(d), _p(out), n.value, C.byref(n)))
-        return out
+            if lights:
+                self._ck(self.L.nori_gpu_path_vertices_lights(self.h, C.byref(d), _p(out), _p(lps), n.value, C.byref(n)))
+            else:
+                self._ck(self.L.nori_gpu_path_vertices(self.h, C.byref(d), _p(out), n.value, C.byref(n)))
+        return (out, lps) if lights else out
+
+    def pathgraph_direct(self, points, lights, neighbors, dknn, knn=None, iterations=None):
+        """computeDirectScatterAllOnGPU: SPoint + LPoint records and the kNN rows (dk consumer's counts) -> (direct (n, 3), ms).
+        With knn and iterations the chained driver (computeScatterRadianceAOGWithProcessRecordingAndDirectLightOPT): the indirect
+        scatter over the k consumer's counts using the filtered direct light -> (direct, blur (it, n, 3), mc (it, n, 3), ms)."""
+        assert points.dtype == SPOINT_DTYPE and lights.dtype == LPOINT_DTYPE
+        pts = np.ascontiguousarray(points); lps = np.ascontiguousarray(lights); n = pts.shape[0]
+        nb = np.ascontiguousarray(neighbors, np.int32); dk = np.ascontiguousarray(dknn, np.int32)
+        assert lps.shape == (n,) and nb.ndim == 2 and nb.shape[0] == n and dk.shape == (n,)
+        out = np.empty((n, 3), np.float32); ms = C.c_float()
+        if iterations is None:
+            self._ck(self.L.nori_gpu_pathgraph_direct(self.h, _p(pts), _p(lps), n, _p(nb), nb.shape[1], _p(dk), _p(out), C.byref(ms)))
+            return out, ms.value
+        kn = np.ascontiguousarray(knn, np.int32)
+        assert kn.shape == (n,)
+        blur = np.empty((iterations, n, 3), np.float32); mc = np.empty((iterations, n, 3), np.float32)
+        self._ck(self.L.nori_gpu_pathgraph_scatter_direct(self.h, _p(pts), _p(lps), n, _p(nb), nb.shape[1], _p(kn), _p(dk), int(iterations),
+                                                          _p(out), _p(blur), _p(mc), C.byref(ms)))
+        return out, blur, mc, ms.value
 
     def pathgraph_knn(self, points, hp: "HashParams"):
         """buildHashGridAndFindKNN: points = (n, 3) float32 or an SPoint record array. Returns (neighbors, knn, dknn, ms)."""

@@ -11,7 +11,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle.pyoracle import RefCuda
-from nori_b200.gpu import SPOINT_DTYPE
+from nori_b200.gpu import SPOINT_DTYPE, LPOINT_DTYPE
 
 
 def unit(v):
@@ -40,7 +40,39 @@ def synthetic_records(n, seed):
     return s
 
 
+def synthetic_lights(n, seed):
+    """LPoint records for the direct-light scatter: a third of the vertices without a light sample (density 0: the reference skips
+    that term), a few emitters."""
+    rng = np.random.default_rng(seed)
+    lp = np.zeros(n, LPOINT_DTYPE)
+    has = rng.random(n) < 0.66
+    lp["L_directsample"] = rng.random((n, 3)) * 20 * has[:, None]
+    lp["lightpdf"] = (0.05 + rng.random(n) * 3) * has
+    lp["L_bsdfsample"] = rng.random((n, 3)) * 15 * (rng.random((n, 1)) < 0.2)
+    lp["L_em"] = rng.random((n, 3)) * 15 * (rng.random((n, 1)) < 0.05)
+    lp["bsdfpdf"] = rng.random(n)
+    return lp
+
+
+def main_direct(out):
+    """(dir_*) computeDirectScatterAllOnGPU (+ computeScatterAllOnGPURecordWithDirectOpt on its result) on the committed fixture's records and rows (tests/golden/pathgraph_scatter_ref.npz) with
+    seeded light records: python oracle/make_pathgraph_scatter_golden.py --direct [out.npz]."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "pathgraph_scatter_ref.npz"))
+    v = np.ascontiguousarray(z["sc_sps"]).view(SPOINT_DTYPE).reshape(-1)
+    nb, knn = z["sc_nb"], z["sc_knn"]
+    rng = np.random.default_rng(23)
+    dknn = np.minimum(knn, rng.integers(1, nb.shape[1] + 1, size=len(v))).astype(np.int32)
+    lp = synthetic_lights(len(v), 29)
+    ref = RefCuda()
+    direct, sec = ref.direct(v, lp, nb, dknn)
+    direct2, blur, mc, _ = ref.direct(v, lp, nb, dknn, knn=knn, iterations=3)     # ... + computeScatterAllOnGPURecordWithDirectOpt
+    np.savez_compressed(out, dir_lps=lp.view(np.uint8).reshape(len(lp), 44), dir_dknn=dknn, dir_out=direct, dir_blur=blur, dir_mc=mc)
+    print("wrote", out, len(v), "records; rows with light", int((np.abs(direct).sum(1) > 0).sum()), "non-finite", int((~np.isfinite(direct)).any(1).sum()))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--direct":
+        return main_direct(sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "pathgraph_direct_ref.npz"))
     out = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "pathgraph_scatter_ref.npz")
     ref = RefCuda()
     res = {}

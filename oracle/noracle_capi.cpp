@@ -314,6 +314,15 @@ void noracle_pathgraph_mis(const void *sps, int n, const int32_t *neighbors, int
                            int sequential, float *blur, float *mc) {
     pathgraphMis(static_cast<const SPointRec *>(sps), n, neighbors, row_ints, knn, iterations, sequential != 0, blur, mc);
 }
+/// The direct-light scatter (computeDirectScatterAllOnGPU) and, iterations >= 0, the indirect scatter that uses its result
+/// (computeScatterAllOnGPURecordWithDirectOpt). lps: n LPoint records (44 bytes). marginal: n x 2 or NULL.
+void noracle_pathgraph_direct(const void *sps, const void *lps, int n, const int32_t *neighbors, int row_ints, const int32_t *knn, const int32_t *dknn,
+                              int iterations, int sequential, float *marginal, float *direct, float *blur, float *mc) {
+    pathgraphDirect(static_cast<const SPointRec *>(sps), static_cast<const LPointRec *>(lps), n, neighbors, row_ints, dknn, sequential != 0,
+                    marginal, direct);
+    if (iterations >= 0)
+        pathgraphScatter(static_cast<const SPointRec *>(sps), n, neighbors, row_ints, knn, iterations, sequential != 0, nullptr, blur, mc, direct);
+}
 /// The tool's evaluations at one vertex each: pdf[i] = pdf_device(sps[i], wi[i]), bsdf[i] = bsdfeval_device(sps[i], wi[i]).
 void noracle_pathgraph_eval(const void *sps, int n, const float *wi, float *pdf, float *bsdf) {
     const SPointRec *p = static_cast<const SPointRec *>(sps);

@@ -177,7 +177,7 @@ inline void bsdfAt(const SPointRec &sp, const float *wi, float *out) {
 
 /// computeScatterAllOnGPURecord. neighbors: n rows of rowInts ints; blur / mc: iterations x n x 3.
 inline void pathgraphScatter(const SPointRec *sps, int n, const int32_t *neighbors, int rowInts, const int32_t *knn, int iterations,
-                             bool sequential, float *pdfmarginal, float *blur, float *mc) {
+                             bool sequential, float *pdfmarginal, float *blur, float *mc, const float *direct = nullptr) {
     using namespace pgs;
     std::vector<float> pm(n), temp(3 * (size_t) n), rad(3 * (size_t) n);
     for (int i = 0; i < n; ++i) {
@@ -227,7 +227,8 @@ inline void pathgraphScatter(const SPointRec *sps, int n, const int32_t *neighbo
         }
         std::memcpy(blur + (size_t) it * 3 * n, rad.data(), sizeof(float) * 3 * (size_t) n);
         for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c)
-            temp[3 * (size_t) i + c] = it == 0 ? sps[i].eLi[c] : rad[3 * (size_t) i + c] + sps[i].eLd[c];
+            temp[3 * (size_t) i + c] = direct ? direct[3 * (size_t) i + c] + rad[3 * (size_t) i + c]      // updateWithOptDirectRadiance (:2196-2199)
+                                              : (it == 0 ? sps[i].eLi[c] : rad[3 * (size_t) i + c] + sps[i].eLd[c]);
         float *out = mc + (size_t) it * 3 * n;
         for (int i = 0; i < n; ++i) {
             out[3 * (size_t) i] = out[3 * (size_t) i + 1] = out[3 * (size_t) i + 2] = 0.0f;
@@ -304,6 +305,50 @@ inline void pathgraphMis(const SPointRec *sps, int n, const int32_t *neighbors, 
             }
         }
     }
+}
+
+
+/// LPoint, include/nori/shadingPoint.h:148-155 (44 bytes)
+struct LPointRec { float L_directsample[3], L_bsdfsample[3], L_em[3], lightpdf, bsdfpdf; };
+static_assert(sizeof(LPointRec) == 44, "LPoint is 44 bytes");
+
+/// computeDirectScatterAllOnGPU (src/pbsdf.cu:2370-2395): allGPUDirectPdfMarginal (:1881-1897), allGPUDirectScatterRadiance
+/// (:1651-1687), addEmitterToDirectLight (:813-818). marginal (optional): n x 2 = {k additions of the vertex's light density, the
+/// neighbours' densities of wi summed in lane order + butterfly or, `sequential`, in list order}. The scatter adds in vertex order i,
+/// neighbour order t (the reference and the product: float atomics, any order).
+inline void pathgraphDirect(const SPointRec *sps, const LPointRec *lps, int n, const int32_t *neighbors, int rowInts, const int32_t *knn,
+                            bool sequential, float *marginal, float *direct) {
+    using namespace pgs;
+    std::vector<float> m(2 * (size_t) n, 0.0f);
+    for (int i = 0; i < n; ++i) {
+        const int32_t *row = neighbors + (size_t) i * rowInts; const int k = knn[i];
+        float x = 0.0f, y = 0.0f;
+        for (int t = 0; t < k; ++t) x += lps[i].lightpdf;
+        if (sequential) {
+            for (int t = 0; t < k; ++t) y += pdfAt(sps[row[t]], sps[i].wi);
+        } else {
+            float lane[32];
+            for (int l = 0; l < 32; ++l) { float s = 0.0f; for (int t = l; t < k; t += 32) s += pdfAt(sps[row[t]], sps[i].wi); lane[l] = s; }
+            for (int d = 16; d > 0; d >>= 1) { float nxt[32]; for (int l = 0; l < 32; ++l) nxt[l] = lane[l] + lane[l ^ d]; std::memcpy(lane, nxt, sizeof nxt); }
+            y = lane[0];
+        }
+        m[2 * (size_t) i] = x; m[2 * (size_t) i + 1] = y;
+    }
+    if (marginal) std::memcpy(marginal, m.data(), sizeof(float) * 2 * (size_t) n);
+    for (size_t q = 0; q < 3 * (size_t) n; ++q) direct[q] = 0.0f;
+    for (int i = 0; i < n; ++i) {
+        const int32_t *row = neighbors + (size_t) i * rowInts; const int k = knn[i];
+        const float mx = m[2 * (size_t) i], my = m[2 * (size_t) i + 1];
+        const float invL = (float) (1.0 / (double) mx), invB = (float) (1.0 / (double) my);
+        for (int t = 0; t < k; ++t) {
+            const int j = row[t];
+            float out[3] = {0.0f, 0.0f, 0.0f};
+            if (mx > 0.0f) { float f[3]; bsdfAt(sps[j], sps[i].wi_d, f); for (int c = 0; c < 3; ++c) out[c] = out[c] + (lps[i].L_directsample[c] * f[c]) * invL; }
+            if (my > 0.0f) { float f[3]; bsdfAt(sps[j], sps[i].wi, f); for (int c = 0; c < 3; ++c) out[c] = out[c] + (lps[i].L_bsdfsample[c] * f[c]) * invB; }
+            for (int c = 0; c < 3; ++c) direct[3 * (size_t) j + c] += out[c];
+        }
+    }
+    for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) direct[3 * (size_t) i + c] += lps[i].L_em[c];
 }
 
 } // namespace noracle

@@ -165,6 +165,7 @@ class Port:
         L.noracle_pathgraph_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p]
+        L.noracle_pathgraph_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, C.c_void_p, _i32p, C.c_int, C.c_int, _f32p, _f32p, C.c_void_p, C.c_void_p]
 
     def pathgraph_knn(self, pts, dim, cellsize, minb, k, dk):
         """noracle_pathgraph.h: hash grid + kNN. Returns (neighbors, knn, dknn, dists) rows nearest first, self swapped to the front."""
@@ -191,6 +192,22 @@ class Port:
         blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
         self.L.noracle_pathgraph_mis(sps.ctypes.data_as(C.c_void_p), n, nb, nb.shape[1], kn, iterations, int(sequential), blur.reshape(-1), mc.reshape(-1))
         return blur[:iterations], mc[:iterations]
+
+    def pathgraph_direct(self, sps, lps, neighbors, dknn, sequential=False, knn=None, iterations=None):
+        """computeDirectScatterAllOnGPU restated: (marginal (n, 2), direct (n, 3)). lps: n 44-byte LPoint records. With knn and
+        iterations also computeScatterAllOnGPURecordWithDirectOpt on the result: (marginal, direct, blur (it, n, 3), mc (it, n, 3))."""
+        sps = np.ascontiguousarray(sps); lps = np.ascontiguousarray(lps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168 and lps.dtype.itemsize == 44 and lps.shape[0] == n
+        nb = np.ascontiguousarray(neighbors, np.int32); dk = np.ascontiguousarray(dknn, np.int32)
+        m = np.empty((n, 2), np.float32); out = np.empty((n, 3), np.float32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        if iterations is None:
+            self.L.noracle_pathgraph_direct(vp(sps), vp(lps), n, nb, nb.shape[1], None, dk, -1, int(sequential), m.reshape(-1), out.reshape(-1), None, None)
+            return m, out
+        kn = np.ascontiguousarray(knn, np.int32)
+        blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
+        self.L.noracle_pathgraph_direct(vp(sps), vp(lps), n, nb, nb.shape[1], vp(kn), dk, iterations, int(sequential), m.reshape(-1), out.reshape(-1), vp(blur), vp(mc))
+        return m, out, blur[:iterations], mc[:iterations]
 
     def pathgraph_eval(self, sps, wi):
         """pdf_device / bsdfeval_device restated: (pdf (n,), bsdf (n, 3)) of record i for direction wi[i]."""
@@ -262,6 +279,8 @@ class RefCuda:
         self.L.refcuda_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         self.L.refcuda_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
         self.L.refcuda_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_double)]
+        if hasattr(self.L, 'refcuda_direct'):
+            self.L.refcuda_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, C.c_void_p, _i32p, C.c_int, _f32p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
 
     def knn(self, pts, dim, cellsize, minb, k, dk):
         """buildHashGridAndFindKNN. Returns (neighbors n x max(k,dk), knn, dknn, seconds)."""
@@ -294,6 +313,26 @@ class RefCuda:
         if rc != 0:
             raise RuntimeError(f"refcuda_mis failed ({rc})")
         return blur[:iterations], mc[:iterations], sec.value
+
+    def direct(self, sps, lps, neighbors, dknn, knn=None, iterations=None):
+        """computeDirectScatterAllOnGPU: (direct (n, 3), seconds); with knn and iterations followed by
+        computeScatterAllOnGPURecordWithDirectOpt: (direct, blur (it, n, 3), mc (it, n, 3), seconds)."""
+        sps = np.ascontiguousarray(sps); lps = np.ascontiguousarray(lps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168 and lps.dtype.itemsize == 44
+        nb = np.ascontiguousarray(neighbors, np.int32); dk = np.ascontiguousarray(dknn, np.int32)
+        out = np.empty((n, 3), np.float32); sec = C.c_double()
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        if iterations is None:
+            rc = self.L.refcuda_direct(vp(sps), vp(lps), n, nb, nb.shape[1], None, dk, -1, out.reshape(-1), None, None, C.byref(sec))
+            if rc != 0:
+                raise RuntimeError(f"refcuda_direct failed ({rc})")
+            return out, sec.value
+        kn = np.ascontiguousarray(knn, np.int32)
+        blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
+        rc = self.L.refcuda_direct(vp(sps), vp(lps), n, nb, nb.shape[1], vp(kn), dk, iterations, out.reshape(-1), vp(blur), vp(mc), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_direct failed ({rc})")
+        return out, blur[:iterations], mc[:iterations], sec.value
 
     def eval(self, sps, wi):
         """pdf_device / bsdfeval_device of the compiled reference: (pdf (n,), bsdf (n, 3))."""

@@ -135,3 +135,40 @@ extern "C" int refcuda_mis(const void *sps, int n, const int *neighbors, int row
     cudaFree(cu_sps); cudaFree(cu_neighbors); cudaFree(cu_knn);
     return e == cudaSuccess ? 0 : -3;
 }
+
+/// computeDirectScatterAllOnGPU on host arrays (the reference's driver, src/pbsdf.cu:2370-2395; direct: n x 3 floats) and, iterations >= 0,
+/// computeScatterAllOnGPURecordWithDirectOpt (:2488-2540) on its result, as SPoints::computeScatterRadianceAOGWithProcessRecordingAndDirectLightOPT
+/// chains them (include/nori/shadingPoint.h:462-476).
+extern "C" int refcuda_direct(const void *sps, const void *lps, int n, const int *neighbors, int row_ints, const int *knn, const int *dknn,
+                              int iterations, float *direct, float *blur, float *mc, double *seconds) {
+    SPoint *cu_sps = nullptr; LPoint *cu_lps = nullptr; int *cu_neighbors = nullptr, *cu_knn = nullptr, *cu_dknn = nullptr; val3f *cu_direct = nullptr; size_t pitch_n = 0;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) return -1;
+    cudaMemcpy(cu_sps, sps, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_lps, sizeof(LPoint) * (size_t) n); cudaMemcpy(cu_lps, lps, sizeof(LPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    if (cudaMallocPitch((void **) &cu_neighbors, &pitch_n, row_ints * sizeof(int), n) != cudaSuccess) return -2;
+    cudaMemcpy2D(cu_neighbors, pitch_n, neighbors, row_ints * sizeof(int), row_ints * sizeof(int), n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_dknn, sizeof(int) * (size_t) n); cudaMemcpy(cu_dknn, dknn, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_direct, sizeof(val3f) * (size_t) n);
+    ResultSpace ret;
+    if (iterations >= 0) {
+        cudaMalloc((void **) &cu_knn, sizeof(int) * (size_t) n); cudaMemcpy(cu_knn, knn, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice);
+        for (int i = 0; i < iterations; ++i) {
+            ret.blur_results.push_back((val3f *) malloc(sizeof(val3f) * (size_t) n));
+            ret.mc_results.push_back((val3f *) malloc(sizeof(val3f) * (size_t) n));
+        }
+    }
+    cudaDeviceSynchronize();
+    auto t0 = std::chrono::steady_clock::now();
+    computeDirectScatterAllOnGPU(cu_sps, cu_lps, cu_neighbors, cu_dknn, n, row_ints, cu_direct, pitch_n);
+    if (iterations >= 0) computeScatterAllOnGPURecordWithDirectOpt(cu_sps, cu_neighbors, cu_knn, n, iterations, row_ints, cu_direct, ret, pitch_n);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    cudaMemcpy(direct, cu_direct, sizeof(val3f) * (size_t) n, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < iterations; ++i) {
+        std::memcpy(blur + (size_t) i * 3 * n, ret.blur_results[i], sizeof(val3f) * (size_t) n);
+        std::memcpy(mc + (size_t) i * 3 * n, ret.mc_results[i], sizeof(val3f) * (size_t) n);
+        free(ret.blur_results[i]); free(ret.mc_results[i]);
+    }
+    cudaFree(cu_sps); cudaFree(cu_lps); cudaFree(cu_neighbors); cudaFree(cu_knn); cudaFree(cu_dknn); cudaFree(cu_direct);
+    return e == cudaSuccess ? 0 : -3;
+}

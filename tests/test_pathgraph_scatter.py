@@ -17,6 +17,7 @@ import pytest
 from conftest import GOLDEN
 
 REF_NPZ = os.path.join(GOLDEN, "pathgraph_scatter_ref.npz")
+DIRECT_NPZ = os.path.join(GOLDEN, "pathgraph_direct_ref.npz")      # computeDirectScatterAllOnGPU on the same records (--direct)
 RTOL_SUM, RTOL_DET = 2e-4, 2e-5
 
 
@@ -41,6 +42,17 @@ def close_rows(got, want, rtol, what):
 
 def unit(v):
     return (v / np.linalg.norm(v, axis=-1, keepdims=True)).astype(np.float32)
+
+
+def light_records(raw):
+    from nori_b200.gpu import LPOINT_DTYPE
+    return np.ascontiguousarray(raw).view(LPOINT_DTYPE).reshape(-1)
+
+
+def direct_case():
+    """Records, rows and light records of the direct-light fixture."""
+    z, d = np.load(REF_NPZ), np.load(DIRECT_NPZ)
+    return records(z["sc_sps"]), light_records(d["dir_lps"]), z["sc_nb"], d["dir_dknn"], d["dir_out"]
 
 
 # ---- CPU: the oracle ---------------------------------------------------------------------------------------------------
@@ -118,6 +130,44 @@ def test_oracle_mis_gather_vs_reference_vectors(port):
     # the lane order of the product's warps changes the sums by rounding only
     lblur, lmc = port.pathgraph_mis(s, nb, knn, it, sequential=False)
     close_rows(lblur[it - 1], blur[it - 1], 1e-5, "lane order vs list order")
+
+
+def test_oracle_direct_scatter_vs_reference_vectors(port):
+    """computeDirectScatterAllOnGPU of the compiled reference (src/pbsdf.cu:2370-2395) on the fixture's records and rows with seeded
+    light records (a third of them without a light sample, dk counts below the k counts): the restatement agrees to the rounding
+    of the reference's atomics; and on self-only rows it is the closed form L_d f(wi_d) / p_light + L_b f(wi) / p(wi) + L_em."""
+    s, lp, nb, dknn, want = direct_case()
+    assert (dknn <= z_knn()).all() and (dknn < z_knn()).any() and (lp["lightpdf"] == 0).mean() > 0.2
+    m, got = port.pathgraph_direct(s, lp, nb, dknn, sequential=True)
+    close_rows(got, want, RTOL_SUM, "direct vs reference")
+    assert np.isfinite(want).all() and (np.abs(want).sum(1) > 0).mean() > 0.5
+    np.testing.assert_allclose(m[:, 0], dknn * lp["lightpdf"], rtol=2e-6)
+    m2, got2 = port.pathgraph_direct(s, lp, nb, dknn, sequential=False)
+    np.testing.assert_allclose(m2, m, rtol=2e-6, atol=1e-30)
+    close_rows(got2, got, 1e-5, "lane order vs list order")
+    n = len(s); idx = np.arange(n, dtype=np.int32)[:, None].copy()
+    m1, self_only = port.pathgraph_direct(s, lp, idx, np.ones(n, np.int32), sequential=True)
+    pdf, f = port.pathgraph_eval(s, s["wi"]); _, fd = port.pathgraph_eval(s, s["wi_d"])
+    np.testing.assert_array_equal(m1[:, 1], pdf)
+    closed = lp["L_em"].astype(np.float64)
+    a = lp["lightpdf"] > 0; closed[a] += lp["L_directsample"][a] * fd[a] / lp["lightpdf"][a, None]
+    b = pdf > 0; closed[b] += lp["L_bsdfsample"][b] * f[b] / pdf[b, None]
+    close_rows(self_only, closed, 1e-5, "self-only rows vs closed form")
+    # ... and the indirect scatter chained to it (computeScatterAllOnGPURecordWithDirectOpt, :2488-2540): the filtered direct light
+    # takes the place of eLd after EVERY pass, so pass 0 equals the plain driver's and the later ones do not
+    d = np.load(DIRECT_NPZ); z = np.load(REF_NPZ)
+    it = d["dir_blur"].shape[0]
+    _, got3, blur, mc = port.pathgraph_direct(s, lp, nb, dknn, sequential=True, knn=z["sc_knn"], iterations=it)
+    np.testing.assert_array_equal(got3, got)
+    for i in range(it):
+        close_rows(blur[i], d["dir_blur"][i], RTOL_SUM, f"direct-opt blur[{i}]")
+        close_rows(mc[i], d["dir_mc"][i], RTOL_SUM, f"direct-opt mc[{i}]")
+    close_rows(d["dir_blur"][0], z["sc_blur"][0], RTOL_SUM, "pass 0 scatters eLi in both drivers")
+    assert not np.allclose(d["dir_blur"][1], z["sc_blur"][1], rtol=1e-3) and not np.allclose(d["dir_mc"][0], z["sc_mc"][0], rtol=1e-3)
+
+
+def z_knn():
+    return np.load(REF_NPZ)["sc_knn"]
 
 
 def test_oracle_mc_row_is_the_paths_own_estimate(port):
@@ -279,6 +329,84 @@ def test_gpu_path_vertices_carry_the_paths_radiance(gpu_scene, scenes, port):
     dif = (v["bsdf_type"] == b"d") & (v["nidx"] > 0) & (np.abs(mc[0]).sum(1) > 0)
     assert dif.sum() > 10_000
     np.testing.assert_allclose(mc[0][dif] + v["eLd"][dif], v["eLi"][dif], rtol=5e-4, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_gpu_direct_scatter_vs_oracle_and_reference(engine, port):
+    """nori_gpu_pathgraph_direct on the direct-light fixture: equal to the oracle (same evaluations, same marginal sums; the scatter's
+    atomics add in another order) and to the compiled reference's vectors to rounding; rows of one vertex — no two additions to the
+    same address — to the bit, also for synthetic records of all four tags with rows longer than a warp; bad rows are refused."""
+    s, lp, nb, dknn, want = direct_case()
+    got, ms = engine.pathgraph_direct(s, lp, nb, dknn)
+    _, ora = port.pathgraph_direct(s, lp, nb, dknn, sequential=False)
+    close_rows(got, ora, RTOL_SUM, "direct vs oracle")
+    close_rows(got, want, RTOL_SUM, "direct vs reference")
+    n = len(s); idx = np.arange(n, dtype=np.int32)[:, None].copy(); one = np.ones(n, np.int32)
+    got1, _ = engine.pathgraph_direct(s, lp, idx, one)
+    _, ora1 = port.pathgraph_direct(s, lp, idx, one, sequential=False)
+    np.testing.assert_array_equal(got1.view(np.uint32), ora1.view(np.uint32))
+    d = np.load(DIRECT_NPZ); knn = np.load(REF_NPZ)["sc_knn"]; it = d["dir_blur"].shape[0]
+    got3, blur, mc, _ = engine.pathgraph_direct(s, lp, nb, dknn, knn=knn, iterations=it)     # nori_gpu_pathgraph_scatter_direct
+    _, ora3, oblur, omc = port.pathgraph_direct(s, lp, nb, dknn, sequential=False, knn=knn, iterations=it)
+    close_rows(got3, ora, RTOL_SUM, "chained: direct vs oracle")
+    for i in range(it):
+        close_rows(blur[i], oblur[i], RTOL_SUM, f"direct-opt blur[{i}] vs oracle")
+        close_rows(mc[i], omc[i], RTOL_SUM, f"direct-opt mc[{i}] vs oracle")
+        close_rows(blur[i], d["dir_blur"][i], RTOL_SUM, f"direct-opt blur[{i}] vs reference")
+        close_rows(mc[i], d["dir_mc"][i], RTOL_SUM, f"direct-opt mc[{i}] vs reference")
+    # all four tags, long rows, every vertex scattering to distinct targets (a permutation per column: one addition per column and address)
+    t = records(np.load(REF_NPZ)["eval_sps"])[:3000].copy(); n = len(t)
+    rng = np.random.default_rng(9)
+    t["wi_d"] = unit(t["shN"] + rng.normal(size=(n, 3)))
+    from nori_b200.gpu import LPOINT_DTYPE
+    tl = np.zeros(n, LPOINT_DTYPE)
+    tl["L_directsample"] = rng.random((n, 3)); tl["L_bsdfsample"] = rng.random((n, 3)); tl["L_em"] = rng.random((n, 3))
+    tl["lightpdf"] = rng.random(n) * (rng.random(n) < 0.7)
+    k = 40
+    tnb = np.stack([rng.permutation(n) for _ in range(k)], 1).astype(np.int32)
+    tk = rng.integers(0, k + 1, size=n).astype(np.int32)
+    gt, _ = engine.pathgraph_direct(t, tl, tnb, tk)
+    _, ot = port.pathgraph_direct(t, tl, tnb, tk, sequential=False)
+    close_rows(gt, ot, 2e-5, "all tags vs oracle")
+    assert np.isfinite(gt).all() and np.abs(gt).sum() > 0
+    from nori_b200.gpu import NoriGpuError
+    bad = tnb.copy(); bad[7, 0] = n
+    with pytest.raises(NoriGpuError, match="neighbour index"):
+        engine.pathgraph_direct(t, tl, bad, np.maximum(tk, 1))
+    with pytest.raises(NoriGpuError, match="dknn"):
+        engine.pathgraph_direct(t, tl, tnb, tk + k)
+
+
+@pytest.mark.gpu
+def test_gpu_path_vertices_light_records(gpu_scene, scenes, port):
+    """nori_gpu_path_vertices_lights: the LPoint of every vertex beside its SPoint. bsdfpdf = SPoint::pdf; L_bsdfsample = L_em of
+    the path's next vertex; at a path's first vertex off the emitters the estimator's own credit eLd is the light sample under the
+    balance heuristic, L_directsample f(wi_d) / (lightpdf + p(wi_d)), with the tool's evaluations f and p; on an emitter it is L_em;
+    and the records without lights are the ones nori_gpu_path_vertices returns."""
+    e = gpu_scene("cbox_mis"); s = scenes("cbox_mis")
+    e.set_camera(s.sample_to_camera, s.camera_to_world, 160, 120, s.near_clip, s.far_clip)
+    try:
+        v, lp = e.path_vertices(sample_first=0, sample_last=2, lights=True)
+        v0 = e.path_vertices(sample_first=0, sample_last=2)
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+    np.testing.assert_array_equal(v.view(np.uint8), v0.view(np.uint8))
+    assert len(lp) == len(v) > 30_000
+    np.testing.assert_array_equal(lp["bsdfpdf"], v["pdf"])
+    inner = np.nonzero(v["nidx"] > 0)[0]
+    np.testing.assert_array_equal(v["nidx"][inner], inner + 1)
+    np.testing.assert_array_equal(lp["L_bsdfsample"][inner], lp["L_em"][inner + 1])
+    assert (lp["L_bsdfsample"][v["nidx"] == 0] == 0).all()
+    first = np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]])
+    em = first & (lp["L_em"].sum(1) > 0)
+    assert em.sum() > 50
+    np.testing.assert_allclose(v["eLd"][em], lp["L_em"][em], rtol=1e-6)
+    lit = first & ~em & (v["bsdf_type"] == b"d") & (lp["L_directsample"].sum(1) > 0)
+    assert lit.sum() > 5_000 and (lp["lightpdf"][lit] > 0).all()
+    p, f = port.pathgraph_eval(v[lit], v["wi_d"][lit])
+    np.testing.assert_allclose(v["eLd"][lit], lp["L_directsample"][lit] * f / (lp["lightpdf"][lit] + p)[:, None], rtol=3e-4, atol=1e-6)
+    shadowed = first & ~em & (lp["L_directsample"].sum(1) == 0)
+    assert shadowed.sum() > 100 and np.abs(v["eLd"][shadowed]).max() == 0
 
 
 @pytest.mark.gpu
