@@ -54,8 +54,23 @@ def scatter_leg(spp, k, iterations):
                          "staged_calls_wall_ms": t_staged * 1e3, "staged": "nori_gpu_path_vertices (records to the host) + nori_gpu_pathgraph_grid + nori_gpu_pathgraph_filter (records back to the device, result rows to the host)"}
     out["mis"] = {"what": "computeMISAllOnGPURecord (the pg tool's knn mode): pdfsum (k^2 evaluations per vertex) + iterations x (gather, update, lastRun)",
                   "nori_b200_ms_device": mis_ms, "Gevals_per_s_device": (float((knn.astype(np.float64) ** 2).sum()) + float(knn.sum()) * iterations) / mis_ms / 1e6}
+    v3, lp = e.path_vertices(sample_first=0, sample_last=spp, lights=True)
+    dms = []
+    for _ in range(3):
+        direct, dblur, dmc, t = e.pathgraph_direct(v3, lp, nb, dknn, knn=knn, iterations=iterations); dms.append(t)
+    direct_ms = float(np.median(dms[1:]))
+    out["direct"] = {"what": "computeDirectScatterAllOnGPU + computeScatterAllOnGPURecordWithDirectOpt (SPoints::computeScatterRadianceAOGWithProcessRecordingAndDirectLightOPT) "
+                             "on the tracer's own light records", "nori_b200_ms_device": direct_ms,
+                     "vertices_with_light_sample": int((lp["lightpdf"] > 0).sum()), "emitter_hits_by_continuation": int((lp["L_bsdfsample"].sum(1) > 0).sum())}
     if have_refcuda():
         ref = RefCuda()
+        dsec = []
+        for _ in range(2):
+            rdirect, rdblur, rdmc, sec = ref.direct(v3, lp, nb, dknn, knn=knn, iterations=iterations); dsec.append(sec)
+        out["direct"]["reference_ms"] = float(dsec[-1]) * 1e3
+        out["direct"]["speedup_vs_reference_device"] = float(dsec[-1]) * 1e3 / direct_ms
+        out["direct"]["max_rel_row_error_direct"] = float((np.abs(direct - rdirect) / (np.abs(rdirect).max(-1, keepdims=True) + 1e-3)).max())
+        out["direct"]["max_rel_row_error_last_blur"] = float((np.abs(dblur[-1] - rdblur[-1]) / (np.abs(rdblur[-1]).max(-1, keepdims=True) + 1e-3)).max())
         msec = []
         for _ in range(2):
             rmblur, rmmc, sec = ref.mis(v, nb, knn, iterations); msec.append(sec)

@@ -56,6 +56,9 @@ def main():
             nb, knn, dknn, _ = eng.pathgraph_knn(v, hp)
             eng.pathgraph_scatter(v, nb, knn, 2); eng.pathgraph_mis(v, nb, dknn, 2)         # dknn: rows longer than a warp
             eng.pathgraph_filter(v, hp, 1); eng.pathgraph_filter(v, hp, 1, mode="mis")
+            v2, lp = eng.path_vertices(sample_first=0, sample_last=2, lights=True)  # light records + direct-light filter + chained scatter
+            assert len(v2) == len(v)
+            eng.pathgraph_direct(v2, lp, nb, dknn); eng.pathgraph_direct(v2, lp, nb, dknn, knn=knn, iterations=2)
             print("  pathgraph", len(v), "vertices", flush=True)
         if name == "bunny_normals":
             eng.render(stream_mode=0, sample_first=0, sample_last=3)          # block-seeded stream
