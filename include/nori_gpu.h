@@ -339,6 +339,19 @@ int nori_gpu_pathgraph_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, co
 int nori_gpu_pathgraph_scatter_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors,
                                       int row_ints, const int32_t *knn, const int32_t *dknn, int iterations, float *direct, float *blur, float *mc,
                                       float *ms);
+/* SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624), what the `pg` tool runs in its default "opt" mode once the
+ * vertices are clustered (src/cluster.cpp:217): every vertex exchanges light with ALL members of its cluster instead of its k nearest
+ * neighbours. clusters[offsets[c] .. offsets[c + 1]) (the last one up to n_listed) = the members of cluster c, a partition of the vertices
+ * whose SPoint::groupIdx names a cluster (groupIdx = c for a member of c, -1 for a vertex outside every cluster: SaveClusters,
+ * src/pbsdf.cu:987-1006) — the arrays SPoints::loadClusters uploads (shadingPoint.h:626-635). Anything else is refused (NORI_GPU_EINVAL).
+ *   direct = ClusterDirect (src/pbsdf.cu:2400-2446): direct light filtered inside the clusters, each cluster scaled back to the light its
+ *            members sampled (clampDirectCluster / computeRatio / updateComputeCluster) + emission       [m_result.blur_direct]
+ *   blur   = the radiance after `iterations` passes of ClusterIterations3 (:3475-3532): per pass the cluster's dense block
+ *            bsdf_j(wi_i) / pm_i applied to temp[i + 1] (MX), the same scaling, temp = direct + radiance   [blur_results[iterations - 1]]
+ *   mc     = lastRun on the temp the last pass read                                                        [mc_results[iterations - 1]]
+ * each n x 3 floats. The sums inside a cluster are taken in list order here (the reference: float atomics, any order). 1 <= iterations <= 64. */
+int nori_gpu_pathgraph_cluster(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *clusters,
+                               int n_listed, const int32_t *offsets, int n_clusters, int iterations, float *direct, float *blur, float *mc, float *ms);
 /* The tool's whole pipeline in one call, as SPoints::BuildKNN + one of the two drivers run it (include/nori/shadingPoint.h:776-806,
  * 496-510): hash grid + kNN over the records' positions, then the scatter (mode NORI_PG_SCATTER) or the MIS gather (NORI_PG_MIS)
  * on the rows the search left ON THE DEVICE (the k consumer's count knn[i] of each row, as the reference passes cu_knn). Same

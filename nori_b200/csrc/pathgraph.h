@@ -33,6 +33,12 @@ bool launchPathgraphMis(const NoriGpuSPoint *d_sps, int n, const int *d_neighbor
 size_t pgDirectScratchBytes(int n);
 bool launchPathgraphDirect(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_neighbors, int pitchInts, const int *d_knn,
                            void *d_scratch, float *d_direct, cudaStream_t st, std::string &err);
+/// clustered variant (SPoints::ClusterScatterWithDirectOptNR): the lists are validated once, then trusted.
+void launchPathgraphClusterValidate(const NoriGpuSPoint *d_sps, int n, const int *d_clusters, int nListed, const int *d_offsets, int nClusters,
+                                    int *d_listed, int *d_flag2, cudaStream_t st);
+size_t pgClusterScratchBytes(int n, int nClusters);
+bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_clusters, int nListed, const int *d_offsets,
+                            int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
 /// Whole pipeline on the device (nori_gpu_pathgraph_render): bounding box of the records, image composition from first vertices.
 void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bounds6, cudaStream_t st);

@@ -466,6 +466,337 @@ bool launchPathgraphDirect(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lp
     return true;
 }
 
+// ---- clustered variant (the `pg` tool's default "opt" mode after BuildClusters: SPoints::ClusterScatterWithDirectOptNR,
+// include/nori/shadingPoint.h:600-624) --------------------------------------------------------------------------------------
+// The vertices are partitioned into clusters (clusters[offsets[c] ...] = the members of cluster c; SPoint::groupIdx = the vertex's
+// cluster or -1) and every vertex exchanges light with ALL members of its cluster: a dense block per cluster. The reference runs a
+// thread per vertex, stores the block's elements (MatrixElementsNumber / precomputedMatrixElemtns, src/pbsdf.cu:3344-3357, 3535-3553),
+// multiplies with float atomics (MX, :1265-1307) and adds the clusters' in / out sums with more atomics (clampCluster, :2127-2144).
+// Here a WARP owns a cluster: its lanes own the receiving members, the sending members are walked in list order, so every sum of the
+// block — what a member receives, the cluster's in / out totals — is taken inside the warp in a fixed order: no atomics, no stored
+// elements (the K evaluations per member are redone each pass: cheaper on this machine than streaming 12 bytes per element), and
+// results that do not depend on scheduling.
+namespace {
+
+__device__ __forceinline__ int pgClusterSize(const int *__restrict__ offsets, int c, int nClusters, int nListed) {   // getCellSize, :828-834
+    return (c == nClusters - 1 ? nListed : offsets[c + 1]) - offsets[c];
+}
+
+/// What the clustered kernels read of the light records, 16-byte aligned: wi_d, L_directsample | lightpdf, L_bsdfsample | bsdfpdf, L_em | cluster.
+__global__ void k_pgPackLights(const NoriGpuSPoint *__restrict__ sps, const NoriGpuLPoint *__restrict__ lps, int n, float4 *__restrict__ wid,
+                               float4 *__restrict__ Ld, float4 *__restrict__ Lb, float4 *__restrict__ Lem) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const NoriGpuLPoint &l = lps[i];
+    wid[i] = make_float4(sps[i].wi_d[0], sps[i].wi_d[1], sps[i].wi_d[2], 0.f);
+    Ld[i] = make_float4(l.L_directsample[0], l.L_directsample[1], l.L_directsample[2], l.lightpdf);
+    Lb[i] = make_float4(l.L_bsdfsample[0], l.L_bsdfsample[1], l.L_bsdfsample[2], l.bsdfpdf);
+    Lem[i] = make_float4(l.L_em[0], l.L_em[1], l.L_em[2], __int_as_float(sps[i].groupIdx));
+}
+
+/// The lists are trusted by the kernels below. flag bits: 1 = offsets not ascending inside [0, nListed], 2 = a member outside [0, n),
+/// 4 = a member whose groupIdx is not the cluster that lists it, 8 = a vertex listed twice, 16 = a groupIdx outside [-1, nClusters).
+/// listed: cleared array of n ints (members are counted in it); the host compares the number of members with the vertices that name a cluster.
+__global__ void k_pgClusterValidate(const NoriGpuSPoint *__restrict__ sps, int n, const int *__restrict__ clusters, int nListed, const int *__restrict__ offsets,
+                                    int nClusters, int *__restrict__ listed, int *__restrict__ flag, int *__restrict__ nNamed) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid < nClusters) {
+        const int lo = offsets[tid], hi = tid == nClusters - 1 ? nListed : offsets[tid + 1];
+        if (lo < 0 || hi < lo || hi > nListed || (tid == 0 && lo != 0)) { atomicOr(flag, 1); return; }
+        for (int t = lo; t < hi; ++t) {
+            const int j = clusters[t];
+            if (j < 0 || j >= n) { atomicOr(flag, 2); continue; }
+            if (sps[j].groupIdx != tid) atomicOr(flag, 4);
+            if (atomicAdd(listed + j, 1) != 0) atomicOr(flag, 8);
+        }
+    }
+    if (tid < n) {
+        const int g = sps[tid].groupIdx;
+        if (g < -1 || g >= nClusters) atomicOr(flag, 16);
+        else if (g >= 0) atomicAdd(nNamed, 1);
+    }
+}
+
+/// ClusterDirectPdfMarginal (src/pbsdf.cu:1899-1937), clustered branch: for the sending member i, over all members j in list order,
+/// x += lightpdf_i (if wi_d_i lies above j's shading normal) + pdf_j(wi_d_i), y += bsdfpdf_i (if wi_i does) + pdf_j(wi_i).
+/// Lane l takes j = l, l + 32, ...; butterfly over the lanes.
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterDirectMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                                           const float4 *__restrict__ widAll, const float4 *__restrict__ Ld, const float4 *__restrict__ Lb,
+                                                                           const int *__restrict__ clusters, int nListed, const int *__restrict__ offsets, int nClusters,
+                                                                           float2 *__restrict__ dm) {
+    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (c >= nClusters) return;
+    const int m = pgClusterSize(offsets, c, nClusters, nListed);
+    const int *mem = clusters + offsets[c];
+    PgVertex own; int tOwn = -1;
+    if (m <= 32 && lane < m) { tOwn = mem[lane]; pgLoadA(A, tOwn, own); pgLoadB(B, tOwn, own); }     // the usual case: one member per lane, loaded once
+    for (int s = 0; s < m; ++s) {
+        const int i = mem[s];
+        const float4 w4 = wiAll[i], d4 = widAll[i];
+        const float wi[3] = {w4.x, w4.y, w4.z}, wid[3] = {d4.x, d4.y, d4.z};
+        const float lp = Ld[i].w, bp = Lb[i].w;
+        float x = 0.0f, y = 0.0f;
+        auto term = [&](const PgVertex &v) {
+            const float pb = pgPdf(v, wi), pl = pgPdf(v, wid);
+            const float cosh1 = pgDot(wi, v.shN), cosh2 = pgDot(wid, v.shN);
+            if (cosh2 > 0.0f) x += lp;
+            if (cosh1 > 0.0f) y += bp;
+            x += pl; y += pb;
+        };
+        if (m <= 32) { if (lane < m) term(own); }
+        else for (int t = lane; t < m; t += 32) { const int j = mem[t]; PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v); term(v); }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) { x += __shfl_xor_sync(0xffffffffu, x, d); y += __shfl_xor_sync(0xffffffffu, y, d); }
+        if (lane == 0) dm[i] = make_float2(x, y);
+    }
+}
+
+/// Three-channel butterfly: every lane ends with the total (xor 16, 8, 4, 2, 1 — the order the oracle restates).
+__device__ __forceinline__ void pgWarpSum3(float *v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { v[0] += __shfl_xor_sync(0xffffffffu, v[0], d); v[1] += __shfl_xor_sync(0xffffffffu, v[1], d); v[2] += __shfl_xor_sync(0xffffffffu, v[2], d); }
+}
+/// computeRatio (src/pbsdf.cu:2146-2172): a cluster that hands out more than it took in is scaled back, channel by channel.
+__device__ __forceinline__ void pgRatio(const float *in, const float *out, float *ratio) {
+    for (int c = 0; c < 3; ++c) ratio[c] = in[c] < out[c] ? in[c] / out[c] : 1.0f;
+}
+
+/// ClusterDirect for one cluster (src/pbsdf.cu:2400-2446): ClusterDirectRadiance (:1939-2010) — member j receives, from every member i in
+/// list order, L_direct_i bsdf_j(wi_d_i) / x_i + L_bsdf_i bsdf_j(wi_i) / y_i —, clampDirectCluster (:2100-2125: in = sum of the members'
+/// L_directsample and L_bsdfsample, out = sum of what they received), computeRatio, updateComputeCluster, addEmitterToDirectLight.
+/// raw: float4 scratch per vertex (a lane re-reads only what it wrote itself).
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterDirect(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                                   const float4 *__restrict__ widAll, const float4 *__restrict__ Ld, const float4 *__restrict__ Lb,
+                                                                   const float4 *__restrict__ Lem, const float2 *__restrict__ dm, const int *__restrict__ clusters,
+                                                                   int nListed, const int *__restrict__ offsets, int nClusters, float4 *__restrict__ raw,
+                                                                   float4 *__restrict__ direct) {
+    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (c >= nClusters) return;
+    const int m = pgClusterSize(offsets, c, nClusters, nListed);
+    const int *mem = clusters + offsets[c];
+    float in[3] = {0.f, 0.f, 0.f}, out[3] = {0.f, 0.f, 0.f};
+    for (int t0 = 0; t0 < m; t0 += 32) {
+        const int t = t0 + lane;
+        if (t >= m) continue;
+        const int j = mem[t];
+        PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
+        float acc[3] = {0.f, 0.f, 0.f};
+        for (int s = 0; s < m; ++s) {
+            const int i = mem[s];
+            const float2 mg = dm[i];
+            float fin[3] = {0.f, 0.f, 0.f};
+            if (mg.x > 0.0f) {
+                const float inv = (float) (1.0 / (double) mg.x);
+                const float4 d4 = widAll[i], L = Ld[i];
+                const float wid[3] = {d4.x, d4.y, d4.z};
+                float f[3]; pgBsdf(v, wid, f);
+                fin[0] = fin[0] + (L.x * f[0]) * inv; fin[1] = fin[1] + (L.y * f[1]) * inv; fin[2] = fin[2] + (L.z * f[2]) * inv;
+            }
+            if (mg.y > 0.0f) {
+                const float inv = (float) (1.0 / (double) mg.y);
+                const float4 w4 = wiAll[i], L = Lb[i];
+                const float wi[3] = {w4.x, w4.y, w4.z};
+                float f[3]; pgBsdf(v, wi, f);
+                fin[0] = fin[0] + (L.x * f[0]) * inv; fin[1] = fin[1] + (L.y * f[1]) * inv; fin[2] = fin[2] + (L.z * f[2]) * inv;
+            }
+            acc[0] += fin[0]; acc[1] += fin[1]; acc[2] += fin[2];
+        }
+        raw[j] = make_float4(acc[0], acc[1], acc[2], 0.f);
+        out[0] += acc[0]; out[1] += acc[1]; out[2] += acc[2];
+        const float4 a = Ld[j], b = Lb[j];
+        in[0] += a.x; in[1] += a.y; in[2] += a.z;
+        in[0] += b.x; in[1] += b.y; in[2] += b.z;
+    }
+    pgWarpSum3(in); pgWarpSum3(out);
+    float ratio[3]; pgRatio(in, out, ratio);
+    for (int t = lane; t < m; t += 32) {
+        const int j = mem[t];
+        const float4 r = raw[j], e = Lem[j];
+        direct[j] = make_float4(r.x * ratio[0] + e.x, r.y * ratio[1] + e.y, r.z * ratio[2] + e.z, 0.f);
+    }
+}
+/// Vertices outside every cluster keep their own estimate (ClusterDirectRadiance's else branch: eLd) + their emission.
+__global__ void k_pgLooseDirect(const float4 *__restrict__ eLd, const float4 *__restrict__ Lem, int n, float4 *__restrict__ direct) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || __float_as_int(Lem[i].w) != -1) return;
+    const float4 d = eLd[i], e = Lem[i];
+    direct[i] = make_float4(d.x + e.x, d.y + e.y, d.z + e.z, 0.f);
+}
+
+/// allGPUClusterPdfMarginal (src/pbsdf.cu:1239-1263): pm[i] = sum over the members j of i's cluster, except i's predecessor on its
+/// path, of pdf_j(wi_i) rrpdf_j; for a vertex outside every cluster its own pdf_i(wi_i) rrpdf_i.
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                                     const int *__restrict__ clusters, int nListed, const int *__restrict__ offsets, int nClusters,
+                                                                     float *__restrict__ pm) {
+    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (c >= nClusters) return;
+    const int m = pgClusterSize(offsets, c, nClusters, nListed);
+    const int *mem = clusters + offsets[c];
+    PgVertex own;
+    if (m <= 32 && lane < m) { const int j = mem[lane]; pgLoadA(A, j, own); pgLoadB(B, j, own); }
+    for (int s = 0; s < m; ++s) {
+        const int i = mem[s];
+        const float4 w4 = wiAll[i];
+        const float wi[3] = {w4.x, w4.y, w4.z};
+        float sum = 0.0f;
+        if (m <= 32) { if (lane < m && own.nidx != i) sum += pgPdf(own, wi) * own.rrpdf; }
+        else for (int t = lane; t < m; t += 32) {
+            const int j = mem[t];
+            PgVertex v; pgLoadA(A, j, v);
+            if (v.nidx == i) continue;
+            pgLoadB(B, j, v);
+            sum += pgPdf(v, wi) * v.rrpdf;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+        if (lane == 0) pm[i] = sum;
+    }
+}
+__global__ void k_pgLooseMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll, const float4 *__restrict__ Lem,
+                                  int n, float *__restrict__ pm) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || __float_as_int(Lem[i].w) != -1) return;
+    PgVertex v; pgLoadA(A, i, v); pgLoadB(B, i, v);
+    const float4 w4 = wiAll[i];
+    const float wi[3] = {w4.x, w4.y, w4.z};
+    pm[i] = pgPdf(v, wi) * v.rrpdf;
+}
+
+/// One pass over one cluster: MX with the elements of computeNoneZeroElements (src/pbsdf.cu:1265-1307, 1059-1085) — member j receives
+/// (bsdf_j(wi_i) / pm_i) * temp[i + 1] from every member i that has a successor, in list order; the element is 0 where the reference
+/// left its cleared array untouched (pm_i <= 0 or rrpdf_i <= 1e-7) —, clampCluster (:2127-2144: in += temp[i + 1] of those members,
+/// out += what the members received; both totals RUN ON over the passes, as the reference never clears them inside its loop, :3492-3516),
+/// computeRatio, updateComputeCluster, and, when another pass follows, updateWithOptDirectRadiance: tempOut = direct + radiance.
+__global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterPass(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
+                                                                 const float *__restrict__ pm, const int *__restrict__ clusters, int nListed,
+                                                                 const int *__restrict__ offsets, int nClusters, int n, const float4 *__restrict__ tempIn,
+                                                                 const float4 *__restrict__ direct, float4 *__restrict__ clusterIn, float4 *__restrict__ clusterOut,
+                                                                 float4 *__restrict__ radiance, float4 *__restrict__ tempOut) {
+    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (c >= nClusters) return;
+    const int m = pgClusterSize(offsets, c, nClusters, nListed);
+    const int *mem = clusters + offsets[c];
+    float in[3] = {0.f, 0.f, 0.f}, out[3] = {0.f, 0.f, 0.f};
+    for (int t0 = 0; t0 < m; t0 += 32) {
+        const int t = t0 + lane;
+        if (t >= m) continue;
+        const int j = mem[t];
+        PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
+        float acc[3] = {0.f, 0.f, 0.f};
+        for (int s = 0; s < m; ++s) {
+            const int i = mem[s];
+            const float4 a1 = __ldg(A + 4 * (size_t) i + 1), a3 = __ldg(A + 4 * (size_t) i + 3);
+            if (__float_as_int(a3.w) <= 0 || i + 1 >= n) continue;
+            const float p = pm[i];
+            float e[3] = {0.f, 0.f, 0.f};
+            if (p > 0.0f && a1.w > 1e-7f) {
+                const float inv = (float) (1.0 / (double) p);
+                const float4 w4 = wiAll[i];
+                const float wi[3] = {w4.x, w4.y, w4.z};
+                float f[3]; pgBsdf(v, wi, f);
+                e[0] = f[0] * inv; e[1] = f[1] * inv; e[2] = f[2] * inv;
+            }
+            const float4 src = tempIn[i + 1];
+            acc[0] += e[0] * src.x; acc[1] += e[1] * src.y; acc[2] += e[2] * src.z;
+        }
+        radiance[j] = make_float4(acc[0], acc[1], acc[2], 0.f);
+        out[0] += acc[0]; out[1] += acc[1]; out[2] += acc[2];
+        if (v.nidx > 0 && j + 1 < n) { const float4 src = tempIn[j + 1]; in[0] += src.x; in[1] += src.y; in[2] += src.z; }
+    }
+    pgWarpSum3(in); pgWarpSum3(out);
+    const float4 pin = clusterIn[c], pout = clusterOut[c];
+    in[0] = pin.x + in[0]; in[1] = pin.y + in[1]; in[2] = pin.z + in[2];
+    out[0] = pout.x + out[0]; out[1] = pout.y + out[1]; out[2] = pout.z + out[2];
+    float ratio[3]; pgRatio(in, out, ratio);
+    __syncwarp();
+    if (lane == 0) { clusterIn[c] = make_float4(in[0], in[1], in[2], 0.f); clusterOut[c] = make_float4(out[0], out[1], out[2], 0.f); }
+    for (int t = lane; t < m; t += 32) {
+        const int j = mem[t];
+        float4 r = radiance[j];
+        r = make_float4(r.x * ratio[0], r.y * ratio[1], r.z * ratio[2], 0.f);
+        radiance[j] = r;
+        if (tempOut) { const float4 d = direct[j]; tempOut[j] = make_float4(d.x + r.x, d.y + r.y, d.z + r.z, 0.f); }
+    }
+}
+/// The same pass for the vertices outside every cluster (MX's else branch: the vertex's own element, no ratio).
+__global__ void k_pgLoosePass(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll, const float4 *__restrict__ Lem,
+                              const float *__restrict__ pm, int n, const float4 *__restrict__ tempIn, const float4 *__restrict__ direct,
+                              float4 *__restrict__ radiance, float4 *__restrict__ tempOut) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || __float_as_int(Lem[i].w) != -1) return;
+    PgVertex v; pgLoadA(A, i, v); pgLoadB(B, i, v);
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (v.nidx > 0 && i + 1 < n) {
+        const float p = pm[i];
+        float e[3] = {0.f, 0.f, 0.f};
+        if (p > 0.0f && v.rrpdf > 1e-7f) {
+            const float inv = (float) (1.0 / (double) p);
+            const float4 w4 = wiAll[i];
+            const float wi[3] = {w4.x, w4.y, w4.z};
+            float f[3]; pgBsdf(v, wi, f);
+            e[0] = f[0] * inv; e[1] = f[1] * inv; e[2] = f[2] * inv;
+        }
+        const float4 src = tempIn[i + 1];
+        r = make_float4(e[0] * src.x, e[1] * src.y, e[2] * src.z, 0.f);
+    }
+    radiance[i] = r;
+    if (tempOut) { const float4 d = direct[i]; tempOut[i] = make_float4(d.x + r.x, d.y + r.y, d.z + r.z, 0.f); }
+}
+
+} // namespace
+
+void launchPathgraphClusterValidate(const NoriGpuSPoint *d_sps, int n, const int *d_clusters, int nListed, const int *d_offsets, int nClusters,
+                                    int *d_listed, int *d_flag2 /* flag, number of vertices that name a cluster */, cudaStream_t st) {
+    cudaMemsetAsync(d_listed, 0, (size_t) n * sizeof(int), st);
+    cudaMemsetAsync(d_flag2, 0, 2 * sizeof(int), st);
+    const int work = std::max(n, nClusters);
+    k_pgClusterValidate<<<(unsigned) ((work + 255) / 256), 256, 0, st>>>(d_sps, n, d_clusters, nListed, d_offsets, nClusters, d_listed, d_flag2, d_flag2 + 1);
+}
+
+size_t pgClusterScratchBytes(int n, int nClusters) {
+    // A, B, wi, eLi, eLd (pack) + wid, Ld, Lb, Lem + direct, tempA, tempB, radiance (16 each) + dm (8) + pm (4) per vertex; in / out per cluster
+    return (size_t) n * (64 + 48 + 3 * 16 + 4 * 16 + 4 * 16 + 8 + 4) + (size_t) nClusters * 32 + 256;
+}
+
+/// SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624): ClusterDirect, then ClusterIterations3 (src/pbsdf.cu:3475-3532)
+/// on the same clusters. d_direct / d_blur / d_mc: n x 3 floats (device): the filtered direct light, the last pass's radiance
+/// (ret.blur_results[iterations - 1]) and lastRun on the temp that pass read (ret.mc_results[iterations - 1]). iterations >= 1.
+bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_clusters, int nListed, const int *d_offsets,
+                            int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err) {
+    if (n <= 0 || nClusters < 0 || iterations < 1) { err = "pathgraph_cluster: bad sizes"; return false; }
+    float4 *A = static_cast<float4 *>(d_scratch), *B = A + 4 * (size_t) n, *wi = B + 3 * (size_t) n, *eLi = wi + n, *eLd = eLi + n;
+    float4 *wid = eLd + n, *Ld = wid + n, *Lb = Ld + n, *Lem = Lb + n, *direct = Lem + n, *tempA = direct + n, *tempB = tempA + n, *radiance = tempB + n;
+    float4 *cin = radiance + n, *cout = cin + nClusters;
+    float2 *dm = reinterpret_cast<float2 *>(cout + nClusters);
+    float *pm = reinterpret_cast<float *>(dm + n);
+    const unsigned gt = (unsigned) ((n + 255) / 256), gc = (unsigned) ((nClusters + kPgWarps - 1) / kPgWarps);
+    k_pgPack<<<gt, 256, 0, st>>>(d_sps, n, A, B, wi, eLi, eLd);
+    k_pgPackLights<<<gt, 256, 0, st>>>(d_sps, d_lps, n, wid, Ld, Lb, Lem);
+    if (nClusters > 0) {
+        k_pgClusterDirectMarginal<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, wid, Ld, Lb, d_clusters, nListed, d_offsets, nClusters, dm);
+        k_pgClusterDirect<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, wid, Ld, Lb, Lem, dm, d_clusters, nListed, d_offsets, nClusters, radiance, direct);
+        k_pgClusterMarginal<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, d_clusters, nListed, d_offsets, nClusters, pm);
+        cudaMemsetAsync(cin, 0, (size_t) nClusters * 2 * sizeof(float4), st);
+    }
+    k_pgLooseDirect<<<gt, 256, 0, st>>>(eLd, Lem, n, direct);
+    k_pgLooseMarginal<<<gt, 256, 0, st>>>(A, B, wi, Lem, n, pm);
+    k_pgUnpack<<<gt, 256, 0, st>>>(direct, d_direct, n);
+    const float4 *tin = eLi;                                 // updateRadiance(..., 0): temp = eLi
+    for (int it = 0; it < iterations; ++it) {
+        float4 *tout = it == iterations - 1 ? nullptr : ((it & 1) ? tempB : tempA);
+        if (nClusters > 0)
+            k_pgClusterPass<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, pm, d_clusters, nListed, d_offsets, nClusters, n, tin, direct, cin, cout, radiance, tout);
+        k_pgLoosePass<<<gt, 256, 0, st>>>(A, B, wi, Lem, pm, n, tin, direct, radiance, tout);
+        if (tout) tin = tout;
+    }
+    k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_blur, n);
+    k_pgLastRun<<<gt, 256, 0, st>>>(A, B, wi, tin, radiance, n);
+    k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_mc, n);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("pathgraph_cluster: ") + cudaGetErrorString(e); return false; }
+    return true;
+}
+
 unsigned pathgraphScatterChecks(unsigned *line) { return fetchChecks(line); }
 
 } // namespace ng

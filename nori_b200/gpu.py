@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
 ]
 
 
@@ -143,6 +143,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_path_vertices.argtypes = [vp, C.POINTER(RenderDesc), vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_path_vertices_lights.argtypes = [vp, C.POINTER(RenderDesc), vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_pathgraph_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
+    L.nori_gpu_pathgraph_cluster.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_scatter_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_grid.argtypes = [vp, C.c_uint64, ip, vp, ip, ip, C.POINTER(HashParams)]
@@ -397,6 +398,20 @@ class Engine:
         self._ck(self.L.nori_gpu_pathgraph_scatter_direct(self.h, _p(pts), _p(lps), n, _p(nb), nb.shape[1], _p(kn), _p(dk), int(iterations),
                                                           _p(out), _p(blur), _p(mc), C.byref(ms)))
         return out, blur, mc, ms.value
+
+    def pathgraph_cluster(self, points, lights, clusters, offsets, iterations: int, cluster_of=None):
+        """SPoints::ClusterScatterWithDirectOptNR (the pg tool's default mode on given clusters): members of cluster c =
+        clusters[offsets[c]:offsets[c + 1]]; points["groupIdx"] = the vertex's cluster or -1 (cluster_of, if given, replaces it in a
+        copy). Returns (direct (n, 3), blur (n, 3), mc (n, 3), ms)."""
+        assert points.dtype == SPOINT_DTYPE and lights.dtype == LPOINT_DTYPE
+        pts = np.ascontiguousarray(points); lps = np.ascontiguousarray(lights); n = pts.shape[0]
+        if cluster_of is not None:
+            pts = pts.copy(); pts["groupIdx"] = np.asarray(cluster_of, np.int32)
+        cl = np.ascontiguousarray(clusters, np.int32).reshape(-1); off = np.ascontiguousarray(offsets, np.int32).reshape(-1)
+        direct = np.empty((n, 3), np.float32); blur = np.empty((n, 3), np.float32); mc = np.empty((n, 3), np.float32); ms = C.c_float()
+        self._ck(self.L.nori_gpu_pathgraph_cluster(self.h, _p(pts), _p(lps), n, _p(cl) if len(cl) else None, len(cl), _p(off) if len(off) else None, len(off),
+                                                   int(iterations), _p(direct), _p(blur), _p(mc), C.byref(ms)))
+        return direct, blur, mc, ms.value
 
     def pathgraph_knn(self, points, hp: "HashParams"):
         """buildHashGridAndFindKNN: points = (n, 3) float32 or an SPoint record array. Returns (neighbors, knn, dknn, ms)."""

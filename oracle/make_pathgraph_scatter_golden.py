@@ -70,7 +70,51 @@ def main_direct(out):
     print("wrote", out, len(v), "records; rows with light", int((np.abs(direct).sum(1) > 0).sum()), "non-finite", int((~np.isfinite(direct)).any(1).sum()))
 
 
+def grid_clusters(pos, cells, max_size, loose, seed):
+    """A clustering for the fixtures and benches (NOT the reference's BuildClusters, whose seeds come from libstdc++'s random_shuffle):
+    vertices sorted by grid cell, every cell's run cut into clusters of at most max_size members; a fraction `loose` stays outside
+    every cluster. Returns (cluster_of (n,), clusters, offsets) in the layout SPoints::loadClusters uploads."""
+    rng = np.random.default_rng(seed)
+    n = len(pos)
+    lo, hi = pos.min(0), pos.max(0)
+    cell = np.minimum(((pos - lo) / np.maximum(hi - lo, 1e-20) * cells).astype(np.int64), cells - 1)
+    key = (cell[:, 0] * cells + cell[:, 1]) * cells + cell[:, 2]
+    inside = np.nonzero(rng.random(n) >= loose)[0]
+    order = inside[np.argsort(key[inside], kind="stable")]
+    k = key[order]
+    cluster_of = np.full(n, -1, np.int32); offsets = []; c = 0; a = 0
+    while a < len(order):
+        b = a + 1
+        size = int(rng.integers(1, max_size + 1))
+        while b < len(order) and k[b] == k[a] and b - a < size:
+            b += 1
+        offsets.append(a); cluster_of[order[a:b]] = c; c += 1; a = b
+    return cluster_of, order.astype(np.int32), np.asarray(offsets, np.int32)
+
+
+def main_cluster(out):
+    """(cl_*) SPoints::ClusterScatterWithDirectOptNR's drivers (ClusterDirect, precomputedMatrixElemtns, ClusterIterations3) on the committed
+    fixture's records with seeded light records and a seeded grid clustering (members up to 45 per cluster: more than a warp; 6 % of the
+    vertices outside every cluster): python oracle/make_pathgraph_scatter_golden.py --cluster [out.npz]."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "pathgraph_scatter_ref.npz"))
+    v = np.ascontiguousarray(z["sc_sps"]).view(SPOINT_DTYPE).reshape(-1).copy()
+    lp = synthetic_lights(len(v), 31)
+    cluster_of, clusters, offsets = grid_clusters(v["pos"], 6, 45, 0.06, 37)
+    v["groupIdx"] = cluster_of
+    ref = RefCuda()
+    res = {"cl_of": cluster_of, "cl_members": clusters, "cl_offsets": offsets, "cl_lps": lp.view(np.uint8).reshape(len(lp), 44)}
+    for it in (1, 3):
+        d, b, m, _ = ref.cluster(v, lp, clusters, offsets, it)
+        res[f"cl_direct_{it}"] = d; res[f"cl_blur_{it}"] = b; res[f"cl_mc_{it}"] = m
+    np.savez_compressed(out, **res)
+    sizes = np.diff(np.append(offsets, len(clusters)))
+    print("wrote", out, len(v), "records,", len(offsets), "clusters, sizes", int(sizes.min()), "..", int(sizes.max()), "loose", int((cluster_of < 0).sum()),
+          "non-finite", int((~np.isfinite(res["cl_blur_3"])).any(1).sum()))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--cluster":
+        return main_cluster(sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "pathgraph_cluster_ref.npz"))
     if len(sys.argv) > 1 and sys.argv[1] == "--direct":
         return main_direct(sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "pathgraph_direct_ref.npz"))
     out = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "pathgraph_scatter_ref.npz")

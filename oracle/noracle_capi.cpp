@@ -323,6 +323,12 @@ void noracle_pathgraph_direct(const void *sps, const void *lps, int n, const int
     if (iterations >= 0)
         pathgraphScatter(static_cast<const SPointRec *>(sps), n, neighbors, row_ints, knn, iterations, sequential != 0, nullptr, blur, mc, direct);
 }
+/// The clustered variant (SPoints::ClusterScatterWithDirectOptNR on given clusters). direct / blur / mc: n x 3.
+void noracle_pathgraph_cluster(const void *sps, const void *lps, int n, const int32_t *clusters, int n_listed, const int32_t *offsets, int n_clusters,
+                               int iterations, int sequential, float *direct, float *blur, float *mc) {
+    pathgraphCluster(static_cast<const SPointRec *>(sps), static_cast<const LPointRec *>(lps), n, clusters, n_listed, offsets, n_clusters, iterations,
+                     sequential != 0, direct, blur, mc);
+}
 /// The tool's evaluations at one vertex each: pdf[i] = pdf_device(sps[i], wi[i]), bsdf[i] = bsdfeval_device(sps[i], wi[i]).
 void noracle_pathgraph_eval(const void *sps, int n, const float *wi, float *pdf, float *bsdf) {
     const SPointRec *p = static_cast<const SPointRec *>(sps);

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <functional>
 #include <vector>
 
 namespace noracle {
@@ -349,6 +350,127 @@ inline void pathgraphDirect(const SPointRec *sps, const LPointRec *lps, int n, c
         }
     }
     for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) direct[3 * (size_t) i + c] += lps[i].L_em[c];
+}
+
+
+/// SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624) on given clusters: ClusterDirect (src/pbsdf.cu:2400-2446:
+/// ClusterDirectPdfMarginal :1899-1937, ClusterDirectRadiance :1939-2010, clampDirectCluster :2100-2125, computeRatio :2146-2172,
+/// updateComputeCluster :2174-2183, addEmitterToDirectLight :813-818), then the elements of computeNoneZeroElements (:1059-1085) with
+/// allGPUClusterPdfMarginal (:1239-1263) applied by ClusterIterations3 (:3475-3532: MX :1265-1307, clampCluster :2127-2144 with totals that
+/// run on over the passes, updateWithOptDirectRadiance, lastRun). clusters[offsets[c] ..] = members of cluster c (the last up to nListed),
+/// sps[i].groupIdx = i's cluster or -1. What a member receives is added in list order of the senders. `sequential`: every other sum in
+/// list order too (one thread's order in the reference; its atomics have none); otherwise as the product's warp takes them: lane l adds the
+/// members l, l + 32, ..., butterfly over the lanes, the clusters' running totals + the pass's sum.
+inline void pathgraphCluster(const SPointRec *sps, const LPointRec *lps, int n, const int32_t *clusters, int nListed, const int32_t *offsets, int nClusters,
+                             int iterations, bool sequential, float *direct, float *blur, float *mc) {
+    using namespace pgs;
+    auto size = [&](int c) { return (c == nClusters - 1 ? nListed : offsets[c + 1]) - offsets[c]; };
+    auto butterfly = [](float *lane) {
+        for (int d = 16; d > 0; d >>= 1) { float nxt[32]; for (int l = 0; l < 32; ++l) nxt[l] = lane[l] + lane[l ^ d]; std::memcpy(lane, nxt, sizeof nxt); }
+        return lane[0];
+    };
+    // sum of term(t) over t < m: list order, or lane-strided partial sums + butterfly
+    auto total = [&](int m, const std::function<void(int, float &)> &term) {
+        if (sequential) { float s = 0.0f; for (int t = 0; t < m; ++t) term(t, s); return s; }
+        float lane[32];
+        for (int l = 0; l < 32; ++l) { float s = 0.0f; for (int t = l; t < m; t += 32) term(t, s); lane[l] = s; }
+        return butterfly(lane);
+    };
+    auto ratioOf = [](float in, float out) { return in < out ? in / out : 1.0f; };
+    std::vector<float> dm(2 * (size_t) n, 0.0f), pm(n, 0.0f), raw(3 * (size_t) n, 0.0f), rad(3 * (size_t) n, 0.0f), temp(3 * (size_t) n), next(3 * (size_t) n);
+    std::vector<float> cin(3 * (size_t) std::max(nClusters, 1), 0.0f), cout(3 * (size_t) std::max(nClusters, 1), 0.0f);
+    // ---- direct light
+    for (int c = 0; c < nClusters; ++c) {
+        const int32_t *mem = clusters + offsets[c]; const int m = size(c);
+        for (int s = 0; s < m; ++s) {
+            const int i = mem[s];
+            dm[2 * (size_t) i] = total(m, [&](int t, float &x) {
+                const SPointRec &o = sps[mem[t]];
+                if (cdot(sps[i].wi_d, o.shN) > 0.0f) x += lps[i].lightpdf;
+                x += pdfAt(o, sps[i].wi_d); });
+            dm[2 * (size_t) i + 1] = total(m, [&](int t, float &y) {
+                const SPointRec &o = sps[mem[t]];
+                if (cdot(sps[i].wi, o.shN) > 0.0f) y += lps[i].bsdfpdf;
+                y += pdfAt(o, sps[i].wi); });
+        }
+        for (int t = 0; t < m; ++t) {
+            const int j = mem[t];
+            float acc[3] = {0.0f, 0.0f, 0.0f};
+            for (int s = 0; s < m; ++s) {
+                const int i = mem[s];
+                const float mx = dm[2 * (size_t) i], my = dm[2 * (size_t) i + 1];
+                float fin[3] = {0.0f, 0.0f, 0.0f};
+                if (mx > 0.0f) { const float inv = (float) (1.0 / (double) mx); float f[3]; bsdfAt(sps[j], sps[i].wi_d, f); for (int k = 0; k < 3; ++k) fin[k] = fin[k] + (lps[i].L_directsample[k] * f[k]) * inv; }
+                if (my > 0.0f) { const float inv = (float) (1.0 / (double) my); float f[3]; bsdfAt(sps[j], sps[i].wi, f); for (int k = 0; k < 3; ++k) fin[k] = fin[k] + (lps[i].L_bsdfsample[k] * f[k]) * inv; }
+                for (int k = 0; k < 3; ++k) acc[k] += fin[k];
+            }
+            for (int k = 0; k < 3; ++k) raw[3 * (size_t) j + k] = acc[k];
+        }
+        float ratio[3];
+        for (int k = 0; k < 3; ++k) {
+            const float in = total(m, [&](int t, float &a) { a += lps[mem[t]].L_directsample[k]; a += lps[mem[t]].L_bsdfsample[k]; });
+            const float out = total(m, [&](int t, float &a) { a += raw[3 * (size_t) mem[t] + k]; });
+            ratio[k] = ratioOf(in, out);
+        }
+        for (int t = 0; t < m; ++t) for (int k = 0; k < 3; ++k) direct[3 * (size_t) mem[t] + k] = raw[3 * (size_t) mem[t] + k] * ratio[k] + lps[mem[t]].L_em[k];
+    }
+    for (int i = 0; i < n; ++i) if (sps[i].groupIdx == -1) for (int k = 0; k < 3; ++k) direct[3 * (size_t) i + k] = sps[i].eLd[k] + lps[i].L_em[k];
+    // ---- densities of the continuation directions inside the clusters
+    for (int c = 0; c < nClusters; ++c) {
+        const int32_t *mem = clusters + offsets[c]; const int m = size(c);
+        for (int s = 0; s < m; ++s) {
+            const int i = mem[s];
+            pm[i] = total(m, [&](int t, float &a) { const SPointRec &o = sps[mem[t]]; if (o.nidx == i) return; a += pdfAt(o, sps[i].wi) * o.rrpdf; });
+        }
+    }
+    for (int i = 0; i < n; ++i) if (sps[i].groupIdx == -1) pm[i] = pdfAt(sps[i], sps[i].wi) * sps[i].rrpdf;
+    // ---- passes
+    auto element = [&](int i, int j, float *e) {          // what computeNoneZeroElements stores for sender i, receiver j (0 where it writes nothing)
+        e[0] = e[1] = e[2] = 0.0f;
+        if (pm[i] > 0.0f && sps[i].rrpdf > 1e-7f) { const float inv = (float) (1.0 / (double) pm[i]); float f[3]; bsdfAt(sps[j], sps[i].wi, f); for (int k = 0; k < 3; ++k) e[k] = f[k] * inv; }
+    };
+    for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) temp[3 * (size_t) i + k] = sps[i].eLi[k];
+    for (int it = 0; it < iterations; ++it) {
+        for (int c = 0; c < nClusters; ++c) {
+            const int32_t *mem = clusters + offsets[c]; const int m = size(c);
+            for (int t = 0; t < m; ++t) {
+                const int j = mem[t];
+                float acc[3] = {0.0f, 0.0f, 0.0f};
+                for (int s = 0; s < m; ++s) {
+                    const int i = mem[s];
+                    if (sps[i].nidx <= 0 || i + 1 >= n) continue;
+                    float e[3]; element(i, j, e);
+                    for (int k = 0; k < 3; ++k) acc[k] += e[k] * temp[3 * (size_t) (i + 1) + k];
+                }
+                for (int k = 0; k < 3; ++k) rad[3 * (size_t) j + k] = acc[k];
+            }
+            for (int k = 0; k < 3; ++k) {
+                const float in = total(m, [&](int t, float &a) { const int i = mem[t]; if (sps[i].nidx > 0 && i + 1 < n) a += temp[3 * (size_t) (i + 1) + k]; });
+                const float out = total(m, [&](int t, float &a) { a += rad[3 * (size_t) mem[t] + k]; });
+                cin[3 * (size_t) c + k] = cin[3 * (size_t) c + k] + in; cout[3 * (size_t) c + k] = cout[3 * (size_t) c + k] + out;
+                const float ratio = ratioOf(cin[3 * (size_t) c + k], cout[3 * (size_t) c + k]);
+                for (int t = 0; t < m; ++t) rad[3 * (size_t) mem[t] + k] *= ratio;
+            }
+        }
+        for (int i = 0; i < n; ++i) if (sps[i].groupIdx == -1) {
+            float e[3] = {0.0f, 0.0f, 0.0f};
+            const bool has = sps[i].nidx > 0 && i + 1 < n;
+            if (has) element(i, i, e);
+            for (int k = 0; k < 3; ++k) rad[3 * (size_t) i + k] = has ? e[k] * temp[3 * (size_t) (i + 1) + k] : 0.0f;
+        }
+        if (it != iterations - 1) { for (size_t q = 0; q < 3 * (size_t) n; ++q) next[q] = direct[q] + rad[q]; temp.swap(next); }
+    }
+    std::memcpy(blur, rad.data(), sizeof(float) * 3 * (size_t) n);
+    for (int i = 0; i < n; ++i) {
+        mc[3 * (size_t) i] = mc[3 * (size_t) i + 1] = mc[3 * (size_t) i + 2] = 0.0f;
+        const SPointRec &sp = sps[i];
+        const float spdf = pdfAt(sp, sp.wi);
+        if (spdf > 0.0f && sp.nidx > 0 && i + 1 < n) {
+            const float inv = (float) (1.0 / (double) (spdf * sp.rrpdf));
+            float f[3]; bsdfAt(sp, sp.wi, f);
+            for (int k = 0; k < 3; ++k) mc[3 * (size_t) i + k] = (temp[3 * (size_t) (i + 1) + k] * f[k]) * inv;
+        }
+    }
 }
 
 } // namespace noracle

@@ -165,6 +165,7 @@ class Port:
         L.noracle_pathgraph_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p]
+        L.noracle_pathgraph_cluster.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, C.c_void_p, _i32p, C.c_int, C.c_int, _f32p, _f32p, C.c_void_p, C.c_void_p]
 
     def pathgraph_knn(self, pts, dim, cellsize, minb, k, dk):
@@ -208,6 +209,17 @@ class Port:
         blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
         self.L.noracle_pathgraph_direct(vp(sps), vp(lps), n, nb, nb.shape[1], vp(kn), dk, iterations, int(sequential), m.reshape(-1), out.reshape(-1), vp(blur), vp(mc))
         return m, out, blur[:iterations], mc[:iterations]
+
+    def pathgraph_cluster(self, sps, lps, clusters, offsets, iterations, sequential=False):
+        """SPoints::ClusterScatterWithDirectOptNR restated: (direct, blur, mc), each (n, 3). sps["groupIdx"] = cluster or -1."""
+        sps = np.ascontiguousarray(sps); lps = np.ascontiguousarray(lps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168 and lps.dtype.itemsize == 44 and lps.shape[0] == n and iterations >= 1
+        cl = np.ascontiguousarray(clusters, np.int32).reshape(-1); off = np.ascontiguousarray(offsets, np.int32).reshape(-1)
+        cl_ = cl if len(cl) else np.zeros(1, np.int32); off_ = off if len(off) else np.zeros(1, np.int32)
+        d = np.empty((n, 3), np.float32); b = np.empty((n, 3), np.float32); m = np.empty((n, 3), np.float32)
+        self.L.noracle_pathgraph_cluster(sps.ctypes.data_as(C.c_void_p), lps.ctypes.data_as(C.c_void_p), n, cl_, len(cl), off_, len(off), iterations,
+                                         int(sequential), d.reshape(-1), b.reshape(-1), m.reshape(-1))
+        return d, b, m
 
     def pathgraph_eval(self, sps, wi):
         """pdf_device / bsdfeval_device restated: (pdf (n,), bsdf (n, 3)) of record i for direction wi[i]."""
@@ -279,6 +291,8 @@ class RefCuda:
         self.L.refcuda_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         self.L.refcuda_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
         self.L.refcuda_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_double)]
+        if hasattr(self.L, 'refcuda_cluster'):
+            self.L.refcuda_cluster.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         if hasattr(self.L, 'refcuda_direct'):
             self.L.refcuda_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, C.c_void_p, _i32p, C.c_int, _f32p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
 
@@ -333,6 +347,18 @@ class RefCuda:
         if rc != 0:
             raise RuntimeError(f"refcuda_direct failed ({rc})")
         return out, blur[:iterations], mc[:iterations], sec.value
+
+    def cluster(self, sps, lps, clusters, offsets, iterations):
+        """SPoints::ClusterScatterWithDirectOptNR's drivers on given clusters: (direct, blur, mc, seconds)."""
+        sps = np.ascontiguousarray(sps); lps = np.ascontiguousarray(lps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168 and lps.dtype.itemsize == 44
+        cl = np.ascontiguousarray(clusters, np.int32).reshape(-1); off = np.ascontiguousarray(offsets, np.int32).reshape(-1)
+        d = np.empty((n, 3), np.float32); b = np.empty((n, 3), np.float32); m = np.empty((n, 3), np.float32); sec = C.c_double()
+        rc = self.L.refcuda_cluster(sps.ctypes.data_as(C.c_void_p), lps.ctypes.data_as(C.c_void_p), n, cl, len(cl), off, len(off), iterations,
+                                    d.reshape(-1), b.reshape(-1), m.reshape(-1), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_cluster failed ({rc})")
+        return d, b, m, sec.value
 
     def eval(self, sps, wi):
         """pdf_device / bsdfeval_device of the compiled reference: (pdf (n,), bsdf (n, 3))."""

@@ -172,3 +172,49 @@ extern "C" int refcuda_direct(const void *sps, const void *lps, int n, const int
     cudaFree(cu_sps); cudaFree(cu_lps); cudaFree(cu_neighbors); cudaFree(cu_knn); cudaFree(cu_dknn); cudaFree(cu_direct);
     return e == cudaSuccess ? 0 : -3;
 }
+
+// ---- clustered variant ------------------------------------------------------------------------------------------------------------
+// The drivers below read three __constant__ sizes that only the reference's cluster BUILDERS set (src/pbsdf.cu:3047-3049, 3259, 3331);
+// with given clusters (SPoints::loadClusters, shadingPoint.h:626-635 — which leaves them unset too) this glue sets them itself.
+extern __constant__ int d_sizeofsp;              // src/pbsdf.cu:36-42
+extern __constant__ int d_num_clusters;
+extern __constant__ int d_num_clusters_point;
+
+/// SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624) on host arrays: ClusterDirect, MatrixElementsNumber,
+/// precomputedMatrixElemtns, ClusterIterations3. sps[i].groupIdx = cluster of i or -1. direct / blur / mc: n x 3 floats.
+extern "C" int refcuda_cluster(const void *sps, const void *lps, int n, const int *clusters, int n_listed, const int *offsets, int n_clusters,
+                               int iterations, float *direct, float *blur, float *mc, double *seconds) {
+    SPoint *cu_sps = nullptr; LPoint *cu_lps = nullptr; int *cu_clusters = nullptr, *cu_offsets = nullptr; val3f *cu_direct = nullptr;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) return -1;
+    cudaMemcpy(cu_sps, sps, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_lps, sizeof(LPoint) * (size_t) n); cudaMemcpy(cu_lps, lps, sizeof(LPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_clusters, sizeof(int) * (size_t) n_listed); cudaMemcpy(cu_clusters, clusters, sizeof(int) * (size_t) n_listed, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_offsets, sizeof(int) * (size_t) n_clusters); cudaMemcpy(cu_offsets, offsets, sizeof(int) * (size_t) n_clusters, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_direct, sizeof(val3f) * (size_t) n);
+    cudaMemcpyToSymbol(d_sizeofsp, &n, sizeof(int));
+    cudaMemcpyToSymbol(d_num_clusters, &n_clusters, sizeof(int));
+    cudaMemcpyToSymbol(d_num_clusters_point, &n_listed, sizeof(int));
+    ResultSpace ret;
+    for (int i = 0; i < iterations; ++i) {
+        ret.blur_results.push_back((val3f *) calloc((size_t) n, sizeof(val3f)));
+        ret.mc_results.push_back((val3f *) calloc((size_t) n, sizeof(val3f)));
+    }
+    cudaDeviceSynchronize();
+    auto t0 = std::chrono::steady_clock::now();
+    ClusterDirect(cu_sps, cu_lps, cu_clusters, cu_offsets, n, n_clusters, cu_direct);
+    size_t *cu_element_offset = nullptr;
+    cudaMalloc((void **) &cu_element_offset, sizeof(size_t) * (size_t) n);
+    const size_t elements = MatrixElementsNumber(cu_sps, cu_offsets, n_clusters, cu_element_offset, n);
+    val3f *cu_elements = nullptr;
+    if (cudaMalloc((void **) &cu_elements, sizeof(val3f) * elements) != cudaSuccess) return -2;
+    precomputedMatrixElemtns(cu_sps, cu_clusters, cu_offsets, cu_element_offset, n_clusters, n, (int) elements, cu_elements);
+    ClusterIterations3(cu_sps, cu_clusters, cu_offsets, n_clusters, cu_element_offset, n, cu_elements, cu_direct, iterations, ret);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    cudaMemcpy(direct, cu_direct, sizeof(val3f) * (size_t) n, cudaMemcpyDeviceToHost);
+    std::memcpy(blur, ret.blur_results[iterations - 1], sizeof(val3f) * (size_t) n);
+    std::memcpy(mc, ret.mc_results[iterations - 1], sizeof(val3f) * (size_t) n);
+    for (int i = 0; i < iterations; ++i) { free(ret.blur_results[i]); free(ret.mc_results[i]); }
+    cudaFree(cu_sps); cudaFree(cu_lps); cudaFree(cu_clusters); cudaFree(cu_offsets); cudaFree(cu_direct); cudaFree(cu_element_offset); cudaFree(cu_elements);
+    return e == cudaSuccess ? 0 : -3;
+}

@@ -59,6 +59,10 @@ def main():
             v2, lp = eng.path_vertices(sample_first=0, sample_last=2, lights=True)  # light records + direct-light filter + chained scatter
             assert len(v2) == len(v)
             eng.pathgraph_direct(v2, lp, nb, dknn); eng.pathgraph_direct(v2, lp, nb, dknn, knn=knn, iterations=2)
+            order = np.argsort(np.floor(v2["pos"] * 3).astype(np.int64) @ np.array([1, 64, 4096]), kind="stable").astype(np.int32)   # clusters: runs of 40 in cell order
+            offs = np.arange(0, len(order) - 100, 40, dtype=np.int32)                                                              # ... the last one long, 0 loose
+            of = np.empty(len(order), np.int32); of[order] = np.minimum(np.arange(len(order)) // 40, len(offs) - 1)
+            eng.pathgraph_cluster(v2, lp, order, offs, 2, cluster_of=of)
             print("  pathgraph", len(v), "vertices", flush=True)
         if name == "bunny_normals":
             eng.render(stream_mode=0, sample_first=0, sample_last=3)          # block-seeded stream

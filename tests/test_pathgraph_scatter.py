@@ -17,6 +17,7 @@ import pytest
 from conftest import GOLDEN
 
 REF_NPZ = os.path.join(GOLDEN, "pathgraph_scatter_ref.npz")
+CLUSTER_NPZ = os.path.join(GOLDEN, "pathgraph_cluster_ref.npz")    # ClusterScatterWithDirectOptNR's drivers on the same records (--cluster)
 DIRECT_NPZ = os.path.join(GOLDEN, "pathgraph_direct_ref.npz")      # computeDirectScatterAllOnGPU on the same records (--direct)
 RTOL_SUM, RTOL_DET = 2e-4, 2e-5
 
@@ -164,6 +165,45 @@ def test_oracle_direct_scatter_vs_reference_vectors(port):
         close_rows(mc[i], d["dir_mc"][i], RTOL_SUM, f"direct-opt mc[{i}]")
     close_rows(d["dir_blur"][0], z["sc_blur"][0], RTOL_SUM, "pass 0 scatters eLi in both drivers")
     assert not np.allclose(d["dir_blur"][1], z["sc_blur"][1], rtol=1e-3) and not np.allclose(d["dir_mc"][0], z["sc_mc"][0], rtol=1e-3)
+
+
+def cluster_case():
+    """Records (groupIdx = cluster or -1), light records, member lists and offsets of the clustered fixture."""
+    z, c = np.load(REF_NPZ), np.load(CLUSTER_NPZ)
+    s = records(z["sc_sps"]).copy(); s["groupIdx"] = c["cl_of"]
+    return s, light_records(c["cl_lps"]), c["cl_members"], c["cl_offsets"], c
+
+
+def test_oracle_cluster_scatter_vs_reference_vectors(port):
+    """SPoints::ClusterScatterWithDirectOptNR's drivers of the compiled reference (ClusterDirect, precomputedMatrixElemtns, ClusterIterations3:
+    the `pg` tool's default mode once the clusters exist) on the fixture's records with a seeded clustering — 321 clusters of 1 .. 45
+    members, 6 % of the vertices outside every cluster — for 1 and 3 passes. All its sums are float atomics: rows agree to rounding. And
+    with every vertex a cluster of its own the direct part is the closed form min(1, in / out) (L_d f(wi_d) / x + L_b f(wi) / y) + L_em."""
+    s, lp, members, offsets, c = cluster_case()
+    sizes = np.diff(np.append(offsets, len(members)))
+    assert sizes.max() > 32 and sizes.min() == 1 and (s["groupIdx"] == -1).sum() > 100
+    for it in (1, 3):
+        d, b, m = port.pathgraph_cluster(s, lp, members, offsets, it, sequential=True)
+        close_rows(d, c[f"cl_direct_{it}"], RTOL_SUM, f"cluster direct ({it})")
+        close_rows(b, c[f"cl_blur_{it}"], RTOL_SUM, f"cluster blur ({it})")
+        close_rows(m, c[f"cl_mc_{it}"], RTOL_SUM, f"cluster mc ({it})")
+        d2, b2, m2 = port.pathgraph_cluster(s, lp, members, offsets, it, sequential=False)
+        close_rows(b2, b, 1e-5, "lane order vs list order")
+    assert np.abs(c["cl_blur_3"]).sum() > 0 and not np.allclose(c["cl_blur_3"], c["cl_blur_1"], rtol=1e-3)
+    close_rows(c["cl_direct_3"], c["cl_direct_1"], 1e-5, "two runs of the reference's ClusterDirect (atomics: equal to rounding only)")
+    loose = s["groupIdx"] == -1
+    np.testing.assert_allclose(c["cl_direct_1"][loose], s["eLd"][loose] + lp["L_em"][loose], rtol=1e-6)
+    n = len(s); one = s.copy(); one["groupIdx"] = np.arange(n); idx = np.arange(n, dtype=np.int32)
+    d1, b1, m1 = port.pathgraph_cluster(one, lp, idx, idx, 1, sequential=True)
+    pdf, f = port.pathgraph_eval(s, s["wi"]); pdfd, fd = port.pathgraph_eval(s, s["wi_d"])
+    x = np.where((s["wi_d"] * s["shN"]).sum(1) > 0, lp["lightpdf"], 0) + pdfd
+    y = np.where((s["wi"] * s["shN"]).sum(1) > 0, lp["bsdfpdf"], 0) + pdf
+    raw = np.zeros((n, 3))
+    a = x > 0; raw[a] += lp["L_directsample"][a] * fd[a] / x[a, None]
+    b = y > 0; raw[b] += lp["L_bsdfsample"][b] * f[b] / y[b, None]
+    took = lp["L_directsample"].astype(np.float64) + lp["L_bsdfsample"]
+    want = raw * np.where(took < raw, took / np.maximum(raw, 1e-300), 1.0) + lp["L_em"]
+    close_rows(d1, want, 1e-5, "singleton clusters vs closed form")
 
 
 def z_knn():
@@ -375,6 +415,60 @@ def test_gpu_direct_scatter_vs_oracle_and_reference(engine, port):
         engine.pathgraph_direct(t, tl, bad, np.maximum(tk, 1))
     with pytest.raises(NoriGpuError, match="dknn"):
         engine.pathgraph_direct(t, tl, tnb, tk + k)
+
+
+@pytest.mark.gpu
+def test_gpu_cluster_scatter_vs_oracle_and_reference(engine, port):
+    """nori_gpu_pathgraph_cluster on the clustered fixture. A warp owns a cluster and takes every sum in a fixed order, so the device
+    equals the oracle (same evaluations, same order) TO THE BIT on all three results, for clusters below and above a warp's width and
+    for the vertices outside every cluster; and it agrees with the compiled reference's vectors to the rounding of that side's atomics.
+    Lists that are not a partition of the vertices naming a cluster are refused."""
+    s, lp, members, offsets, c = cluster_case()
+    for it in (1, 3):
+        d, b, m, ms = engine.pathgraph_cluster(s, lp, members, offsets, it)
+        od, ob, om = port.pathgraph_cluster(s, lp, members, offsets, it, sequential=False)
+        np.testing.assert_array_equal(d.view(np.uint32), od.view(np.uint32))
+        np.testing.assert_array_equal(b.view(np.uint32), ob.view(np.uint32))
+        np.testing.assert_array_equal(m.view(np.uint32), om.view(np.uint32))
+        close_rows(d, c[f"cl_direct_{it}"], RTOL_SUM, f"cluster direct ({it}) vs reference")
+        close_rows(b, c[f"cl_blur_{it}"], RTOL_SUM, f"cluster blur ({it}) vs reference")
+        close_rows(m, c[f"cl_mc_{it}"], RTOL_SUM, f"cluster mc ({it}) vs reference")
+    # all four tags, cluster_of passed beside the records; no clusters at all = every vertex keeps its own estimate
+    t = records(np.load(REF_NPZ)["eval_sps"])[:3000].copy(); n = len(t); idx = np.arange(n)
+    rng = np.random.default_rng(13)
+    inner = idx % 4 != 3
+    t["nidx"] = 0; t["nidx"][inner] = idx[inner] + 1
+    t["wi_d"] = unit(t["shN"] + rng.normal(size=(n, 3))); t["eLi"] = rng.random((n, 3)); t["eLd"] = rng.random((n, 3))
+    from nori_b200.gpu import LPOINT_DTYPE, NoriGpuError
+    tl = np.zeros(n, LPOINT_DTYPE)
+    tl["L_directsample"] = rng.random((n, 3)); tl["L_bsdfsample"] = rng.random((n, 3)); tl["L_em"] = rng.random((n, 3))
+    tl["lightpdf"] = rng.random(n) * (rng.random(n) < 0.7); tl["bsdfpdf"] = rng.random(n)
+    perm = rng.permutation(n).astype(np.int32)[:2800]
+    offs = np.concatenate([[0], np.cumsum(rng.integers(1, 70, size=200))]); offs = offs[offs < len(perm)].astype(np.int32)
+    of = np.full(n, -1, np.int32)
+    for ci, (a, b_) in enumerate(zip(offs, np.append(offs[1:], len(perm)))):
+        of[perm[a:b_]] = ci
+    d, b, m, _ = engine.pathgraph_cluster(t, tl, perm, offs, 2, cluster_of=of)
+    tt = t.copy(); tt["groupIdx"] = of
+    od, ob, om = port.pathgraph_cluster(tt, tl, perm, offs, 2, sequential=False)
+    for got, want in ((d, od), (b, ob), (m, om)):
+        np.testing.assert_array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.isfinite(b).all() and np.abs(b).sum() > 0
+    d0, b0, m0, _ = engine.pathgraph_cluster(t, tl, [], [], 1, cluster_of=np.full(n, -1, np.int32))
+    np.testing.assert_array_equal(d0, t["eLd"] + tl["L_em"])
+    bad = of.copy(); bad[perm[5]] = (of[perm[5]] + 1) % len(offs)
+    with pytest.raises(NoriGpuError, match="not the cluster that lists it"):
+        engine.pathgraph_cluster(t, tl, perm, offs, 1, cluster_of=bad)
+    twice = perm.copy(); twice[1] = twice[0]
+    with pytest.raises(NoriGpuError, match="listed twice|not the cluster"):
+        engine.pathgraph_cluster(t, tl, twice, offs, 1, cluster_of=of)
+    names = of.copy(); names[np.nonzero(of == -1)[0][0]] = 0
+    with pytest.raises(NoriGpuError, match="does not list it"):
+        engine.pathgraph_cluster(t, tl, perm, offs, 1, cluster_of=names)
+    with pytest.raises(NoriGpuError, match="offsets"):
+        engine.pathgraph_cluster(t, tl, perm, offs[::-1].copy(), 1, cluster_of=of)
+    with pytest.raises(NoriGpuError, match="iterations"):
+        engine.pathgraph_cluster(t, tl, perm, offs, 0, cluster_of=of)
 
 
 @pytest.mark.gpu
