@@ -339,6 +339,20 @@ int nori_gpu_pathgraph_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, co
 int nori_gpu_pathgraph_scatter_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *neighbors,
                                       int row_ints, const int32_t *knn, const int32_t *dknn, int iterations, float *direct, float *blur, float *mc,
                                       float *ms);
+/* SPoints::BuildClusters (include/nori/shadingPoint.h:637-760): the clustering the `pg` tool's default mode works on. `seeds` = the vertices
+ * the clusters grow from (the reference takes the first n / K + 1 entries of an index list shuffled by std::random_shuffle under srand(1994),
+ * :640-647; here they are an input), hp->k = K = the members a cluster should have, hp->dim / cellsize / minb = the grid (nori_gpu_pathgraph_grid).
+ *   1. every vertex joins the nearest seed found through a hashed table (n_seeds buckets) of the seeds' grid cells, searched over the 2x2x2 cell
+ *      block around the vertex, or stays outside (-1) if none lies within twice the cell diagonal (buildBatchClusters, src/pbsdf.cu:3555-3622);
+ *   2. twice: every cluster of `size` members is split into size / K + 1 clusters around its first size / K + 1 listed members (countMyClusters +
+ *      subClusters, :3236-3310);   3. member lists and offsets (FinalizeCluster, :3312-3332).
+ * The reference lists a cluster's members in the order its atomics arrive; here they are listed in index order (stable sorts), one of the
+ * orders it can produce, so the result is deterministic. cluster_of: n ints (SPoint::groupIdx as SaveClusters leaves it), clusters: n ints
+ * (*n_listed used), offsets: offsets_capacity ints (*n_clusters used; NORI_GPU_EINVAL if more clusters arise — n / K + 2 n_seeds always fits).
+ * points / stride as nori_gpu_pathgraph_knn. */
+int nori_gpu_pathgraph_build_clusters(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp, const int32_t *seeds,
+                                      int n_seeds, int32_t *cluster_of, int32_t *clusters, int32_t *offsets, int offsets_capacity, int *n_clusters,
+                                      int *n_listed, float *ms);
 /* SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624), what the `pg` tool runs in its default "opt" mode once the
  * vertices are clustered (src/cluster.cpp:217): every vertex exchanges light with ALL members of its cluster instead of its k nearest
  * neighbours. clusters[offsets[c] .. offsets[c + 1]) (the last one up to n_listed) = the members of cluster c, a partition of the vertices

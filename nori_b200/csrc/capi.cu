@@ -1142,6 +1142,44 @@ extern "C" int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uin
     return NORI_GPU_OK;
 }
 
+extern "C" int nori_gpu_pathgraph_build_clusters(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp, const int32_t *seeds,
+                                                 int n_seeds, int32_t *cluster_of, int32_t *clusters, int32_t *offsets, int offsets_capacity, int *n_clusters,
+                                                 int *n_listed, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(points && hp && seeds && cluster_of && clusters && offsets && n_clusters && n_listed && n > 0 && stride >= 12 && stride % 4 == 0, "pathgraph_build_clusters: bad arguments");
+    REQUIRE(hp->k >= 2 && hp->dim[0] >= 1 && hp->dim[1] >= 1 && hp->dim[2] >= 1, "pathgraph_build_clusters: bad grid parameters (k = members per cluster >= 2)");
+    REQUIRE(n_seeds >= 1 && n_seeds <= n && offsets_capacity >= n_seeds, "pathgraph_build_clusters: need 1 <= n_seeds <= n and offsets_capacity >= n_seeds");
+    const unsigned long long cells = (unsigned long long) hp->dim[0] * hp->dim[1] * hp->dim[2];
+    REQUIRE(cells < (1ull << 30), "pathgraph_build_clusters: more than 2^30 grid cells");
+    REQUIRE(hp->cellsize[0] > 0 && hp->cellsize[1] > 0 && hp->cellsize[2] > 0, "pathgraph_build_clusters: cell sizes must be positive");
+    for (int s = 0; s < n_seeds; ++s) REQUIRE(seeds[s] >= 0 && seeds[s] < n, "pathgraph_build_clusters: seed outside [0, n)");
+    CK(cudaSetDevice(ctx->device));
+    PgParams P;
+    for (int c = 0; c < 3; ++c) { P.minb[c] = hp->minb[c]; P.cell[c] = hp->cellsize[c]; P.dim[c] = hp->dim[c]; }
+    P.k = hp->k; P.dk = hp->k; P.maxK = hp->k; P.nCells = (int) cells;
+    DevBuf<unsigned char> pts, scratch; DevBuf<int> sd, g, lists, off;
+    CK(pts.alloc((size_t) n * stride)); CK(scratch.alloc(pgBuildClustersScratchBytes(n, n_seeds, offsets_capacity)));
+    CK(sd.alloc(n_seeds)); CK(g.alloc(n)); CK(lists.alloc(n)); CK(off.alloc((size_t) offsets_capacity + 1));
+    cudaStream_t st = ctx->stream;
+    if (int rc = stagedCopy(ctx, pts.p, points, (size_t) n * stride)) return rc;
+    CK(cudaMemcpyAsync(sd.p, seeds, (size_t) n_seeds * 4, cudaMemcpyHostToDevice, st));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    int nc = 0, nl = 0;
+    if (!launchPathgraphBuildClusters(pts.p, (size_t) stride, n, P, sd.p, n_seeds, hp->k, scratch.p, g.p, lists.p, off.p, offsets_capacity, &nc, &nl, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    CK(cudaMemcpyAsync(cluster_of, g.p, (size_t) n * 4, cudaMemcpyDeviceToHost, st));
+    if (nl > 0) CK(cudaMemcpyAsync(clusters, lists.p, (size_t) nl * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(offsets, off.p, (size_t) nc * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    *n_clusters = nc; *n_listed = nl;
+    if (ms) cudaEventElapsedTime(ms, e0, e1);
+    unsigned line = 0;
+    if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_build_clusters: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
+
 namespace {
 /// Device side of the scatter stage shared by the two entry points: rows already on the device and validated.
 int pathgraphScatterOnDevice(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *d_sps, int n, const int *d_nb, int rowInts, const int *d_knn, int iterations,

@@ -16,6 +16,7 @@
 //     atomics filled a cell. The reference's quickselect breaks distance ties arbitrarily.
 // The cell arithmetic (getKeys / getKeysAndDirs / makesureGrid, pbsdf.cu:630-661, 762-777) and the distance
 // (dev_distance, pbsdf.cu:667-675, as nvcc contracts it: fused multiply-adds) are restated operation for operation.
+#include <cub/cub.cuh>
 #include "engine.h"
 #include "check.cuh"
 #include "pathgraph.h"
@@ -266,6 +267,181 @@ bool launchPathgraphKnn(const void *d_pos, size_t stride, int n, const PgParams 
     const size_t smem = (size_t) P.maxK * NT * 8;
     cudaFuncSetAttribute(k_pgKnn<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPgMaxK * NT * 8);      // per device; cheap
     k_pgKnn<NT><<<(unsigned) ((n + NT - 1) / NT), NT, smem, st>>>(entries, cellStart, n, P, d_neighbors, pitchInts, d_knn, d_dknn);
+    return true;
+}
+
+// ---- SPoints::BuildClusters (include/nori/shadingPoint.h:637-760) ---------------------------------------------------------------
+// seeds -> nearest seed through a hashed table of the seeds' cells (buildBatchClusters, src/pbsdf.cu:3555-3622) -> two rounds of splitting
+// every cluster around its first size / K + 1 members (countMyClusters + subClusters, :3236-3310) -> member lists (FinalizeCluster).
+// HOW it differs: the reference fills its table buckets and member lists with atomics (buildHashSub :888-902, SaveClusters :987-1006), so
+// the order inside a bucket or a cluster — and with it which members seed a split — depends on scheduling, and it scans sizes into
+// offsets through thrust with host round trips. Here both are STABLE radix sorts by bucket / cluster (members in index order: one of the
+// orders the reference can produce) with the offsets read off the sorted keys by binary search: deterministic, no atomics.
+namespace {
+
+__device__ __forceinline__ unsigned int pgHashBucket(unsigned int key, unsigned int table) { return (key * 5039u + 39916801u) % table; }   // hashbmap, :798-800
+__device__ __forceinline__ const float *pgPosOf(const unsigned char *pos, size_t stride, int i) { return reinterpret_cast<const float *>(pos + (size_t) i * stride); }
+
+/// HashTableSize / buildHashSub (src/pbsdf.cu:853-861, 888-902): bucket of every seed; sorted by bucket afterwards.
+__global__ void k_pgSeedKeys(const unsigned char *__restrict__ pos, size_t stride, const int *__restrict__ seeds, int nSeeds, int n, PgParams P,
+                             unsigned int *__restrict__ keys, int *__restrict__ vals) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nSeeds) return;
+    const int i = seeds[s];
+    NG_CHECK(i >= 0 && i < n);
+    const float *p = pgPosOf(pos, stride, i);
+    keys[s] = pgHashBucket((unsigned int) pgKey(P, pgKeys(P, p[0], p[1], p[2])), (unsigned int) nSeeds);
+    vals[s] = s;
+}
+/// start[b] = first position in the ascending keys with key >= b, for b in [0, nKeys]: offsets of buckets / clusters without a scan.
+__global__ void k_pgLowerBounds(const unsigned int *__restrict__ sorted, int nSorted, int nKeys, int *__restrict__ start) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > nKeys) return;
+    int lo = 0, hi = nSorted;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (sorted[mid] < (unsigned int) b) lo = mid + 1; else hi = mid; }
+    start[b] = lo;
+}
+__global__ void k_pgSeedEntries(const unsigned char *__restrict__ pos, size_t stride, const int *__restrict__ seeds, const int *__restrict__ sortedSeed, int nSeeds,
+                                float4 *__restrict__ entries) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nSeeds) return;
+    const int s = sortedSeed[e];
+    const float *p = pgPosOf(pos, stride, seeds[s]);
+    entries[e] = make_float4(p[0], p[1], p[2], __int_as_float(s));
+}
+/// Cluster (src/pbsdf.cu:1008-1044): nearest seed among the table buckets of the 2 x 2 x 2 cell block around the vertex; `<=`: the last
+/// of equals wins; -1 if none within minDist (twice the cell diagonal).
+__global__ void k_pgAssign(const unsigned char *__restrict__ pos, size_t stride, int n, PgParams P, const float4 *__restrict__ entries,
+                           const int *__restrict__ bucketStart, int nSeeds, float minDist, int *__restrict__ groupIdx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *p = pgPosOf(pos, stride, i);
+    const float qx = p[0], qy = p[1], qz = p[2];
+    const I3 key = pgKeys(P, qx, qy, qz);
+    const int dx = pgDir(qx, P.cell[0], P.minb[0], key.x), dy = pgDir(qy, P.cell[1], P.minb[1], key.y), dz = pgDir(qz, P.cell[2], P.minb[2], key.z);
+    int lx = max(0, min(key.x, key.x + dx)), ly = max(0, min(key.y, key.y + dy)), lz = max(0, min(key.z, key.z + dz));
+    int hx = min(P.dim[0] - 1, max(key.x, key.x + dx)), hy = min(P.dim[1] - 1, max(key.y, key.y + dy)), hz = min(P.dim[2] - 1, max(key.z, key.z + dz));
+    pgCheckOneDim(lx, hx, P.dim[0]); pgCheckOneDim(ly, hy, P.dim[1]); pgCheckOneDim(lz, hz, P.dim[2]);
+    float best = minDist; int who = -1;
+    for (int ix = lx; ix <= hx; ++ix)
+        for (int iy = ly; iy <= hy; ++iy)
+            for (int iz = lz; iz <= hz; ++iz) {
+                I3 c = {ix, iy, iz};
+                const unsigned int b = pgHashBucket((unsigned int) pgKey(P, c), (unsigned int) nSeeds);
+                const int begin = __ldg(bucketStart + b), end = __ldg(bucketStart + b + 1);
+                for (int e = begin; e < end; ++e) {
+                    const float4 g = __ldg(entries + e);
+                    const float d = pgDistance(g.x, g.y, g.z, qx, qy, qz);
+                    if (d <= best) { best = d; who = __float_as_int(g.w); }
+                }
+            }
+    groupIdx[i] = who;
+}
+__global__ void k_pgGroupKeys(const int *__restrict__ groupIdx, int n, unsigned int *__restrict__ keys, int *__restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = (unsigned int) groupIdx[i];          // -1 -> 0xffffffff: behind every cluster
+    vals[i] = i;
+}
+/// countClusters (src/pbsdf.cu:910-920): a cluster of `size` members becomes size / K + 1 clusters. small[nClusters] = 0 (so that the
+/// exclusive sum over nClusters + 1 entries ends with the total).
+__global__ void k_pgSmall(const int *__restrict__ offsets /* nClusters + 1 */, int nClusters, int K, int *__restrict__ small) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c > nClusters) return;
+    small[c] = c == nClusters ? 0 : max((offsets[c + 1] - offsets[c]) / K + 1, 1);
+}
+/// SubdivideClusters (src/pbsdf.cu:942-974): a member joins the nearest of its cluster's first `pnum` listed members (strict <: the first
+/// of equals; nothing nearer than 262144 -> the first).
+__global__ void k_pgSubdivide(const unsigned char *__restrict__ pos, size_t stride, int n, const int *__restrict__ lists, const int *__restrict__ offsets,
+                              const int *__restrict__ first /* nClusters + 1 */, int *__restrict__ groupIdx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = groupIdx[i];
+    if (c < 0) return;
+    const int f = first[c], pnum = first[c + 1] - f;
+    int g = f;
+    if (pnum > 1) {
+        const float *p = pgPosOf(pos, stride, i);
+        const int *mem = lists + offsets[c];
+        float best = 262144.0f; int who = 0;
+        for (int t = 0; t < pnum; ++t) {
+            const float *q = pgPosOf(pos, stride, mem[t]);
+            const float d = pgDistance(q[0], q[1], q[2], p[0], p[1], p[2]);
+            if (d < best) { best = d; who = t; }
+        }
+        g += who;
+    }
+    groupIdx[i] = g;
+}
+
+inline size_t pgAl(size_t b) { return (b + 255) / 256 * 256; }
+size_t pgSortTempBytes(int n) {
+    size_t a = 0, b = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, a, (const unsigned int *) nullptr, (unsigned int *) nullptr, (const int *) nullptr, (int *) nullptr, n);
+    cub::DeviceScan::ExclusiveSum(nullptr, b, (const int *) nullptr, (int *) nullptr, n + 1);
+    return std::max(a, b);
+}
+
+} // namespace
+
+size_t pgBuildClustersScratchBytes(int n, int nSeeds, int cap) {
+    const int m = std::max(n, nSeeds), c = std::max(cap, nSeeds) + 2;
+    return 4 * pgAl((size_t) m * 4) + pgAl((size_t) nSeeds * 16) + 3 * pgAl((size_t) c * 4) + pgAl(pgSortTempBytes(std::max(m, c))) + 1024;
+}
+
+/// BuildClusters on device-resident positions. d_groupIdx: n ints (cluster of every vertex or -1), d_lists: n ints, d_offsets: `cap` + 1 ints
+/// (offsets[nClusters] = members listed). Synchronises the stream three times to read a cluster count (the reference: after every kernel).
+bool launchPathgraphBuildClusters(const void *d_pos, size_t stride, int n, const PgParams &P, const int *d_seeds, int nSeeds, int K, void *scratch,
+                                  int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClustersOut, int *nListedOut, cudaStream_t st, std::string &err) {
+    if (n <= 0 || nSeeds <= 0 || nSeeds > n || K < 2) { err = "pathgraph_build_clusters: need 0 < n_seeds <= n and K >= 2"; return false; }
+    const int m = std::max(n, nSeeds), c = std::max(cap, nSeeds) + 2;
+    unsigned char *s = static_cast<unsigned char *>(scratch);
+    unsigned int *keysA = reinterpret_cast<unsigned int *>(s); s += pgAl((size_t) m * 4);
+    unsigned int *keysB = reinterpret_cast<unsigned int *>(s); s += pgAl((size_t) m * 4);
+    int *valsA = reinterpret_cast<int *>(s); s += pgAl((size_t) m * 4);
+    int *valsB = reinterpret_cast<int *>(s); s += pgAl((size_t) m * 4);
+    float4 *entries = reinterpret_cast<float4 *>(s); s += pgAl((size_t) nSeeds * 16);
+    int *offs = reinterpret_cast<int *>(s); s += pgAl((size_t) c * 4);
+    int *small = reinterpret_cast<int *>(s); s += pgAl((size_t) c * 4);
+    int *first = reinterpret_cast<int *>(s); s += pgAl((size_t) c * 4);
+    void *tmp = s;
+    size_t tmpBytes = pgSortTempBytes(std::max(m, c));
+    const unsigned char *pos = static_cast<const unsigned char *>(d_pos);
+    auto grid = [](int work) { return (unsigned) ((work + 255) / 256); };
+    auto fail = [&](const char *what, cudaError_t e) { err = std::string("pathgraph_build_clusters: ") + what + ": " + cudaGetErrorString(e); return false; };
+    // table of the seeds (size nSeeds: shadingPoint.h:667), buckets in ascending seed order
+    k_pgSeedKeys<<<grid(nSeeds), 256, 0, st>>>(pos, stride, d_seeds, nSeeds, n, P, keysA, valsA);
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmpBytes, keysA, keysB, valsA, valsB, nSeeds, 0, 32, st);
+    if (e != cudaSuccess) return fail("sort", e);
+    k_pgLowerBounds<<<grid(nSeeds + 1), 256, 0, st>>>(keysB, nSeeds, nSeeds, offs);
+    k_pgSeedEntries<<<grid(nSeeds), 256, 0, st>>>(pos, stride, d_seeds, valsB, nSeeds, entries);
+    const float diag = std::sqrt(P.cell[0] * P.cell[0] + P.cell[1] * P.cell[1] + P.cell[2] * P.cell[2]);
+    const float minDist = (float) ((double) diag * 2.0);
+    k_pgAssign<<<grid(n), 256, 0, st>>>(pos, stride, n, P, entries, offs, nSeeds, minDist, d_groupIdx);
+    int nClusters = nSeeds;
+    for (int round = 0; round < 3; ++round) {
+        // member lists in index order + offsets (countMyClusters' scan + SaveClusters; FinalizeCluster in the last round)
+        int *offOut = round == 2 ? d_offsets : offs;
+        k_pgGroupKeys<<<grid(n), 256, 0, st>>>(d_groupIdx, n, keysA, valsA);
+        tmpBytes = pgSortTempBytes(std::max(m, c));
+        e = cub::DeviceRadixSort::SortPairs(tmp, tmpBytes, keysA, keysB, valsA, d_lists, n, 0, 32, st);
+        if (e != cudaSuccess) return fail("sort", e);
+        k_pgLowerBounds<<<grid(nClusters + 1), 256, 0, st>>>(keysB, n, nClusters, offOut);
+        if (round == 2) break;
+        k_pgSmall<<<grid(nClusters + 1), 256, 0, st>>>(offs, nClusters, K, small);
+        tmpBytes = pgSortTempBytes(std::max(m, c));
+        e = cub::DeviceScan::ExclusiveSum(tmp, tmpBytes, small, first, nClusters + 1, st);
+        if (e != cudaSuccess) return fail("scan", e);
+        int next = 0;
+        if ((e = cudaMemcpyAsync(&next, first + nClusters, sizeof(int), cudaMemcpyDeviceToHost, st)) != cudaSuccess || (e = cudaStreamSynchronize(st)) != cudaSuccess) return fail("count", e);
+        if (next > cap) { err = "pathgraph_build_clusters: " + std::to_string(next) + " clusters exceed the capacity " + std::to_string(cap); return false; }
+        k_pgSubdivide<<<grid(n), 256, 0, st>>>(pos, stride, n, d_lists, offs, first, d_groupIdx);
+        nClusters = next;
+    }
+    int listed = 0;
+    if ((e = cudaMemcpyAsync(&listed, d_offsets + nClusters, sizeof(int), cudaMemcpyDeviceToHost, st)) != cudaSuccess || (e = cudaStreamSynchronize(st)) != cudaSuccess) return fail("count", e);
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail("launch", e);
+    *nClustersOut = nClusters; *nListedOut = listed;
     return true;
 }
 

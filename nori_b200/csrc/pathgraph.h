@@ -20,6 +20,10 @@ struct PgParams {
 size_t pgScratchBytes(int n, int nCells);
 bool launchPathgraphKnn(const void *d_pos, size_t strideBytes, int n, const PgParams &P, void *d_scratch, int *d_neighbors, int pitchInts,
                         int *d_knn, int *d_dknn, cudaStream_t st, std::string &err);
+/// SPoints::BuildClusters (include/nori/shadingPoint.h:637-760) with given seeds; deterministic (members in index order).
+size_t pgBuildClustersScratchBytes(int n, int nSeeds, int cap);
+bool launchPathgraphBuildClusters(const void *d_pos, size_t strideBytes, int n, const PgParams &P, const int *d_seeds, int nSeeds, int K, void *d_scratch,
+                                  int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClusters, int *nListed, cudaStream_t st, std::string &err);
 unsigned pathgraphChecks(unsigned *line);
 
 /// pathgraph_scatter.cu: marginal densities + iterated radiance scatter over the kNN graph (src/pbsdf.cu:2317-2368).

@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_build_clusters", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
 ]
 
 
@@ -143,6 +143,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_path_vertices.argtypes = [vp, C.POINTER(RenderDesc), vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_path_vertices_lights.argtypes = [vp, C.POINTER(RenderDesc), vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_pathgraph_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
+    L.nori_gpu_pathgraph_build_clusters.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, ip, vp, vp, vp, ip, C.POINTER(ip), C.POINTER(ip), C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_cluster.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_scatter_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
@@ -398,6 +399,16 @@ class Engine:
         self._ck(self.L.nori_gpu_pathgraph_scatter_direct(self.h, _p(pts), _p(lps), n, _p(nb), nb.shape[1], _p(kn), _p(dk), int(iterations),
                                                           _p(out), _p(blur), _p(mc), C.byref(ms)))
         return out, blur, mc, ms.value
+
+    def pathgraph_build_clusters(self, points, hp: "HashParams", seeds):
+        """SPoints::BuildClusters with given seeds (hp.k = members per cluster): (cluster_of (n,), members, offsets, ms)."""
+        pts = points if points.dtype == SPOINT_DTYPE else _f32(points, (-1, 3))
+        pts = np.ascontiguousarray(pts); n, stride = pts.shape[0], pts.strides[0]
+        sd = np.ascontiguousarray(seeds, np.int32).reshape(-1); cap = n // max(hp.k, 1) + 2 * len(sd) + 2
+        of = np.empty(n, np.int32); lists = np.empty(n, np.int32); off = np.empty(cap, np.int32); nc = C.c_int(); nl = C.c_int(); ms = C.c_float()
+        self._ck(self.L.nori_gpu_pathgraph_build_clusters(self.h, _p(pts), stride, n, C.byref(hp), _p(sd), len(sd), _p(of), _p(lists), _p(off), cap,
+                                                          C.byref(nc), C.byref(nl), C.byref(ms)))
+        return of, lists[:nl.value].copy(), off[:nc.value].copy(), ms.value
 
     def pathgraph_cluster(self, points, lights, clusters, offsets, iterations: int, cluster_of=None):
         """SPoints::ClusterScatterWithDirectOptNR (the pg tool's default mode on given clusters): members of cluster c =

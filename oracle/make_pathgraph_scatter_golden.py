@@ -112,7 +112,33 @@ def main_cluster(out):
           "non-finite", int((~np.isfinite(res["cl_blur_3"])).any(1).sum()))
 
 
+def main_build_clusters(out):
+    """(bc_*) SPoints::BuildClusters of the compiled reference step by step (buildBatchClusters, countMyClusters, subClusters x 2, FinalizeCluster)
+    with seeded seeds, and the intermediate state each step left: python oracle/make_pathgraph_scatter_golden.py --build-clusters [out.npz].
+    Positions: the fixture's 7 000 path vertices + 9 000 uniform points in their bounding box (cells with many and with few points)."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "pathgraph_scatter_ref.npz"))
+    v = np.ascontiguousarray(z["sc_sps"]).view(SPOINT_DTYPE).reshape(-1)
+    rng = np.random.default_rng(41)
+    lo, hi = v["pos"].min(0), v["pos"].max(0)
+    pts = np.concatenate([v["pos"], (lo + rng.random((9000, 3)) * (hi - lo)).astype(np.float32)]).astype(np.float32)
+    K = 12
+    dim = np.array([7, 5, 6], np.int32)
+    lo, hi = pts.min(0), pts.max(0)
+    cs = ((hi - lo) / dim).astype(np.float32)
+    seeds = rng.permutation(len(pts))[:len(pts) // K + 1].astype(np.int32)
+    r = RefCuda().build_clusters(pts, dim, cs, lo.astype(np.float32), seeds, K)
+    res = {"bc_pts": pts, "bc_dim": dim, "bc_cellsize": cs, "bc_minb": lo.astype(np.float32), "bc_seeds": seeds, "bc_K": np.int32(K)}
+    for k in ("g1", "lists1", "off1", "g2", "lists2", "off2", "g3", "lists3", "off3"):
+        res["bc_" + k] = r[k]
+    np.savez_compressed(out, **res)
+    sizes = np.diff(np.append(r["off3"], r["n_listed"]))
+    print("wrote", out, len(pts), "points,", len(seeds), "seeds ->", len(r["off2"]), "->", len(r["off3"]), "clusters, sizes", int(sizes.min()), "..", int(sizes.max()),
+          "outside", int((r["g3"] < 0).sum()))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--build-clusters":
+        return main_build_clusters(sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "pathgraph_clusters_ref.npz"))
     if len(sys.argv) > 1 and sys.argv[1] == "--cluster":
         return main_cluster(sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "pathgraph_cluster_ref.npz"))
     if len(sys.argv) > 1 and sys.argv[1] == "--direct":

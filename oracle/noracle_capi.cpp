@@ -304,6 +304,20 @@ void noracle_pathgraph_knn(const float *pts, int n, const int *dim, const float 
     pathgraphKnn(pts, n, h, neighbors, knn, dknn, dists);
 }
 
+/// BuildClusters restated (noracle_pathgraph.h). mode 0: the whole builder (index-ordered lists) -> returns the number of clusters, fills
+/// group_idx (n), lists (n), offsets (capacity n + n_seeds), *n_listed. mode 1: only the nearest-seed assignment (group_idx).
+/// mode 2: only one subdivision of the clustering given in group_idx / lists / offsets (n_seeds = its number of clusters, *n_listed = its
+/// listed members): group_idx rewritten, returns the new number of clusters.
+int noracle_pathgraph_clusters(int mode, const float *pts, int n, const int *dim, const float *cellsize, const float *minb, const int32_t *seeds, int n_seeds,
+                               int K, int32_t *group_idx, int32_t *lists, int32_t *offsets, int *n_listed) {
+    HashParams h;
+    for (int c = 0; c < 3; ++c) { h.dim[c] = dim[c]; h.cellsize[c] = cellsize[c]; h.minb[c] = minb[c]; }
+    h.k = h.dk = K;
+    if (mode == 1) { pgClusterAssign(pts, n, h, seeds, n_seeds, group_idx); return n_seeds; }
+    if (mode == 2) return pgClusterSubdivide(pts, n, group_idx, lists, *n_listed, offsets, n_seeds, K);
+    return pathgraphBuildClusters(pts, n, h, seeds, n_seeds, K, group_idx, lists, offsets, n_listed);
+}
+
 /// Path-graph marginal densities + radiance scatter (noracle_pathgraph_scatter.h). sps: n SPoint records of 168 bytes.
 void noracle_pathgraph_scatter(const void *sps, int n, const int32_t *neighbors, int row_ints, const int32_t *knn, int iterations,
                                int sequential, float *pdfmarginal, float *blur, float *mc) {

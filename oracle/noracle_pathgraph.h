@@ -85,4 +85,102 @@ inline void pathgraphKnn(const float *pts, int n, const HashParams &h, int32_t *
     }
 }
 
+
+// ---- SPoints::BuildClusters (include/nori/shadingPoint.h:637-760) -------------------------------------------------------------------
+// Seeds (the first n / K + 1 entries of a shuffled index list: the reference draws it with libstdc++'s random_shuffle under srand(1994);
+// here the seeds are an INPUT) -> every vertex joins the nearest seed found through a hashed table of the seeds' grid cells
+// (buildBatchClusters, src/pbsdf.cu:3555-3622) -> two rounds that split every cluster of more than K members around its first
+// size / K + 1 members (countMyClusters + subClusters, :3236-3310) -> member lists (FinalizeCluster, :3312-3332).
+// The reference fills its lists with atomics (SaveClusters, :987-1006), so the order of a cluster's members — and with it WHICH members
+// seed the split — depends on scheduling. The step functions below take the lists as they are given (to be checked against the reference's
+// own intermediate state); the driver at the end builds them in index order, which is one of the orders the reference can produce.
+
+/// hashbmap (src/pbsdf.cu:798-800)
+inline uint32_t pgHashBucket(uint32_t key, uint32_t tableSize) { return (key * 5039u + 39916801u) % tableSize; }
+
+/// buildBatchClusters: groupIdx[i] = index (into seeds) of the nearest seed among the table buckets of the 2 x 2 x 2 cell block around
+/// vertex i (Cluster, src/pbsdf.cu:1008-1044: `dist <= mindistance`, so among equals the last one visited wins; buckets hold the seeds
+/// in ascending order here), or -1 if none lies within twice the cell diagonal. Table size = nSeeds (shadingPoint.h:667).
+inline void pgClusterAssign(const float *pts, int n, const HashParams &h, const int32_t *seeds, int nSeeds, int32_t *groupIdx) {
+    const uint32_t table = (uint32_t) nSeeds;
+    std::vector<std::vector<int> > bucket(nSeeds);
+    for (int s = 0; s < nSeeds; ++s) {
+        const float *p = pts + 3 * (size_t) seeds[s];
+        bucket[pgHashBucket((uint32_t) pgKey(h, pgCell(h, 0, p[0]), pgCell(h, 1, p[1]), pgCell(h, 2, p[2])), table)].push_back(s);
+    }
+    const float diag = std::sqrt(h.cellsize[0] * h.cellsize[0] + h.cellsize[1] * h.cellsize[1] + h.cellsize[2] * h.cellsize[2]);
+    const float minDist = (float) ((double) diag * 2.0);
+    for (int i = 0; i < n; ++i) {
+        const float *p = pts + 3 * (size_t) i;
+        int lo[3], hi[3];
+        for (int c = 0; c < 3; ++c) {
+            const int k = pgCell(h, c, p[c]), d = pgDir(h, c, p[c], k);
+            lo[c] = std::max(0, std::min(k, k + d)); hi[c] = std::min(h.dim[c] - 1, std::max(k, k + d));
+            pgCheckOneDim(lo[c], hi[c], h.dim[c]);
+        }
+        float best = minDist; int who = -1;
+        for (int ix = lo[0]; ix <= hi[0]; ++ix) for (int iy = lo[1]; iy <= hi[1]; ++iy) for (int iz = lo[2]; iz <= hi[2]; ++iz) {
+            const std::vector<int> &b = bucket[pgHashBucket((uint32_t) pgKey(h, ix, iy, iz), table)];
+            for (size_t e = 0; e < b.size(); ++e) {
+                const float d = pgDistance(pts + 3 * (size_t) seeds[b[e]], p);
+                if (d <= best) { best = d; who = b[e]; }
+            }
+        }
+        groupIdx[i] = who;
+    }
+}
+
+/// Member lists in index order + offsets (what SaveClusters leaves when its atomics arrive in index order). Returns the number listed.
+inline int pgClusterLists(const int32_t *groupIdx, int n, int nClusters, int32_t *lists, int32_t *offsets) {
+    std::vector<int> count(nClusters + 1, 0);
+    for (int i = 0; i < n; ++i) if (groupIdx[i] >= 0) count[groupIdx[i] + 1]++;
+    for (int c = 0; c < nClusters; ++c) count[c + 1] += count[c];
+    for (int c = 0; c < nClusters; ++c) offsets[c] = count[c];
+    std::vector<int> fill(count.begin(), count.end() - 1);
+    for (int i = 0; i < n; ++i) if (groupIdx[i] >= 0) lists[fill[groupIdx[i]]++] = i;
+    return count[nClusters];
+}
+
+/// countClusters + SubdivideClusters (src/pbsdf.cu:910-920, 942-974): cluster c of `size` members becomes size / K + 1 clusters around its
+/// first size / K + 1 listed members; a member joins the nearest of them (strict <: the first of equals; nothing nearer than 262144 -> the
+/// first). groupIdx is rewritten to the new numbering (cluster c's children are consecutive). Returns the new number of clusters.
+inline int pgClusterSubdivide(const float *pts, int n, int32_t *groupIdx, const int32_t *lists, int nListed, const int32_t *offsets, int nClusters, int K) {
+    std::vector<int> first(nClusters + 1, 0);
+    for (int c = 0; c < nClusters; ++c) {
+        const int size = (c == nClusters - 1 ? nListed : offsets[c + 1]) - offsets[c];
+        first[c + 1] = first[c] + std::max(size / K + 1, 1);
+    }
+    for (int i = 0; i < n; ++i) {
+        const int c = groupIdx[i];
+        if (c < 0) continue;
+        const int pnum = first[c + 1] - first[c];
+        int g = first[c];
+        if (pnum > 1) {
+            float best = 262144.0f; int who = 0;
+            for (int t = 0; t < pnum; ++t) {
+                const float d = pgDistance(pts + 3 * (size_t) lists[offsets[c] + t], pts + 3 * (size_t) i);
+                if (d < best) { best = d; who = t; }
+            }
+            g += who;
+        }
+        groupIdx[i] = g;
+    }
+    return first[nClusters];
+}
+
+/// BuildClusters with index-ordered lists. lists: n ints, offsets: room for the final number of clusters (<= n / K + 2 * nSeeds + n / K ...:
+/// pass n + nSeeds). Returns the number of clusters; *nListed = members listed (vertices with groupIdx != -1).
+inline int pathgraphBuildClusters(const float *pts, int n, const HashParams &h, const int32_t *seeds, int nSeeds, int K, int32_t *groupIdx,
+                                  int32_t *lists, int32_t *offsets, int *nListed) {
+    pgClusterAssign(pts, n, h, seeds, nSeeds, groupIdx);
+    int nClusters = nSeeds;
+    for (int round = 0; round < 2; ++round) {
+        std::vector<int32_t> off(nClusters);
+        const int listed = pgClusterLists(groupIdx, n, nClusters, lists, off.data());
+        nClusters = pgClusterSubdivide(pts, n, groupIdx, lists, listed, off.data(), nClusters, K);
+    }
+    *nListed = pgClusterLists(groupIdx, n, nClusters, lists, offsets);
+    return nClusters;
+}
+
 } // namespace noracle

@@ -165,6 +165,8 @@ class Port:
         L.noracle_pathgraph_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p]
+        L.noracle_pathgraph_clusters.argtypes = [C.c_int, _f32p, C.c_int, _i32p, _f32p, _f32p, _i32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, C.POINTER(C.c_int)]
+        L.noracle_pathgraph_clusters.restype = C.c_int
         L.noracle_pathgraph_cluster.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, C.c_void_p, _i32p, C.c_int, C.c_int, _f32p, _f32p, C.c_void_p, C.c_void_p]
 
@@ -209,6 +211,28 @@ class Port:
         blur = np.empty((max(iterations, 1), n, 3), np.float32); mc = np.empty((max(iterations, 1), n, 3), np.float32)
         self.L.noracle_pathgraph_direct(vp(sps), vp(lps), n, nb, nb.shape[1], vp(kn), dk, iterations, int(sequential), m.reshape(-1), out.reshape(-1), vp(blur), vp(mc))
         return m, out, blur[:iterations], mc[:iterations]
+
+    def pathgraph_build_clusters(self, pts, dim, cellsize, minb, seeds, K):
+        """SPoints::BuildClusters restated with index-ordered lists: (cluster_of (n,), members, offsets)."""
+        pts = _f32(pts, (-1, 3)); n = pts.shape[0]; seeds = np.ascontiguousarray(seeds, np.int32)
+        g = np.empty(n, np.int32); lists = np.empty(n, np.int32); off = np.empty(n + len(seeds), np.int32); nl = C.c_int()
+        nc = self.L.noracle_pathgraph_clusters(0, pts, n, np.asarray(dim, np.int32), _f32(cellsize), _f32(minb), seeds, len(seeds), K, g, lists, off, C.byref(nl))
+        return g, lists[:nl.value].copy(), off[:nc].copy()
+
+    def pathgraph_cluster_assign(self, pts, dim, cellsize, minb, seeds):
+        """buildBatchClusters restated: index of the nearest seed (or -1) per point."""
+        pts = _f32(pts, (-1, 3)); n = pts.shape[0]; seeds = np.ascontiguousarray(seeds, np.int32)
+        g = np.empty(n, np.int32); d = np.zeros(1, np.int32); nl = C.c_int()
+        self.L.noracle_pathgraph_clusters(1, pts, n, np.asarray(dim, np.int32), _f32(cellsize), _f32(minb), seeds, len(seeds), 2, g, d, d, C.byref(nl))
+        return g
+
+    def pathgraph_cluster_subdivide(self, pts, cluster_of, members, offsets, K):
+        """countClusters + SubdivideClusters restated on a given clustering (lists in the given order): (new cluster_of, new count)."""
+        pts = _f32(pts, (-1, 3)); n = pts.shape[0]
+        g = np.ascontiguousarray(cluster_of, np.int32).copy(); lists = np.ascontiguousarray(members, np.int32); off = np.ascontiguousarray(offsets, np.int32)
+        nl = C.c_int(len(lists)); z3 = np.zeros(3, np.float32)
+        nc = self.L.noracle_pathgraph_clusters(2, pts, n, np.ones(3, np.int32), z3, z3, np.zeros(1, np.int32), len(off), K, g, lists, off, C.byref(nl))
+        return g, nc
 
     def pathgraph_cluster(self, sps, lps, clusters, offsets, iterations, sequential=False):
         """SPoints::ClusterScatterWithDirectOptNR restated: (direct, blur, mc), each (n, 3). sps["groupIdx"] = cluster or -1."""
@@ -291,6 +315,8 @@ class RefCuda:
         self.L.refcuda_scatter.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         self.L.refcuda_eval.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p]
         self.L.refcuda_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_double)]
+        if hasattr(self.L, 'refcuda_build_clusters'):
+            self.L.refcuda_build_clusters.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, _i32p, C.c_int, C.c_int] + [_i32p] * 9 + [C.c_int, _i32p, C.POINTER(C.c_double)]
         if hasattr(self.L, 'refcuda_cluster'):
             self.L.refcuda_cluster.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         if hasattr(self.L, 'refcuda_direct'):
@@ -347,6 +373,20 @@ class RefCuda:
         if rc != 0:
             raise RuntimeError(f"refcuda_direct failed ({rc})")
         return out, blur[:iterations], mc[:iterations], sec.value
+
+    def build_clusters(self, pts, dim, cellsize, minb, seeds, K):
+        """SPoints::BuildClusters step by step with given seeds. Returns a dict: g1, lists1, off1 (after buildBatchClusters + countMyClusters),
+        g2, lists2, off2 (after the first subdivision), g3, lists3, off3 (final), seconds."""
+        pts = _f32(pts, (-1, 3)); n = pts.shape[0]; seeds = np.ascontiguousarray(seeds, np.int32); cap = n + len(seeds)
+        a = {k: np.full(n, -1, np.int32) for k in ("g1", "lists1", "g2", "lists2", "g3", "lists3")}
+        off1 = np.zeros(len(seeds), np.int32); off2 = np.zeros(cap, np.int32); off3 = np.zeros(cap, np.int32); counts = np.zeros(3, np.int32); sec = C.c_double()
+        rc = self.L.refcuda_build_clusters(pts, n, np.asarray(dim, np.int32), _f32(cellsize), _f32(minb), seeds, len(seeds), K, a["g1"], a["lists1"], off1,
+                                           a["g2"], a["lists2"], off2, a["g3"], a["lists3"], off3, cap, counts, C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_build_clusters failed ({rc})")
+        a["off1"] = off1; a["off2"] = off2[:counts[0]].copy(); a["off3"] = off3[:counts[1]].copy(); a["n_listed"] = int(counts[2]); a["seconds"] = sec.value
+        a["lists3"] = a["lists3"][:counts[2]].copy()
+        return a
 
     def cluster(self, sps, lps, clusters, offsets, iterations):
         """SPoints::ClusterScatterWithDirectOptNR's drivers on given clusters: (direct, blur, mc, seconds)."""

@@ -218,3 +218,72 @@ extern "C" int refcuda_cluster(const void *sps, const void *lps, int n, const in
     cudaFree(cu_sps); cudaFree(cu_lps); cudaFree(cu_clusters); cudaFree(cu_offsets); cudaFree(cu_direct); cudaFree(cu_element_offset); cudaFree(cu_elements);
     return e == cudaSuccess ? 0 : -3;
 }
+
+namespace {
+void glueGroupIdx(const SPoint *cu_sps, int n, int *out) {           // SPoint::groupIdx of every record (what the builders rewrite)
+    SPoint *h = new SPoint[n];
+    cudaMemcpy((void *) h, cu_sps, sizeof(SPoint) * (size_t) n, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < n; ++i) out[i] = h[i].groupIdx;
+    delete[] h;
+}
+}
+
+/// SPoints::BuildClusters (include/nori/shadingPoint.h:637-760) step by step on n positions with GIVEN seeds (the reference shuffles an
+/// index list with std::random_shuffle; `seeds` takes the place of its first n_seeds entries), with the intermediate state the steps
+/// leave — which depends on the order its atomics arrive in — handed out so that each step can be checked on its own inputs:
+///   g1 (n): groupIdx after buildBatchClusters;  lists1 (n) / off1 (n_seeds): the member lists countMyClusters built from it;
+///   g2 (n): groupIdx after the first subClusters, counts[0] clusters;  lists2 (n) / off2 (capacity cap): the lists of those;
+///   g3 (n), lists3 (n), off3 (cap): the final clustering (second subClusters + FinalizeCluster), counts[1] clusters, counts[2] members listed.
+extern "C" int refcuda_build_clusters(const float *pos, int n, const int *dim, const float *cellsize, const float *minb, const int *seeds, int n_seeds, int K,
+                                      int *g1, int *lists1, int *off1, int *g2, int *lists2, int *off2, int *g3, int *lists3, int *off3, int cap, int *counts,
+                                      double *seconds) {
+    SPoint *h = new SPoint[n];
+    for (int i = 0; i < n; ++i) { std::memset((void *) &h[i], 0, sizeof(SPoint)); h[i].pos[0] = pos[3 * i]; h[i].pos[1] = pos[3 * i + 1]; h[i].pos[2] = pos[3 * i + 2]; h[i].bsdf_type = 'd'; }
+    SPoint *cu_sps = nullptr;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) { delete[] h; return -1; }
+    cudaMemcpy(cu_sps, h, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    delete[] h;
+    hparam hp{{dim[0], dim[1], dim[2]}, {cellsize[0], cellsize[1], cellsize[2]}, {minb[0], minb[1], minb[2]}, K, K};
+    int *cu_clusters = nullptr, *cu_np = nullptr, *cu_small = nullptr, *cu_new1 = nullptr, *cu_small2 = nullptr, *cu_new2 = nullptr;
+    cudaMalloc((void **) &cu_clusters, sizeof(int) * (size_t) n); cudaMemset(cu_clusters, 0xff, sizeof(int) * (size_t) n);
+    cudaMalloc((void **) &cu_np, sizeof(int) * (size_t) n_seeds);
+    cudaDeviceSynchronize();
+    auto t0 = std::chrono::steady_clock::now();
+    buildBatchClusters(cu_sps, n, n_seeds, hp, n_seeds, const_cast<int *>(seeds), cu_clusters, cu_np);
+    double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    glueGroupIdx(cu_sps, n, g1);
+    t0 = std::chrono::steady_clock::now();
+    cudaMalloc((void **) &cu_small, sizeof(int) * (size_t) n_seeds);
+    const int new1 = countMyClusters(cu_sps, n, hp, n_seeds, cu_clusters, cu_np, cu_small);
+    sec += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (new1 > cap) return -4;
+    cudaMemcpy(lists1, cu_clusters, sizeof(int) * (size_t) n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(off1, cu_np, sizeof(int) * (size_t) n_seeds, cudaMemcpyDeviceToHost);
+    t0 = std::chrono::steady_clock::now();
+    cudaMalloc((void **) &cu_new1, sizeof(int) * (size_t) new1);
+    subClusters(cu_sps, n, hp, n_seeds, new1, cu_clusters, cu_np, cu_new1, cu_small);
+    sec += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    glueGroupIdx(cu_sps, n, g2);
+    t0 = std::chrono::steady_clock::now();
+    cudaMalloc((void **) &cu_small2, sizeof(int) * (size_t) new1);
+    const int new2 = countMyClusters(cu_sps, n, hp, new1, cu_clusters, cu_new1, cu_small2);
+    sec += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (new2 > cap) return -4;
+    cudaMemcpy(lists2, cu_clusters, sizeof(int) * (size_t) n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(off2, cu_new1, sizeof(int) * (size_t) new1, cudaMemcpyDeviceToHost);
+    t0 = std::chrono::steady_clock::now();
+    cudaMalloc((void **) &cu_new2, sizeof(int) * (size_t) new2);
+    subClusters(cu_sps, n, hp, new1, new2, cu_clusters, cu_new1, cu_new2, cu_small2);
+    int lastSize = 0;
+    cudaMemcpy(&lastSize, cu_new2 + new2 - 1, sizeof(int), cudaMemcpyDeviceToHost);
+    FinalizeCluster(cu_sps, n, hp, new2, cu_clusters, cu_new2);
+    cudaError_t e = cudaDeviceSynchronize();
+    sec += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (seconds) *seconds = sec;
+    glueGroupIdx(cu_sps, n, g3);
+    cudaMemcpy(lists3, cu_clusters, sizeof(int) * (size_t) n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(off3, cu_new2, sizeof(int) * (size_t) new2, cudaMemcpyDeviceToHost);
+    counts[0] = new1; counts[1] = new2; counts[2] = off3[new2 - 1] + lastSize;
+    cudaFree(cu_sps); cudaFree(cu_clusters); cudaFree(cu_np); cudaFree(cu_small); cudaFree(cu_new1); cudaFree(cu_small2); cudaFree(cu_new2);
+    return e == cudaSuccess ? 0 : -3;
+}
