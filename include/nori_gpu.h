@@ -353,6 +353,9 @@ int nori_gpu_pathgraph_scatter_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *po
 int nori_gpu_pathgraph_build_clusters(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp, const int32_t *seeds,
                                       int n_seeds, int32_t *cluster_of, int32_t *clusters, int32_t *offsets, int offsets_capacity, int *n_clusters,
                                       int *n_listed, float *ms);
+/* Seeds for nori_gpu_pathgraph_build_clusters when the caller has no shuffled list of its own: seeds[s] = (s * step) mod n with step the
+ * smallest integer >= 0.618 n coprime to n — n_seeds distinct vertices, consecutive ones far apart in record order. Host-only, no context. */
+int nori_gpu_pathgraph_stride_seeds(int n, int n_seeds, int32_t *seeds);
 /* SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624), what the `pg` tool runs in its default "opt" mode once the
  * vertices are clustered (src/cluster.cpp:217): every vertex exchanges light with ALL members of its cluster instead of its k nearest
  * neighbours. clusters[offsets[c] .. offsets[c + 1]) (the last one up to n_listed) = the members of cluster c, a partition of the vertices
@@ -373,6 +376,7 @@ int nori_gpu_pathgraph_cluster(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, c
  * rows through host memory. pdfmarginal (optional) is written in scatter mode only. ms[0]: search, ms[1]: scatter / gather. */
 #define NORI_PG_SCATTER 0
 #define NORI_PG_MIS 1
+#define NORI_PG_CLUSTER 2       /* nori_gpu_pathgraph_render only: BuildClusters + ClusterScatterWithDirectOptNR, the tool's default "opt" mode */
 int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
                               float *pdfmarginal, float *blur, float *mc, float ms[2]);
 /* The `pg` tool end to end on the scene's own paths (src/cluster.cpp:156-253 in its "knn" mode, minus the file I/O), everything
@@ -381,7 +385,10 @@ int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *
  * nearest neighbours, `iterations` passes of the scatter (NORI_PG_SCATTER) or the MIS gather (NORI_PG_MIS), and the images
  * writeFullLight / writeIndirectLight / writeFullinit compose from each path's first vertex (src/cluster.cpp:23-107).
  * images: 5 x height x width x 3 floats (HOST): full = eLd + mc, indirect = mc, pt = eLi - eLd, blur, init = eLd, all of the last
- * pass, averaged over a pixel's samples in sample order (the reference keeps the last path of a pixel). */
+ * pass, averaged over a pixel's samples in sample order (the reference keeps the last path of a pixel).
+ * NORI_PG_CLUSTER = the tool's default "opt" mode (src/cluster.cpp:204-218): light records beside the vertices (nori_gpu_path_vertices_lights),
+ * BuildClusters with k members per cluster from n / k + 1 seeds (nori_gpu_pathgraph_stride_seeds), ClusterScatterWithDirectOptNR; `images` then
+ * holds SIX images: the five above + direct = the filtered direct light writeDirectLight writes (:102-126). ms_knn = the cluster build. */
 typedef struct {
     uint64_t vertices;
     float ms_vertices, ms_knn, ms_stage;    /* device time: records + bounding box, grid + search, scatter / gather + images */

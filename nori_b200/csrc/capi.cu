@@ -1142,6 +1142,13 @@ extern "C" int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uin
     return NORI_GPU_OK;
 }
 
+extern "C" int nori_gpu_pathgraph_stride_seeds(int n, int n_seeds, int32_t *seeds) {
+    if (n <= 0 || n_seeds <= 0 || n_seeds > n || !seeds) return NORI_GPU_EINVAL;
+    const long long step = pathgraphSeedStep(n);
+    for (int s = 0; s < n_seeds; ++s) seeds[s] = (int32_t) (((long long) s * step) % n);
+    return NORI_GPU_OK;
+}
+
 extern "C" int nori_gpu_pathgraph_build_clusters(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp, const int32_t *seeds,
                                                  int n_seeds, int32_t *cluster_of, int32_t *clusters, int32_t *offsets, int offsets_capacity, int *n_clusters,
                                                  int *n_listed, float *ms) {
@@ -1381,7 +1388,8 @@ extern "C" int nori_gpu_pathgraph_render(nori_gpu_ctx *ctx, const NoriGpuRenderD
                                          NoriGpuPathGraphStats *stats) {
     if (!ctx) return NORI_GPU_EINVAL;
     REQUIRE(d && images, "pathgraph_render: bad arguments");
-    REQUIRE(mode == NORI_PG_SCATTER || mode == NORI_PG_MIS, "pathgraph_render: unknown mode");
+    REQUIRE(mode == NORI_PG_SCATTER || mode == NORI_PG_MIS || mode == NORI_PG_CLUSTER, "pathgraph_render: unknown mode");
+    REQUIRE(mode != NORI_PG_CLUSTER || k >= 2, "pathgraph_render: clusters need k >= 2 members");
     REQUIRE(k >= 1 && k <= kPgMaxK && iterations >= 1 && iterations <= 64, "pathgraph_render: k in [1, 200], iterations in [1, 64]");
     REQUIRE(ctx->haveBvh && ctx->haveCamera, "pathgraph_render: scene, camera and accel must be set first");
     REQUIRE(d->sample_last > d->sample_first && d->sample_last <= 0x7fffffffu, "pathgraph_render: bad sample range");
@@ -1413,7 +1421,9 @@ extern "C" int nori_gpu_pathgraph_render(nori_gpu_ctx *ctx, const NoriGpuRenderD
     REQUIRE(total <= 0x7fffffffull, "pathgraph_render: more than 2^31 path vertices; render fewer samples per call");
     const int n = (int) total;
     DevBuf<NoriGpuSPoint> recs; CK(recs.alloc(total));
-    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, offsets.p, recs.p, st);
+    DevBuf<NoriGpuLPoint> lrecs;
+    if (mode == NORI_PG_CLUSTER) CK(lrecs.alloc(total));             // the clustered mode filters direct light too: light records beside the vertices
+    enqueuePathVertices(sc, rp, spp, nPaths, counts.p, offsets.p, recs.p, st, mode == NORI_PG_CLUSTER ? lrecs.p : nullptr);
     // 2. grid as SPoints::BuildKNN / PathGraph::computeDimensions size it, from the records' bounding box
     launchPathgraphBounds(recs.p, n, bounds.p, st);
     unsigned int hb[6];
@@ -1431,6 +1441,33 @@ extern "C" int nori_gpu_pathgraph_render(nori_gpu_ctx *ctx, const NoriGpuRenderD
     P.k = k; P.dk = k; P.maxK = k; P.nCells = (int) cells;
     // 3. neighbours, 4. scatter or MIS gather, 5. images: all on the records where they lie
     DevBuf<unsigned char> scratch, stage; DevBuf<int> nb, dk1, dk2; DevBuf<float> pm, db, dm, img;
+    if (mode == NORI_PG_CLUSTER) {
+        // 3'. BuildClusters from n / k + 1 scattered seeds, 4'. ClusterScatterWithDirectOptNR, 5'. the five images + the filtered direct light
+        const int nSeeds = n / k + 1, cap = n / k + 2 * nSeeds + 2;
+        DevBuf<int> seeds, of, lists, off;
+        CK(seeds.alloc(nSeeds)); CK(of.alloc(n)); CK(lists.alloc(n)); CK(off.alloc((size_t) cap + 1));
+        CK(scratch.alloc(pgBuildClustersScratchBytes(n, nSeeds, cap)));
+        launchPathgraphStrideSeeds(seeds.p, nSeeds, n, st);
+        int nc = 0, nl = 0;
+        if (!launchPathgraphBuildClusters(recs.p, sizeof(NoriGpuSPoint), n, P, seeds.p, nSeeds, k, scratch.p, of.p, lists.p, off.p, cap, &nc, &nl, st, ctx->err)) return NORI_GPU_EINVAL;
+        CK(cudaEventRecord(ev[2], st));
+        CK(stage.alloc(pgClusterScratchBytes(n, nc))); CK(db.alloc((size_t) 9 * n)); CK(img.alloc((size_t) 6 * nPixels * 3));
+        if (!launchPathgraphCluster(recs.p, lrecs.p, n, lists.p, nl, off.p, nc, iterations, stage.p, db.p, db.p + (size_t) 3 * n, db.p + (size_t) 6 * n, st, ctx->err, of.p))
+            return NORI_GPU_EINVAL;
+        launchPathgraphCompose(recs.p, offsets.p, counts.p, db.p + (size_t) 3 * n, db.p + (size_t) 6 * n, nPixels, spp, img.p, st, db.p);
+        CK(cudaEventRecord(ev[3], st));
+        CK(cudaMemcpyAsync(images, img.p, (size_t) 6 * nPixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+        if (stats) {
+            stats->vertices = total;
+            cudaEventElapsedTime(&stats->ms_vertices, ev[0], ev[1]); cudaEventElapsedTime(&stats->ms_knn, ev[1], ev[2]); cudaEventElapsedTime(&stats->ms_stage, ev[2], ev[3]);
+            for (int c = 0; c < 3; ++c) stats->dim[c] = hp.dim[c];
+        }
+        unsigned line = 0;
+        if (const unsigned bad = pathgraphChecks(&line)) { ctx->err = "pathgraph_render: device range check failed (" + std::to_string(bad) + " at pathgraph.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+        if (const unsigned bad = pathgraphScatterChecks(&line)) { ctx->err = "pathgraph_render: device range check failed (" + std::to_string(bad) + " at pathgraph_scatter.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+        return NORI_GPU_OK;
+    }
     CK(scratch.alloc(pgScratchBytes(n, P.nCells))); CK(nb.alloc((size_t) n * k)); CK(dk1.alloc(n)); CK(dk2.alloc(n));
     if (!launchPathgraphKnn(recs.p, sizeof(NoriGpuSPoint), n, P, scratch.p, nb.p, k, dk1.p, dk2.p, st, ctx->err)) return NORI_GPU_EINVAL;
     CK(cudaEventRecord(ev[2], st));

@@ -445,6 +445,24 @@ bool launchPathgraphBuildClusters(const void *d_pos, size_t stride, int n, const
     return true;
 }
 
+namespace {
+__global__ void k_pgStrideSeeds(int *__restrict__ seeds, int nSeeds, int n, long long step) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < nSeeds) seeds[s] = (int) (((long long) s * step) % n);
+}
+}
+/// The smallest step >= 0.618 n that shares no factor with n: s -> (s * step) mod n then visits n distinct vertices, consecutive seeds far apart
+/// in the record order (= pixel order), so the seeds spread over the image the way a shuffled list's head does.
+long long pathgraphSeedStep(int n) {
+    long long step = std::max(1LL, (long long) ((double) n * 0.6180339887498949));
+    auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
+    while (gcd(step, n) != 1) ++step;
+    return step;
+}
+void launchPathgraphStrideSeeds(int *d_seeds, int nSeeds, int n, cudaStream_t st) {
+    k_pgStrideSeeds<<<(unsigned) ((nSeeds + 255) / 256), 256, 0, st>>>(d_seeds, nSeeds, n, pathgraphSeedStep(n));
+}
+
 unsigned pathgraphChecks(unsigned *line) { return fetchChecks(line); }
 
 } // namespace ng

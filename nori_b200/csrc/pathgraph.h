@@ -24,6 +24,9 @@ bool launchPathgraphKnn(const void *d_pos, size_t strideBytes, int n, const PgPa
 size_t pgBuildClustersScratchBytes(int n, int nSeeds, int cap);
 bool launchPathgraphBuildClusters(const void *d_pos, size_t strideBytes, int n, const PgParams &P, const int *d_seeds, int nSeeds, int K, void *d_scratch,
                                   int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClusters, int *nListed, cudaStream_t st, std::string &err);
+/// seeds[s] = (s * step) mod n, step = pathgraphSeedStep(n): a fixed scattered choice of distinct vertices (the reference: the head of a shuffled list).
+long long pathgraphSeedStep(int n);
+void launchPathgraphStrideSeeds(int *d_seeds, int nSeeds, int n, cudaStream_t st);
 unsigned pathgraphChecks(unsigned *line);
 
 /// pathgraph_scatter.cu: marginal densities + iterated radiance scatter over the kNN graph (src/pbsdf.cu:2317-2368).
@@ -42,13 +45,14 @@ void launchPathgraphClusterValidate(const NoriGpuSPoint *d_sps, int n, const int
                                     int *d_listed, int *d_flag2, cudaStream_t st);
 size_t pgClusterScratchBytes(int n, int nClusters);
 bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_clusters, int nListed, const int *d_offsets,
-                            int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
+                            int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err,
+                            const int *d_clusterOf = nullptr);
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
 /// Whole pipeline on the device (nori_gpu_pathgraph_render): bounding box of the records, image composition from first vertices.
 void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bounds6, cudaStream_t st);
 float pathgraphOrderedToFloat(unsigned int ordered);
 void launchPathgraphCompose(const NoriGpuSPoint *d_sps, const unsigned long long *d_offsets, const unsigned int *d_counts, const float *d_blur, const float *d_mc,
-                            int nPixels, unsigned int spp, float *d_images, cudaStream_t st);
+                            int nPixels, unsigned int spp, float *d_images, cudaStream_t st, const float *d_direct = nullptr);
 unsigned pathgraphScatterChecks(unsigned *line);
 
 } // namespace ng

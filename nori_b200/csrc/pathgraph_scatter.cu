@@ -356,10 +356,11 @@ __global__ void __launch_bounds__(256) k_pgBounds(const NoriGpuSPoint *__restric
 /// blur, init = eLd, averaged over the pixel's samples in sample order (one thread per pixel: no atomics, a fixed order).
 /// offsets[g] / counts[g]: first record and number of records of camera sample g = pixel * spp + k (the vertex pass's own scan).
 __global__ void k_pgCompose(const NoriGpuSPoint *__restrict__ sps, const unsigned long long *__restrict__ offsets, const unsigned int *__restrict__ counts,
-                            const float *__restrict__ blur, const float *__restrict__ mc, int nPixels, unsigned int spp, float *__restrict__ images) {
+                            const float *__restrict__ blur, const float *__restrict__ mc, const float *__restrict__ direct, int nPixels, unsigned int spp,
+                            float *__restrict__ images) {
     const int pixel = blockIdx.x * blockDim.x + threadIdx.x;
     if (pixel >= nPixels) return;
-    float acc[5][3] = {};
+    float acc[6][3] = {};
     const float inv = 1.0f / (float) spp;
     for (unsigned int k = 0; k < spp; ++k) {
         const unsigned long long g = (unsigned long long) pixel * spp + k;
@@ -368,9 +369,10 @@ __global__ void k_pgCompose(const NoriGpuSPoint *__restrict__ sps, const unsigne
         for (int c = 0; c < 3; ++c) {
             const float eLd = sps[i].eLd[c], eLi = sps[i].eLi[c], m = mc[3 * i + c], b = blur[3 * i + c];
             acc[0][c] += (eLd + m) * inv; acc[1][c] += m * inv; acc[2][c] += (eLi - eLd) * inv; acc[3][c] += b * inv; acc[4][c] += eLd * inv;
+            if (direct) acc[5][c] += direct[3 * i + c] * inv;                 // writeDirectLight (src/cluster.cpp:102-126): the filtered direct light
         }
     }
-    for (int im = 0; im < 5; ++im) for (int c = 0; c < 3; ++c) images[((size_t) im * nPixels + pixel) * 3 + c] = acc[im][c];
+    for (int im = 0; im < (direct ? 6 : 5); ++im) for (int c = 0; c < 3; ++c) images[((size_t) im * nPixels + pixel) * 3 + c] = acc[im][c];
 }
 
 } // namespace
@@ -382,8 +384,8 @@ void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bo
 }
 float pathgraphOrderedToFloat(unsigned int u) { const unsigned int b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; float f; memcpy(&f, &b, 4); return f; }
 void launchPathgraphCompose(const NoriGpuSPoint *d_sps, const unsigned long long *d_offsets, const unsigned int *d_counts, const float *d_blur, const float *d_mc,
-                            int nPixels, unsigned int spp, float *d_images, cudaStream_t st) {
-    k_pgCompose<<<(unsigned) ((nPixels + 127) / 128), 128, 0, st>>>(d_sps, d_offsets, d_counts, d_blur, d_mc, nPixels, spp, d_images);
+                            int nPixels, unsigned int spp, float *d_images, cudaStream_t st, const float *d_direct) {
+    k_pgCompose<<<(unsigned) ((nPixels + 127) / 128), 128, 0, st>>>(d_sps, d_offsets, d_counts, d_blur, d_mc, d_direct, nPixels, spp, d_images);
 }
 
 size_t pgScatterScratchBytes(int n) {
@@ -483,15 +485,15 @@ __device__ __forceinline__ int pgClusterSize(const int *__restrict__ offsets, in
 }
 
 /// What the clustered kernels read of the light records, 16-byte aligned: wi_d, L_directsample | lightpdf, L_bsdfsample | bsdfpdf, L_em | cluster.
-__global__ void k_pgPackLights(const NoriGpuSPoint *__restrict__ sps, const NoriGpuLPoint *__restrict__ lps, int n, float4 *__restrict__ wid,
-                               float4 *__restrict__ Ld, float4 *__restrict__ Lb, float4 *__restrict__ Lem) {
+__global__ void k_pgPackLights(const NoriGpuSPoint *__restrict__ sps, const NoriGpuLPoint *__restrict__ lps, const int *__restrict__ clusterOf, int n,
+                               float4 *__restrict__ wid, float4 *__restrict__ Ld, float4 *__restrict__ Lb, float4 *__restrict__ Lem) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const NoriGpuLPoint &l = lps[i];
     wid[i] = make_float4(sps[i].wi_d[0], sps[i].wi_d[1], sps[i].wi_d[2], 0.f);
     Ld[i] = make_float4(l.L_directsample[0], l.L_directsample[1], l.L_directsample[2], l.lightpdf);
     Lb[i] = make_float4(l.L_bsdfsample[0], l.L_bsdfsample[1], l.L_bsdfsample[2], l.bsdfpdf);
-    Lem[i] = make_float4(l.L_em[0], l.L_em[1], l.L_em[2], __int_as_float(sps[i].groupIdx));
+    Lem[i] = make_float4(l.L_em[0], l.L_em[1], l.L_em[2], __int_as_float(clusterOf ? clusterOf[i] : sps[i].groupIdx));
 }
 
 /// The lists are trusted by the kernels below. flag bits: 1 = offsets not ascending inside [0, nListed], 2 = a member outside [0, n),
@@ -517,45 +519,104 @@ __global__ void k_pgClusterValidate(const NoriGpuSPoint *__restrict__ sps, int n
     }
 }
 
+/// Sub-warp groups. A cluster of at most 8 (16) members is worked on by a quarter (half) of a warp, so that a warp takes up to four
+/// clusters at once; the sums are those of a full warp whose other lanes hold +0: `+ 0.0f` stands for the butterfly steps that would
+/// have added those lanes (it also turns -0 into +0 exactly as they would), then xor W/2 .. 1 inside the group.
+template <int W> __device__ __forceinline__ float pgGroupSum(unsigned int mask, float v) {
+    if (W < 32) v += 0.0f;
+#pragma unroll
+    for (int d = W / 2; d > 0; d >>= 1) v += __shfl_xor_sync(mask, v, d);
+    return v;
+}
+template <int W> __device__ __forceinline__ void pgGroupSum3(unsigned int mask, float *v) {
+    v[0] = pgGroupSum<W>(mask, v[0]); v[1] = pgGroupSum<W>(mask, v[1]); v[2] = pgGroupSum<W>(mask, v[2]);
+}
+/// A warp takes four consecutive clusters: all of at most 8 members -> one per quarter warp; else pair by pair: both of at most 16
+/// members -> one per half warp, else one after the other on the whole warp. F::run<W>(c, lane in group, mask of the group).
+/// The loops are NOT unrolled: one copy of the body per width. The bodies are thousands of instructions long and these kernels wait
+/// on instruction fetch as it is: with the seven copies full unrolling makes they ran 45 % longer (r02_notes.md); a single copy with
+/// W as a run-time value was slower again (4.6 vs 4.2 ms).
+template <class F> __device__ __forceinline__ void pgClusterDispatch(const F &f, const int *__restrict__ offsets, int nClusters, int nListed) {
+    const int c4 = (blockIdx.x * kPgWarps + (threadIdx.x >> 5)) * 4, lane = threadIdx.x & 31;
+    if (c4 >= nClusters) return;
+    int m[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) m[q] = c4 + q < nClusters ? pgClusterSize(offsets, c4 + q, nClusters, nListed) : 0;
+    if (max(max(m[0], m[1]), max(m[2], m[3])) <= 8) { f.template run<8>(c4 + (lane >> 3), lane & 7, 0xffu << (lane & 24)); return; }
+    const int pairMax[2] = {max(m[0], m[1]), max(m[2], m[3])};
+#pragma unroll 1
+    for (int pr = 0; pr < 2; ++pr) {
+        if ((pr ? pairMax[1] : pairMax[0]) <= 16) f.template run<16>(c4 + 2 * pr + (lane >> 4), lane & 15, 0xffffu << (lane & 16));
+        else {
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) f.template run<32>(c4 + 2 * pr + h, lane, 0xffffffffu);
+        }
+    }
+}
+
+/// The senders of a cluster are staged W at a time: lane q of the group loads sender s0 + q — W independent loads in flight instead of
+/// a chain of dependent ones per receiver — and hands it to the group's lanes by shuffle when its turn in the list order comes.
+template <int W> __device__ __forceinline__ float4 pgBcast4(unsigned int mask, const float4 &v, int q) {
+    return make_float4(__shfl_sync(mask, v.x, q, W), __shfl_sync(mask, v.y, q, W), __shfl_sync(mask, v.z, q, W), __shfl_sync(mask, v.w, q, W));
+}
+template <int W> __device__ __forceinline__ float2 pgBcast2(unsigned int mask, const float2 &v, int q) {
+    return make_float2(__shfl_sync(mask, v.x, q, W), __shfl_sync(mask, v.y, q, W));
+}
+
 /// ClusterDirectPdfMarginal (src/pbsdf.cu:1899-1937), clustered branch: for the sending member i, over all members j in list order,
 /// x += lightpdf_i (if wi_d_i lies above j's shading normal) + pdf_j(wi_d_i), y += bsdfpdf_i (if wi_i does) + pdf_j(wi_i).
 /// Lane l takes j = l, l + 32, ...; butterfly over the lanes.
+struct PgClusterDirectMarginal {
+    const float4 *A;
+    const float4 *B;
+    const float4 *wiAll;
+    const float4 *widAll;
+    const float4 *Ld;
+    const float4 *Lb;
+    const int *clusters;
+    int nListed;
+    const int *offsets;
+    int nClusters;
+    float2 *dm;
+    template <int W> __device__ __forceinline__ void run(int c, int lane, unsigned int mask) const {
+        if (c >= nClusters) return;
+        const int m = pgClusterSize(offsets, c, nClusters, nListed);
+        const int *mem = clusters + offsets[c];
+        PgVertex own;
+        if (m <= W && lane < m) { const int j = mem[lane]; pgLoadA(A, j, own); pgLoadB(B, j, own); }     // the usual case: one member per lane, loaded once
+        for (int s0 = 0; s0 < m; s0 += W) {
+            int iMine = 0; float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f), d4 = w4;            // sender s0 + lane: wi | lightpdf, wi_d | bsdfpdf
+            if (s0 + lane < m) { iMine = mem[s0 + lane]; w4 = wiAll[iMine]; d4 = widAll[iMine]; w4.w = Ld[iMine].w; d4.w = Lb[iMine].w; }
+            const int cnt = min(W, m - s0);
+            for (int q = 0; q < cnt; ++q) {
+                const int i = __shfl_sync(mask, iMine, q, W);
+                const float4 sw = pgBcast4<W>(mask, w4, q), sd = pgBcast4<W>(mask, d4, q);
+                const float wi[3] = {sw.x, sw.y, sw.z}, wid[3] = {sd.x, sd.y, sd.z};
+                const float lp = sw.w, bp = sd.w;
+                float x = 0.0f, y = 0.0f;
+                auto term = [&](const PgVertex &v) {
+                    const float pb = pgPdf(v, wi), pl = pgPdf(v, wid);
+                    const float cosh1 = pgDot(wi, v.shN), cosh2 = pgDot(wid, v.shN);
+                    if (cosh2 > 0.0f) x += lp;
+                    if (cosh1 > 0.0f) y += bp;
+                    x += pl; y += pb;
+                };
+                if (m <= W) { if (lane < m) term(own); }
+                else for (int t = lane; t < m; t += W) { const int j = mem[t]; PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v); term(v); }
+                x = pgGroupSum<W>(mask, x); y = pgGroupSum<W>(mask, y);
+                // what ClusterDirectRadiance divides by, once per sender instead of once per pair: 1 / x, 1 / y in double, rounded (-1: term skipped)
+                if (lane == 0) dm[i] = make_float2(x > 0.0f ? (float) (1.0 / (double) x) : -1.0f, y > 0.0f ? (float) (1.0 / (double) y) : -1.0f);
+            }
+        }
+    }
+};
 __global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterDirectMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
                                                                            const float4 *__restrict__ widAll, const float4 *__restrict__ Ld, const float4 *__restrict__ Lb,
                                                                            const int *__restrict__ clusters, int nListed, const int *__restrict__ offsets, int nClusters,
                                                                            float2 *__restrict__ dm) {
-    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (c >= nClusters) return;
-    const int m = pgClusterSize(offsets, c, nClusters, nListed);
-    const int *mem = clusters + offsets[c];
-    PgVertex own; int tOwn = -1;
-    if (m <= 32 && lane < m) { tOwn = mem[lane]; pgLoadA(A, tOwn, own); pgLoadB(B, tOwn, own); }     // the usual case: one member per lane, loaded once
-    for (int s = 0; s < m; ++s) {
-        const int i = mem[s];
-        const float4 w4 = wiAll[i], d4 = widAll[i];
-        const float wi[3] = {w4.x, w4.y, w4.z}, wid[3] = {d4.x, d4.y, d4.z};
-        const float lp = Ld[i].w, bp = Lb[i].w;
-        float x = 0.0f, y = 0.0f;
-        auto term = [&](const PgVertex &v) {
-            const float pb = pgPdf(v, wi), pl = pgPdf(v, wid);
-            const float cosh1 = pgDot(wi, v.shN), cosh2 = pgDot(wid, v.shN);
-            if (cosh2 > 0.0f) x += lp;
-            if (cosh1 > 0.0f) y += bp;
-            x += pl; y += pb;
-        };
-        if (m <= 32) { if (lane < m) term(own); }
-        else for (int t = lane; t < m; t += 32) { const int j = mem[t]; PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v); term(v); }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) { x += __shfl_xor_sync(0xffffffffu, x, d); y += __shfl_xor_sync(0xffffffffu, y, d); }
-        if (lane == 0) dm[i] = make_float2(x, y);
-    }
+    pgClusterDispatch(PgClusterDirectMarginal{A, B, wiAll, widAll, Ld, Lb, clusters, nListed, offsets, nClusters, dm}, offsets, nClusters, nListed);
 }
 
-/// Three-channel butterfly: every lane ends with the total (xor 16, 8, 4, 2, 1 — the order the oracle restates).
-__device__ __forceinline__ void pgWarpSum3(float *v) {
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) { v[0] += __shfl_xor_sync(0xffffffffu, v[0], d); v[1] += __shfl_xor_sync(0xffffffffu, v[1], d); v[2] += __shfl_xor_sync(0xffffffffu, v[2], d); }
-}
 /// computeRatio (src/pbsdf.cu:2146-2172): a cluster that hands out more than it took in is scaled back, channel by channel.
 __device__ __forceinline__ void pgRatio(const float *in, const float *out, float *ratio) {
     for (int c = 0; c < 3; ++c) ratio[c] = in[c] < out[c] ? in[c] / out[c] : 1.0f;
@@ -565,55 +626,77 @@ __device__ __forceinline__ void pgRatio(const float *in, const float *out, float
 /// list order, L_direct_i bsdf_j(wi_d_i) / x_i + L_bsdf_i bsdf_j(wi_i) / y_i —, clampDirectCluster (:2100-2125: in = sum of the members'
 /// L_directsample and L_bsdfsample, out = sum of what they received), computeRatio, updateComputeCluster, addEmitterToDirectLight.
 /// raw: float4 scratch per vertex (a lane re-reads only what it wrote itself).
+struct PgClusterDirect {
+    const float4 *A;
+    const float4 *B;
+    const float4 *wiAll;
+    const float4 *widAll;
+    const float4 *Ld;
+    const float4 *Lb;
+    const float4 *Lem;
+    const float2 *dm;
+    const int *clusters;
+    int nListed;
+    const int *offsets;
+    int nClusters;
+    float4 *raw;
+    float4 *direct;
+    template <int W> __device__ __forceinline__ void run(int c, int lane, unsigned int mask) const {
+        if (c >= nClusters) return;
+        const int m = pgClusterSize(offsets, c, nClusters, nListed);
+        const int *mem = clusters + offsets[c];
+        float in[3] = {0.f, 0.f, 0.f}, out[3] = {0.f, 0.f, 0.f};
+        for (int t0 = 0; t0 < m; t0 += W) {
+            const int t = t0 + lane;
+            const bool valid = t < m;
+            const int j = mem[valid ? t : 0];
+            PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
+            float acc[3] = {0.f, 0.f, 0.f};
+            for (int s0 = 0; s0 < m; s0 += W) {
+                float2 mg = make_float2(-1.f, -1.f); float4 d4 = make_float4(0.f, 0.f, 0.f, 0.f), w4 = d4, La = d4, Lc = d4;      // sender s0 + lane
+                if (s0 + lane < m) { const int i = mem[s0 + lane]; mg = dm[i]; if (mg.x >= 0.0f) { d4 = widAll[i]; La = Ld[i]; } if (mg.y >= 0.0f) { w4 = wiAll[i]; Lc = Lb[i]; } }
+                const int cnt = min(W, m - s0);
+                for (int q = 0; q < cnt; ++q) {
+                    const float2 g = pgBcast2<W>(mask, mg, q);
+                    float fin[3] = {0.f, 0.f, 0.f};
+                    if (g.x >= 0.0f) {
+                        const float4 sd = pgBcast4<W>(mask, d4, q), L = pgBcast4<W>(mask, La, q);
+                        const float wid[3] = {sd.x, sd.y, sd.z};
+                        float f[3]; pgBsdf(v, wid, f);
+                        fin[0] = fin[0] + (L.x * f[0]) * g.x; fin[1] = fin[1] + (L.y * f[1]) * g.x; fin[2] = fin[2] + (L.z * f[2]) * g.x;
+                    }
+                    if (g.y >= 0.0f) {
+                        const float4 sw = pgBcast4<W>(mask, w4, q), L = pgBcast4<W>(mask, Lc, q);
+                        const float wi[3] = {sw.x, sw.y, sw.z};
+                        float f[3]; pgBsdf(v, wi, f);
+                        fin[0] = fin[0] + (L.x * f[0]) * g.y; fin[1] = fin[1] + (L.y * f[1]) * g.y; fin[2] = fin[2] + (L.z * f[2]) * g.y;
+                    }
+                    acc[0] += fin[0]; acc[1] += fin[1]; acc[2] += fin[2];
+                }
+            }
+            if (valid) {
+                raw[j] = make_float4(acc[0], acc[1], acc[2], 0.f);
+                out[0] += acc[0]; out[1] += acc[1]; out[2] += acc[2];
+                const float4 a = Ld[j], b = Lb[j];
+                in[0] += a.x; in[1] += a.y; in[2] += a.z;
+                in[0] += b.x; in[1] += b.y; in[2] += b.z;
+            }
+        }
+        pgGroupSum3<W>(mask, in); pgGroupSum3<W>(mask, out);
+        float ratio[3]; pgRatio(in, out, ratio);
+        for (int t = lane; t < m; t += W) {
+            const int j = mem[t];
+            const float4 r = raw[j], e = Lem[j];
+            direct[j] = make_float4(r.x * ratio[0] + e.x, r.y * ratio[1] + e.y, r.z * ratio[2] + e.z, 0.f);
+        }
+    }
+};
 __global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterDirect(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
                                                                    const float4 *__restrict__ widAll, const float4 *__restrict__ Ld, const float4 *__restrict__ Lb,
                                                                    const float4 *__restrict__ Lem, const float2 *__restrict__ dm, const int *__restrict__ clusters,
                                                                    int nListed, const int *__restrict__ offsets, int nClusters, float4 *__restrict__ raw,
                                                                    float4 *__restrict__ direct) {
-    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (c >= nClusters) return;
-    const int m = pgClusterSize(offsets, c, nClusters, nListed);
-    const int *mem = clusters + offsets[c];
-    float in[3] = {0.f, 0.f, 0.f}, out[3] = {0.f, 0.f, 0.f};
-    for (int t0 = 0; t0 < m; t0 += 32) {
-        const int t = t0 + lane;
-        if (t >= m) continue;
-        const int j = mem[t];
-        PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
-        float acc[3] = {0.f, 0.f, 0.f};
-        for (int s = 0; s < m; ++s) {
-            const int i = mem[s];
-            const float2 mg = dm[i];
-            float fin[3] = {0.f, 0.f, 0.f};
-            if (mg.x > 0.0f) {
-                const float inv = (float) (1.0 / (double) mg.x);
-                const float4 d4 = widAll[i], L = Ld[i];
-                const float wid[3] = {d4.x, d4.y, d4.z};
-                float f[3]; pgBsdf(v, wid, f);
-                fin[0] = fin[0] + (L.x * f[0]) * inv; fin[1] = fin[1] + (L.y * f[1]) * inv; fin[2] = fin[2] + (L.z * f[2]) * inv;
-            }
-            if (mg.y > 0.0f) {
-                const float inv = (float) (1.0 / (double) mg.y);
-                const float4 w4 = wiAll[i], L = Lb[i];
-                const float wi[3] = {w4.x, w4.y, w4.z};
-                float f[3]; pgBsdf(v, wi, f);
-                fin[0] = fin[0] + (L.x * f[0]) * inv; fin[1] = fin[1] + (L.y * f[1]) * inv; fin[2] = fin[2] + (L.z * f[2]) * inv;
-            }
-            acc[0] += fin[0]; acc[1] += fin[1]; acc[2] += fin[2];
-        }
-        raw[j] = make_float4(acc[0], acc[1], acc[2], 0.f);
-        out[0] += acc[0]; out[1] += acc[1]; out[2] += acc[2];
-        const float4 a = Ld[j], b = Lb[j];
-        in[0] += a.x; in[1] += a.y; in[2] += a.z;
-        in[0] += b.x; in[1] += b.y; in[2] += b.z;
-    }
-    pgWarpSum3(in); pgWarpSum3(out);
-    float ratio[3]; pgRatio(in, out, ratio);
-    for (int t = lane; t < m; t += 32) {
-        const int j = mem[t];
-        const float4 r = raw[j], e = Lem[j];
-        direct[j] = make_float4(r.x * ratio[0] + e.x, r.y * ratio[1] + e.y, r.z * ratio[2] + e.z, 0.f);
-    }
+    pgClusterDispatch(PgClusterDirect{A, B, wiAll, widAll, Ld, Lb, Lem, dm, clusters, nListed, offsets, nClusters, raw, direct}, offsets, nClusters, nListed);
 }
 /// Vertices outside every cluster keep their own estimate (ClusterDirectRadiance's else branch: eLd) + their emission.
 __global__ void k_pgLooseDirect(const float4 *__restrict__ eLd, const float4 *__restrict__ Lem, int n, float4 *__restrict__ direct) {
@@ -623,43 +706,69 @@ __global__ void k_pgLooseDirect(const float4 *__restrict__ eLd, const float4 *__
     direct[i] = make_float4(d.x + e.x, d.y + e.y, d.z + e.z, 0.f);
 }
 
+/// What a pass needs of a sender, once per vertex instead of once per pair: x = the factor computeNoneZeroElements multiplies the
+/// evaluations by, 1 / pm_i in double, rounded (-1 where it leaves its cleared elements untouched: pm_i <= 0 or rrpdf_i <= 1e-7),
+/// y = 1 if the vertex has a successor whose radiance it hands on (MX's `nidx > 0`), else 0.
+__device__ __forceinline__ float2 pgSenderTerms(const float4 *__restrict__ A, int i, int n, float pmI) {
+    const float4 a1 = __ldg(A + 4 * (size_t) i + 1), a3 = __ldg(A + 4 * (size_t) i + 3);
+    const bool live = pmI > 0.0f && a1.w > 1e-7f;
+    return make_float2(live ? (float) (1.0 / (double) pmI) : -1.0f, (__float_as_int(a3.w) > 0 && i + 1 < n) ? 1.0f : 0.0f);
+}
+
 /// allGPUClusterPdfMarginal (src/pbsdf.cu:1239-1263): pm[i] = sum over the members j of i's cluster, except i's predecessor on its
 /// path, of pdf_j(wi_i) rrpdf_j; for a vertex outside every cluster its own pdf_i(wi_i) rrpdf_i.
+struct PgClusterMarginal {
+    const float4 *A;
+    const float4 *B;
+    const float4 *wiAll;
+    const int *clusters;
+    int nListed;
+    const int *offsets;
+    int nClusters;
+    int n;
+    float2 *pm;
+    template <int W> __device__ __forceinline__ void run(int c, int lane, unsigned int mask) const {
+        if (c >= nClusters) return;
+        const int m = pgClusterSize(offsets, c, nClusters, nListed);
+        const int *mem = clusters + offsets[c];
+        PgVertex own;
+        if (m <= W && lane < m) { const int j = mem[lane]; pgLoadA(A, j, own); pgLoadB(B, j, own); }
+        for (int s0 = 0; s0 < m; s0 += W) {
+            float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);                                     // sender s0 + lane: wi | index
+            if (s0 + lane < m) { const int i = mem[s0 + lane]; w4 = wiAll[i]; w4.w = __int_as_float(i); }
+            const int cnt = min(W, m - s0);
+            for (int q = 0; q < cnt; ++q) {
+                const float4 sw = pgBcast4<W>(mask, w4, q);
+                const int i = __float_as_int(sw.w);
+                const float wi[3] = {sw.x, sw.y, sw.z};
+                float sum = 0.0f;
+                if (m <= W) { if (lane < m && own.nidx != i) sum += pgPdf(own, wi) * own.rrpdf; }
+                else for (int t = lane; t < m; t += W) {
+                    const int j = mem[t];
+                    PgVertex v; pgLoadA(A, j, v);
+                    if (v.nidx == i) continue;
+                    pgLoadB(B, j, v);
+                    sum += pgPdf(v, wi) * v.rrpdf;
+                }
+                sum = pgGroupSum<W>(mask, sum);
+                if (lane == 0) pm[i] = pgSenderTerms(A, i, n, sum);
+            }
+        }
+    }
+};
 __global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
                                                                      const int *__restrict__ clusters, int nListed, const int *__restrict__ offsets, int nClusters,
-                                                                     float *__restrict__ pm) {
-    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (c >= nClusters) return;
-    const int m = pgClusterSize(offsets, c, nClusters, nListed);
-    const int *mem = clusters + offsets[c];
-    PgVertex own;
-    if (m <= 32 && lane < m) { const int j = mem[lane]; pgLoadA(A, j, own); pgLoadB(B, j, own); }
-    for (int s = 0; s < m; ++s) {
-        const int i = mem[s];
-        const float4 w4 = wiAll[i];
-        const float wi[3] = {w4.x, w4.y, w4.z};
-        float sum = 0.0f;
-        if (m <= 32) { if (lane < m && own.nidx != i) sum += pgPdf(own, wi) * own.rrpdf; }
-        else for (int t = lane; t < m; t += 32) {
-            const int j = mem[t];
-            PgVertex v; pgLoadA(A, j, v);
-            if (v.nidx == i) continue;
-            pgLoadB(B, j, v);
-            sum += pgPdf(v, wi) * v.rrpdf;
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
-        if (lane == 0) pm[i] = sum;
-    }
+                                                                     int n, float2 *__restrict__ pm) {
+    pgClusterDispatch(PgClusterMarginal{A, B, wiAll, clusters, nListed, offsets, nClusters, n, pm}, offsets, nClusters, nListed);
 }
 __global__ void k_pgLooseMarginal(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll, const float4 *__restrict__ Lem,
-                                  int n, float *__restrict__ pm) {
+                                  int n, float2 *__restrict__ pm) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || __float_as_int(Lem[i].w) != -1) return;
     PgVertex v; pgLoadA(A, i, v); pgLoadB(B, i, v);
     const float4 w4 = wiAll[i];
     const float wi[3] = {w4.x, w4.y, w4.z};
-    pm[i] = pgPdf(v, wi) * v.rrpdf;
+    pm[i] = pgSenderTerms(A, i, n, pgPdf(v, wi) * v.rrpdf);
 }
 
 /// One pass over one cluster: MX with the elements of computeNoneZeroElements (src/pbsdf.cu:1265-1307, 1059-1085) — member j receives
@@ -667,70 +776,93 @@ __global__ void k_pgLooseMarginal(const float4 *__restrict__ A, const float4 *__
 /// left its cleared array untouched (pm_i <= 0 or rrpdf_i <= 1e-7) —, clampCluster (:2127-2144: in += temp[i + 1] of those members,
 /// out += what the members received; both totals RUN ON over the passes, as the reference never clears them inside its loop, :3492-3516),
 /// computeRatio, updateComputeCluster, and, when another pass follows, updateWithOptDirectRadiance: tempOut = direct + radiance.
+struct PgClusterPass {
+    const float4 *A;
+    const float4 *B;
+    const float4 *wiAll;
+    const float2 *pm;
+    const int *clusters;
+    int nListed;
+    const int *offsets;
+    int nClusters;
+    int n;
+    const float4 *tempIn;
+    const float4 *direct;
+    float4 *clusterIn;
+    float4 *clusterOut;
+    float4 *radiance;
+    float4 *tempOut;
+    template <int W> __device__ __forceinline__ void run(int c, int lane, unsigned int mask) const {
+        if (c >= nClusters) return;
+        const int m = pgClusterSize(offsets, c, nClusters, nListed);
+        const int *mem = clusters + offsets[c];
+        float in[3] = {0.f, 0.f, 0.f}, out[3] = {0.f, 0.f, 0.f};
+        for (int t0 = 0; t0 < m; t0 += W) {
+            const int t = t0 + lane;
+            const bool valid = t < m;
+            const int j = mem[valid ? t : 0];
+            PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
+            float acc[3] = {0.f, 0.f, 0.f};
+            for (int s0 = 0; s0 < m; s0 += W) {
+                float2 ps = make_float2(-1.f, 0.f); float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f), src = w4;      // sender s0 + lane (pgSenderTerms, wi, temp[i + 1])
+                if (s0 + lane < m) { const int i = mem[s0 + lane]; ps = pm[i]; if (ps.y != 0.0f) { src = tempIn[i + 1]; if (ps.x >= 0.0f) w4 = wiAll[i]; } }
+                const int cnt = min(W, m - s0);
+                for (int q = 0; q < cnt; ++q) {
+                    const float2 g = pgBcast2<W>(mask, ps, q);
+                    if (g.y == 0.0f) continue;                   // no successor: hands nothing on (the same for every lane of the group)
+                    float e[3] = {0.f, 0.f, 0.f};
+                    if (g.x >= 0.0f) {
+                        const float4 sw = pgBcast4<W>(mask, w4, q);
+                        const float wi[3] = {sw.x, sw.y, sw.z};
+                        float f[3]; pgBsdf(v, wi, f);
+                        e[0] = f[0] * g.x; e[1] = f[1] * g.x; e[2] = f[2] * g.x;
+                    }
+                    const float4 sr = pgBcast4<W>(mask, src, q);
+                    acc[0] += e[0] * sr.x; acc[1] += e[1] * sr.y; acc[2] += e[2] * sr.z;
+                }
+            }
+            if (valid) {
+                radiance[j] = make_float4(acc[0], acc[1], acc[2], 0.f);
+                out[0] += acc[0]; out[1] += acc[1]; out[2] += acc[2];
+                if (v.nidx > 0 && j + 1 < n) { const float4 sr = tempIn[j + 1]; in[0] += sr.x; in[1] += sr.y; in[2] += sr.z; }
+            }
+        }
+        pgGroupSum3<W>(mask, in); pgGroupSum3<W>(mask, out);
+        const float4 pin = clusterIn[c], pout = clusterOut[c];
+        in[0] = pin.x + in[0]; in[1] = pin.y + in[1]; in[2] = pin.z + in[2];
+        out[0] = pout.x + out[0]; out[1] = pout.y + out[1]; out[2] = pout.z + out[2];
+        float ratio[3]; pgRatio(in, out, ratio);
+        __syncwarp(mask);
+        if (lane == 0) { clusterIn[c] = make_float4(in[0], in[1], in[2], 0.f); clusterOut[c] = make_float4(out[0], out[1], out[2], 0.f); }
+        for (int t = lane; t < m; t += W) {
+            const int j = mem[t];
+            float4 r = radiance[j];
+            r = make_float4(r.x * ratio[0], r.y * ratio[1], r.z * ratio[2], 0.f);
+            radiance[j] = r;
+            if (tempOut) { const float4 d = direct[j]; tempOut[j] = make_float4(d.x + r.x, d.y + r.y, d.z + r.z, 0.f); }
+        }
+    }
+};
 __global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterPass(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll,
-                                                                 const float *__restrict__ pm, const int *__restrict__ clusters, int nListed,
+                                                                 const float2 *__restrict__ pm, const int *__restrict__ clusters, int nListed,
                                                                  const int *__restrict__ offsets, int nClusters, int n, const float4 *__restrict__ tempIn,
                                                                  const float4 *__restrict__ direct, float4 *__restrict__ clusterIn, float4 *__restrict__ clusterOut,
                                                                  float4 *__restrict__ radiance, float4 *__restrict__ tempOut) {
-    const int c = blockIdx.x * kPgWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (c >= nClusters) return;
-    const int m = pgClusterSize(offsets, c, nClusters, nListed);
-    const int *mem = clusters + offsets[c];
-    float in[3] = {0.f, 0.f, 0.f}, out[3] = {0.f, 0.f, 0.f};
-    for (int t0 = 0; t0 < m; t0 += 32) {
-        const int t = t0 + lane;
-        if (t >= m) continue;
-        const int j = mem[t];
-        PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
-        float acc[3] = {0.f, 0.f, 0.f};
-        for (int s = 0; s < m; ++s) {
-            const int i = mem[s];
-            const float4 a1 = __ldg(A + 4 * (size_t) i + 1), a3 = __ldg(A + 4 * (size_t) i + 3);
-            if (__float_as_int(a3.w) <= 0 || i + 1 >= n) continue;
-            const float p = pm[i];
-            float e[3] = {0.f, 0.f, 0.f};
-            if (p > 0.0f && a1.w > 1e-7f) {
-                const float inv = (float) (1.0 / (double) p);
-                const float4 w4 = wiAll[i];
-                const float wi[3] = {w4.x, w4.y, w4.z};
-                float f[3]; pgBsdf(v, wi, f);
-                e[0] = f[0] * inv; e[1] = f[1] * inv; e[2] = f[2] * inv;
-            }
-            const float4 src = tempIn[i + 1];
-            acc[0] += e[0] * src.x; acc[1] += e[1] * src.y; acc[2] += e[2] * src.z;
-        }
-        radiance[j] = make_float4(acc[0], acc[1], acc[2], 0.f);
-        out[0] += acc[0]; out[1] += acc[1]; out[2] += acc[2];
-        if (v.nidx > 0 && j + 1 < n) { const float4 src = tempIn[j + 1]; in[0] += src.x; in[1] += src.y; in[2] += src.z; }
-    }
-    pgWarpSum3(in); pgWarpSum3(out);
-    const float4 pin = clusterIn[c], pout = clusterOut[c];
-    in[0] = pin.x + in[0]; in[1] = pin.y + in[1]; in[2] = pin.z + in[2];
-    out[0] = pout.x + out[0]; out[1] = pout.y + out[1]; out[2] = pout.z + out[2];
-    float ratio[3]; pgRatio(in, out, ratio);
-    __syncwarp();
-    if (lane == 0) { clusterIn[c] = make_float4(in[0], in[1], in[2], 0.f); clusterOut[c] = make_float4(out[0], out[1], out[2], 0.f); }
-    for (int t = lane; t < m; t += 32) {
-        const int j = mem[t];
-        float4 r = radiance[j];
-        r = make_float4(r.x * ratio[0], r.y * ratio[1], r.z * ratio[2], 0.f);
-        radiance[j] = r;
-        if (tempOut) { const float4 d = direct[j]; tempOut[j] = make_float4(d.x + r.x, d.y + r.y, d.z + r.z, 0.f); }
-    }
+    pgClusterDispatch(PgClusterPass{A, B, wiAll, pm, clusters, nListed, offsets, nClusters, n, tempIn, direct, clusterIn, clusterOut, radiance, tempOut}, offsets, nClusters, nListed);
 }
 /// The same pass for the vertices outside every cluster (MX's else branch: the vertex's own element, no ratio).
 __global__ void k_pgLoosePass(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll, const float4 *__restrict__ Lem,
-                              const float *__restrict__ pm, int n, const float4 *__restrict__ tempIn, const float4 *__restrict__ direct,
+                              const float2 *__restrict__ pm, int n, const float4 *__restrict__ tempIn, const float4 *__restrict__ direct,
                               float4 *__restrict__ radiance, float4 *__restrict__ tempOut) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || __float_as_int(Lem[i].w) != -1) return;
     PgVertex v; pgLoadA(A, i, v); pgLoadB(B, i, v);
     float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (v.nidx > 0 && i + 1 < n) {
-        const float p = pm[i];
+    const float2 ps = pm[i];
+    if (ps.y != 0.0f) {
         float e[3] = {0.f, 0.f, 0.f};
-        if (p > 0.0f && v.rrpdf > 1e-7f) {
-            const float inv = (float) (1.0 / (double) p);
+        if (ps.x >= 0.0f) {
+            const float inv = ps.x;
             const float4 w4 = wiAll[i];
             const float wi[3] = {w4.x, w4.y, w4.z};
             float f[3]; pgBsdf(v, wi, f);
@@ -754,28 +886,29 @@ void launchPathgraphClusterValidate(const NoriGpuSPoint *d_sps, int n, const int
 }
 
 size_t pgClusterScratchBytes(int n, int nClusters) {
-    // A, B, wi, eLi, eLd (pack) + wid, Ld, Lb, Lem + direct, tempA, tempB, radiance (16 each) + dm (8) + pm (4) per vertex; in / out per cluster
-    return (size_t) n * (64 + 48 + 3 * 16 + 4 * 16 + 4 * 16 + 8 + 4) + (size_t) nClusters * 32 + 256;
+    // A, B, wi, eLi, eLd (pack) + wid, Ld, Lb, Lem + direct, tempA, tempB, radiance (16 each) + dm (8) + pm (8) per vertex; in / out per cluster
+    return (size_t) n * (64 + 48 + 3 * 16 + 4 * 16 + 4 * 16 + 8 + 8) + (size_t) nClusters * 32 + 256;
 }
 
 /// SPoints::ClusterScatterWithDirectOptNR (include/nori/shadingPoint.h:600-624): ClusterDirect, then ClusterIterations3 (src/pbsdf.cu:3475-3532)
 /// on the same clusters. d_direct / d_blur / d_mc: n x 3 floats (device): the filtered direct light, the last pass's radiance
 /// (ret.blur_results[iterations - 1]) and lastRun on the temp that pass read (ret.mc_results[iterations - 1]). iterations >= 1.
 bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_clusters, int nListed, const int *d_offsets,
-                            int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err) {
+                            int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err,
+                            const int *d_clusterOf) {
     if (n <= 0 || nClusters < 0 || iterations < 1) { err = "pathgraph_cluster: bad sizes"; return false; }
     float4 *A = static_cast<float4 *>(d_scratch), *B = A + 4 * (size_t) n, *wi = B + 3 * (size_t) n, *eLi = wi + n, *eLd = eLi + n;
     float4 *wid = eLd + n, *Ld = wid + n, *Lb = Ld + n, *Lem = Lb + n, *direct = Lem + n, *tempA = direct + n, *tempB = tempA + n, *radiance = tempB + n;
     float4 *cin = radiance + n, *cout = cin + nClusters;
     float2 *dm = reinterpret_cast<float2 *>(cout + nClusters);
-    float *pm = reinterpret_cast<float *>(dm + n);
-    const unsigned gt = (unsigned) ((n + 255) / 256), gc = (unsigned) ((nClusters + kPgWarps - 1) / kPgWarps);
+    float2 *pm = dm + n;
+    const unsigned gt = (unsigned) ((n + 255) / 256), gc = (unsigned) (((nClusters + 3) / 4 + kPgWarps - 1) / kPgWarps);    // a warp takes four clusters
     k_pgPack<<<gt, 256, 0, st>>>(d_sps, n, A, B, wi, eLi, eLd);
-    k_pgPackLights<<<gt, 256, 0, st>>>(d_sps, d_lps, n, wid, Ld, Lb, Lem);
+    k_pgPackLights<<<gt, 256, 0, st>>>(d_sps, d_lps, d_clusterOf, n, wid, Ld, Lb, Lem);
     if (nClusters > 0) {
         k_pgClusterDirectMarginal<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, wid, Ld, Lb, d_clusters, nListed, d_offsets, nClusters, dm);
         k_pgClusterDirect<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, wid, Ld, Lb, Lem, dm, d_clusters, nListed, d_offsets, nClusters, radiance, direct);
-        k_pgClusterMarginal<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, d_clusters, nListed, d_offsets, nClusters, pm);
+        k_pgClusterMarginal<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, d_clusters, nListed, d_offsets, nClusters, n, pm);
         cudaMemsetAsync(cin, 0, (size_t) nClusters * 2 * sizeof(float4), st);
     }
     k_pgLooseDirect<<<gt, 256, 0, st>>>(eLd, Lem, n, direct);

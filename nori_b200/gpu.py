@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_build_clusters", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_build_clusters", "nori_gpu_pathgraph_stride_seeds", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
 ]
 
 
@@ -144,6 +144,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_path_vertices_lights.argtypes = [vp, C.POINTER(RenderDesc), vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_pathgraph_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_build_clusters.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, ip, vp, vp, vp, ip, C.POINTER(ip), C.POINTER(ip), C.POINTER(C.c_float)]
+    L.nori_gpu_pathgraph_stride_seeds.argtypes = [ip, ip, vp]
     L.nori_gpu_pathgraph_cluster.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_scatter_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_knn.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, vp, vp, C.POINTER(C.c_float)]
@@ -163,6 +164,14 @@ def _f32(a, shape=None):
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def pathgraph_stride_seeds(n: int, n_seeds: int):
+    """nori_gpu_pathgraph_stride_seeds: n_seeds distinct scattered vertex indices (what the cluster mode of pathgraph_render seeds with)."""
+    out = np.empty(n_seeds, np.int32)
+    if load_library().nori_gpu_pathgraph_stride_seeds(int(n), int(n_seeds), _p(out)) != 0:
+        raise NoriGpuError("pathgraph_stride_seeds: need 0 < n_seeds <= n")
+    return out
 
 
 def pathgraph_grid(points, k: int, dk: int, dim=None) -> HashParams:
@@ -445,12 +454,14 @@ class Engine:
         return pm, blur, mc, ms.value
 
     def pathgraph_render(self, k: int, iterations: int, mode: str = "mis", integrator=None, sample_first=0, sample_last=1):
-        """The pg tool end to end on the device: {"full", "indirect", "pt", "blur", "init"} images (H, W, 3) + stats."""
+        """The pg tool end to end on the device: {"full", "indirect", "pt", "blur", "init"} images (H, W, 3) + stats; mode "cluster"
+        (the tool's default: BuildClusters + ClusterScatterWithDirectOptNR) adds "direct"."""
         d = self.render_desc(integrator, 1, sample_first, sample_last)
         W, H = self._wh
-        img = np.empty((5, H, W, 3), np.float32); st = PathGraphStats()
-        self._ck(self.L.nori_gpu_pathgraph_render(self.h, C.byref(d), {"scatter": 0, "mis": 1}[mode], int(k), int(iterations), _p(img), C.byref(st)))
-        out = dict(zip(("full", "indirect", "pt", "blur", "init"), img))
+        names = ("full", "indirect", "pt", "blur", "init") + (("direct",) if mode == "cluster" else ())
+        img = np.empty((len(names), H, W, 3), np.float32); st = PathGraphStats()
+        self._ck(self.L.nori_gpu_pathgraph_render(self.h, C.byref(d), {"scatter": 0, "mis": 1, "cluster": 2}[mode], int(k), int(iterations), _p(img), C.byref(st)))
+        out = dict(zip(names, img))
         return out, {"vertices": int(st.vertices), "ms_vertices": st.ms_vertices, "ms_knn": st.ms_knn, "ms_stage": st.ms_stage, "dim": list(st.dim)}
 
     def pathgraph_mis(self, points, neighbors, knn, iterations: int):

@@ -62,8 +62,32 @@ def scatter_leg(spp, k, iterations):
     out["direct"] = {"what": "computeDirectScatterAllOnGPU + computeScatterAllOnGPURecordWithDirectOpt (SPoints::computeScatterRadianceAOGWithProcessRecordingAndDirectLightOPT) "
                              "on the tracer's own light records", "nori_b200_ms_device": direct_ms,
                      "vertices_with_light_sample": int((lp["lightpdf"] > 0).sum()), "emitter_hits_by_continuation": int((lp["L_bsdfsample"].sum(1) > 0).sum())}
+    # the tool's default mode: cluster builder + clustered scatter (seeds: every vertex index s * step mod n, K = k members)
+    from nori_b200.gpu import pathgraph_stride_seeds
+    seeds = pathgraph_stride_seeds(len(v3), len(v3) // k + 1)
+    bms, cms = [], []
+    for _ in range(3):
+        of, members, offsets, t = e.pathgraph_build_clusters(v3, hp, seeds); bms.append(t)
+        cdirect, cblur, cmc, t = e.pathgraph_cluster(v3, lp, members, offsets, iterations, cluster_of=of); cms.append(t)
+    t0 = time.perf_counter(); cimg, cst = e.pathgraph_render(k, iterations, mode="cluster", sample_first=0, sample_last=spp); t_cr = time.perf_counter() - t0
+    sizes = np.diff(np.append(offsets, len(members)))
+    out["cluster"] = {"what": "SPoints::BuildClusters + ClusterScatterWithDirectOptNR (the pg tool's default mode)", "clusters": int(len(offsets)),
+                      "members_mean_max": [float(sizes.mean()), int(sizes.max())], "pairs": int((sizes.astype(np.int64) ** 2).sum()),
+                      "build_ms_device": float(np.median(bms[1:])), "scatter_ms_device": float(np.median(cms[1:])),
+                      "render_wall_ms": t_cr * 1e3, "render_device_ms": [cst["ms_vertices"], cst["ms_knn"], cst["ms_stage"]]}
     if have_refcuda():
         ref = RefCuda()
+        vc = v3.copy(); vc["groupIdx"] = of
+        csec = []
+        for _ in range(2):
+            rd, rb, rm, sec = ref.cluster(vc, lp, members, offsets, iterations); csec.append(sec)
+        out["cluster"]["reference_scatter_ms"] = float(csec[-1]) * 1e3
+        out["cluster"]["scatter_speedup_vs_reference"] = float(csec[-1]) * 1e3 / out["cluster"]["scatter_ms_device"]
+        out["cluster"]["max_rel_row_error_blur"] = float((np.abs(cblur - rb) / (np.abs(rb).max(-1, keepdims=True) + 1e-3)).max())
+        rb_ = ref.build_clusters(np.ascontiguousarray(v3["pos"]), list(hp.dim), list(hp.cellsize), list(hp.minb), seeds, k)
+        out["cluster"]["reference_build_ms"] = rb_["seconds"] * 1e3
+        out["cluster"]["reference_clusters"] = int(len(rb_["off3"]))
+        out["cluster"]["first_level_equal"] = bool(np.array_equal(rb_["g3"] >= 0, of >= 0))
         dsec = []
         for _ in range(2):
             rdirect, rdblur, rdmc, sec = ref.direct(v3, lp, nb, dknn, knn=knn, iterations=iterations); dsec.append(sec)

@@ -63,6 +63,11 @@ def main():
             offs = np.arange(0, len(order) - 100, 40, dtype=np.int32)                                                              # ... the last one long, 0 loose
             of = np.empty(len(order), np.int32); of[order] = np.minimum(np.arange(len(order)) // 40, len(offs) - 1)
             eng.pathgraph_cluster(v2, lp, order, offs, 2, cluster_of=of)
+            from nori_b200.gpu import pathgraph_stride_seeds
+            hpc = pathgraph_grid(v2, 12, 12)
+            of2, mem2, off2, _ = eng.pathgraph_build_clusters(v2, hpc, pathgraph_stride_seeds(len(v2), len(v2) // 12 + 1))
+            eng.pathgraph_cluster(v2, lp, mem2, off2, 1, cluster_of=of2)
+            eng.pathgraph_render(12, 2, mode="cluster", sample_first=0, sample_last=2)
             print("  pathgraph", len(v), "vertices", flush=True)
         if name == "bunny_normals":
             eng.render(stream_mode=0, sample_first=0, sample_last=3)          # block-seeded stream

@@ -136,3 +136,53 @@ def test_gpu_builder_vs_compiled_reference_live(engine, port):
     g3, n3 = port.pathgraph_cluster_subdivide(pts, r["g2"], lists2, r["off2"], K)
     np.testing.assert_array_equal(g3, r["g3"])
     assert n3 == len(r["off3"]) and abs(len(off) - n3) < 0.05 * n3
+
+
+@pytest.mark.gpu
+def test_gpu_cluster_mode_end_to_end_equals_the_stages(gpu_scene, scenes, port):
+    """nori_gpu_pathgraph_render in NORI_PG_CLUSTER mode = the `pg` tool's default mode on the scene's own paths, everything on the device:
+    the six images equal — to the bit, there is no atomic anywhere in this mode — what the host composes (src/cluster.cpp:23-126) from the
+    stages called one by one: vertex + light records, grid, stride seeds, cluster builder, clustered scatter. The oracle's pipeline on
+    the same records agrees to the bit as well; the filter moves light between the vertices of a cluster but (the ratio clamps) never
+    creates any: every cluster's filtered direct light stays within what its members sampled."""
+    from nori_b200.gpu import pathgraph_grid, pathgraph_stride_seeds
+    e = gpu_scene("table_mis"); s = scenes("table_mis")
+    W, H, spp, K, it = 160, 120, 2, 12, 2
+    e.set_camera(s.sample_to_camera, s.camera_to_world, W, H, s.near_clip, s.far_clip)
+    try:
+        v, lp = e.path_vertices(sample_first=0, sample_last=spp, lights=True)
+        n = len(v)
+        hp = pathgraph_grid(v, K, K)
+        seeds = pathgraph_stride_seeds(n, n // K + 1)
+        of, members, offsets, _ = e.pathgraph_build_clusters(v, hp, seeds)
+        check_lists(of, members, offsets)
+        direct, blur, mc, _ = e.pathgraph_cluster(v, lp, members, offsets, it, cluster_of=of)
+        img, st = e.pathgraph_render(K, it, mode="cluster", sample_first=0, sample_last=spp)
+    finally:
+        e.set_camera(s.sample_to_camera, s.camera_to_world, s.width, s.height, s.near_clip, s.far_clip)
+    assert st["vertices"] == n and st["dim"] == list(hp.dim) and set(img) == {"full", "indirect", "pt", "blur", "init", "direct"}
+    first = np.nonzero(np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]]))[0]
+    g = v["groupIdx"][first]
+
+    def image(rows):
+        out = np.zeros((H * W, 3), np.float32)
+        for kk in range(spp):                               # sample order, float32 accumulation as the kernel's
+            sel = g % spp == kk
+            out[g[sel] // spp] += rows[first[sel]] * np.float32(1.0 / spp)
+        return out.reshape(H, W, 3)
+    np.testing.assert_array_equal(img["direct"], image(direct))
+    np.testing.assert_array_equal(img["blur"], image(blur))
+    np.testing.assert_array_equal(img["indirect"], image(mc))
+    np.testing.assert_array_equal(img["full"], image(v["eLd"] + mc))
+    np.testing.assert_array_equal(img["init"], image(v["eLd"]))
+    assert np.isfinite(img["full"]).all() and img["direct"].mean() > 0 and img["blur"].mean() > 0
+    vv = v.copy(); vv["groupIdx"] = of
+    od, ob, om = port.pathgraph_cluster(vv, lp, members, offsets, it, sequential=False)
+    for got, want in ((direct, od), (blur, ob), (mc, om)):
+        np.testing.assert_array_equal(got.view(np.uint32), want.view(np.uint32))
+    og, olists, ooff = port.pathgraph_build_clusters(np.ascontiguousarray(v["pos"]), list(hp.dim), list(hp.cellsize), list(hp.minb), seeds, K)
+    np.testing.assert_array_equal(of, og); np.testing.assert_array_equal(members, olists); np.testing.assert_array_equal(offsets, ooff)
+    inside = of >= 0
+    took = np.zeros((len(offsets), 3)); np.add.at(took, of[inside], lp["L_directsample"][inside].astype(np.float64) + lp["L_bsdfsample"][inside])
+    gave = np.zeros((len(offsets), 3)); np.add.at(gave, of[inside], (direct[inside] - lp["L_em"][inside]).astype(np.float64))
+    assert (gave <= took * (1 + 1e-4) + 1e-4).all()
