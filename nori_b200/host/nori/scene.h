@@ -264,11 +264,13 @@ void sampleRadianceGpu(const Scene *scene, int n, const uint32_t *pixel, const u
 /// scatter driver computeScatterAllOnGPURecord), then the images writeFullLight / writeIndirectLight / writeFullinit compose from each path's
 /// FIRST vertex (src/cluster.cpp:23-107): full = eLd + mc, indirect = mc, pt = eLi - eLd, blur, init = eLd, all of the last
 /// pass. With several samples per pixel the reference's loop keeps the last path of a pixel; here they are averaged.
+/// mode NORI_PG_CLUSTER (2) = the tool's DEFAULT "opt" mode (src/cluster.cpp:204-218): SPoints::BuildClusters with k members per cluster +
+/// ClusterScatterWithDirectOptNR, with `direct` = the filtered direct light writeDirectLight writes (:102-126) beside the five.
 struct PathGraphImages {
-    std::unique_ptr<Bitmap> full, indirect, pt, blur, init;
+    std::unique_ptr<Bitmap> full, indirect, pt, blur, init, direct;
     uint64_t vertices = 0; double msVertices = 0, msKnn = 0, msScatter = 0;
 };
-PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, bool mis = true, int device = 0);
+PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, int mode = 1 /* NORI_PG_MIS; 0 scatter, 2 cluster */, int device = 0);
 
 /// Search path for files named in scene descriptions (the reference prepends the scene's directory)
 class FileResolver {

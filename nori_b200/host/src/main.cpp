@@ -134,21 +134,23 @@ void liStream(const Scene *scene, const std::string &path, int sppOverride) {
 
 /// The `pg` tool's "knn" mode (src/cluster.cpp:156-253) on this scene's own paths: <out>_k-K_full / _indirect / _indirect_pt /
 /// _indirect_blur and <out>_Le_init, named as the reference names them.
-void pathGraph(const Scene *scene, const std::string &outName, int device, int sppOverride, int k, int iterations, bool mis) {
+void pathGraph(const Scene *scene, const std::string &outName, int device, int sppOverride, int k, int iterations, int mode) {
     const uint32_t spp = sppOverride > 0 ? (uint32_t) sppOverride : 1u;
-    std::cout << "Path graph: " << spp << " spp, k = " << k << ", " << iterations << " iterations (" << (mis ? "MIS gather" : "scatter") << ") .. " << std::flush;
-    PathGraphImages r = pathGraphGpu(scene, 0, spp, k, iterations, mis, device);
-    std::cout << "done. (" << r.vertices << " vertices in " << timeString(r.msVertices) << ", kNN " << r.msKnn << " ms, scatter " << r.msScatter << " ms)" << std::endl;
+    const char *what = mode == 2 ? "clusters" : (mode == 1 ? "MIS gather" : "scatter");
+    std::cout << "Path graph: " << spp << " spp, k = " << k << ", " << iterations << " iterations (" << what << ") .. " << std::flush;
+    PathGraphImages r = pathGraphGpu(scene, 0, spp, k, iterations, mode, device);
+    std::cout << "done. (" << r.vertices << " vertices in " << timeString(r.msVertices) << ", " << (mode == 2 ? "clusters " : "kNN ") << r.msKnn << " ms, scatter " << r.msScatter << " ms)" << std::endl;
     const std::string stem = outName + "_k-" + std::to_string(k);
     r.full->saveEXR(stem + "_full"); r.indirect->saveEXR(stem + "_indirect"); r.pt->saveEXR(stem + "_indirect_pt");
     r.blur->saveEXR(stem + "_indirect_blur"); r.init->saveEXR(outName + "_Le_init");
+    if (r.direct) { r.direct->saveEXR(stem + "_direct"); r.init->saveEXR(stem + "_direct_o"); }      // writeDirectLight (src/cluster.cpp:102-126)
 }
 
 } // namespace
 
 int main(int argc, char **argv) {
     std::string sceneFile, dumpFile, outName, resumeFile, checkpointFile, liFile;
-    bool pgMis = true;
+    int pgMode = 1;                                      // 1: the tool's "knn" mode (MIS gather), 0: scatter driver, 2: its default "opt" mode (clusters)
     int device = 0, spp = 0, pgK = 0, pgIterations = 1; long first = -1, last = -1; bool png = true;
     std::vector<int> devices;
     for (int i = 1; i < argc; ++i) {
@@ -169,7 +171,8 @@ int main(int argc, char **argv) {
         else if (a == "--checkpoint") checkpointFile = value("--checkpoint");
         else if (a == "--no-png") png = false;
         else if (a == "--device-dedup") setDeviceObjDedup(true);
-        else if (a == "--pathgraph-scatter") pgMis = false;
+        else if (a == "--pathgraph-scatter") pgMode = 0;
+        else if (a == "--pathgraph-cluster") pgMode = 2;
         else if (a == "--pathgraph") { pgK = atoi(value("--pathgraph").c_str()); if (i + 1 < argc && argv[i + 1][0] != '-' && isdigit((unsigned char) argv[i + 1][0]) && i + 2 < argc) pgIterations = atoi(argv[++i]); }
         else if (a == "--warptest") {
             try {
@@ -189,7 +192,7 @@ int main(int argc, char **argv) {
         else sceneFile = a;
     }
     if (sceneFile.empty()) {
-        std::cerr << "Syntax: " << argv[0] << " [--device N | --devices A,B,..] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--resume FILE] [--checkpoint FILE] [--dump FILE] [--pathgraph K [ITERATIONS] [--pathgraph-scatter]] <scene.xml>" << std::endl;
+        std::cerr << "Syntax: " << argv[0] << " [--device N | --devices A,B,..] [--spp N] [--first A --last B] [--out NAME] [--no-png] [--resume FILE] [--checkpoint FILE] [--dump FILE] [--pathgraph K [ITERATIONS] [--pathgraph-scatter | --pathgraph-cluster]] <scene.xml>" << std::endl;
         return -1;
     }
     try {
@@ -204,7 +207,7 @@ int main(int argc, char **argv) {
             const size_t dot = sceneFile.find_last_of('.');
             outName = dot == std::string::npos || (slash != std::string::npos && dot < slash) ? sceneFile : sceneFile.substr(0, dot);
         }
-        if (pgK > 0) { pathGraph(scene, outName, device, spp, pgK, pgIterations, pgMis); return 0; }
+        if (pgK > 0) { pathGraph(scene, outName, device, spp, pgK, pgIterations, pgMode); return 0; }
         render(scene, outName, device, spp, first, last, png, resumeFile, checkpointFile, devices);
     } catch (const std::exception &e) {
         std::cerr << "Fatal error: " << e.what() << std::endl;

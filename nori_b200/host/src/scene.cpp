@@ -336,21 +336,23 @@ void renderGpu(const Scene *scene, ImageBlock &result, uint32_t sampleFirst, uin
     }
 }
 
-PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, bool mis, int device) {
+PathGraphImages pathGraphGpu(const Scene *scene, uint32_t sampleFirst, uint32_t sampleLast, int k, int iterations, int mode, int device) {
     if (sampleLast <= sampleFirst) throw NoriException("pathGraphGpu: empty sample range");
     if (k < 1 || iterations < 1) throw NoriException("pathGraphGpu: k and the number of iterations must be positive");
     nori_gpu_ctx *ctx = scene->gpu(device);
     const NoriGpuRenderDesc d = renderDesc(scene, sampleFirst, sampleLast);
     const Vector2i size = scene->getCamera()->getOutputSize();
     const size_t plane = (size_t) size.x * size.y * 3;
-    std::vector<float> images(5 * plane);
+    if (mode != NORI_PG_SCATTER && mode != NORI_PG_MIS && mode != NORI_PG_CLUSTER) throw NoriException("pathGraphGpu: unknown mode %d", mode);
+    const int nImages = mode == NORI_PG_CLUSTER ? 6 : 5;
+    std::vector<float> images(nImages * plane);
     NoriGpuPathGraphStats st;
-    // records, grid, neighbours, scatter / gather and the five images in one call: nothing but the images leaves the device
-    check(ctx, nori_gpu_pathgraph_render(ctx, &d, mis ? NORI_PG_MIS : NORI_PG_SCATTER, k, iterations, images.data(), &st), "nori_gpu_pathgraph_render");
+    // records, grid, neighbours or clusters, scatter / gather and the images in one call: nothing but the images leaves the device
+    check(ctx, nori_gpu_pathgraph_render(ctx, &d, mode, k, iterations, images.data(), &st), "nori_gpu_pathgraph_render");
     PathGraphImages out;
     out.vertices = st.vertices; out.msVertices = st.ms_vertices; out.msKnn = st.ms_knn; out.msScatter = st.ms_stage;
-    std::unique_ptr<Bitmap> *slots[5] = {&out.full, &out.indirect, &out.pt, &out.blur, &out.init};
-    for (int i = 0; i < 5; ++i) {
+    std::unique_ptr<Bitmap> *slots[6] = {&out.full, &out.indirect, &out.pt, &out.blur, &out.init, &out.direct};
+    for (int i = 0; i < nImages; ++i) {
         slots[i]->reset(new Bitmap(size.x, size.y));
         std::copy(images.begin() + (std::ptrdiff_t) (i * plane), images.begin() + (std::ptrdiff_t) ((i + 1) * plane), (*slots[i])->data());
     }

@@ -268,3 +268,40 @@ def test_cli_pathgraph_tool_writes_the_reference_tools_images(tmp_path):
     np.testing.assert_array_equal(ind, image(wmc[0]))                 # a gather without atomics: deterministic
     np.testing.assert_array_equal(blur, image(wblur[0]))
     assert init.mean() > 1e-3 and blur.mean() > 0 and first.sum() > 0.2 * flat.height * flat.width
+
+
+@pytest.mark.gpu
+def test_cli_pathgraph_cluster_mode_is_the_tools_default_mode(tmp_path):
+    """`nori_b200 --pathgraph K ITER --pathgraph-cluster`: the `pg` tool's DEFAULT "opt" mode (src/cluster.cpp:204-218: BuildClusters +
+    ClusterScatterWithDirectOptNR) on the scene's own paths; beside the five images it writes the filtered direct light as
+    writeDirectLight does (<out>_k-K_direct, and the unfiltered one as _direct_o). Equal, to the bit, to the same stages called one by
+    one through the Python binding of the same C ABI."""
+    xml = os.path.join(HOST, "all_tags.xml")
+    out = str(tmp_path / "pgc")
+    r = subprocess.run([HOST_BIN, "--out", out, "--spp", "1", "--pathgraph", "10", "2", "--pathgraph-cluster", xml], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Path graph: 1 spp, k = 10, 2 iterations (clusters)" in r.stdout and "clusters " in r.stdout, r.stdout
+    names = ("_k-10_full", "_k-10_indirect", "_k-10_indirect_pt", "_k-10_indirect_blur", "_Le_init", "_k-10_direct", "_k-10_direct_o")
+    full, ind, pt, blur, init, direct, direct_o = (read_exr(out + s + ".exr") for s in names)
+    flat = FlatScene.load(os.path.join(HOST, "all_tags.npz"))
+    from nori_b200.gpu import Engine, pathgraph_grid, pathgraph_stride_seeds
+    engine = Engine(0)
+    engine.load_scene(flat)
+    v, lp = engine.path_vertices(sample_first=0, sample_last=1, lights=True)
+    hp = pathgraph_grid(v, 10, 10)
+    of, members, offsets, _ = engine.pathgraph_build_clusters(v, hp, pathgraph_stride_seeds(len(v), len(v) // 10 + 1))
+    wdirect, wblur, wmc, _ = engine.pathgraph_cluster(v, lp, members, offsets, 2, cluster_of=of)
+    engine.close()
+    first = np.concatenate([[True], v["groupIdx"][1:] != v["groupIdx"][:-1]])
+    pix = v["groupIdx"][first]
+    def image(rows):
+        img = np.zeros((flat.height * flat.width, 3), np.float32); img[pix] = rows[first]
+        return img.reshape(flat.height, flat.width, 3)
+    np.testing.assert_array_equal(direct, image(wdirect))
+    np.testing.assert_array_equal(direct_o, image(v["eLd"]))
+    np.testing.assert_array_equal(init, direct_o)
+    np.testing.assert_array_equal(blur, image(wblur))
+    np.testing.assert_array_equal(ind, image(wmc))
+    np.testing.assert_array_equal(full, image(v["eLd"] + wmc))
+    assert np.isfinite(full).all(), "non-finite pixels"
+    assert direct.mean() > 1e-4 and blur.mean() > 0, (float(direct.mean()), float(blur.mean()), float(init.mean()))
