@@ -369,6 +369,18 @@ int nori_gpu_pathgraph_stride_seeds(int n, int n_seeds, int32_t *seeds);
  * each n x 3 floats. The sums inside a cluster are taken in list order here (the reference: float atomics, any order). 1 <= iterations <= 64. */
 int nori_gpu_pathgraph_cluster(nori_gpu_ctx *ctx, const NoriGpuSPoint *points, const NoriGpuLPoint *lights, int n, const int32_t *clusters,
                                int n_listed, const int32_t *offsets, int n_clusters, int iterations, float *direct, float *blur, float *mc, float *ms);
+/* The tool's other cluster modes, without direct light (src/cluster.cpp:219-224), on the same cluster arrays:
+ *   NORI_PG_CLUSTER_ELEMENTS  mode "n", SPoints::ClusterScatter2 (include/nori/shadingPoint.h:556-573): the blocks' elements bsdf_j(wi_i) / pm_i of
+ *                             precomputedMatrixElemtns applied by ClusterIterations (src/pbsdf.cu:3359-3418);
+ *   NORI_PG_CLUSTER_SCATTER   modes "t" / "l", SPoints::ClusterScatter / loadClusterScatter (:536-554): computeClusterScatterAllOnGPURecord /
+ *                             ClusterScatterRecord (src/pbsdf.cu:3108-3172, 3030-3106) with allGPUClusterScatterRadiance (:1309-1345): (bsdf_j(wi_i) * temp) / pm_i,
+ *                             nothing to the sender's own successor, nothing at all from a sender without a usable density.
+ * Per pass: the cluster blocks, each cluster scaled back by its running in / out totals -> blur[it]; temp = radiance + eLd; lastRun -> mc[it].
+ * blur / mc: iterations x n x 3 floats. */
+#define NORI_PG_CLUSTER_ELEMENTS 0
+#define NORI_PG_CLUSTER_SCATTER 1
+int nori_gpu_pathgraph_cluster_scatter(nori_gpu_ctx *ctx, int order, const NoriGpuSPoint *points, int n, const int32_t *clusters, int n_listed,
+                                       const int32_t *offsets, int n_clusters, int iterations, float *blur, float *mc, float *ms);
 /* The tool's whole pipeline in one call, as SPoints::BuildKNN + one of the two drivers run it (include/nori/shadingPoint.h:776-806,
  * 496-510): hash grid + kNN over the records' positions, then the scatter (mode NORI_PG_SCATTER) or the MIS gather (NORI_PG_MIS)
  * on the rows the search left ON THE DEVICE (the k consumer's count knn[i] of each row, as the reference passes cu_knn). Same

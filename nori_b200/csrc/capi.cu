@@ -1352,6 +1352,45 @@ extern "C" int nori_gpu_pathgraph_cluster(nori_gpu_ctx *ctx, const NoriGpuSPoint
     return NORI_GPU_OK;
 }
 
+extern "C" int nori_gpu_pathgraph_cluster_scatter(nori_gpu_ctx *ctx, int order, const NoriGpuSPoint *points, int n, const int32_t *clusters, int n_listed,
+                                                  const int32_t *offsets, int n_clusters, int iterations, float *blur, float *mc, float *ms) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    REQUIRE(points && blur && mc && n > 0, "pathgraph_cluster_scatter: bad arguments");
+    REQUIRE(order == NORI_PG_CLUSTER_ELEMENTS || order == NORI_PG_CLUSTER_SCATTER, "pathgraph_cluster_scatter: unknown order");
+    REQUIRE(n_clusters >= 0 && n_listed >= 0 && n_listed <= n && (n_clusters == 0 ? n_listed == 0 : (clusters && offsets)), "pathgraph_cluster_scatter: bad cluster lists");
+    REQUIRE(iterations >= 1 && iterations <= 64, "pathgraph_cluster_scatter: iterations outside [1, 64]");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<NoriGpuSPoint> sps; DevBuf<int> cl, off, listed, flag; DevBuf<unsigned char> scratch; DevBuf<float> out;
+    CK(sps.alloc(n)); CK(cl.alloc(std::max(n_listed, 1))); CK(off.alloc(std::max(n_clusters, 1))); CK(listed.alloc(n)); CK(flag.alloc(2));
+    CK(scratch.alloc(pgClusterScratchBytes(n, n_clusters))); CK(out.alloc((size_t) 6 * n * iterations));
+    cudaStream_t st = ctx->stream;
+    if (int rc = stagedCopy(ctx, sps.p, points, (size_t) n * sizeof(NoriGpuSPoint))) return rc;
+    if (n_listed > 0) if (int rc = stagedCopy(ctx, cl.p, clusters, (size_t) n_listed * 4)) return rc;
+    if (n_clusters > 0) CK(cudaMemcpyAsync(off.p, offsets, (size_t) n_clusters * 4, cudaMemcpyHostToDevice, st));
+    launchPathgraphClusterValidate(sps.p, n, cl.p, n_listed, off.p, n_clusters, listed.p, flag.p, st);
+    int chk[2] = {0, 0};
+    CK(cudaMemcpyAsync(chk, flag.p, sizeof chk, cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
+    REQUIRE(!(chk[0] & 1), "pathgraph_cluster_scatter: offsets must start at 0 and ascend inside [0, n_listed]");
+    REQUIRE(!(chk[0] & 2), "pathgraph_cluster_scatter: cluster member outside [0, n)");
+    REQUIRE(!(chk[0] & 16), "pathgraph_cluster_scatter: groupIdx outside [-1, n_clusters)");
+    REQUIRE(!(chk[0] & 4), "pathgraph_cluster_scatter: a member's groupIdx is not the cluster that lists it");
+    REQUIRE(!(chk[0] & 8), "pathgraph_cluster_scatter: a vertex is listed twice");
+    REQUIRE(chk[1] == n_listed, "pathgraph_cluster_scatter: a vertex names a cluster that does not list it");
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    struct Ev { cudaEvent_t a, b; ~Ev() { cudaEventDestroy(a); cudaEventDestroy(b); } } evGuard{e0, e1};
+    CK(cudaEventRecord(e0, st));
+    const size_t rows = (size_t) 3 * n * iterations;
+    if (!launchPathgraphClusterScatter(sps.p, n, cl.p, n_listed, off.p, n_clusters, iterations, order, scratch.p, out.p, out.p + rows, st, ctx->err)) return NORI_GPU_EINVAL;
+    CK(cudaEventRecord(e1, st));
+    CK(cudaMemcpyAsync(blur, out.p, rows * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(mc, out.p + rows, rows * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st)); CK(cudaGetLastError());
+    if (ms) cudaEventElapsedTime(ms, e0, e1);
+    unsigned line = 0;
+    if (const unsigned b = pathgraphScatterChecks(&line)) { ctx->err = "pathgraph_cluster_scatter: device range check failed (" + std::to_string(b) + " at pathgraph_scatter.cu:" + std::to_string(line) + ")"; return NORI_GPU_ECUDA; }
+    return NORI_GPU_OK;
+}
+
 extern "C" int nori_gpu_pathgraph_filter(nori_gpu_ctx *ctx, int mode, const NoriGpuSPoint *points, int n, const NoriGpuHashParams *hp, int iterations,
                                          float *pdfmarginal, float *blur, float *mc, float ms[2]) {
     if (!ctx) return NORI_GPU_EINVAL;

@@ -47,6 +47,8 @@ size_t pgClusterScratchBytes(int n, int nClusters);
 bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_lps, int n, const int *d_clusters, int nListed, const int *d_offsets,
                             int nClusters, int iterations, void *d_scratch, float *d_direct, float *d_blur, float *d_mc, cudaStream_t st, std::string &err,
                             const int *d_clusterOf = nullptr);
+bool launchPathgraphClusterScatter(const NoriGpuSPoint *d_sps, int n, const int *d_clusters, int nListed, const int *d_offsets, int nClusters, int iterations,
+                                   int scatterOrder, void *d_scratch, float *d_blur, float *d_mc, cudaStream_t st, std::string &err);
 void launchPathgraphValidate(const int *d_neighbors, int pitchInts, int rowInts, const int *d_knn, int n, int *d_flag, cudaStream_t st);
 /// Whole pipeline on the device (nori_gpu_pathgraph_render): bounding box of the records, image composition from first vertices.
 void launchPathgraphBounds(const NoriGpuSPoint *d_sps, int n, unsigned int *d_bounds6, cudaStream_t st);

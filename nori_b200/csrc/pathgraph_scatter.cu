@@ -489,7 +489,8 @@ __global__ void k_pgPackLights(const NoriGpuSPoint *__restrict__ sps, const Nori
                                float4 *__restrict__ wid, float4 *__restrict__ Ld, float4 *__restrict__ Lb, float4 *__restrict__ Lem) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const NoriGpuLPoint &l = lps[i];
+    NoriGpuLPoint l = {};                                       // no light records (the drivers without direct light): zeros
+    if (lps) l = lps[i];
     wid[i] = make_float4(sps[i].wi_d[0], sps[i].wi_d[1], sps[i].wi_d[2], 0.f);
     Ld[i] = make_float4(l.L_directsample[0], l.L_directsample[1], l.L_directsample[2], l.lightpdf);
     Lb[i] = make_float4(l.L_bsdfsample[0], l.L_bsdfsample[1], l.L_bsdfsample[2], l.bsdfpdf);
@@ -792,6 +793,7 @@ struct PgClusterPass {
     float4 *clusterOut;
     float4 *radiance;
     float4 *tempOut;
+    int scatterOrder;            // 0: MX on computeNoneZeroElements' elements, (bsdf * inv) * temp; 1: allGPUClusterScatterRadiance, (bsdf * temp) * inv, not to the sender's own successor
     template <int W> __device__ __forceinline__ void run(int c, int lane, unsigned int mask) const {
         if (c >= nClusters) return;
         const int m = pgClusterSize(offsets, c, nClusters, nListed);
@@ -804,20 +806,25 @@ struct PgClusterPass {
             PgVertex v; pgLoadA(A, j, v); pgLoadB(B, j, v);
             float acc[3] = {0.f, 0.f, 0.f};
             for (int s0 = 0; s0 < m; s0 += W) {
-                float2 ps = make_float2(-1.f, 0.f); float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f), src = w4;      // sender s0 + lane (pgSenderTerms, wi, temp[i + 1])
-                if (s0 + lane < m) { const int i = mem[s0 + lane]; ps = pm[i]; if (ps.y != 0.0f) { src = tempIn[i + 1]; if (ps.x >= 0.0f) w4 = wiAll[i]; } }
+                float2 ps = make_float2(-1.f, 0.f); float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f), src = w4;      // sender s0 + lane (pgSenderTerms, wi | index, temp[i + 1])
+                if (s0 + lane < m) { const int i = mem[s0 + lane]; ps = pm[i]; if (ps.y != 0.0f) { src = tempIn[i + 1]; if (ps.x >= 0.0f) { w4 = wiAll[i]; w4.w = __int_as_float(i); } } }
                 const int cnt = min(W, m - s0);
                 for (int q = 0; q < cnt; ++q) {
                     const float2 g = pgBcast2<W>(mask, ps, q);
                     if (g.y == 0.0f) continue;                   // no successor: hands nothing on (the same for every lane of the group)
+                    if (scatterOrder && g.x < 0.0f) continue;    // allGPUClusterScatterRadiance: a sender without a usable density does nothing at all
                     float e[3] = {0.f, 0.f, 0.f};
+                    const float4 sr = pgBcast4<W>(mask, src, q);
                     if (g.x >= 0.0f) {
                         const float4 sw = pgBcast4<W>(mask, w4, q);
                         const float wi[3] = {sw.x, sw.y, sw.z};
                         float f[3]; pgBsdf(v, wi, f);
+                        if (scatterOrder) {
+                            if (j != __float_as_int(sw.w) + 1) { acc[0] += (f[0] * sr.x) * g.x; acc[1] += (f[1] * sr.y) * g.x; acc[2] += (f[2] * sr.z) * g.x; }
+                            continue;
+                        }
                         e[0] = f[0] * g.x; e[1] = f[1] * g.x; e[2] = f[2] * g.x;
                     }
-                    const float4 sr = pgBcast4<W>(mask, src, q);
                     acc[0] += e[0] * sr.x; acc[1] += e[1] * sr.y; acc[2] += e[2] * sr.z;
                 }
             }
@@ -847,13 +854,13 @@ __global__ void __launch_bounds__(kPgWarps * 32) k_pgClusterPass(const float4 *_
                                                                  const float2 *__restrict__ pm, const int *__restrict__ clusters, int nListed,
                                                                  const int *__restrict__ offsets, int nClusters, int n, const float4 *__restrict__ tempIn,
                                                                  const float4 *__restrict__ direct, float4 *__restrict__ clusterIn, float4 *__restrict__ clusterOut,
-                                                                 float4 *__restrict__ radiance, float4 *__restrict__ tempOut) {
-    pgClusterDispatch(PgClusterPass{A, B, wiAll, pm, clusters, nListed, offsets, nClusters, n, tempIn, direct, clusterIn, clusterOut, radiance, tempOut}, offsets, nClusters, nListed);
+                                                                 float4 *__restrict__ radiance, float4 *__restrict__ tempOut, int scatterOrder) {
+    pgClusterDispatch(PgClusterPass{A, B, wiAll, pm, clusters, nListed, offsets, nClusters, n, tempIn, direct, clusterIn, clusterOut, radiance, tempOut, scatterOrder}, offsets, nClusters, nListed);
 }
 /// The same pass for the vertices outside every cluster (MX's else branch: the vertex's own element, no ratio).
 __global__ void k_pgLoosePass(const float4 *__restrict__ A, const float4 *__restrict__ B, const float4 *__restrict__ wiAll, const float4 *__restrict__ Lem,
                               const float2 *__restrict__ pm, int n, const float4 *__restrict__ tempIn, const float4 *__restrict__ direct,
-                              float4 *__restrict__ radiance, float4 *__restrict__ tempOut) {
+                              float4 *__restrict__ radiance, float4 *__restrict__ tempOut, int scatterOrder) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || __float_as_int(Lem[i].w) != -1) return;
     PgVertex v; pgLoadA(A, i, v); pgLoadB(B, i, v);
@@ -867,9 +874,10 @@ __global__ void k_pgLoosePass(const float4 *__restrict__ A, const float4 *__rest
             const float wi[3] = {w4.x, w4.y, w4.z};
             float f[3]; pgBsdf(v, wi, f);
             e[0] = f[0] * inv; e[1] = f[1] * inv; e[2] = f[2] * inv;
+            if (scatterOrder) { const float4 src = tempIn[i + 1]; e[0] = (f[0] * src.x) * inv; e[1] = (f[1] * src.y) * inv; e[2] = (f[2] * src.z) * inv; }
         }
         const float4 src = tempIn[i + 1];
-        r = make_float4(e[0] * src.x, e[1] * src.y, e[2] * src.z, 0.f);
+        r = scatterOrder ? make_float4(e[0], e[1], e[2], 0.f) : make_float4(e[0] * src.x, e[1] * src.y, e[2] * src.z, 0.f);
     }
     radiance[i] = r;
     if (tempOut) { const float4 d = direct[i]; tempOut[i] = make_float4(d.x + r.x, d.y + r.y, d.z + r.z, 0.f); }
@@ -918,8 +926,8 @@ bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_l
     for (int it = 0; it < iterations; ++it) {
         float4 *tout = it == iterations - 1 ? nullptr : ((it & 1) ? tempB : tempA);
         if (nClusters > 0)
-            k_pgClusterPass<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, pm, d_clusters, nListed, d_offsets, nClusters, n, tin, direct, cin, cout, radiance, tout);
-        k_pgLoosePass<<<gt, 256, 0, st>>>(A, B, wi, Lem, pm, n, tin, direct, radiance, tout);
+            k_pgClusterPass<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, pm, d_clusters, nListed, d_offsets, nClusters, n, tin, direct, cin, cout, radiance, tout, 0);
+        k_pgLoosePass<<<gt, 256, 0, st>>>(A, B, wi, Lem, pm, n, tin, direct, radiance, tout, 0);
         if (tout) tin = tout;
     }
     k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_blur, n);
@@ -927,6 +935,42 @@ bool launchPathgraphCluster(const NoriGpuSPoint *d_sps, const NoriGpuLPoint *d_l
     k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_mc, n);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("pathgraph_cluster: ") + cudaGetErrorString(e); return false; }
+    return true;
+}
+
+/// The tool's cluster modes without direct light: scatterOrder 0 = SPoints::ClusterScatter2 (mode "n": precomputedMatrixElemtns + ClusterIterations,
+/// src/pbsdf.cu:3359-3418), 1 = SPoints::ClusterScatter / loadClusterScatter (modes "t", "l": computeClusterScatterAllOnGPURecord / ClusterScatterRecord,
+/// :3108-3172, 3030-3106, with allGPUClusterScatterRadiance :1309-1345). Per pass: the cluster block, the clusters' running totals and ratio -> blur[it];
+/// temp = radiance + eLd (updateRadiance with it + 1); lastRun -> mc[it]. d_blur / d_mc: iterations x n x 3 floats. Scratch: pgClusterScratchBytes.
+bool launchPathgraphClusterScatter(const NoriGpuSPoint *d_sps, int n, const int *d_clusters, int nListed, const int *d_offsets, int nClusters, int iterations,
+                                   int scatterOrder, void *d_scratch, float *d_blur, float *d_mc, cudaStream_t st, std::string &err) {
+    if (n <= 0 || nClusters < 0 || iterations < 1) { err = "pathgraph_cluster_scatter: bad sizes"; return false; }
+    float4 *A = static_cast<float4 *>(d_scratch), *B = A + 4 * (size_t) n, *wi = B + 3 * (size_t) n, *eLi = wi + n, *eLd = eLi + n;
+    float4 *wid = eLd + n, *Ld = wid + n, *Lb = Ld + n, *Lem = Lb + n, *direct = Lem + n, *temp = direct + n, *tempB = temp + n, *radiance = tempB + n;
+    float4 *cin = radiance + n, *cout = cin + nClusters;
+    float2 *dm = reinterpret_cast<float2 *>(cout + nClusters);
+    float2 *pm = dm + n;
+    const unsigned gt = (unsigned) ((n + 255) / 256), gc = (unsigned) (((nClusters + 3) / 4 + kPgWarps - 1) / kPgWarps);
+    k_pgPack<<<gt, 256, 0, st>>>(d_sps, n, A, B, wi, eLi, eLd);
+    k_pgPackLights<<<gt, 256, 0, st>>>(d_sps, nullptr, nullptr, n, wid, Ld, Lb, Lem);          // only Lem.w = the vertex's cluster is read
+    if (nClusters > 0) {
+        k_pgClusterMarginal<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, d_clusters, nListed, d_offsets, nClusters, n, pm);
+        cudaMemsetAsync(cin, 0, (size_t) nClusters * 2 * sizeof(float4), st);
+    }
+    k_pgLooseMarginal<<<gt, 256, 0, st>>>(A, B, wi, Lem, n, pm);
+    k_pgUpdate<<<gt, 256, 0, st>>>(eLi, eLd, radiance, temp, n, 0);                            // temp = eLi
+    for (int it = 0; it < iterations; ++it) {
+        if (nClusters > 0)
+            k_pgClusterPass<<<gc, kPgWarps * 32, 0, st>>>(A, B, wi, pm, d_clusters, nListed, d_offsets, nClusters, n, temp, nullptr, cin, cout, radiance, nullptr, scatterOrder);
+        k_pgLoosePass<<<gt, 256, 0, st>>>(A, B, wi, Lem, pm, n, temp, nullptr, radiance, nullptr, scatterOrder);
+        k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_blur + (size_t) it * 3 * n, n);
+        k_pgUpdate<<<gt, 256, 0, st>>>(eLi, eLd, radiance, temp, n, it + 1);                   // temp = radiance + eLd
+        k_pgLastRun<<<gt, 256, 0, st>>>(A, B, wi, temp, radiance, n);
+        k_pgUnpack<<<gt, 256, 0, st>>>(radiance, d_mc + (size_t) it * 3 * n, n);
+    }
+    (void) direct; (void) tempB;
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("pathgraph_cluster_scatter: ") + cudaGetErrorString(e); return false; }
     return true;
 }
 

@@ -29,7 +29,7 @@ EXPORTS = [
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
-    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_build_clusters", "nori_gpu_pathgraph_stride_seeds", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
+    "nori_gpu_li", "nori_gpu_obj_dedup", "nori_gpu_path_vertices", "nori_gpu_path_vertices_lights", "nori_gpu_pathgraph_direct", "nori_gpu_pathgraph_scatter_direct", "nori_gpu_pathgraph_cluster", "nori_gpu_pathgraph_cluster_scatter", "nori_gpu_pathgraph_build_clusters", "nori_gpu_pathgraph_stride_seeds", "nori_gpu_pathgraph_knn", "nori_gpu_pathgraph_grid", "nori_gpu_pathgraph_scatter", "nori_gpu_pathgraph_mis", "nori_gpu_pathgraph_filter", "nori_gpu_pathgraph_render",
 ]
 
 
@@ -144,6 +144,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_path_vertices_lights.argtypes = [vp, C.POINTER(RenderDesc), vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.nori_gpu_pathgraph_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_build_clusters.argtypes = [vp, vp, C.c_uint64, ip, C.POINTER(HashParams), vp, ip, vp, vp, vp, ip, C.POINTER(ip), C.POINTER(ip), C.POINTER(C.c_float)]
+    L.nori_gpu_pathgraph_cluster_scatter.argtypes = [vp, ip, vp, ip, vp, ip, vp, ip, ip, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_stride_seeds.argtypes = [ip, ip, vp]
     L.nori_gpu_pathgraph_cluster.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, ip, vp, vp, vp, C.POINTER(C.c_float)]
     L.nori_gpu_pathgraph_scatter_direct.argtypes = [vp, vp, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp, C.POINTER(C.c_float)]
@@ -432,6 +433,19 @@ class Engine:
         self._ck(self.L.nori_gpu_pathgraph_cluster(self.h, _p(pts), _p(lps), n, _p(cl) if len(cl) else None, len(cl), _p(off) if len(off) else None, len(off),
                                                    int(iterations), _p(direct), _p(blur), _p(mc), C.byref(ms)))
         return direct, blur, mc, ms.value
+
+    def pathgraph_cluster_scatter(self, points, clusters, offsets, iterations: int, order: str = "elements", cluster_of=None):
+        """The pg tool's cluster modes without direct light: order "elements" = ClusterScatter2 (mode n), "scatter" = ClusterScatter /
+        loadClusterScatter (modes t, l). Returns (blur (it, n, 3), mc (it, n, 3), ms)."""
+        assert points.dtype == SPOINT_DTYPE
+        pts = np.ascontiguousarray(points); n = pts.shape[0]
+        if cluster_of is not None:
+            pts = pts.copy(); pts["groupIdx"] = np.asarray(cluster_of, np.int32)
+        cl = np.ascontiguousarray(clusters, np.int32).reshape(-1); off = np.ascontiguousarray(offsets, np.int32).reshape(-1)
+        blur = np.empty((iterations, n, 3), np.float32); mc = np.empty((iterations, n, 3), np.float32); ms = C.c_float()
+        self._ck(self.L.nori_gpu_pathgraph_cluster_scatter(self.h, {"elements": 0, "scatter": 1}[order], _p(pts), n, _p(cl) if len(cl) else None, len(cl),
+                                                           _p(off) if len(off) else None, len(off), int(iterations), _p(blur), _p(mc), C.byref(ms)))
+        return blur, mc, ms.value
 
     def pathgraph_knn(self, points, hp: "HashParams"):
         """buildHashGridAndFindKNN: points = (n, 3) float32 or an SPoint record array. Returns (neighbors, knn, dknn, ms)."""

@@ -100,12 +100,24 @@ def main_cluster(out):
     v = np.ascontiguousarray(z["sc_sps"]).view(SPOINT_DTYPE).reshape(-1).copy()
     lp = synthetic_lights(len(v), 31)
     cluster_of, clusters, offsets = grid_clusters(v["pos"], 6, 45, 0.06, 37)
+    # consecutive path vertices rarely share a grid cell: move 300 successors into their predecessor's cluster, so that the drivers'
+    # different treatment of a sender's own successor (allGPUClusterScatterRadiance skips it, MX does not) shows in the vectors
+    rng = np.random.default_rng(43)
+    inner = np.nonzero((v["nidx"] > 0) & (cluster_of >= 0))[0]
+    for i in rng.choice(inner, 300, replace=False):
+        cluster_of[i + 1] = cluster_of[i]
+    order = np.argsort(np.where(cluster_of < 0, np.iinfo(np.int32).max, cluster_of), kind="stable")
+    clusters = order[:(cluster_of >= 0).sum()].astype(np.int32)
+    offsets = np.searchsorted(cluster_of[clusters], np.arange(len(offsets))).astype(np.int32)
     v["groupIdx"] = cluster_of
     ref = RefCuda()
     res = {"cl_of": cluster_of, "cl_members": clusters, "cl_offsets": offsets, "cl_lps": lp.view(np.uint8).reshape(len(lp), 44)}
     for it in (1, 3):
         d, b, m, _ = ref.cluster(v, lp, clusters, offsets, it)
         res[f"cl_direct_{it}"] = d; res[f"cl_blur_{it}"] = b; res[f"cl_mc_{it}"] = m
+    for order in ("elements", "scatter"):                     # the tool's modes "n" (ClusterScatter2) and "t" / "l" (ClusterScatter), 3 passes
+        b, m, _ = ref.cluster_scatter(v, clusters, offsets, 3, order=order)
+        res[f"cl_{order}_blur"] = b; res[f"cl_{order}_mc"] = m
     np.savez_compressed(out, **res)
     sizes = np.diff(np.append(offsets, len(clusters)))
     print("wrote", out, len(v), "records,", len(offsets), "clusters, sizes", int(sizes.min()), "..", int(sizes.max()), "loose", int((cluster_of < 0).sum()),

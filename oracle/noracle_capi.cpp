@@ -343,6 +343,11 @@ void noracle_pathgraph_cluster(const void *sps, const void *lps, int n, const in
     pathgraphCluster(static_cast<const SPointRec *>(sps), static_cast<const LPointRec *>(lps), n, clusters, n_listed, offsets, n_clusters, iterations,
                      sequential != 0, direct, blur, mc);
 }
+/// The cluster modes without direct light (order 0: ClusterScatter2, 1: ClusterScatter / loadClusterScatter). blur / mc: iterations x n x 3.
+void noracle_pathgraph_cluster_scatter(int order, const void *sps, int n, const int32_t *clusters, int n_listed, const int32_t *offsets, int n_clusters,
+                                       int iterations, int sequential, float *blur, float *mc) {
+    pathgraphClusterScatter(static_cast<const SPointRec *>(sps), n, clusters, n_listed, offsets, n_clusters, iterations, order != 0, sequential != 0, blur, mc);
+}
 /// The tool's evaluations at one vertex each: pdf[i] = pdf_device(sps[i], wi[i]), bsdf[i] = bsdfeval_device(sps[i], wi[i]).
 void noracle_pathgraph_eval(const void *sps, int n, const float *wi, float *pdf, float *bsdf) {
     const SPointRec *p = static_cast<const SPointRec *>(sps);

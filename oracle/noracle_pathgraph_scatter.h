@@ -473,4 +473,99 @@ inline void pathgraphCluster(const SPointRec *sps, const LPointRec *lps, int n, 
     }
 }
 
+
+/// The tool's cluster modes without direct light. scatterOrder false: SPoints::ClusterScatter2 (mode "n": precomputedMatrixElemtns + ClusterIterations,
+/// src/pbsdf.cu:3359-3418, the elements applied by MX); true: SPoints::ClusterScatter / loadClusterScatter (modes "t" / "l":
+/// computeClusterScatterAllOnGPURecord :3108-3172, allGPUClusterScatterRadiance :1309-1345: (bsdf * temp) * inv, nothing to the sender's own successor,
+/// nothing at all from a sender whose density is unusable). Per pass: blocks, running cluster totals + ratio -> blur[it]; temp = radiance + eLd; lastRun -> mc[it].
+inline void pathgraphClusterScatter(const SPointRec *sps, int n, const int32_t *clusters, int nListed, const int32_t *offsets, int nClusters, int iterations,
+                                    bool scatterOrder, bool sequential, float *blur, float *mc) {
+    using namespace pgs;
+    auto size = [&](int c) { return (c == nClusters - 1 ? nListed : offsets[c + 1]) - offsets[c]; };
+    auto butterfly = [](float *lane) {
+        for (int d = 16; d > 0; d >>= 1) { float nxt[32]; for (int l = 0; l < 32; ++l) nxt[l] = lane[l] + lane[l ^ d]; std::memcpy(lane, nxt, sizeof nxt); }
+        return lane[0];
+    };
+    auto total = [&](int m, const std::function<void(int, float &)> &term) {
+        if (sequential) { float s = 0.0f; for (int t = 0; t < m; ++t) term(t, s); return s; }
+        float lane[32];
+        for (int l = 0; l < 32; ++l) { float s = 0.0f; for (int t = l; t < m; t += 32) term(t, s); lane[l] = s; }
+        return butterfly(lane);
+    };
+    std::vector<float> pm(n, 0.0f), rad(3 * (size_t) n, 0.0f), temp(3 * (size_t) n);
+    std::vector<float> cin(3 * (size_t) std::max(nClusters, 1), 0.0f), cout(3 * (size_t) std::max(nClusters, 1), 0.0f);
+    for (int c = 0; c < nClusters; ++c) {
+        const int32_t *mem = clusters + offsets[c]; const int m = size(c);
+        for (int s = 0; s < m; ++s) {
+            const int i = mem[s];
+            pm[i] = total(m, [&](int t, float &a) { const SPointRec &o = sps[mem[t]]; if (o.nidx == i) return; a += pdfAt(o, sps[i].wi) * o.rrpdf; });
+        }
+    }
+    for (int i = 0; i < n; ++i) if (sps[i].groupIdx == -1) pm[i] = pdfAt(sps[i], sps[i].wi) * sps[i].rrpdf;
+    // what sender i hands to receiver j from temp; returns false if nothing is added at all
+    auto handed = [&](int i, int j, const float *src, float *out) {
+        const bool live = pm[i] > 0.0f && sps[i].rrpdf > 1e-7f;
+        out[0] = out[1] = out[2] = 0.0f;
+        if (scatterOrder) {
+            if (!live || j == i + 1) return false;
+            const float inv = (float) (1.0 / (double) pm[i]); float f[3]; bsdfAt(sps[j], sps[i].wi, f);
+            for (int k = 0; k < 3; ++k) out[k] = (f[k] * src[k]) * inv;
+            return true;
+        }
+        float e[3] = {0.0f, 0.0f, 0.0f};
+        if (live) { const float inv = (float) (1.0 / (double) pm[i]); float f[3]; bsdfAt(sps[j], sps[i].wi, f); for (int k = 0; k < 3; ++k) e[k] = f[k] * inv; }
+        for (int k = 0; k < 3; ++k) out[k] = e[k] * src[k];
+        return true;
+    };
+    for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) temp[3 * (size_t) i + k] = sps[i].eLi[k];
+    for (int it = 0; it < iterations; ++it) {
+        for (int c = 0; c < nClusters; ++c) {
+            const int32_t *mem = clusters + offsets[c]; const int m = size(c);
+            for (int t = 0; t < m; ++t) {
+                const int j = mem[t];
+                float acc[3] = {0.0f, 0.0f, 0.0f};
+                for (int s = 0; s < m; ++s) {
+                    const int i = mem[s];
+                    if (sps[i].nidx <= 0 || i + 1 >= n) continue;
+                    float h[3];
+                    if (handed(i, j, &temp[3 * (size_t) (i + 1)], h)) for (int k = 0; k < 3; ++k) acc[k] += h[k];
+                }
+                for (int k = 0; k < 3; ++k) rad[3 * (size_t) j + k] = acc[k];
+            }
+            for (int k = 0; k < 3; ++k) {
+                const float in = total(m, [&](int t, float &a) { const int i = mem[t]; if (sps[i].nidx > 0 && i + 1 < n) a += temp[3 * (size_t) (i + 1) + k]; });
+                const float out = total(m, [&](int t, float &a) { a += rad[3 * (size_t) mem[t] + k]; });
+                cin[3 * (size_t) c + k] = cin[3 * (size_t) c + k] + in; cout[3 * (size_t) c + k] = cout[3 * (size_t) c + k] + out;
+                const float ratio = cin[3 * (size_t) c + k] < cout[3 * (size_t) c + k] ? cin[3 * (size_t) c + k] / cout[3 * (size_t) c + k] : 1.0f;
+                for (int t = 0; t < m; ++t) rad[3 * (size_t) mem[t] + k] *= ratio;
+            }
+        }
+        for (int i = 0; i < n; ++i) if (sps[i].groupIdx == -1) {
+            float h[3] = {0.0f, 0.0f, 0.0f};
+            if (sps[i].nidx > 0 && i + 1 < n) {
+                // the vertex's own element; in scatter order there is no successor exception here (allGPUClusterScatterRadiance's else branch)
+                const bool live = pm[i] > 0.0f && sps[i].rrpdf > 1e-7f;
+                if (live) {
+                    const float inv = (float) (1.0 / (double) pm[i]); float f[3]; bsdfAt(sps[i], sps[i].wi, f);
+                    for (int k = 0; k < 3; ++k) h[k] = scatterOrder ? (f[k] * temp[3 * (size_t) (i + 1) + k]) * inv : (f[k] * inv) * temp[3 * (size_t) (i + 1) + k];
+                } else if (!scatterOrder) for (int k = 0; k < 3; ++k) h[k] = 0.0f * temp[3 * (size_t) (i + 1) + k];
+            }
+            for (int k = 0; k < 3; ++k) rad[3 * (size_t) i + k] = h[k];
+        }
+        std::memcpy(blur + (size_t) it * 3 * n, rad.data(), sizeof(float) * 3 * (size_t) n);
+        for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) temp[3 * (size_t) i + k] = rad[3 * (size_t) i + k] + sps[i].eLd[k];
+        float *out = mc + (size_t) it * 3 * n;
+        for (int i = 0; i < n; ++i) {
+            out[3 * (size_t) i] = out[3 * (size_t) i + 1] = out[3 * (size_t) i + 2] = 0.0f;
+            const SPointRec &sp = sps[i];
+            const float spdf = pdfAt(sp, sp.wi);
+            if (spdf > 0.0f && sp.nidx > 0 && i + 1 < n) {
+                const float inv = (float) (1.0 / (double) (spdf * sp.rrpdf));
+                float f[3]; bsdfAt(sp, sp.wi, f);
+                for (int k = 0; k < 3; ++k) out[3 * (size_t) i + k] = (temp[3 * (size_t) (i + 1) + k] * f[k]) * inv;
+            }
+        }
+    }
+}
+
 } // namespace noracle

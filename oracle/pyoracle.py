@@ -167,6 +167,7 @@ class Port:
         L.noracle_pathgraph_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p]
         L.noracle_pathgraph_clusters.argtypes = [C.c_int, _f32p, C.c_int, _i32p, _f32p, _f32p, _i32p, C.c_int, C.c_int, _i32p, _i32p, _i32p, C.POINTER(C.c_int)]
         L.noracle_pathgraph_clusters.restype = C.c_int
+        L.noracle_pathgraph_cluster_scatter.argtypes = [C.c_int, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, C.c_int, _f32p, _f32p]
         L.noracle_pathgraph_cluster.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         L.noracle_pathgraph_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, C.c_void_p, _i32p, C.c_int, C.c_int, _f32p, _f32p, C.c_void_p, C.c_void_p]
 
@@ -245,6 +246,17 @@ class Port:
                                          int(sequential), d.reshape(-1), b.reshape(-1), m.reshape(-1))
         return d, b, m
 
+    def pathgraph_cluster_scatter(self, sps, clusters, offsets, iterations, order="elements", sequential=False):
+        """The cluster modes without direct light restated ("elements": ClusterScatter2, "scatter": ClusterScatter): (blur, mc), each (it, n, 3)."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168 and iterations >= 1
+        cl = np.ascontiguousarray(clusters, np.int32).reshape(-1); off = np.ascontiguousarray(offsets, np.int32).reshape(-1)
+        cl_ = cl if len(cl) else np.zeros(1, np.int32); off_ = off if len(off) else np.zeros(1, np.int32)
+        b = np.empty((iterations, n, 3), np.float32); m = np.empty((iterations, n, 3), np.float32)
+        self.L.noracle_pathgraph_cluster_scatter({"elements": 0, "scatter": 1}[order], sps.ctypes.data_as(C.c_void_p), n, cl_, len(cl), off_, len(off), iterations,
+                                                 int(sequential), b.reshape(-1), m.reshape(-1))
+        return b, m
+
     def pathgraph_eval(self, sps, wi):
         """pdf_device / bsdfeval_device restated: (pdf (n,), bsdf (n, 3)) of record i for direction wi[i]."""
         sps = np.ascontiguousarray(sps); n = sps.shape[0]; wi = _f32(wi, (-1, 3))
@@ -317,6 +329,8 @@ class RefCuda:
         self.L.refcuda_mis.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_double)]
         if hasattr(self.L, 'refcuda_build_clusters'):
             self.L.refcuda_build_clusters.argtypes = [_f32p, C.c_int, _i32p, _f32p, _f32p, _i32p, C.c_int, C.c_int] + [_i32p] * 9 + [C.c_int, _i32p, C.POINTER(C.c_double)]
+        if hasattr(self.L, 'refcuda_cluster_scatter'):
+            self.L.refcuda_cluster_scatter.argtypes = [C.c_int, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, C.POINTER(C.c_double)]
         if hasattr(self.L, 'refcuda_cluster'):
             self.L.refcuda_cluster.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, C.c_int, _i32p, C.c_int, C.c_int, _f32p, _f32p, _f32p, C.POINTER(C.c_double)]
         if hasattr(self.L, 'refcuda_direct'):
@@ -387,6 +401,18 @@ class RefCuda:
         a["off1"] = off1; a["off2"] = off2[:counts[0]].copy(); a["off3"] = off3[:counts[1]].copy(); a["n_listed"] = int(counts[2]); a["seconds"] = sec.value
         a["lists3"] = a["lists3"][:counts[2]].copy()
         return a
+
+    def cluster_scatter(self, sps, clusters, offsets, iterations, order="elements"):
+        """SPoints::ClusterScatter2 ("elements") / ClusterScatter ("scatter") on given clusters: (blur, mc (it, n, 3), seconds)."""
+        sps = np.ascontiguousarray(sps); n = sps.shape[0]
+        assert sps.dtype.itemsize == 168
+        cl = np.ascontiguousarray(clusters, np.int32).reshape(-1); off = np.ascontiguousarray(offsets, np.int32).reshape(-1)
+        b = np.empty((iterations, n, 3), np.float32); m = np.empty((iterations, n, 3), np.float32); sec = C.c_double()
+        rc = self.L.refcuda_cluster_scatter({"elements": 0, "scatter": 1}[order], sps.ctypes.data_as(C.c_void_p), n, cl, len(cl), off, len(off), iterations,
+                                            b.reshape(-1), m.reshape(-1), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(f"refcuda_cluster_scatter failed ({rc})")
+        return b, m, sec.value
 
     def cluster(self, sps, lps, clusters, offsets, iterations):
         """SPoints::ClusterScatterWithDirectOptNR's drivers on given clusters: (direct, blur, mc, seconds)."""

@@ -287,3 +287,44 @@ extern "C" int refcuda_build_clusters(const float *pos, int n, const int *dim, c
     cudaFree(cu_sps); cudaFree(cu_clusters); cudaFree(cu_np); cudaFree(cu_small); cudaFree(cu_new1); cudaFree(cu_small2); cudaFree(cu_new2);
     return e == cudaSuccess ? 0 : -3;
 }
+
+/// The tool's cluster modes without direct light on host arrays. order 0: SPoints::ClusterScatter2 (MatrixElementsNumber, precomputedMatrixElemtns,
+/// ClusterIterations); order 1: SPoints::ClusterScatter (computeClusterScatterAllOnGPURecord). blur / mc: iterations x n x 3 floats.
+extern "C" int refcuda_cluster_scatter(int order, const void *sps, int n, const int *clusters, int n_listed, const int *offsets, int n_clusters, int iterations,
+                                       float *blur, float *mc, double *seconds) {
+    SPoint *cu_sps = nullptr; int *cu_clusters = nullptr, *cu_offsets = nullptr;
+    if (cudaMalloc((void **) &cu_sps, sizeof(SPoint) * (size_t) n) != cudaSuccess) return -1;
+    cudaMemcpy(cu_sps, sps, sizeof(SPoint) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_clusters, sizeof(int) * (size_t) n_listed); cudaMemcpy(cu_clusters, clusters, sizeof(int) * (size_t) n_listed, cudaMemcpyHostToDevice);
+    cudaMalloc((void **) &cu_offsets, sizeof(int) * (size_t) n_clusters); cudaMemcpy(cu_offsets, offsets, sizeof(int) * (size_t) n_clusters, cudaMemcpyHostToDevice);
+    cudaMemcpyToSymbol(d_sizeofsp, &n, sizeof(int));
+    cudaMemcpyToSymbol(d_num_clusters, &n_clusters, sizeof(int));
+    cudaMemcpyToSymbol(d_num_clusters_point, &n_listed, sizeof(int));
+    ResultSpace ret;
+    for (int i = 0; i < iterations; ++i) {
+        ret.blur_results.push_back((val3f *) calloc((size_t) n, sizeof(val3f)));
+        ret.mc_results.push_back((val3f *) calloc((size_t) n, sizeof(val3f)));
+    }
+    cudaDeviceSynchronize();
+    auto t0 = std::chrono::steady_clock::now();
+    if (order == 1) computeClusterScatterAllOnGPURecord(cu_sps, n_clusters, cu_clusters, cu_offsets, n, iterations, ret);
+    else {
+        size_t *cu_element_offset = nullptr;
+        cudaMalloc((void **) &cu_element_offset, sizeof(size_t) * (size_t) n);
+        const size_t elements = MatrixElementsNumber(cu_sps, cu_offsets, n_clusters, cu_element_offset, n);
+        val3f *cu_elements = nullptr;
+        if (cudaMalloc((void **) &cu_elements, sizeof(val3f) * elements) != cudaSuccess) return -2;
+        precomputedMatrixElemtns(cu_sps, cu_clusters, cu_offsets, cu_element_offset, n_clusters, n, (int) elements, cu_elements);
+        ClusterIterations(cu_sps, cu_clusters, cu_offsets, n_clusters, cu_element_offset, n, cu_elements, iterations, ret);
+        cudaFree(cu_element_offset); cudaFree(cu_elements);
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (int i = 0; i < iterations; ++i) {
+        std::memcpy(blur + (size_t) i * 3 * n, ret.blur_results[i], sizeof(val3f) * (size_t) n);
+        std::memcpy(mc + (size_t) i * 3 * n, ret.mc_results[i], sizeof(val3f) * (size_t) n);
+        free(ret.blur_results[i]); free(ret.mc_results[i]);
+    }
+    cudaFree(cu_sps); cudaFree(cu_clusters); cudaFree(cu_offsets);
+    return e == cudaSuccess ? 0 : -3;
+}

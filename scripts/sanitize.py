@@ -67,6 +67,7 @@ def main():
             hpc = pathgraph_grid(v2, 12, 12)
             of2, mem2, off2, _ = eng.pathgraph_build_clusters(v2, hpc, pathgraph_stride_seeds(len(v2), len(v2) // 12 + 1))
             eng.pathgraph_cluster(v2, lp, mem2, off2, 1, cluster_of=of2)
+            eng.pathgraph_cluster_scatter(v2, mem2, off2, 2, order="elements", cluster_of=of2); eng.pathgraph_cluster_scatter(v2, order, offs, 2, order="scatter", cluster_of=of)
             eng.pathgraph_render(12, 2, mode="cluster", sample_first=0, sample_last=2)
             print("  pathgraph", len(v), "vertices", flush=True)
         if name == "bunny_normals":
