@@ -513,6 +513,42 @@ def timed_render(eng, scene, spp, warm_spp, gpu):
             "build_ms_device": accel["build_ms"], "upload_and_build_ms_wall": load_ms, "upload_and_build_ms_wall_first_call": first_ms, "sah_cost": accel["sah_cost"], "clocks": clocks}
 
 
+def measure_pathgraph(eng, gpu, spp=2, k=16, iterations=3):
+    """SURVEY 8f row 4 — the fork's path-graph tool (src/pbsdf.cu, src/cluster.cpp) on the veach scene's own path vertices, every stage
+    through the C ABI under the clock sampler. Device times are the calls' own CUDA events (records and rows resident); *_wall_ms are whole
+    calls from / to host buffers. The reference's drivers on the same GPU are builder-run only (scripts/bench_pathgraph.py ->
+    profiles/pathgraph_r02g.json): bench.py does not execute oracle/_ref outside its cpu_baseline / --impl reference legs."""
+    from nori_b200.gpu import pathgraph_grid, pathgraph_stride_seeds
+    scene = FlatScene.load(os.path.join(ROOT, "tests", "golden", "scenes", "veach_mis.npz"))
+    eng.load_scene(scene)
+    med = lambda xs: float(np.median(xs[1:])) if len(xs) > 1 else float(xs[0])
+    v, lp = eng.path_vertices(sample_first=0, sample_last=spp, lights=True)
+    hp = pathgraph_grid(v, k, k)
+    seeds = pathgraph_stride_seeds(len(v), len(v) // k + 1)
+    cs = ClockSampler(gpu); cs.start()
+    t = {"knn": [], "scatter": [], "mis": [], "direct": [], "build": [], "cluster": [], "render_mis": [], "render_cluster": []}
+    for _ in range(3):
+        nb, knn, dknn, ms = eng.pathgraph_knn(v, hp); t["knn"].append(ms)
+        t["scatter"].append(eng.pathgraph_scatter(v, nb, knn, iterations)[3])
+        t["mis"].append(eng.pathgraph_mis(v, nb, knn, iterations)[2])
+        t["direct"].append(eng.pathgraph_direct(v, lp, nb, dknn, knn=knn, iterations=iterations)[3])
+        of, members, offsets, ms = eng.pathgraph_build_clusters(v, hp, seeds); t["build"].append(ms)
+        t["cluster"].append(eng.pathgraph_cluster(v, lp, members, offsets, iterations, cluster_of=of)[3])
+        for mode in ("mis", "cluster"):
+            t0 = time.perf_counter(); img, st = eng.pathgraph_render(k, iterations, mode=mode, sample_first=0, sample_last=spp)
+            t["render_" + mode].append((time.perf_counter() - t0) * 1e3)
+    clocks = cs.summary()
+    sizes = np.diff(np.append(offsets, len(members)))
+    return {"workload": f"F4: path-graph tool on veach path_mis {scene.width}x{scene.height}, {spp} spp: {len(v)} path vertices, k = {k}, {iterations} passes",
+            "vertices": int(len(v)), "edges": int(knn.sum()), "clusters": int(len(offsets)), "cluster_pairs": int((sizes.astype(np.int64) ** 2).sum()),
+            "device_ms": {"hash_grid_knn": med(t["knn"]), "scatter": med(t["scatter"]), "mis_gather": med(t["mis"]), "direct_filter_and_scatter": med(t["direct"]),
+                          "cluster_build": med(t["build"]), "cluster_direct_and_scatter": med(t["cluster"])},
+            "Mpoints_per_s_knn": len(v) / med(t["knn"]) / 1e3,
+            "tool_end_to_end_wall_ms": {"knn_mode": med(t["render_mis"]), "default_cluster_mode": med(t["render_cluster"])},
+            "tool_end_to_end_device_ms_cluster_mode": [st["ms_vertices"], st["ms_knn"], st["ms_stage"]],
+            "image_mean_full": float(img["full"].mean()), "clocks": clocks}
+
+
 def measure_configs(eng, torch, gpu, hbm):
     """The other single-GPU BASELINE configs through the same C ABI (outside the timed region of the headline)."""
     from nori_b200 import synth
@@ -531,6 +567,7 @@ def measure_configs(eng, torch, gpu, hbm):
     r["h2d_bytes"] = int(sum(m.V.nbytes + m.F.nbytes + (m.N.nbytes if m.N is not None else 0) for m in c4.meshes))
     r["traversal_kernel_only"] = trace_only(eng, torch, c4, gpu, hbm)
     out["C4"] = r
+    out["F4"] = measure_pathgraph(eng, gpu)
     return out
 
 
