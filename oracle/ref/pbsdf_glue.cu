@@ -9,6 +9,22 @@
 
 extern "C" int refcuda_sizeof_spoint() { return (int) sizeof(SPoint); }
 
+// The boundary records of include/nori_gpu.h ARE the reference's structs: checked here, where both headers are in sight, when this file is compiled.
+#include "../../include/nori_gpu.h"
+#include <cstddef>
+#define SAME_FIELD(A, B, f) static_assert(offsetof(A, f) == offsetof(B, f) && sizeof(((A *) 0)->f) == sizeof(((B *) 0)->f), "layout of " #A "::" #f)
+static_assert(sizeof(SPoint) == sizeof(NoriGpuSPoint) && sizeof(LPoint) == sizeof(NoriGpuLPoint) && sizeof(hparam) == sizeof(NoriGpuHashParams), "record sizes");
+SAME_FIELD(SPoint, NoriGpuSPoint, pos); SAME_FIELD(SPoint, NoriGpuSPoint, wi); SAME_FIELD(SPoint, NoriGpuSPoint, wi_d); SAME_FIELD(SPoint, NoriGpuSPoint, wo);
+SAME_FIELD(SPoint, NoriGpuSPoint, shN); SAME_FIELD(SPoint, NoriGpuSPoint, geoN); SAME_FIELD(SPoint, NoriGpuSPoint, diffuse); SAME_FIELD(SPoint, NoriGpuSPoint, specular);
+SAME_FIELD(SPoint, NoriGpuSPoint, eLi); SAME_FIELD(SPoint, NoriGpuSPoint, eLd); SAME_FIELD(SPoint, NoriGpuSPoint, eta); SAME_FIELD(SPoint, NoriGpuSPoint, k);
+SAME_FIELD(SPoint, NoriGpuSPoint, roughness); SAME_FIELD(SPoint, NoriGpuSPoint, pdf); SAME_FIELD(SPoint, NoriGpuSPoint, rrpdf); SAME_FIELD(SPoint, NoriGpuSPoint, nidx);
+SAME_FIELD(SPoint, NoriGpuSPoint, groupIdx); SAME_FIELD(SPoint, NoriGpuSPoint, bsdf_type);
+SAME_FIELD(LPoint, NoriGpuLPoint, L_directsample); SAME_FIELD(LPoint, NoriGpuLPoint, L_bsdfsample); SAME_FIELD(LPoint, NoriGpuLPoint, L_em);
+SAME_FIELD(LPoint, NoriGpuLPoint, lightpdf); SAME_FIELD(LPoint, NoriGpuLPoint, bsdfpdf);
+SAME_FIELD(hparam, NoriGpuHashParams, dim); SAME_FIELD(hparam, NoriGpuHashParams, cellsize); SAME_FIELD(hparam, NoriGpuHashParams, minb);
+SAME_FIELD(hparam, NoriGpuHashParams, k); SAME_FIELD(hparam, NoriGpuHashParams, dk);
+#undef SAME_FIELD
+
 /// SPoints::BuildKNN (include/nori/shadingPoint.h:776-806) on n positions: device SPoint array, pitched neighbour rows,
 /// buildHashGridAndFindKNN (src/pbsdf.cu:3173-3235). neighbors: n x max(k, dk) ints (rows beyond knn/dknn are whatever the
 /// reference left in its uninitialised allocation; this glue clears the array first so that they read -1).
