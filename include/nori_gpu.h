@@ -360,7 +360,8 @@ int nori_gpu_pathgraph_stride_seeds(int n, int n_seeds, int32_t *seeds);
  * vertices are clustered (src/cluster.cpp:217): every vertex exchanges light with ALL members of its cluster instead of its k nearest
  * neighbours. clusters[offsets[c] .. offsets[c + 1]) (the last one up to n_listed) = the members of cluster c, a partition of the vertices
  * whose SPoint::groupIdx names a cluster (groupIdx = c for a member of c, -1 for a vertex outside every cluster: SaveClusters,
- * src/pbsdf.cu:987-1006) — the arrays SPoints::loadClusters uploads (shadingPoint.h:626-635). Anything else is refused (NORI_GPU_EINVAL).
+ * src/pbsdf.cu:987-1006) — the arrays SPoints::loadClusters uploads (shadingPoint.h:626-635). Anything else is refused (NORI_GPU_EINVAL), and so is
+ * a cluster of more than 8192 members (the work is quadratic in a cluster's size; the tool's builder cuts clusters down to about K members).
  *   direct = ClusterDirect (src/pbsdf.cu:2400-2446): direct light filtered inside the clusters, each cluster scaled back to the light its
  *            members sampled (clampDirectCluster / computeRatio / updateComputeCluster) + emission       [m_result.blur_direct]
  *   blur   = the radiance after `iterations` passes of ClusterIterations3 (:3475-3532): per pass the cluster's dense block

@@ -1331,6 +1331,7 @@ extern "C" int nori_gpu_pathgraph_cluster(nori_gpu_ctx *ctx, const NoriGpuSPoint
     int chk[2] = {0, 0};
     CK(cudaMemcpyAsync(chk, flag.p, sizeof chk, cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
     REQUIRE(!(chk[0] & 1), "pathgraph_cluster: offsets must start at 0 and ascend inside [0, n_listed]");
+    REQUIRE(!(chk[0] & 32), "pathgraph_cluster: a cluster of more than 8192 members");
     REQUIRE(!(chk[0] & 2), "pathgraph_cluster: cluster member outside [0, n)");
     REQUIRE(!(chk[0] & 16), "pathgraph_cluster: groupIdx outside [-1, n_clusters)");
     REQUIRE(!(chk[0] & 4), "pathgraph_cluster: a member's groupIdx is not the cluster that lists it");
@@ -1371,6 +1372,7 @@ extern "C" int nori_gpu_pathgraph_cluster_scatter(nori_gpu_ctx *ctx, int order, 
     int chk[2] = {0, 0};
     CK(cudaMemcpyAsync(chk, flag.p, sizeof chk, cudaMemcpyDeviceToHost, st)); CK(cudaStreamSynchronize(st));
     REQUIRE(!(chk[0] & 1), "pathgraph_cluster_scatter: offsets must start at 0 and ascend inside [0, n_listed]");
+    REQUIRE(!(chk[0] & 32), "pathgraph_cluster_scatter: a cluster of more than 8192 members");
     REQUIRE(!(chk[0] & 2), "pathgraph_cluster_scatter: cluster member outside [0, n)");
     REQUIRE(!(chk[0] & 16), "pathgraph_cluster_scatter: groupIdx outside [-1, n_clusters)");
     REQUIRE(!(chk[0] & 4), "pathgraph_cluster_scatter: a member's groupIdx is not the cluster that lists it");
@@ -1487,8 +1489,9 @@ extern "C" int nori_gpu_pathgraph_render(nori_gpu_ctx *ctx, const NoriGpuRenderD
         CK(seeds.alloc(nSeeds)); CK(of.alloc(n)); CK(lists.alloc(n)); CK(off.alloc((size_t) cap + 1));
         CK(scratch.alloc(pgBuildClustersScratchBytes(n, nSeeds, cap)));
         launchPathgraphStrideSeeds(seeds.p, nSeeds, n, st);
-        int nc = 0, nl = 0;
-        if (!launchPathgraphBuildClusters(recs.p, sizeof(NoriGpuSPoint), n, P, seeds.p, nSeeds, k, scratch.p, of.p, lists.p, off.p, cap, &nc, &nl, st, ctx->err)) return NORI_GPU_EINVAL;
+        int nc = 0, nl = 0, largest = 0;
+        if (!launchPathgraphBuildClusters(recs.p, sizeof(NoriGpuSPoint), n, P, seeds.p, nSeeds, k, scratch.p, of.p, lists.p, off.p, cap, &nc, &nl, st, ctx->err, &largest)) return NORI_GPU_EINVAL;
+        REQUIRE(largest <= kPgMaxClusterSize, "pathgraph_render: the builder left a cluster of more than 8192 members (coincident vertices?); use another k");
         CK(cudaEventRecord(ev[2], st));
         CK(stage.alloc(pgClusterScratchBytes(n, nc))); CK(db.alloc((size_t) 9 * n)); CK(img.alloc((size_t) 6 * nPixels * 3));
         if (!launchPathgraphCluster(recs.p, lrecs.p, n, lists.p, nl, off.p, nc, iterations, stage.p, db.p, db.p + (size_t) 3 * n, db.p + (size_t) 6 * n, st, ctx->err, of.p))

@@ -374,6 +374,15 @@ __global__ void k_pgSubdivide(const unsigned char *__restrict__ pos, size_t stri
     groupIdx[i] = g;
 }
 
+/// Largest cluster of a listing (offsets[nClusters] = members listed).
+__global__ void k_pgMaxCluster(const int *__restrict__ offsets, int nClusters, int *__restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    int m = c < nClusters ? offsets[c + 1] - offsets[c] : 0;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, d));
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
 inline size_t pgAl(size_t b) { return (b + 255) / 256 * 256; }
 size_t pgSortTempBytes(int n) {
     size_t a = 0, b = 0;
@@ -392,7 +401,8 @@ size_t pgBuildClustersScratchBytes(int n, int nSeeds, int cap) {
 /// BuildClusters on device-resident positions. d_groupIdx: n ints (cluster of every vertex or -1), d_lists: n ints, d_offsets: `cap` + 1 ints
 /// (offsets[nClusters] = members listed). Synchronises the stream three times to read a cluster count (the reference: after every kernel).
 bool launchPathgraphBuildClusters(const void *d_pos, size_t stride, int n, const PgParams &P, const int *d_seeds, int nSeeds, int K, void *scratch,
-                                  int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClustersOut, int *nListedOut, cudaStream_t st, std::string &err) {
+                                  int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClustersOut, int *nListedOut, cudaStream_t st, std::string &err,
+                                  int *maxClusterOut) {
     if (n <= 0 || nSeeds <= 0 || nSeeds > n || K < 2) { err = "pathgraph_build_clusters: need 0 < n_seeds <= n and K >= 2"; return false; }
     const int m = std::max(n, nSeeds), c = std::max(cap, nSeeds) + 2;
     unsigned char *s = static_cast<unsigned char *>(scratch);
@@ -432,14 +442,23 @@ bool launchPathgraphBuildClusters(const void *d_pos, size_t stride, int n, const
         tmpBytes = pgSortTempBytes(std::max(m, c));
         e = cub::DeviceScan::ExclusiveSum(tmp, tmpBytes, small, first, nClusters + 1, st);
         if (e != cudaSuccess) return fail("scan", e);
-        int next = 0;
+        int next = 0, biggest = 0;
+        cudaMemsetAsync(small, 0, sizeof(int), st);              // (k_pgSmall's values are consumed: the scan above read them)
+        k_pgMaxCluster<<<grid(nClusters), 256, 0, st>>>(offs, nClusters, small);
+        cudaMemcpyAsync(&biggest, small, sizeof(int), cudaMemcpyDeviceToHost, st);
         if ((e = cudaMemcpyAsync(&next, first + nClusters, sizeof(int), cudaMemcpyDeviceToHost, st)) != cudaSuccess || (e = cudaStreamSynchronize(st)) != cudaSuccess) return fail("count", e);
+        // a split compares every member with the cluster's size / K + 1 first members: refuse what would run for seconds (coincident vertices, seeds far from the data)
+        if ((double) biggest * ((double) biggest / K + 1.0) > 1.4e11) { err = "pathgraph_build_clusters: a cluster of " + std::to_string(biggest) + " members is too large to split (are the seeds spread over the vertices?)"; return false; }
         if (next > cap) { err = "pathgraph_build_clusters: " + std::to_string(next) + " clusters exceed the capacity " + std::to_string(cap); return false; }
         k_pgSubdivide<<<grid(n), 256, 0, st>>>(pos, stride, n, d_lists, offs, first, d_groupIdx);
         nClusters = next;
     }
-    int listed = 0;
+    int listed = 0, largest = 0;
+    cudaMemsetAsync(small, 0, sizeof(int), st);                  // `small` is free again: the largest cluster goes there
+    k_pgMaxCluster<<<grid(nClusters), 256, 0, st>>>(d_offsets, nClusters, small);
+    cudaMemcpyAsync(&largest, small, sizeof(int), cudaMemcpyDeviceToHost, st);
     if ((e = cudaMemcpyAsync(&listed, d_offsets + nClusters, sizeof(int), cudaMemcpyDeviceToHost, st)) != cudaSuccess || (e = cudaStreamSynchronize(st)) != cudaSuccess) return fail("count", e);
+    if (maxClusterOut) *maxClusterOut = largest;
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("launch", e);
     *nClustersOut = nClusters; *nListedOut = listed;
     return true;

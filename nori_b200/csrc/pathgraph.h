@@ -7,6 +7,7 @@
 
 namespace ng {
 
+constexpr int kPgMaxClusterSize = 8192;   // clustered drivers: one warp takes a cluster's size^2 pairs (67 M at the limit); the tool's builder cuts clusters down to ~K members
 constexpr int kPgMaxK = 200;          // max(k, dk): the per-thread heaps of a 128-thread CTA must fit shared memory (8 * K * 128 bytes)
 
 /// KPara (src/pbsdf.cu:16-24) = hparam (include/nori/shadingPoint.h:18-24) + derived sizes.
@@ -23,7 +24,8 @@ bool launchPathgraphKnn(const void *d_pos, size_t strideBytes, int n, const PgPa
 /// SPoints::BuildClusters (include/nori/shadingPoint.h:637-760) with given seeds; deterministic (members in index order).
 size_t pgBuildClustersScratchBytes(int n, int nSeeds, int cap);
 bool launchPathgraphBuildClusters(const void *d_pos, size_t strideBytes, int n, const PgParams &P, const int *d_seeds, int nSeeds, int K, void *d_scratch,
-                                  int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClusters, int *nListed, cudaStream_t st, std::string &err);
+                                  int *d_groupIdx, int *d_lists, int *d_offsets, int cap, int *nClusters, int *nListed, cudaStream_t st, std::string &err,
+                                  int *maxCluster = nullptr);
 /// seeds[s] = (s * step) mod n, step = pathgraphSeedStep(n): a fixed scattered choice of distinct vertices (the reference: the head of a shuffled list).
 long long pathgraphSeedStep(int n);
 void launchPathgraphStrideSeeds(int *d_seeds, int nSeeds, int n, cudaStream_t st);

@@ -498,7 +498,8 @@ __global__ void k_pgPackLights(const NoriGpuSPoint *__restrict__ sps, const Nori
 }
 
 /// The lists are trusted by the kernels below. flag bits: 1 = offsets not ascending inside [0, nListed], 2 = a member outside [0, n),
-/// 4 = a member whose groupIdx is not the cluster that lists it, 8 = a vertex listed twice, 16 = a groupIdx outside [-1, nClusters).
+/// 4 = a member whose groupIdx is not the cluster that lists it, 8 = a vertex listed twice, 16 = a groupIdx outside [-1, nClusters),
+/// 32 = a cluster of more than kPgMaxClusterSize members.
 /// listed: cleared array of n ints (members are counted in it); the host compares the number of members with the vertices that name a cluster.
 __global__ void k_pgClusterValidate(const NoriGpuSPoint *__restrict__ sps, int n, const int *__restrict__ clusters, int nListed, const int *__restrict__ offsets,
                                     int nClusters, int *__restrict__ listed, int *__restrict__ flag, int *__restrict__ nNamed) {
@@ -506,6 +507,7 @@ __global__ void k_pgClusterValidate(const NoriGpuSPoint *__restrict__ sps, int n
     if (tid < nClusters) {
         const int lo = offsets[tid], hi = tid == nClusters - 1 ? nListed : offsets[tid + 1];
         if (lo < 0 || hi < lo || hi > nListed || (tid == 0 && lo != 0)) { atomicOr(flag, 1); return; }
+        if (hi - lo > kPgMaxClusterSize) { atomicOr(flag, 32); return; }          // a warp works through a cluster's size^2 pairs
         for (int t = lo; t < hi; ++t) {
             const int j = clusters[t];
             if (j < 0 || j >= n) { atomicOr(flag, 2); continue; }

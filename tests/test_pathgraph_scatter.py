@@ -521,6 +521,11 @@ def test_gpu_cluster_scatter_vs_oracle_and_reference(engine, port):
         engine.pathgraph_cluster(t, tl, perm, offs[::-1].copy(), 1, cluster_of=of)
     with pytest.raises(NoriGpuError, match="iterations"):
         engine.pathgraph_cluster(t, tl, perm, offs, 0, cluster_of=of)
+    big = records(np.load(REF_NPZ)["eval_sps"])                           # one cluster of 6 000 is fine, one of more than 8 192 is refused
+    big = np.concatenate([big, big])[:9000].copy(); big["nidx"] = 0
+    bl = np.zeros(len(big), LPOINT_DTYPE)
+    with pytest.raises(NoriGpuError, match="more than 8192 members"):
+        engine.pathgraph_cluster(big, bl, np.arange(9000, dtype=np.int32), [0], 1, cluster_of=np.zeros(9000, np.int32))
 
 
 @pytest.mark.gpu
