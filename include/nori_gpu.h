@@ -297,7 +297,8 @@ int nori_gpu_path_vertices_lights(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *de
  * apart whose first 12 bytes are the position (NoriGpuSPoint array: stride 168; packed float3: stride 12), HOST memory.
  * neighbors: n x max(k, dk) ints (row i = point i; nearest first by (distance, index), the point itself swapped to the front as
  * the reference does; unused entries -1). knn / dknn: neighbours available for the k / dk consumers (pbsdf.cu:1141-1164).
- * ms (optional): device time of grid build + search. max(k, dk) <= 200. */
+ * ms (optional): device time of grid build + search. max(k, dk) <= 200. A grid whose squared cell counts sum to more than 5e11 (nearly all
+ * points in a few cells: every query would scan them all) is refused with NORI_GPU_EINVAL before the search starts. */
 int nori_gpu_pathgraph_knn(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp,
                            int32_t *neighbors, int32_t *knn, int32_t *dknn, float *ms);
 /* SPoints::BuildKNN's grid (shadingPoint.h:794-801) for a cell count per axis: bounding box of the points, cellsize = extent / dim. */

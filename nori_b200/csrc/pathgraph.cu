@@ -242,6 +242,18 @@ size_t pgScratchBytes(int n, int nCells) {
     return al(((size_t) nCells + 1) * 4) + al((size_t) nCells * 4) + al(tiles * 4) + al((size_t) n * 16);
 }
 
+namespace {
+/// Sum over the cells of (points in the cell)^2: an eighth of the candidate distances the search will compute, roughly.
+__global__ void k_pgSearchCost(const int *__restrict__ cellStart, int nCells, unsigned long long *__restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long v = 0;
+    if (c < nCells) { const unsigned long long m = (unsigned long long) (cellStart[c + 1] - cellStart[c]); v = m * m; }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
+}
+}
+
 /// Grid build + kNN on device-resident positions. `scratch`: pgScratchBytes(n, nCells) bytes of device memory.
 /// Returns false (with a message) for parameters the kernels do not cover.
 bool launchPathgraphKnn(const void *d_pos, size_t stride, int n, const PgParams &P, void *scratch, int *d_neighbors, int pitchInts, int *d_knn, int *d_dknn,
@@ -263,6 +275,15 @@ bool launchPathgraphKnn(const void *d_pos, size_t stride, int n, const PgParams 
     k_pgScanSums<<<1, kScanThreads, 0, st>>>(tileSums, tiles);
     k_pgScanAdd<<<tiles, kScanThreads, 0, st>>>(cellStart, nCells, tileSums, n);
     k_pgScatter<<<g, 256, 0, st>>>(static_cast<const unsigned char *>(d_pos), stride, n, P, cellStart, cellFill, entries);
+    {   // every query scans the cells around it: with nearly all points in a few cells that is quadratic. Refuse what would run for many seconds
+        // (the grid PathGraph::computeDimensions derives from the points' bounding box keeps this sum near n x a few hundred).
+        unsigned long long *cost = reinterpret_cast<unsigned long long *>(tileSums), h = 0;          // tileSums is free again
+        static_assert(sizeof(unsigned long long) <= 256, "fits the smallest tileSums allocation");
+        cudaMemsetAsync(cost, 0, sizeof(unsigned long long), st);
+        k_pgSearchCost<<<(unsigned) ((nCells + 255) / 256), 256, 0, st>>>(cellStart, nCells, cost);
+        if (cudaMemcpyAsync(&h, cost, sizeof h, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { err = "pathgraph_knn: cost read failed"; return false; }
+        if ((double) h > 5e11) { err = "pathgraph_knn: the grid puts too many points into too few cells (sum of squared cell counts " + std::to_string(h) + "): choose a finer grid"; return false; }
+    }
     constexpr int NT = 128;
     const size_t smem = (size_t) P.maxK * NT * 8;
     cudaFuncSetAttribute(k_pgKnn<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPgMaxK * NT * 8);      // per device; cheap

@@ -170,6 +170,12 @@ def test_knn_rejects_what_it_does_not_cover(engine):
     hp = pathgraph_grid(pts, 4, 4, (2, 2, 2)); hp.cellsize[1] = 0.0
     with pytest.raises(RuntimeError, match="cell sizes must be positive"):
         engine.pathgraph_knn(pts, hp)
+    # a grid that puts 800 000 points into one cell would make every query scan all of them (6.4e11 distances): refused before it starts
+    many = np.random.default_rng(2).random((800_000, 3)).astype(np.float32)
+    with pytest.raises(RuntimeError, match="too many points into too few cells"):
+        engine.pathgraph_knn(many, pathgraph_grid(many, 4, 4, (1, 1, 1)))
+    nb, knn, dknn, _ = engine.pathgraph_knn(many, pathgraph_grid(many, 4, 4))              # the tool's own grid for them is fine
+    assert (knn == 4).mean() > 0.9
 
 
 @pytest.mark.gpu
