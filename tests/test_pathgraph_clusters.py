@@ -127,7 +127,12 @@ def test_gpu_builder_vs_compiled_reference_live(engine, port):
     hp = HashParams(); hp.dim[:] = [int(d) for d in dim]; hp.cellsize[:] = [float(c) for c in cs]; hp.minb[:] = [float(m) for m in lo]; hp.k = K; hp.dk = K
     g, lists, off, ms = engine.pathgraph_build_clusters(pts, hp, seeds)
     check_lists(g, lists, off)
-    np.testing.assert_array_equal(port.pathgraph_cluster_assign(pts, dim, cs, lo, seeds), r["g1"])
+    mine = port.pathgraph_cluster_assign(pts, dim, cs, lo, seeds)
+    differ = np.nonzero(mine != r["g1"])[0]                              # only where two seeds are EXACTLY as far: the reference takes whichever its
+    assert len(differ) <= 5                                              # atomics listed last in the bucket (`<=`), the oracle the higher seed index
+    for i in differ:
+        da, db = (np.linalg.norm(pts[i].astype(np.float64) - pts[seeds[q]]) for q in (mine[i], r["g1"][i]))
+        assert abs(da - db) <= 1e-6 * max(da, 1e-12), (i, da, db)
     np.testing.assert_array_equal(g >= 0, r["g1"] >= 0)
     lists1 = r["lists1"][:(r["g1"] >= 0).sum()]
     g2, n2 = port.pathgraph_cluster_subdivide(pts, r["g1"], lists1, r["off1"], K)
