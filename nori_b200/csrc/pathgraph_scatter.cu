@@ -181,20 +181,24 @@ __global__ void __launch_bounds__(kPgWarps * 32) k_pgPdfSum(const float4 *__rest
         // whole warp's would (the other lanes hold zeros), so the grouping does not change a bit of the result.
         const int G = k <= 8 ? 8 : (k <= 16 ? 16 : 32), group = lane / G, l = lane % G, groups = 32 / G;
         if (l < k) { const int jb = row[l]; NG_CHECK(jb >= 0 && jb < n); pgLoadA(A, jb, mine); pgLoadB(B, jb, mine); }
+        // What the loop needs of neighbour a — does its path continue, and in which direction — is fetched ONCE, by lane a, all k chains of
+        // dependent loads (row -> record -> direction) in flight together, and handed to the group that works on a by shuffle.
+        float4 wMine = make_float4(0.f, 0.f, 0.f, 0.f);           // wi of neighbour `lane` | 1 if it continues
+        if (lane < k) {
+            const int ja = row[lane];
+            NG_CHECK(ja >= 0 && ja < n);
+            const float4 a1 = __ldg(A + 4 * (size_t) ja + 1), a3 = __ldg(A + 4 * (size_t) ja + 3);
+            if (__float_as_int(a3.w) > 0 && a1.w > 1e-7f) { wMine = __ldg(wiAll + ja); wMine.w = 1.0f; }
+        }
         for (int a0 = 0; a0 < k; a0 += groups) {
-            const int a = a0 + group;
+            const int a = a0 + group, src = min(a, 31);
             float sum = 0.0f;
-            bool want = false;
-            if (a < k) {
-                const int ja = row[a];
-                NG_CHECK(ja >= 0 && ja < n);
-                const float4 a1 = __ldg(A + 4 * (size_t) ja + 1), a3 = __ldg(A + 4 * (size_t) ja + 3);
-                want = __float_as_int(a3.w) > 0 && a1.w > 1e-7f;
-                if (want && l < k) {
-                    const float4 w4 = __ldg(wiAll + ja);
-                    const float wi[3] = {w4.x, w4.y, w4.z};
-                    sum += pgPdf(mine, wi) * mine.rrpdf;
-                }
+            const float wx = __shfl_sync(0xffffffffu, wMine.x, src), wy = __shfl_sync(0xffffffffu, wMine.y, src), wz = __shfl_sync(0xffffffffu, wMine.z, src);
+            const float goes = __shfl_sync(0xffffffffu, wMine.w, src);          // (every lane takes part in the shuffles: no short circuit)
+            const bool want = a < k && goes != 0.0f;
+            if (want && l < k) {
+                const float wi[3] = {wx, wy, wz};
+                sum += pgPdf(mine, wi) * mine.rrpdf;
             }
 #pragma unroll
             for (int d = 16; d > 0; d >>= 1) { const float t = __shfl_xor_sync(0xffffffffu, sum, d); if (d < G) sum += t; }
