@@ -167,6 +167,10 @@ int nori_gpu_set_pool_size(nori_gpu_ctx *ctx, uint32_t n_paths);
  * it on or off. No counterpart in the reference (its render loop, src/main.cpp:57-100, traces one ray at a time per thread).
  * Pools beyond 16 Mi slots render without it. */
 int nori_gpu_set_ray_binning(nori_gpu_ctx *ctx, int on);
+/* Scenes without a microfacet BSDF (src/microfacet.cpp) — the Cornell box among them — are shaded by an instance of the path integrators'
+ * kernel that carries no Beckmann code (default on; the census is taken from the uploaded meshes). The branches left out would never have
+ * run: the radiance of every camera sample is identical bit for bit with it on or off. */
+int nori_gpu_set_plain_bsdf_kernels(nori_gpu_ctx *ctx, int on);
 /* Mesh::rayIntersect variant (src/mesh.cpp:51-88) used by the raw operators below (trace, trace_device,
  * trace_count, intersect): NORI_ISECT_*. nori_gpu_render takes it from NoriGpuRenderDesc::intersect_mode. */
 int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode);

@@ -51,6 +51,7 @@ struct nori_gpu_ctx {
     float4 *recA = nullptr; float *recB = nullptr; size_t recCap = 0;
     uint32_t *tileDone = nullptr, *tileGen = nullptr, *tileArrive = nullptr, *readyTiles = nullptr; size_t tileDoneCap = 0;
     bool profiling = false;
+    bool plainKernels = true;                   // scenes without microfacet surfaces render with the shade kernel that carries no Beckmann code (nori_gpu_set_plain_bsdf_kernels)
     bool rayBins = true;                        // bounce rays binned by origin cell + direction signs between shade and the next closest-hit pass (nori_gpu_set_ray_binning)
     int accelLayout = NORI_ACCEL_FLOAT;         // node layout the persistent traversal kernels read
     int isectMode = NORI_ISECT_REFERENCE_MT;   // used by the raw operators; nori_gpu_render takes it from its descriptor
@@ -86,6 +87,8 @@ DeviceScene deviceScene(const nori_gpu_ctx *c) {
     s.nTris = c->nTris; s.nVerts = c->nVerts;
     s.nodes = c->bvh.nodes; s.leafTris = c->bvh.leafTris; s.nNodes = c->bvh.nNodes;
     s.cam = c->cam; s.filter = c->filter; s.isectMode = c->isectMode;
+    s.plainBsdfs = c->plainKernels && !c->meshes.empty();
+    for (const MeshInfo &m : c->meshes) if (m.bsdfType == NORI_BSDF_MICROFACET) s.plainBsdfs = 0;
     s.qnodes = c->accelLayout == NORI_ACCEL_QUANTISED ? c->bvh.qnodes : nullptr;
     s.wnodes = c->accelLayout == NORI_ACCEL_WIDE4 ? c->bvh.wnodes : nullptr;
     for (int k = 0; k < 3; ++k) { s.qBase[k] = c->bvh.qBase[k]; s.qExt[k] = c->bvh.qExt[k]; }
@@ -216,6 +219,7 @@ int nori_gpu_create(nori_gpu_ctx **out, int device_id) {
     if (const char *s = getenv("NORI_GPU_MAX_LEAF")) ctx->bvhParams.maxLeaf = atoi(s);
     if (const char *s = getenv("NORI_GPU_ROTATIONS")) ctx->bvhParams.rotationPasses = atoi(s);
     if (const char *s = getenv("NORI_GPU_BINS")) ctx->rayBins = atoi(s) != 0;
+    if (const char *s = getenv("NORI_GPU_PLAIN")) ctx->plainKernels = atoi(s) != 0;
     if (const char *s = getenv("NORI_GPU_SAH_CI")) ctx->bvhParams.costInner = (float) atof(s);
     if (const char *s = getenv("NORI_GPU_SAH_CT")) ctx->bvhParams.costTri = (float) atof(s);
     if (const char *e = getenv("NORI_GPU_ACCEL_LAYOUT")) ctx->accelLayout = atoi(e) == 1 ? NORI_ACCEL_QUANTISED : (atoi(e) == 2 ? NORI_ACCEL_WIDE4 : NORI_ACCEL_FLOAT);
@@ -658,6 +662,11 @@ int nori_gpu_li(nori_gpu_ctx *ctx, const NoriGpuRenderDesc *d, int n, const floa
 int nori_gpu_set_ray_binning(nori_gpu_ctx *ctx, int on) {
     if (!ctx) return NORI_GPU_EINVAL;
     ctx->rayBins = on != 0;          // takes effect at the next render (ensurePool reallocates the two index arrays)
+    return NORI_GPU_OK;
+}
+int nori_gpu_set_plain_bsdf_kernels(nori_gpu_ctx *ctx, int on) {
+    if (!ctx) return NORI_GPU_EINVAL;
+    ctx->plainKernels = on != 0;
     return NORI_GPU_OK;
 }
 int nori_gpu_set_intersect_mode(nori_gpu_ctx *ctx, int mode) {

@@ -226,7 +226,9 @@ struct ShadowOut { bool cast; V3 o, d; float maxt; V3 contrib; };
 /// What the path-graph tool's LPoint records want of a vertex (k_pathVertices only; nullptr everywhere else: the code folds away).
 struct LightOut { V3 Lem, Ldirect; float lightPdf; };
 
-template <int INTEGRATOR>
+/// PLAIN: the caller knows that no mesh of the scene has a microfacet BSDF (DeviceScene::plainBsdfs); the Beckmann branches of
+/// Bsdf::eval / pdf / sample — by far the largest — are then dead code and leave the kernel (same results: they would never have run).
+template <int INTEGRATOR, bool PLAIN = false>
 __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderParams &rp, Ray &ray, uint32_t gid, float t, float u, float v,
                                             Pcg32 &rng, V3 &T, V3 &L, float &eta, float &bsdfPdf, uint32_t &flags, ShadowOut &sh,
                                             const float4 *lazyOrigin = nullptr, float *rrProb = nullptr, LightOut *lo = nullptr) {
@@ -268,7 +270,8 @@ __device__ __forceinline__ bool shadeVertex(const DeviceScene &sc, const RenderP
         sh.cast = true; sh.o = its.p; sh.d = ls.wi; sh.maxt = ls.dist - kEpsilon; sh.contrib = mk(c, c, c);
         return false;
     }
-    const Bsdf bsdf = meshBsdf(mesh);
+    Bsdf bsdf = meshBsdf(mesh);
+    if (PLAIN && bsdf.type == kMicrofacet) bsdf.type = kDiffuse; // a no-op under the caller's promise; tells the compiler the type's range
     const V3 wiLocal = its.sh.toLocal(-ray.d);
 
     if (INTEGRATOR == NORI_INT_WHITTED) {                        // LiWhitted
@@ -492,7 +495,7 @@ __device__ __forceinline__ void regenSlot(const DeviceScene &sc, const Pool &poo
 #ifndef NORI_SHADE_THREADS_PER_SM
 #define NORI_SHADE_THREADS_PER_SM 1024      // 64 registers per thread
 #endif
-template <int INTEGRATOR, int NT>
+template <int INTEGRATOR, int NT, bool PLAIN = false>
 __global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeRegen(DeviceScene sc, Pool pool, RenderParams rp, Counters *c) {
     constexpr int NK = kNumKeys + 1, NW = NT / 32;
     static_assert(NK * NW <= 64 && (NW == 8 || NW == 4), "the warp scan below keeps the NK x NW sort counts in two registers per lane");
@@ -613,7 +616,7 @@ __global__ void __launch_bounds__(NT, NORI_SHADE_THREADS_PER_SM / NT) k_shadeReg
         V3 T = mk(th.x, th.y, th.z), L = mk(ra.x, ra.y, ra.z);
         float bsdfPdf = th.w, eta = ra.w;
         uint32_t flags = st.w;
-        const bool cont = shadeVertex<INTEGRATOR>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh, pool.rayO + slot);
+        const bool cont = shadeVertex<INTEGRATOR, PLAIN>(sc, rp, ray, __float_as_uint(h.w), h.x, h.y, h.z, rng, T, L, eta, bsdfPdf, flags, sh, pool.rayO + slot);
         if (cont) {
             pool.rayO[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
             pool.rayD[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
@@ -980,6 +983,12 @@ template <int I> static void launchShade(const DeviceScene &sc, const Pool &pool
     static const bool small = getenv("NORI_GPU_SHADE_NT") && atoi(getenv("NORI_GPU_SHADE_NT")) == 128;   // sweep: profiles/r01_pipeline.md
     if (small) { k_shadeRegen<I, 128><<<pool.capacity / 128, 128, 0, st>>>(sc, pool, rp, c); return; }
 #endif
+    // scenes without microfacet surfaces (the Cornell box of the headline config: diffuse walls, a mirror and a glass sphere): the path
+    // integrators' kernel without the Beckmann code. Same results bit for bit (tests/test_gpu_render.py: test_plain_bsdf_kernel_...).
+    constexpr bool kPath = I == NORI_INT_PATH_MATS || I == NORI_INT_PATH_EMS || I == NORI_INT_PATH_MIS;
+    if constexpr (kPath) {
+        if (sc.plainBsdfs) { k_shadeRegen<I, 256, true><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c); return; }
+    }
     k_shadeRegen<I, 256><<<pool.capacity / 256, 256, 0, st>>>(sc, pool, rp, c);
 }
 

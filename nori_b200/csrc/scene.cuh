@@ -60,6 +60,7 @@ struct DeviceScene {
     float qBase[3], qExt[3];
     const float4 *wnodes;        // 4-wide copy of the tree (NORI_ACCEL_WIDE4) or nullptr: 8 x float4 per node
     int isectMode;               // NORI_ISECT_*: ray-triangle test used by every traversal (0 = the reference's Moeller-Trumbore)
+    int plainBsdfs;              // 1: no mesh has a microfacet BSDF (host-side census of the uploaded meshes): the shade kernel without the Beckmann code is launched
     Camera cam;
     FilterTab filter;
 };

@@ -25,7 +25,7 @@ EXPORTS = [
     "nori_gpu_create", "nori_gpu_destroy", "nori_gpu_last_error", "nori_gpu_device_name",
     "nori_gpu_upload_meshes", "nori_gpu_set_camera", "nori_gpu_set_filter", "nori_gpu_build_accel", "nori_gpu_set_accel_layout",
     "nori_gpu_render", "nori_gpu_download_block", "nori_gpu_download_bitmap", "nori_gpu_download_srgb8", "nori_gpu_upload_block", "nori_gpu_block_device_ptr",
-    "nori_gpu_block_dims", "nori_gpu_reduce_blocks", "nori_gpu_device_count", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_ray_binning", "nori_gpu_set_intersect_mode",
+    "nori_gpu_block_dims", "nori_gpu_reduce_blocks", "nori_gpu_device_count", "nori_gpu_set_profiling", "nori_gpu_set_pool_size", "nori_gpu_set_ray_binning", "nori_gpu_set_plain_bsdf_kernels", "nori_gpu_set_intersect_mode",
     "nori_gpu_trace", "nori_gpu_trace_device", "nori_gpu_trace_count", "nori_gpu_intersect", "nori_gpu_camera_rays",
     "nori_gpu_bsdf_sample", "nori_gpu_bsdf_eval_pdf", "nori_gpu_warp", "nori_gpu_warp_pdf", "nori_gpu_pcg32", "nori_gpu_splat",
     "nori_gpu_sample_radiance", "nori_gpu_trace_static",
@@ -124,6 +124,7 @@ def load_library() -> C.CDLL:
     L.nori_gpu_device_count.argtypes = []
     L.nori_gpu_set_pool_size.argtypes = [vp, C.c_uint32]
     L.nori_gpu_set_ray_binning.argtypes = [vp, C.c_int]
+    L.nori_gpu_set_plain_bsdf_kernels.argtypes = [vp, C.c_int]
     L.nori_gpu_set_intersect_mode.argtypes = [vp, ip]
     L.nori_gpu_trace.argtypes = [vp, vp, ip, ip, vp, vp, vp]
     L.nori_gpu_trace_static.argtypes = [vp, vp, ip, ip, vp, vp, vp]
@@ -278,6 +279,10 @@ class Engine:
     def set_ray_binning(self, on: bool):
         """Counting sort of the path slots by origin cell and direction signs between bounces (default on; never changes an image)."""
         self._ck(self.L.nori_gpu_set_ray_binning(self.h, int(bool(on))))
+
+    def set_plain_bsdf_kernels(self, on: bool):
+        """Scenes without microfacet surfaces use the shade kernel without the Beckmann code (default on; never changes a sample's radiance)."""
+        self._ck(self.L.nori_gpu_set_plain_bsdf_kernels(self.h, int(bool(on))))
 
     def block_dims(self):
         r, c, b = C.c_int(), C.c_int(), C.c_int()

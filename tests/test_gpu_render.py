@@ -148,6 +148,32 @@ def test_ray_binning_never_changes_the_image(gpu_scene, scenes):
         e.set_ray_binning(True); e.set_pool_size(1 << 21)
 
 
+def test_plain_bsdf_kernel_returns_the_same_radiance_bit_for_bit(gpu_scene, scenes):
+    """nori_gpu_set_plain_bsdf_kernels: a scene without microfacet surfaces — the Cornell box: diffuse walls, a mirror and a glass sphere
+    — is shaded by the instance of the path integrators' kernel that carries no Beckmann code. Those branches would never have run: the
+    radiance of every camera sample is the same to the bit with the switch on or off, for all three path integrators; a scene WITH
+    microfacet surfaces (the table) never takes that kernel."""
+    e = gpu_scene("cbox_mis"); s = scenes("cbox_mis")
+    rng = np.random.default_rng(3)
+    pix = rng.integers(0, s.width * s.height, size=40_000).astype(np.uint32); smp = rng.integers(0, 64, size=40_000).astype(np.uint32)
+    try:
+        for integ in (MIS, MATS, EMS):
+            e.set_plain_bsdf_kernels(True); a, _ = e.sample_radiance(pix, smp, integrator=integ)
+            e.set_plain_bsdf_kernels(False); b, _ = e.sample_radiance(pix, smp, integrator=integ)
+            np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+            assert a.sum() > 0
+    finally:
+        e.set_plain_bsdf_kernels(True)
+    t = gpu_scene("table_mis")
+    tp = rng.integers(0, 800 * 600, size=20_000).astype(np.uint32); ts = rng.integers(0, 16, size=20_000).astype(np.uint32)
+    try:
+        t.set_plain_bsdf_kernels(True); a, _ = t.sample_radiance(tp, ts)
+        t.set_plain_bsdf_kernels(False); b, _ = t.sample_radiance(tp, ts)
+        np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+    finally:
+        t.set_plain_bsdf_kernels(True)
+
+
 def test_tiny_pool_many_tiles_splat_outlasts_trace(gpu_scene, scenes):
     """Stream ordering of the overlapped launch: with a 4 096-slot pool over 640 tiles the closest-hit pass takes
     microseconds while the splat of the previous iteration still has whole tiles to go. k_prepare must nevertheless
