@@ -11,7 +11,7 @@ usage = {}
 for m in re.finditer(r"Function (\S+):\s*\n\s*(REG:\d+[^\n]*)", res):
     usage[m.group(1)] = m.group(2)
 WANT = [("k_traceClosestILi9ELb0ELi0", "k_traceClosest<9, false, 0>"), ("k_traceShadowILi10ELb0ELi0", "k_traceShadow<10, false, 0>"),
-        ("k_shadeRegenILi3ELi256", "k_shadeRegen<3, 256>"), ("k_binScatter", "k_binScatter"), ("k_splatPixelILi2ELi256", "k_splatPixel<2, 256>")]
+        ("k_shadeRegenILi3ELi256ELb1", "k_shadeRegen<3, 256, true> (scenes without microfacet surfaces: the Cornell box)"), ("k_shadeRegenILi3ELi256ELb0", "k_shadeRegen<3, 256, false>"), ("k_binScatter", "k_binScatter"), ("k_splatPixelILi2ELi256", "k_splatPixel<2, 256>")]
 funcs = collections.OrderedDict(); cur = None
 for line in sass.splitlines():
     m = re.search(r"Function : (\S+)", line)
