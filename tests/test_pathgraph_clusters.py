@@ -75,6 +75,25 @@ def test_oracle_builder_is_a_partition_with_small_clusters(port):
     assert g_far[-1] == -1 and np.array_equal(g_far[:-1] >= 0, g >= 0)
 
 
+def test_stride_seeds_are_distinct_and_spread():
+    """nori_gpu_pathgraph_stride_seeds (host-only, no GPU): n_seeds DISTINCT vertex indices s * step mod n with step coprime to n near 0.618 n —
+    what the cluster mode of nori_gpu_pathgraph_render seeds BuildClusters with in place of the reference's shuffled list."""
+    import math
+    from nori_b200.gpu import NoriGpuError, pathgraph_stride_seeds
+    for n, m in ((1, 1), (2, 2), (16, 16), (97, 40), (1000, 1000), (1_555_934, 97_246), (2**20, 2**16)):
+        s = pathgraph_stride_seeds(n, m)
+        assert s.shape == (m,) and s.min() >= 0 and s.max() < n and len(np.unique(s)) == m
+        if m > 1:
+            step = int(s[1])
+            assert math.gcd(step, n) == 1 and (n <= 2 or abs(step - 0.618 * n) < 0.05 * n + 2)
+            np.testing.assert_array_equal(s, (np.arange(m, dtype=np.int64) * step) % n)
+    spread = np.sort(pathgraph_stride_seeds(100_000, 1000))
+    assert np.diff(spread).max() < 400                                        # no large stretch of the record order without a seed
+    for bad in ((0, 1), (10, 0), (10, 11)):
+        with pytest.raises(NoriGpuError):
+            pathgraph_stride_seeds(*bad)
+
+
 @pytest.mark.gpu
 def test_gpu_builder_equals_the_oracle(engine, port):
     """nori_gpu_pathgraph_build_clusters == the oracle's builder, integer for integer (cluster of every vertex, member lists, offsets), on
