@@ -353,7 +353,8 @@ int nori_gpu_pathgraph_scatter_direct(nori_gpu_ctx *ctx, const NoriGpuSPoint *po
  *      subClusters, :3236-3310);   3. member lists and offsets (FinalizeCluster, :3312-3332).
  * The reference lists a cluster's members in the order its atomics arrive; here they are listed in index order (stable sorts), one of the
  * orders it can produce, so the result is deterministic. cluster_of: n ints (SPoint::groupIdx as SaveClusters leaves it), clusters: n ints
- * (*n_listed used), offsets: offsets_capacity ints (*n_clusters used; NORI_GPU_EINVAL if more clusters arise — n / K + 2 n_seeds always fits).
+ * (*n_listed used), offsets: offsets_capacity ints (*n_clusters used; NORI_GPU_EINVAL if more clusters arise — 2 n / K + n_seeds + 2 always fits:
+ * a split of clusters with n members in all adds at most n / K of them).
  * points / stride as nori_gpu_pathgraph_knn. */
 int nori_gpu_pathgraph_build_clusters(nori_gpu_ctx *ctx, const void *points, uint64_t stride, int n, const NoriGpuHashParams *hp, const int32_t *seeds,
                                       int n_seeds, int32_t *cluster_of, int32_t *clusters, int32_t *offsets, int offsets_capacity, int *n_clusters,

@@ -419,7 +419,7 @@ class Engine:
         """SPoints::BuildClusters with given seeds (hp.k = members per cluster): (cluster_of (n,), members, offsets, ms)."""
         pts = points if points.dtype == SPOINT_DTYPE else _f32(points, (-1, 3))
         pts = np.ascontiguousarray(pts); n, stride = pts.shape[0], pts.strides[0]
-        sd = np.ascontiguousarray(seeds, np.int32).reshape(-1); cap = n // max(hp.k, 1) + 2 * len(sd) + 2
+        sd = np.ascontiguousarray(seeds, np.int32).reshape(-1); cap = 2 * (n // max(hp.k, 1)) + len(sd) + 4              # two splits add at most n / K clusters each
         of = np.empty(n, np.int32); lists = np.empty(n, np.int32); off = np.empty(cap, np.int32); nc = C.c_int(); nl = C.c_int(); ms = C.c_float()
         self._ck(self.L.nori_gpu_pathgraph_build_clusters(self.h, _p(pts), stride, n, C.byref(hp), _p(sd), len(sd), _p(of), _p(lists), _p(off), cap,
                                                           C.byref(nc), C.byref(nl), C.byref(ms)))

@@ -168,8 +168,8 @@ inline int pgClusterSubdivide(const float *pts, int n, int32_t *groupIdx, const 
     return first[nClusters];
 }
 
-/// BuildClusters with index-ordered lists. lists: n ints, offsets: room for the final number of clusters (<= n / K + 2 * nSeeds + n / K ...:
-/// pass n + nSeeds). Returns the number of clusters; *nListed = members listed (vertices with groupIdx != -1).
+/// BuildClusters with index-ordered lists. lists: n ints, offsets: room for the final number of clusters (<= 2 n / K + nSeeds: every split adds
+/// at most n / K; n + nSeeds is always enough for K >= 2). Returns the number of clusters; *nListed = members listed (vertices with groupIdx != -1).
 inline int pathgraphBuildClusters(const float *pts, int n, const HashParams &h, const int32_t *seeds, int nSeeds, int K, int32_t *groupIdx,
                                   int32_t *lists, int32_t *offsets, int *nListed) {
     pgClusterAssign(pts, n, h, seeds, nSeeds, groupIdx);
